@@ -1,0 +1,10 @@
+"""bsarec_b200 — B200-native (sm_100a) drop-in for BSARec's training / full-ranking-eval hot path.
+
+``MODEL_DICT["bsarec"]`` mirrors ``src/model/__init__.py:10-11`` of the reference.
+"""
+from .model import BSARecModel
+from .trainer import Trainer
+
+MODEL_DICT = {"bsarec": BSARecModel}
+
+__all__ = ["BSARecModel", "Trainer", "MODEL_DICT"]

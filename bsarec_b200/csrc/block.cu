@@ -1,0 +1,268 @@
+// bsa_block_fwd / bsa_block_bwd: one BSARecBlock (model/bsarec.py:62-104, model/_modules.py:61-140).
+#include "../../include/bsarec_b200.h"
+#include "common.cuh"
+#include "gemm_simt.cuh"
+#include "rowwise.cuh"
+
+#include <cmath>
+
+namespace bsa {
+
+namespace {
+
+struct Bump {               // bump allocator over caller-provided memory, 256-byte aligned
+    char* base; size_t off = 0, cap;
+    Bump(void* p, size_t bytes) : base((char*)p), cap(bytes) {}
+    float* f(long long n) {
+        size_t bytes = ((size_t)n * sizeof(float) + 255) / 256 * 256;
+        float* r = (float*)(base + off);
+        off += bytes;
+        return r;
+    }
+    bool ok() const { return off <= cap; }
+};
+
+struct Saved {              // layout of the per-layer saved-activation buffer
+    float *z_f, *mean_f, *rstd_f, *q, *k, *v, *P, *ctx, *z_a, *mean_a, *rstd_a, *y, *h_pre, *h_act, *z_o, *mean_o,
+        *rstd_o;
+    size_t bytes;
+};
+
+Saved carve_saved(void* p, const bsa_block_desc& c) {
+    const long long M = (long long)c.B * c.L, d = c.d;
+    Bump b(p, ~(size_t)0);
+    Saved s;
+    s.z_f = b.f(M * d); s.mean_f = b.f(M); s.rstd_f = b.f(M);
+    s.q = b.f(M * d); s.k = b.f(M * d); s.v = b.f(M * d);
+    s.P = b.f((long long)c.B * c.H * c.L * c.L);
+    s.ctx = b.f(M * d);
+    s.z_a = b.f(M * d); s.mean_a = b.f(M); s.rstd_a = b.f(M);
+    s.y = b.f(M * d);
+    s.h_pre = b.f(M * 4 * d); s.h_act = b.f(M * 4 * d);
+    s.z_o = b.f(M * d); s.mean_o = b.f(M); s.rstd_o = b.f(M);
+    s.bytes = b.off;
+    return s;
+}
+
+// floats of split-K scratch that covers every weight-gradient GEMM of the block
+long long splitk_floats(long long M, long long d) {
+    long long a = (long long)choose_splitk((int)(4 * d), (int)d, (int)M) * 4 * d * d;
+    long long b = (long long)choose_splitk((int)d, (int)(4 * d), (int)M) * 4 * d * d;
+    long long c = (long long)choose_splitk((int)d, (int)d, (int)M) * d * d;
+    long long m = a > b ? a : b;
+    return (m > c ? m : c) + 1024;
+}
+
+size_t workspace_bytes(const bsa_block_desc& c) {
+    const long long M = (long long)c.B * c.L, d = c.d;
+    const long long PL = (long long)c.B * c.H * c.L * c.L;
+    Bump b(nullptr, ~(size_t)0);
+    // backward is the larger user: dyb, dd, dzf, dq, dk, dv, dctx [M,d]; dh [M,4d]; Pd, dP [B,H,L,L]
+    for (int i = 0; i < 7; ++i) b.f(M * d);
+    b.f(M * 4 * d);
+    b.f(PL); b.f(PL);
+    // partials: LN gamma/beta, column sums, split-K, beta2
+    b.f(2ll * rowwise_partial_blocks(M) * d);
+    b.f((long long)colsum_partial_rows(M) * 4 * d);
+    b.f(splitk_floats(M, d));
+    b.f((long long)c.B * d);
+    return b.off + 4096;
+}
+
+// x [M, K] @ W[N, K]^T + bias -> out [M, N]      (nn.Linear forward)
+int linear_fwd(const float* x, const float* W, const float* bias, float* out, long long M, int N, int K, int act,
+               float* aux_out, cudaStream_t st) {
+    GemmP p;
+    p.A = x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
+    p.bias = bias; p.act = act; p.aux_out = aux_out;
+    return launch_gemm(p, st);
+}
+
+// dx [M, K] (+)= dy [M, N] @ W[N, K]              (nn.Linear input gradient)
+int linear_bwd_input(const float* dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
+                     const float* aux_in, cudaStream_t st) {
+    GemmP p;
+    p.A = dy; p.B = W; p.C = dx; p.M = (int)M; p.N = K; p.K = N; p.lda = N; p.ldb = K; p.ldc = K;
+    p.b_kmajor = false; p.accumulate = accumulate; p.act = act; p.aux_in = aux_in;
+    return launch_gemm(p, st);
+}
+
+// dW [N, K] = dy[M, N]^T @ x [M, K] ; db [N] = colsum(dy)   (deterministic split-K + column sums)
+int linear_bwd_weight(const float* dy, const float* x, float* dW, float* db, long long M, int N, int K, float* part_sk,
+                      float* part_cs, cudaStream_t st) {
+    GemmP p;
+    p.A = dy; p.B = x; p.C = dW; p.M = N; p.N = K; p.K = (int)M; p.lda = N; p.ldb = K; p.ldc = K;
+    p.a_kmajor = false; p.b_kmajor = false;
+    p.splitk = choose_splitk(N, K, (int)M);
+    if (p.splitk > 1) p.partial = part_sk;
+    int rc = launch_gemm(p, st);
+    if (rc) return rc;
+    return colsum(dy, M, N, part_cs, db, 0, st);
+}
+
+}  // namespace
+
+int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+              const float* x, float* x_out, void* saved_p, void* ws, size_t ws_bytes, cudaStream_t st) {
+    const int B = c.B, L = c.L, d = c.d, H = c.H, dh = d / H;
+    const long long M = (long long)B * L, PL = (long long)B * H * L * L;
+    BSA_REQUIRE(H > 0 && d % H == 0, "hidden size (%d) is not a multiple of the number of attention heads (%d)", d, H);
+    BSA_REQUIRE(d % 4 == 0 && d <= 1024 && L <= 1024, "unsupported shape: d=%d (need d%%4==0, <=1024), L=%d (<=1024)", d, L);
+    BSA_REQUIRE((long long)B * H <= 65535, "batch*heads = %lld exceeds 65535 per call; split the batch", (long long)B * H);
+    if (M == 0) return 0;
+    Saved s = carve_saved(saved_p, c);
+    Bump b(ws, ws_bytes);
+    float* dsp = b.f(M * d);
+    float* tmp = b.f(M * d);
+    const Dropout dr_f = make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training);
+    const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
+    const Dropout dr_a = make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training);
+    const Dropout dr_o = make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training);
+    float* Pd = dr_p.thr ? b.f(PL) : s.P;
+    BSA_REQUIRE(b.ok(), "bsa_block_fwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
+    const int r = filter_rank(L, c.kept_bins);
+    int rc;
+    // filter branch
+    if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, s.z_f, s.mean_f, s.rstd_f, B, L, d, r, dr_f, st))) return rc;
+    // attention branch
+    if ((rc = linear_fwd(x, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(x, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(x, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    {   // scores = q k^T / sqrt(dh)   -> written where P will live
+        GemmP p;
+        p.A = s.q; p.B = s.k; p.C = s.P; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
+        p.batch = B * H; p.inner = H;
+        p.sAo = (long long)L * d; p.sAi = dh; p.sBo = (long long)L * d; p.sBi = dh;
+        p.sCo = (long long)H * L * L; p.sCi = (long long)L * L;
+        p.alpha = 1.0f / sqrtf((float)dh);
+        if ((rc = launch_gemm(p, st))) return rc;
+    }
+    if ((rc = softmax_mask_dropout_fwd(s.P, ids, s.P, Pd, B, H, L, dr_p, st))) return rc;
+    {   // ctx = Pd v
+        GemmP p;
+        p.A = Pd; p.B = s.v; p.C = s.ctx; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+        p.b_kmajor = false; p.batch = B * H; p.inner = H;
+        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+        p.sCo = (long long)L * d; p.sCi = dh;
+        if ((rc = launch_gemm(p, st))) return rc;
+    }
+    if ((rc = linear_fwd(s.ctx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
+    if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, s.z_a, s.mean_a, s.rstd_a, dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
+    // feed-forward
+    if ((rc = linear_fwd(s.y, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, st))) return rc;
+    if ((rc = linear_fwd(s.h_act, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, M, d, dr_o, st))) return rc;
+    return 0;
+}
+
+int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+              const float* x, const void* saved_p, const float* g_out, float* dx, const bsa_block_grads& g, void* ws,
+              size_t ws_bytes, cudaStream_t st) {
+    (void)ids;
+    const int B = c.B, L = c.L, d = c.d, H = c.H, dh = d / H;
+    const long long M = (long long)B * L, PL = (long long)B * H * L * L;
+    BSA_REQUIRE(H > 0 && d % H == 0 && d % 4 == 0, "bsa_block_bwd: bad shape");
+    if (M == 0) return 0;
+    Saved s = carve_saved(const_cast<void*>(saved_p), c);
+    Bump b(ws, ws_bytes);
+    float* dyb = b.f(M * d);
+    float* dd = b.f(M * d);
+    float* dzf = b.f(M * d);
+    float* dq = b.f(M * d);
+    float* dk = b.f(M * d);
+    float* dv = b.f(M * d);
+    float* dctx = b.f(M * d);
+    float* dh_ = b.f(M * 4 * d);
+    float* Pd_ws = b.f(PL);
+    float* dP = b.f(PL);
+    const int nrb = rowwise_partial_blocks(M);
+    float* pgam = b.f((long long)nrb * d);
+    float* pbet = b.f((long long)nrb * d);
+    float* part_cs = b.f((long long)colsum_partial_rows(M) * 4 * d);
+    float* part_sk = b.f(splitk_floats(M, d));
+    float* pbeta2 = b.f((long long)B * d);
+    BSA_REQUIRE(b.ok(), "bsa_block_bwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
+    const Dropout dr_f = make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training);
+    const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
+    const Dropout dr_a = make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training);
+    const Dropout dr_o = make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training);
+    const int r = filter_rank(L, c.kept_bins);
+    const float inv_sqrt_dh = 1.0f / sqrtf((float)dh);
+    int rc, nblk = 0;
+
+    // ---- feed-forward: x_out = LN(drop(tmp2) + y)
+    if ((rc = ln_bwd(g_out, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_o, st))) return rc;
+    if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
+    const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
+    if ((rc = linear_bwd_weight(t2, s.h_act, g.w2, g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(t2, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, st))) return rc;
+    if ((rc = linear_bwd_weight(dh_, s.y, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(dh_, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, st))) return rc;   // dyb = dL/dy
+
+    // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
+    if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_a, st))) return rc;
+    if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
+    const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
+    if ((rc = linear_bwd_weight(t1, s.ctx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(t1, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, st))) return rc;
+    const float* Pd = s.P;
+    if (dr_p.thr) {
+        if ((rc = apply_dropout(s.P, Pd_ws, PL, dr_p, st))) return rc;
+        Pd = Pd_ws;
+    }
+    {   // dv[j,:] = sum_i Pd[i,j] dctx[i,:]
+        GemmP p;
+        p.A = Pd; p.B = dctx; p.C = dv; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+        p.a_kmajor = false; p.b_kmajor = false; p.batch = B * H; p.inner = H;
+        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+        p.sCo = (long long)L * d; p.sCi = dh;
+        if ((rc = launch_gemm(p, st))) return rc;
+    }
+    {   // dPd[i,j] = dctx[i,:] . v[j,:]
+        GemmP p;
+        p.A = dctx; p.B = s.v; p.C = dP; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
+        p.batch = B * H; p.inner = H;
+        p.sAo = (long long)L * d; p.sAi = dh; p.sBo = (long long)L * d; p.sBi = dh;
+        p.sCo = (long long)H * L * L; p.sCi = (long long)L * L;
+        if ((rc = launch_gemm(p, st))) return rc;
+    }
+    if ((rc = softmax_bwd(s.P, dP, B, H, L, dr_p, st))) return rc;            // dP now holds dS
+    {   // dq = dS k / sqrt(dh)
+        GemmP p;
+        p.A = dP; p.B = s.k; p.C = dq; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+        p.b_kmajor = false; p.batch = B * H; p.inner = H; p.alpha = inv_sqrt_dh;
+        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+        p.sCo = (long long)L * d; p.sCi = dh;
+        if ((rc = launch_gemm(p, st))) return rc;
+    }
+    {   // dk = dS^T q / sqrt(dh)
+        GemmP p;
+        p.A = dP; p.B = s.q; p.C = dk; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+        p.a_kmajor = false; p.b_kmajor = false; p.batch = B * H; p.inner = H; p.alpha = inv_sqrt_dh;
+        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+        p.sCo = (long long)L * d; p.sCi = dh;
+        if ((rc = launch_gemm(p, st))) return rc;
+    }
+    if ((rc = linear_bwd_weight(dq, x, g.wq, g.bq, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(dk, x, g.wk, g.bk, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(dv, x, g.wv, g.bv, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(dq, w.wq, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_bwd_input(dk, w.wk, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_bwd_input(dv, w.wv, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+
+    // ---- filter branch: dsp = LN(drop(u) + x), weight alpha
+    if ((rc = ln_bwd(dyb, c.alpha, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, nullptr, pgam, pbet, &nblk, M, d, dr_f, st))) return rc;
+    if ((rc = reduce_partials(pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = filter_bwd(x, basis, w.sqrt_beta, dzf, dx, pbeta2, B, L, d, r, dr_f, st))) return rc;
+    if ((rc = reduce_partials(pbeta2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
+    return 0;
+}
+
+size_t block_saved_bytes(const bsa_block_desc& c) { return carve_saved(nullptr, c).bytes + 256; }
+size_t block_workspace_bytes(const bsa_block_desc& c) { return workspace_bytes(c); }
+
+}  // namespace bsa

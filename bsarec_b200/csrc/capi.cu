@@ -1,0 +1,201 @@
+// extern "C" surface declared in include/bsarec_b200.h.  Argument checking and workspace carving only;
+// the kernels live in the other translation units.
+#include "../../include/bsarec_b200.h"
+#include "common.cuh"
+#include "rowwise.cuh"
+#include "ce_topk.cuh"
+#include "umma_engine.cuh"
+
+#include <cstdarg>
+
+namespace bsa {
+
+static thread_local char g_err[1024] = "";
+unsigned long long g_launch_count = 0;
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+              const float* x, float* x_out, void* saved_p, void* ws, size_t ws_bytes, cudaStream_t st);
+int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+              const float* x, const void* saved_p, const float* g_out, float* dx, const bsa_block_grads& g, void* ws,
+              size_t ws_bytes, cudaStream_t st);
+size_t block_saved_bytes(const bsa_block_desc& c);
+size_t block_workspace_bytes(const bsa_block_desc& c);
+
+static inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
+
+}  // namespace bsa
+
+using namespace bsa;
+
+extern "C" {
+
+int bsa_abi_version(void) { return BSA_ABI_VERSION; }
+const char* bsa_last_error_string(void) { return g_err; }
+unsigned long long bsa_launch_count(void) { return g_launch_count; }
+
+// ------------------------------------------------------------------------------------------ embedding
+int bsa_embed_ln_dropout_fwd(const bsa_embed_desc* c, const int64_t* ids, const float* item_emb, const float* pos_emb,
+                             const float* ln_w, const float* ln_b, float* out, float* mean, float* rstd, void* stream) {
+    BSA_REQUIRE(c && ids && item_emb && pos_emb && ln_w && ln_b && out && mean && rstd, "bsa_embed_ln_dropout_fwd: null argument");
+    BSA_REQUIRE(c->d % 4 == 0, "hidden size must be a multiple of 4 (got %d)", c->d);
+    return embed_ln_dropout_fwd((const long long*)ids, item_emb, pos_emb, ln_w, ln_b, out, mean, rstd, c->B, c->L, c->d,
+                                c->item_size, make_dropout(c->seed, 0, c->p_hidden, c->training), (cudaStream_t)stream);
+}
+
+size_t bsa_embed_bwd_workspace_bytes(const bsa_embed_desc* c) {
+    const long long M = (long long)c->B * c->L;
+    return al((size_t)M * c->d * sizeof(float)) + 2 * al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float)) +
+           al(scatter_plan_bytes(M)) + 1024;
+}
+
+int bsa_embed_ln_dropout_bwd(const bsa_embed_desc* c, const int64_t* ids, const float* item_emb, const float* pos_emb,
+                             const float* ln_w, const float* mean, const float* rstd, const float* d_out,
+                             float* d_item_emb, float* d_pos_emb, float* d_ln_w, float* d_ln_b, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && ids && item_emb && pos_emb && ln_w && mean && rstd && d_out && d_item_emb && d_pos_emb && d_ln_w && d_ln_b && workspace,
+                "bsa_embed_ln_dropout_bwd: null argument");
+    BSA_REQUIRE(workspace_bytes >= bsa_embed_bwd_workspace_bytes(c), "bsa_embed_ln_dropout_bwd: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long M = (long long)c->B * c->L;
+    if (M == 0) return 0;
+    char* p = (char*)workspace;
+    float* dz = (float*)p; p += al((size_t)M * c->d * sizeof(float));
+    const size_t pb = al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float));
+    float* pg = (float*)p; p += pb;
+    float* pbt = (float*)p; p += pb;
+    void* plan = p;
+    const size_t plan_bytes = al(scatter_plan_bytes(M));
+    int nblk = 0, rc;
+    if ((rc = embed_ln_dropout_bwd(d_out, (const long long*)ids, item_emb, pos_emb, ln_w, mean, rstd, dz, pg, pbt, &nblk,
+                                   c->B, c->L, c->d, make_dropout(c->seed, 0, c->p_hidden, c->training), st))) return rc;
+    if ((rc = reduce_partials(pg, nblk, c->d, d_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbt, nblk, c->d, d_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = pos_grad(dz, d_pos_emb, c->B, c->L, c->d, 0, st))) return rc;
+    if ((rc = scatter_plan((const long long*)ids, M, c->item_size, plan, plan_bytes, st))) return rc;
+    return scatter_add_rows(plan, M, dz, d_item_emb, c->d, st);
+}
+
+size_t bsa_sort_scatter_plan_bytes(int64_t n) { return al(scatter_plan_bytes(n)); }
+
+int bsa_sort_scatter_plan(const int64_t* ids, int64_t n, int64_t item_size, void* plan, size_t plan_bytes,
+                          int32_t* sorted_ids, int32_t* sorted_rows, void* stream) {
+    BSA_REQUIRE(ids && plan, "bsa_sort_scatter_plan: null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = scatter_plan((const long long*)ids, n, item_size, plan, plan_bytes, st);
+    if (rc || n == 0) return rc;
+    const size_t arr = al((size_t)n * sizeof(int));
+    if (sorted_ids) BSA_CHECK_CUDA(cudaMemcpyAsync(sorted_ids, (char*)plan + 2 * arr, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    if (sorted_rows) BSA_CHECK_CUDA(cudaMemcpyAsync(sorted_rows, (char*)plan + 3 * arr, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------ block
+int bsa_filter_rank(int L, int kept_bins) { return filter_rank(L, kept_bins); }
+
+int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream) {
+    BSA_REQUIRE(basis && L >= 1 && kept_bins >= 1, "bsa_build_filter_basis: bad argument");
+    return build_filter_basis(basis, L, kept_bins, nullptr, (cudaStream_t)stream);
+}
+
+size_t bsa_block_saved_bytes(const bsa_block_desc* c) { return block_saved_bytes(*c); }
+size_t bsa_block_workspace_bytes(const bsa_block_desc* c) { return block_workspace_bytes(*c); }
+
+int bsa_block_fwd(const bsa_block_desc* c, const bsa_block_weights* w, const float* basis, const int64_t* ids,
+                  const float* x_in, float* x_out, void* saved, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && w && basis && ids && x_in && x_out && saved && workspace, "bsa_block_fwd: null argument");
+    return block_fwd(*c, *w, basis, (const long long*)ids, x_in, x_out, saved, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int bsa_block_bwd(const bsa_block_desc* c, const bsa_block_weights* w, const float* basis, const int64_t* ids,
+                  const float* x_in, const void* saved, const float* d_x_out, float* d_x_in, const bsa_block_grads* g,
+                  void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && w && basis && ids && x_in && saved && d_x_out && d_x_in && g && workspace, "bsa_block_bwd: null argument");
+    return block_bwd(*c, *w, basis, (const long long*)ids, x_in, saved, d_x_out, d_x_in, *g, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------ cross-entropy
+static int ce_impl(const bsa_ce_desc* c) {
+    if (c->impl == 1 || c->impl == 2) return c->impl;
+    return umma_ce_supported(c->B, c->d, c->item_size) ? 2 : 1;
+}
+
+size_t bsa_ce_workspace_bytes(const bsa_ce_desc* c) {
+    size_t a = ce_simt_workspace_bytes(c->B, c->item_size);
+    size_t b = umma_ce_workspace_bytes(c->B, c->d, c->item_size);
+    return a > b ? a : b;
+}
+
+int bsa_ce_fwd(const bsa_ce_desc* c, const float* seq_out, const float* item_emb, const int64_t* answers, float* loss,
+               float* lse, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && seq_out && item_emb && answers && loss && lse && workspace, "bsa_ce_fwd: null argument");
+    BSA_REQUIRE(c->B > 0 && c->item_size > 0, "bsa_ce_fwd: empty batch or catalog");
+    if (ce_impl(c) == 2) {
+        BSA_REQUIRE(umma_ce_supported(c->B, c->d, c->item_size), "bsa_ce_fwd: tcgen05 path does not support B=%d d=%d", c->B, c->d);
+        return umma_ce_fwd(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, loss, lse, workspace, workspace_bytes, (cudaStream_t)stream);
+    }
+    return ce_fwd_simt(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, loss, lse, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int bsa_ce_bwd(const bsa_ce_desc* c, const float* seq_out, const float* item_emb, const int64_t* answers, const float* lse,
+               const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && seq_out && item_emb && answers && lse && d_loss && d_seq_out && d_item_emb && workspace, "bsa_ce_bwd: null argument");
+    if (ce_impl(c) == 2) {
+        BSA_REQUIRE(umma_ce_supported(c->B, c->d, c->item_size), "bsa_ce_bwd: tcgen05 path does not support B=%d d=%d", c->B, c->d);
+        return umma_ce_bwd(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, lse, d_loss, d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
+    }
+    return ce_bwd_simt(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, lse, d_loss, d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------ scoring / top-k
+static int topk_impl(const bsa_topk_desc* c) {
+    if (c->impl == 1 || c->impl == 2) return c->impl;
+    return umma_topk_supported(c->B, c->d, c->k, c->shard_rows) ? 2 : 1;
+}
+
+size_t bsa_score_topk_workspace_bytes(const bsa_topk_desc* c) {
+    size_t a = topk_simt_workspace_bytes(c->B, c->shard_rows);
+    size_t b = umma_topk_workspace_bytes(c->B, c->d, c->k, c->shard_rows);
+    return a > b ? a : b;
+}
+
+int bsa_score_topk(const bsa_topk_desc* c, const float* seq_out, const float* item_shard, const int64_t* hist_indptr,
+                   const int64_t* hist_indices, float* top_val, int64_t* top_idx, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+    BSA_REQUIRE(c && seq_out && item_shard && top_val && top_idx && workspace, "bsa_score_topk: null argument");
+    BSA_REQUIRE((hist_indptr == nullptr) == (hist_indices == nullptr) || hist_indptr, "bsa_score_topk: hist_indices without hist_indptr");
+    if (c->B == 0) return 0;
+    if (topk_impl(c) == 2) {
+        BSA_REQUIRE(umma_topk_supported(c->B, c->d, c->k, c->shard_rows), "bsa_score_topk: tcgen05 path does not support this shape");
+        return umma_score_topk(c->B, c->d, c->k, c->shard_rows, c->shard_offset, seq_out, item_shard, (const long long*)hist_indptr,
+                               (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, (cudaStream_t)stream);
+    }
+    return score_topk_simt(c->B, c->d, c->k, c->shard_rows, c->shard_offset, seq_out, item_shard, (const long long*)hist_indptr,
+                           (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int bsa_topk_merge(const float* cand_val, const int64_t* cand_idx, int G, int B, int k, float* top_val, int64_t* top_idx, void* stream) {
+    BSA_REQUIRE(cand_val && cand_idx && top_val && top_idx, "bsa_topk_merge: null argument");
+    return topk_merge(cand_val, (const long long*)cand_idx, G, B, k, top_val, (long long*)top_idx, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------ utilities
+int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* stream) {
+    BSA_REQUIRE(src && dst, "bsa_gather_last: null argument");
+    if (B == 0) return 0;
+    return gather_last_rows(src, dst, B, L, d, (cudaStream_t)stream);
+}
+
+int bsa_scatter_last(const float* src, float* dst, int B, int L, int d, void* stream) {
+    BSA_REQUIRE(src && dst, "bsa_scatter_last: null argument");
+    if (B == 0) return 0;
+    return scatter_last_rows(src, dst, B, L, d, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,99 @@
+// Shared device/host helpers for the bsarec_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+
+namespace bsa {
+
+// ---------------------------------------------------------------------------- errors / counters
+// Every C-ABI export returns int (0 = ok); the message is kept per thread and read back with
+// bsa_last_error_string() (SURVEY.md §8b "Errors").
+void set_error(const char* fmt, ...);
+extern unsigned long long g_launch_count;      // kernels launched by this library (bench.py "gpu_launches")
+
+#define BSA_CHECK_CUDA(expr)                                                                   \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            bsa::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return (int)_e;                                                                    \
+        }                                                                                      \
+    } while (0)
+
+#define BSA_REQUIRE(cond, ...)                 \
+    do {                                       \
+        if (!(cond)) {                         \
+            bsa::set_error(__VA_ARGS__);       \
+            return -1;                         \
+        }                                      \
+    } while (0)
+
+#define BSA_LAUNCH_CHECK()                     \
+    do {                                       \
+        ++bsa::g_launch_count;                 \
+        BSA_CHECK_CUDA(cudaPeekAtLastError()); \
+    } while (0)
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ---------------------------------------------------------------------------- dropout RNG
+// Stateless counter RNG, restated bit-for-bit in oracle/rng_ref.py.
+struct Dropout {
+    unsigned long long key;   // site key
+    unsigned int thr;         // keep iff r16 >= thr ; thr == 0 -> dropout off
+    float scale;              // 1/(1-p)
+};
+
+__host__ __device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+static inline Dropout make_dropout(unsigned long long seed, int site, float p, int training) {
+    Dropout d;
+    d.key = splitmix64(seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(site + 1));
+    d.thr = (training && p > 0.f) ? (unsigned int)(p * 65536.0f + 0.5f) : 0u;
+    d.scale = (d.thr ? 1.0f / (1.0f - p) : 1.0f);
+    return d;
+}
+
+// multiplier (0 or scale) for linear element index i
+__device__ __forceinline__ float dropout_mult(const Dropout& dr, unsigned long long i) {
+    if (dr.thr == 0u) return 1.0f;
+    unsigned long long w = splitmix64(dr.key + (i >> 2));
+    unsigned int r16 = (unsigned int)(w >> (16 * (unsigned int)(i & 3ull))) & 0xFFFFu;
+    return r16 >= dr.thr ? dr.scale : 0.0f;
+}
+
+// four consecutive elements starting at i (i % 4 == 0): one hash for all four
+__device__ __forceinline__ void dropout_mult4(const Dropout& dr, unsigned long long i, float m[4]) {
+    if (dr.thr == 0u) { m[0] = m[1] = m[2] = m[3] = 1.0f; return; }
+    unsigned long long w = splitmix64(dr.key + (i >> 2));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) m[j] = (((unsigned int)(w >> (16 * j)) & 0xFFFFu) >= dr.thr) ? dr.scale : 0.0f;
+}
+
+// ---------------------------------------------------------------------------- reductions
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ float gelu_erf(float x) { return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
+    return cdf + x * pdf;
+}
+
+}  // namespace bsa

@@ -1,0 +1,202 @@
+// fp32 FFMA GEMM: 128 x BN x 16 tiles, 256 threads, (2x4) x (CGx4) register tile per thread,
+// register-staged double buffering.  See gemm_simt.cuh for the operand conventions.
+#include "gemm_simt.cuh"
+
+namespace bsa {
+
+namespace {
+
+template <int BN, bool AK, bool BKM>
+__global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
+    constexpr int BM = 128, BK = 16, LDSA = BM + 4, LDSB = BN + 4;
+    constexpr int CG = BN / 64;            // column groups of 4 per thread
+    constexpr int NBL = BN / 16;           // B elements loaded per thread per k-tile
+    __shared__ __align__(16) float As[2][BK][LDSA];
+    __shared__ __align__(16) float Bs[2][BK][LDSB];
+
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    int z = blockIdx.z, split = 0;
+    if (p.splitk > 1) { split = z; z = 0; }
+    const int zo = z / p.inner, zi = z - zo * p.inner;
+    const float* __restrict__ A = p.A + zo * p.sAo + zi * p.sAi;
+    const float* __restrict__ B = p.B + zo * p.sBo + zi * p.sBi;
+
+    int kbeg = 0, kend = p.K;
+    if (p.splitk > 1) {
+        int kc = ((p.K + p.splitk - 1) / p.splitk + BK - 1) / BK * BK;
+        kbeg = split * kc;
+        kend = min(p.K, kbeg + kc);
+    }
+
+    float acc[8][CG * 4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < CG * 4; ++j) acc[i][j] = 0.f;
+
+    float ra[8], rb[NBL];
+
+    auto load_tiles = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            int m, k;
+            if (AK) { k = tid & 15; m = (tid >> 4) + 16 * i; }
+            else    { m = tid & 127; k = (tid >> 7) + 2 * i; }
+            const int gm = m0 + m, gk = k0 + k;
+            float v = 0.f;
+            if (gm < p.M && gk < kend)
+                v = AK ? __ldg(A + (long long)gm * p.lda + gk) : __ldg(A + (long long)gk * p.lda + gm);
+            ra[i] = v;
+        }
+#pragma unroll
+        for (int i = 0; i < NBL; ++i) {
+            int n, k;
+            if (BKM) { k = tid & 15; n = (tid >> 4) + 16 * i; }
+            else     { n = tid % BN; k = tid / BN + (256 / BN) * i; }
+            const int gn = n0 + n, gk = k0 + k;
+            float v = 0.f;
+            if (gn < p.N && gk < kend)
+                v = BKM ? __ldg(B + (long long)gn * p.ldb + gk) : __ldg(B + (long long)gk * p.ldb + gn);
+            rb[i] = v;
+        }
+    };
+    auto store_tiles = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            int m, k;
+            if (AK) { k = tid & 15; m = (tid >> 4) + 16 * i; }
+            else    { m = tid & 127; k = (tid >> 7) + 2 * i; }
+            As[buf][k][m] = ra[i];
+        }
+#pragma unroll
+        for (int i = 0; i < NBL; ++i) {
+            int n, k;
+            if (BKM) { k = tid & 15; n = (tid >> 4) + 16 * i; }
+            else     { n = tid % BN; k = tid / BN + (256 / BN) * i; }
+            Bs[buf][k][n] = rb[i];
+        }
+    };
+
+    const int ntiles = (kend > kbeg) ? (kend - kbeg + BK - 1) / BK : 0;
+    if (ntiles > 0) {
+        load_tiles(kbeg);
+        store_tiles(0);
+    }
+    __syncthreads();
+    for (int t = 0; t < ntiles; ++t) {
+        const int buf = t & 1;
+        if (t + 1 < ntiles) load_tiles(kbeg + (t + 1) * BK);
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            float a[8], b[CG * 4];
+            const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
+            a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
+            a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+#pragma unroll
+            for (int g = 0; g < CG; ++g) {
+                const float4 bv = *reinterpret_cast<const float4*>(&Bs[buf][k][g * 64 + tx * 4]);
+                b[g * 4 + 0] = bv.x; b[g * 4 + 1] = bv.y; b[g * 4 + 2] = bv.z; b[g * 4 + 3] = bv.w;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < CG * 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        if (t + 1 < ntiles) store_tiles(buf ^ 1);
+        __syncthreads();
+    }
+
+    // ------------------------------------------------------------------ epilogue
+    if (p.splitk > 1) {
+        float* __restrict__ part = p.partial + (long long)split * p.M * p.N;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+            if (gm >= p.M) continue;
+#pragma unroll
+            for (int j = 0; j < CG * 4; ++j) {
+                const int gn = n0 + (j >> 2) * 64 + tx * 4 + (j & 3);
+                if (gn < p.N) part[(long long)gm * p.N + gn] = acc[i][j];
+            }
+        }
+        return;
+    }
+    float* __restrict__ C = p.C + zo * p.sCo + zi * p.sCi;
+    float* __restrict__ auxo = p.aux_out ? p.aux_out + zo * p.sCo + zi * p.sCi : nullptr;
+    const float* __restrict__ auxi = p.aux_in ? p.aux_in + zo * p.sCo + zi * p.sCi : nullptr;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        if (gm >= p.M) continue;
+#pragma unroll
+        for (int j = 0; j < CG * 4; ++j) {
+            const int gn = n0 + (j >> 2) * 64 + tx * 4 + (j & 3);
+            if (gn >= p.N) continue;
+            const long long off = (long long)gm * p.ldc + gn;
+            float v = p.alpha * acc[i][j];
+            if (p.bias) v += __ldg(p.bias + gn);
+            if (p.act == ACT_GELU_SAVE_PRE) { auxo[off] = v; v = gelu_erf(v); }
+            else if (p.act == ACT_MUL_GELU_GRAD) v *= gelu_erf_grad(auxi[off]);
+            if (p.accumulate) v += C[off];
+            C[off] = v;
+        }
+    }
+}
+
+__global__ void splitk_reduce_kernel(const float* __restrict__ part, float* __restrict__ C, long long MN, int N,
+                                     int ldc, int splitk, float alpha, int accumulate) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= MN) return;
+    float s = 0.f;
+    for (int k = 0; k < splitk; ++k) s += part[(long long)k * MN + i];   // fixed order
+    const long long m = i / N, n = i - m * N;
+    const long long off = m * ldc + n;
+    float v = alpha * s;
+    if (accumulate) v += C[off];
+    C[off] = v;
+}
+
+template <int BN>
+int dispatch(const GemmP& p, dim3 grid, cudaStream_t st) {
+    if (p.a_kmajor && p.b_kmajor) gemm_kernel<BN, true, true><<<grid, 256, 0, st>>>(p);
+    else if (p.a_kmajor && !p.b_kmajor) gemm_kernel<BN, true, false><<<grid, 256, 0, st>>>(p);
+    else if (!p.a_kmajor && p.b_kmajor) gemm_kernel<BN, false, true><<<grid, 256, 0, st>>>(p);
+    else gemm_kernel<BN, false, false><<<grid, 256, 0, st>>>(p);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+
+int choose_splitk(int M, int N, int K) {
+    const int tiles = cdiv(M, 128) * cdiv(N, N <= 64 ? 64 : 128);
+    int s = (148 * 2 + tiles - 1) / tiles;
+    const int maxs = (K + 255) / 256;      // at least 256 of K per split
+    if (s > maxs) s = maxs;
+    if (s < 1) s = 1;
+    if (s > 512) s = 512;
+    return s;
+}
+
+int launch_gemm(const GemmP& p, cudaStream_t st) {
+    if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return 0;
+    BSA_REQUIRE(p.splitk >= 1 && (p.splitk == 1 || (p.batch == 1 && p.partial && !p.bias && p.act == ACT_NONE)),
+                "launch_gemm: invalid split-K configuration");
+    BSA_REQUIRE(p.inner >= 1 && p.batch % p.inner == 0, "launch_gemm: batch %% inner != 0");
+    const int BN = p.N <= 64 ? 64 : 128;
+    dim3 grid(cdiv(p.M, 128), cdiv(p.N, BN), p.splitk > 1 ? p.splitk : p.batch);
+    BSA_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "launch_gemm: grid too large (M=%d batch=%d)", p.M, p.batch);
+    int rc = BN == 64 ? dispatch<64>(p, grid, st) : dispatch<128>(p, grid, st);
+    if (rc) return rc;
+    if (p.splitk > 1) {
+        const long long MN = (long long)p.M * p.N;
+        splitk_reduce_kernel<<<cdiv(MN, 256), 256, 0, st>>>(p.partial, p.C, MN, p.N, p.ldc, p.splitk, p.alpha,
+                                                           p.accumulate);
+        BSA_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+}  // namespace bsa

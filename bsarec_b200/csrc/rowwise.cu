@@ -1,0 +1,722 @@
+// Row-wise kernels (one warp per row of d or L values, values held in registers).
+#include "rowwise.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cmath>
+#include <vector>
+
+namespace bsa {
+
+namespace {
+
+constexpr int WARPS = 8;                 // warps per block for the row-per-warp kernels
+constexpr int MAX_ROW_BLOCKS = 148 * 4;  // persistent-style grid: <= 4 blocks per SM
+constexpr float LN_EPS = 1e-12f;
+
+#define BSA_DISPATCH_VPL(n, ...)                                                            \
+    do {                                                                                    \
+        if ((n) <= 64) { constexpr int VPL = 2; __VA_ARGS__; }                              \
+        else if ((n) <= 256) { constexpr int VPL = 8; __VA_ARGS__; }                        \
+        else if ((n) <= 1024) { constexpr int VPL = 32; __VA_ARGS__; }                      \
+        else { set_error("row length %d > 1024 is not supported", (int)(n)); return -1; }   \
+    } while (0)
+
+inline int row_grid(long long rows) {
+    long long g = (rows + WARPS - 1) / WARPS;
+    if (g > MAX_ROW_BLOCKS) g = MAX_ROW_BLOCKS;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+// mean / rstd of one row held as v[VPL] per lane (two-pass, as _modules.py:16-20)
+template <int VPL>
+__device__ __forceinline__ void row_stats(const float (&v)[VPL], int d, int lane, float& mean, float& rstd) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) if (lane + 32 * i < d) s += v[i];
+    mean = warp_sum(s) / (float)d;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) if (lane + 32 * i < d) { const float c = v[i] - mean; q += c * c; }
+    const float var = warp_sum(q) / (float)d;
+    rstd = 1.0f / sqrtf(var + LN_EPS);
+}
+
+// block-level fixed-order reduction of per-warp/per-lane partials into part[blockIdx.x][0..d)
+template <int VPL>
+__device__ __forceinline__ void block_store_partials(const float (&a)[VPL], float* __restrict__ part, int d) {
+    __shared__ float stage[WARPS][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        __syncthreads();
+        stage[w][lane] = a[i];
+        __syncthreads();
+        if (w == 0) {
+            float s = 0.f;
+#pragma unroll
+            for (int k = 0; k < WARPS; ++k) s += stage[k][lane];
+            const int j = lane + 32 * i;
+            if (j < d) part[(long long)blockIdx.x * d + j] = s;
+        }
+    }
+}
+
+// ============================================================================ embedding
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+embed_fwd_kernel(const long long* __restrict__ ids, const float* __restrict__ E, const float* __restrict__ Ppos,
+                 const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
+                 float* __restrict__ mean_o, float* __restrict__ rstd_o, long long M, int L, int d, Dropout dr) {
+    const int lane = threadIdx.x & 31;
+    for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
+        const long long id = ids[row];
+        const int t = (int)(row % L);
+        const float* __restrict__ e = E + id * d;
+        const float* __restrict__ pp = Ppos + (long long)t * d;
+        float v[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) { const int j = lane + 32 * i; v[i] = j < d ? __ldg(e + j) + __ldg(pp + j) : 0.f; }
+        float mean, rstd;
+        row_stats<VPL>(v, d, lane, mean, rstd);
+        if (lane == 0) { mean_o[row] = mean; rstd_o[row] = rstd; }
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) {
+                const float y = __ldg(gamma + j) * ((v[i] - mean) * rstd) + __ldg(beta + j);
+                out[row * d + j] = y * dropout_mult(dr, (unsigned long long)(row * d + j));
+            }
+        }
+    }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+embed_bwd_kernel(const float* __restrict__ dout, const long long* __restrict__ ids, const float* __restrict__ E,
+                 const float* __restrict__ Ppos, const float* __restrict__ gamma, const float* __restrict__ mean_i,
+                 const float* __restrict__ rstd_i, float* __restrict__ dz, float* __restrict__ pgamma,
+                 float* __restrict__ pbeta, long long M, int L, int d, Dropout dr) {
+    const int lane = threadIdx.x & 31;
+    float ag[VPL], ab[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) ag[i] = ab[i] = 0.f;
+    for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
+        const long long id = ids[row];
+        const int t = (int)(row % L);
+        const float mean = mean_i[row], rstd = rstd_i[row];
+        float xh[VPL], g[VPL];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            xh[i] = g[i] = 0.f;
+            if (j < d) {
+                const float zv = __ldg(E + id * d + j) + __ldg(Ppos + (long long)t * d + j);
+                xh[i] = (zv - mean) * rstd;
+                const float dy = dout[row * d + j] * dropout_mult(dr, (unsigned long long)(row * d + j));
+                ag[i] += dy * xh[i];
+                ab[i] += dy;
+                g[i] = dy * __ldg(gamma + j);
+                c1 += g[i];
+                c2 += g[i] * xh[i];
+            }
+        }
+        c1 = warp_sum(c1) / (float)d;
+        c2 = warp_sum(c2) / (float)d;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) dz[row * d + j] = rstd * (g[i] - c1 - xh[i] * c2);
+        }
+    }
+    block_store_partials<VPL>(ag, pgamma, d);
+    block_store_partials<VPL>(ab, pbeta, d);
+}
+
+// ============================================================================ residual + LN (+ blend)
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+residual_ln_fwd_kernel(const float* __restrict__ tmp, const float* __restrict__ resid, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, float* __restrict__ out, float* __restrict__ z_save,
+                       float* __restrict__ mean_o, float* __restrict__ rstd_o, const float* __restrict__ blend_with,
+                       float blend_a, float blend_b, long long M, int d, Dropout dr) {
+    const int lane = threadIdx.x & 31;
+    for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
+        float v[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            v[i] = 0.f;
+            if (j < d) {
+                const long long o = row * d + j;
+                v[i] = tmp[o] * dropout_mult(dr, (unsigned long long)o) + resid[o];
+                if (z_save) z_save[o] = v[i];
+            }
+        }
+        float mean, rstd;
+        row_stats<VPL>(v, d, lane, mean, rstd);
+        if (lane == 0 && mean_o) { mean_o[row] = mean; rstd_o[row] = rstd; }
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) {
+                const long long o = row * d + j;
+                float y = __ldg(gamma + j) * ((v[i] - mean) * rstd) + __ldg(beta + j);
+                if (blend_with) y = blend_a * blend_with[o] + blend_b * y;
+                out[o] = y;
+            }
+        }
+    }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+ln_bwd_kernel(const float* __restrict__ dy, float dy_scale, const float* __restrict__ z, const float* __restrict__ mean_i,
+              const float* __restrict__ rstd_i, const float* __restrict__ gamma, float* __restrict__ dz,
+              float* __restrict__ ddrop, float* __restrict__ pgamma, float* __restrict__ pbeta, long long M, int d,
+              Dropout dr) {
+    const int lane = threadIdx.x & 31;
+    float ag[VPL], ab[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) ag[i] = ab[i] = 0.f;
+    for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
+        const float mean = mean_i[row], rstd = rstd_i[row];
+        float xh[VPL], g[VPL];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            xh[i] = g[i] = 0.f;
+            if (j < d) {
+                const long long o = row * d + j;
+                xh[i] = (z[o] - mean) * rstd;
+                const float up = dy[o] * dy_scale;
+                ag[i] += up * xh[i];
+                ab[i] += up;
+                g[i] = up * __ldg(gamma + j);
+                c1 += g[i];
+                c2 += g[i] * xh[i];
+            }
+        }
+        c1 = warp_sum(c1) / (float)d;
+        c2 = warp_sum(c2) / (float)d;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) {
+                const long long o = row * d + j;
+                const float r = rstd * (g[i] - c1 - xh[i] * c2);
+                dz[o] = r;
+                if (ddrop) ddrop[o] = r * dropout_mult(dr, (unsigned long long)o);
+            }
+        }
+    }
+    block_store_partials<VPL>(ag, pgamma, d);
+    block_store_partials<VPL>(ab, pbeta, d);
+}
+
+// ============================================================================ filter branch
+// One CTA per sequence.  coef[r][d] = C^T x kept in shared memory, then one warp per position.
+constexpr int RCH = 8;   // basis vectors accumulated per pass over the sequence
+
+// coef[rr][j] = sum_t Cb[t][rr] * src(t,j)   (src supplied by a functor so fwd/bwd share it)
+template <class Src>
+__device__ __forceinline__ void project_onto_basis(float* __restrict__ coef, const float* __restrict__ Cb, int L, int d,
+                                                   int r, Src src) {
+    for (int j = threadIdx.x; j < d; j += blockDim.x) {
+        for (int r0 = 0; r0 < r; r0 += RCH) {
+            float acc[RCH];
+#pragma unroll
+            for (int q = 0; q < RCH; ++q) acc[q] = 0.f;
+            for (int t = 0; t < L; ++t) {
+                const float xv = src(t, j);
+#pragma unroll
+                for (int q = 0; q < RCH; ++q)
+                    if (r0 + q < r) acc[q] = fmaf(__ldg(Cb + (long long)t * r + r0 + q), xv, acc[q]);
+            }
+#pragma unroll
+            for (int q = 0; q < RCH; ++q)
+                if (r0 + q < r) coef[(r0 + q) * d + j] = acc[q];
+        }
+    }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+filter_ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dsp,
+                     float* __restrict__ z_save, float* __restrict__ mean_o, float* __restrict__ rstd_o, int L, int d,
+                     int r, Dropout dr) {
+    extern __shared__ float coef[];     // [r][d]
+    const int b = blockIdx.x;
+    const float* __restrict__ xb = x + (long long)b * L * d;
+    project_onto_basis(coef, Cb, L, d, r, [&](int t, int j) { return xb[(long long)t * d + j]; });
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    for (int t = threadIdx.x >> 5; t < L; t += WARPS) {
+        const long long row = (long long)b * L + t;
+        float v[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            v[i] = 0.f;
+            if (j < d) {
+                float low = 0.f;
+                for (int q = 0; q < r; ++q) low = fmaf(__ldg(Cb + (long long)t * r + q), coef[q * d + j], low);
+                const float xv = xb[(long long)t * d + j];
+                const float sb = __ldg(sqrt_beta + j);
+                const float u = low + (sb * sb) * (xv - low);
+                const long long o = row * d + j;
+                v[i] = u * dropout_mult(dr, (unsigned long long)o) + xv;
+                z_save[o] = v[i];
+            }
+        }
+        float mean, rstd;
+        row_stats<VPL>(v, d, lane, mean, rstd);
+        if (lane == 0) { mean_o[row] = mean; rstd_o[row] = rstd; }
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) dsp[row * d + j] = __ldg(gamma + j) * ((v[i] - mean) * rstd) + __ldg(beta + j);
+        }
+    }
+}
+
+// u = beta2*x + (1-beta2)*F x  =>  dx += dz_f + beta2*du + F((1-beta2)*du)   (F symmetric)
+// dbeta2[j] = sum_{t} du*(x - low)
+__global__ void __launch_bounds__(WARPS * 32)
+filter_bwd_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
+                  const float* __restrict__ dz_f, float* __restrict__ dx, float* __restrict__ pbeta2, int L, int d, int r,
+                  Dropout dr) {
+    extern __shared__ float sm[];       // coef_x [r][d], coef_g [r][d]
+    float* coef_x = sm;
+    float* coef_g = sm + (long long)r * d;
+    const int b = blockIdx.x;
+    const long long base = (long long)b * L * d;
+    project_onto_basis(coef_x, Cb, L, d, r, [&](int t, int j) { return x[base + (long long)t * d + j]; });
+    project_onto_basis(coef_g, Cb, L, d, r, [&](int t, int j) {
+        const long long o = base + (long long)t * d + j;
+        const float sb = __ldg(sqrt_beta + j);
+        return (1.0f - sb * sb) * dz_f[o] * dropout_mult(dr, (unsigned long long)o);
+    });
+    __syncthreads();
+    // thread per channel walks the sequence: coalesced across threads, fixed order over t
+    for (int j = threadIdx.x; j < d; j += blockDim.x) {
+        const float sb = __ldg(sqrt_beta + j);
+        const float b2 = sb * sb;
+        float acc = 0.f;
+        for (int t = 0; t < L; ++t) {
+            const long long o = base + (long long)t * d + j;
+            float low = 0.f, fg = 0.f;
+            for (int q = 0; q < r; ++q) {
+                const float c = __ldg(Cb + (long long)t * r + q);
+                low = fmaf(c, coef_x[q * d + j], low);
+                fg = fmaf(c, coef_g[q * d + j], fg);
+            }
+            const float dzf = dz_f[o];
+            const float du = dzf * dropout_mult(dr, (unsigned long long)o);
+            acc = fmaf(du, x[o] - low, acc);
+            dx[o] += dzf + b2 * du + fg;
+        }
+        pbeta2[(long long)b * d + j] = acc;
+    }
+}
+
+__global__ void filter_basis_kernel(float* __restrict__ Cb, int L, int kept, int r) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= L * r) return;
+    const int t = idx / r, q = idx - t * r;
+    double v;
+    if (q == 0) v = 1.0 / sqrt((double)L);
+    else {
+        const int k = (q + 1) / 2;
+        const double w = 2.0 * 3.14159265358979323846 * (double)k * (double)t / (double)L;
+        if ((L % 2 == 0) && k == L / 2) v = cos(w) / sqrt((double)L);      // Nyquist: cos only
+        else v = ((q & 1) ? cos(w) : sin(w)) * sqrt(2.0 / (double)L);
+    }
+    Cb[idx] = (float)v;
+}
+
+// ============================================================================ attention probabilities
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+softmax_fwd_kernel(const float* __restrict__ S, const long long* __restrict__ ids, float* __restrict__ P,
+                   float* __restrict__ Pd, long long rows, int H, int L, Dropout dr) {
+    const int lane = threadIdx.x & 31;
+    for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < rows; row += (long long)gridDim.x * WARPS) {
+        const int i = (int)(row % L);
+        const long long b = row / ((long long)H * L);
+        const long long* __restrict__ idb = ids + b * L;
+        float v[VPL];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const int j = lane + 32 * q;
+            v[q] = -INFINITY;
+            if (j < L) {
+                // additive mask exactly as _abstract_model.py:53-69: 0 if (key is an item and j<=i) else -10000
+                const float add = (j <= i && idb[j] > 0) ? 0.0f : -10000.0f;
+                v[q] = S[row * L + j] + add;
+                mx = fmaxf(mx, v[q]);
+            }
+        }
+        mx = warp_max(mx);
+        float sum = 0.f;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) { v[q] = expf(v[q] - mx); sum += v[q]; }
+        }
+        sum = warp_sum(sum);
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) {
+                const long long o = row * L + j;
+                const float pr = v[q] * inv;
+                P[o] = pr;
+                if (Pd != P) Pd[o] = pr * dropout_mult(dr, (unsigned long long)o);
+            }
+        }
+    }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(WARPS * 32)
+softmax_bwd_kernel(const float* __restrict__ P, float* __restrict__ G, long long rows, int L, Dropout dr) {
+    const int lane = threadIdx.x & 31;
+    for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < rows; row += (long long)gridDim.x * WARPS) {
+        float p[VPL], dp[VPL];
+        float dot = 0.f;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const int j = lane + 32 * q;
+            p[q] = dp[q] = 0.f;
+            if (j < L) {
+                const long long o = row * L + j;
+                p[q] = P[o];
+                dp[q] = G[o] * dropout_mult(dr, (unsigned long long)o);
+                dot += p[q] * dp[q];
+            }
+        }
+        dot = warp_sum(dot);
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+            const int j = lane + 32 * q;
+            if (j < L) G[row * L + j] = p[q] * (dp[q] - dot);
+        }
+    }
+}
+
+__global__ void apply_dropout_kernel(const float* __restrict__ x, float* __restrict__ y, long long n, Dropout dr) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        y[i] = x[i] * dropout_mult(dr, (unsigned long long)i);
+}
+
+// ============================================================================ reductions
+constexpr int COLSUM_ROWS = 128;
+
+__global__ void colsum_partial_kernel(const float* __restrict__ X, long long M, int N, int rows_per_blk,
+                                      float* __restrict__ part) {
+    const long long r0 = (long long)blockIdx.x * rows_per_blk;
+    const long long r1 = min(M, r0 + rows_per_blk);
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        float s = 0.f;
+        for (long long m = r0; m < r1; ++m) s += X[m * N + n];
+        part[(long long)blockIdx.x * N + n] = s;
+    }
+}
+
+__global__ void reduce_partials_kernel(const float* __restrict__ part, int nblk, int n, float* __restrict__ out,
+                                       const float* __restrict__ mult, float scale, int accumulate) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    float s = 0.f;
+    for (int k = 0; k < nblk; ++k) s += part[(long long)k * n + j];
+    s *= scale;
+    if (mult) s *= mult[j];
+    out[j] = accumulate ? out[j] + s : s;
+}
+
+__global__ void pos_grad_kernel(const float* __restrict__ dz, float* __restrict__ dP, int B, long long LD, int accumulate) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= LD) return;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dz[(long long)b * LD + i];
+    dP[i] = accumulate ? dP[i] + s : s;
+}
+
+// ============================================================================ sorted scatter-add
+__global__ void scatter_keys_kernel(const long long* __restrict__ ids, int* __restrict__ keys, int* __restrict__ vals,
+                                    long long M) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < M) { keys[i] = (int)ids[i]; vals[i] = (int)i; }
+}
+
+// one warp per segment start; the warp sums the segment's rows in ascending row order (stable sort)
+__global__ void __launch_bounds__(256)
+scatter_add_kernel(const int* __restrict__ keys, const int* __restrict__ rows, long long M, const float* __restrict__ dz,
+                   float* __restrict__ dE, int d) {
+    const long long i = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= M) return;
+    const int key = keys[i];
+    if (key == 0) return;                              // padding_idx=0: no gradient through the gather
+    if (i > 0 && keys[i - 1] == key) return;           // not a segment start
+    const int lane = threadIdx.x & 31;
+    long long end = i + 1;
+    while (end < M && keys[end] == key) ++end;
+    float* __restrict__ out = dE + (long long)key * d;
+    for (int j0 = 0; j0 < d; j0 += 128) {
+        const int j = j0 + lane * 4;
+        if (j >= d) continue;
+        if (j + 3 < d) {
+            float4 acc = *reinterpret_cast<const float4*>(out + j);
+            for (long long s = i; s < end; ++s) {
+                const float4 v = *reinterpret_cast<const float4*>(dz + (long long)rows[s] * d + j);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            *reinterpret_cast<float4*>(out + j) = acc;
+        } else {
+            for (int jj = j; jj < d; ++jj) {
+                float acc = out[jj];
+                for (long long s = i; s < end; ++s) acc += dz[(long long)rows[s] * d + jj];
+                out[jj] = acc;
+            }
+        }
+    }
+}
+
+__global__ void last_rows_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int L, int d, int scatter) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)B * d) return;
+    const long long b = i / d, j = i - b * d;
+    const long long full = (b * L + (L - 1)) * d + j;
+    if (scatter) dst[full] = src[i]; else dst[i] = src[full];
+}
+
+struct ScatterPlan {        // laid out in the caller's workspace
+    int* keys_in; int* vals_in; int* keys_out; int* vals_out; void* tmp; size_t tmp_bytes;
+};
+
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+inline ScatterPlan carve_plan(void* plan, long long M, size_t cub_bytes) {
+    char* p = (char*)plan;
+    ScatterPlan s;
+    const size_t arr = align_up((size_t)M * sizeof(int));
+    s.keys_in = (int*)p; p += arr;
+    s.vals_in = (int*)p; p += arr;
+    s.keys_out = (int*)p; p += arr;
+    s.vals_out = (int*)p; p += arr;
+    s.tmp = p; s.tmp_bytes = cub_bytes;
+    return s;
+}
+
+inline size_t cub_sort_bytes(long long M) {
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const int*)nullptr, (int*)nullptr, (const int*)nullptr,
+                                    (int*)nullptr, (int)M, 0, 32, (cudaStream_t)0);
+    return bytes;
+}
+
+}  // namespace
+
+// ============================================================================ host launchers
+int rowwise_partial_blocks(long long rows) { return row_grid(rows); }
+
+int embed_ln_dropout_fwd(const long long* ids, const float* E, const float* Ppos, const float* gamma,
+                         const float* beta, float* out, float* mean, float* rstd, int B, int L, int d,
+                         long long item_size, Dropout dr, cudaStream_t st) {
+    (void)item_size;
+    const long long M = (long long)B * L;
+    if (M == 0) return 0;
+    BSA_DISPATCH_VPL(d, (embed_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(ids, E, Ppos, gamma, beta, out, mean,
+                                                                                  rstd, M, L, d, dr)));
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int embed_ln_dropout_bwd(const float* dout, const long long* ids, const float* E, const float* Ppos,
+                         const float* gamma, const float* mean, const float* rstd, float* dz, float* pgamma,
+                         float* pbeta, int* nblk, int B, int L, int d, Dropout dr, cudaStream_t st) {
+    const long long M = (long long)B * L;
+    const int g = row_grid(M);
+    *nblk = g;
+    BSA_DISPATCH_VPL(d, (embed_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dout, ids, E, Ppos, gamma, mean, rstd, dz,
+                                                                       pgamma, pbeta, M, L, d, dr)));
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, const float* beta, float* out,
+                    float* z_save, float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b,
+                    long long M, int d, Dropout dr, cudaStream_t st) {
+    if (M == 0) return 0;
+    BSA_DISPATCH_VPL(d, (residual_ln_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(
+                            tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr)));
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
+           float* dz, float* ddrop, float* pgamma, float* pbeta, int* nblk, long long M, int d, Dropout dr,
+           cudaStream_t st) {
+    const int g = row_grid(M);
+    *nblk = g;
+    BSA_DISPATCH_VPL(d, (ln_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop,
+                                                                    pgamma, pbeta, M, d, dr)));
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int filter_rank(int L, int kept_bins) {
+    int kept = kept_bins < L / 2 + 1 ? kept_bins : L / 2 + 1;
+    if (kept < 1) kept = 1;
+    int r = 2 * kept - 1;
+    if (L % 2 == 0 && kept == L / 2 + 1) r -= 1;       // Nyquist bin has no sin column
+    return r;
+}
+
+int build_filter_basis(float* Cb, int L, int kept_bins, int* r_out, cudaStream_t st) {
+    int kept = kept_bins < L / 2 + 1 ? kept_bins : L / 2 + 1;
+    if (kept < 1) kept = 1;
+    const int r = filter_rank(L, kept_bins);
+    if (r_out) *r_out = r;
+    filter_basis_kernel<<<cdiv((long long)L * r, 256), 256, 0, st>>>(Cb, L, kept, r);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta,
+                  float* dsp, float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr,
+                  cudaStream_t st) {
+    if (B == 0) return 0;
+    const size_t smem = (size_t)r * d * sizeof(float);
+    BSA_REQUIRE(smem <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);
+    BSA_DISPATCH_VPL(d, {
+        if (smem > 48 * 1024)
+            BSA_CHECK_CUDA(cudaFuncSetAttribute(filter_ln_fwd_kernel<VPL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)smem));
+        filter_ln_fwd_kernel<VPL><<<B, WARPS * 32, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L,
+                                                             d, r, dr);
+    });
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int filter_bwd(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2,
+               int B, int L, int d, int r, Dropout dr, cudaStream_t st) {
+    if (B == 0) return 0;
+    const size_t smem = 2 * (size_t)r * d * sizeof(float);
+    BSA_REQUIRE(smem <= 200 * 1024, "filter bwd: basis rank %d x hidden %d does not fit shared memory", r, d);
+    if (smem > 48 * 1024)
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(filter_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    filter_bwd_kernel<<<B, WARPS * 32, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, dr);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int softmax_mask_dropout_fwd(const float* S, const long long* ids, float* P, float* Pd, int B, int H, int L,
+                             Dropout dr, cudaStream_t st) {
+    const long long rows = (long long)B * H * L;
+    if (rows == 0) return 0;
+    BSA_DISPATCH_VPL(L, (softmax_fwd_kernel<VPL><<<row_grid(rows), WARPS * 32, 0, st>>>(S, ids, P, Pd, rows, H, L, dr)));
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int softmax_bwd(const float* P, float* G, int B, int H, int L, Dropout dr, cudaStream_t st) {
+    const long long rows = (long long)B * H * L;
+    if (rows == 0) return 0;
+    BSA_DISPATCH_VPL(L, (softmax_bwd_kernel<VPL><<<row_grid(rows), WARPS * 32, 0, st>>>(P, G, rows, L, dr)));
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int apply_dropout(const float* x, float* y, long long n, Dropout dr, cudaStream_t st) {
+    if (n == 0) return 0;
+    long long g = (n + 255) / 256;
+    if (g > 148 * 16) g = 148 * 16;
+    apply_dropout_kernel<<<(int)g, 256, 0, st>>>(x, y, n, dr);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int colsum_partial_rows(long long M) { return (int)((M + COLSUM_ROWS - 1) / COLSUM_ROWS); }
+
+int colsum(const float* X, long long M, int N, float* part, float* out, int accumulate, cudaStream_t st) {
+    const int nblk = colsum_partial_rows(M);
+    if (nblk == 0) return 0;
+    colsum_partial_kernel<<<nblk, 256, 0, st>>>(X, M, N, COLSUM_ROWS, part);
+    BSA_LAUNCH_CHECK();
+    return reduce_partials(part, nblk, N, out, nullptr, 1.0f, accumulate, st);
+}
+
+int reduce_partials(const float* part, int nblk, int n, float* out, const float* mult, float scale, int accumulate,
+                    cudaStream_t st) {
+    reduce_partials_kernel<<<cdiv(n, 128), 128, 0, st>>>(part, nblk, n, out, mult, scale, accumulate);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int pos_grad(const float* dz, float* dP, int B, int L, int d, int accumulate, cudaStream_t st) {
+    const long long LD = (long long)L * d;
+    pos_grad_kernel<<<cdiv(LD, 256), 256, 0, st>>>(dz, dP, B, LD, accumulate);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+size_t scatter_plan_bytes(long long M) {
+    if (M <= 0) return 256;
+    return 4 * align_up((size_t)M * sizeof(int)) + align_up(cub_sort_bytes(M)) + 256;
+}
+
+int scatter_plan(const long long* ids, long long M, long long item_size, void* plan, size_t plan_bytes, cudaStream_t st) {
+    if (M == 0) return 0;
+    BSA_REQUIRE(M < (1ll << 31) && item_size < (1ll << 31), "scatter_plan: sizes exceed int32");
+    const size_t cb = cub_sort_bytes(M);
+    BSA_REQUIRE(plan_bytes >= scatter_plan_bytes(M), "scatter_plan: workspace too small");
+    ScatterPlan s = carve_plan(plan, M, cb);
+    scatter_keys_kernel<<<cdiv(M, 256), 256, 0, st>>>(ids, s.keys_in, s.vals_in, M);
+    BSA_LAUNCH_CHECK();
+    int end_bit = 1;
+    while ((1ll << end_bit) < item_size && end_bit < 31) ++end_bit;
+    size_t tb = s.tmp_bytes;
+    BSA_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(s.tmp, tb, s.keys_in, s.keys_out, s.vals_in, s.vals_out, (int)M, 0,
+                                                   end_bit, st));
+    bsa::g_launch_count += 3;   // radix sort passes (library kernels)
+    return 0;
+}
+
+int scatter_add_rows(const void* plan, long long M, const float* dz, float* dE, int d, cudaStream_t st) {
+    if (M == 0) return 0;
+    BSA_REQUIRE(d % 4 == 0, "scatter_add_rows: hidden size must be a multiple of 4");
+    ScatterPlan s = carve_plan(const_cast<void*>(plan), M, 0);
+    scatter_add_kernel<<<cdiv(M, 8), 256, 0, st>>>(s.keys_out, s.vals_out, M, dz, dE, d);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int fill_zero(float* p, long long n, cudaStream_t st) {
+    if (n == 0) return 0;
+    BSA_CHECK_CUDA(cudaMemsetAsync(p, 0, (size_t)n * sizeof(float), st));
+    return 0;
+}
+
+int scatter_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st) {
+    int rc = fill_zero(dst, (long long)B * L * d, st);
+    if (rc) return rc;
+    last_rows_kernel<<<cdiv((long long)B * d, 256), 256, 0, st>>>(src, dst, B, L, d, 1);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st) {
+    last_rows_kernel<<<cdiv((long long)B * d, 256), 256, 0, st>>>(src, dst, B, L, d, 0);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace bsa

@@ -1,0 +1,267 @@
+"""Host-side orchestration of the C-ABI kernels: encoder forward/backward, fused loss, fused top-k.
+
+PyTorch is used for device memory, streams and autograd plumbing only; every FLOP of the hot path runs in
+libbsarec_sm100a.so.  Tensors handed to the library are fp32/int64, contiguous and on the same CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _cabi
+from ._cabi import BlockDesc, BlockPtrs, CeDesc, EmbedDesc, TopkDesc, check
+
+_basis_cache: Dict[Tuple[int, int, int], torch.Tensor] = {}
+
+
+@dataclass
+class Hyper:
+    """What the kernels need from ``args`` (SURVEY.md §8b ctor-input row)."""
+    item_size: int
+    hidden_size: int
+    max_seq_length: int
+    num_attention_heads: int
+    num_hidden_layers: int
+    kept_bins: int
+    alpha: float
+    p_hidden: float
+    p_attn: float
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _require_cuda(t: torch.Tensor, name: str, dtype):
+    if not t.is_cuda:
+        raise RuntimeError(f"bsarec_b200: `{name}` must be a CUDA tensor — this build has no CPU fallback "
+                           f"(got device {t.device}). Move the model and batch to the GPU.")
+    if t.dtype != dtype:
+        raise RuntimeError(f"bsarec_b200: `{name}` must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def filter_basis(L: int, kept_bins: int, device) -> torch.Tensor:
+    """C [L, r] with C C^T == the reference's rfft/low-pass/irfft operator (model/bsarec.py:93-97)."""
+    lib = _cabi.load()
+    key = (L, kept_bins, torch.device(device).index or 0)
+    if key not in _basis_cache:
+        r = lib.bsa_filter_rank(L, kept_bins)
+        basis = torch.empty(L, r, dtype=torch.float32, device=device)
+        check(lib.bsa_build_filter_basis(_ptr(basis), L, kept_bins, _stream()), "bsa_build_filter_basis")
+        _basis_cache[key] = basis
+    return _basis_cache[key]
+
+
+def _block_desc(h: Hyper, B: int, L: int, layer: int, training: bool, seed: int) -> BlockDesc:
+    return BlockDesc(B=B, L=L, d=h.hidden_size, H=h.num_attention_heads, kept_bins=h.kept_bins, alpha=h.alpha,
+                     p_hidden=h.p_hidden, p_attn=h.p_attn, training=int(training), seed=seed, layer=layer)
+
+
+def _block_ptrs(tensors: Dict[str, torch.Tensor], layer: int) -> BlockPtrs:
+    pre = f"item_encoder.blocks.{layer}."
+    return BlockPtrs(**{f: tensors[pre + key].data_ptr() for f, key in _cabi.BLOCK_PARAM_KEYS.items()})
+
+
+class EncoderState:
+    """Everything one forward pass leaves behind for its backward pass."""
+    __slots__ = ("ids", "B", "L", "seed", "training", "mean", "rstd", "xs", "saved", "workspace")
+
+
+def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor, training: bool, seed: int,
+                    keep_for_backward: bool) -> Tuple[List[torch.Tensor], Optional[EncoderState]]:
+    """ids int64 [B,L] -> [h0, x1, ..., xP] (each [B,L,d]); mirrors BSARecModel.forward (bsarec.py:16-28)."""
+    lib = _cabi.load()
+    ids = _require_cuda(ids, "input_ids", torch.int64)
+    B, L = ids.shape
+    d, dev = h.hidden_size, ids.device
+    if L > h.max_seq_length:
+        raise RuntimeError(f"sequence length {L} exceeds max_seq_length {h.max_seq_length} (position table rows)")
+    E = params["item_embeddings.weight"]
+    with torch.cuda.device(dev):
+        st = _stream()
+        basis = filter_basis(L, h.kept_bins, dev)
+        h0 = torch.empty(B, L, d, dtype=torch.float32, device=dev)
+        mean = torch.empty(B, L, dtype=torch.float32, device=dev)
+        rstd = torch.empty(B, L, dtype=torch.float32, device=dev)
+        ed = EmbedDesc(B=B, L=L, d=d, item_size=E.shape[0], p_hidden=h.p_hidden, training=int(training), seed=seed)
+        check(lib.bsa_embed_ln_dropout_fwd(C.byref(ed), _ptr(ids), _ptr(E), _ptr(params["position_embeddings.weight"]),
+                                           _ptr(params["LayerNorm.weight"]), _ptr(params["LayerNorm.bias"]), _ptr(h0),
+                                           _ptr(mean), _ptr(rstd), st), "bsa_embed_ln_dropout_fwd")
+        xs = [h0]
+        saved_list = []
+        bd0 = _block_desc(h, B, L, 0, training, seed)
+        saved_bytes = lib.bsa_block_saved_bytes(C.byref(bd0))
+        ws_bytes = lib.bsa_block_workspace_bytes(C.byref(bd0))
+        workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        shared_saved = None
+        for l in range(h.num_hidden_layers):
+            bd = _block_desc(h, B, L, l, training, seed)
+            if keep_for_backward or shared_saved is None:
+                saved = torch.empty(saved_bytes, dtype=torch.uint8, device=dev)
+                shared_saved = saved
+            else:
+                saved = shared_saved
+            w = _block_ptrs(params, l)
+            x_out = torch.empty(B, L, d, dtype=torch.float32, device=dev)
+            check(lib.bsa_block_fwd(C.byref(bd), C.byref(w), _ptr(basis), _ptr(ids), _ptr(xs[-1]), _ptr(x_out), _ptr(saved),
+                                    _ptr(workspace), ws_bytes, st), "bsa_block_fwd")
+            xs.append(x_out)
+            saved_list.append(saved)
+    if not keep_for_backward:
+        return xs, None
+    state = EncoderState()
+    state.ids, state.B, state.L, state.seed, state.training = ids, B, L, seed, training
+    state.mean, state.rstd, state.xs, state.saved, state.workspace = mean, rstd, xs, saved_list, workspace
+    return xs, state
+
+
+def encoder_backward(h: Hyper, params: Dict[str, torch.Tensor], state: EncoderState, d_out: torch.Tensor,
+                     grads: Dict[str, torch.Tensor]) -> None:
+    """d_out: gradient wrt the last block's output [B,L,d].  Writes every encoder/embedding gradient into
+    ``grads`` (item table: accumulated on top of what is already there)."""
+    lib = _cabi.load()
+    B, L, d, dev = state.B, state.L, h.hidden_size, d_out.device
+    with torch.cuda.device(dev):
+        st = _stream()
+        basis = filter_basis(L, h.kept_bins, dev)
+        ws_bytes = state.workspace.numel()
+        g = d_out
+        for l in reversed(range(h.num_hidden_layers)):
+            bd = _block_desc(h, B, L, l, state.training, state.seed)
+            w = _block_ptrs(params, l)
+            gp = _block_ptrs(grads, l)
+            dx = torch.empty(B, L, d, dtype=torch.float32, device=dev)
+            check(lib.bsa_block_bwd(C.byref(bd), C.byref(w), _ptr(basis), _ptr(state.ids), _ptr(state.xs[l]),
+                                    _ptr(state.saved[l]), _ptr(g), _ptr(dx), C.byref(gp), _ptr(state.workspace), ws_bytes, st),
+                  "bsa_block_bwd")
+            g = dx
+            state.saved[l] = None            # release the layer's activations as soon as they are consumed
+        E = params["item_embeddings.weight"]
+        ed = EmbedDesc(B=B, L=L, d=d, item_size=E.shape[0], p_hidden=h.p_hidden, training=int(state.training),
+                       seed=state.seed)
+        eb = lib.bsa_embed_bwd_workspace_bytes(C.byref(ed))
+        ws = state.workspace if ws_bytes >= eb else torch.empty(eb, dtype=torch.uint8, device=dev)
+        check(lib.bsa_embed_ln_dropout_bwd(C.byref(ed), _ptr(state.ids), _ptr(E), _ptr(params["position_embeddings.weight"]),
+                                           _ptr(params["LayerNorm.weight"]), _ptr(state.mean), _ptr(state.rstd), _ptr(g),
+                                           _ptr(grads["item_embeddings.weight"]), _ptr(grads["position_embeddings.weight"]),
+                                           _ptr(grads["LayerNorm.weight"]), _ptr(grads["LayerNorm.bias"]), _ptr(ws),
+                                           ws.numel(), st), "bsa_embed_ln_dropout_bwd")
+
+
+def gather_last(x: torch.Tensor) -> torch.Tensor:
+    lib = _cabi.load()
+    B, L, d = x.shape
+    out = torch.empty(B, d, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.bsa_gather_last(_ptr(x), _ptr(out), B, L, d, _stream()), "bsa_gather_last")
+    return out
+
+
+def ce_forward(s: torch.Tensor, E: torch.Tensor, answers: torch.Tensor, impl: int = 0):
+    """-> (loss 0-dim, lse [B]); logits never materialised (bsarec.py:32-35)."""
+    lib = _cabi.load()
+    B, d = s.shape
+    answers = _require_cuda(answers, "answers", torch.int64)
+    cd = CeDesc(B=B, d=d, item_size=E.shape[0], impl=impl)
+    with torch.cuda.device(s.device):
+        wsb = lib.bsa_ce_workspace_bytes(C.byref(cd))
+        ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+        loss = torch.empty((), dtype=torch.float32, device=s.device)
+        lse = torch.empty(B, dtype=torch.float32, device=s.device)
+        check(lib.bsa_ce_fwd(C.byref(cd), _ptr(s), _ptr(E), _ptr(answers), _ptr(loss), _ptr(lse), _ptr(ws), wsb, _stream()),
+              "bsa_ce_fwd")
+    return loss, lse
+
+
+def ce_backward(s, E, answers, lse, d_loss, dE: torch.Tensor, impl: int = 0) -> torch.Tensor:
+    """Overwrites dE [N,d] with the dense gradient; returns ds [B,d]."""
+    lib = _cabi.load()
+    B, d = s.shape
+    cd = CeDesc(B=B, d=d, item_size=E.shape[0], impl=impl)
+    with torch.cuda.device(s.device):
+        wsb = lib.bsa_ce_workspace_bytes(C.byref(cd))
+        ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+        ds = torch.empty(B, d, dtype=torch.float32, device=s.device)
+        d_loss = d_loss.to(dtype=torch.float32).contiguous()
+        check(lib.bsa_ce_bwd(C.byref(cd), _ptr(s), _ptr(E), _ptr(answers), _ptr(lse), _ptr(d_loss), _ptr(ds), _ptr(dE),
+                             _ptr(ws), wsb, _stream()), "bsa_ce_bwd")
+    return ds
+
+
+def scatter_last(ds: torch.Tensor, L: int) -> torch.Tensor:
+    lib = _cabi.load()
+    B, d = ds.shape
+    out = torch.empty(B, L, d, dtype=torch.float32, device=ds.device)
+    with torch.cuda.device(ds.device):
+        check(lib.bsa_scatter_last(_ptr(ds), _ptr(out), B, L, d, _stream()), "bsa_scatter_last")
+    return out
+
+
+def score_topk(s: torch.Tensor, item_shard: torch.Tensor, hist_indptr: Optional[torch.Tensor],
+               hist_indices: Optional[torch.Tensor], k: int = 20, shard_offset: int = 0, impl: int = 0):
+    """-> (top_val fp32 [B,k], top_idx int64 [B,k]); replaces trainers.py:62-68,130-149 for one item shard."""
+    lib = _cabi.load()
+    B, d = s.shape
+    td = TopkDesc(B=B, d=d, k=k, shard_rows=item_shard.shape[0], shard_offset=shard_offset, impl=impl)
+    with torch.cuda.device(s.device):
+        wsb = lib.bsa_score_topk_workspace_bytes(C.byref(td))
+        ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+        val = torch.empty(B, k, dtype=torch.float32, device=s.device)
+        idx = torch.empty(B, k, dtype=torch.int64, device=s.device)
+        if hist_indptr is not None:
+            hist_indptr = _require_cuda(hist_indptr, "hist_indptr", torch.int64)
+            hist_indices = _require_cuda(hist_indices, "hist_indices", torch.int64)
+        check(lib.bsa_score_topk(C.byref(td), _ptr(s.contiguous()), _ptr(item_shard), _ptr(hist_indptr), _ptr(hist_indices),
+                                 _ptr(val), _ptr(idx), _ptr(ws), wsb, _stream()), "bsa_score_topk")
+    return val, idx
+
+
+def topk_merge(cand_val: torch.Tensor, cand_idx: torch.Tensor):
+    """[G,B,k] candidates -> merged [B,k] (score desc, id asc)."""
+    lib = _cabi.load()
+    G, B, k = cand_val.shape
+    val = torch.empty(B, k, dtype=torch.float32, device=cand_val.device)
+    idx = torch.empty(B, k, dtype=torch.int64, device=cand_val.device)
+    with torch.cuda.device(cand_val.device):
+        check(lib.bsa_topk_merge(_ptr(cand_val.contiguous()), _ptr(cand_idx.contiguous()), G, B, k, _ptr(val), _ptr(idx),
+                                 _stream()), "bsa_topk_merge")
+    return val, idx
+
+
+class FusedLoss(torch.autograd.Function):
+    """calculate_loss as one autograd node: encoder fwd -> last position -> fused CE; backward in reverse."""
+
+    @staticmethod
+    def forward(ctx, hyper: Hyper, names: Sequence[str], ids, answers, training: bool, seed: int, ce_impl: int,
+                *tensors):
+        params = dict(zip(names, tensors))
+        xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True)
+        s = gather_last(xs[-1])
+        loss, lse = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
+        ctx.hyper, ctx.names, ctx.state, ctx.ce_impl = hyper, names, state, ce_impl
+        ctx.answers, ctx.s, ctx.lse = answers, s, lse
+        ctx.save_for_backward(*tensors)
+        return loss
+
+    @staticmethod
+    def backward(ctx, d_loss):
+        tensors = ctx.saved_tensors
+        names, hyper, state = ctx.names, ctx.hyper, ctx.state
+        params = dict(zip(names, tensors))
+        grads = {n: torch.empty_like(t) for n, t in params.items()}
+        if state.L < params["position_embeddings.weight"].shape[0]:
+            grads["position_embeddings.weight"].zero_()      # rows >= L are never touched by the kernels
+        E = params["item_embeddings.weight"]
+        ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, grads["item_embeddings.weight"], ctx.ce_impl)
+        d_out = scatter_last(ds, state.L)
+        encoder_backward(hyper, params, state, d_out, grads)
+        ctx.state = None
+        return (None, None, None, None, None, None, None) + tuple(grads[n] for n in names)

@@ -1,0 +1,170 @@
+"""Drop-in ``BSARecModel``: the reference's class contract over the sm_100a kernels.
+
+Same constructor (``Cls(args=args)``), same ``calculate_loss`` / ``predict`` / ``forward`` signatures, same
+``nn.Module`` parameter tree — hence the same 42 ``state_dict`` keys and shapes, the same ``parameters()``
+order and, under the same ``torch.manual_seed``, bit-identical initial weights — as
+``src/model/bsarec.py:7-37`` + ``src/model/_abstract_model.py:6-75``.
+The modules below are parameter containers only: no torch op of theirs runs on the hot path.
+"""
+from __future__ import annotations
+
+import copy
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+
+
+class TFLayerNorm(nn.Module):
+    """Container for the reference's custom LayerNorm (weight, bias; eps=1e-12 inside the sqrt)."""
+
+    def __init__(self, hidden_size: int, eps: float = 1e-12):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(hidden_size))
+        self.bias = nn.Parameter(torch.zeros(hidden_size))
+        self.variance_epsilon = eps
+
+
+class _FilterLayer(nn.Module):          # bsarec.py:82-88
+    def __init__(self, args):
+        super().__init__()
+        self.out_dropout = nn.Dropout(args.hidden_dropout_prob)
+        self.LayerNorm = TFLayerNorm(args.hidden_size, eps=1e-12)
+        self.c = args.c // 2 + 1
+        self.sqrt_beta = nn.Parameter(torch.randn(1, 1, args.hidden_size))
+
+
+class _AttentionLayer(nn.Module):       # _modules.py:76-98
+    def __init__(self, args):
+        super().__init__()
+        if args.hidden_size % args.num_attention_heads != 0:
+            raise ValueError("The hidden size (%d) is not a multiple of the number of attention heads (%d)"
+                             % (args.hidden_size, args.num_attention_heads))
+        self.num_attention_heads = args.num_attention_heads
+        self.attention_head_size = args.hidden_size // args.num_attention_heads
+        self.query = nn.Linear(args.hidden_size, args.hidden_size)
+        self.key = nn.Linear(args.hidden_size, args.hidden_size)
+        self.value = nn.Linear(args.hidden_size, args.hidden_size)
+        self.attn_dropout = nn.Dropout(args.attention_probs_dropout_prob)
+        self.dense = nn.Linear(args.hidden_size, args.hidden_size)
+        self.LayerNorm = nn.LayerNorm(args.hidden_size, eps=1e-12)
+        self.out_dropout = nn.Dropout(args.hidden_dropout_prob)
+
+
+class _FeedForward(nn.Module):          # _modules.py:22-35
+    def __init__(self, args):
+        super().__init__()
+        if args.hidden_act != "gelu":
+            raise ValueError(f"bsarec_b200 implements hidden_act='gelu' only (got {args.hidden_act!r})")
+        self.dense_1 = nn.Linear(args.hidden_size, 4 * args.hidden_size)
+        self.dense_2 = nn.Linear(4 * args.hidden_size, args.hidden_size)
+        self.LayerNorm = TFLayerNorm(args.hidden_size, eps=1e-12)
+        self.dropout = nn.Dropout(args.hidden_dropout_prob)
+
+
+class _Layer(nn.Module):                # bsarec.py:67-73
+    def __init__(self, args):
+        super().__init__()
+        self.filter_layer = _FilterLayer(args)
+        self.attention_layer = _AttentionLayer(args)
+        self.alpha = args.alpha
+
+
+class _Block(nn.Module):                # bsarec.py:56-60
+    def __init__(self, args):
+        super().__init__()
+        self.layer = _Layer(args)
+        self.feed_forward = _FeedForward(args)
+
+
+class _Encoder(nn.Module):              # bsarec.py:39-44: one block built, deep-copied P times
+    def __init__(self, args):
+        super().__init__()
+        block = _Block(args)
+        self.blocks = nn.ModuleList([copy.deepcopy(block) for _ in range(args.num_hidden_layers)])
+
+
+class BSARecModel(nn.Module):
+    def __init__(self, args):
+        super().__init__()
+        self.args = args
+        self.item_embeddings = nn.Embedding(args.item_size, args.hidden_size, padding_idx=0)
+        self.position_embeddings = nn.Embedding(args.max_seq_length, args.hidden_size)
+        self.batch_size = args.batch_size
+        self.LayerNorm = TFLayerNorm(args.hidden_size, eps=1e-12)
+        self.dropout = nn.Dropout(args.hidden_dropout_prob)
+        self.item_encoder = _Encoder(args)
+        self.apply(self.init_weights)
+        self.ce_impl = 0          # 0 auto | 1 fp32 FFMA | 2 tcgen05 3xTF32   (bsa_ce_desc.impl)
+        self.topk_impl = 0
+        self._fixed_seed: Optional[int] = None
+
+    # ------------------------------------------------------------------ reference-compatible surface
+    def init_weights(self, module):
+        """N(0, initializer_range^2) for Linear/Embedding weights (padding row included), zero Linear
+        biases, custom LayerNorm -> (1, 0); sqrt_beta and nn.LayerNorm untouched (_abstract_model.py:26-39)."""
+        if isinstance(module, (nn.Linear, nn.Embedding)):
+            module.weight.data.normal_(mean=0.0, std=self.args.initializer_range)
+        elif isinstance(module, TFLayerNorm):
+            module.bias.data.zero_()
+            module.weight.data.fill_(1.0)
+        if isinstance(module, nn.Linear) and module.bias is not None:
+            module.bias.data.zero_()
+
+    def forward(self, input_ids, user_ids=None, all_sequence_output=False):
+        """[B,L] ids -> last block output [B,L,d] (or the list of P+1 layer outputs).  Inference path:
+        the result is detached; training goes through ``calculate_loss``."""
+        xs, _ = Fn.encoder_forward(self._hyper(), self._tensors(), input_ids, self.training, self._next_seed(),
+                                   keep_for_backward=False)
+        return xs if all_sequence_output else xs[-1]
+
+    def predict(self, input_ids, user_ids, all_sequence_output=False):
+        return self.forward(input_ids, user_ids, all_sequence_output)
+
+    def calculate_loss(self, input_ids, answers, neg_answers, same_target, user_ids):
+        """Mean full-catalog cross-entropy at the last position (bsarec.py:30-37); neg_answers, same_target
+        and user_ids are accepted and ignored, as in the reference."""
+        names = [n for n, _ in self.named_parameters()]
+        tensors = [p for _, p in self.named_parameters()]
+        return Fn.FusedLoss.apply(self._hyper(), names, input_ids, answers, self.training, self._next_seed(),
+                                  self.ce_impl, *tensors)
+
+    # ------------------------------------------------------------------ fused evaluation (additional API)
+    @torch.no_grad()
+    def last_hidden(self, input_ids) -> torch.Tensor:
+        """[B,d] = predict(input_ids)[:, -1, :] without building the full output list on the host side."""
+        xs, _ = Fn.encoder_forward(self._hyper(), self._tensors(), input_ids, False, 0, keep_for_backward=False)
+        return Fn.gather_last(xs[-1])
+
+    @torch.no_grad()
+    def full_sort_topk(self, input_ids, user_ids=None, hist_indptr=None, hist_indices=None, k: int = 20):
+        """Top-k item ids per user, descending score, history items scored 0.0 — the eval branch of
+        ``Trainer.iteration`` (trainers.py:126-149) kept on the device.  ``hist_indptr`` [B+1] /
+        ``hist_indices`` are a CSR over the batch rows (int64, CUDA).  Returns int64 [B,k]."""
+        s = self.last_hidden(input_ids)
+        _, idx = Fn.score_topk(s, self.item_embeddings.weight.detach(), hist_indptr, hist_indices, k, 0, self.topk_impl)
+        return idx
+
+    # ------------------------------------------------------------------ helpers
+    def set_dropout_seed(self, seed: Optional[int]):
+        """Pin the per-call dropout seed (tests); ``None`` draws one per call from torch's CPU generator."""
+        self._fixed_seed = seed
+
+    def _next_seed(self) -> int:
+        if self._fixed_seed is not None:
+            return int(self._fixed_seed)
+        if not self.training:
+            return 0
+        return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+    def _hyper(self) -> Fn.Hyper:
+        a = self.args
+        return Fn.Hyper(item_size=a.item_size, hidden_size=a.hidden_size, max_seq_length=a.max_seq_length,
+                        num_attention_heads=a.num_attention_heads, num_hidden_layers=a.num_hidden_layers,
+                        kept_bins=a.c // 2 + 1, alpha=float(a.alpha), p_hidden=float(a.hidden_dropout_prob),
+                        p_attn=float(a.attention_probs_dropout_prob))
+
+    def _tensors(self) -> Dict[str, torch.Tensor]:
+        return {n: p.detach() for n, p in self.named_parameters()}

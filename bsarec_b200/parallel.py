@@ -1,0 +1,78 @@
+"""Multi-GPU plumbing (one process per GPU, torch.distributed; NCCL on the box, gloo in CPU tests).
+
+Training is data-parallel: every rank holds a full replica, the global batch is split evenly, and one
+flat fp32 all-reduce averages the gradients.  Evaluation shards the item table by rows:
+user vectors are all-gathered, every rank scores all users against its shard and keeps a local top-k,
+the candidates are all-gathered and merged.
+"""
+from __future__ import annotations
+
+from typing import Callable, Iterable, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_rows: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous row range [lo, hi) of rank's shard; the first n_rows % world shards get one extra row."""
+    base, extra = divmod(n_rows, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def allreduce_gradients(params: Iterable[torch.nn.Parameter], group=None, bucket_elems: int = 1 << 28) -> int:
+    """Average ``p.grad`` over the group in flat buckets (sum / world).  Returns the number of collectives.
+    Ranks must hold equally sized local batches so that the mean of local means is the global mean."""
+    world = dist.get_world_size(group)
+    grads = [p.grad for p in params if p.grad is not None]
+    if world == 1 or not grads:
+        return 0
+    calls, i = 0, 0
+    while i < len(grads):
+        j, n = i, 0
+        while j < len(grads) and (n == 0 or n + grads[j].numel() <= bucket_elems):
+            n += grads[j].numel()
+            j += 1
+        chunk = grads[i:j]
+        if len(chunk) == 1:
+            flat = chunk[0].view(-1)
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+            flat.div_(world)
+        else:
+            flat = torch.cat([g.reshape(-1) for g in chunk])
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+            flat.div_(world)
+            off = 0
+            for g in chunk:
+                g.copy_(flat[off:off + g.numel()].view_as(g))
+                off += g.numel()
+        calls += 1
+        i = j
+    return calls
+
+
+def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shard_offset: int,
+                           hist_indptr_all: Optional[torch.Tensor], hist_indices_all: Optional[torch.Tensor], k: int,
+                           score_fn: Callable, merge_fn: Callable, group=None) -> torch.Tensor:
+    """Item-sharded evaluation step.
+
+    s_local [B_local, d]: this rank's users' last-position vectors (equal B_local on every rank).
+    hist_*_all: CSR history of ALL world*B_local users of the global batch, rank-major order.
+    score_fn(s, shard, indptr, indices, k, offset) -> (val [B,k], idx [B,k]); merge_fn(val [G,B,k], idx) -> (val, idx).
+    Returns int64 [B_local, k] for this rank's users."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    Bl = s_local.shape[0]
+    if world == 1:
+        _, idx = score_fn(s_local, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)
+        return idx
+    s_all = torch.empty(world * Bl, s_local.shape[1], dtype=s_local.dtype, device=s_local.device)
+    dist.all_gather_into_tensor(s_all, s_local.contiguous(), group=group)
+    val, idx = score_fn(s_all, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)
+    val_all = torch.empty(world, world * Bl, k, dtype=val.dtype, device=val.device)
+    idx_all = torch.empty(world, world * Bl, k, dtype=idx.dtype, device=idx.device)
+    dist.all_gather_into_tensor(val_all, val.contiguous(), group=group)
+    dist.all_gather_into_tensor(idx_all, idx.contiguous(), group=group)
+    mine = slice(rank * Bl, (rank + 1) * Bl)
+    _, top = merge_fn(val_all[:, mine].contiguous(), idx_all[:, mine].contiguous())
+    return top

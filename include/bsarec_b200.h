@@ -1,0 +1,187 @@
+/* bsarec_b200 — C ABI of the B200 (sm_100a) kernels behind BSARec's training and full-ranking
+ * evaluation hot path.  This is the drop-in boundary: plain pointers and sizes, no torch types.
+ *
+ * The reference has no FFI of its own (it is pure Python/PyTorch); each entry point below replaces a
+ * group of eager ATen call sites, cited as file:line relative to the reference's src/ directory.
+ *
+ * Conventions
+ *  - every function returns 0 on success, non-zero (a cudaError_t or -1) on failure; the message is
+ *    read with bsa_last_error_string().  Nothing throws, nothing synchronises the device.
+ *  - all pointers are DEVICE pointers unless the name ends in _host; tensors are dense row-major fp32,
+ *    ids are int64 (torch.long) exactly as the reference's DataLoader yields them.
+ *  - `stream` is a cudaStream_t passed as void* (torch.cuda.current_stream().cuda_stream).
+ *  - the caller owns every buffer; the library keeps no reference after the call returns and allocates
+ *    no device memory.  Scratch comes in through (workspace, workspace_bytes); the *_bytes() queries
+ *    give the sizes.
+ *  - dropout uses the stateless counter RNG restated in oracle/rng_ref.py; `seed` selects the stream of
+ *    one forward/backward pair, `training == 0` disables it (nn.Module.eval()).
+ */
+#ifndef BSAREC_B200_H
+#define BSAREC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
+#endif
+
+#define BSA_ABI_VERSION 1
+
+/* ------------------------------------------------------------------------------------------------
+ * Library
+ * ---------------------------------------------------------------------------------------------- */
+int bsa_abi_version(void);
+const char* bsa_last_error_string(void);
+/* kernels launched by this library since load (bench.py's "gpu_launches") */
+unsigned long long bsa_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * (1) Embedding: h0 = dropout(LayerNorm_tf(E[ids] + P[t]))
+ *     replaces SequentialRecModel.add_position_embedding  (model/_abstract_model.py:14-24)
+ *     and the custom LayerNorm                             (model/_modules.py:16-20)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    int B, L, d;               /* batch, max_seq_length, hidden_size */
+    int64_t item_size;         /* rows of the item table */
+    float p_hidden;            /* hidden_dropout_prob */
+    int training;
+    uint64_t seed;
+} bsa_embed_desc;
+
+/* out [B,L,d]; mean/rstd [B,L] are saved for the backward pass */
+int bsa_embed_ln_dropout_fwd(const bsa_embed_desc* desc, const int64_t* ids, const float* item_emb,
+                             const float* pos_emb, const float* ln_w, const float* ln_b, float* out,
+                             float* mean, float* rstd, void* stream);
+
+size_t bsa_embed_bwd_workspace_bytes(const bsa_embed_desc* desc);
+/* d_item_emb [item_size,d] is ACCUMULATED into (the dense cross-entropy gradient is already there; the
+ * gather adds rows for ids != 0 only — padding_idx=0, _abstract_model.py:10) through a sorted,
+ * atomic-free segmented sum: fixed summation order, bit-reproducible.
+ * d_pos_emb [L,d], d_ln_w [d], d_ln_b [d] are overwritten. */
+int bsa_embed_ln_dropout_bwd(const bsa_embed_desc* desc, const int64_t* ids, const float* item_emb,
+                             const float* pos_emb, const float* ln_w, const float* mean, const float* rstd,
+                             const float* d_out, float* d_item_emb, float* d_pos_emb, float* d_ln_w,
+                             float* d_ln_b, void* workspace, size_t workspace_bytes, void* stream);
+
+/* helper: stable (id, row) sort plan used by the scatter-add; exposed for tests.
+ * sorted_ids/sorted_rows are int32 [B*L]. */
+size_t bsa_sort_scatter_plan_bytes(int64_t n);
+int bsa_sort_scatter_plan(const int64_t* ids, int64_t n, int64_t item_size, void* plan, size_t plan_bytes,
+                          int32_t* sorted_ids, int32_t* sorted_rows, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (2) One BSARecBlock: filter branch + causal multi-head attention + alpha blend + GELU FFN
+ *     replaces BSARecBlock/BSARecLayer/FrequencyLayer.forward   (model/bsarec.py:62-104),
+ *              MultiHeadAttention.forward                        (model/_modules.py:108-140),
+ *              FeedForward.forward                               (model/_modules.py:61-69),
+ *              get_attention_mask (computed from ids in-kernel)  (model/_abstract_model.py:53-69)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    int B, L, d, H;            /* batch, sequence length, hidden size, attention heads */
+    int kept_bins;             /* c//2 + 1 rfft bins kept by the low-pass (bsarec.py:87) */
+    float alpha;               /* blend: alpha*filter + (1-alpha)*attention (bsarec.py:78) */
+    float p_hidden, p_attn;    /* hidden_dropout_prob, attention_probs_dropout_prob */
+    int training;
+    uint64_t seed;
+    int layer;                 /* block index: selects the dropout sites 1+4*layer .. 4+4*layer */
+} bsa_block_desc;
+
+/* nn.Linear weights are [out,in] row-major, exactly the state_dict tensors */
+typedef struct {
+    const float *sqrt_beta, *f_ln_w, *f_ln_b;                 /* filter_layer.{sqrt_beta,LayerNorm.*} */
+    const float *wq, *bq, *wk, *bk, *wv, *bv, *wo, *bo;       /* attention_layer.{query,key,value,dense} */
+    const float *a_ln_w, *a_ln_b;                             /* attention_layer.LayerNorm (nn.LayerNorm) */
+    const float *w1, *b1, *w2, *b2, *o_ln_w, *o_ln_b;         /* feed_forward.{dense_1,dense_2,LayerNorm} */
+} bsa_block_weights;
+
+typedef struct {
+    float *sqrt_beta, *f_ln_w, *f_ln_b;
+    float *wq, *bq, *wk, *bk, *wv, *bv, *wo, *bo;
+    float *a_ln_w, *a_ln_b;
+    float *w1, *b1, *w2, *b2, *o_ln_w, *o_ln_b;
+} bsa_block_grads;
+
+/* orthonormal basis C [L, r] of the exact real low-pass operator F = C C^T
+ * (== irfft(zero_{k>=kept}(rfft(x, norm='ortho')), norm='ortho'), bsarec.py:93-97) */
+int bsa_filter_rank(int L, int kept_bins);
+int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream);
+
+size_t bsa_block_saved_bytes(const bsa_block_desc* desc);      /* activations kept for backward */
+size_t bsa_block_workspace_bytes(const bsa_block_desc* desc);  /* scratch for fwd and bwd */
+
+/* x_out [B,L,d] = block(x_in); `saved` receives the activations backward needs (always required:
+ * inference may reuse one buffer for all layers). */
+int bsa_block_fwd(const bsa_block_desc* desc, const bsa_block_weights* w, const float* basis,
+                  const int64_t* ids, const float* x_in, float* x_out, void* saved, void* workspace,
+                  size_t workspace_bytes, void* stream);
+
+/* d_x_in [B,L,d] and every member of `g` are OVERWRITTEN with this block's gradients. */
+int bsa_block_bwd(const bsa_block_desc* desc, const bsa_block_weights* w, const float* basis,
+                  const int64_t* ids, const float* x_in, const void* saved, const float* d_x_out,
+                  float* d_x_in, const bsa_block_grads* g, void* workspace, size_t workspace_bytes,
+                  void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (3) Full-catalog cross-entropy without materialising the [B, item_size] logits
+ *     replaces BSARecModel.calculate_loss's matmul + CrossEntropyLoss   (model/bsarec.py:32-35)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    int B, d;
+    int64_t item_size;
+    int impl;                  /* 0 = auto, 1 = fp32 FFMA, 2 = tcgen05 3xTF32 */
+} bsa_ce_desc;
+
+size_t bsa_ce_workspace_bytes(const bsa_ce_desc* desc);
+/* seq_out [B,d] (last position), answers int64 [B].  loss: one float = mean_b(lse_b - logit_b[ans_b]);
+ * lse [B] is saved for the backward pass. */
+int bsa_ce_fwd(const bsa_ce_desc* desc, const float* seq_out, const float* item_emb, const int64_t* answers,
+               float* loss, float* lse, void* workspace, size_t workspace_bytes, void* stream);
+/* d_loss: device scalar (upstream gradient).  d_seq_out [B,d] overwritten; d_item_emb [item_size,d]
+ * OVERWRITTEN with the dense gradient (every row, including row 0). */
+int bsa_ce_bwd(const bsa_ce_desc* desc, const float* seq_out, const float* item_emb, const int64_t* answers,
+               const float* lse, const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace,
+               size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (4) Full-catalog scoring + history masking + per-user top-k (+ cross-shard merge)
+ *     replaces Trainer.predict_full                (trainers.py:62-68) and the numpy masking /
+ *              argpartition / argsort eval branch   (trainers.py:130-149)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    int B, d, k;               /* users in the batch, hidden size, list length (<= 128) */
+    int64_t shard_rows;        /* rows of this item-table shard */
+    int64_t shard_offset;      /* global id of the shard's row 0 */
+    int impl;                  /* 0 = auto, 1 = fp32 FFMA, 2 = tcgen05 3xTF32 */
+} bsa_topk_desc;
+
+size_t bsa_score_topk_workspace_bytes(const bsa_topk_desc* desc);
+/* History is CSR over the batch rows: hist_indptr int64 [B+1], hist_indices int64 (GLOBAL item ids, sorted
+ * ascending within a row).  History items score exactly 0.0f (trainers.py:134), they are not removed.
+ * Outputs: top_val fp32 [B,k], top_idx int64 [B,k] (global ids), descending score, ties by ascending id;
+ * unused slots (fewer than k candidates in the shard) hold -inf / -1. */
+int bsa_score_topk(const bsa_topk_desc* desc, const float* seq_out, const float* item_shard,
+                   const int64_t* hist_indptr, const int64_t* hist_indices, float* top_val, int64_t* top_idx,
+                   void* workspace, size_t workspace_bytes, void* stream);
+/* merge G candidate lists [G,B,k] (one per shard) into [B,k] */
+int bsa_topk_merge(const float* cand_val, const int64_t* cand_idx, int G, int B, int k, float* top_val,
+                   int64_t* top_idx, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Small utilities shared by the host wrappers
+ * ---------------------------------------------------------------------------------------------- */
+/* dst [B,d] = src[:, L-1, :] */
+int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* stream);
+/* dst [B,L,d] = 0 except dst[:, L-1, :] = src [B,d] */
+int bsa_scatter_last(const float* src, float* dst, int B, int L, int d, void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSAREC_B200_H */

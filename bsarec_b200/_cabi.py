@@ -61,6 +61,11 @@ SIGNATURES = {
     "bsa_abi_version": (_I, []),
     "bsa_last_error_string": (C.c_char_p, []),
     "bsa_launch_count": (C.c_ulonglong, []),
+    "bsa_profile_enable": (None, [_I]),
+    "bsa_profile_reset": (None, []),
+    "bsa_profile_num_tags": (_I, []),
+    "bsa_profile_get": (_I, [_I, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                            C.POINTER(C.c_longlong)]),
     "bsa_embed_ln_dropout_fwd": (_I, [C.POINTER(EmbedDesc)] + [_VP] * 9),
     "bsa_embed_bwd_workspace_bytes": (_SZ, [C.POINTER(EmbedDesc)]),
     "bsa_embed_ln_dropout_bwd": (_I, [C.POINTER(EmbedDesc)] + [_VP] * 12 + [_SZ, _VP]),
@@ -114,3 +119,21 @@ def check(rc, what=""):
 
 def launch_count() -> int:
     return int(load().bsa_launch_count())
+
+
+def profile(on: bool):
+    lib = load()
+    lib.bsa_profile_reset()
+    lib.bsa_profile_enable(int(on))
+
+
+def profile_results():
+    """{tag: {"ms": total device ms, "work": algorithmic FLOPs or bytes, "launches": n}} for tags that ran."""
+    lib = load()
+    out = {}
+    for t in range(lib.bsa_profile_num_tags()):
+        name, ms, work, n = C.c_char_p(), C.c_double(), C.c_double(), C.c_longlong()
+        check(lib.bsa_profile_get(t, C.byref(name), C.byref(ms), C.byref(work), C.byref(n)), "bsa_profile_get")
+        if n.value:
+            out[name.value.decode()] = {"ms": ms.value, "work": work.value, "launches": n.value}
+    return out

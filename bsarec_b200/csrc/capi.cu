@@ -7,6 +7,8 @@
 #include "umma_engine.cuh"
 
 #include <cstdarg>
+#include <utility>
+#include <vector>
 
 namespace bsa {
 
@@ -30,6 +32,53 @@ size_t block_workspace_bytes(const bsa_block_desc& c);
 
 static inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
 
+// ---- kernel timing registry
+int g_profile_on = 0;
+namespace {
+struct ProfRec {
+    const char* name;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+    cudaEvent_t open = nullptr;
+    double ms = 0, work = 0;
+    long long launches = 0;
+};
+ProfRec g_prof[PROF_NUM_TAGS] = {{"gemm_simt"}, {"ce_fwd_umma"}, {"ce_bwd_umma"}, {"score_topk_umma"}, {"linear_umma"},
+                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}};
+std::vector<cudaEvent_t> g_event_pool;
+cudaEvent_t get_event() {
+    if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+void drain(ProfRec& r) {
+    for (auto& pr : r.pending) {
+        cudaEventSynchronize(pr.second);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) r.ms += ms;
+        g_event_pool.push_back(pr.first);
+        g_event_pool.push_back(pr.second);
+    }
+    r.pending.clear();
+}
+}  // namespace
+void prof_begin(int tag, cudaStream_t st) {
+    ProfRec& r = g_prof[tag];
+    r.open = get_event();
+    cudaEventRecord(r.open, st);
+}
+void prof_end(int tag, cudaStream_t st, double work) {
+    ProfRec& r = g_prof[tag];
+    if (!r.open) return;
+    cudaEvent_t e = get_event();
+    cudaEventRecord(e, st);
+    r.pending.emplace_back(r.open, e);
+    r.open = nullptr;
+    r.work += work;
+    r.launches += 1;
+    if (r.pending.size() > 4096) drain(r);
+}
+
 }  // namespace bsa
 
 using namespace bsa;
@@ -39,6 +88,22 @@ extern "C" {
 int bsa_abi_version(void) { return BSA_ABI_VERSION; }
 const char* bsa_last_error_string(void) { return g_err; }
 unsigned long long bsa_launch_count(void) { return g_launch_count; }
+
+void bsa_profile_enable(int on) { g_profile_on = on ? 1 : 0; }
+void bsa_profile_reset(void) {
+    for (auto& r : g_prof) { drain(r); r.ms = 0; r.work = 0; r.launches = 0; }
+}
+int bsa_profile_num_tags(void) { return PROF_NUM_TAGS; }
+int bsa_profile_get(int tag, const char** name, double* ms, double* work, long long* launches) {
+    BSA_REQUIRE(tag >= 0 && tag < PROF_NUM_TAGS, "bsa_profile_get: bad tag %d", tag);
+    ProfRec& r = g_prof[tag];
+    drain(r);
+    if (name) *name = r.name;
+    if (ms) *ms = r.ms;
+    if (work) *work = r.work;
+    if (launches) *launches = r.launches;
+    return 0;
+}
 
 // ------------------------------------------------------------------------------------------ embedding
 int bsa_embed_ln_dropout_fwd(const bsa_embed_desc* c, const int64_t* ids, const float* item_emb, const float* pos_emb,

@@ -38,6 +38,22 @@ extern unsigned long long g_launch_count;      // kernels launched by this libra
 
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// ---------------------------------------------------------------------------- kernel timing (bench.py roofline)
+// When enabled through bsa_profile_enable(1), tagged launches are bracketed by CUDA events on the launching
+// stream; bsa_profile_get() synchronises those events and reports total device time, algorithmic work
+// (FLOPs or bytes, supplied by the launcher) and launch count per tag.  Off by default: zero overhead.
+extern int g_profile_on;
+void prof_begin(int tag, cudaStream_t st);
+void prof_end(int tag, cudaStream_t st, double work);
+enum ProfTag : int { PROF_GEMM_SIMT = 0, PROF_CE_FWD_UMMA, PROF_CE_BWD_UMMA, PROF_TOPK_UMMA, PROF_LINEAR_UMMA,
+                     PROF_EMBED_FWD, PROF_EMBED_BWD, PROF_SCATTER_ADD, PROF_NUM_TAGS };
+
+struct ProfScope {
+    int tag; cudaStream_t st; double work;
+    ProfScope(int t, cudaStream_t s, double w) : tag(t), st(s), work(w) { if (g_profile_on) prof_begin(tag, st); }
+    ~ProfScope() { if (g_profile_on) prof_end(tag, st, work); }
+};
+
 // ---------------------------------------------------------------------------- dropout RNG
 // Stateless counter RNG, restated bit-for-bit in oracle/rng_ref.py.
 struct Dropout {

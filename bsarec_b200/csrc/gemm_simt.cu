@@ -188,7 +188,11 @@ int launch_gemm(const GemmP& p, cudaStream_t st) {
     const int BN = p.N <= 64 ? 64 : 128;
     dim3 grid(cdiv(p.M, 128), cdiv(p.N, BN), p.splitk > 1 ? p.splitk : p.batch);
     BSA_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "launch_gemm: grid too large (M=%d batch=%d)", p.M, p.batch);
-    int rc = BN == 64 ? dispatch<64>(p, grid, st) : dispatch<128>(p, grid, st);
+    int rc;
+    {
+        ProfScope prof(PROF_GEMM_SIMT, st, 2.0 * p.M * p.N * (double)p.K * p.batch);
+        rc = BN == 64 ? dispatch<64>(p, grid, st) : dispatch<128>(p, grid, st);
+    }
     if (rc) return rc;
     if (p.splitk > 1) {
         const long long MN = (long long)p.M * p.N;

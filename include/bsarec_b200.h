@@ -38,6 +38,13 @@ int bsa_abi_version(void);
 const char* bsa_last_error_string(void);
 /* kernels launched by this library since load (bench.py's "gpu_launches") */
 unsigned long long bsa_launch_count(void);
+/* Per-kernel device timing for the roofline report: when enabled, tagged launches are bracketed by CUDA
+ * events on the launching stream.  bsa_profile_get synchronises them and returns the tag's name, total
+ * device milliseconds, algorithmic work (FLOPs or bytes as the tag defines) and launch count. */
+void bsa_profile_enable(int on);
+void bsa_profile_reset(void);
+int bsa_profile_num_tags(void);
+int bsa_profile_get(int tag, const char** name, double* ms, double* work, long long* launches);
 
 /* ------------------------------------------------------------------------------------------------
  * (1) Embedding: h0 = dropout(LayerNorm_tf(E[ids] + P[t]))

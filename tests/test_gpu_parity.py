@@ -20,16 +20,19 @@ def grads_of(model):
     return {n: p.grad.detach().cpu() for n, p in model.named_parameters()}
 
 
-def check_grads(got, ref64, ref32=None, tol=TOL):
+def check_grads(got, ref64, ref32, tol=TOL):
+    """got: CUDA grads; ref64: fp64 oracle; ref32: the fp32 reference (golden) or the fp32 oracle.
+    Bar: within tol of the fp32 reference, or within tol of the fp64 value; on cancellation-heavy tensors
+    (key.weight: softmax shift-invariance) where the fp32 reference is itself ~1e-4 from the fp64 value, at
+    least as close to the fp64 value as twice the fp32 reference's own distance."""
     for k in ref64:
         if k.endswith("key.bias"):     # analytically zero (SURVEY Appendix B #13): absolute bound
             assert got[k].abs().max() < 1e-6, k
             continue
-        e = rel_err(got[k], ref64[k])
-        # the fp32 reference itself can be up to ~1e-4 from the fp64 value on cancellation-heavy tensors;
-        # accept the CUDA result when it is within tol of either
-        e32 = rel_err(got[k], ref32[k]) if ref32 is not None else e
-        assert min(e, e32) < tol, (k, e, e32)
+        e64 = rel_err(got[k], ref64[k])
+        e32 = rel_err(got[k], ref32[k])
+        own = rel_err(ref32[k], ref64[k])
+        assert min(e64, e32) < max(tol, 2 * own), (k, e64, e32, own)
 
 
 @pytest.mark.parametrize("name", SMALL)
@@ -78,8 +81,9 @@ def test_train_mode_dropout_masks_match_oracle_rng(p_hidden, p_attn, cuda_device
     loss.backward()
     l64, g64 = oracle.loss_and_grads({k: v.double() for k, v in P.items()}, ids, answers, cfg, train=True,
                                      plan=oracle.DropoutPlan(seed), use_fft=False)
+    _, g32 = oracle.loss_and_grads(P, ids, answers, cfg, train=True, plan=oracle.DropoutPlan(seed))
     assert abs(loss.item() - float(l64)) < TOL * abs(float(l64))
-    check_grads(grads_of(model), g64)
+    check_grads(grads_of(model), g64, g32)
     outs = model.predict(ids.to(cuda_device), None, all_sequence_output=True)       # train mode, same seed
     ref = oracle.encode({k: v.double() for k, v in P.items()}, ids, cfg, train=True, plan=oracle.DropoutPlan(seed), use_fft=False)
     for a, b in zip(outs, ref):
@@ -114,8 +118,9 @@ def test_varying_batch_and_short_sequence_length(cuda_device):
         loss = model.calculate_loss(ids.to(cuda_device), answers.to(cuda_device), None, None, None)
         loss.backward()
         l64, g64 = oracle.loss_and_grads({k: v.double() for k, v in P.items()}, ids, answers, cfg, use_fft=False)
+        _, g32 = oracle.loss_and_grads(P, ids, answers, cfg)
         assert abs(loss.item() - float(l64)) < TOL * abs(float(l64))
-        check_grads(grads_of(model), g64)
+        check_grads(grads_of(model), g64, g32)
 
 
 @pytest.mark.parametrize("name", SMALL)

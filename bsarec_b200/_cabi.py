@@ -84,6 +84,8 @@ SIGNATURES = {
     "bsa_score_topk_workspace_bytes": (_SZ, [C.POINTER(TopkDesc)]),
     "bsa_score_topk": (_I, [C.POINTER(TopkDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_topk_merge": (_I, [_VP, _VP, _I, _I, _I, _VP, _VP, _VP]),
+    "bsa_gemm_workspace_bytes": (_SZ, [_I, _I, _I, _I64, _I64, _I, _I]),
+    "bsa_gemm": (_I, [_I, _I, _I, _I, _VP, _I64, _I, _VP, _I64, _I, _VP, _I64, _VP, C.c_float, _I, _VP, _SZ, _VP]),
     "bsa_gather_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
     "bsa_scatter_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
 }

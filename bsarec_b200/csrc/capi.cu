@@ -5,6 +5,7 @@
 #include "rowwise.cuh"
 #include "ce_topk.cuh"
 #include "umma_engine.cuh"
+#include "gemm_simt.cuh"
 
 #include <cstdarg>
 #include <utility>
@@ -248,6 +249,28 @@ int bsa_score_topk(const bsa_topk_desc* c, const float* seq_out, const float* it
 int bsa_topk_merge(const float* cand_val, const int64_t* cand_idx, int G, int B, int k, float* top_val, int64_t* top_idx, void* stream) {
     BSA_REQUIRE(cand_val && cand_idx && top_val && top_idx, "bsa_topk_merge: null argument");
     return topk_merge(cand_val, (const long long*)cand_idx, G, B, k, top_val, (long long*)top_idx, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------ generic GEMM
+size_t bsa_gemm_workspace_bytes(int M, int N, int K, int64_t lda, int64_t ldb, int a_mn, int b_mn) {
+    const long long a_rows = a_mn ? K : M, b_rows = b_mn ? K : N;
+    return umma_gemm_workspace_bytes(a_rows * lda, b_rows * ldb, M, N, K);
+}
+
+int bsa_gemm(int impl, int M, int N, int K, const float* A, int64_t lda, int a_mn, const float* B, int64_t ldb, int b_mn,
+             float* C, int64_t ldc, const float* bias, float alpha, int accumulate, void* workspace, size_t workspace_bytes,
+             void* stream) {
+    BSA_REQUIRE(A && B && C, "bsa_gemm: null argument");
+    if (impl == 1) {
+        GemmP p;
+        p.A = A; p.B = B; p.C = C; p.M = M; p.N = N; p.K = K; p.lda = (int)lda; p.ldb = (int)ldb; p.ldc = (int)ldc;
+        p.a_kmajor = !a_mn; p.b_kmajor = !b_mn; p.bias = bias; p.alpha = alpha; p.accumulate = accumulate;
+        return launch_gemm(p, (cudaStream_t)stream);
+    }
+    BSA_REQUIRE(workspace && workspace_bytes >= bsa_gemm_workspace_bytes(M, N, K, lda, ldb, a_mn, b_mn), "bsa_gemm: workspace too small");
+    const long long a_rows = a_mn ? K : M, a_cols = a_mn ? M : K, b_rows = b_mn ? K : N, b_cols = b_mn ? N : K;
+    return umma_gemm(M, N, K, A, a_rows, a_cols, lda, a_mn != 0, B, b_rows, b_cols, ldb, b_mn != 0, C, ldc, bias, 0, nullptr,
+                     nullptr, alpha, accumulate, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------ utilities

@@ -1,24 +1,617 @@
-// tcgen05 (UMMA) 3xTF32 engine — placeholder until the kernels land: reports "unsupported" so the
-// C ABI routes to the fp32 FFMA paths.
+// tcgen05 3xTF32 engine: epilogues, launchers and the cross-entropy / scoring / linear entry points built on
+// umma_gemm.cuh.
 #include "umma_engine.cuh"
+#include "umma_gemm.cuh"
+#include "ce_topk.cuh"
 
 namespace bsa {
 
-bool umma_ce_supported(int, int, long long) { return false; }
-size_t umma_ce_workspace_bytes(int, int, long long) { return 0; }
-int umma_ce_fwd(int, int, long long, const float*, const float*, const long long*, float*, float*, void*, size_t, cudaStream_t) {
-    set_error("tcgen05 cross-entropy path not built");
-    return -1;
+using namespace umma;
+
+namespace {
+
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+    hi = __uint_as_float(h);
+    lo = x - hi;                       // exact in fp32
 }
-int umma_ce_bwd(int, int, long long, const float*, const float*, const long long*, const float*, const float*, float*, float*, void*, size_t, cudaStream_t) {
-    set_error("tcgen05 cross-entropy path not built");
-    return -1;
+
+__global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, long long n) {
+    const long long n4 = n >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = reinterpret_cast<const float4*>(x)[i];
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        reinterpret_cast<float4*>(hi)[i] = h;
+        reinterpret_cast<float4*>(lo)[i] = l;
+    }
+    const long long t = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) split_tf32(x[t], hi[t], lo[t]);
 }
-bool umma_topk_supported(int, int, int, long long) { return false; }
-size_t umma_topk_workspace_bytes(int, int, int, long long) { return 0; }
-int umma_score_topk(int, int, int, long long, long long, const float*, const float*, const long long*, const long long*, float*, long long*, void*, size_t, cudaStream_t) {
-    set_error("tcgen05 scoring path not built");
-    return -1;
+
+// ============================================================================ epilogues
+// ---- plain store: C = alpha*acc (+bias) (act) (+C)   or raw split-K partials
+struct StoreParams {
+    float* C; long long ldc; const float* bias; int act; float* aux_out; const float* aux_in; float alpha;
+    int accumulate; float* partial;
+};
+template <int BN>
+struct EpiStore {
+    using Params = StoreParams;
+    static constexpr int SMEM_BYTES = 0;
+    const Params& p; const GemmCore& g; int rit;
+    __device__ EpiStore(const Params& p_, const GemmCore& g_, unsigned char*, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {}
+    __device__ void tile(uint32_t acc, const TileCoord& tc) {
+        const long long row = (long long)tc.m * BM + rit;
+        const int n0 = tc.n * BN;
+        const bool row_ok = row < g.M;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(acc + c0, v);
+            if (!row_ok || n0 + c0 >= g.N) continue;
+            if (p.partial) {
+                float* dst = p.partial + ((long long)tc.split * g.M + row) * g.N + n0 + c0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (n0 + c0 + j < g.N) dst[j] = v[j];
+                continue;
+            }
+            const long long off = row * p.ldc + n0 + c0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                float x = p.alpha * v[j];
+                const int col = n0 + c0 + j;
+                if (col < g.N) {
+                    if (p.bias) x += __ldg(p.bias + col);
+                    if (p.act == 1) { p.aux_out[off + j] = x; x = gelu_erf(x); }
+                    else if (p.act == 2) x *= gelu_erf_grad(p.aux_in[off + j]);
+                    if (p.accumulate) x += p.C[off + j];
+                }
+                v[j] = x;
+            }
+            if ((p.ldc & 3) == 0 && n0 + c0 + 32 <= g.N && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0)) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(p.C + off + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (n0 + c0 + j < g.N) p.C[off + j] = v[j];
+            }
+        }
+    }
+    __device__ void finish() {}
+};
+
+// ---- online log-sum-exp over the CTA's strip of item tiles (thread = user row)
+template <int BN>
+struct EpiLse {
+    struct Params { const long long* answers; float* part_m; float* part_s; float* tgt; };
+    static constexpr int SMEM_BYTES = 0;
+    const Params& p; const GemmCore& g; int rit;
+    float m = -INFINITY, s = 0.f;
+    long long ans = -1;
+    __device__ EpiLse(const Params& p_, const GemmCore& g_, unsigned char*, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {
+        const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
+        if (row < g.M) ans = p.answers[row];
+    }
+    __device__ void tile(uint32_t acc, const TileCoord& tc) {
+        const int n0 = tc.n * BN;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(acc + c0, v);
+            if (n0 + c0 >= g.N) continue;
+            float cm = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (n0 + c0 + j >= g.N) v[j] = -INFINITY;
+                cm = fmaxf(cm, v[j]);
+            }
+            const float mn = fmaxf(m, cm);
+            float acc_s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc_s += expf(v[j] - mn);
+            s = s * expf(m - mn) + acc_s;          // m == -inf on the first chunk: exp(-inf) = 0
+            m = mn;
+            const long long a = ans - (n0 + c0);
+            if (a >= 0 && a < 32) {
+                float t = 0.f;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j == (int)a) t = v[j];
+                const long long row = (long long)tc.m * BM + rit;
+                p.tgt[row] = t;
+            }
+        }
+    }
+    __device__ void finish() {
+        const int m_tile = blockIdx.x % g.m_tiles, strip = blockIdx.x / g.m_tiles;
+        const long long row = (long long)m_tile * BM + rit;
+        if (row < g.M) { p.part_m[(long long)strip * g.M + row] = m; p.part_s[(long long)strip * g.M + row] = s; }
+    }
+};
+
+// ---- per-user running top-k over the CTA's strip (thread = user row; sorted list in shared memory)
+template <int BN>
+struct EpiTopk {
+    struct Params {
+        const long long* indptr; const long long* indices; long long offset; int k;
+        float* cand_val; long long* cand_idx;      // [nstrips][B][k]
+    };
+    static constexpr int KMAX = 32;
+    static constexpr int SMEM_BYTES = KMAX * 128 * 8;
+    const Params& p; const GemmCore& g; int rit;
+    float* lv; int* li;
+    float thr = -INFINITY; int thr_i = 0x7fffffff;
+    long long hlo = 0, hhi = 0;
+    __device__ EpiTopk(const Params& p_, const GemmCore& g_, unsigned char* smem, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {
+        lv = reinterpret_cast<float*>(smem);
+        li = reinterpret_cast<int*>(smem + KMAX * 128 * 4);
+        for (int i = 0; i < p.k; ++i) { lv[i * 128 + rit] = -INFINITY; li[i * 128 + rit] = 0x7fffffff; }
+        const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
+        if (row < g.M && p.indptr) { hlo = p.indptr[row]; hhi = p.indptr[row + 1]; }
+    }
+    __device__ __forceinline__ bool before(float va, int ia, float vb, int ib) const { return va > vb || (va == vb && ia < ib); }
+    __device__ void insert(float v, int id) {
+        long long lo = hlo, hi = hhi;                    // history items are scored 0.0 elsewhere: skip them here
+        const long long gid = p.offset + id;
+        while (lo < hi) {
+            const long long mid = (lo + hi) >> 1;
+            const long long hv = p.indices[mid];
+            if (hv == gid) return;
+            if (hv < gid) lo = mid + 1; else hi = mid;
+        }
+        int q = p.k - 1;
+        while (q > 0 && before(v, id, lv[(q - 1) * 128 + rit], li[(q - 1) * 128 + rit])) {
+            lv[q * 128 + rit] = lv[(q - 1) * 128 + rit];
+            li[q * 128 + rit] = li[(q - 1) * 128 + rit];
+            --q;
+        }
+        lv[q * 128 + rit] = v; li[q * 128 + rit] = id;
+        thr = lv[(p.k - 1) * 128 + rit]; thr_i = li[(p.k - 1) * 128 + rit];
+    }
+    __device__ void tile(uint32_t acc, const TileCoord& tc) {
+        const int n0 = tc.n * BN;
+        const bool row_ok = (long long)tc.m * BM + rit < g.M;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(acc + c0, v);
+            if (!row_ok || n0 + c0 >= g.N) continue;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int id = n0 + c0 + j;
+                if (id < g.N && before(v[j], id, thr, thr_i)) insert(v[j], id);
+            }
+        }
+    }
+    __device__ void finish() {
+        const int m_tile = blockIdx.x % g.m_tiles, strip = blockIdx.x / g.m_tiles;
+        const long long row = (long long)m_tile * BM + rit;
+        if (row >= g.M) return;
+        for (int i = 0; i < p.k; ++i) {
+            const long long o = ((long long)strip * g.M + row) * p.k + i;
+            const int id = li[i * 128 + rit];
+            p.cand_val[o] = lv[i * 128 + rit];
+            p.cand_idx[o] = id == 0x7fffffff ? -1 : p.offset + id;
+        }
+    }
+};
+
+// ---- CE gradient of one logits chunk: G = (softmax - onehot) * d_loss / B, emitted as (hi, lo) in both
+//      orientations so the two gradient GEMMs read K-major A operands
+template <int BN>
+struct EpiCeGrad {
+    struct Params {
+        const float* lse; const long long* answers; const float* d_loss; long long n_base;
+        float *g_hi, *g_lo; long long ldg;          // [B][ldg]   (cols = chunk items)
+        float *gt_hi, *gt_lo; long long ldgt;       // [chunk items][ldgt] (cols = users)
+    };
+    static constexpr int SMEM_BYTES = 0;
+    const Params& p; const GemmCore& g; int rit;
+    __device__ EpiCeGrad(const Params& p_, const GemmCore& g_, unsigned char*, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {}
+    __device__ void tile(uint32_t acc, const TileCoord& tc) {
+        const long long row = (long long)tc.m * BM + rit;
+        const int n0 = tc.n * BN;
+        const bool row_ok = row < g.M;
+        const float l = row_ok ? p.lse[row] : 0.f;
+        const long long a = row_ok ? p.answers[row] - p.n_base : -1;
+        const float scale = __ldg(p.d_loss) / (float)g.M;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(acc + c0, v);
+            if (!row_ok || n0 + c0 >= g.N) continue;
+            float hi[32], lo[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                float pr = expf(v[j] - l);
+                if (a == n0 + c0 + j) pr -= 1.0f;
+                split_tf32(pr * scale, hi[j], lo[j]);
+            }
+            const int nv = min(32, g.N - (n0 + c0));
+            float* gh = p.g_hi + row * p.ldg + n0 + c0;
+            float* gl = p.g_lo + row * p.ldg + n0 + c0;
+            if (nv == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    *reinterpret_cast<float4*>(gh + j) = make_float4(hi[j], hi[j + 1], hi[j + 2], hi[j + 3]);
+                    *reinterpret_cast<float4*>(gl + j) = make_float4(lo[j], lo[j + 1], lo[j + 2], lo[j + 3]);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j < nv) { gh[j] = hi[j]; gl[j] = lo[j]; }
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (j < nv) {
+                p.gt_hi[(long long)(n0 + c0 + j) * p.ldgt + row] = hi[j];
+                p.gt_lo[(long long)(n0 + c0 + j) * p.ldgt + row] = lo[j];
+            }
+        }
+    }
+    __device__ void finish() {}
+};
+
+// ============================================================================ host side
+struct Operand {           // a (hi, lo) pair as stored in global memory
+    const float* hi; const float* lo;
+    long long rows, cols, pitch;      // row-major [rows, cols]
+    bool mn;                          // true: rows index K (contraction), cols index M/N
+};
+
+int make_core(GemmCore& g, int M, int N, int K, const Operand& A, const Operand& B, int BN, int sched, int splits) {
+    g.M = M; g.N = N; g.K = K;
+    g.m_tiles = cdiv(M, BM); g.n_tiles = cdiv(N, BN);
+    g.k_blocks_total = cdiv(K, BK);
+    if (splits < 1) splits = 1;
+    if (splits > g.k_blocks_total) splits = g.k_blocks_total;
+    g.k_blocks_per_split = cdiv(g.k_blocks_total, splits);
+    g.splits = cdiv(g.k_blocks_total, g.k_blocks_per_split);      // every split owns >= 1 k-block
+    g.sched = sched;
+    int rc;
+    if ((rc = make_tmap_2d(&g.a_hi, A.hi, A.rows, A.cols, A.pitch, A.mn ? BK : BM, A.mn))) return rc;
+    if ((rc = make_tmap_2d(&g.a_lo, A.lo, A.rows, A.cols, A.pitch, A.mn ? BK : BM, A.mn))) return rc;
+    if ((rc = make_tmap_2d(&g.b_hi, B.hi, B.rows, B.cols, B.pitch, B.mn ? BK : BN, B.mn))) return rc;
+    if ((rc = make_tmap_2d(&g.b_lo, B.lo, B.rows, B.cols, B.pitch, B.mn ? BK : BN, B.mn))) return rc;
+    return 0;
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN, class Epi>
+int launch(const GemmCore& g, const typename Epi::Params& ep, int grid, cudaStream_t st) {
+    constexpr int smem = gemm_smem_bytes<BN, STAGES>(Epi::SMEM_BYTES);
+    static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
+    static bool configured = false;
+    auto* kern = umma_gemm_kernel<BN, STAGES, A_MN, B_MN, Epi>;
+    if (!configured) {
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    kern<<<grid, GEMM_THREADS, smem, st>>>(g, ep);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int num_sms() {
+    static int n = 0;
+    if (!n) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+template <int BN, int STAGES, class Epi>
+int launch_major(const GemmCore& g, const typename Epi::Params& ep, bool a_mn, bool b_mn, int grid, cudaStream_t st) {
+    if (!a_mn && !b_mn) return launch<BN, STAGES, false, false, Epi>(g, ep, grid, st);
+    if (!a_mn && b_mn) return launch<BN, STAGES, false, true, Epi>(g, ep, grid, st);
+    if (a_mn && !b_mn) return launch<BN, STAGES, true, false, Epi>(g, ep, grid, st);
+    return launch<BN, STAGES, true, true, Epi>(g, ep, grid, st);
+}
+
+__global__ void splitk_reduce_kernel2(const float* __restrict__ part, float* __restrict__ C, long long MN, int N, long long ldc,
+                                      int splits, float alpha, int accumulate) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= MN) return;
+    float s = 0.f;
+    for (int k = 0; k < splits; ++k) s += part[(long long)k * MN + i];
+    const long long m = i / N, n = i - m * N;
+    float v = alpha * s;
+    if (accumulate) v += C[m * ldc + n];
+    C[m * ldc + n] = v;
+}
+
+int do_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st) {
+    if (n == 0) return 0;
+    long long blocks = (n / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    split_tf32_kernel<<<(int)blocks, 256, 0, st>>>(x, hi, lo, n);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+inline size_t al(size_t x) { return (x + 1023) / 1024 * 1024; }
+
+}  // namespace
+
+// ============================================================================ generic GEMM (plain store epilogue)
+// C[M,N] = alpha * A B^T (+bias)(act)(+C).  Operands are given UNSPLIT; (hi, lo) pairs are produced into `ws`.
+size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, int N, int K) {
+    const int splits_max = 64;
+    return 2 * al((size_t)a_elems * 4) + 2 * al((size_t)b_elems * 4) + al((size_t)splits_max * M * N * 4) + 4096;
+}
+
+int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a_cols, long long lda, bool a_mn,
+              const float* B, long long b_rows, long long b_cols, long long ldb, bool b_mn, float* C, long long ldc,
+              const float* bias, int act, float* aux_out, const float* aux_in, float alpha, int accumulate, void* ws,
+              size_t ws_bytes, cudaStream_t st) {
+    BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
+    char* p = (char*)ws;
+    const size_t ab = al((size_t)a_rows * lda * 4), bb = al((size_t)b_rows * ldb * 4);
+    float* a_hi = (float*)p; p += ab;
+    float* a_lo = (float*)p; p += ab;
+    float* b_hi = (float*)p; p += bb;
+    float* b_lo = (float*)p; p += bb;
+    float* partial = (float*)p;
+    int rc;
+    if ((rc = do_split(A, a_hi, a_lo, a_rows * lda, st))) return rc;
+    if ((rc = do_split(B, b_hi, b_lo, b_rows * ldb, st))) return rc;
+    Operand oa{a_hi, a_lo, a_rows, a_cols, lda, a_mn}, ob{b_hi, b_lo, b_rows, b_cols, ldb, b_mn};
+    const int BN = N > 128 ? 256 : 128;
+    const int tiles = cdiv(M, BM) * cdiv(N, BN);
+    int splits = 1;
+    if (tiles < num_sms() && !bias && act == 0) {
+        splits = num_sms() / tiles;
+        const int kb = cdiv(K, BK);
+        if (splits > kb / 4) splits = kb / 4;
+        if (splits > 64) splits = 64;
+        if (splits < 1) splits = 1;
+    }
+    GemmCore g;
+    if ((rc = make_core(g, M, N, K, oa, ob, BN, SCHED_N_FASTEST, splits))) return rc;
+    StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr};
+    if (g.splits > 1) {
+        BSA_REQUIRE((size_t)(p - (char*)ws) + (size_t)g.splits * M * N * 4 <= ws_bytes, "umma_gemm: workspace too small for split-K");
+        ep.partial = partial;
+    }
+    const long long total = (long long)g.m_tiles * g.n_tiles * g.splits;
+    const int grid = (int)(total < num_sms() ? total : num_sms());
+    {
+        ProfScope prof(PROF_LINEAR_UMMA, st, 2.0 * M * N * (double)K);
+        if (BN == 256) rc = launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
+        else rc = launch_major<128, 3, EpiStore<128>>(g, ep, a_mn, b_mn, grid, st);
+    }
+    if (rc) return rc;
+    if (g.splits > 1) {
+        const long long MN = (long long)M * N;
+        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(partial, C, MN, N, ldc, g.splits, alpha, accumulate);
+        BSA_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+// ============================================================================ cross-entropy
+namespace {
+constexpr int CE_BN = 128;
+constexpr int CE_STAGES = 3;
+
+struct CeWs {
+    float *s_hi, *s_lo, *e_hi, *e_lo, *part_m, *part_s, *tgt;
+    float *g_hi, *g_lo, *gt_hi, *gt_lo, *partial;
+    int nstrips, chunk; long long ldgt;
+    size_t bytes;
+};
+
+int ce_strips(int B) {
+    const int m_tiles = cdiv(B, BM);
+    int s = num_sms() / m_tiles;
+    return s < 1 ? 1 : s;
+}
+
+int ce_bwd_chunk(int B, long long N) {
+    // one wave of 128 x 256 logits tiles per chunk, and small enough that G, G^T (hi, lo) stay in L2
+    const int m_tiles = cdiv(B, BM);
+    long long per_wave = (long long)(num_sms() / m_tiles > 0 ? num_sms() / m_tiles : 1) * 256;
+    long long cap = (80ll << 20) / (16ll * (B > 0 ? B : 1));         // 4 arrays x 4 B per element <= 80 MiB (L2 is 126 MB)
+    long long c = per_wave;
+    while (c * 2 <= cap) c *= 2;
+    if (c > cap && cap >= 256) c = cap / 256 * 256;
+    if (c > N) c = (N + 31) / 32 * 32;
+    if (c < 32) c = 32;
+    return (int)c;
+}
+
+CeWs carve_ce(void* ws, int B, int d, long long N, bool bwd) {
+    CeWs w;
+    char* p = (char*)ws;
+    auto take = [&](size_t bytes) { char* r = p; p += al(bytes); return (float*)r; };
+    w.s_hi = take((size_t)B * d * 4); w.s_lo = take((size_t)B * d * 4);
+    w.e_hi = take((size_t)N * d * 4); w.e_lo = take((size_t)N * d * 4);
+    w.nstrips = ce_strips(B);
+    w.part_m = take((size_t)w.nstrips * B * 4); w.part_s = take((size_t)w.nstrips * B * 4);
+    w.tgt = take((size_t)B * 4);
+    w.chunk = ce_bwd_chunk(B, N);
+    w.ldgt = (B + 3) / 4 * 4;
+    if (bwd) {
+        w.g_hi = take((size_t)B * w.chunk * 4); w.g_lo = take((size_t)B * w.chunk * 4);
+        w.gt_hi = take((size_t)w.chunk * w.ldgt * 4); w.gt_lo = take((size_t)w.chunk * w.ldgt * 4);
+        w.partial = take((size_t)64 * B * d * 4);
+    }
+    w.bytes = (size_t)(p - (char*)ws) + 1024;
+    return w;
+}
+
+__global__ void ce_combine_kernel(const float* __restrict__ part_m, const float* __restrict__ part_s,
+                                  const float* __restrict__ tgt, int nstrips, int B, float* __restrict__ lse,
+                                  float* __restrict__ loss) {
+    __shared__ float sh[8];
+    float acc = 0.f;
+    for (int r = threadIdx.x; r < B; r += blockDim.x) {
+        float m = -INFINITY;
+        for (int s = 0; s < nstrips; ++s) m = fmaxf(m, part_m[(long long)s * B + r]);
+        float sum = 0.f;
+        for (int s = 0; s < nstrips; ++s) {
+            const float ps = part_s[(long long)s * B + r];
+            if (ps > 0.f) sum += ps * expf(part_m[(long long)s * B + r] - m);
+        }
+        const float l = m + logf(sum);
+        lse[r] = l;
+        acc += l - tgt[r];
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += sh[i];
+        *loss = t / (float)B;
+    }
+}
+}  // namespace
+
+bool umma_ce_supported(int B, int d, long long N) { return B >= 1 && d % 4 == 0 && d >= 4 && N >= 1; }
+
+size_t umma_ce_workspace_bytes(int B, int d, long long N) { return carve_ce(nullptr, B, d, N, true).bytes; }
+
+int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, float* loss,
+                float* lse, void* ws, size_t ws_bytes, cudaStream_t st) {
+    CeWs w = carve_ce(ws, B, d, N, false);
+    BSA_REQUIRE(ws_bytes >= w.bytes, "bsa_ce_fwd: workspace too small (%zu < %zu)", ws_bytes, w.bytes);
+    int rc;
+    if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
+    if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
+    Operand oa{w.s_hi, w.s_lo, B, d, d, false}, ob{w.e_hi, w.e_lo, N, d, d, false};
+    GemmCore g;
+    if ((rc = make_core(g, B, (int)N, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;
+    int nstrips = w.nstrips;
+    if (nstrips > g.n_tiles) nstrips = g.n_tiles;
+    EpiLse<CE_BN>::Params ep{answers, w.part_m, w.part_s, w.tgt};
+    {
+        ProfScope prof(PROF_CE_FWD_UMMA, st, 2.0 * B * (double)N * d);
+        if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiLse<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;
+    }
+    ce_combine_kernel<<<1, 256, 0, st>>>(w.part_m, w.part_s, w.tgt, nstrips, B, lse, loss);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, const float* lse,
+                const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st) {
+    CeWs w = carve_ce(ws, B, d, N, true);
+    BSA_REQUIRE(ws_bytes >= w.bytes, "bsa_ce_bwd: workspace too small (%zu < %zu)", ws_bytes, w.bytes);
+    int rc;
+    if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
+    if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
+    BSA_CHECK_CUDA(cudaMemsetAsync(ds, 0, (size_t)B * d * 4, st));
+    ProfScope prof(PROF_CE_BWD_UMMA, st, 4.0 * B * (double)N * d);
+    const int BNd = d > 128 ? 256 : 128;
+    for (long long n0 = 0; n0 < N; n0 += w.chunk) {
+        const int cols = (int)((N - n0) < w.chunk ? (N - n0) : w.chunk);
+        {   // logits chunk -> G, G^T (hi, lo)
+            Operand oa{w.s_hi, w.s_lo, B, d, d, false}, ob{w.e_hi + n0 * d, w.e_lo + n0 * d, cols, d, d, false};
+            GemmCore g;
+            if ((rc = make_core(g, B, cols, d, oa, ob, 256, SCHED_M_FASTEST, 1))) return rc;
+            EpiCeGrad<256>::Params ep{lse, answers, d_loss, n0, w.g_hi, w.g_lo, (long long)w.chunk, w.gt_hi, w.gt_lo, w.ldgt};
+            const long long total = (long long)g.m_tiles * g.n_tiles;
+            if ((rc = launch<256, 2, false, false, EpiCeGrad<256>>(g, ep, (int)(total < num_sms() ? total : num_sms()), st))) return rc;
+        }
+        {   // ds += G E_chunk : A = G [B, cols] K-major ; B operand = E_chunk [cols (K), d (N)] MN-major ; split-K
+            Operand oa{w.g_hi, w.g_lo, B, cols, (long long)w.chunk, false}, ob{w.e_hi + n0 * d, w.e_lo + n0 * d, cols, d, d, true};
+            GemmCore g;
+            int splits = num_sms() / (cdiv(B, BM) * cdiv(d, BNd));
+            if (splits > 64) splits = 64;
+            if ((rc = make_core(g, B, d, cols, oa, ob, BNd, SCHED_N_FASTEST, splits))) return rc;
+            const long long total = (long long)g.m_tiles * g.n_tiles * g.splits;
+            const int grid = (int)(total < num_sms() ? total : num_sms());
+            if (BNd == 256) {
+                StoreParams ep{ds, d, nullptr, 0, nullptr, nullptr, 1.f, 1, g.splits > 1 ? w.partial : nullptr};
+                if ((rc = launch<256, 2, false, true, EpiStore<256>>(g, ep, grid, st))) return rc;
+            } else {
+                StoreParams ep{ds, d, nullptr, 0, nullptr, nullptr, 1.f, 1, g.splits > 1 ? w.partial : nullptr};
+                if ((rc = launch<128, 3, false, true, EpiStore<128>>(g, ep, grid, st))) return rc;
+            }
+            if (g.splits > 1) {
+                const long long MN = (long long)B * d;
+                splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, g.splits, 1.f, 1);
+                BSA_LAUNCH_CHECK();
+            }
+        }
+        {   // dE_chunk = G^T s : A = G^T [cols, B] K-major ; B operand = s [B (K), d (N)] MN-major
+            Operand oa{w.gt_hi, w.gt_lo, cols, B, w.ldgt, false}, ob{w.s_hi, w.s_lo, B, d, d, true};
+            GemmCore g;
+            if ((rc = make_core(g, cols, d, B, oa, ob, 128, SCHED_N_FASTEST, 1))) return rc;
+            StoreParams ep{dE + n0 * d, d, nullptr, 0, nullptr, nullptr, 1.f, 0, nullptr};
+            const long long total = (long long)g.m_tiles * g.n_tiles;
+            if ((rc = launch<128, 3, false, true, EpiStore<128>>(g, ep, (int)(total < num_sms() ? total : num_sms()), st))) return rc;
+        }
+    }
+    return 0;
+}
+
+// ============================================================================ scoring + top-k
+namespace {
+__global__ void hist_list_kernel(const long long* __restrict__ indptr, const long long* __restrict__ indices,
+                                 long long offset, long long rows, int k, int B, float* __restrict__ val,
+                                 long long* __restrict__ idx) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= B) return;
+    int n = 0;
+    const long long lo = indptr ? indptr[row] : 0, hi = indptr ? indptr[row + 1] : 0;
+    for (long long q = lo; q < hi && n < k; ++q) {
+        const long long gid = indices[q];
+        if (gid >= offset && gid < offset + rows) { val[(long long)row * k + n] = 0.0f; idx[(long long)row * k + n] = gid; ++n; }
+    }
+    for (; n < k; ++n) { val[(long long)row * k + n] = -INFINITY; idx[(long long)row * k + n] = -1; }
+}
+
+int topk_strips(int B, int k) {
+    int s = ce_strips(B);
+    const int cap = 1024 / k - 1;
+    if (s > cap) s = cap;
+    return s < 1 ? 1 : s;
+}
+}  // namespace
+
+bool umma_topk_supported(int B, int d, int k, long long rows) {
+    return B >= 1 && d % 4 == 0 && d >= 4 && k >= 1 && k <= 32 && rows >= 1 && rows < (1ll << 31);
+}
+
+size_t umma_topk_workspace_bytes(int B, int d, int k, long long rows) {
+    const int ns = topk_strips(B, k) + 1;
+    return 2 * al((size_t)B * d * 4) + 2 * al((size_t)rows * d * 4) + al((size_t)ns * B * k * 4) + al((size_t)ns * B * k * 8) + 4096;
+}
+
+int umma_score_topk(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,
+                    const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
+                    void* ws, size_t ws_bytes, cudaStream_t st) {
+    BSA_REQUIRE(ws_bytes >= umma_topk_workspace_bytes(B, d, k, rows), "bsa_score_topk: workspace too small");
+    char* p = (char*)ws;
+    auto take = [&](size_t bytes) { char* r = p; p += al(bytes); return r; };
+    float* s_hi = (float*)take((size_t)B * d * 4); float* s_lo = (float*)take((size_t)B * d * 4);
+    float* e_hi = (float*)take((size_t)rows * d * 4); float* e_lo = (float*)take((size_t)rows * d * 4);
+    int nstrips = topk_strips(B, k);
+    float* cand_val = (float*)take((size_t)(nstrips + 1) * B * k * 4);
+    long long* cand_idx = (long long*)take((size_t)(nstrips + 1) * B * k * 8);
+    int rc;
+    if ((rc = do_split(s, s_hi, s_lo, (long long)B * d, st))) return rc;
+    if ((rc = do_split(E, e_hi, e_lo, rows * d, st))) return rc;
+    Operand oa{s_hi, s_lo, B, d, d, false}, ob{e_hi, e_lo, rows, d, d, false};
+    GemmCore g;
+    if ((rc = make_core(g, B, (int)rows, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;
+    if (nstrips > g.n_tiles) nstrips = g.n_tiles;
+    EpiTopk<CE_BN>::Params ep{hist_indptr, hist_indices, offset, k, cand_val, cand_idx};
+    {
+        ProfScope prof(PROF_TOPK_UMMA, st, 2.0 * B * (double)rows * d);
+        if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiTopk<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;
+    }
+    // history items enter as one more candidate list with score exactly 0.0 (trainers.py:134)
+    hist_list_kernel<<<cdiv(B, 128), 128, 0, st>>>(hist_indptr, hist_indices, offset, rows, k, B,
+                                                  cand_val + (size_t)nstrips * B * k, cand_idx + (size_t)nstrips * B * k);
+    BSA_LAUNCH_CHECK();
+    return topk_merge(cand_val, cand_idx, nstrips + 1, B, k, top_val, top_idx, st);
 }
 
 }  // namespace bsa

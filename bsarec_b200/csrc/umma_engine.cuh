@@ -17,4 +17,11 @@ int umma_score_topk(int B, int d, int k, long long rows, long long offset, const
                     const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
                     void* ws, size_t ws_bytes, cudaStream_t st);
 
+// generic C = alpha * A B^T (+bias)(act)(+C) on the tcgen05 engine; operands given unsplit (see umma_engine.cu)
+size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, int N, int K);
+int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a_cols, long long lda, bool a_mn,
+              const float* B, long long b_rows, long long b_cols, long long ldb, bool b_mn, float* C, long long ldc,
+              const float* bias, int act, float* aux_out, const float* aux_in, float alpha, int accumulate, void* ws,
+              size_t ws_bytes, cudaStream_t st);
+
 }  // namespace bsa

@@ -178,6 +178,19 @@ int bsa_topk_merge(const float* cand_val, const int64_t* cand_idx, int G, int B,
                    int64_t* top_idx, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * The tcgen05 engine as a plain GEMM (what cuBLAS sgemm is to the reference's nn.Linear / torch.matmul
+ * call sites, model/_modules.py:62-66,109-136): C[M,N] = A B^T with error-compensated TF32 (3 tcgen05.mma
+ * per k-step, fp32 accumulate in TMEM), results within fp32 rounding of an FFMA GEMM.
+ *   a_mn == 0: A is [M rows, K cols] row-major (lda = row pitch);  a_mn != 0: A is [K rows, M cols].
+ *   b_mn == 0: B is [N rows, K cols] row-major;                    b_mn != 0: B is [K rows, N cols].
+ * impl: 2 = tcgen05, 1 = fp32 FFMA reference kernel (same semantics; used as the on-GPU cross-check).
+ * ---------------------------------------------------------------------------------------------- */
+size_t bsa_gemm_workspace_bytes(int M, int N, int K, int64_t lda, int64_t ldb, int a_mn, int b_mn);
+int bsa_gemm(int impl, int M, int N, int K, const float* A, int64_t lda, int a_mn, const float* B, int64_t ldb,
+             int b_mn, float* C, int64_t ldc, const float* bias, float alpha, int accumulate, void* workspace,
+             size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Small utilities shared by the host wrappers
  * ---------------------------------------------------------------------------------------------- */
 /* dst [B,d] = src[:, L-1, :] */

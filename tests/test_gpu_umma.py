@@ -1,0 +1,153 @@
+"""tcgen05 (3xTF32) engine through the C ABI: GEMM in all operand orientations, fused cross-entropy and
+fused scoring/top-k, each against a torch fp64 reference and against the fp32 FFMA path of the same library."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _gemm(impl, A, B, M, N, K, a_mn, b_mn, bias=None, alpha=1.0, acc=None):
+    from bsarec_b200 import _cabi
+    lib = _cabi.load()
+    dev = A.device
+    Cout = acc.clone() if acc is not None else torch.empty(M, N, device=dev)
+    lda, ldb = A.stride(0), B.stride(0)
+    wsb = lib.bsa_gemm_workspace_bytes(M, N, K, lda, ldb, int(a_mn), int(b_mn))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    _cabi.check(lib.bsa_gemm(impl, M, N, K, A.data_ptr(), lda, int(a_mn), B.data_ptr(), ldb, int(b_mn), Cout.data_ptr(),
+                             Cout.stride(0), None if bias is None else bias.data_ptr(), alpha, int(acc is not None),
+                             ws.data_ptr(), wsb, st), "bsa_gemm")
+    torch.cuda.synchronize()
+    return Cout
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 32), (128, 256, 64), (200, 130, 72), (517, 300, 260), (6, 24, 8), (1000, 64, 1024)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_umma_gemm_matches_fp64_and_ffma(M, N, K, a_mn, b_mn, cuda_device):
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K + 2 * a_mn + b_mn)
+    # pitches are multiples of 4 elements (16 B, a TMA requirement); logical sizes stay ragged
+    lda = ((M if a_mn else K) + 3) // 4 * 4
+    ldb = ((N if b_mn else K) + 3) // 4 * 4
+    A = torch.randn((K if a_mn else M), lda, generator=g)
+    B = torch.randn((K if b_mn else N), ldb, generator=g)
+    Al = (A[:, :M].t() if a_mn else A[:, :K]).double()
+    Bl = (B[:, :N].t() if b_mn else B[:, :K]).double()
+    ref = Al @ Bl.t()
+    Ad, Bd = A.to(cuda_device), B.to(cuda_device)
+    got = _gemm(2, Ad, Bd, M, N, K, a_mn, b_mn).cpu()
+    ffma = _gemm(1, Ad, Bd, M, N, K, a_mn, b_mn).cpu()
+    e_umma, e_ffma = rel_err(got, ref), rel_err(ffma, ref)
+    assert e_umma < 5e-6, (e_umma, e_ffma)          # 3xTF32 stays at fp32-rounding level
+    assert e_ffma < 5e-6
+
+
+def test_umma_gemm_bias_alpha_accumulate(cuda_device):
+    g = torch.Generator().manual_seed(1)
+    M, N, K = 300, 200, 96
+    A, B = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g)
+    bias, C0 = torch.randn(N, generator=g), torch.randn(M, N, generator=g)
+    ref = 0.5 * (A.double() @ B.double().t()) + bias.double() + C0.double()
+    got = _gemm(2, A.to(cuda_device), B.to(cuda_device), M, N, K, False, False, bias.to(cuda_device), 0.5, C0.to(cuda_device)).cpu()
+    assert rel_err(got, ref) < 5e-6
+
+
+def _ce(impl, s, E, ans, dloss=1.0):
+    from bsarec_b200 import functional as Fn
+    loss, lse = Fn.ce_forward(s, E, ans, impl)
+    dE = torch.empty_like(E)
+    ds = Fn.ce_backward(s, E, ans, lse, torch.tensor(dloss, device=s.device), dE, impl)
+    torch.cuda.synchronize()
+    return loss.cpu(), lse.cpu(), ds.cpu(), dE.cpu()
+
+
+@pytest.mark.parametrize("B,d,N", [(6, 32, 211), (128, 64, 1000), (37, 64, 12102), (512, 256, 20000), (130, 128, 5003)])
+def test_fused_cross_entropy_fwd_bwd(B, d, N, cuda_device):
+    g = torch.Generator().manual_seed(B + d + N)
+    s = torch.randn(B, d, generator=g) * 1.5
+    E = torch.randn(N, d, generator=g) * 0.3
+    ans = torch.randint(1, N, (B,), generator=g)
+    ans[0] = N - 1                                  # target in the ragged last tile
+    sd, Ed = s.double().requires_grad_(True), E.double().requires_grad_(True)
+    logits = sd @ Ed.t()
+    ref_loss = torch.nn.functional.cross_entropy(logits, ans)
+    (2.5 * ref_loss).backward()
+    ref_lse = torch.logsumexp(logits.detach(), dim=1)
+    for impl in (1, 2):
+        loss, lse, ds, dE = _ce(impl, s.to(cuda_device), E.to(cuda_device), ans.to(cuda_device), 2.5)
+        assert abs(float(loss) - float(ref_loss)) < 2e-6 * abs(float(ref_loss)), impl
+        assert rel_err(lse, ref_lse) < 2e-6, impl
+        assert rel_err(ds, sd.grad) < 1e-5, impl
+        assert rel_err(dE, Ed.grad) < 1e-5, impl
+
+
+def _topk(impl, s, E, indptr, indices, k, offset=0):
+    from bsarec_b200 import functional as Fn
+    val, idx = Fn.score_topk(s, E, indptr, indices, k, offset, impl)
+    torch.cuda.synchronize()
+    return val.cpu().numpy(), idx.cpu().numpy()
+
+
+def _ref_topk(s, E, indptr, indices, k, offset=0):
+    """numpy: exact fp64 scores, history -> 0.0, order by (score desc, id asc)."""
+    sc = (s.double() @ E.double().t()).numpy()
+    out_v, out_i = [], []
+    for b in range(sc.shape[0]):
+        row = sc[b].copy()
+        h = indices[indptr[b]:indptr[b + 1]] - offset
+        h = h[(h >= 0) & (h < row.shape[0])]
+        row[h] = 0.0
+        order = np.lexsort((np.arange(row.shape[0]), -row))[:k]
+        out_v.append(row[order])
+        out_i.append(order + offset)
+    return np.array(out_v), np.array(out_i)
+
+
+@pytest.mark.parametrize("B,d,N,k", [(5, 32, 97, 20), (64, 64, 3417, 20), (130, 64, 12102, 10), (256, 128, 30000, 20)])
+@pytest.mark.parametrize("negative", [False, True])
+def test_fused_score_topk(B, d, N, k, negative, cuda_device):
+    g = torch.Generator().manual_seed(B * 3 + N + k)
+    s = torch.randn(B, d, generator=g)
+    E = torch.randn(N, d, generator=g) * 0.2
+    if negative:                       # most scores negative -> the 0.0 history entries must surface in the top-k
+        E = -E.abs() * 0.1
+        s = s.abs()
+    counts = torch.randint(0, 60, (B,), generator=g).numpy()
+    indptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    indices = np.concatenate([np.sort(np.random.default_rng(b).choice(np.arange(1, N), c, replace=False)) for b, c in enumerate(counts)] + [np.zeros(0, np.int64)]).astype(np.int64)
+    rv, ri = _ref_topk(s, E, indptr, indices, k)
+    ip = torch.from_numpy(indptr).to(cuda_device)
+    ix = torch.from_numpy(indices if len(indices) else np.zeros(1, np.int64)).to(cuda_device)
+    for impl in (1, 2):
+        v, i = _topk(impl, s.to(cuda_device), E.to(cuda_device), ip, ix, k)
+        assert np.allclose(v, rv, rtol=2e-5, atol=2e-6), impl
+        diff = (i != ri)
+        # an index may differ only where two fp64 scores are closer than fp32 resolution
+        for b, q in zip(*np.nonzero(diff)):
+            assert abs(rv[b, q] - v[b, q]) <= 2e-5 * max(1.0, abs(rv[b, q])), (impl, b, q)
+        assert diff.mean() < 0.01, impl
+        assert np.all(np.diff(v, axis=1) <= 0)          # descending
+
+
+def test_sharded_topk_merge_equals_unsharded(cuda_device):
+    from bsarec_b200 import functional as Fn
+    g = torch.Generator().manual_seed(4)
+    B, d, N, k, G = 70, 64, 10007, 20, 4
+    s, E = torch.randn(B, d, generator=g).to(cuda_device), (torch.randn(N, d, generator=g) * 0.2).to(cuda_device)
+    ids = torch.randint(1, N, (B, 30), generator=g)
+    rows = [torch.unique(ids[b]) for b in range(B)]       # sorted, de-duplicated
+    indptr = torch.tensor([0] + list(np.cumsum([len(r) for r in rows])), dtype=torch.int64).to(cuda_device)
+    indices = torch.cat(rows).to(cuda_device)
+    for impl in (1, 2):
+        full_v, full_i = Fn.score_topk(s, E, indptr, indices, k, 0, impl)
+        bounds = [N * j // G for j in range(G + 1)]
+        cv, ci = [], []
+        for j in range(G):
+            v, i = Fn.score_topk(s, E[bounds[j]:bounds[j + 1]].contiguous(), indptr, indices, k, bounds[j], impl)
+            cv.append(v)
+            ci.append(i)
+        mv, mi = Fn.topk_merge(torch.stack(cv), torch.stack(ci))
+        assert torch.equal(mi, full_i) and torch.equal(mv, full_v), impl

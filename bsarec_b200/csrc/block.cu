@@ -3,10 +3,13 @@
 #include "common.cuh"
 #include "gemm_simt.cuh"
 #include "rowwise.cuh"
+#include "umma_engine.cuh"
 
 #include <cmath>
 
 namespace bsa {
+
+int linear_impl();
 
 namespace {
 
@@ -53,6 +56,15 @@ long long splitk_floats(long long M, long long d) {
     return (m > c ? m : c) + 1024;
 }
 
+// scratch of the tcgen05 linears: (hi, lo) pairs of the largest activation operand on both sides + split-K partials
+size_t umma_linear_ws_bytes(long long M, long long d) {
+    return umma_gemm_workspace_bytes(M * 4 * d, M * 4 * d, (int)(4 * d), (int)d, 0);
+}
+
+struct Lin {               // where the linears run: tcgen05 3xTF32 engine (default) or the fp32 FFMA kernel
+    bool umma; void* ws; size_t ws_bytes;
+};
+
 size_t workspace_bytes(const bsa_block_desc& c) {
     const long long M = (long long)c.B * c.L, d = c.d;
     const long long PL = (long long)c.B * c.H * c.L * c.L;
@@ -66,12 +78,16 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     b.f((long long)colsum_partial_rows(M) * 4 * d);
     b.f(splitk_floats(M, d));
     b.f((long long)c.B * d);
+    b.f((long long)(umma_linear_ws_bytes(M, d) / 4));
     return b.off + 4096;
 }
 
 // x [M, K] @ W[N, K]^T + bias -> out [M, N]      (nn.Linear forward)
-int linear_fwd(const float* x, const float* W, const float* bias, float* out, long long M, int N, int K, int act,
+int linear_fwd(const Lin& ln, const float* x, const float* W, const float* bias, float* out, long long M, int N, int K, int act,
                float* aux_out, cudaStream_t st) {
+    if (ln.umma)
+        return umma_gemm((int)M, N, K, x, M, K, K, false, W, N, K, K, false, out, N, bias, act, aux_out, nullptr, 1.f, 0,
+                         ln.ws, ln.ws_bytes, st);
     GemmP p;
     p.A = x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
     p.bias = bias; p.act = act; p.aux_out = aux_out;
@@ -79,8 +95,11 @@ int linear_fwd(const float* x, const float* W, const float* bias, float* out, lo
 }
 
 // dx [M, K] (+)= dy [M, N] @ W[N, K]              (nn.Linear input gradient)
-int linear_bwd_input(const float* dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
+int linear_bwd_input(const Lin& ln, const float* dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
                      const float* aux_in, cudaStream_t st) {
+    if (ln.umma)
+        return umma_gemm((int)M, K, N, dy, M, N, N, false, W, N, K, K, true, dx, K, nullptr, act, nullptr, aux_in, 1.f,
+                         accumulate, ln.ws, ln.ws_bytes, st);
     GemmP p;
     p.A = dy; p.B = W; p.C = dx; p.M = (int)M; p.N = K; p.K = N; p.lda = N; p.ldb = K; p.ldc = K;
     p.b_kmajor = false; p.accumulate = accumulate; p.act = act; p.aux_in = aux_in;
@@ -88,8 +107,14 @@ int linear_bwd_input(const float* dy, const float* W, float* dx, long long M, in
 }
 
 // dW [N, K] = dy[M, N]^T @ x [M, K] ; db [N] = colsum(dy)   (deterministic split-K + column sums)
-int linear_bwd_weight(const float* dy, const float* x, float* dW, float* db, long long M, int N, int K, float* part_sk,
+int linear_bwd_weight(const Lin& ln, const float* dy, const float* x, float* dW, float* db, long long M, int N, int K, float* part_sk,
                       float* part_cs, cudaStream_t st) {
+    if (ln.umma) {
+        int rc = umma_gemm(N, K, (int)M, dy, M, N, N, true, x, M, K, K, true, dW, K, nullptr, 0, nullptr, nullptr, 1.f, 0,
+                           ln.ws, ln.ws_bytes, st);
+        if (rc) return rc;
+        return colsum(dy, M, N, part_cs, db, 0, st);
+    }
     GemmP p;
     p.A = dy; p.B = x; p.C = dW; p.M = N; p.N = K; p.K = (int)M; p.lda = N; p.ldb = K; p.ldc = K;
     p.a_kmajor = false; p.b_kmajor = false;
@@ -101,6 +126,10 @@ int linear_bwd_weight(const float* dy, const float* x, float* dW, float* db, lon
 }
 
 }  // namespace
+
+int g_linear_impl = 2;      // 1 = fp32 FFMA, 2 = tcgen05 3xTF32 (bsa_set_linear_impl)
+int linear_impl() { return g_linear_impl; }
+void set_linear_impl(int impl) { g_linear_impl = impl == 1 ? 1 : 2; }
 
 int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
               const float* x, float* x_out, void* saved_p, void* ws, size_t ws_bytes, cudaStream_t st) {
@@ -119,15 +148,17 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const Dropout dr_a = make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training);
     const Dropout dr_o = make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training);
     float* Pd = dr_p.thr ? b.f(PL) : s.P;
+    Lin lin{linear_impl() == 2, nullptr, umma_linear_ws_bytes(M, d)};
+    lin.ws = b.f((long long)(lin.ws_bytes / 4));
     BSA_REQUIRE(b.ok(), "bsa_block_fwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
     const int r = filter_rank(L, c.kept_bins);
     int rc;
     // filter branch
     if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, s.z_f, s.mean_f, s.rstd_f, B, L, d, r, dr_f, st))) return rc;
     // attention branch
-    if ((rc = linear_fwd(x, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_fwd(x, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_fwd(x, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, x, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, x, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, x, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, st))) return rc;
     {   // scores = q k^T / sqrt(dh)   -> written where P will live
         GemmP p;
         p.A = s.q; p.B = s.k; p.C = s.P; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
@@ -146,12 +177,12 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         p.sCo = (long long)L * d; p.sCi = dh;
         if ((rc = launch_gemm(p, st))) return rc;
     }
-    if ((rc = linear_fwd(s.ctx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, s.ctx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, st))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
     if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, s.z_a, s.mean_a, s.rstd_a, dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
     // feed-forward
-    if ((rc = linear_fwd(s.y, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, st))) return rc;
-    if ((rc = linear_fwd(s.h_act, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, s.y, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, st))) return rc;
+    if ((rc = linear_fwd(lin, s.h_act, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, st))) return rc;
     if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, M, d, dr_o, st))) return rc;
     return 0;
 }
@@ -182,6 +213,8 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     float* part_cs = b.f((long long)colsum_partial_rows(M) * 4 * d);
     float* part_sk = b.f(splitk_floats(M, d));
     float* pbeta2 = b.f((long long)B * d);
+    Lin lin{linear_impl() == 2, nullptr, umma_linear_ws_bytes(M, d)};
+    lin.ws = b.f((long long)(lin.ws_bytes / 4));
     BSA_REQUIRE(b.ok(), "bsa_block_bwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
     const Dropout dr_f = make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training);
     const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
@@ -196,18 +229,18 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
     const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
-    if ((rc = linear_bwd_weight(t2, s.h_act, g.w2, g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(t2, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, st))) return rc;
-    if ((rc = linear_bwd_weight(dh_, s.y, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(dh_, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, st))) return rc;   // dyb = dL/dy
+    if ((rc = linear_bwd_weight(lin, t2, s.h_act, g.w2, g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, t2, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, dh_, s.y, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, dh_, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, st))) return rc;   // dyb = dL/dy
 
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
     if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_a, st))) return rc;
     if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
     const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
-    if ((rc = linear_bwd_weight(t1, s.ctx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(t1, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, t1, s.ctx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, t1, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, st))) return rc;
     const float* Pd = s.P;
     if (dr_p.thr) {
         if ((rc = apply_dropout(s.P, Pd_ws, PL, dr_p, st))) return rc;
@@ -246,12 +279,12 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         p.sCo = (long long)L * d; p.sCi = dh;
         if ((rc = launch_gemm(p, st))) return rc;
     }
-    if ((rc = linear_bwd_weight(dq, x, g.wq, g.bq, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_weight(dk, x, g.wk, g.bk, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_weight(dv, x, g.wv, g.bv, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(dq, w.wq, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_bwd_input(dk, w.wk, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_bwd_input(dv, w.wv, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, dq, x, g.wq, g.bq, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, dk, x, g.wk, g.bk, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, dv, x, g.wv, g.bv, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, dq, w.wq, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_bwd_input(lin, dk, w.wk, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = linear_bwd_input(lin, dv, w.wv, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
 
     // ---- filter branch: dsp = LN(drop(u) + x), weight alpha
     if ((rc = ln_bwd(dyb, c.alpha, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, nullptr, pgam, pbet, &nblk, M, d, dr_f, st))) return rc;

@@ -30,6 +30,8 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
               size_t ws_bytes, cudaStream_t st);
 size_t block_saved_bytes(const bsa_block_desc& c);
 size_t block_workspace_bytes(const bsa_block_desc& c);
+void set_linear_impl(int impl);
+int linear_impl();
 
 static inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
 
@@ -169,6 +171,9 @@ int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream) {
     BSA_REQUIRE(basis && L >= 1 && kept_bins >= 1, "bsa_build_filter_basis: bad argument");
     return build_filter_basis(basis, L, kept_bins, nullptr, (cudaStream_t)stream);
 }
+
+void bsa_set_linear_impl(int impl) { set_linear_impl(impl); }
+int bsa_get_linear_impl(void) { return linear_impl(); }
 
 size_t bsa_block_saved_bytes(const bsa_block_desc* c) { return block_saved_bytes(*c); }
 size_t bsa_block_workspace_bytes(const bsa_block_desc* c) { return block_workspace_bytes(*c); }

@@ -117,6 +117,11 @@ typedef struct {
 int bsa_filter_rank(int L, int kept_bins);
 int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream);
 
+/* where the block's nn.Linear contractions run: 2 = tcgen05 3xTF32 engine (default), 1 = fp32 FFMA kernels
+ * (the on-GPU cross-check).  Process-wide. */
+void bsa_set_linear_impl(int impl);
+int bsa_get_linear_impl(void);
+
 size_t bsa_block_saved_bytes(const bsa_block_desc* desc);      /* activations kept for backward */
 size_t bsa_block_workspace_bytes(const bsa_block_desc* desc);  /* scratch for fwd and bwd */
 

@@ -69,10 +69,13 @@ def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shar
     s_all = torch.empty(world * Bl, s_local.shape[1], dtype=s_local.dtype, device=s_local.device)
     dist.all_gather_into_tensor(s_all, s_local.contiguous(), group=group)
     val, idx = score_fn(s_all, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)
-    val_all = torch.empty(world, world * Bl, k, dtype=val.dtype, device=val.device)
-    idx_all = torch.empty(world, world * Bl, k, dtype=idx.dtype, device=idx.device)
+    # gathered along dim 0 ([world * B, k], the layout every backend accepts), viewed as [world, B, k]
+    val_all = torch.empty(world * world * Bl, k, dtype=val.dtype, device=val.device)
+    idx_all = torch.empty(world * world * Bl, k, dtype=idx.dtype, device=idx.device)
     dist.all_gather_into_tensor(val_all, val.contiguous(), group=group)
     dist.all_gather_into_tensor(idx_all, idx.contiguous(), group=group)
+    val_all = val_all.view(world, world * Bl, k)
+    idx_all = idx_all.view(world, world * Bl, k)
     mine = slice(rank * Bl, (rank + 1) * Bl)
     _, top = merge_fn(val_all[:, mine].contiguous(), idx_all[:, mine].contiguous())
     return top

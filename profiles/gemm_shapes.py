@@ -14,6 +14,9 @@ shapes = [  # name, M, N, K, a_mn, b_mn
     ("dX d<-d", Mtok, d, d, 0, 1), ("dX d<-4d", Mtok, d, 4 * d, 0, 1), ("dX 4d<-d", Mtok, 4 * d, d, 0, 1),
     ("dW dxd", d, d, Mtok, 1, 1), ("dW dx4d", d, 4 * d, Mtok, 1, 1), ("dW 4dxd", 4 * d, d, Mtok, 1, 1),
 ]
+only = os.environ.get("SHAPES")
+if only:
+    shapes = [s for s in shapes if s[0] in only.split(",")]
 st = torch.cuda.current_stream().cuda_stream
 for name, M, N, K, a_mn, b_mn in shapes:
     A = torch.randn((K, M) if a_mn else (M, K), device=dev)

@@ -33,52 +33,102 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
 
 // ============================================================================ epilogues
 // ---- plain store: C = alpha*acc (+bias) (act) (+C)   or raw split-K partials
+// Eight epilogue warps: warp e drains TMEM lane quarter e % 4 (32 accumulator rows) and column half e / 4 of the
+// tile, 32 columns at a time.  Each 32 x 32 block goes registers -> XOR-swizzled shared staging -> registers, so
+// that global traffic is row-contiguous: one warp instruction moves 4 rows x 128 B (full lines) instead of 32
+// rows x 16 B.  Bias / activation / accumulate run after the transpose, where aux and C reads coalesce too.
 struct StoreParams {
     float* C; long long ldc; const float* bias; int act; float* aux_out; const float* aux_in; float alpha;
     int accumulate; float* partial;
+    float* out_hi; float* out_lo;        // optional: also emit the result as a split-TF32 (hi, lo) pair [same ldc]
+    int partial_accumulate;              // split-K partial slabs are running sums (added to, not overwritten)
 };
 template <int BN>
 struct EpiStore {
     using Params = StoreParams;
-    static constexpr int SMEM_BYTES = 0;
-    const Params& p; const GemmCore& g; int rit;
-    __device__ EpiStore(const Params& p_, const GemmCore& g_, unsigned char*, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {}
+    static constexpr int WARPS = 8;
+    static constexpr int SMEM_BYTES = WARPS * 32 * 32 * 4;       // one 32 x 32 fp32 staging block per warp
+    const Params& p; const GemmCore& g;
+    float4* stg; int quarter, half, lane;
+    __device__ EpiStore(const Params& p_, const GemmCore& g_, unsigned char* smem, int epi_warp, int lane_)
+        : p(p_), g(g_), quarter(epi_warp & 3), half(epi_warp >> 2), lane(lane_) {
+        stg = reinterpret_cast<float4*>(smem) + epi_warp * 256;
+    }
     __device__ void tile(uint32_t acc, const TileCoord& tc) {
-        const long long row = (long long)tc.m * BM + rit;
+        const long long row0 = (long long)tc.m * BM + quarter * 32;
         const int n0 = tc.n * BN;
-        const bool row_ok = row < g.M;
+        const int sub = lane >> 3, c4 = lane & 7;                // store phase: 4 rows x 8 float4 per instruction
+        float* base; long long ld; bool plain = p.partial == nullptr;
+        if (plain) { base = p.C; ld = p.ldc; }
+        else { base = p.partial + (long long)tc.split * g.M * g.N; ld = g.N; }
+        const bool vec_ok = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
             float v[32];
             tmem_ld32(acc + c0, v);
-            if (!row_ok || n0 + c0 >= g.N) continue;
-            if (p.partial) {
-                float* dst = p.partial + ((long long)tc.split * g.M + row) * g.N + n0 + c0;
+            if (n0 + c0 >= g.N || row0 >= g.M) continue;         // warp-uniform
 #pragma unroll
-                for (int j = 0; j < 32; ++j) if (n0 + c0 + j < g.N) dst[j] = v[j];
-                continue;
-            }
-            const long long off = row * p.ldc + n0 + c0;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                float x = p.alpha * v[j];
-                const int col = n0 + c0 + j;
-                if (col < g.N) {
-                    if (p.bias) x += __ldg(p.bias + col);
-                    if (p.act == 1) { p.aux_out[off + j] = x; x = gelu_erf(x); }
-                    else if (p.act == 2) x *= gelu_erf_grad(p.aux_in[off + j]);
-                    if (p.accumulate) x += p.C[off + j];
+            for (int j = 0; j < 8; ++j)
+                stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            __syncwarp();
+            const int col = n0 + c0 + c4 * 4;
+            float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (plain && p.bias) {
+                if (col + 3 < g.N) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                else {
+                    if (col < g.N) bias4.x = __ldg(p.bias + col);
+                    if (col + 1 < g.N) bias4.y = __ldg(p.bias + col + 1);
+                    if (col + 2 < g.N) bias4.z = __ldg(p.bias + col + 2);
                 }
-                v[j] = x;
             }
-            if ((p.ldc & 3) == 0 && n0 + c0 + 32 <= g.N && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0)) {
+            const bool full = vec_ok && (col + 3 < g.N);
 #pragma unroll
-                for (int j = 0; j < 32; j += 4)
-                    *reinterpret_cast<float4*>(p.C + off + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (n0 + c0 + j < g.N) p.C[off + j] = v[j];
+            for (int it = 0; it < 8; ++it) {
+                const int r = it * 4 + sub;
+                const long long row = row0 + r;
+                float4 x = stg[r * 8 + (c4 ^ (r & 7))];
+                if (row >= g.M || col >= g.N) continue;
+                const long long off = row * ld + col;
+                if (!plain) {                                    // split-K partials: raw (or running) sums
+                    if (full) {
+                        if (p.partial_accumulate) { const float4 o = *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
+                        *reinterpret_cast<float4*>(base + off) = x;
+                    } else {
+                        const float xs[4] = {x.x, x.y, x.z, x.w};
+                        for (int e = 0; e < 4; ++e) if (col + e < g.N) base[off + e] = xs[e] + (p.partial_accumulate ? base[off + e] : 0.f);
+                    }
+                    continue;
+                }
+                x.x = p.alpha * x.x + bias4.x; x.y = p.alpha * x.y + bias4.y; x.z = p.alpha * x.z + bias4.z; x.w = p.alpha * x.w + bias4.w;
+                if (full) {
+                    if (p.act == 1) {
+                        *reinterpret_cast<float4*>(p.aux_out + off) = x;
+                        x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
+                    } else if (p.act == 2) {
+                        const float4 a = *reinterpret_cast<const float4*>(p.aux_in + off);
+                        x.x *= gelu_erf_grad(a.x); x.y *= gelu_erf_grad(a.y); x.z *= gelu_erf_grad(a.z); x.w *= gelu_erf_grad(a.w);
+                    }
+                    if (p.accumulate) { const float4 o = *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
+                    *reinterpret_cast<float4*>(base + off) = x;
+                    if (p.out_hi) {
+                        float4 h, l;
+                        split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
+                        *reinterpret_cast<float4*>(p.out_hi + off) = h;
+                        *reinterpret_cast<float4*>(p.out_lo + off) = l;
+                    }
+                } else {
+                    float xs[4] = {x.x, x.y, x.z, x.w};
+                    for (int e = 0; e < 4; ++e) if (col + e < g.N) {
+                        float y = xs[e];
+                        if (p.act == 1) { p.aux_out[off + e] = y; y = gelu_erf(y); }
+                        else if (p.act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
+                        if (p.accumulate) y += base[off + e];
+                        base[off + e] = y;
+                        if (p.out_hi) { float h, l; split_tf32(y, h, l); p.out_hi[off + e] = h; p.out_lo[off + e] = l; }
+                    }
+                }
             }
+            __syncwarp();                                        // staging block is reused by the next chunk
         }
     }
     __device__ void finish() {}
@@ -89,10 +139,11 @@ template <int BN>
 struct EpiLse {
     struct Params { const long long* answers; float* part_m; float* part_s; float* tgt; };
     static constexpr int SMEM_BYTES = 0;
+    static constexpr int WARPS = 4;
     const Params& p; const GemmCore& g; int rit;
     float m = -INFINITY, s = 0.f;
     long long ans = -1;
-    __device__ EpiLse(const Params& p_, const GemmCore& g_, unsigned char*, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {
+    __device__ EpiLse(const Params& p_, const GemmCore& g_, unsigned char*, int epi_warp, int lane) : p(p_), g(g_), rit(epi_warp * 32 + lane) {
         const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
         if (row < g.M) ans = p.answers[row];
     }
@@ -140,12 +191,13 @@ struct EpiTopk {
         float* cand_val; long long* cand_idx;      // [nstrips][B][k]
     };
     static constexpr int KMAX = 32;
+    static constexpr int WARPS = 4;
     static constexpr int SMEM_BYTES = KMAX * 128 * 8;
     const Params& p; const GemmCore& g; int rit;
     float* lv; int* li;
     float thr = -INFINITY; int thr_i = 0x7fffffff;
     long long hlo = 0, hhi = 0;
-    __device__ EpiTopk(const Params& p_, const GemmCore& g_, unsigned char* smem, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {
+    __device__ EpiTopk(const Params& p_, const GemmCore& g_, unsigned char* smem, int epi_warp, int lane) : p(p_), g(g_), rit(epi_warp * 32 + lane) {
         lv = reinterpret_cast<float*>(smem);
         li = reinterpret_cast<int*>(smem + KMAX * 128 * 4);
         for (int i = 0; i < p.k; ++i) { lv[i * 128 + rit] = -INFINITY; li[i * 128 + rit] = 0x7fffffff; }
@@ -199,55 +251,69 @@ struct EpiTopk {
     }
 };
 
-// ---- CE gradient of one logits chunk: G = (softmax - onehot) * d_loss / B, emitted as (hi, lo) in both
-//      orientations so the two gradient GEMMs read K-major A operands
+// ---- CE gradient of one logits chunk: G = (softmax - onehot) * d_loss / B, emitted as a split-TF32 (hi, lo) pair
+//      [B][ldg] (items contiguous).  The same arrays feed both gradient GEMMs: ds = G E reads them as a K-major A
+//      operand, dE = G^T s as an MN-major A operand.  Same staged, coalesced store scheme as EpiStore.
 template <int BN>
 struct EpiCeGrad {
     struct Params {
         const float* lse; const long long* answers; const float* d_loss; long long n_base;
-        float *g_hi, *g_lo; long long ldg;          // [B][ldg]   (cols = chunk items)
-        float *gt_hi, *gt_lo; long long ldgt;       // [chunk items][ldgt] (cols = users)
+        float *g_hi, *g_lo; long long ldg;          // [B][ldg]   (cols = chunk items), ldg % 4 == 0
     };
-    static constexpr int SMEM_BYTES = 0;
-    const Params& p; const GemmCore& g; int rit;
-    __device__ EpiCeGrad(const Params& p_, const GemmCore& g_, unsigned char*, int row_in_tile) : p(p_), g(g_), rit(row_in_tile) {}
+    static constexpr int WARPS = 8;
+    static constexpr int SMEM_BYTES = WARPS * 32 * 32 * 4;
+    const Params& p; const GemmCore& g;
+    float4* stg; int quarter, half, lane;
+    __device__ EpiCeGrad(const Params& p_, const GemmCore& g_, unsigned char* smem, int epi_warp, int lane_)
+        : p(p_), g(g_), quarter(epi_warp & 3), half(epi_warp >> 2), lane(lane_) {
+        stg = reinterpret_cast<float4*>(smem) + epi_warp * 256;
+    }
     __device__ void tile(uint32_t acc, const TileCoord& tc) {
-        const long long row = (long long)tc.m * BM + rit;
+        const long long row0 = (long long)tc.m * BM + quarter * 32;
         const int n0 = tc.n * BN;
-        const bool row_ok = row < g.M;
-        const float l = row_ok ? p.lse[row] : 0.f;
-        const long long a = row_ok ? p.answers[row] - p.n_base : -1;
+        const int sub = lane >> 3, c4 = lane & 7;
         const float scale = __ldg(p.d_loss) / (float)g.M;
+        float l[8]; long long a[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const long long row = row0 + it * 4 + sub;
+            const bool ok = row < g.M;
+            l[it] = ok ? __ldg(p.lse + row) : 0.f;
+            a[it] = ok ? __ldg(p.answers + row) - p.n_base : -1;
+        }
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
             float v[32];
             tmem_ld32(acc + c0, v);
-            if (!row_ok || n0 + c0 >= g.N) continue;
-            float hi[32], lo[32];
+            if (n0 + c0 >= g.N || row0 >= g.M) continue;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                float pr = expf(v[j] - l);
-                if (a == n0 + c0 + j) pr -= 1.0f;
-                split_tf32(pr * scale, hi[j], lo[j]);
-            }
-            const int nv = min(32, g.N - (n0 + c0));
-            float* gh = p.g_hi + row * p.ldg + n0 + c0;
-            float* gl = p.g_lo + row * p.ldg + n0 + c0;
-            if (nv == 32) {
+            for (int j = 0; j < 8; ++j)
+                stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            __syncwarp();
+            const int col = n0 + c0 + c4 * 4;
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    *reinterpret_cast<float4*>(gh + j) = make_float4(hi[j], hi[j + 1], hi[j + 2], hi[j + 3]);
-                    *reinterpret_cast<float4*>(gl + j) = make_float4(lo[j], lo[j + 1], lo[j + 2], lo[j + 3]);
+            for (int it = 0; it < 8; ++it) {
+                const int r = it * 4 + sub;
+                const long long row = row0 + r;
+                const float4 x = stg[r * 8 + (c4 ^ (r & 7))];
+                if (row >= g.M || col >= g.N) continue;
+                float pr[4] = {expf(x.x - l[it]), expf(x.y - l[it]), expf(x.z - l[it]), expf(x.w - l[it])};
+                const long long da = a[it] - col;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (da == e) pr[e] -= 1.0f;
+                float4 h, lo;
+                split_tf32(pr[0] * scale, h.x, lo.x); split_tf32(pr[1] * scale, h.y, lo.y);
+                split_tf32(pr[2] * scale, h.z, lo.z); split_tf32(pr[3] * scale, h.w, lo.w);
+                const long long off = row * p.ldg + col;
+                if (col + 3 < g.N) {
+                    *reinterpret_cast<float4*>(p.g_hi + off) = h;
+                    *reinterpret_cast<float4*>(p.g_lo + off) = lo;
+                } else {
+                    const float hs[4] = {h.x, h.y, h.z, h.w}, ls[4] = {lo.x, lo.y, lo.z, lo.w};
+                    for (int e = 0; e < 4; ++e) if (col + e < g.N) { p.g_hi[off + e] = hs[e]; p.g_lo[off + e] = ls[e]; }
                 }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (j < nv) { gh[j] = hi[j]; gl[j] = lo[j]; }
             }
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (j < nv) {
-                p.gt_hi[(long long)(n0 + c0 + j) * p.ldgt + row] = hi[j];
-                p.gt_lo[(long long)(n0 + c0 + j) * p.ldgt + row] = lo[j];
-            }
+            __syncwarp();
         }
     }
     __device__ void finish() {}
@@ -287,7 +353,7 @@ int launch(const GemmCore& g, const typename Epi::Params& ep, int grid, cudaStre
         BSA_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    kern<<<grid, GEMM_THREADS, smem, st>>>(g, ep);
+    kern<<<grid, gemm_threads(Epi::WARPS), smem, st>>>(g, ep);
     BSA_LAUNCH_CHECK();
     return 0;
 }
@@ -400,8 +466,8 @@ constexpr int CE_STAGES = 3;
 
 struct CeWs {
     float *s_hi, *s_lo, *e_hi, *e_lo, *part_m, *part_s, *tgt;
-    float *g_hi, *g_lo, *gt_hi, *gt_lo, *partial;
-    int nstrips, chunk; long long ldgt;
+    float *g_hi, *g_lo, *partial;
+    int nstrips, chunk;
     size_t bytes;
 };
 
@@ -415,7 +481,7 @@ int ce_bwd_chunk(int B, long long N) {
     // one wave of 128 x 256 logits tiles per chunk, and small enough that G, G^T (hi, lo) stay in L2
     const int m_tiles = cdiv(B, BM);
     long long per_wave = (long long)(num_sms() / m_tiles > 0 ? num_sms() / m_tiles : 1) * 256;
-    long long cap = (80ll << 20) / (16ll * (B > 0 ? B : 1));         // 4 arrays x 4 B per element <= 80 MiB (L2 is 126 MB)
+    long long cap = (80ll << 20) / (8ll * (B > 0 ? B : 1));          // G (hi, lo): 8 B per element <= 80 MiB (L2 is 126 MB)
     long long c = per_wave;
     while (c * 2 <= cap) c *= 2;
     if (c > cap && cap >= 256) c = cap / 256 * 256;
@@ -434,10 +500,8 @@ CeWs carve_ce(void* ws, int B, int d, long long N, bool bwd) {
     w.part_m = take((size_t)w.nstrips * B * 4); w.part_s = take((size_t)w.nstrips * B * 4);
     w.tgt = take((size_t)B * 4);
     w.chunk = ce_bwd_chunk(B, N);
-    w.ldgt = (B + 3) / 4 * 4;
     if (bwd) {
         w.g_hi = take((size_t)B * w.chunk * 4); w.g_lo = take((size_t)B * w.chunk * 4);
-        w.gt_hi = take((size_t)w.chunk * w.ldgt * 4); w.gt_lo = take((size_t)w.chunk * w.ldgt * 4);
         w.partial = take((size_t)64 * B * d * 4);
     }
     w.bytes = (size_t)(p - (char*)ws) + 1024;
@@ -505,48 +569,57 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
     int rc;
     if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
     if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
-    BSA_CHECK_CUDA(cudaMemsetAsync(ds, 0, (size_t)B * d * 4, st));
     ProfScope prof(PROF_CE_BWD_UMMA, st, 4.0 * B * (double)N * d);
     const int BNd = d > 128 ? 256 : 128;
+    // ds = G E is split over K (= items); its partial sums stay in `partial` ACROSS chunks and are reduced once
+    int ds_splits = num_sms() / (cdiv(B, BM) * cdiv(d, BNd));
+    if (ds_splits > 64) ds_splits = 64;
+    if (ds_splits < 1) ds_splits = 1;
+    int used_splits = 0;
+    bool first = true;
     for (long long n0 = 0; n0 < N; n0 += w.chunk) {
         const int cols = (int)((N - n0) < w.chunk ? (N - n0) : w.chunk);
-        {   // logits chunk -> G, G^T (hi, lo)
+        {   // logits chunk -> G (hi, lo)
             Operand oa{w.s_hi, w.s_lo, B, d, d, false}, ob{w.e_hi + n0 * d, w.e_lo + n0 * d, cols, d, d, false};
             GemmCore g;
             if ((rc = make_core(g, B, cols, d, oa, ob, 256, SCHED_M_FASTEST, 1))) return rc;
-            EpiCeGrad<256>::Params ep{lse, answers, d_loss, n0, w.g_hi, w.g_lo, (long long)w.chunk, w.gt_hi, w.gt_lo, w.ldgt};
+            EpiCeGrad<256>::Params ep{lse, answers, d_loss, n0, w.g_hi, w.g_lo, (long long)w.chunk};
             const long long total = (long long)g.m_tiles * g.n_tiles;
             if ((rc = launch<256, 2, false, false, EpiCeGrad<256>>(g, ep, (int)(total < num_sms() ? total : num_sms()), st))) return rc;
         }
-        {   // ds += G E_chunk : A = G [B, cols] K-major ; B operand = E_chunk [cols (K), d (N)] MN-major ; split-K
+        {   // ds partials (+)= G E_chunk : A = G [B, cols] K-major ; B operand = E_chunk [cols (K), d (N)] MN-major
             Operand oa{w.g_hi, w.g_lo, B, cols, (long long)w.chunk, false}, ob{w.e_hi + n0 * d, w.e_lo + n0 * d, cols, d, d, true};
             GemmCore g;
-            int splits = num_sms() / (cdiv(B, BM) * cdiv(d, BNd));
-            if (splits > 64) splits = 64;
-            if ((rc = make_core(g, B, d, cols, oa, ob, BNd, SCHED_N_FASTEST, splits))) return rc;
+            if ((rc = make_core(g, B, d, cols, oa, ob, BNd, SCHED_N_FASTEST, ds_splits))) return rc;
+            // a short last chunk may use fewer splits: its tiles still add into the first g.splits partial slabs
+            if (g.splits > used_splits) {
+                if (!first) {      // slabs never written before must start from zero
+                    BSA_CHECK_CUDA(cudaMemsetAsync(w.partial + (size_t)used_splits * B * d, 0, (size_t)(g.splits - used_splits) * B * d * 4, st));
+                }
+                used_splits = g.splits;
+            }
             const long long total = (long long)g.m_tiles * g.n_tiles * g.splits;
             const int grid = (int)(total < num_sms() ? total : num_sms());
-            if (BNd == 256) {
-                StoreParams ep{ds, d, nullptr, 0, nullptr, nullptr, 1.f, 1, g.splits > 1 ? w.partial : nullptr};
-                if ((rc = launch<256, 2, false, true, EpiStore<256>>(g, ep, grid, st))) return rc;
-            } else {
-                StoreParams ep{ds, d, nullptr, 0, nullptr, nullptr, 1.f, 1, g.splits > 1 ? w.partial : nullptr};
-                if ((rc = launch<128, 3, false, true, EpiStore<128>>(g, ep, grid, st))) return rc;
-            }
-            if (g.splits > 1) {
-                const long long MN = (long long)B * d;
-                splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, g.splits, 1.f, 1);
-                BSA_LAUNCH_CHECK();
-            }
+            StoreParams ep{ds, d, nullptr, 0, nullptr, nullptr, 1.f, 0, w.partial, nullptr, nullptr, first ? 0 : 1};
+            if (BNd == 256) { if ((rc = launch<256, 2, false, true, EpiStore<256>>(g, ep, grid, st))) return rc; }
+            else            { if ((rc = launch<128, 3, false, true, EpiStore<128>>(g, ep, grid, st))) return rc; }
         }
-        {   // dE_chunk = G^T s : A = G^T [cols, B] K-major ; B operand = s [B (K), d (N)] MN-major
-            Operand oa{w.gt_hi, w.gt_lo, cols, B, w.ldgt, false}, ob{w.s_hi, w.s_lo, B, d, d, true};
+        {   // dE_chunk = G^T s : A = G [B (K), cols (M)] MN-major ; B operand = s [B (K), d (N)] MN-major
+            Operand oa{w.g_hi, w.g_lo, B, cols, (long long)w.chunk, true}, ob{w.s_hi, w.s_lo, B, d, d, true};
             GemmCore g;
-            if ((rc = make_core(g, cols, d, B, oa, ob, 128, SCHED_N_FASTEST, 1))) return rc;
+            if ((rc = make_core(g, cols, d, B, oa, ob, BNd, SCHED_N_FASTEST, 1))) return rc;
             StoreParams ep{dE + n0 * d, d, nullptr, 0, nullptr, nullptr, 1.f, 0, nullptr};
             const long long total = (long long)g.m_tiles * g.n_tiles;
-            if ((rc = launch<128, 3, false, true, EpiStore<128>>(g, ep, (int)(total < num_sms() ? total : num_sms()), st))) return rc;
+            const int grid = (int)(total < num_sms() ? total : num_sms());
+            if (BNd == 256) { if ((rc = launch<256, 2, true, true, EpiStore<256>>(g, ep, grid, st))) return rc; }
+            else            { if ((rc = launch<128, 3, true, true, EpiStore<128>>(g, ep, grid, st))) return rc; }
         }
+        first = false;
+    }
+    {
+        const long long MN = (long long)B * d;
+        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, used_splits, 1.f, 0);
+        BSA_LAUNCH_CHECK();
     }
     return 0;
 }

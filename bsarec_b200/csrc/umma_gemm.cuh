@@ -22,7 +22,8 @@ namespace umma {
 constexpr int BM = 128;          // UMMA M (cta_group::1)
 constexpr int BK = 32;           // fp32 elements per k-block = one 128-byte swizzle row
 constexpr int UMMA_K = 8;        // tf32 elements per tcgen05.mma
-constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_THREADS = 256;          // 4 control warps + 4 epilogue warps (Epi::WARPS == 4)
+constexpr int gemm_threads(int epi_warps) { return 128 + 32 * epi_warps; }
 
 enum Sched : int {
     SCHED_N_FASTEST = 0,   // tile t -> (m = t / n_tiles, n = t % n_tiles): neighbouring CTAs share the A tile
@@ -69,11 +70,13 @@ __device__ __forceinline__ bool tile_of(const GemmCore& g, int it, TileCoord& tc
 
 // Epi contract:
 //   struct Params;  static constexpr int SMEM_BYTES;
-//   __device__ Epi(const Params&, const GemmCore&, unsigned char* smem, int row_in_tile);
+//   static constexpr int WARPS;    // epilogue warps: 4 (thread = accumulator row) or 8 (two warps per TMEM lane
+//                                  // quarter, each owning half of the tile's columns)
+//   __device__ Epi(const Params&, const GemmCore&, unsigned char* smem, int epi_warp, int lane);
 //   __device__ void tile(uint32_t acc_taddr, const TileCoord&);   // acc_taddr already carries this warp's lane base
 //   __device__ void finish();                                      // once, after the CTA's last tile
 template <int BN, int STAGES, bool A_MN, bool B_MN, class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(gemm_threads(Epi::WARPS), 1)
 umma_gemm_kernel(const __grid_constant__ GemmCore g, const __grid_constant__ typename Epi::Params ep) {
     using SL = StageLayout<BN>;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -95,7 +98,7 @@ umma_gemm_kernel(const __grid_constant__ GemmCore g, const __grid_constant__ typ
     }
     if (warp == 1 && elect_one()) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], Epi::WARPS); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, TMEM_COLS);
@@ -194,9 +197,8 @@ umma_gemm_kernel(const __grid_constant__ GemmCore g, const __grid_constant__ typ
         }
     } else if (warp >= 4) {
         // ===================================================================== epilogue
-        const int quarter = warp & 3;
-        const int row_in_tile = quarter * 32 + (threadIdx.x & 31);
-        Epi epi(ep, g, epi_smem, row_in_tile);
+        const int quarter = warp & 3;          // TMEM lanes a warp may touch: 32 * (warp id % 4) ...
+        Epi epi(ep, g, epi_smem, warp - 4, threadIdx.x & 31);
         TileCoord tc;
         for (int it = 0; tile_of(g, it, tc); ++it) {
             const int buf = it & 1;

@@ -75,6 +75,8 @@ SIGNATURES = {
     "bsa_build_filter_basis": (_I, [_VP, _I, _I, _VP]),
     "bsa_set_linear_impl": (None, [_I]),
     "bsa_get_linear_impl": (_I, []),
+    "bsa_set_attn_impl": (None, [_I]),
+    "bsa_get_attn_impl": (_I, []),
     "bsa_block_saved_bytes": (_SZ, [C.POINTER(BlockDesc)]),
     "bsa_block_workspace_bytes": (_SZ, [C.POINTER(BlockDesc)]),
     "bsa_block_fwd": (_I, [C.POINTER(BlockDesc), C.POINTER(BlockPtrs), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),

@@ -1,0 +1,23 @@
+// Fused causal multi-head attention (model/_modules.py:108-133 + get_attention_mask, _abstract_model.py:53-69):
+// scores, additive -10000 mask from ids, softmax, dropout and the value contraction in one kernel; the [B,H,L,L]
+// probabilities are never written.  Backward recomputes them from the saved row log-sum-exp.
+#pragma once
+#include "common.cuh"
+
+namespace bsa {
+
+// head sizes the fused kernels are instantiated for (other shapes use the unfused GEMM + softmax path)
+bool attn_fused_supported(int L, int d, int H);
+
+// q, k, v, ctx: [B*L, d] row-major, head h in columns [h*dh, (h+1)*dh).  lse: [B, H, L, 2] = (row max, log row sum) of the
+// masked, scaled scores of each query row, saved for the backward pass (kept apart: rows whose every key is masked
+// sit near -10000, where max + log sum would lose the low bits the softmax needs).
+int attn_fwd(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
+             int L, int d, Dropout dr, cudaStream_t st);
+
+// dq, dk, dv [B*L, d] are overwritten.  delta: [B, H, L] scratch (row sums of dctx * ctx).
+int attn_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
+             const float* dctx, float* dq, float* dk, float* dv, float* delta, int B, int H, int L, int d, Dropout dr,
+             cudaStream_t st);
+
+}  // namespace bsa

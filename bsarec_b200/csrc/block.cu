@@ -4,12 +4,14 @@
 #include "gemm_simt.cuh"
 #include "rowwise.cuh"
 #include "umma_engine.cuh"
+#include "attn.cuh"
 
 #include <cmath>
 
 namespace bsa {
 
 int linear_impl();
+int attn_impl();
 
 namespace {
 
@@ -26,8 +28,9 @@ struct Bump {               // bump allocator over caller-provided memory, 256-b
 };
 
 struct Saved {              // layout of the per-layer saved-activation buffer
-    float *z_f, *mean_f, *rstd_f, *q, *k, *v, *P, *ctx, *z_a, *mean_a, *rstd_a, *y, *h_pre, *h_act, *z_o, *mean_o,
+    float *z_f, *mean_f, *rstd_f, *q, *k, *v, *P, *lse, *ctx, *z_a, *mean_a, *rstd_a, *y, *h_pre, *h_act, *z_o, *mean_o,
         *rstd_o;
+    bool fused;             // attention ran in the fused kernel: lse [B,H,L] is saved instead of P [B,H,L,L]
     size_t bytes;
 };
 
@@ -37,7 +40,9 @@ Saved carve_saved(void* p, const bsa_block_desc& c) {
     Saved s;
     s.z_f = b.f(M * d); s.mean_f = b.f(M); s.rstd_f = b.f(M);
     s.q = b.f(M * d); s.k = b.f(M * d); s.v = b.f(M * d);
-    s.P = b.f((long long)c.B * c.H * c.L * c.L);
+    s.fused = attn_fused_supported(c.L, c.d, c.H) && attn_impl() == 2;
+    s.P = s.fused ? nullptr : b.f((long long)c.B * c.H * c.L * c.L);
+    s.lse = b.f(2ll * c.B * c.H * c.L);
     s.ctx = b.f(M * d);
     s.z_a = b.f(M * d); s.mean_a = b.f(M); s.rstd_a = b.f(M);
     s.y = b.f(M * d);
@@ -72,7 +77,8 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     // backward is the larger user: dyb, dd, dzf, dq, dk, dv, dctx [M,d]; dh [M,4d]; Pd, dP [B,H,L,L]
     for (int i = 0; i < 7; ++i) b.f(M * d);
     b.f(M * 4 * d);
-    b.f(PL); b.f(PL);
+    if (attn_fused_supported(c.L, c.d, c.H) && attn_impl() == 2) b.f((long long)c.B * c.H * c.L);   // delta
+    else { b.f(PL); b.f(PL); }
     // partials: LN gamma/beta, column sums, split-K, beta2
     b.f(2ll * rowwise_partial_blocks(M) * d);
     b.f((long long)colsum_partial_rows(M) * 4 * d);
@@ -127,6 +133,9 @@ int linear_bwd_weight(const Lin& ln, const float* dy, const float* x, float* dW,
 
 }  // namespace
 
+int g_attn_impl = 2;        // 1 = unfused GEMM + softmax kernels, 2 = fused attention kernel where the head size allows
+int attn_impl() { return g_attn_impl; }
+void set_attn_impl(int impl) { g_attn_impl = impl == 1 ? 1 : 2; }
 int g_linear_impl = 2;      // 1 = fp32 FFMA, 2 = tcgen05 3xTF32 (bsa_set_linear_impl)
 int linear_impl() { return g_linear_impl; }
 void set_linear_impl(int impl) { g_linear_impl = impl == 1 ? 1 : 2; }
@@ -147,7 +156,7 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
     const Dropout dr_a = make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training);
     const Dropout dr_o = make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training);
-    float* Pd = dr_p.thr ? b.f(PL) : s.P;
+    float* Pd = s.fused ? nullptr : (dr_p.thr ? b.f(PL) : s.P);
     Lin lin{linear_impl() == 2, nullptr, umma_linear_ws_bytes(M, d)};
     lin.ws = b.f((long long)(lin.ws_bytes / 4));
     BSA_REQUIRE(b.ok(), "bsa_block_fwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
@@ -159,23 +168,27 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = linear_fwd(lin, x, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, st))) return rc;
     if ((rc = linear_fwd(lin, x, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, st))) return rc;
     if ((rc = linear_fwd(lin, x, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, st))) return rc;
-    {   // scores = q k^T / sqrt(dh)   -> written where P will live
-        GemmP p;
-        p.A = s.q; p.B = s.k; p.C = s.P; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
-        p.batch = B * H; p.inner = H;
-        p.sAo = (long long)L * d; p.sAi = dh; p.sBo = (long long)L * d; p.sBi = dh;
-        p.sCo = (long long)H * L * L; p.sCi = (long long)L * L;
-        p.alpha = 1.0f / sqrtf((float)dh);
-        if ((rc = launch_gemm(p, st))) return rc;
-    }
-    if ((rc = softmax_mask_dropout_fwd(s.P, ids, s.P, Pd, B, H, L, dr_p, st))) return rc;
-    {   // ctx = Pd v
-        GemmP p;
-        p.A = Pd; p.B = s.v; p.C = s.ctx; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
-        p.b_kmajor = false; p.batch = B * H; p.inner = H;
-        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
-        p.sCo = (long long)L * d; p.sCi = dh;
-        if ((rc = launch_gemm(p, st))) return rc;
+    if (s.fused) {
+        if ((rc = attn_fwd(s.q, s.k, s.v, ids, s.ctx, s.lse, B, H, L, d, dr_p, st))) return rc;
+    } else {
+        {   // scores = q k^T / sqrt(dh)   -> written where P will live
+            GemmP p;
+            p.A = s.q; p.B = s.k; p.C = s.P; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
+            p.batch = B * H; p.inner = H;
+            p.sAo = (long long)L * d; p.sAi = dh; p.sBo = (long long)L * d; p.sBi = dh;
+            p.sCo = (long long)H * L * L; p.sCi = (long long)L * L;
+            p.alpha = 1.0f / sqrtf((float)dh);
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        if ((rc = softmax_mask_dropout_fwd(s.P, ids, s.P, Pd, B, H, L, dr_p, st))) return rc;
+        {   // ctx = Pd v
+            GemmP p;
+            p.A = Pd; p.B = s.v; p.C = s.ctx; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+            p.b_kmajor = false; p.batch = B * H; p.inner = H;
+            p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+            p.sCo = (long long)L * d; p.sCi = dh;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
     }
     if ((rc = linear_fwd(lin, s.ctx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, st))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
@@ -190,7 +203,6 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
 int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
               const float* x, const void* saved_p, const float* g_out, float* dx, const bsa_block_grads& g, void* ws,
               size_t ws_bytes, cudaStream_t st) {
-    (void)ids;
     const int B = c.B, L = c.L, d = c.d, H = c.H, dh = d / H;
     const long long M = (long long)B * L, PL = (long long)B * H * L * L;
     BSA_REQUIRE(H > 0 && d % H == 0 && d % 4 == 0, "bsa_block_bwd: bad shape");
@@ -205,8 +217,8 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     float* dv = b.f(M * d);
     float* dctx = b.f(M * d);
     float* dh_ = b.f(M * 4 * d);
-    float* Pd_ws = b.f(PL);
-    float* dP = b.f(PL);
+    float* Pd_ws = s.fused ? nullptr : b.f(PL);
+    float* dP = s.fused ? b.f((long long)B * H * L) : b.f(PL);
     const int nrb = rowwise_partial_blocks(M);
     float* pgam = b.f((long long)nrb * d);
     float* pbet = b.f((long long)nrb * d);
@@ -241,43 +253,48 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
     if ((rc = linear_bwd_weight(lin, t1, s.ctx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, t1, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, st))) return rc;
-    const float* Pd = s.P;
-    if (dr_p.thr) {
-        if ((rc = apply_dropout(s.P, Pd_ws, PL, dr_p, st))) return rc;
-        Pd = Pd_ws;
-    }
-    {   // dv[j,:] = sum_i Pd[i,j] dctx[i,:]
-        GemmP p;
-        p.A = Pd; p.B = dctx; p.C = dv; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
-        p.a_kmajor = false; p.b_kmajor = false; p.batch = B * H; p.inner = H;
-        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
-        p.sCo = (long long)L * d; p.sCi = dh;
-        if ((rc = launch_gemm(p, st))) return rc;
-    }
-    {   // dPd[i,j] = dctx[i,:] . v[j,:]
-        GemmP p;
-        p.A = dctx; p.B = s.v; p.C = dP; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
-        p.batch = B * H; p.inner = H;
-        p.sAo = (long long)L * d; p.sAi = dh; p.sBo = (long long)L * d; p.sBi = dh;
-        p.sCo = (long long)H * L * L; p.sCi = (long long)L * L;
-        if ((rc = launch_gemm(p, st))) return rc;
-    }
-    if ((rc = softmax_bwd(s.P, dP, B, H, L, dr_p, st))) return rc;            // dP now holds dS
-    {   // dq = dS k / sqrt(dh)
-        GemmP p;
-        p.A = dP; p.B = s.k; p.C = dq; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
-        p.b_kmajor = false; p.batch = B * H; p.inner = H; p.alpha = inv_sqrt_dh;
-        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
-        p.sCo = (long long)L * d; p.sCi = dh;
-        if ((rc = launch_gemm(p, st))) return rc;
-    }
-    {   // dk = dS^T q / sqrt(dh)
-        GemmP p;
-        p.A = dP; p.B = s.q; p.C = dk; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
-        p.a_kmajor = false; p.b_kmajor = false; p.batch = B * H; p.inner = H; p.alpha = inv_sqrt_dh;
-        p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
-        p.sCo = (long long)L * d; p.sCi = dh;
-        if ((rc = launch_gemm(p, st))) return rc;
+    if (s.fused) {
+        // dP (workspace, unused by this path) doubles as the [B,H,L] delta scratch
+        if ((rc = attn_bwd(s.q, s.k, s.v, ids, s.ctx, s.lse, dctx, dq, dk, dv, dP, B, H, L, d, dr_p, st))) return rc;
+    } else {
+        const float* Pd = s.P;
+        if (dr_p.thr) {
+            if ((rc = apply_dropout(s.P, Pd_ws, PL, dr_p, st))) return rc;
+            Pd = Pd_ws;
+        }
+        {   // dv[j,:] = sum_i Pd[i,j] dctx[i,:]
+            GemmP p;
+            p.A = Pd; p.B = dctx; p.C = dv; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+            p.a_kmajor = false; p.b_kmajor = false; p.batch = B * H; p.inner = H;
+            p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+            p.sCo = (long long)L * d; p.sCi = dh;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        {   // dPd[i,j] = dctx[i,:] . v[j,:]
+            GemmP p;
+            p.A = dctx; p.B = s.v; p.C = dP; p.M = L; p.N = L; p.K = dh; p.lda = d; p.ldb = d; p.ldc = L;
+            p.batch = B * H; p.inner = H;
+            p.sAo = (long long)L * d; p.sAi = dh; p.sBo = (long long)L * d; p.sBi = dh;
+            p.sCo = (long long)H * L * L; p.sCi = (long long)L * L;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        if ((rc = softmax_bwd(s.P, dP, B, H, L, dr_p, st))) return rc;            // dP now holds dS
+        {   // dq = dS k / sqrt(dh)
+            GemmP p;
+            p.A = dP; p.B = s.k; p.C = dq; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+            p.b_kmajor = false; p.batch = B * H; p.inner = H; p.alpha = inv_sqrt_dh;
+            p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+            p.sCo = (long long)L * d; p.sCi = dh;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
+        {   // dk = dS^T q / sqrt(dh)
+            GemmP p;
+            p.A = dP; p.B = s.q; p.C = dk; p.M = L; p.N = dh; p.K = L; p.lda = L; p.ldb = d; p.ldc = d;
+            p.a_kmajor = false; p.b_kmajor = false; p.batch = B * H; p.inner = H; p.alpha = inv_sqrt_dh;
+            p.sAo = (long long)H * L * L; p.sAi = (long long)L * L; p.sBo = (long long)L * d; p.sBi = dh;
+            p.sCo = (long long)L * d; p.sCi = dh;
+            if ((rc = launch_gemm(p, st))) return rc;
+        }
     }
     if ((rc = linear_bwd_weight(lin, dq, x, g.wq, g.bq, M, d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_weight(lin, dk, x, g.wk, g.bk, M, d, d, part_sk, part_cs, st))) return rc;

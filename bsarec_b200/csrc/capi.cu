@@ -32,6 +32,8 @@ size_t block_saved_bytes(const bsa_block_desc& c);
 size_t block_workspace_bytes(const bsa_block_desc& c);
 void set_linear_impl(int impl);
 int linear_impl();
+void set_attn_impl(int impl);
+int attn_impl();
 
 static inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
 
@@ -46,7 +48,7 @@ struct ProfRec {
     long long launches = 0;
 };
 ProfRec g_prof[PROF_NUM_TAGS] = {{"gemm_simt"}, {"ce_fwd_umma"}, {"ce_bwd_umma"}, {"score_topk_umma"}, {"linear_umma"},
-                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}};
+                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}};
 std::vector<cudaEvent_t> g_event_pool;
 cudaEvent_t get_event() {
     if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
@@ -174,6 +176,8 @@ int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream) {
 
 void bsa_set_linear_impl(int impl) { set_linear_impl(impl); }
 int bsa_get_linear_impl(void) { return linear_impl(); }
+void bsa_set_attn_impl(int impl) { set_attn_impl(impl); }
+int bsa_get_attn_impl(void) { return attn_impl(); }
 
 size_t bsa_block_saved_bytes(const bsa_block_desc* c) { return block_saved_bytes(*c); }
 size_t bsa_block_workspace_bytes(const bsa_block_desc* c) { return block_workspace_bytes(*c); }

@@ -121,6 +121,12 @@ int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream);
  * (the on-GPU cross-check).  Process-wide. */
 void bsa_set_linear_impl(int impl);
 int bsa_get_linear_impl(void);
+/* how the attention branch runs: 2 = fused kernel (scores, mask, softmax, dropout and P V in one pass, backward by
+ * recomputation from the saved row log-sum-exp; head sizes 32 and 64), 1 = unfused GEMM + softmax kernels that
+ * materialise the [B,H,L,L] probabilities (every head size; the on-GPU cross-check).  Process-wide; must not change
+ * between a bsa_block_fwd and its bsa_block_bwd. */
+void bsa_set_attn_impl(int impl);
+int bsa_get_attn_impl(void);
 
 size_t bsa_block_saved_bytes(const bsa_block_desc* desc);      /* activations kept for backward */
 size_t bsa_block_workspace_bytes(const bsa_block_desc* desc);  /* scratch for fwd and bwd */

@@ -169,3 +169,43 @@ def test_beauty_test_split_metrics_identical_to_reference(cuda_device):
         got += [recall_at_k(ans, pred, k), ndcg_k(ans, pred, k)]
     assert ["%.4f" % v for v in got] == ["0.0736", "0.0523", "0.1008", "0.0611", "0.1373", "0.0703"]
     assert got == pytest.approx(list(data["metrics"]), abs=1e-9)
+
+
+@pytest.mark.parametrize("cfgkw,B,p_attn", [
+    (dict(item_size=157, hidden_size=64, max_seq_length=20, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.6), 5, 0.5),
+    (dict(item_size=300, hidden_size=64, max_seq_length=150, num_attention_heads=1, num_hidden_layers=1, c=7, alpha=0.5), 6, 0.3),
+    (dict(item_size=300, hidden_size=128, max_seq_length=75, num_attention_heads=2, num_hidden_layers=1, c=5, alpha=0.4), 4, 0.0),
+])
+def test_fused_attention_kernel_vs_oracle_and_unfused(cfgkw, B, p_attn, cuda_device):
+    """Head sizes 32/64 run the fused attention kernel (flash-style, P never materialised): checked value for value
+    against the oracle (same dropout masks) over several key blocks (L > 64), padded and all-padding rows, and
+    against the unfused GEMM + softmax path of the same library."""
+    from bsarec_b200 import _cabi
+    lib = _cabi.load()
+    assert lib.bsa_get_attn_impl() == 2
+    L, N = cfgkw["max_seq_length"], cfgkw["item_size"]
+    cfg = oracle_cfg(cfgkw, 0.25, p_attn)
+    P = perturbed_params(cfg, 5)
+    ids, answers = synth_batch(11, B, L, N)
+    ids[0, :] = torch.randint(1, N, (L,))              # one full-length row: every key block is live
+    seed = 0x51DE5EED
+    grads = {}
+    for impl in (2, 1):
+        lib.bsa_set_attn_impl(impl)
+        try:
+            model = build_model(cfgkw, P, cuda_device, 0.25, p_attn).train()
+            model.set_dropout_seed(seed)
+            loss = model.calculate_loss(ids.to(cuda_device), answers.to(cuda_device), None, None, None)
+            loss.backward()
+            grads[impl] = (loss.item(), grads_of(model))
+        finally:
+            lib.bsa_set_attn_impl(2)
+    l64, g64 = oracle.loss_and_grads({k: v.double() for k, v in P.items()}, ids, answers, cfg, train=True,
+                                     plan=oracle.DropoutPlan(seed), use_fft=False)
+    _, g32 = oracle.loss_and_grads(P, ids, answers, cfg, train=True, plan=oracle.DropoutPlan(seed))
+    assert abs(grads[2][0] - float(l64)) < TOL * abs(float(l64))
+    check_grads(grads[2][1], g64, g32)
+    assert abs(grads[2][0] - grads[1][0]) < 2e-5 * abs(grads[1][0])
+    for k in g64:
+        if not k.endswith("key.bias"):
+            assert rel_err(grads[2][1][k], grads[1][1][k]) < TOL, k

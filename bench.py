@@ -163,6 +163,8 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ce-impl", type=int, default=0)
+    ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
+                    help="fused: bsarec_b200.FusedAdam (one kernel pass per tensor); torch: torch.optim.Adam (foreach)")
     args = ap.parse_args()
     desc, cfg, B, cpu_B = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
@@ -176,7 +178,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from bsarec_b200 import BSARecModel, _cabi
+    from bsarec_b200 import BSARecModel, FusedAdam, _cabi
     from bsarec_b200.parallel import allreduce_gradients
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from helpers import make_args
@@ -190,7 +192,8 @@ def main():
     torch.manual_seed(42)
     model = BSARecModel(make_args(cfg, P_DROP, P_DROP, batch_size=B)).to(dev)
     model.ce_impl = args.ce_impl
-    optim = torch.optim.Adam(model.parameters(), lr=1e-3, betas=(0.9, 0.999), weight_decay=0.0)
+    opt_cls = FusedAdam if args.optimizer == "fused" else torch.optim.Adam
+    optim = opt_cls(model.parameters(), lr=1e-3, betas=(0.9, 0.999), weight_decay=0.0)
     params = list(model.parameters())
     host = synth_batches(cfg, B, 1234 + rank, NBATCH)
     pinned = [{k: v.pin_memory() for k, v in b.items()} for b in host]
@@ -277,19 +280,30 @@ def main():
     except Exception:
         pass
     bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained / 2 for TF32 operands / 3 split-TF32 passes)" if peaks \
-        else "fallback 1400 TF/s bf16 sustained / 2 / 3"
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md: 6.65 TB/s, 1.4 PF/s sustained bf16)"
     tensor_peak = bf16_peak / 2.0 / 3.0          # fp32-parity bar => 3xTF32: effective tensor peak
+    hbm_tags = {"adam", "embed_fwd", "embed_bwd", "scatter_add"}       # work counted in algorithmic bytes
+
+    def kernel_line(name, rec):
+        sec = rec["ms"] * 1e-3
+        if name in hbm_tags:
+            ach = rec["work"] / sec / 1e9
+            return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
+        ach = rec["work"] / sec / 1e12
+        return {"bound": "tensor", "achieved": ach, "peak": tensor_peak, "unit": "TFLOP/s", "frac": ach / tensor_peak}
+
+    prof = {k: v for k, v in prof.items() if v["launches"] > 0 and v["ms"] > 0}
     dom = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else (None, None)
     roofline = None
     if dom[0]:
-        per_launch_ms = dom[1]["ms"] / dom[1]["launches"]
-        ach = dom[1]["work"] / (dom[1]["ms"] * 1e-3) / 1e12
-        roofline = {"kernel": dom[0], "bound": "tensor", "achieved": ach, "peak": tensor_peak, "unit": "TFLOP/s",
-                    "frac": ach / tensor_peak, "traffic": None, "peak_source": peak_src,
-                    "avg_launch_ms": per_launch_ms, "launches_per_step": dom[1]["launches"] / args.steps,
-                    "share_of_step": dom[1]["ms"] / (ms_train if ms_train > 0 else 1.0),
-                    "all_kernels_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items()}}
+        roofline = kernel_line(dom[0], dom[1])
+        roofline.update({
+            "kernel": dom[0], "traffic": None,
+            "peak_source": src + ("; tensor peak = bf16 sustained / 2 (TF32 operands) / 3 (split-TF32 passes)" if roofline["bound"] == "tensor" else ""),
+            "avg_launch_ms": dom[1]["ms"] / dom[1]["launches"], "launches_per_step": dom[1]["launches"] / args.steps,
+            "share_of_step": dom[1]["ms"] / (ms_train if ms_train > 0 else 1.0),
+            "all_kernels": {k: dict(kernel_line(k, v), ms_per_step=v["ms"] / args.steps) for k, v in prof.items()}})
     seqs = args.steps * B * world
     value = seqs / (ms_train * 1e-3)
     h2d = B * cfg["max_seq_length"] * 8 + B * 8
@@ -299,7 +313,8 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "per_gpu_batch": B, "global_batch": B * world, "dropout": P_DROP,
                    "parallelism": f"dp{world}", "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)",
-                   "optimizer": "torch.optim.Adam inside the step", "ce_impl": args.ce_impl},
+                   "optimizer": ("bsarec_b200.FusedAdam" if args.optimizer == "fused" else "torch.optim.Adam") + " inside the step",
+                   "ce_impl": args.ce_impl},
         "model_tflops": value * flops_train_per_seq(cfg) / 1e12,
         "eval": {"metric": "full-ranking eval users/sec", "value": seqs / (ms_eval * 1e-3), "unit": "users/s",
                  "ms_per_step": ms_eval / args.steps,

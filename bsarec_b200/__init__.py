@@ -4,7 +4,8 @@
 """
 from .model import BSARecModel
 from .trainer import Trainer
+from .optim import FusedAdam
 
 MODEL_DICT = {"bsarec": BSARecModel}
 
-__all__ = ["BSARecModel", "Trainer", "MODEL_DICT"]
+__all__ = ["BSARecModel", "Trainer", "FusedAdam", "MODEL_DICT"]

@@ -47,7 +47,7 @@ class BlockPtrs(C.Structure):           # bsa_block_weights and bsa_block_grads 
 
 
 class CeDesc(C.Structure):
-    _fields_ = [("B", C.c_int), ("d", C.c_int), ("item_size", C.c_int64), ("impl", C.c_int)]
+    _fields_ = [("B", C.c_int), ("d", C.c_int), ("item_size", C.c_int64), ("impl", C.c_int), ("reuse_split", C.c_int)]
 
 
 class TopkDesc(C.Structure):
@@ -90,6 +90,7 @@ SIGNATURES = {
     "bsa_topk_merge": (_I, [_VP, _VP, _I, _I, _I, _VP, _VP, _VP]),
     "bsa_gemm_workspace_bytes": (_SZ, [_I, _I, _I, _I64, _I64, _I, _I]),
     "bsa_gemm": (_I, [_I, _I, _I, _I, _VP, _I64, _I, _VP, _I64, _I, _VP, _I64, _VP, C.c_float, _I, _VP, _SZ, _VP]),
+    "bsa_adam_step": (_I, [_VP, _VP, _VP, _VP, _I64] + [C.c_float] * 5 + [_I64, _VP]),
     "bsa_gather_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
     "bsa_scatter_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
 }

@@ -30,6 +30,9 @@ struct Bump {               // bump allocator over caller-provided memory, 256-b
 struct Saved {              // layout of the per-layer saved-activation buffer
     float *z_f, *mean_f, *rstd_f, *q, *k, *v, *P, *lse, *ctx, *z_a, *mean_a, *rstd_a, *y, *h_pre, *h_act, *z_o, *mean_o,
         *rstd_o;
+    // tcgen05 path: split-TF32 (hi, lo) copies of the four linear inputs, written once in forward and reused by the
+    // weight-gradient GEMMs in backward
+    float *x_hi, *x_lo, *ctx_hi, *ctx_lo, *y_hi, *y_lo, *h_hi, *h_lo;
     bool fused;             // attention ran in the fused kernel: lse [B,H,L] is saved instead of P [B,H,L,L]
     size_t bytes;
 };
@@ -48,6 +51,11 @@ Saved carve_saved(void* p, const bsa_block_desc& c) {
     s.y = b.f(M * d);
     s.h_pre = b.f(M * 4 * d); s.h_act = b.f(M * 4 * d);
     s.z_o = b.f(M * d); s.mean_o = b.f(M); s.rstd_o = b.f(M);
+    s.x_hi = s.x_lo = s.ctx_hi = s.ctx_lo = s.y_hi = s.y_lo = s.h_hi = s.h_lo = nullptr;
+    if (linear_impl() == 2) {
+        s.x_hi = b.f(M * d); s.x_lo = b.f(M * d); s.ctx_hi = b.f(M * d); s.ctx_lo = b.f(M * d);
+        s.y_hi = b.f(M * d); s.y_lo = b.f(M * d); s.h_hi = b.f(M * 4 * d); s.h_lo = b.f(M * 4 * d);
+    }
     s.bytes = b.off;
     return s;
 }
@@ -61,14 +69,25 @@ long long splitk_floats(long long M, long long d) {
     return (m > c ? m : c) + 1024;
 }
 
-// scratch of the tcgen05 linears: (hi, lo) pairs of the largest activation operand on both sides + split-K partials
-size_t umma_linear_ws_bytes(long long M, long long d) {
-    return umma_gemm_workspace_bytes(M * 4 * d, M * 4 * d, (int)(4 * d), (int)d, 0);
-}
+// an activation operand: the fp32 tensor and (tcgen05 path) its split pair
+struct Act { const float* x; const float* hi; const float* lo; };
 
 struct Lin {               // where the linears run: tcgen05 3xTF32 engine (default) or the fp32 FFMA kernel
-    bool umma; void* ws; size_t ws_bytes;
+    bool umma;
+    float *w_hi, *w_lo;    // [4d*d] scratch for the weight's split pair
+    float* partial; size_t partial_bytes;      // split-K slabs (weight gradients)
 };
+
+long long lin_ws_floats(long long d) { return 2 * (4 * d * d + 256) + (long long)(umma_gemm_partial_bytes((int)(4 * d), (int)d) / 4); }
+
+Lin make_lin(Bump& b, long long d) {
+    Lin ln;
+    ln.umma = linear_impl() == 2;
+    ln.w_hi = b.f(4 * d * d + 256); ln.w_lo = b.f(4 * d * d + 256);
+    ln.partial_bytes = umma_gemm_partial_bytes((int)(4 * d), (int)d);
+    ln.partial = b.f((long long)(ln.partial_bytes / 4));
+    return ln;
+}
 
 size_t workspace_bytes(const bsa_block_desc& c) {
     const long long M = (long long)c.B * c.L, d = c.d;
@@ -84,51 +103,66 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     b.f((long long)colsum_partial_rows(M) * 4 * d);
     b.f(splitk_floats(M, d));
     b.f((long long)c.B * d);
-    b.f((long long)(umma_linear_ws_bytes(M, d) / 4));
-    return b.off + 4096;
+    // tcgen05 linears: weight split, split-K slabs, split pairs of the upstream gradients ([M,d] and [M,4d])
+    b.f(lin_ws_floats(d));
+    b.f(M * d); b.f(M * d); b.f(M * 4 * d); b.f(M * 4 * d);
+    return b.off + 8192;
 }
 
-// x [M, K] @ W[N, K]^T + bias -> out [M, N]      (nn.Linear forward)
-int linear_fwd(const Lin& ln, const float* x, const float* W, const float* bias, float* out, long long M, int N, int K, int act,
-               float* aux_out, cudaStream_t st) {
-    if (ln.umma)
-        return umma_gemm((int)M, N, K, x, M, K, K, false, W, N, K, K, false, out, N, bias, act, aux_out, nullptr, 1.f, 0,
-                         ln.ws, ln.ws_bytes, st);
+// x [M, K] @ W[N, K]^T + bias -> out [M, N]      (nn.Linear forward); out_hi/out_lo: also emit out's split pair
+int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, float* out, long long M, int N, int K, int act,
+               float* aux_out, float* out_hi, float* out_lo, cudaStream_t st) {
+    if (ln.umma) {
+        int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
+        if (rc) return rc;
+        return umma_gemm_ps((int)M, N, K, a.hi, a.lo, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out, N, bias, act, aux_out,
+                            nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
+    }
     GemmP p;
-    p.A = x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
+    p.A = a.x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
     p.bias = bias; p.act = act; p.aux_out = aux_out;
     return launch_gemm(p, st);
 }
 
 // dx [M, K] (+)= dy [M, N] @ W[N, K]              (nn.Linear input gradient)
-int linear_bwd_input(const Lin& ln, const float* dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
-                     const float* aux_in, cudaStream_t st) {
-    if (ln.umma)
-        return umma_gemm((int)M, K, N, dy, M, N, N, false, W, N, K, K, true, dx, K, nullptr, act, nullptr, aux_in, 1.f,
-                         accumulate, ln.ws, ln.ws_bytes, st);
+int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
+                     const float* aux_in, float* out_hi, float* out_lo, cudaStream_t st) {
+    if (ln.umma) {
+        int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
+        if (rc) return rc;
+        return umma_gemm_ps((int)M, K, N, dy.hi, dy.lo, M, N, N, false, ln.w_hi, ln.w_lo, N, K, K, true, dx, K, nullptr, act, nullptr,
+                            aux_in, 1.f, accumulate, out_hi, out_lo, nullptr, 0, st);
+    }
     GemmP p;
-    p.A = dy; p.B = W; p.C = dx; p.M = (int)M; p.N = K; p.K = N; p.lda = N; p.ldb = K; p.ldc = K;
+    p.A = dy.x; p.B = W; p.C = dx; p.M = (int)M; p.N = K; p.K = N; p.lda = N; p.ldb = K; p.ldc = K;
     p.b_kmajor = false; p.accumulate = accumulate; p.act = act; p.aux_in = aux_in;
     return launch_gemm(p, st);
 }
 
 // dW [N, K] = dy[M, N]^T @ x [M, K] ; db [N] = colsum(dy)   (deterministic split-K + column sums)
-int linear_bwd_weight(const Lin& ln, const float* dy, const float* x, float* dW, float* db, long long M, int N, int K, float* part_sk,
+int linear_bwd_weight(const Lin& ln, const Act& dy, const Act& x, float* dW, float* db, long long M, int N, int K, float* part_sk,
                       float* part_cs, cudaStream_t st) {
     if (ln.umma) {
-        int rc = umma_gemm(N, K, (int)M, dy, M, N, N, true, x, M, K, K, true, dW, K, nullptr, 0, nullptr, nullptr, 1.f, 0,
-                           ln.ws, ln.ws_bytes, st);
+        int rc = umma_gemm_ps(N, K, (int)M, dy.hi, dy.lo, M, N, N, true, x.hi, x.lo, M, K, K, true, dW, K, nullptr, 0, nullptr,
+                              nullptr, 1.f, 0, nullptr, nullptr, ln.partial, ln.partial_bytes, st);
         if (rc) return rc;
-        return colsum(dy, M, N, part_cs, db, 0, st);
+        return colsum(dy.x, M, N, part_cs, db, 0, st);
     }
     GemmP p;
-    p.A = dy; p.B = x; p.C = dW; p.M = N; p.N = K; p.K = (int)M; p.lda = N; p.ldb = K; p.ldc = K;
+    p.A = dy.x; p.B = x.x; p.C = dW; p.M = N; p.N = K; p.K = (int)M; p.lda = N; p.ldb = K; p.ldc = K;
     p.a_kmajor = false; p.b_kmajor = false;
     p.splitk = choose_splitk(N, K, (int)M);
     if (p.splitk > 1) p.partial = part_sk;
     int rc = launch_gemm(p, st);
     if (rc) return rc;
-    return colsum(dy, M, N, part_cs, db, 0, st);
+    return colsum(dy.x, M, N, part_cs, db, 0, st);
+}
+
+// split an activation into (hi, lo) when the tcgen05 path will consume it
+int split_act(const Lin& ln, const float* x, float* hi, float* lo, long long n, Act& out, cudaStream_t st) {
+    out.x = x; out.hi = hi; out.lo = lo;
+    if (!ln.umma) return 0;
+    return umma_split(x, hi, lo, n, st);
 }
 
 }  // namespace
@@ -157,17 +191,18 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const Dropout dr_a = make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training);
     const Dropout dr_o = make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training);
     float* Pd = s.fused ? nullptr : (dr_p.thr ? b.f(PL) : s.P);
-    Lin lin{linear_impl() == 2, nullptr, umma_linear_ws_bytes(M, d)};
-    lin.ws = b.f((long long)(lin.ws_bytes / 4));
+    Lin lin = make_lin(b, d);
     BSA_REQUIRE(b.ok(), "bsa_block_fwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
     const int r = filter_rank(L, c.kept_bins);
     int rc;
     // filter branch
     if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, s.z_f, s.mean_f, s.rstd_f, B, L, d, r, dr_f, st))) return rc;
     // attention branch
-    if ((rc = linear_fwd(lin, x, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_fwd(lin, x, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_fwd(lin, x, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    Act ax, actx, ay, ah;
+    if ((rc = split_act(lin, x, s.x_hi, s.x_lo, M * d, ax, st))) return rc;        // one split feeds q, k, v (and dW in backward)
+    if ((rc = linear_fwd(lin, ax, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, ax, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, ax, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     if (s.fused) {
         if ((rc = attn_fwd(s.q, s.k, s.v, ids, s.ctx, s.lse, B, H, L, d, dr_p, st))) return rc;
     } else {
@@ -190,12 +225,16 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
             if ((rc = launch_gemm(p, st))) return rc;
         }
     }
-    if ((rc = linear_fwd(lin, s.ctx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = split_act(lin, s.ctx, s.ctx_hi, s.ctx_lo, M * d, actx, st))) return rc;
+    if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
     if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, s.z_a, s.mean_a, s.rstd_a, dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
     // feed-forward
-    if ((rc = linear_fwd(lin, s.y, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, st))) return rc;
-    if ((rc = linear_fwd(lin, s.h_act, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
+    // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
+    if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, s.h_hi, s.h_lo, st))) return rc;
+    ah.x = s.h_act; ah.hi = s.h_hi; ah.lo = s.h_lo;
+    if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, M, d, dr_o, st))) return rc;
     return 0;
 }
@@ -225,9 +264,12 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     float* part_cs = b.f((long long)colsum_partial_rows(M) * 4 * d);
     float* part_sk = b.f(splitk_floats(M, d));
     float* pbeta2 = b.f((long long)B * d);
-    Lin lin{linear_impl() == 2, nullptr, umma_linear_ws_bytes(M, d)};
-    lin.ws = b.f((long long)(lin.ws_bytes / 4));
+    Lin lin = make_lin(b, d);
+    float* g_hi = b.f(M * d); float* g_lo = b.f(M * d);            // split pair of the current [M,d] upstream gradient
+    float* dh_hi = b.f(M * 4 * d); float* dh_lo = b.f(M * 4 * d);  // split pair of dh [M,4d]
     BSA_REQUIRE(b.ok(), "bsa_block_bwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
+    const Act ax{x, s.x_hi, s.x_lo}, actx{s.ctx, s.ctx_hi, s.ctx_lo}, ay{s.y, s.y_hi, s.y_lo}, ah{s.h_act, s.h_hi, s.h_lo};
+    Act ag;
     const Dropout dr_f = make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training);
     const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
     const Dropout dr_a = make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training);
@@ -241,18 +283,21 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
     const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
-    if ((rc = linear_bwd_weight(lin, t2, s.h_act, g.w2, g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, t2, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, st))) return rc;
-    if ((rc = linear_bwd_weight(lin, dh_, s.y, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, dh_, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, st))) return rc;   // dyb = dL/dy
+    if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
+    if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, dh_hi, dh_lo, st))) return rc;
+    const Act adh{dh_, dh_hi, dh_lo};                                          // emitted split by the epilogue above
+    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
     if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_a, st))) return rc;
     if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
     const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
-    if ((rc = linear_bwd_weight(lin, t1, s.ctx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, t1, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, st))) return rc;
+    if ((rc = split_act(lin, t1, g_hi, g_lo, M * d, ag, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, ag, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     if (s.fused) {
         // dP (workspace, unused by this path) doubles as the [B,H,L] delta scratch
         if ((rc = attn_bwd(s.q, s.k, s.v, ids, s.ctx, s.lse, dctx, dq, dk, dv, dP, B, H, L, d, dr_p, st))) return rc;
@@ -296,12 +341,17 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
             if ((rc = launch_gemm(p, st))) return rc;
         }
     }
-    if ((rc = linear_bwd_weight(lin, dq, x, g.wq, g.bq, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_weight(lin, dk, x, g.wk, g.bk, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_weight(lin, dv, x, g.wv, g.bv, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, dq, w.wq, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_bwd_input(lin, dk, w.wk, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
-    if ((rc = linear_bwd_input(lin, dv, w.wv, dx, M, d, d, 1, ACT_NONE, nullptr, st))) return rc;
+    {
+        const float* grads3[3] = {dq, dk, dv};
+        const float* ws3[3] = {w.wq, w.wk, w.wv};
+        float* dws3[3] = {g.wq, g.wk, g.wv};
+        float* dbs3[3] = {g.bq, g.bk, g.bv};
+        for (int i = 0; i < 3; ++i) {
+            if ((rc = split_act(lin, grads3[i], g_hi, g_lo, M * d, ag, st))) return rc;
+            if ((rc = linear_bwd_weight(lin, ag, ax, dws3[i], dbs3[i], M, d, d, part_sk, part_cs, st))) return rc;
+            if ((rc = linear_bwd_input(lin, ag, ws3[i], dx, M, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+        }
+    }
 
     // ---- filter branch: dsp = LN(drop(u) + x), weight alpha
     if ((rc = ln_bwd(dyb, c.alpha, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, nullptr, pgam, pbet, &nblk, M, d, dr_f, st))) return rc;

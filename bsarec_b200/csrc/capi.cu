@@ -48,7 +48,7 @@ struct ProfRec {
     long long launches = 0;
 };
 ProfRec g_prof[PROF_NUM_TAGS] = {{"gemm_simt"}, {"ce_fwd_umma"}, {"ce_bwd_umma"}, {"score_topk_umma"}, {"linear_umma"},
-                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}};
+                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}, {"adam"}};
 std::vector<cudaEvent_t> g_event_pool;
 cudaEvent_t get_event() {
     if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
@@ -223,7 +223,7 @@ int bsa_ce_bwd(const bsa_ce_desc* c, const float* seq_out, const float* item_emb
     BSA_REQUIRE(c && seq_out && item_emb && answers && lse && d_loss && d_seq_out && d_item_emb && workspace, "bsa_ce_bwd: null argument");
     if (ce_impl(c) == 2) {
         BSA_REQUIRE(umma_ce_supported(c->B, c->d, c->item_size), "bsa_ce_bwd: tcgen05 path does not support B=%d d=%d", c->B, c->d);
-        return umma_ce_bwd(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, lse, d_loss, d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
+        return umma_ce_bwd(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, lse, d_loss, d_seq_out, d_item_emb, workspace, workspace_bytes, c->reuse_split != 0, (cudaStream_t)stream);
     }
     return ce_bwd_simt(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, lse, d_loss, d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
 }

@@ -410,26 +410,23 @@ size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, in
     return 2 * al((size_t)a_elems * 4) + 2 * al((size_t)b_elems * 4) + al((size_t)splits_max * M * N * 4) + 4096;
 }
 
-int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a_cols, long long lda, bool a_mn,
-              const float* B, long long b_rows, long long b_cols, long long ldb, bool b_mn, float* C, long long ldc,
-              const float* bias, int act, float* aux_out, const float* aux_in, float alpha, int accumulate, void* ws,
-              size_t ws_bytes, cudaStream_t st) {
+int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st) { return do_split(x, hi, lo, n, st); }
+
+size_t umma_gemm_partial_bytes(int M, int N) { return al((size_t)64 * M * N * 4) + 1024; }
+
+// Operands already split: a = (a_hi, a_lo), b = (b_hi, b_lo).  `partial` backs split-K (may be null: no split-K).
+int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long long a_rows, long long a_cols,
+                 long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
+                 long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
+                 const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
+                 size_t partial_bytes, cudaStream_t st) {
     BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
-    char* p = (char*)ws;
-    const size_t ab = al((size_t)a_rows * lda * 4), bb = al((size_t)b_rows * ldb * 4);
-    float* a_hi = (float*)p; p += ab;
-    float* a_lo = (float*)p; p += ab;
-    float* b_hi = (float*)p; p += bb;
-    float* b_lo = (float*)p; p += bb;
-    float* partial = (float*)p;
     int rc;
-    if ((rc = do_split(A, a_hi, a_lo, a_rows * lda, st))) return rc;
-    if ((rc = do_split(B, b_hi, b_lo, b_rows * ldb, st))) return rc;
     Operand oa{a_hi, a_lo, a_rows, a_cols, lda, a_mn}, ob{b_hi, b_lo, b_rows, b_cols, ldb, b_mn};
     const int BN = N > 128 ? 256 : 128;
     const int tiles = cdiv(M, BM) * cdiv(N, BN);
     int splits = 1;
-    if (tiles < num_sms() && !bias && act == 0) {
+    if (tiles < num_sms() && !bias && act == 0 && !out_hi && partial) {
         splits = num_sms() / tiles;
         const int kb = cdiv(K, BK);
         if (splits > kb / 4) splits = kb / 4;
@@ -438,9 +435,9 @@ int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a
     }
     GemmCore g;
     if ((rc = make_core(g, M, N, K, oa, ob, BN, SCHED_N_FASTEST, splits))) return rc;
-    StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr};
+    StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr, out_hi, out_lo, 0};
     if (g.splits > 1) {
-        BSA_REQUIRE((size_t)(p - (char*)ws) + (size_t)g.splits * M * N * 4 <= ws_bytes, "umma_gemm: workspace too small for split-K");
+        BSA_REQUIRE((size_t)g.splits * M * N * 4 <= partial_bytes, "umma_gemm: workspace too small for split-K");
         ep.partial = partial;
     }
     const long long total = (long long)g.m_tiles * g.n_tiles * g.splits;
@@ -457,6 +454,26 @@ int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a
         BSA_LAUNCH_CHECK();
     }
     return 0;
+}
+
+int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a_cols, long long lda, bool a_mn,
+              const float* B, long long b_rows, long long b_cols, long long ldb, bool b_mn, float* C, long long ldc,
+              const float* bias, int act, float* aux_out, const float* aux_in, float alpha, int accumulate, void* ws,
+              size_t ws_bytes, cudaStream_t st) {
+    BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
+    char* p = (char*)ws;
+    const size_t ab = al((size_t)a_rows * lda * 4), bb = al((size_t)b_rows * ldb * 4);
+    float* a_hi = (float*)p; p += ab;
+    float* a_lo = (float*)p; p += ab;
+    float* b_hi = (float*)p; p += bb;
+    float* b_lo = (float*)p; p += bb;
+    float* partial = (float*)p;
+    BSA_REQUIRE((size_t)(p - (char*)ws) <= ws_bytes, "umma_gemm: workspace too small");
+    int rc;
+    if ((rc = do_split(A, a_hi, a_lo, a_rows * lda, st))) return rc;
+    if ((rc = do_split(B, b_hi, b_lo, b_rows * ldb, st))) return rc;
+    return umma_gemm_ps(M, N, K, a_hi, a_lo, a_rows, a_cols, lda, a_mn, b_hi, b_lo, b_rows, b_cols, ldb, b_mn, C, ldc, bias,
+                        act, aux_out, aux_in, alpha, accumulate, nullptr, nullptr, partial, ws_bytes - (size_t)(p - (char*)ws), st);
 }
 
 // ============================================================================ cross-entropy
@@ -563,12 +580,14 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
 }
 
 int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, const float* lse,
-                const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st) {
+                const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st) {
     CeWs w = carve_ce(ws, B, d, N, true);
     BSA_REQUIRE(ws_bytes >= w.bytes, "bsa_ce_bwd: workspace too small (%zu < %zu)", ws_bytes, w.bytes);
     int rc;
-    if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
-    if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
+    if (!reuse_split) {       // else: left there by umma_ce_fwd (same carve order for the forward-only part)
+        if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
+        if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
+    }
     ProfScope prof(PROF_CE_BWD_UMMA, st, 4.0 * B * (double)N * d);
     const int BNd = d > 128 ? 256 : 128;
     // ds = G E is split over K (= items); its partial sums stay in `partial` ACROSS chunks and are reduced once

@@ -9,7 +9,7 @@ size_t umma_ce_workspace_bytes(int B, int d, long long N);
 int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, float* loss,
                 float* lse, void* ws, size_t ws_bytes, cudaStream_t st);
 int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, const float* lse,
-                const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st);
+                const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st);
 
 bool umma_topk_supported(int B, int d, int k, long long rows);
 size_t umma_topk_workspace_bytes(int B, int d, int k, long long rows);
@@ -23,5 +23,15 @@ int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a
               const float* B, long long b_rows, long long b_cols, long long ldb, bool b_mn, float* C, long long ldc,
               const float* bias, int act, float* aux_out, const float* aux_in, float alpha, int accumulate, void* ws,
               size_t ws_bytes, cudaStream_t st);
+
+// the same with operands supplied as split-TF32 (hi, lo) pairs (produced once by umma_split or by a producer
+// epilogue and reused by several GEMMs); out_hi/out_lo (optional) also receive the result as a split pair.
+int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st);
+size_t umma_gemm_partial_bytes(int M, int N);
+int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long long a_rows, long long a_cols,
+                 long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
+                 long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
+                 const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
+                 size_t partial_bytes, cudaStream_t st);
 
 }  // namespace bsa

@@ -170,7 +170,7 @@ def ce_forward(s: torch.Tensor, E: torch.Tensor, answers: torch.Tensor, impl: in
     lib = _cabi.load()
     B, d = s.shape
     answers = _require_cuda(answers, "answers", torch.int64)
-    cd = CeDesc(B=B, d=d, item_size=E.shape[0], impl=impl)
+    cd = CeDesc(B=B, d=d, item_size=E.shape[0], impl=impl, reuse_split=0)
     with torch.cuda.device(s.device):
         wsb = lib.bsa_ce_workspace_bytes(C.byref(cd))
         ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
@@ -178,17 +178,18 @@ def ce_forward(s: torch.Tensor, E: torch.Tensor, answers: torch.Tensor, impl: in
         lse = torch.empty(B, dtype=torch.float32, device=s.device)
         check(lib.bsa_ce_fwd(C.byref(cd), _ptr(s), _ptr(E), _ptr(answers), _ptr(loss), _ptr(lse), _ptr(ws), wsb, _stream()),
               "bsa_ce_fwd")
-    return loss, lse
+    return loss, lse, ws
 
 
-def ce_backward(s, E, answers, lse, d_loss, dE: torch.Tensor, impl: int = 0) -> torch.Tensor:
-    """Overwrites dE [N,d] with the dense gradient; returns ds [B,d]."""
+def ce_backward(s, E, answers, lse, d_loss, dE: torch.Tensor, impl: int = 0, fwd_ws: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Overwrites dE [N,d] with the dense gradient; returns ds [B,d].  ``fwd_ws``: the workspace ``ce_forward``
+    returned for the same (s, E) — its split copies of both operands are reused instead of being rebuilt."""
     lib = _cabi.load()
     B, d = s.shape
-    cd = CeDesc(B=B, d=d, item_size=E.shape[0], impl=impl)
+    cd = CeDesc(B=B, d=d, item_size=E.shape[0], impl=impl, reuse_split=int(fwd_ws is not None))
     with torch.cuda.device(s.device):
         wsb = lib.bsa_ce_workspace_bytes(C.byref(cd))
-        ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+        ws = fwd_ws if fwd_ws is not None else torch.empty(wsb, dtype=torch.uint8, device=s.device)
         ds = torch.empty(B, d, dtype=torch.float32, device=s.device)
         d_loss = d_loss.to(dtype=torch.float32).contiguous()
         check(lib.bsa_ce_bwd(C.byref(cd), _ptr(s), _ptr(E), _ptr(answers), _ptr(lse), _ptr(d_loss), _ptr(ds), _ptr(dE),
@@ -245,9 +246,9 @@ class FusedLoss(torch.autograd.Function):
         params = dict(zip(names, tensors))
         xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True)
         s = gather_last(xs[-1])
-        loss, lse = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
+        loss, lse, ce_ws = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
         ctx.hyper, ctx.names, ctx.state, ctx.ce_impl = hyper, names, state, ce_impl
-        ctx.answers, ctx.s, ctx.lse = answers, s, lse
+        ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
         ctx.save_for_backward(*tensors)
         return loss
 
@@ -260,7 +261,8 @@ class FusedLoss(torch.autograd.Function):
         if state.L < params["position_embeddings.weight"].shape[0]:
             grads["position_embeddings.weight"].zero_()      # rows >= L are never touched by the kernels
         E = params["item_embeddings.weight"]
-        ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, grads["item_embeddings.weight"], ctx.ce_impl)
+        ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, grads["item_embeddings.weight"], ctx.ce_impl, ctx.ce_ws)
+        ctx.ce_ws = None
         d_out = scatter_last(ds, state.L)
         encoder_backward(hyper, params, state, d_out, grads)
         ctx.state = None

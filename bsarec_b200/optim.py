@@ -1,0 +1,51 @@
+"""``FusedAdam``: drop-in for the ``torch.optim.Adam`` the reference's Trainer builds (``trainers.py:27-28``) with the
+update done by one sm_100a kernel pass per tensor (``bsa_adam_step``) instead of ~13 foreach passes.
+
+Same constructor arguments, same update rule (no amsgrad / maximize), ``state_dict`` entries named as torch's
+(``step``, ``exp_avg``, ``exp_avg_sq``).  CUDA fp32 parameters only — there is no CPU path.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _cabi
+from ._cabi import check
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        if lr < 0.0 or eps < 0.0 or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0 or weight_decay < 0.0:
+            raise ValueError("invalid Adam hyper-parameter")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        lib = _cabi.load()
+        for group in self.param_groups:
+            b1, b2 = group["betas"]
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                if not p.is_cuda or p.dtype != torch.float32 or p.grad.dtype != torch.float32:
+                    raise RuntimeError("FusedAdam: parameters and gradients must be CUDA fp32 (no CPU fallback)")
+                if p.grad.is_sparse:
+                    raise RuntimeError("FusedAdam does not support sparse gradients")
+                st = self.state[p]
+                if not st:
+                    st["step"] = 0
+                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["step"] = int(st["step"]) + 1
+                g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+                if not p.is_contiguous():
+                    raise RuntimeError("FusedAdam: parameters must be contiguous")
+                with torch.cuda.device(p.device):
+                    check(lib.bsa_adam_step(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(),
+                                            p.numel(), float(group["lr"]), float(b1), float(b2), float(group["eps"]),
+                                            float(group["weight_decay"]), st["step"],
+                                            torch.cuda.current_stream().cuda_stream), "bsa_adam_step")
+        return loss

@@ -151,6 +151,9 @@ typedef struct {
     int B, d;
     int64_t item_size;
     int impl;                  /* 0 = auto, 1 = fp32 FFMA, 2 = tcgen05 3xTF32 */
+    int reuse_split;           /* bsa_ce_bwd only: `workspace` is the buffer bsa_ce_fwd just used with the same
+                                  seq_out / item_emb and still holds their split-TF32 copies (skips re-splitting the
+                                  item table: 3 GB of traffic at 1 M items) */
 } bsa_ce_desc;
 
 size_t bsa_ce_workspace_bytes(const bsa_ce_desc* desc);
@@ -200,6 +203,14 @@ size_t bsa_gemm_workspace_bytes(int M, int N, int K, int64_t lda, int64_t ldb, i
 int bsa_gemm(int impl, int M, int N, int K, const float* A, int64_t lda, int a_mn, const float* B, int64_t ldb,
              int b_mn, float* C, int64_t ldc, const float* bias, float alpha, int accumulate, void* workspace,
              size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Optimizer step: torch.optim.Adam's update — Trainer.__init__ / optim.step(),
+ * trainers.py:27-28 and :107 — as one pass over (param, grad, exp_avg, exp_avg_sq), all fp32 [n], updated in place.
+ * No amsgrad / maximize; weight_decay is Adam's L2 term (grad += wd * param).  `step` counts from 1.
+ * ---------------------------------------------------------------------------------------------- */
+int bsa_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, int64_t step, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Small utilities shared by the host wrappers

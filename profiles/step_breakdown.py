@@ -16,7 +16,7 @@ import torch
 from torch.profiler import ProfilerActivity, profile
 
 import bench
-from bsarec_b200 import BSARecModel
+from bsarec_b200 import BSARecModel, FusedAdam
 from helpers import make_args
 
 wl = sys.argv[1] if len(sys.argv) > 1 else "c3"
@@ -27,7 +27,7 @@ if len(sys.argv) > 3:
 dev = torch.device("cuda:0")
 torch.manual_seed(42)
 model = BSARecModel(make_args(cfg, bench.P_DROP, bench.P_DROP, batch_size=B)).to(dev)
-optim = torch.optim.Adam(model.parameters(), lr=1e-3)
+optim = (torch.optim.Adam if os.environ.get('OPT') == 'torch' else FusedAdam)(model.parameters(), lr=1e-3)
 batches = [{k: v.to(dev) for k, v in b.items()} for b in bench.synth_batches(cfg, B, 1234, 2)]
 
 

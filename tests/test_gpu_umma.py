@@ -55,11 +55,11 @@ def test_umma_gemm_bias_alpha_accumulate(cuda_device):
     assert rel_err(got, ref) < 5e-6
 
 
-def _ce(impl, s, E, ans, dloss=1.0):
+def _ce(impl, s, E, ans, dloss=1.0, reuse=False):
     from bsarec_b200 import functional as Fn
-    loss, lse = Fn.ce_forward(s, E, ans, impl)
+    loss, lse, ws = Fn.ce_forward(s, E, ans, impl)
     dE = torch.empty_like(E)
-    ds = Fn.ce_backward(s, E, ans, lse, torch.tensor(dloss, device=s.device), dE, impl)
+    ds = Fn.ce_backward(s, E, ans, lse, torch.tensor(dloss, device=s.device), dE, impl, ws if reuse else None)
     torch.cuda.synchronize()
     return loss.cpu(), lse.cpu(), ds.cpu(), dE.cpu()
 
@@ -76,8 +76,8 @@ def test_fused_cross_entropy_fwd_bwd(B, d, N, cuda_device):
     ref_loss = torch.nn.functional.cross_entropy(logits, ans)
     (2.5 * ref_loss).backward()
     ref_lse = torch.logsumexp(logits.detach(), dim=1)
-    for impl in (1, 2):
-        loss, lse, ds, dE = _ce(impl, s.to(cuda_device), E.to(cuda_device), ans.to(cuda_device), 2.5)
+    for impl, reuse in ((1, False), (2, False), (2, True)):        # reuse: backward reads the forward's operand splits
+        loss, lse, ds, dE = _ce(impl, s.to(cuda_device), E.to(cuda_device), ans.to(cuda_device), 2.5, reuse)
         assert abs(float(loss) - float(ref_loss)) < 2e-6 * abs(float(ref_loss)), impl
         assert rel_err(lse, ref_lse) < 2e-6, impl
         assert rel_err(ds, sd.grad) < 1e-5, impl
@@ -151,3 +151,24 @@ def test_sharded_topk_merge_equals_unsharded(cuda_device):
             ci.append(i)
         mv, mi = Fn.topk_merge(torch.stack(cv), torch.stack(ci))
         assert torch.equal(mi, full_i) and torch.equal(mv, full_v), impl
+
+
+@pytest.mark.parametrize("wd", [0.0, 0.01])
+def test_fused_adam_matches_torch_adam(wd, cuda_device):
+    """bsa_adam_step vs torch.optim.Adam (trainers.py:27-28) over several steps, ragged sizes included."""
+    from bsarec_b200 import FusedAdam
+    g = torch.Generator().manual_seed(3)
+    shapes = [(1001, 64), (7,), (64, 64), (1, 1, 33)]
+    ref = [torch.randn(s, generator=g).to(cuda_device).requires_grad_(True) for s in shapes]
+    got = [r.detach().clone().requires_grad_(True) for r in ref]
+    o_ref = torch.optim.Adam(ref, lr=1e-3, betas=(0.9, 0.999), weight_decay=wd)
+    o_got = FusedAdam(got, lr=1e-3, betas=(0.9, 0.999), weight_decay=wd)
+    for step in range(5):
+        for r, q in zip(ref, got):
+            grad = (torch.randn(r.shape, generator=g) * (10.0 ** (step - 2))).to(cuda_device)
+            r.grad, q.grad = grad.clone(), grad.clone()
+        o_ref.step()
+        o_got.step()
+    for r, q in zip(ref, got):
+        assert rel_err(q.detach().cpu(), r.detach().cpu()) < 1e-6
+    assert o_got.state[got[0]]["step"] == 5

@@ -82,6 +82,12 @@ SIGNATURES = {
     "bsa_block_fwd": (_I, [C.POINTER(BlockDesc), C.POINTER(BlockPtrs), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_block_bwd": (_I, [C.POINTER(BlockDesc), C.POINTER(BlockPtrs), _VP, _VP, _VP, _VP, _VP, _VP,
                            C.POINTER(BlockPtrs), _VP, _SZ, _VP]),
+    "bsa_block_last_supported": (_I, [C.POINTER(BlockDesc)]),
+    "bsa_block_last_saved_bytes": (_SZ, [C.POINTER(BlockDesc)]),
+    "bsa_block_last_workspace_bytes": (_SZ, [C.POINTER(BlockDesc)]),
+    "bsa_block_last_fwd": (_I, [C.POINTER(BlockDesc), C.POINTER(BlockPtrs), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "bsa_block_last_bwd": (_I, [C.POINTER(BlockDesc), C.POINTER(BlockPtrs), _VP, _VP, _VP, _VP, _VP, _VP,
+                                C.POINTER(BlockPtrs), _VP, _SZ, _VP]),
     "bsa_ce_workspace_bytes": (_SZ, [C.POINTER(CeDesc)]),
     "bsa_ce_fwd": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_ce_bwd": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),

@@ -5,6 +5,7 @@
 #include "rowwise.cuh"
 #include "umma_engine.cuh"
 #include "attn.cuh"
+#include "lastrow.cuh"
 
 #include <cmath>
 
@@ -361,6 +362,178 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = reduce_partials(pbeta2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
     return 0;
 }
+
+// ================================================================================================ last block, last row
+// bsa_block_last_fwd / bsa_block_last_bwd: the block evaluated at position L-1 only (see lastrow.cu for the math).
+namespace {
+
+struct SavedLast {
+    float *xl, *low, *z_f, *mean_f, *rstd_f, *ql, *gq, *p, *xs, *sp, *ctx, *z_a, *mean_a, *rstd_a, *y, *h_pre, *h_act,
+        *z_o, *mean_o, *rstd_o;
+    size_t bytes;
+};
+
+SavedLast carve_saved_last(void* ptr, const bsa_block_desc& c) {
+    const long long B = c.B, d = c.d, H = c.H, L = c.L;
+    Bump b(ptr, ~(size_t)0);
+    SavedLast s;
+    s.xl = b.f(B * d); s.low = b.f(B * d); s.z_f = b.f(B * d); s.mean_f = b.f(B); s.rstd_f = b.f(B);
+    s.ql = b.f(B * d); s.gq = b.f(B * H * d); s.p = b.f(B * H * L); s.xs = b.f(B * H * d); s.sp = b.f(B * H);
+    s.ctx = b.f(B * d); s.z_a = b.f(B * d); s.mean_a = b.f(B); s.rstd_a = b.f(B); s.y = b.f(B * d);
+    s.h_pre = b.f(B * 4 * d); s.h_act = b.f(B * 4 * d); s.z_o = b.f(B * d); s.mean_o = b.f(B); s.rstd_o = b.f(B);
+    s.bytes = b.off;
+    return s;
+}
+
+// C[z] = A[z] op B[z] for z over heads: strides in floats
+int head_gemm(const float* A, int lda, bool a_k, long long sA, const float* Bm, int ldb, bool b_k, long long sB, float* C,
+              int ldc, long long sC, int M, int N, int K, int H, cudaStream_t st) {
+    GemmP p;
+    p.A = A; p.B = Bm; p.C = C; p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc;
+    p.a_kmajor = a_k; p.b_kmajor = b_k; p.batch = H; p.inner = H; p.sAi = sA; p.sBi = sB; p.sCi = sC;
+    return launch_gemm(p, st);
+}
+
+size_t last_workspace_bytes(const bsa_block_desc& c) {
+    const long long B = c.B, d = c.d, H = c.H;
+    Bump b(nullptr, ~(size_t)0);
+    for (int i = 0; i < 10; ++i) b.f(B * d);        // tmp, u, dsp | dyb, dd, dxl, dzf, dctx, dql, dlow/pb2/tmp
+    b.f(B * 4 * d);                                 // dh
+    b.f(B * H * d); b.f(B * H * d); b.f(B * H); b.f(B * H);       // dxs, dgq, dsp, dcq
+    b.f(2ll * rowwise_partial_blocks(B) * d);
+    b.f((long long)colsum_partial_rows(B) * 4 * d);
+    b.f(splitk_floats(B, d));
+    return b.off + 8192;
+}
+
+}  // namespace
+
+bool block_last_supported(const bsa_block_desc& c) {
+    return c.H > 0 && c.d % c.H == 0 && c.d % 4 == 0 && lastrow_supported(c.L, c.d, c.H);
+}
+
+int block_last_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+                   const float* x, float* out_last, void* saved_p, void* ws, size_t ws_bytes, cudaStream_t st) {
+    const int B = c.B, L = c.L, d = c.d, H = c.H, dh = d / H;
+    BSA_REQUIRE(block_last_supported(c), "bsa_block_last_fwd: unsupported shape (L=%d d=%d H=%d)", L, d, H);
+    if (B == 0) return 0;
+    SavedLast s = carve_saved_last(saved_p, c);
+    Bump b(ws, ws_bytes);
+    float* tmp = b.f((long long)B * d);
+    float* u = b.f((long long)B * d);
+    float* dsp = b.f((long long)B * d);
+    BSA_REQUIRE(b.ok(), "bsa_block_last_fwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
+    const Dropout dr_f = dropout_rows(make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
+    const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
+    const Dropout dr_a = dropout_rows(make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
+    const Dropout dr_o = dropout_rows(make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
+    const Lin lin{false, nullptr, nullptr, nullptr, 0};           // [B, d] problems: fp32 FFMA GEMMs
+    const int r = filter_rank(L, c.kept_bins);
+    int rc;
+    if ((rc = gather_last_rows(x, s.xl, B, L, d, st))) return rc;
+    const Act axl{s.xl, nullptr, nullptr};
+    if ((rc = linear_fwd(lin, axl, w.wq, w.bq, s.ql, B, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    // gq[b,h,:] = Wk_h^T q_h
+    if ((rc = head_gemm(s.ql, d, true, dh, w.wk, d, false, (long long)dh * d, s.gq, H * d, d, B, d, dh, H, st))) return rc;
+    if ((rc = last_attn_fwd(x, ids, s.gq, s.ql, w.bk, basis, r, s.p, s.xs, s.sp, s.low, B, H, L, d, dr_p, st))) return rc;
+    // ctx[b, h cols] = Wv_h xs_h + bv_h sp_h
+    if ((rc = head_gemm(s.xs, H * d, true, d, w.wv, d, true, (long long)dh * d, s.ctx, d, dh, B, dh, d, H, st))) return rc;
+    if ((rc = last_ctx_bias(s.ctx, w.bv, s.sp, B, d, H, st))) return rc;
+    const Act actx{s.ctx, nullptr, nullptr};
+    if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, B, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    // filter branch at row L-1
+    if ((rc = last_filter_u(u, s.low, s.xl, w.sqrt_beta, B, d, st))) return rc;
+    if ((rc = residual_ln_fwd(u, s.xl, w.f_ln_w, w.f_ln_b, dsp, s.z_f, s.mean_f, s.rstd_f, nullptr, 0.f, 0.f, B, d, dr_f, st))) return rc;
+    if ((rc = residual_ln_fwd(tmp, s.xl, w.a_ln_w, w.a_ln_b, s.y, s.z_a, s.mean_a, s.rstd_a, dsp, c.alpha, 1.0f - c.alpha, B, d, dr_a, st))) return rc;
+    const Act ay{s.y, nullptr, nullptr}, ah{s.h_act, nullptr, nullptr};
+    if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, B, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, nullptr, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, B, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    return residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, out_last, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, B, d, dr_o, st);
+}
+
+// d_out_last [B,d] = gradient wrt the block's output at position L-1.  dx [B,L,d] (every position) and all of `g`
+// are overwritten.
+int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+                   const float* x, const void* saved_p, const float* d_out_last, float* dx, const bsa_block_grads& g,
+                   void* ws, size_t ws_bytes, cudaStream_t st) {
+    (void)ids;
+    const int B = c.B, L = c.L, d = c.d, H = c.H, dh = d / H;
+    BSA_REQUIRE(block_last_supported(c), "bsa_block_last_bwd: unsupported shape (L=%d d=%d H=%d)", L, d, H);
+    if (B == 0) return 0;
+    SavedLast s = carve_saved_last(const_cast<void*>(saved_p), c);
+    Bump b(ws, ws_bytes);
+    const long long Bd = (long long)B * d;
+    float* dyb = b.f(Bd); float* dd = b.f(Bd); float* dxl = b.f(Bd); float* dzf = b.f(Bd); float* dctx = b.f(Bd);
+    float* dql = b.f(Bd); float* dlow = b.f(Bd); float* pb2 = b.f(Bd); float* tmpbd = b.f(Bd);
+    float* dh_ = b.f(Bd * 4);
+    float* dxs = b.f(Bd * H); float* dgq = b.f(Bd * H); float* dsp = b.f((long long)B * H); float* dcq = b.f((long long)B * H);
+    const int nrb = rowwise_partial_blocks(B);
+    float* pgam = b.f((long long)nrb * d);
+    float* pbet = b.f((long long)nrb * d);
+    float* part_cs = b.f((long long)colsum_partial_rows(B) * 4 * d);
+    float* part_sk = b.f(splitk_floats(B, d));
+    BSA_REQUIRE(b.ok(), "bsa_block_last_bwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
+    const Dropout dr_f = dropout_rows(make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
+    const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
+    const Dropout dr_a = dropout_rows(make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
+    const Dropout dr_o = dropout_rows(make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
+    const Lin lin{false, nullptr, nullptr, nullptr, 0};
+    const int r = filter_rank(L, c.kept_bins);
+    int rc, nblk = 0;
+    const Act axl{s.xl, nullptr, nullptr}, actx{s.ctx, nullptr, nullptr}, ay{s.y, nullptr, nullptr}, ah{s.h_act, nullptr, nullptr};
+
+    // ---- feed-forward
+    if ((rc = ln_bwd(d_out_last, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, B, d, dr_o, st))) return rc;
+    if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
+    const Act at2{dr_o.thr ? dd : dyb, nullptr, nullptr};
+    if ((rc = linear_bwd_weight(lin, at2, ah, g.w2, g.b2, B, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, at2, w.w2, dh_, B, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, nullptr, nullptr, st))) return rc;
+    const Act adh{dh_, nullptr, nullptr};
+    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, B, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, B, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
+
+    // ---- attention branch: gsp = LN(drop(tmp) + xl), weight (1-alpha); dxl starts as the residual gradient
+    if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dxl, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, B, d, dr_a, st))) return rc;
+    if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
+    const Act at1{dr_a.thr ? dd : dxl, nullptr, nullptr};
+    if ((rc = linear_bwd_weight(lin, at1, actx, g.wo, g.bo, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, at1, w.wo, dctx, B, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    // ctx_h = Wv_h xs_h + bv_h sp_h
+    //   dWv[h rows] = sum_b dctx_h^T xs_h   (M = dh, N = d, K = B per head)
+    if ((rc = head_gemm(dctx, d, false, dh, s.xs, H * d, false, d, g.wv, d, (long long)dh * d, dh, d, B, H, st))) return rc;
+    if ((rc = last_head_scale(tmpbd, dctx, s.sp, B, d, H, st))) return rc;
+    if ((rc = colsum(tmpbd, B, d, part_cs, g.bv, 0, st))) return rc;
+    //   dxs_h = Wv_h^T dctx_h  ;  dsp_h = bv_h . dctx_h
+    if ((rc = head_gemm(dctx, d, true, dh, w.wv, d, false, (long long)dh * d, dxs, H * d, d, B, d, dh, H, st))) return rc;
+    if ((rc = last_dsp(dctx, w.bv, dsp, B, d, H, st))) return rc;
+
+    // ---- filter branch: dsp = LN(drop(u) + xl), weight alpha
+    if ((rc = ln_bwd(dyb, c.alpha, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, nullptr, pgam, pbet, &nblk, B, d, dr_f, st))) return rc;
+    if ((rc = reduce_partials(pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = last_filter_bwd(dzf, s.xl, s.low, w.sqrt_beta, dlow, dxl, pb2, B, d, dr_f, st))) return rc;
+    if ((rc = reduce_partials(pb2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
+
+    // ---- per-sequence adjoint over all positions
+    if ((rc = last_attn_bwd(x, s.p, s.gq, dxs, dsp, dlow, basis, r, dx, dgq, dcq, B, H, L, d, dr_p, st))) return rc;
+    // gq_h = Wk_h^T q_h ; cq_h = q_h . bk_h
+    if ((rc = head_gemm(dgq, H * d, true, d, w.wk, d, true, (long long)dh * d, dql, d, dh, B, dh, d, H, st))) return rc;
+    if ((rc = last_add_head_bias(dql, dcq, w.bk, B, d, H, st))) return rc;
+    if ((rc = head_gemm(s.ql, d, false, dh, dgq, H * d, false, d, g.wk, d, (long long)dh * d, dh, d, B, H, st))) return rc;
+    if ((rc = last_head_scale(tmpbd, s.ql, dcq, B, d, H, st))) return rc;
+    if ((rc = colsum(tmpbd, B, d, part_cs, g.bk, 0, st))) return rc;
+    // q = xl Wq^T + bq
+    const Act adql{dql, nullptr, nullptr};
+    if ((rc = linear_bwd_weight(lin, adql, axl, g.wq, g.bq, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_input(lin, adql, w.wq, dxl, B, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    // value.bias / key.bias done; the row L-1 residual paths go into dx last
+    return last_add_rows(dx, dxl, B, L, d, st);
+}
+
+size_t block_last_saved_bytes(const bsa_block_desc& c) { return carve_saved_last(nullptr, c).bytes + 256; }
+size_t block_last_workspace_bytes(const bsa_block_desc& c) { return last_workspace_bytes(c); }
 
 size_t block_saved_bytes(const bsa_block_desc& c) { return carve_saved(nullptr, c).bytes + 256; }
 size_t block_workspace_bytes(const bsa_block_desc& c) { return workspace_bytes(c); }

@@ -30,6 +30,14 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
               size_t ws_bytes, cudaStream_t st);
 size_t block_saved_bytes(const bsa_block_desc& c);
 size_t block_workspace_bytes(const bsa_block_desc& c);
+bool block_last_supported(const bsa_block_desc& c);
+int block_last_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+                   const float* x, float* out_last, void* saved_p, void* ws, size_t ws_bytes, cudaStream_t st);
+int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
+                   const float* x, const void* saved_p, const float* d_out_last, float* dx, const bsa_block_grads& g,
+                   void* ws, size_t ws_bytes, cudaStream_t st);
+size_t block_last_saved_bytes(const bsa_block_desc& c);
+size_t block_last_workspace_bytes(const bsa_block_desc& c);
 void set_linear_impl(int impl);
 int linear_impl();
 void set_attn_impl(int impl);
@@ -48,7 +56,7 @@ struct ProfRec {
     long long launches = 0;
 };
 ProfRec g_prof[PROF_NUM_TAGS] = {{"gemm_simt"}, {"ce_fwd_umma"}, {"ce_bwd_umma"}, {"score_topk_umma"}, {"linear_umma"},
-                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}, {"adam"}};
+                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}, {"adam"}, {"last_row_fwd"}, {"last_row_bwd"}};
 std::vector<cudaEvent_t> g_event_pool;
 cudaEvent_t get_event() {
     if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
@@ -193,6 +201,23 @@ int bsa_block_bwd(const bsa_block_desc* c, const bsa_block_weights* w, const flo
                   void* workspace, size_t workspace_bytes, void* stream) {
     BSA_REQUIRE(c && w && basis && ids && x_in && saved && d_x_out && d_x_in && g && workspace, "bsa_block_bwd: null argument");
     return block_bwd(*c, *w, basis, (const long long*)ids, x_in, saved, d_x_out, d_x_in, *g, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int bsa_block_last_supported(const bsa_block_desc* c) { return c && block_last_supported(*c) ? 1 : 0; }
+size_t bsa_block_last_saved_bytes(const bsa_block_desc* c) { return block_last_saved_bytes(*c); }
+size_t bsa_block_last_workspace_bytes(const bsa_block_desc* c) { return block_last_workspace_bytes(*c); }
+
+int bsa_block_last_fwd(const bsa_block_desc* c, const bsa_block_weights* w, const float* basis, const int64_t* ids,
+                       const float* x_in, float* out_last, void* saved, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && w && basis && ids && x_in && out_last && saved && workspace, "bsa_block_last_fwd: null argument");
+    return block_last_fwd(*c, *w, basis, (const long long*)ids, x_in, out_last, saved, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int bsa_block_last_bwd(const bsa_block_desc* c, const bsa_block_weights* w, const float* basis, const int64_t* ids,
+                       const float* x_in, const void* saved, const float* d_out_last, float* d_x_in, const bsa_block_grads* g,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && w && basis && ids && x_in && saved && d_out_last && d_x_in && g && workspace, "bsa_block_last_bwd: null argument");
+    return block_last_bwd(*c, *w, basis, (const long long*)ids, x_in, saved, d_out_last, d_x_in, *g, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------ cross-entropy

@@ -46,7 +46,7 @@ extern int g_profile_on;
 void prof_begin(int tag, cudaStream_t st);
 void prof_end(int tag, cudaStream_t st, double work);
 enum ProfTag : int { PROF_GEMM_SIMT = 0, PROF_CE_FWD_UMMA, PROF_CE_BWD_UMMA, PROF_TOPK_UMMA, PROF_LINEAR_UMMA,
-                     PROF_EMBED_FWD, PROF_EMBED_BWD, PROF_SCATTER_ADD, PROF_ATTN_FWD, PROF_ATTN_BWD, PROF_ADAM, PROF_NUM_TAGS };
+                     PROF_EMBED_FWD, PROF_EMBED_BWD, PROF_SCATTER_ADD, PROF_ATTN_FWD, PROF_ATTN_BWD, PROF_ADAM, PROF_LAST_FWD, PROF_LAST_BWD, PROF_NUM_TAGS };
 
 struct ProfScope {
     int tag; cudaStream_t st; double work;
@@ -60,6 +60,9 @@ struct Dropout {
     unsigned long long key;   // site key
     unsigned int thr;         // keep iff r16 >= thr ; thr == 0 -> dropout off
     float scale;              // 1/(1-p)
+    // row mapping for kernels that run on a row subset of a [rows, d] tensor (the last-position path): element (row, j)
+    // draws the mask of element (row * rmul + radd, j) of the full tensor.  Identity by default.
+    long long rmul = 1, radd = 0;
 };
 
 __host__ __device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
@@ -77,12 +80,19 @@ static inline Dropout make_dropout(unsigned long long seed, int site, float p, i
     return d;
 }
 
+static inline Dropout dropout_rows(Dropout d, long long rmul, long long radd) { d.rmul = rmul; d.radd = radd; return d; }
+
 // multiplier (0 or scale) for linear element index i
 __device__ __forceinline__ float dropout_mult(const Dropout& dr, unsigned long long i) {
     if (dr.thr == 0u) return 1.0f;
     unsigned long long w = splitmix64(dr.key + (i >> 2));
     unsigned int r16 = (unsigned int)(w >> (16 * (unsigned int)(i & 3ull))) & 0xFFFFu;
     return r16 >= dr.thr ? dr.scale : 0.0f;
+}
+
+// element (row, j) of a [*, d] tensor under the row mapping
+__device__ __forceinline__ float dropout_mult_row(const Dropout& dr, long long row, int d, int j) {
+    return dropout_mult(dr, (unsigned long long)((row * dr.rmul + dr.radd) * d + j));
 }
 
 // four consecutive elements starting at i (i % 4 == 0): one hash for all four

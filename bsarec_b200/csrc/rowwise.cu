@@ -150,7 +150,7 @@ residual_ln_fwd_kernel(const float* __restrict__ tmp, const float* __restrict__ 
             v[i] = 0.f;
             if (j < d) {
                 const long long o = row * d + j;
-                v[i] = tmp[o] * dropout_mult(dr, (unsigned long long)o) + resid[o];
+                v[i] = tmp[o] * dropout_mult_row(dr, row, d, j) + resid[o];
                 if (z_save) z_save[o] = v[i];
             }
         }
@@ -208,7 +208,7 @@ ln_bwd_kernel(const float* __restrict__ dy, float dy_scale, const float* __restr
                 const long long o = row * d + j;
                 const float r = rstd * (g[i] - c1 - xh[i] * c2);
                 dz[o] = r;
-                if (ddrop) ddrop[o] = r * dropout_mult(dr, (unsigned long long)o);
+                if (ddrop) ddrop[o] = r * dropout_mult_row(dr, row, d, j);
             }
         }
     }

@@ -231,6 +231,11 @@ struct EpiTopk {
             float v[32];
             tmem_ld32(acc + c0, v);
             if (!row_ok || n0 + c0 >= g.N) continue;
+            // once the list is warm almost no chunk holds a candidate: one max over the chunk decides
+            float cm = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) cm = fmaxf(cm, (n0 + c0 + j < g.N) ? v[j] : -INFINITY);
+            if (cm < thr) continue;                     // ties with thr still take the exact path below
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
                 const int id = n0 + c0 + j;

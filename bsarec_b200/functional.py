@@ -72,12 +72,19 @@ def _block_ptrs(tensors: Dict[str, torch.Tensor], layer: int) -> BlockPtrs:
 
 class EncoderState:
     """Everything one forward pass leaves behind for its backward pass."""
-    __slots__ = ("ids", "B", "L", "seed", "training", "mean", "rstd", "xs", "saved", "workspace")
+    __slots__ = ("ids", "B", "L", "seed", "training", "mean", "rstd", "xs", "saved", "workspace", "last_row")
+
+
+LAST_ROW_PATH = True      # module switch (tests): run the last block at position L-1 only when the caller needs no more
 
 
 def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor, training: bool, seed: int,
-                    keep_for_backward: bool) -> Tuple[List[torch.Tensor], Optional[EncoderState]]:
-    """ids int64 [B,L] -> [h0, x1, ..., xP] (each [B,L,d]); mirrors BSARecModel.forward (bsarec.py:16-28)."""
+                    keep_for_backward: bool, last_only: bool = False) -> Tuple[List[torch.Tensor], Optional[EncoderState]]:
+    """ids int64 [B,L] -> [h0, x1, ..., xP] (each [B,L,d]); mirrors BSARecModel.forward (bsarec.py:16-28).
+
+    ``last_only``: the caller reads nothing but position L-1 of the last block (calculate_loss, bsarec.py:32; the eval
+    branch, trainers.py:127).  The last list entry is then ``[B,d]`` = ``xP[:, -1, :]``, computed by
+    ``bsa_block_last_fwd`` without evaluating the other L-1 rows of that block."""
     lib = _cabi.load()
     ids = _require_cuda(ids, "input_ids", torch.int64)
     B, L = ids.shape
@@ -102,8 +109,22 @@ def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor
         ws_bytes = lib.bsa_block_workspace_bytes(C.byref(bd0))
         workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         shared_saved = None
+        last_row = False
         for l in range(h.num_hidden_layers):
             bd = _block_desc(h, B, L, l, training, seed)
+            if last_only and LAST_ROW_PATH and l == h.num_hidden_layers - 1 and lib.bsa_block_last_supported(C.byref(bd)):
+                last_row = True
+                lsaved = torch.empty(lib.bsa_block_last_saved_bytes(C.byref(bd)), dtype=torch.uint8, device=dev)
+                lws_bytes = lib.bsa_block_last_workspace_bytes(C.byref(bd))
+                if lws_bytes > workspace.numel():
+                    workspace = torch.empty(lws_bytes, dtype=torch.uint8, device=dev)
+                w = _block_ptrs(params, l)
+                out_last = torch.empty(B, d, dtype=torch.float32, device=dev)
+                check(lib.bsa_block_last_fwd(C.byref(bd), C.byref(w), _ptr(basis), _ptr(ids), _ptr(xs[-1]), _ptr(out_last),
+                                             _ptr(lsaved), _ptr(workspace), workspace.numel(), st), "bsa_block_last_fwd")
+                xs.append(out_last)
+                saved_list.append(lsaved)
+                break
             if keep_for_backward or shared_saved is None:
                 saved = torch.empty(saved_bytes, dtype=torch.uint8, device=dev)
                 shared_saved = saved
@@ -115,9 +136,12 @@ def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor
                                     _ptr(workspace), ws_bytes, st), "bsa_block_fwd")
             xs.append(x_out)
             saved_list.append(saved)
+    if last_only and not last_row:          # full last block was run: hand back its last position
+        xs[-1] = gather_last(xs[-1])
     if not keep_for_backward:
         return xs, None
     state = EncoderState()
+    state.last_row = last_row
     state.ids, state.B, state.L, state.seed, state.training = ids, B, L, seed, training
     state.mean, state.rstd, state.xs, state.saved, state.workspace = mean, rstd, xs, saved_list, workspace
     return xs, state
@@ -125,7 +149,8 @@ def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor
 
 def encoder_backward(h: Hyper, params: Dict[str, torch.Tensor], state: EncoderState, d_out: torch.Tensor,
                      grads: Dict[str, torch.Tensor]) -> None:
-    """d_out: gradient wrt the last block's output [B,L,d].  Writes every encoder/embedding gradient into
+    """d_out: gradient wrt the last block's output — [B,d] (position L-1) if the forward ran with ``last_only``,
+    else [B,L,d].  Writes every encoder/embedding gradient into
     ``grads`` (item table: accumulated on top of what is already there)."""
     lib = _cabi.load()
     B, L, d, dev = state.B, state.L, h.hidden_size, d_out.device
@@ -139,6 +164,13 @@ def encoder_backward(h: Hyper, params: Dict[str, torch.Tensor], state: EncoderSt
             w = _block_ptrs(params, l)
             gp = _block_ptrs(grads, l)
             dx = torch.empty(B, L, d, dtype=torch.float32, device=dev)
+            if l == h.num_hidden_layers - 1 and state.last_row:       # g is [B,d]: gradient at position L-1
+                check(lib.bsa_block_last_bwd(C.byref(bd), C.byref(w), _ptr(basis), _ptr(state.ids), _ptr(state.xs[l]),
+                                             _ptr(state.saved[l]), _ptr(g), _ptr(dx), C.byref(gp), _ptr(state.workspace),
+                                             ws_bytes, st), "bsa_block_last_bwd")
+                g = dx
+                state.saved[l] = None
+                continue
             check(lib.bsa_block_bwd(C.byref(bd), C.byref(w), _ptr(basis), _ptr(state.ids), _ptr(state.xs[l]),
                                     _ptr(state.saved[l]), _ptr(g), _ptr(dx), C.byref(gp), _ptr(state.workspace), ws_bytes, st),
                   "bsa_block_bwd")
@@ -244,8 +276,8 @@ class FusedLoss(torch.autograd.Function):
     def forward(ctx, hyper: Hyper, names: Sequence[str], ids, answers, training: bool, seed: int, ce_impl: int,
                 *tensors):
         params = dict(zip(names, tensors))
-        xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True)
-        s = gather_last(xs[-1])
+        xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
+        s = xs[-1]
         loss, lse, ce_ws = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
         ctx.hyper, ctx.names, ctx.state, ctx.ce_impl = hyper, names, state, ce_impl
         ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
@@ -263,7 +295,7 @@ class FusedLoss(torch.autograd.Function):
         E = params["item_embeddings.weight"]
         ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, grads["item_embeddings.weight"], ctx.ce_impl, ctx.ce_ws)
         ctx.ce_ws = None
-        d_out = scatter_last(ds, state.L)
+        d_out = ds if state.last_row else scatter_last(ds, state.L)
         encoder_backward(hyper, params, state, d_out, grads)
         ctx.state = None
         return (None, None, None, None, None, None, None) + tuple(grads[n] for n in names)

@@ -135,8 +135,9 @@ class BSARecModel(nn.Module):
     @torch.no_grad()
     def last_hidden(self, input_ids) -> torch.Tensor:
         """[B,d] = predict(input_ids)[:, -1, :] without building the full output list on the host side."""
-        xs, _ = Fn.encoder_forward(self._hyper(), self._tensors(), input_ids, False, 0, keep_for_backward=False)
-        return Fn.gather_last(xs[-1])
+        xs, _ = Fn.encoder_forward(self._hyper(), self._tensors(), input_ids, False, 0, keep_for_backward=False,
+                                   last_only=True)
+        return xs[-1]
 
     @torch.no_grad()
     def full_sort_topk(self, input_ids, user_ids=None, hist_indptr=None, hist_indices=None, k: int = 20):

@@ -143,6 +143,22 @@ int bsa_block_bwd(const bsa_block_desc* desc, const bsa_block_weights* w, const 
                   float* d_x_in, const bsa_block_grads* g, void* workspace, size_t workspace_bytes,
                   void* stream);
 
+/* The LAST block evaluated at position L-1 only.  calculate_loss (model/bsarec.py:32) and the trainer's eval branch
+ * (trainers.py:127) read nothing but out[:, -1, :] of the last block, so there only one query row per sequence is
+ * live; with the key/value projections folded into the query side the block needs no [B*L, d] GEMM (csrc/lastrow.cu).
+ * Same values as bsa_block_fwd(...)[:, L-1, :] up to fp32 rounding, same dropout masks, exact adjoint.
+ *   out_last [B,d];  bsa_block_last_bwd: d_out_last [B,d] in, d_x_in [B,L,d] (every position) and `g` overwritten.
+ * Supported for heads <= 8, d <= 1024 (bsa_block_last_supported); the host falls back to the full block otherwise. */
+int bsa_block_last_supported(const bsa_block_desc* desc);
+size_t bsa_block_last_saved_bytes(const bsa_block_desc* desc);
+size_t bsa_block_last_workspace_bytes(const bsa_block_desc* desc);
+int bsa_block_last_fwd(const bsa_block_desc* desc, const bsa_block_weights* w, const float* basis, const int64_t* ids,
+                       const float* x_in, float* out_last, void* saved, void* workspace, size_t workspace_bytes,
+                       void* stream);
+int bsa_block_last_bwd(const bsa_block_desc* desc, const bsa_block_weights* w, const float* basis, const int64_t* ids,
+                       const float* x_in, const void* saved, const float* d_out_last, float* d_x_in,
+                       const bsa_block_grads* g, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * (3) Full-catalog cross-entropy without materialising the [B, item_size] logits
  *     replaces BSARecModel.calculate_loss's matmul + CrossEntropyLoss   (model/bsarec.py:32-35)

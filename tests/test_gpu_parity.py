@@ -48,9 +48,19 @@ def test_forward_all_layers_vs_reference_golden(name, cuda_device):
     assert torch.equal(last, outs[-1])
 
 
+@pytest.fixture(params=[True, False], ids=["lastrow", "fullblock"])
+def last_row_path(request):
+    """Both ways of running the last block: at position L-1 only (default) and as a full block."""
+    from bsarec_b200 import functional as Fn
+    old = Fn.LAST_ROW_PATH
+    Fn.LAST_ROW_PATH = request.param
+    yield request.param
+    Fn.LAST_ROW_PATH = old
+
+
 @pytest.mark.parametrize("name", SMALL)
 @pytest.mark.parametrize("ce_impl", [1, 0])
-def test_loss_and_42_grads_vs_reference_golden(name, ce_impl, cuda_device):
+def test_loss_and_42_grads_vs_reference_golden(name, ce_impl, last_row_path, cuda_device):
     cfgkw, data = load_golden(name)
     P = golden_params(data)
     model = build_model(cfgkw, P, cuda_device).train()          # dropout probs are 0 in the golden runs
@@ -68,7 +78,7 @@ def test_loss_and_42_grads_vs_reference_golden(name, ce_impl, cuda_device):
 
 
 @pytest.mark.parametrize("p_hidden,p_attn", [(0.5, 0.5), (0.25, 0.0), (0.0, 0.3)])
-def test_train_mode_dropout_masks_match_oracle_rng(p_hidden, p_attn, cuda_device):
+def test_train_mode_dropout_masks_match_oracle_rng(p_hidden, p_attn, last_row_path, cuda_device):
     """Same counter RNG on both sides -> identical masks -> the p>0 path is checked value for value."""
     cfgkw = dict(item_size=157, hidden_size=32, max_seq_length=20, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.6)
     cfg = oracle_cfg(cfgkw, p_hidden, p_attn)
@@ -176,7 +186,7 @@ def test_beauty_test_split_metrics_identical_to_reference(cuda_device):
     (dict(item_size=300, hidden_size=64, max_seq_length=150, num_attention_heads=1, num_hidden_layers=1, c=7, alpha=0.5), 6, 0.3),
     (dict(item_size=300, hidden_size=128, max_seq_length=75, num_attention_heads=2, num_hidden_layers=1, c=5, alpha=0.4), 4, 0.0),
 ])
-def test_fused_attention_kernel_vs_oracle_and_unfused(cfgkw, B, p_attn, cuda_device):
+def test_fused_attention_kernel_vs_oracle_and_unfused(cfgkw, B, p_attn, last_row_path, cuda_device):
     """Head sizes 32/64 run the fused attention kernel (flash-style, P never materialised): checked value for value
     against the oracle (same dropout masks) over several key blocks (L > 64), padded and all-padding rows, and
     against the unfused GEMM + softmax path of the same library."""

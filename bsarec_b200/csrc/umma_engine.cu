@@ -324,6 +324,12 @@ struct EpiCeGrad {
     __device__ void finish() {}
 };
 
+}  // namespace
+}  // namespace bsa
+#include "ce_grad_ds.cuh"
+namespace bsa {
+namespace {
+
 // ============================================================================ host side
 struct Operand {           // a (hi, lo) pair as stored in global memory
     const float* hi; const float* lo;
@@ -558,6 +564,9 @@ __global__ void ce_combine_kernel(const float* __restrict__ part_m, const float*
 }
 }  // namespace
 
+int g_ce_fused = 1;      // 1: gradient tile + ds in one kernel (ce_grad_ds.cuh) where d allows; 0: separate GEMMs
+void set_ce_fused(int on) { g_ce_fused = on ? 1 : 0; }
+
 bool umma_ce_supported(int B, int d, long long N) { return B >= 1 && d % 4 == 0 && d >= 4 && N >= 1; }
 
 size_t umma_ce_workspace_bytes(int B, int d, long long N) { return carve_ce(nullptr, B, d, N, true).bytes; }
@@ -595,14 +604,43 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
     }
     ProfScope prof(PROF_CE_BWD_UMMA, st, 4.0 * B * (double)N * d);
     const int BNd = d > 128 ? 256 : 128;
-    // ds = G E is split over K (= items); its partial sums stay in `partial` ACROSS chunks and are reduced once
+    // ds = G E: partial sums stay in `partial` ACROSS chunks and are reduced once at the end
     int ds_splits = num_sms() / (cdiv(B, BM) * cdiv(d, BNd));
     if (ds_splits > 64) ds_splits = 64;
     if (ds_splits < 1) ds_splits = 1;
+    const bool fused = g_ce_fused && d > 128 && d <= CGD_ND && (d & 3) == 0;     // gradient tile + ds in one kernel
     int used_splits = 0;
     bool first = true;
+    if (fused) {
+        static bool configured = false;
+        if (!configured) {
+            BSA_CHECK_CUDA(cudaFuncSetAttribute(ce_grad_ds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CGD_SMEM));
+            configured = true;
+        }
+        used_splits = ce_strips(B);
+        if (used_splits > 64) used_splits = 64;
+        BSA_CHECK_CUDA(cudaMemsetAsync(w.partial, 0, (size_t)used_splits * B * d * 4, st));
+    }
     for (long long n0 = 0; n0 < N; n0 += w.chunk) {
         const int cols = (int)((N - n0) < w.chunk ? (N - n0) : w.chunk);
+        if (fused) {
+            CeGradDsParams fp;
+            if ((rc = make_tmap_2d(&fp.s_hi, w.s_hi, B, d, d, BM, false))) return rc;
+            if ((rc = make_tmap_2d(&fp.s_lo, w.s_lo, B, d, d, BM, false))) return rc;
+            if ((rc = make_tmap_2d(&fp.e_hi, w.e_hi + n0 * d, cols, d, d, CGD_BN, false))) return rc;
+            if ((rc = make_tmap_2d(&fp.e_lo, w.e_lo + n0 * d, cols, d, d, CGD_BN, false))) return rc;
+            if ((rc = make_tmap_2d(&fp.em_hi, w.e_hi + n0 * d, cols, d, d, BK, true))) return rc;
+            if ((rc = make_tmap_2d(&fp.em_lo, w.e_lo + n0 * d, cols, d, d, BK, true))) return rc;
+            fp.B = B; fp.cols = cols; fp.d = d;
+            fp.m_tiles = cdiv(B, BM); fp.n_tiles = cdiv(cols, CGD_BN);
+            fp.nstrips = used_splits < fp.n_tiles ? used_splits : fp.n_tiles;
+            fp.k1_blocks = cdiv(d, BK);
+            fp.lse = lse; fp.answers = answers; fp.d_loss = d_loss; fp.n_base = n0;
+            fp.g_hi = w.g_hi; fp.g_lo = w.g_lo; fp.ldg = w.chunk;
+            fp.partial = w.partial;
+            ce_grad_ds_kernel<<<fp.nstrips * fp.m_tiles, CGD_THREADS, CGD_SMEM, st>>>(fp);
+            BSA_LAUNCH_CHECK();
+        } else {
         {   // logits chunk -> G (hi, lo)
             Operand oa{w.s_hi, w.s_lo, B, d, d, false}, ob{w.e_hi + n0 * d, w.e_lo + n0 * d, cols, d, d, false};
             GemmCore g;
@@ -627,6 +665,7 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
             StoreParams ep{ds, d, nullptr, 0, nullptr, nullptr, 1.f, 0, w.partial, nullptr, nullptr, first ? 0 : 1};
             if (BNd == 256) { if ((rc = launch<256, 2, false, true, EpiStore<256>>(g, ep, grid, st))) return rc; }
             else            { if ((rc = launch<128, 3, false, true, EpiStore<128>>(g, ep, grid, st))) return rc; }
+        }
         }
         {   // dE_chunk = G^T s : A = G [B (K), cols (M)] MN-major ; B operand = s [B (K), d (N)] MN-major
             Operand oa{w.g_hi, w.g_lo, B, cols, (long long)w.chunk, true}, ob{w.s_hi, w.s_lo, B, d, d, true};

@@ -64,7 +64,7 @@ def _ce(impl, s, E, ans, dloss=1.0, reuse=False):
     return loss.cpu(), lse.cpu(), ds.cpu(), dE.cpu()
 
 
-@pytest.mark.parametrize("B,d,N", [(6, 32, 211), (128, 64, 1000), (37, 64, 12102), (512, 256, 20000), (130, 128, 5003)])
+@pytest.mark.parametrize("B,d,N", [(6, 32, 211), (128, 64, 1000), (37, 64, 12102), (512, 256, 20000), (130, 128, 5003), (300, 192, 40000), (77, 256, 333)])
 def test_fused_cross_entropy_fwd_bwd(B, d, N, cuda_device):
     g = torch.Generator().manual_seed(B + d + N)
     s = torch.randn(B, d, generator=g) * 1.5
@@ -79,7 +79,7 @@ def test_fused_cross_entropy_fwd_bwd(B, d, N, cuda_device):
     for impl, reuse in ((1, False), (2, False), (2, True)):        # reuse: backward reads the forward's operand splits
         loss, lse, ds, dE = _ce(impl, s.to(cuda_device), E.to(cuda_device), ans.to(cuda_device), 2.5, reuse)
         assert abs(float(loss) - float(ref_loss)) < 2e-6 * abs(float(ref_loss)), impl
-        assert rel_err(lse, ref_lse) < 2e-6, impl
+        assert rel_err(lse, ref_lse) < 4e-6, impl
         assert rel_err(ds, sd.grad) < 1e-5, impl
         assert rel_err(dE, Ed.grad) < 1e-5, impl
 

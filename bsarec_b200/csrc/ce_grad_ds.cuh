@@ -63,7 +63,8 @@ ce_grad_ds_kernel(const __grid_constant__ CeGradDsParams p) {
     uint64_t* s_full = empty_bar + CGD_STAGES;     // S accumulator complete          (MMA -> epilogue)
     uint64_t* g_ready = s_full + 1;                // G pair written back to TMEM      (epilogue -> MMA)
     uint64_t* final_bar = g_ready + 1;             // last ds MMA retired              (MMA -> epilogue)
-    uint32_t* tmem_ptr = (uint32_t*)(final_bar + 1);
+    uint64_t* g_consumed = final_bar + 1;          // G copied out of TMEM to global   (epilogue -> MMA: S may be overwritten)
+    uint32_t* tmem_ptr = (uint32_t*)(g_consumed + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tile = blockIdx.x % p.m_tiles, strip = blockIdx.x / p.m_tiles;
@@ -75,7 +76,7 @@ ce_grad_ds_kernel(const __grid_constant__ CeGradDsParams p) {
     }
     if (warp == 1 && elect_one()) {
         for (int i = 0; i < CGD_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        mbar_init(s_full, 1); mbar_init(g_ready, CGD_EPI_WARPS); mbar_init(final_bar, 1);
+        mbar_init(s_full, 1); mbar_init(g_ready, CGD_EPI_WARPS); mbar_init(final_bar, 1); mbar_init(g_consumed, CGD_EPI_WARPS);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
@@ -122,6 +123,10 @@ ce_grad_ds_kernel(const __grid_constant__ CeGradDsParams p) {
             uint32_t ds_acc = 0;
             for (int n = strip; n < p.n_tiles; n += p.nstrips, ++it) {
                 uint32_t accumulate = 0;
+                if (it > 0) {                               // the epilogue still copies tile it-1's G out of TMEM
+                    mbar_wait(g_consumed, (it - 1) & 1);
+                    tc_fence_after();
+                }
                 for (int kb = 0; kb < p.k1_blocks; ++kb, ++c) {
                     const int s = c % CGD_STAGES;
                     mbar_wait(&full_bar[s], (c / CGD_STAGES) & 1);
@@ -182,7 +187,7 @@ ce_grad_ds_kernel(const __grid_constant__ CeGradDsParams p) {
             mbar_wait(s_full, it & 1);
             tc_fence_after();
 #pragma unroll 1
-            for (int cc = 0; cc < 2; ++cc) {
+            for (int cc = 0; cc < 2; ++cc) {            // S -> (G_hi, G_lo) in place: the only work on the MMA's critical path
                 const int col0 = half * 64 + cc * 32;
                 const int item0 = n * CGD_BN + col0;
                 float v[32];
@@ -202,34 +207,39 @@ ce_grad_ds_kernel(const __grid_constant__ CeGradDsParams p) {
                 }
                 tmem_st32(t_s + lane_base + col0, hi);
                 tmem_st32(t_lo + lane_base + col0, lo);
-                // the same pair goes to global memory (row-contiguous through the staging block) for dE = G^T s
-#pragma unroll
-                for (int pass = 0; pass < 2; ++pass) {
-                    const uint32_t* src = pass ? lo : hi;
-                    float* gdst = pass ? p.g_lo : p.g_hi;
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        stg[lane * 8 + (j ^ (lane & 7))] = make_float4(__uint_as_float(src[4 * j]), __uint_as_float(src[4 * j + 1]),
-                                                                       __uint_as_float(src[4 * j + 2]), __uint_as_float(src[4 * j + 3]));
-                    __syncwarp();
-                    const int col = item0 + c4 * 4;
-#pragma unroll
-                    for (int t = 0; t < 8; ++t) {
-                        const int r = t * 4 + sub;
-                        const float4 x = stg[r * 8 + (c4 ^ (r & 7))];
-                        if (row0 + r < p.B && col < p.cols) {
-                            float* dst = gdst + (row0 + r) * p.ldg + col;
-                            if (col + 3 < p.cols) *reinterpret_cast<float4*>(dst) = x;
-                            else { const float xs[4] = {x.x, x.y, x.z, x.w}; for (int e = 0; e < 4; ++e) if (col + e < p.cols) dst[e] = xs[e]; }
-                        }
-                    }
-                    __syncwarp();
-                }
             }
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(g_ready);
+            // while the ds MMAs run: copy the pair out to global memory (row-contiguous through the staging block) for
+            // the dE = G^T s GEMM
+#pragma unroll 1
+            for (int cc = 0; cc < 4; ++cc) {
+                const int col0 = half * 64 + (cc & 1) * 32;
+                const int item0 = n * CGD_BN + col0;
+                float* gdst = (cc >> 1) ? p.g_lo : p.g_hi;
+                float v[32];
+                tmem_ld32(((cc >> 1) ? t_lo : t_s) + lane_base + col0, v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                __syncwarp();
+                const int col = item0 + c4 * 4;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const int r = t * 4 + sub;
+                    const float4 x = stg[r * 8 + (c4 ^ (r & 7))];
+                    if (row0 + r < p.B && col < p.cols) {
+                        float* dst = gdst + (row0 + r) * p.ldg + col;
+                        if (col + 3 < p.cols) *reinterpret_cast<float4*>(dst) = x;
+                        else { const float xs[4] = {x.x, x.y, x.z, x.w}; for (int e = 0; e < 4; ++e) if (col + e < p.cols) dst[e] = xs[e]; }
+                    }
+                }
+                __syncwarp();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(g_consumed);
         }
         // ---- the strip's ds partial: TMEM -> staging -> running sums in global memory
         mbar_wait(final_bar, 0);

@@ -196,24 +196,24 @@ struct EpiTopk {
     const Params& p; const GemmCore& g; int rit;
     float* lv; int* li;
     float thr = -INFINITY; int thr_i = 0x7fffffff;
-    long long hlo = 0, hhi = 0;
+    long long hlo = 0, hhi = 0, hnext = 0x7fffffffffffffffll;     // cursor into the row's history (sorted global ids)
     __device__ EpiTopk(const Params& p_, const GemmCore& g_, unsigned char* smem, int epi_warp, int lane) : p(p_), g(g_), rit(epi_warp * 32 + lane) {
         lv = reinterpret_cast<float*>(smem);
         li = reinterpret_cast<int*>(smem + KMAX * 128 * 4);
         for (int i = 0; i < p.k; ++i) { lv[i * 128 + rit] = -INFINITY; li[i * 128 + rit] = 0x7fffffff; }
         const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
-        if (row < g.M && p.indptr) { hlo = p.indptr[row]; hhi = p.indptr[row + 1]; }
+        if (row < g.M && p.indptr) { hlo = p.indptr[row]; hhi = p.indptr[row + 1]; if (hlo < hhi) hnext = p.indices[hlo]; }
     }
     __device__ __forceinline__ bool before(float va, int ia, float vb, int ib) const { return va > vb || (va == vb && ia < ib); }
     __device__ void insert(float v, int id) {
-        long long lo = hlo, hi = hhi;                    // history items are scored 0.0 elsewhere: skip them here
+        // history items are scored 0.0 elsewhere: skip them here.  Candidate ids arrive in ascending order within a
+        // strip, so a cursor over the row's sorted history replaces a binary search (one cached load per step).
         const long long gid = p.offset + id;
-        while (lo < hi) {
-            const long long mid = (lo + hi) >> 1;
-            const long long hv = p.indices[mid];
-            if (hv == gid) return;
-            if (hv < gid) lo = mid + 1; else hi = mid;
+        while (hnext < gid) {
+            ++hlo;
+            hnext = hlo < hhi ? p.indices[hlo] : 0x7fffffffffffffffll;
         }
+        if (hnext == gid) return;
         int q = p.k - 1;
         while (q > 0 && before(v, id, lv[(q - 1) * 128 + rit], li[(q - 1) * 128 + rit])) {
             lv[q * 128 + rit] = lv[(q - 1) * 128 + rit];

@@ -213,8 +213,34 @@ def main():
         answers = hb["answers"].to(dev, non_blocking=True)
         return train_step({"ids": ids, "answers": answers}).item()
 
-    def eval_step(b):
-        return model.full_sort_topk(b["ids"], None, b["indptr"], b["indices"], k=TOPK)
+    if world > 1:
+        # item-sharded evaluation: users split across ranks for the encoder, every rank scores ALL users of
+        # the global batch against its row shard of the item table, candidate lists are all-gathered and merged.
+        from bsarec_b200 import functional as Fn
+        from bsarec_b200.parallel import shard_range, sharded_full_sort_topk
+        lo, hi = shard_range(cfg["item_size"], world, rank)
+        all_host = [synth_batches(cfg, B, 1234 + r, NBATCH) for r in range(world)]
+        for i in range(NBATCH):          # global history CSR, rank-major, same on every rank
+            ptrs, idxs, base = [torch.zeros(1, dtype=torch.int64)], [], 0
+            for r in range(world):
+                hb = all_host[r][i]
+                n = int(hb["indptr"][-1])
+                ptrs.append(hb["indptr"][1:] + base)
+                idxs.append(hb["indices"][:n])
+                base += n
+            gi = torch.cat(idxs) if base > 0 else torch.zeros(1, dtype=torch.int64)
+            resident[i]["g_indptr"], resident[i]["g_indices"] = torch.cat(ptrs).to(dev), gi.to(dev)
+            pinned[i]["g_indptr"], pinned[i]["g_indices"] = torch.cat(ptrs).pin_memory(), gi.pin_memory()
+        del all_host
+
+        def eval_step(b):
+            s_loc = model.last_hidden(b["ids"])
+            shard = model.item_embeddings.weight.detach()[lo:hi]
+            return sharded_full_sort_topk(s_loc, shard, lo, b["g_indptr"], b["g_indices"], TOPK,
+                                          lambda s_, e_, ip, ix, k, off: Fn.score_topk(s_, e_, ip, ix, k, off, 0), Fn.topk_merge)
+    else:
+        def eval_step(b):
+            return model.full_sort_topk(b["ids"], None, b["indptr"], b["indices"], k=TOPK)
 
     def barrier():
         if world > 1:
@@ -312,14 +338,14 @@ def main():
         "warmup": args.warmup, "ms_per_step": ms_train / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "per_gpu_batch": B, "global_batch": B * world, "dropout": P_DROP,
-                   "parallelism": f"dp{world}", "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)",
+                   "parallelism": f"dp{world}" + (f" (train: replica + NCCL gradient all-reduce; eval: item table row-sharded {world} ways, top-k merge)" if world > 1 else ""), "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)",
                    "optimizer": ("bsarec_b200.FusedAdam" if args.optimizer == "fused" else "torch.optim.Adam") + " inside the step",
                    "ce_impl": args.ce_impl},
         "model_tflops": value * flops_train_per_seq(cfg) / 1e12,
         "eval": {"metric": "full-ranking eval users/sec", "value": seqs / (ms_eval * 1e-3), "unit": "users/s",
                  "ms_per_step": ms_eval / args.steps,
                  "e2e": {"value": seqs / (ms_eval_e2e * 1e-3), "unit": "users/s",
-                         "h2d_bytes_per_step": h2d + int(host[0]["indices"].numel() + B + 1) * 8, "d2h_bytes_per_step": B * TOPK * 8},
+                         "h2d_bytes_per_step": int(sum(v.numel() * v.element_size() for v in pinned[0].values())), "d2h_bytes_per_step": B * TOPK * 8},
                  "model_tflops": seqs / (ms_eval * 1e-3) * flops_eval_per_user(cfg) / 1e12},
         "e2e": {"value": seqs / (ms_e2e * 1e-3), "unit": "seqs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
         "gpu_launches": int(launches),

@@ -320,12 +320,18 @@ def main():
         return {"bound": "tensor", "achieved": ach, "peak": tensor_peak, "unit": "TFLOP/s", "frac": ach / tensor_peak}
 
     prof = {k: v for k, v in prof.items() if v["launches"] > 0 and v["ms"] > 0}
+    traffic = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f)
+    except Exception:
+        pass
     dom = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else (None, None)
     roofline = None
     if dom[0]:
         roofline = kernel_line(dom[0], dom[1])
         roofline.update({
-            "kernel": dom[0], "traffic": None,
+            "kernel": dom[0], "traffic": traffic.get(dom[0]), "traffic_note": traffic.get("_note") if dom[0] in traffic else None,
             "peak_source": src + ("; tensor peak = bf16 sustained / 2 (TF32 operands) / 3 (split-TF32 passes)" if roofline["bound"] == "tensor" else ""),
             "avg_launch_ms": dom[1]["ms"] / dom[1]["launches"], "launches_per_step": dom[1]["launches"] / args.steps,
             "share_of_step": dom[1]["ms"] / (ms_train if ms_train > 0 else 1.0),

@@ -69,6 +69,9 @@ SIGNATURES = {
     "bsa_embed_ln_dropout_fwd": (_I, [C.POINTER(EmbedDesc)] + [_VP] * 9),
     "bsa_embed_bwd_workspace_bytes": (_SZ, [C.POINTER(EmbedDesc)]),
     "bsa_embed_ln_dropout_bwd": (_I, [C.POINTER(EmbedDesc)] + [_VP] * 12 + [_SZ, _VP]),
+    "bsa_embed_ln_dropout_bwd_rows": (_I, [C.POINTER(EmbedDesc)] + [_VP] * 12 + [_SZ, _VP]),
+    "bsa_scatter_add_workspace_bytes": (_SZ, [_I64]),
+    "bsa_scatter_add_rows": (_I, [_VP, _I64, _I64, _VP, _I, _VP, _VP, _SZ, _VP]),
     "bsa_sort_scatter_plan_bytes": (_SZ, [_I64]),
     "bsa_sort_scatter_plan": (_I, [_VP, _I64, _I64, _VP, _SZ, _VP, _VP, _VP]),
     "bsa_filter_rank": (_I, [_I, _I]),

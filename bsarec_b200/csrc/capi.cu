@@ -133,6 +133,23 @@ size_t bsa_embed_bwd_workspace_bytes(const bsa_embed_desc* c) {
            al(scatter_plan_bytes(M)) + 1024;
 }
 
+// Everything of the embedding backward except the scatter into the item table; dz_rows [B*L,d] is the gradient of the
+// gathered rows (what the scatter-add consumes).
+static int embed_bwd_rows(const bsa_embed_desc* c, const int64_t* ids, const float* item_emb, const float* pos_emb,
+                          const float* ln_w, const float* mean, const float* rstd, const float* d_out, float* dz,
+                          float* d_pos_emb, float* d_ln_w, float* d_ln_b, char* p, cudaStream_t st) {
+    const long long M = (long long)c->B * c->L;
+    const size_t pb = al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float));
+    float* pg = (float*)p; p += pb;
+    float* pbt = (float*)p; p += pb;
+    int nblk = 0, rc;
+    if ((rc = embed_ln_dropout_bwd(d_out, (const long long*)ids, item_emb, pos_emb, ln_w, mean, rstd, dz, pg, pbt, &nblk,
+                                   c->B, c->L, c->d, make_dropout(c->seed, 0, c->p_hidden, c->training), st))) return rc;
+    if ((rc = reduce_partials(pg, nblk, c->d, d_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_partials(pbt, nblk, c->d, d_ln_b, nullptr, 1.f, 0, st))) return rc;
+    return pos_grad(dz, d_pos_emb, c->B, c->L, c->d, 0, st);
+}
+
 int bsa_embed_ln_dropout_bwd(const bsa_embed_desc* c, const int64_t* ids, const float* item_emb, const float* pos_emb,
                              const float* ln_w, const float* mean, const float* rstd, const float* d_out,
                              float* d_item_emb, float* d_pos_emb, float* d_ln_w, float* d_ln_b, void* workspace,
@@ -145,19 +162,38 @@ int bsa_embed_ln_dropout_bwd(const bsa_embed_desc* c, const int64_t* ids, const 
     if (M == 0) return 0;
     char* p = (char*)workspace;
     float* dz = (float*)p; p += al((size_t)M * c->d * sizeof(float));
-    const size_t pb = al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float));
-    float* pg = (float*)p; p += pb;
-    float* pbt = (float*)p; p += pb;
+    int rc;
+    if ((rc = embed_bwd_rows(c, ids, item_emb, pos_emb, ln_w, mean, rstd, d_out, dz, d_pos_emb, d_ln_w, d_ln_b, p, st))) return rc;
+    p += 2 * al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float));
     void* plan = p;
     const size_t plan_bytes = al(scatter_plan_bytes(M));
-    int nblk = 0, rc;
-    if ((rc = embed_ln_dropout_bwd(d_out, (const long long*)ids, item_emb, pos_emb, ln_w, mean, rstd, dz, pg, pbt, &nblk,
-                                   c->B, c->L, c->d, make_dropout(c->seed, 0, c->p_hidden, c->training), st))) return rc;
-    if ((rc = reduce_partials(pg, nblk, c->d, d_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbt, nblk, c->d, d_ln_b, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = pos_grad(dz, d_pos_emb, c->B, c->L, c->d, 0, st))) return rc;
     if ((rc = scatter_plan((const long long*)ids, M, c->item_size, plan, plan_bytes, st))) return rc;
     return scatter_add_rows(plan, M, dz, d_item_emb, c->d, st);
+}
+
+int bsa_embed_ln_dropout_bwd_rows(const bsa_embed_desc* c, const int64_t* ids, const float* item_emb, const float* pos_emb,
+                                  const float* ln_w, const float* mean, const float* rstd, const float* d_out,
+                                  float* dz_rows, float* d_pos_emb, float* d_ln_w, float* d_ln_b, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && ids && item_emb && pos_emb && ln_w && mean && rstd && d_out && dz_rows && d_pos_emb && d_ln_w && d_ln_b && workspace,
+                "bsa_embed_ln_dropout_bwd_rows: null argument");
+    BSA_REQUIRE(workspace_bytes >= bsa_embed_bwd_workspace_bytes(c), "bsa_embed_ln_dropout_bwd_rows: workspace too small");
+    if ((long long)c->B * c->L == 0) return 0;
+    return embed_bwd_rows(c, ids, item_emb, pos_emb, ln_w, mean, rstd, d_out, dz_rows, d_pos_emb, d_ln_w, d_ln_b,
+                          (char*)workspace, (cudaStream_t)stream);
+}
+
+size_t bsa_scatter_add_workspace_bytes(int64_t n_rows) { return al(scatter_plan_bytes(n_rows)) + 256; }
+
+int bsa_scatter_add_rows(const int64_t* ids, int64_t n_rows, int64_t item_size, const float* rows, int d, float* d_item_emb,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(ids && rows && d_item_emb && workspace, "bsa_scatter_add_rows: null argument");
+    BSA_REQUIRE(workspace_bytes >= bsa_scatter_add_workspace_bytes(n_rows), "bsa_scatter_add_rows: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_rows == 0) return 0;
+    int rc;
+    if ((rc = scatter_plan((const long long*)ids, n_rows, item_size, workspace, al(scatter_plan_bytes(n_rows)), st))) return rc;
+    return scatter_add_rows(workspace, n_rows, rows, d_item_emb, d, st);
 }
 
 size_t bsa_sort_scatter_plan_bytes(int64_t n) { return al(scatter_plan_bytes(n)); }

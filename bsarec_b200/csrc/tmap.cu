@@ -23,6 +23,14 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 
 int make_tmap_2d(CUtensorMap* map, const float* base, long long rows, long long cols, long long pitch_elems, int box_rows,
                  bool atom32) {
+    // The driver entry point needs a current context on the calling thread.  A thread that has made no runtime call yet
+    // (PyTorch's autograd worker entering the backward pass with every buffer served from the caching allocator) has
+    // none bound and the encode fails with CUDA_ERROR_INVALID_CONTEXT; cudaFree(0) binds the primary context.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        BSA_CHECK_CUDA(cudaFree(nullptr));
+        ctx_bound = true;
+    }
     auto enc = get_encode();
     BSA_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
     BSA_REQUIRE(((uintptr_t)base & 15) == 0 && (pitch_elems * 4) % 16 == 0,

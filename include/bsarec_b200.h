@@ -74,6 +74,21 @@ int bsa_embed_ln_dropout_bwd(const bsa_embed_desc* desc, const int64_t* ids, con
                              const float* d_out, float* d_item_emb, float* d_pos_emb, float* d_ln_w,
                              float* d_ln_b, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same backward in two halves, for data-parallel training: the dense cross-entropy part of the
+ * item-table gradient is all-reduced while the encoder backward runs, the sparse gather part is exchanged as rows.
+ *   bsa_embed_ln_dropout_bwd_rows: everything above except the scatter; dz_rows [B*L,d] (out) is the gradient of the
+ *     gathered rows E[ids] (the operand of ATen's embedding_dense_backward, _abstract_model.py:17).
+ *   bsa_scatter_add_rows: d_item_emb[ids[i]] += rows[i] for ids[i] != 0, i < n_rows, through the sorted atomic-free
+ *     segmented sum (ties summed in row order -> every rank that feeds the same (ids, rows) gets the same bits).
+ * Workspace of the first: bsa_embed_bwd_workspace_bytes. */
+int bsa_embed_ln_dropout_bwd_rows(const bsa_embed_desc* desc, const int64_t* ids, const float* item_emb,
+                                  const float* pos_emb, const float* ln_w, const float* mean, const float* rstd,
+                                  const float* d_out, float* dz_rows, float* d_pos_emb, float* d_ln_w, float* d_ln_b,
+                                  void* workspace, size_t workspace_bytes, void* stream);
+size_t bsa_scatter_add_workspace_bytes(int64_t n_rows);
+int bsa_scatter_add_rows(const int64_t* ids, int64_t n_rows, int64_t item_size, const float* rows, int d,
+                         float* d_item_emb, void* workspace, size_t workspace_bytes, void* stream);
+
 /* helper: stable (id, row) sort plan used by the scatter-add; exposed for tests.
  * sorted_ids/sorted_rows are int32 [B*L]. */
 size_t bsa_sort_scatter_plan_bytes(int64_t n);

@@ -163,6 +163,9 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ce-impl", type=int, default=0)
+    ap.add_argument("--dp", default="overlap", choices=["overlap", "bucket"],
+                    help="N>1 gradient exchange: overlap = GradExchange inside backward (dense CE part all-reduced under the "
+                         "encoder backward, sparse rows all-gathered); bucket = one flat all-reduce after backward")
     ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
                     help="fused: bsarec_b200.FusedAdam (one kernel pass per tensor); torch: torch.optim.Adam (foreach)")
     args = ap.parse_args()
@@ -192,6 +195,8 @@ def main():
     torch.manual_seed(42)
     model = BSARecModel(make_args(cfg, P_DROP, P_DROP, batch_size=B)).to(dev)
     model.ce_impl = args.ce_impl
+    if world > 1 and args.dp == "overlap":
+        model.enable_data_parallel()
     opt_cls = FusedAdam if args.optimizer == "fused" else torch.optim.Adam
     optim = opt_cls(model.parameters(), lr=1e-3, betas=(0.9, 0.999), weight_decay=0.0)
     params = list(model.parameters())
@@ -203,7 +208,7 @@ def main():
         loss = model.calculate_loss(b["ids"], b["answers"], None, None, None)
         optim.zero_grad()
         loss.backward()
-        if world > 1:
+        if world > 1 and args.dp == "bucket":
             allreduce_gradients(params)
         optim.step()
         return loss
@@ -344,7 +349,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": ms_train / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "per_gpu_batch": B, "global_batch": B * world, "dropout": P_DROP,
-                   "parallelism": f"dp{world}" + (f" (train: replica + NCCL gradient all-reduce; eval: item table row-sharded {world} ways, top-k merge)" if world > 1 else ""), "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)",
+                   "parallelism": f"dp{world}" + (f" (train: replica + NCCL gradient exchange [{args.dp}]; eval: item table row-sharded {world} ways, top-k merge)" if world > 1 else ""), "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)",
                    "optimizer": ("bsarec_b200.FusedAdam" if args.optimizer == "fused" else "torch.optim.Adam") + " inside the step",
                    "ce_impl": args.ce_impl},
         "model_tflops": value * flops_train_per_seq(cfg) / 1e12,

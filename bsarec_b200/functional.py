@@ -148,10 +148,13 @@ def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor
 
 
 def encoder_backward(h: Hyper, params: Dict[str, torch.Tensor], state: EncoderState, d_out: torch.Tensor,
-                     grads: Dict[str, torch.Tensor]) -> None:
+                     grads: Dict[str, torch.Tensor], rows_only: bool = False) -> Optional[torch.Tensor]:
     """d_out: gradient wrt the last block's output — [B,d] (position L-1) if the forward ran with ``last_only``,
     else [B,L,d].  Writes every encoder/embedding gradient into
-    ``grads`` (item table: accumulated on top of what is already there)."""
+    ``grads`` (item table: accumulated on top of what is already there).
+
+    ``rows_only`` (data-parallel training): the item-table scatter is left to the caller; returns ``dz`` [B*L,d], the
+    gradient of the gathered rows ``E[ids]``, and does not touch ``grads["item_embeddings.weight"]``."""
     lib = _cabi.load()
     B, L, d, dev = state.B, state.L, h.hidden_size, d_out.device
     with torch.cuda.device(dev):
@@ -181,11 +184,30 @@ def encoder_backward(h: Hyper, params: Dict[str, torch.Tensor], state: EncoderSt
                        seed=state.seed)
         eb = lib.bsa_embed_bwd_workspace_bytes(C.byref(ed))
         ws = state.workspace if ws_bytes >= eb else torch.empty(eb, dtype=torch.uint8, device=dev)
-        check(lib.bsa_embed_ln_dropout_bwd(C.byref(ed), _ptr(state.ids), _ptr(E), _ptr(params["position_embeddings.weight"]),
-                                           _ptr(params["LayerNorm.weight"]), _ptr(state.mean), _ptr(state.rstd), _ptr(g),
-                                           _ptr(grads["item_embeddings.weight"]), _ptr(grads["position_embeddings.weight"]),
-                                           _ptr(grads["LayerNorm.weight"]), _ptr(grads["LayerNorm.bias"]), _ptr(ws),
-                                           ws.numel(), st), "bsa_embed_ln_dropout_bwd")
+        common = (_ptr(state.ids), _ptr(E), _ptr(params["position_embeddings.weight"]), _ptr(params["LayerNorm.weight"]),
+                  _ptr(state.mean), _ptr(state.rstd), _ptr(g))
+        tail = (_ptr(grads["position_embeddings.weight"]), _ptr(grads["LayerNorm.weight"]), _ptr(grads["LayerNorm.bias"]),
+                _ptr(ws), ws.numel(), st)
+        if rows_only:
+            dz = torch.empty(B * L, d, dtype=torch.float32, device=dev)
+            check(lib.bsa_embed_ln_dropout_bwd_rows(C.byref(ed), *common, _ptr(dz), *tail), "bsa_embed_ln_dropout_bwd_rows")
+            return dz
+        check(lib.bsa_embed_ln_dropout_bwd(C.byref(ed), *common, _ptr(grads["item_embeddings.weight"]), *tail),
+              "bsa_embed_ln_dropout_bwd")
+    return None
+
+
+def scatter_add_rows(ids: torch.Tensor, rows: torch.Tensor, dE: torch.Tensor) -> None:
+    """dE[ids[i]] += rows[i] for ids[i] != 0 (sorted, atomic-free; ties summed in row order).  ids int64 [M] (any shape
+    with M elements), rows fp32 [M,d]."""
+    lib = _cabi.load()
+    M, d = rows.shape
+    assert ids.numel() == M and dE.shape[1] == d
+    with torch.cuda.device(rows.device):
+        wsb = lib.bsa_scatter_add_workspace_bytes(M)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=rows.device)
+        check(lib.bsa_scatter_add_rows(_ptr(ids.contiguous()), M, dE.shape[0], _ptr(rows.contiguous()), d, _ptr(dE), _ptr(ws), wsb,
+                                       _stream()), "bsa_scatter_add_rows")
 
 
 def gather_last(x: torch.Tensor) -> torch.Tensor:
@@ -269,17 +291,35 @@ def topk_merge(cand_val: torch.Tensor, cand_idx: torch.Tensor):
     return val, idx
 
 
+def alloc_grads(params: Dict[str, torch.Tensor], big: str = "item_embeddings.weight"):
+    """Gradient buffers: the item table's on its own, every other tensor a view into ONE flat fp32 buffer (so a
+    data-parallel run all-reduces the 41 small gradients with a single collective and no packing copies).
+    -> ({name: tensor}, flat)"""
+    small = [(n, t) for n, t in params.items() if n != big]
+    flat = torch.empty(sum(t.numel() for _, t in small), dtype=torch.float32, device=params[big].device)
+    grads, off = {big: torch.empty_like(params[big])}, 0
+    for n, t in small:
+        grads[n] = flat[off:off + t.numel()].view_as(t)
+        off += t.numel()
+    return grads, flat
+
+
 class FusedLoss(torch.autograd.Function):
-    """calculate_loss as one autograd node: encoder fwd -> last position -> fused CE; backward in reverse."""
+    """calculate_loss as one autograd node: encoder fwd -> last position -> fused CE; backward in reverse.
+
+    ``exchange`` (``parallel.GradExchange`` or None): data-parallel gradient averaging woven into the backward pass —
+    the dense cross-entropy part of the item-table gradient is all-reduced WHILE the encoder backward runs, the 41 small
+    gradients go in one flat all-reduce, and the sparse gather part travels as (ids, rows) and is scatter-added on
+    every rank."""
 
     @staticmethod
     def forward(ctx, hyper: Hyper, names: Sequence[str], ids, answers, training: bool, seed: int, ce_impl: int,
-                *tensors):
+                exchange, *tensors):
         params = dict(zip(names, tensors))
         xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
         s = xs[-1]
         loss, lse, ce_ws = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
-        ctx.hyper, ctx.names, ctx.state, ctx.ce_impl = hyper, names, state, ce_impl
+        ctx.hyper, ctx.names, ctx.state, ctx.ce_impl, ctx.exchange = hyper, names, state, ce_impl, exchange
         ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
         ctx.save_for_backward(*tensors)
         return loss
@@ -287,15 +327,23 @@ class FusedLoss(torch.autograd.Function):
     @staticmethod
     def backward(ctx, d_loss):
         tensors = ctx.saved_tensors
-        names, hyper, state = ctx.names, ctx.hyper, ctx.state
+        names, hyper, state, ex = ctx.names, ctx.hyper, ctx.state, ctx.exchange
         params = dict(zip(names, tensors))
-        grads = {n: torch.empty_like(t) for n, t in params.items()}
+        grads, flat = alloc_grads(params)
         if state.L < params["position_embeddings.weight"].shape[0]:
             grads["position_embeddings.weight"].zero_()      # rows >= L are never touched by the kernels
         E = params["item_embeddings.weight"]
-        ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, grads["item_embeddings.weight"], ctx.ce_impl, ctx.ce_ws)
+        gE = grads["item_embeddings.weight"]
+        if ex is not None:
+            d_loss = d_loss * ex.scale                       # sum over ranks == mean over the global batch
+            ex.begin(state.ids)
+        ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, gE, ctx.ce_impl, ctx.ce_ws)
         ctx.ce_ws = None
+        if ex is not None:
+            ex.start_dense(gE)                               # overlaps everything below
         d_out = ds if state.last_row else scatter_last(ds, state.L)
-        encoder_backward(hyper, params, state, d_out, grads)
+        dz = encoder_backward(hyper, params, state, d_out, grads, rows_only=ex is not None)
+        if ex is not None:
+            ex.finish(flat, dz, gE, scatter_add_rows)
         ctx.state = None
-        return (None, None, None, None, None, None, None) + tuple(grads[n] for n in names)
+        return (None,) * 8 + tuple(grads[n] for n in names)

@@ -100,6 +100,7 @@ class BSARecModel(nn.Module):
         self.ce_impl = 0          # 0 auto | 1 fp32 FFMA | 2 tcgen05 3xTF32   (bsa_ce_desc.impl)
         self.topk_impl = 0
         self._fixed_seed: Optional[int] = None
+        self._exchange = None     # parallel.GradExchange when data-parallel training is on
 
     # ------------------------------------------------------------------ reference-compatible surface
     def init_weights(self, module):
@@ -129,7 +130,19 @@ class BSARecModel(nn.Module):
         names = [n for n, _ in self.named_parameters()]
         tensors = [p for _, p in self.named_parameters()]
         return Fn.FusedLoss.apply(self._hyper(), names, input_ids, answers, self.training, self._next_seed(),
-                                  self.ce_impl, *tensors)
+                                  self.ce_impl, self._exchange, *tensors)
+
+    # ------------------------------------------------------------------ data-parallel training (additional API)
+    def enable_data_parallel(self, group=None):
+        """One process per GPU, full replica, equal local batches: after this call ``loss.backward()`` leaves the
+        GLOBAL-batch-mean gradient in every ``p.grad`` (NCCL exchange overlapped with the backward pass), so the
+        reference's loop — ``calculate_loss -> zero_grad -> backward -> step`` (trainers.py:103-107) — runs unchanged."""
+        from .parallel import GradExchange
+        self._exchange = GradExchange(group)
+        return self
+
+    def disable_data_parallel(self):
+        self._exchange = None
 
     # ------------------------------------------------------------------ fused evaluation (additional API)
     @torch.no_grad()

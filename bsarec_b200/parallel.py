@@ -51,6 +51,52 @@ def allreduce_gradients(params: Iterable[torch.nn.Parameter], group=None, bucket
     return calls
 
 
+class GradExchange:
+    """Data-parallel gradient averaging woven into ``functional.FusedLoss.backward`` (one instance per model).
+
+    sum_r (dE_ce[r] + scatter(ids[r], dz[r]))  ==  all_reduce(dE_ce) + scatter(all_gather(ids), all_gather(dz)):
+      * ``start_dense``: the dense cross-entropy part of the item-table gradient ([N,d], 1.02 GB at C3) is produced first
+        in the backward pass; its all-reduce is issued at once on the communicator's stream and runs under the whole
+        encoder backward;
+      * ``finish``: the 41 small gradients are one flat buffer -> one all-reduce; the sparse gather part is exchanged as
+        rows (ids [B*L] + dz [B*L,d] per rank, 105 MB at C3) and scatter-added on every rank in the same (rank, row)
+        order, so all replicas hold bit-identical gradients.
+    ``scale`` = 1/world is folded into d_loss (no averaging pass over the gradients).  Ranks must hold equally sized local
+    batches (the mean of local means is then the global mean of ``CrossEntropyLoss``, bsarec.py:35)."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.scale = 1.0 / self.world
+        self._w_dense = self._w_ids = self._ids_all = None
+        self.collectives = 0
+
+    def _issue(self, fn, *a):
+        self.collectives += 1
+        return fn(*a, group=self.group, async_op=True)
+
+    def begin(self, ids: torch.Tensor):
+        """ids int64 [B,L] of this rank's batch: gathered early, it is not on anybody's critical path."""
+        flat = ids.reshape(-1).contiguous()
+        self._ids_all = torch.empty(self.world * flat.numel(), dtype=flat.dtype, device=flat.device)
+        self._w_ids = self._issue(dist.all_gather_into_tensor, self._ids_all, flat)
+
+    def start_dense(self, g_item: torch.Tensor):
+        self._w_dense = self._issue(dist.all_reduce, g_item.view(-1), dist.ReduceOp.SUM)
+
+    def finish(self, small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable):
+        w_small = self._issue(dist.all_reduce, small_flat, dist.ReduceOp.SUM) if small_flat.numel() else None
+        dz_all = torch.empty(self.world * dz.shape[0], dz.shape[1], dtype=dz.dtype, device=dz.device)
+        w_rows = self._issue(dist.all_gather_into_tensor, dz_all, dz.contiguous())
+        self._w_ids.wait()
+        w_rows.wait()
+        self._w_dense.wait()
+        scatter_fn(self._ids_all, dz_all, g_item)
+        if w_small is not None:
+            w_small.wait()
+        self._w_dense = self._w_ids = self._ids_all = None
+
+
 def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shard_offset: int,
                            hist_indptr_all: Optional[torch.Tensor], hist_indices_all: Optional[torch.Tensor], k: int,
                            score_fn: Callable, merge_fn: Callable, group=None) -> torch.Tensor:

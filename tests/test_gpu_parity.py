@@ -219,3 +219,33 @@ def test_fused_attention_kernel_vs_oracle_and_unfused(cfgkw, B, p_attn, last_row
     for k in g64:
         if not k.endswith("key.bias"):
             assert rel_err(grads[2][1][k], grads[1][1][k]) < TOL, k
+
+
+def test_data_parallel_exchange_path_single_rank_bit_identical(cuda_device):
+    """enable_data_parallel() on a 1-rank NCCL group: the backward goes through bsa_embed_ln_dropout_bwd_rows, the
+    collectives and bsa_scatter_add_rows instead of the fused embedding backward — same bits in all 42 gradients."""
+    import os
+    import torch.distributed as dist
+    cfgkw = dict(item_size=157, hidden_size=64, max_seq_length=20, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.6)
+    cfg = oracle_cfg(cfgkw, 0.5, 0.5)
+    P = perturbed_params(cfg, 3)
+    ids, answers = synth_batch(5, 19, 20, 157)
+    own_group = not dist.is_initialized()
+    if own_group:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=cuda_device)
+    try:
+        runs = []
+        for dp in (False, True):
+            model = build_model(cfgkw, P, cuda_device, 0.5, 0.5).train()
+            model.set_dropout_seed(99)
+            if dp:
+                model.enable_data_parallel()
+            model.calculate_loss(ids.to(cuda_device), answers.to(cuda_device), None, None, None).backward()
+            runs.append(grads_of(model))
+        for k in runs[0]:
+            assert torch.equal(runs[0][k], runs[1][k]), k
+    finally:
+        if own_group:
+            dist.destroy_process_group()

@@ -11,7 +11,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from bsarec_b200.parallel import allreduce_gradients, shard_range, sharded_full_sort_topk
+from bsarec_b200.parallel import GradExchange, allreduce_gradients, shard_range, sharded_full_sort_topk
 
 import oracle
 
@@ -96,6 +96,48 @@ def _noop_worker(rank, world):
 
 def test_allreduce_is_a_noop_on_one_rank():
     _spawn(_noop_worker, 1)
+
+
+def _index_add_scatter(ids, rows, dE):
+    """torch stand-in for bsa_scatter_add_rows: dE[ids[i]] += rows[i], id 0 (padding_idx) skipped, row order."""
+    keep = ids != 0
+    dE.index_add_(0, ids[keep], rows[keep])
+
+
+def _exchange_worker(rank, world, out_dir):
+    """GradExchange == all-reduce of the full per-rank gradients: sum_r (dense_r + scatter(ids_r, dz_r)), and the flat
+    small-gradient buffer summed; replicas end bit-identical."""
+    N, d, M = 53, 8, 40
+    per_rank = []
+    for r in range(world):
+        g = torch.Generator().manual_seed(100 + r)
+        ids = torch.randint(0, N, (5, 8), generator=g)            # zeros included: padding rows are skipped
+        per_rank.append(dict(ids=ids, dense=torch.randn(N, d, generator=g), dz=torch.randn(M, d, generator=g),
+                             small=torch.randn(77, generator=g)))
+    me = {k: v.clone() for k, v in per_rank[rank].items()}
+    ex = GradExchange()
+    assert ex.world == world and ex.scale == 1.0 / world
+    ex.begin(me["ids"])
+    ex.start_dense(me["dense"])
+    ex.finish(me["small"], me["dz"], me["dense"], _index_add_scatter)
+    want = torch.zeros(N, d, dtype=torch.float64)
+    small = torch.zeros(77, dtype=torch.float64)
+    for r in range(world):
+        want += per_rank[r]["dense"].double()
+        _index_add_scatter(per_rank[r]["ids"].reshape(-1), per_rank[r]["dz"].double(), want)
+        small += per_rank[r]["small"].double()
+    assert (me["dense"].double() - want).abs().max() < 1e-5
+    assert (me["small"].double() - small).abs().max() < 1e-5
+    assert ex.collectives == 4                                    # ids, dense, small, rows
+    torch.save([me["dense"], me["small"]], os.path.join(out_dir, f"x{rank}.pt"))
+
+
+def test_overlapped_gradient_exchange_equals_full_allreduce(tmp_path):
+    _spawn(_exchange_worker, 2, str(tmp_path))
+    a = torch.load(os.path.join(tmp_path, "x0.pt"))
+    b = torch.load(os.path.join(tmp_path, "x1.pt"))
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
 
 
 # ------------------------------------------------------------------------------------------- evaluation

@@ -6,9 +6,13 @@ namespace bsa {
 
 namespace {
 
-template <int BN, bool AK, bool BKM>
+// BM = 128: (2x4) x (CGx4) register tile per thread.  BM = 32: 2 x (CGx4) — the small-problem variant: a [512, 256]
+// output (the last-row path's [B, d] linears) is 8 CTAs at 128 x 128 but 64 at 32 x 64, and those launches are bound by
+// how many SMs they reach, not by FMA:LDS ratio.
+template <int BM, int BN, bool AK, bool BKM>
 __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
-    constexpr int BM = 128, BK = 16, LDSA = BM + 4, LDSB = BN + 4;
+    constexpr int BK = 16, LDSA = BM + 4, LDSB = BN + 4;
+    constexpr int TM = BM / 16;            // rows per thread
     constexpr int CG = BN / 64;            // column groups of 4 per thread
     constexpr int NBL = BN / 16;           // B elements loaded per thread per k-tile
     __shared__ __align__(16) float As[2][BK][LDSA];
@@ -29,20 +33,21 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
         kend = min(p.K, kbeg + kc);
     }
 
-    float acc[8][CG * 4];
+    float acc[TM][CG * 4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < CG * 4; ++j) acc[i][j] = 0.f;
+    auto row_of = [&](int i) { return BM == 128 ? (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4)) : ty * TM + i; };
 
-    float ra[8], rb[NBL];
+    float ra[TM], rb[NBL];
 
     auto load_tiles = [&](int k0) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < TM; ++i) {
             int m, k;
             if (AK) { k = tid & 15; m = (tid >> 4) + 16 * i; }
-            else    { m = tid & 127; k = (tid >> 7) + 2 * i; }
+            else    { m = tid % BM; k = tid / BM + (256 / BM) * i; }
             const int gm = m0 + m, gk = k0 + k;
             float v = 0.f;
             if (gm < p.M && gk < kend)
@@ -63,10 +68,10 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
     };
     auto store_tiles = [&](int buf) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < TM; ++i) {
             int m, k;
             if (AK) { k = tid & 15; m = (tid >> 4) + 16 * i; }
-            else    { m = tid & 127; k = (tid >> 7) + 2 * i; }
+            else    { m = tid % BM; k = tid / BM + (256 / BM) * i; }
             As[buf][k][m] = ra[i];
         }
 #pragma unroll
@@ -89,18 +94,23 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
         if (t + 1 < ntiles) load_tiles(kbeg + (t + 1) * BK);
 #pragma unroll
         for (int k = 0; k < BK; ++k) {
-            float a[8], b[CG * 4];
-            const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
-            const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
-            a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
-            a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+            float a[TM], b[CG * 4];
+            if constexpr (BM == 128) {
+                const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+                const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
+                a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
+                a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+            } else {
+#pragma unroll
+                for (int i = 0; i < TM; ++i) a[i] = As[buf][k][ty * TM + i];
+            }
 #pragma unroll
             for (int g = 0; g < CG; ++g) {
                 const float4 bv = *reinterpret_cast<const float4*>(&Bs[buf][k][g * 64 + tx * 4]);
                 b[g * 4 + 0] = bv.x; b[g * 4 + 1] = bv.y; b[g * 4 + 2] = bv.z; b[g * 4 + 3] = bv.w;
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < TM; ++i)
 #pragma unroll
                 for (int j = 0; j < CG * 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
         }
@@ -112,8 +122,8 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
     if (p.splitk > 1) {
         float* __restrict__ part = p.partial + (long long)split * p.M * p.N;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        for (int i = 0; i < TM; ++i) {
+            const int gm = m0 + row_of(i);
             if (gm >= p.M) continue;
 #pragma unroll
             for (int j = 0; j < CG * 4; ++j) {
@@ -127,8 +137,8 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
     float* __restrict__ auxo = p.aux_out ? p.aux_out + zo * p.sCo + zi * p.sCi : nullptr;
     const float* __restrict__ auxi = p.aux_in ? p.aux_in + zo * p.sCo + zi * p.sCi : nullptr;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+    for (int i = 0; i < TM; ++i) {
+        const int gm = m0 + row_of(i);
         if (gm >= p.M) continue;
 #pragma unroll
         for (int j = 0; j < CG * 4; ++j) {
@@ -158,12 +168,12 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, float* __re
     C[off] = v;
 }
 
-template <int BN>
+template <int BM, int BN>
 int dispatch(const GemmP& p, dim3 grid, cudaStream_t st) {
-    if (p.a_kmajor && p.b_kmajor) gemm_kernel<BN, true, true><<<grid, 256, 0, st>>>(p);
-    else if (p.a_kmajor && !p.b_kmajor) gemm_kernel<BN, true, false><<<grid, 256, 0, st>>>(p);
-    else if (!p.a_kmajor && p.b_kmajor) gemm_kernel<BN, false, true><<<grid, 256, 0, st>>>(p);
-    else gemm_kernel<BN, false, false><<<grid, 256, 0, st>>>(p);
+    if (p.a_kmajor && p.b_kmajor) gemm_kernel<BM, BN, true, true><<<grid, 256, 0, st>>>(p);
+    else if (p.a_kmajor && !p.b_kmajor) gemm_kernel<BM, BN, true, false><<<grid, 256, 0, st>>>(p);
+    else if (!p.a_kmajor && p.b_kmajor) gemm_kernel<BM, BN, false, true><<<grid, 256, 0, st>>>(p);
+    else gemm_kernel<BM, BN, false, false><<<grid, 256, 0, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }
@@ -185,13 +195,16 @@ int launch_gemm(const GemmP& p, cudaStream_t st) {
     BSA_REQUIRE(p.splitk >= 1 && (p.splitk == 1 || (p.batch == 1 && p.partial && !p.bias && p.act == ACT_NONE)),
                 "launch_gemm: invalid split-K configuration");
     BSA_REQUIRE(p.inner >= 1 && p.batch % p.inner == 0, "launch_gemm: batch %% inner != 0");
-    const int BN = p.N <= 64 ? 64 : 128;
-    dim3 grid(cdiv(p.M, 128), cdiv(p.N, BN), p.splitk > 1 ? p.splitk : p.batch);
+    int BN = p.N <= 64 ? 64 : 128;
+    const int nz = p.splitk > 1 ? p.splitk : p.batch;
+    const bool small = (long long)cdiv(p.M, 128) * cdiv(p.N, BN) * nz < 96;      // would leave a third of the SMs idle
+    if (small) BN = 64;
+    dim3 grid(cdiv(p.M, small ? 32 : 128), cdiv(p.N, BN), nz);
     BSA_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "launch_gemm: grid too large (M=%d batch=%d)", p.M, p.batch);
     int rc;
     {
         ProfScope prof(PROF_GEMM_SIMT, st, 2.0 * p.M * p.N * (double)p.K * p.batch);
-        rc = BN == 64 ? dispatch<64>(p, grid, st) : dispatch<128>(p, grid, st);
+        rc = small ? dispatch<32, 64>(p, grid, st) : BN == 64 ? dispatch<128, 64>(p, grid, st) : dispatch<128, 128>(p, grid, st);
     }
     if (rc) return rc;
     if (p.splitk > 1) {

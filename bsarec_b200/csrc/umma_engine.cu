@@ -1,5 +1,6 @@
 // tcgen05 3xTF32 engine: epilogues, launchers and the cross-entropy / scoring / linear entry points built on
 // umma_gemm.cuh.
+#include <cstdlib>
 #include "umma_engine.cuh"
 #include "umma_gemm.cuh"
 #include "ce_topk.cuh"
@@ -509,7 +510,8 @@ int ce_bwd_chunk(int B, long long N) {
     // one wave of 128 x 256 logits tiles per chunk, and small enough that G, G^T (hi, lo) stay in L2
     const int m_tiles = cdiv(B, BM);
     long long per_wave = (long long)(num_sms() / m_tiles > 0 ? num_sms() / m_tiles : 1) * 256;
-    long long cap = (80ll << 20) / (8ll * (B > 0 ? B : 1));          // G (hi, lo): 8 B per element <= 80 MiB (L2 is 126 MB)
+    static long long g_mib = [] { const char* e = getenv("BSA_CE_G_MIB"); long long v = e ? atoll(e) : 0; return v > 0 ? v : 640ll; }();
+    long long cap = (g_mib << 20) / (8ll * (B > 0 ? B : 1));         // G (hi, lo): 8 B per element
     long long c = per_wave;
     while (c * 2 <= cap) c *= 2;
     if (c > cap && cap >= 256) c = cap / 256 * 256;

@@ -242,7 +242,7 @@ def main():
             s_loc = model.last_hidden(b["ids"])
             shard = model.item_embeddings.weight.detach()[lo:hi]
             return sharded_full_sort_topk(s_loc, shard, lo, b["g_indptr"], b["g_indices"], TOPK,
-                                          lambda s_, e_, ip, ix, k, off: Fn.score_topk(s_, e_, ip, ix, k, off, 0), Fn.topk_merge)
+                                          lambda s_, e_, ip, ix, k, off: Fn.score_topk(s_, e_, ip, ix, k, off, 0, cache=model._topk_cache), Fn.topk_merge)
     else:
         def eval_step(b):
             return model.full_sort_topk(b["ids"], None, b["indptr"], b["indices"], k=TOPK)

@@ -52,7 +52,7 @@ class CeDesc(C.Structure):
 
 class TopkDesc(C.Structure):
     _fields_ = [("B", C.c_int), ("d", C.c_int), ("k", C.c_int), ("shard_rows", C.c_int64),
-                ("shard_offset", C.c_int64), ("impl", C.c_int)]
+                ("shard_offset", C.c_int64), ("impl", C.c_int), ("reuse_split", C.c_int)]
 
 
 # name -> (restype, argtypes); mirrors include/bsarec_b200.h one to one

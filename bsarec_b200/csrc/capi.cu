@@ -310,7 +310,7 @@ int bsa_score_topk(const bsa_topk_desc* c, const float* seq_out, const float* it
     if (topk_impl(c) == 2) {
         BSA_REQUIRE(umma_topk_supported(c->B, c->d, c->k, c->shard_rows), "bsa_score_topk: tcgen05 path does not support this shape");
         return umma_score_topk(c->B, c->d, c->k, c->shard_rows, c->shard_offset, seq_out, item_shard, (const long long*)hist_indptr,
-                               (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, (cudaStream_t)stream);
+                               (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, c->reuse_split != 0, (cudaStream_t)stream);
     }
     return score_topk_simt(c->B, c->d, c->k, c->shard_rows, c->shard_offset, seq_out, item_shard, (const long long*)hist_indptr,
                            (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, (cudaStream_t)stream);

@@ -190,6 +190,8 @@ struct EpiTopk {
     struct Params {
         const long long* indptr; const long long* indices; long long offset; int k;
         float* cand_val; long long* cand_idx;      // [nstrips][B][k]
+        const float* seed_val;                     // optional [B][seed_ld]: seed_val[row*seed_ld + k-1] is a proven lower
+        int seed_ld;                               //   bound of the row's final k-th score (a k-th best over a sample)
     };
     static constexpr int KMAX = 32;
     static constexpr int WARPS = 4;
@@ -204,6 +206,8 @@ struct EpiTopk {
         for (int i = 0; i < p.k; ++i) { lv[i * 128 + rit] = -INFINITY; li[i * 128 + rit] = 0x7fffffff; }
         const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
         if (row < g.M && p.indptr) { hlo = p.indptr[row]; hhi = p.indptr[row + 1]; if (hlo < hhi) hnext = p.indices[hlo]; }
+        // seeded threshold: (thr, INT_MAX) admits every score >= thr, so the sample's own k-th item re-enters
+        if (row < g.M && p.seed_val) thr = p.seed_val[row * p.seed_ld + p.k - 1];
     }
     __device__ __forceinline__ bool before(float va, int ia, float vb, int ib) const { return va > vb || (va == vb && ia < ib); }
     __device__ void insert(float v, int id) {
@@ -222,7 +226,8 @@ struct EpiTopk {
             --q;
         }
         lv[q * 128 + rit] = v; li[q * 128 + rit] = id;
-        thr = lv[(p.k - 1) * 128 + rit]; thr_i = li[(p.k - 1) * 128 + rit];
+        const float l20 = lv[(p.k - 1) * 128 + rit];
+        if (!(l20 < thr)) { thr = l20; thr_i = li[(p.k - 1) * 128 + rit]; }      // a seeded threshold stays until the list beats it
     }
     __device__ void tile(uint32_t acc, const TileCoord& tc) {
         const int n0 = tc.n * BN;
@@ -705,6 +710,8 @@ __global__ void hist_list_kernel(const long long* __restrict__ indptr, const lon
     for (; n < k; ++n) { val[(long long)row * k + n] = -INFINITY; idx[(long long)row * k + n] = -1; }
 }
 
+constexpr long long TOPK_SEED_ROWS = 32768;      // sample scored ahead of the main pass to seed the per-user thresholds
+
 int topk_strips(int B, int k) {
     int s = ce_strips(B);
     const int cap = 1024 / k - 1;
@@ -719,12 +726,13 @@ bool umma_topk_supported(int B, int d, int k, long long rows) {
 
 size_t umma_topk_workspace_bytes(int B, int d, int k, long long rows) {
     const int ns = topk_strips(B, k) + 1;
-    return 2 * al((size_t)B * d * 4) + 2 * al((size_t)rows * d * 4) + al((size_t)ns * B * k * 4) + al((size_t)ns * B * k * 8) + 4096;
+    return 2 * al((size_t)B * d * 4) + 2 * al((size_t)rows * d * 4) + al((size_t)ns * B * k * 4) + al((size_t)ns * B * k * 8) +
+           al((size_t)B * k * 4) + al((size_t)B * k * 8) + 4096;
 }
 
 int umma_score_topk(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,
                     const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
-                    void* ws, size_t ws_bytes, cudaStream_t st) {
+                    void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st) {
     BSA_REQUIRE(ws_bytes >= umma_topk_workspace_bytes(B, d, k, rows), "bsa_score_topk: workspace too small");
     char* p = (char*)ws;
     auto take = [&](size_t bytes) { char* r = p; p += al(bytes); return r; };
@@ -735,12 +743,31 @@ int umma_score_topk(int B, int d, int k, long long rows, long long offset, const
     long long* cand_idx = (long long*)take((size_t)(nstrips + 1) * B * k * 8);
     int rc;
     if ((rc = do_split(s, s_hi, s_lo, (long long)B * d, st))) return rc;
-    if ((rc = do_split(E, e_hi, e_lo, rows * d, st))) return rc;
+    if (!reuse_split && (rc = do_split(E, e_hi, e_lo, rows * d, st))) return rc;
     Operand oa{s_hi, s_lo, B, d, d, false}, ob{e_hi, e_lo, rows, d, d, false};
     GemmCore g;
     if ((rc = make_core(g, B, (int)rows, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;
     if (nstrips > g.n_tiles) nstrips = g.n_tiles;
-    EpiTopk<CE_BN>::Params ep{hist_indptr, hist_indices, offset, k, cand_val, cand_idx};
+    float* seed_val = (float*)take((size_t)B * k * 4);
+    long long* seed_idx = (long long*)take((size_t)B * k * 8);
+    // Threshold seeding.  Every strip starts its per-user list cold, and a cold list is where the epilogue's time goes
+    // (a warp takes the serial insertion path whenever ANY of its 32 users has a candidate).  So the first TOPK_SEED_ROWS
+    // rows are scored once ahead of time; each user's k-th best there (history excluded, as in the main pass) is a lower
+    // bound of the final k-th score, and the main pass skips everything below it from its first tile on.  The sample
+    // rows are scored again by the main pass, so the result does not depend on the seed.
+    const float* seed = nullptr;
+    if (rows >= 8 * TOPK_SEED_ROWS) {
+        GemmCore gs;
+        Operand obs{e_hi, e_lo, TOPK_SEED_ROWS, d, d, false};
+        if ((rc = make_core(gs, B, (int)TOPK_SEED_ROWS, d, oa, obs, CE_BN, SCHED_STRIP, 1))) return rc;
+        int ss = nstrips < gs.n_tiles ? nstrips : gs.n_tiles;
+        EpiTopk<CE_BN>::Params sp{hist_indptr, hist_indices, offset, k, cand_val, cand_idx, nullptr, 0};
+        ProfScope prof(PROF_TOPK_UMMA, st, 0.0);     // time counted, no work credited: the sample is scored again below
+        if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiTopk<CE_BN>>(gs, sp, ss * gs.m_tiles, st))) return rc;
+        if ((rc = topk_merge(cand_val, cand_idx, ss, B, k, seed_val, seed_idx, st))) return rc;
+        seed = seed_val;
+    }
+    EpiTopk<CE_BN>::Params ep{hist_indptr, hist_indices, offset, k, cand_val, cand_idx, seed, k};
     {
         ProfScope prof(PROF_TOPK_UMMA, st, 2.0 * B * (double)rows * d);
         if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiTopk<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;

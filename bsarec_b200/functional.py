@@ -261,14 +261,29 @@ def scatter_last(ds: torch.Tensor, L: int) -> torch.Tensor:
 
 
 def score_topk(s: torch.Tensor, item_shard: torch.Tensor, hist_indptr: Optional[torch.Tensor],
-               hist_indices: Optional[torch.Tensor], k: int = 20, shard_offset: int = 0, impl: int = 0):
-    """-> (top_val fp32 [B,k], top_idx int64 [B,k]); replaces trainers.py:62-68,130-149 for one item shard."""
+               hist_indices: Optional[torch.Tensor], k: int = 20, shard_offset: int = 0, impl: int = 0,
+               cache: Optional[dict] = None):
+    """-> (top_val fp32 [B,k], top_idx int64 [B,k]); replaces trainers.py:62-68,130-149 for one item shard.
+
+    ``cache``: a dict owned by the caller (the model).  While ``item_shard`` is the same storage at the same version
+    counter (no optimizer step, no load_state_dict since) and the batch shape repeats, the workspace — and with it the
+    split-TF32 copy of the shard, 2 N d floats — is kept and ``reuse_split`` is set: an evaluation sweep splits the
+    table once, not once per batch."""
     lib = _cabi.load()
     B, d = s.shape
-    td = TopkDesc(B=B, d=d, k=k, shard_rows=item_shard.shape[0], shard_offset=shard_offset, impl=impl)
+    td = TopkDesc(B=B, d=d, k=k, shard_rows=item_shard.shape[0], shard_offset=shard_offset, impl=impl, reuse_split=0)
     with torch.cuda.device(s.device):
         wsb = lib.bsa_score_topk_workspace_bytes(C.byref(td))
-        ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+        key = (item_shard.data_ptr(), item_shard._version, tuple(item_shard.shape), B, k, impl, s.device.index)
+        if cache is not None and cache.get("key") == key:
+            ws = cache["ws"]
+            td.reuse_split = 1
+        else:
+            if cache is not None:
+                cache.clear()                   # drop the old 2 N d buffer before taking a new one
+            ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+            if cache is not None:
+                cache["key"], cache["ws"] = key, ws
         val = torch.empty(B, k, dtype=torch.float32, device=s.device)
         idx = torch.empty(B, k, dtype=torch.int64, device=s.device)
         if hist_indptr is not None:

@@ -101,6 +101,7 @@ class BSARecModel(nn.Module):
         self.topk_impl = 0
         self._fixed_seed: Optional[int] = None
         self._exchange = None     # parallel.GradExchange when data-parallel training is on
+        self._topk_cache: dict = {}   # scoring workspace kept while the item table is unchanged (functional.score_topk)
 
     # ------------------------------------------------------------------ reference-compatible surface
     def init_weights(self, module):
@@ -158,7 +159,8 @@ class BSARecModel(nn.Module):
         ``Trainer.iteration`` (trainers.py:126-149) kept on the device.  ``hist_indptr`` [B+1] /
         ``hist_indices`` are a CSR over the batch rows (int64, CUDA).  Returns int64 [B,k]."""
         s = self.last_hidden(input_ids)
-        _, idx = Fn.score_topk(s, self.item_embeddings.weight.detach(), hist_indptr, hist_indices, k, 0, self.topk_impl)
+        _, idx = Fn.score_topk(s, self.item_embeddings.weight.detach(), hist_indptr, hist_indices, k, 0, self.topk_impl,
+                               cache=self._topk_cache)
         return idx
 
     # ------------------------------------------------------------------ helpers

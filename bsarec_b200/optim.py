@@ -48,4 +48,5 @@ class FusedAdam(torch.optim.Optimizer):
                                             p.numel(), float(group["lr"]), float(b1), float(b2), float(group["eps"]),
                                             float(group["weight_decay"]), st["step"],
                                             torch.cuda.current_stream().cuda_stream), "bsa_adam_step")
+                torch.autograd.graph.increment_version(p)     # written through a raw pointer: tell autograd / caches
         return loss

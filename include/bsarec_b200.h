@@ -208,6 +208,9 @@ typedef struct {
     int64_t shard_rows;        /* rows of this item-table shard */
     int64_t shard_offset;      /* global id of the shard's row 0 */
     int impl;                  /* 0 = auto, 1 = fp32 FFMA, 2 = tcgen05 3xTF32 */
+    int reuse_split;           /* 1: `workspace` was last used by bsa_score_topk with the SAME item_shard contents and
+                                  shard_rows/d/B/k: its split-TF32 copy of the shard is reused (evaluation sweeps score
+                                  millions of users against a table that does not change, trainers.py:118-158) */
 } bsa_topk_desc;
 
 size_t bsa_score_topk_workspace_bytes(const bsa_topk_desc* desc);

@@ -106,7 +106,8 @@ def _ref_topk(s, E, indptr, indices, k, offset=0):
     return np.array(out_v), np.array(out_i)
 
 
-@pytest.mark.parametrize("B,d,N,k", [(5, 32, 97, 20), (64, 64, 3417, 20), (130, 64, 12102, 10), (256, 128, 30000, 20)])
+@pytest.mark.parametrize("B,d,N,k", [(5, 32, 97, 20), (64, 64, 3417, 20), (130, 64, 12102, 10), (256, 128, 30000, 20),
+                                     (37, 32, 300000, 20)])       # last: large enough for the seeded-threshold pre-pass
 @pytest.mark.parametrize("negative", [False, True])
 def test_fused_score_topk(B, d, N, k, negative, cuda_device):
     g = torch.Generator().manual_seed(B * 3 + N + k)
@@ -172,3 +173,25 @@ def test_fused_adam_matches_torch_adam(wd, cuda_device):
     for r, q in zip(ref, got):
         assert rel_err(q.detach().cpu(), r.detach().cpu()) < 1e-6
     assert o_got.state[got[0]]["step"] == 5
+
+
+def test_score_topk_split_cache_follows_item_table_version(cuda_device):
+    """The scoring workspace (split-TF32 copy of the item table) is reused across eval batches while the table's
+    version counter stands still, and rebuilt after any in-place update — including FusedAdam's raw-pointer update."""
+    from bsarec_b200 import functional as Fn, FusedAdam
+    g = torch.Generator().manual_seed(8)
+    B, d, N, k = 70, 64, 5003, 20
+    s = torch.randn(B, d, generator=g).to(cuda_device)
+    E = torch.nn.Parameter((torch.randn(N, d, generator=g) * 0.2).to(cuda_device))
+    cache = {}
+    v0, i0 = Fn.score_topk(s, E.detach(), None, None, k, 0, 2, cache=cache)
+    ws = cache["ws"]
+    v1, i1 = Fn.score_topk(s, E.detach(), None, None, k, 0, 2, cache=cache)          # reuse_split = 1
+    assert cache["ws"] is ws and torch.equal(v0, v1) and torch.equal(i0, i1)
+    E.grad = torch.randn(N, d, generator=g).to(cuda_device)
+    FusedAdam([E], lr=0.05).step()                                                   # table changes, version bumps
+    v2, i2 = Fn.score_topk(s, E.detach(), None, None, k, 0, 2, cache=cache)
+    fresh_v, fresh_i = Fn.score_topk(s, E.detach(), None, None, k, 0, 2)
+    assert cache["ws"] is not ws
+    assert torch.equal(v2, fresh_v) and torch.equal(i2, fresh_i)
+    assert not torch.equal(i2, i0)

@@ -11,6 +11,7 @@
 // left padding) attends to ALL L keys.  Key tiles whose every pair is masked for rows that do have a permitted key
 // contribute exp(-10000 - max) == 0 exactly and are skipped.
 #include "attn.cuh"
+#include <cstdlib>
 
 namespace bsa {
 namespace {
@@ -493,6 +494,9 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
 
 }  // namespace
 
+// 1: the forward goes to the tcgen05 kernel where its shape allows (BSA_ATTN_UMMA=0 keeps the mma.sync kernel)
+int g_attn_fwd_umma = [] { const char* e = getenv("BSA_ATTN_UMMA"); return e ? atoi(e) : 1; }();
+
 bool attn_fused_supported(int L, int d, int H) {
     if (H <= 0 || d % H != 0 || d % 4 != 0 || L < 1) return false;
     const int dh = d / H;
@@ -503,6 +507,7 @@ int attn_fwd(const float* q, const float* k, const float* v, const long long* id
              int L, int d, Dropout dr, cudaStream_t st) {
     BSA_REQUIRE(attn_fused_supported(L, d, H), "attn_fwd: unsupported head size %d", H ? d / H : 0);
     if (B == 0) return 0;
+    if (g_attn_fwd_umma && attn_umma_supported(L, d, H)) return attn_fwd_umma(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
     if (d / H == 64) return launch_fwd<64>(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
     return launch_fwd<32>(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
 }

@@ -15,6 +15,12 @@ bool attn_fused_supported(int L, int d, int H);
 int attn_fwd(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
              int L, int d, Dropout dr, cudaStream_t st);
 
+// The same forward on tcgen05 / TMEM (attn_umma.cu): head size 64 and L <= 208, i.e. the whole key axis in one accumulator.
+extern int g_attn_fwd_umma;      // 1 (default): use it where the shape allows; 0: always the mma.sync kernel
+bool attn_umma_supported(int L, int d, int H);
+int attn_fwd_umma(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
+                  int L, int d, Dropout dr, cudaStream_t st);
+
 // dq, dk, dv [B*L, d] are overwritten.  delta: [B, H, L] scratch (row sums of dctx * ctx).
 int attn_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
              const float* dctx, float* dq, float* dk, float* dv, float* delta, int B, int H, int L, int d, Dropout dr,

@@ -1,0 +1,297 @@
+// Causal multi-head attention forward on the 5th-generation tensor cores (tcgen05 + TMEM), for sequences whose whole
+// key axis fits one accumulator: L <= 208 (C1: L = 50, C2/C3: L = 200).  Same semantics as attn.cu (the mma.sync
+// kernel, which stays for longer sequences and for the backward pass): model/_modules.py:108-133 with the literal
+// additive -10000 mask of _abstract_model.py:53-69, dropout on the probabilities, error-compensated TF32.
+//
+// One CTA = (sequence b, head h, 128 query rows).
+//   TMA   : Q tile, K rows, V rows of the head arrive as raw fp32 (128-byte swizzle; V in the 32-byte-atom variant
+//           that MN-major tf32 operands need); every thread then splits them IN PLACE into the (hi, lo) pair of the
+//           3xTF32 scheme — elementwise, so the swizzled layout is untouched — and publishes with fence.proxy.async.
+//   MMA 1 : S[128, NK] = Q K^T          (both operands from shared memory, accumulator in TMEM columns [0, NK))
+//   warps 4-7 (thread = query row): two sweeps over the row in TMEM — max, then exp / sum / dropout — and the
+//           probabilities go BACK into TMEM as a split pair (hi over S, lo beside it).
+//   MMA 2 : O[128, dh] = P V            (A operand read from TMEM, B = V rows as MN-major operand)
+//   epilogue: O / rowsum -> ctx, (rowmax, log rowsum) -> lse for the backward pass.
+// TMEM columns: [0,224) S then P_hi, [224,448) P_lo, [448,512) O.
+#include "attn.cuh"
+#include "umma.cuh"
+
+namespace bsa {
+
+using namespace umma;
+
+namespace {
+
+constexpr int AU_DH = 64;                  // head size this kernel is built for
+constexpr int AU_NK_MAX = 208;             // keys per sequence (UMMA N, multiple of 16)
+constexpr int AU_SCOLS = 224;              // TMEM columns reserved for S / P_hi (7 chunks of 32)
+constexpr int AU_THREADS = 256;
+constexpr int AU_Q_BYTES = 128 * AU_DH * 4;                 // 32 KiB: 2 k-blocks x [128 rows x 128 B]
+constexpr int AU_K_BYTES = AU_NK_MAX * AU_DH * 4;           // 52 KiB: 2 k-blocks x [NK rows x 128 B]
+constexpr int AU_V_BYTES = 7 * 2 * 4096;                    // 56 KiB: 7 k-blocks x 2 column chunks x [32 rows x 128 B]
+constexpr int AU_OFF_QHI = 0;
+constexpr int AU_OFF_QLO = AU_OFF_QHI + AU_Q_BYTES;
+constexpr int AU_OFF_KHI = AU_OFF_QLO + AU_Q_BYTES;         // after MMA 1: V_lo (56 KiB, runs on into K_lo)
+constexpr int AU_OFF_KLO = AU_OFF_KHI + AU_K_BYTES;
+constexpr int AU_OFF_V = AU_OFF_KLO + AU_K_BYTES;
+constexpr int AU_OFF_BAR = AU_OFF_V + AU_V_BYTES;
+constexpr int AU_SMEM = 1024 + AU_OFF_BAR + 128 + 256;      // alignment slack + barriers + valid[]
+static_assert(AU_SMEM <= 232448, "attention tile does not fit shared memory");
+static_assert(AU_V_BYTES <= 2 * AU_K_BYTES, "V_lo must fit the retired K region");
+
+struct AttnUmmaParams {
+    CUtensorMap q, k, v;          // [B*L, d] fp32: box 32 x 128, box 32 x NK/2, box 32 x 32 (atom32)
+    const long long* ids;
+    float* ctx; float* lse;
+    int H, L, d, NK;
+    float scale;
+    Dropout dr;
+};
+
+__device__ __forceinline__ void split_tf32_dev(float x, float& hi, float& lo) {
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+    hi = __uint_as_float(h);
+    lo = x - hi;
+}
+
+// raw fp32 region -> hi in place, lo at +lo_off (same swizzled positions)
+__device__ __forceinline__ void split_region(unsigned char* base, int bytes, int lo_off, int tid, int nthreads) {
+    for (int o = tid * 16; o < bytes; o += nthreads * 16) {
+        const float4 x = *reinterpret_cast<const float4*>(base + o);
+        float4 h, l;
+        split_tf32_dev(x.x, h.x, l.x); split_tf32_dev(x.y, h.y, l.y);
+        split_tf32_dev(x.z, h.z, l.z); split_tf32_dev(x.w, h.w, l.w);
+        *reinterpret_cast<float4*>(base + o) = h;
+        *reinterpret_cast<float4*>(base + o + lo_off) = l;
+    }
+}
+
+__global__ void __launch_bounds__(AU_THREADS, 1)
+attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
+    extern __shared__ __align__(1024) unsigned char au_smem_raw[];
+    unsigned char* smem = (unsigned char*)(((uintptr_t)au_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* bar_qk = (uint64_t*)(smem + AU_OFF_BAR);       // Q and K tiles landed              (TMA -> all)
+    uint64_t* bar_v = bar_qk + 1;                            // V rows landed                     (TMA -> warps 0-3)
+    uint64_t* s_full = bar_qk + 2;                           // S complete in TMEM                (MMA -> all)
+    uint64_t* p_ready = bar_qk + 3;                          // P pair written back to TMEM       (warps 4-7 -> MMA)
+    uint64_t* v_ready = bar_qk + 4;                          // V split published                 (warps 0-3 -> MMA)
+    uint64_t* o_full = bar_qk + 5;                           // O complete in TMEM                (MMA -> warps 4-7)
+    uint32_t* tmem_ptr = (uint32_t*)(bar_qk + 6);
+    unsigned char* valid = smem + AU_OFF_BAR + 128;          // [AU_SCOLS + 32]: 1 = key j is an item, 0 = padding / j >= L
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
+    const int qt = blockIdx.y;
+    const long long seq_base = (long long)b * p.L;
+    const int NK = p.NK, nkb = (NK + 31) / 32;
+    const int col0 = h * AU_DH;
+    const int k_kb_bytes = NK * 128;                         // one 32-float k-block of the K operand
+
+    if (warp == 0 && elect_one()) { prefetch_tmap(&p.q); prefetch_tmap(&p.k); prefetch_tmap(&p.v); }
+    if (warp == 1 && elect_one()) {
+        mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(s_full, 1);
+        mbar_init(p_ready, 4); mbar_init(v_ready, 4); mbar_init(o_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AU_THREADS)
+        valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t t_s = tmem_base, t_lo = tmem_base + AU_SCOLS, t_o = tmem_base + 2 * AU_SCOLS;
+
+    if (warp == 0 && elect_one()) {
+        mbar_expect_tx(bar_qk, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+            tma_load_2d(smem + AU_OFF_QHI + kb * 16384, &p.q, bar_qk, col0 + kb * 32, (int)(seq_base + qt * 128));
+            tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes, &p.k, bar_qk, col0 + kb * 32, (int)seq_base);
+            tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes + (NK / 2) * 128, &p.k, bar_qk, col0 + kb * 32, (int)seq_base + NK / 2);
+        }
+        mbar_expect_tx(bar_v, (uint32_t)(nkb * 8192));
+        for (int kb = 0; kb < nkb; ++kb) {
+            tma_load_2d(smem + AU_OFF_V + kb * 8192, &p.v, bar_v, col0, (int)seq_base + kb * 32);
+            tma_load_2d(smem + AU_OFF_V + kb * 8192 + 4096, &p.v, bar_v, col0 + 32, (int)seq_base + kb * 32);
+        }
+    }
+    // ---- Q, K: raw fp32 -> (hi, lo), all 8 warps
+    mbar_wait(bar_qk, 0);
+    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AU_THREADS);
+    fence_proxy_async_smem();
+    __syncthreads();
+
+    if (warp < 4) {
+        if (warp == 1 && elect_one()) {
+            // ================================================================= MMA 1: S = Q K^T
+            const uint32_t idesc = idesc_tf32(128, NK, false, false);
+            const uint32_t qh = smem_u32(smem + AU_OFF_QHI), ql = smem_u32(smem + AU_OFF_QLO);
+            const uint32_t kh = smem_u32(smem + AU_OFF_KHI), kl = smem_u32(smem + AU_OFF_KLO);
+            uint32_t acc = 0;
+#pragma unroll
+            for (int kb = 0; kb < 2; ++kb) {
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t dah = smem_desc(qh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                    const uint64_t dal = smem_desc(ql + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                    const uint64_t dbh = smem_desc(kh + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                    const uint64_t dbl = smem_desc(kl + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                    mma_tf32(t_s, dal, dbh, idesc, acc);
+                    mma_tf32(t_s, dah, dbl, idesc, 1u);
+                    mma_tf32(t_s, dah, dbh, idesc, 1u);
+                    acc = 1u;
+                }
+            }
+            mma_commit(s_full);
+        }
+        __syncwarp();
+        // ---- V: raw fp32 -> hi in place, lo into the K region once MMA 1 has retired
+        mbar_wait(bar_v, 0);
+        mbar_wait(s_full, 0);
+        split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, 128);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(v_ready);
+        if (warp == 1 && elect_one()) {
+            // ================================================================= MMA 2: O = P V
+            mbar_wait(v_ready, 0);
+            mbar_wait(p_ready, 0);
+            tc_fence_after();
+            const uint32_t idesc = idesc_tf32(128, AU_DH, false, true);
+            const uint32_t vh = smem_u32(smem + AU_OFF_V), vl = smem_u32(smem + AU_OFF_KHI);
+            uint32_t acc = 0;
+            for (int kstep = 0; kstep < NK / 8; ++kstep) {
+                const int kb = kstep >> 2, ks = kstep & 3;
+                const uint64_t dbh = smem_desc(vh + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+                const uint64_t dbl = smem_desc(vl + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+                const uint32_t col = (uint32_t)(kstep * 8);
+                mma_tf32_ts(t_o, t_lo + col, dbh, idesc, acc);
+                mma_tf32_ts(t_o, t_s + col, dbl, idesc, 1u);
+                mma_tf32_ts(t_o, t_s + col, dbh, idesc, 1u);
+                acc = 1u;
+            }
+            mma_commit(o_full);
+        }
+    } else {
+        // ===================================================================== softmax + epilogue (thread = query row)
+        const int quarter = warp - 4;
+        const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
+        const int i = qt * 128 + quarter * 32 + lane;              // position in the sequence
+        const bool row_ok = i < p.L;
+        const int nch = (NK + 31) / 32;
+        const unsigned long long pbase = ((unsigned long long)bh * p.L + (unsigned long long)(row_ok ? i : 0)) * p.L;
+        mbar_wait(s_full, 0);
+        tc_fence_after();
+        float m = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < nch; ++c) {                            // sweep 1: row max of the masked, scaled scores
+            float v[32];
+            tmem_ld32(t_s + lane_base + c * 32, v);
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj) {
+                const int j = c * 32 + jj;
+                const float s = v[jj] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
+                if (j < p.L) m = fmaxf(m, s);
+            }
+        }
+        float l = 0.f;
+        const bool fast_rng = (pbase & 3ull) == 0ull;
+#pragma unroll 1
+        for (int c = 0; c < nch; ++c) {                            // sweep 2: exp, sum, dropout, split, back into TMEM
+            float v[32];
+            tmem_ld32(t_s + lane_base + c * 32, v);
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int g4 = 0; g4 < 8; ++g4) {
+                float mult[4];
+                const int j0 = c * 32 + g4 * 4;
+                if (fast_rng) dropout_mult4(p.dr, pbase + j0, mult);
+                else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(p.dr, pbase + j0 + e);
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int j = j0 + e;
+                    const float s = v[g4 * 4 + e] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
+                    float pr = 0.f;
+                    if (row_ok && j < p.L) {
+                        pr = expf(s - m);
+                        l += pr;
+                        pr *= mult[e];
+                    }
+                    float h, lw;
+                    split_tf32_dev(pr, h, lw);
+                    hi[g4 * 4 + e] = __float_as_uint(h); lo[g4 * 4 + e] = __float_as_uint(lw);
+                }
+            }
+            tmem_st32(t_s + lane_base + c * 32, hi);
+            tmem_st32(t_lo + lane_base + c * 32, lo);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_ready);
+
+        mbar_wait(o_full, 0);
+        tc_fence_after();
+        const float inv = row_ok ? 1.0f / l : 0.f;
+        float* dst = p.ctx + (seq_base + (row_ok ? i : 0)) * p.d + col0;
+#pragma unroll 1
+        for (int c = 0; c < AU_DH / 32; ++c) {
+            float v[32];
+            tmem_ld32(t_o + lane_base + c * 32, v);
+            if (row_ok) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    *reinterpret_cast<float4*>(dst + c * 32 + e * 4) =
+                        make_float4(v[4 * e] * inv, v[4 * e + 1] * inv, v[4 * e + 2] * inv, v[4 * e + 3] * inv);
+            }
+        }
+        if (row_ok) *reinterpret_cast<float2*>(p.lse + 2 * ((long long)bh * p.L + i)) = make_float2(m, logf(l));
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace
+
+bool attn_umma_supported(int L, int d, int H) {
+    if (H <= 0 || d % H != 0 || d / H != AU_DH || d % 4 != 0) return false;
+    return L >= 1 && L <= AU_NK_MAX;
+}
+
+int attn_fwd_umma(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
+                  int L, int d, Dropout dr, cudaStream_t st) {
+    BSA_REQUIRE(attn_umma_supported(L, d, H), "attn_fwd_umma: unsupported shape (L=%d d=%d H=%d)", L, d, H);
+    if (B == 0) return 0;
+    static bool configured = false;
+    if (!configured) {
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
+        configured = true;
+    }
+    AttnUmmaParams p;
+    const int NK = (L + 15) / 16 * 16;
+    const long long rows = (long long)B * L;
+    int rc;
+    if ((rc = make_tmap_2d(&p.q, q, rows, d, d, 128, false))) return rc;
+    if ((rc = make_tmap_2d(&p.k, k, rows, d, d, NK / 2, false))) return rc;
+    if ((rc = make_tmap_2d(&p.v, v, rows, d, d, 32, true))) return rc;
+    p.ids = ids; p.ctx = ctx; p.lse = lse; p.H = H; p.L = L; p.d = d; p.NK = NK;
+    p.scale = 1.0f / sqrtf((float)AU_DH);
+    p.dr = dr;
+    const dim3 grid(B * H, (L + 127) / 128);
+    ProfScope prof(PROF_ATTN_FWD, st, 4.0 * B * H * (double)L * L * AU_DH);
+    attn_fwd_umma_kernel<<<grid, AU_THREADS, AU_SMEM, st>>>(p);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace bsa

@@ -169,8 +169,11 @@ int split_act(const Lin& ln, const float* x, float* hi, float* lo, long long n, 
 }  // namespace
 
 int g_attn_impl = 2;        // 1 = unfused GEMM + softmax kernels, 2 = fused attention kernel where the head size allows
-int attn_impl() { return g_attn_impl; }
-void set_attn_impl(int impl) { g_attn_impl = impl == 1 ? 1 : 2; }
+int attn_impl() { return g_attn_impl == 2 && !g_attn_fwd_umma ? 3 : g_attn_impl; }
+void set_attn_impl(int impl) {        // 1 unfused | 2 fused, forward on tcgen05 where the shape allows | 3 fused, mma.sync only
+    g_attn_impl = impl == 1 ? 1 : 2;
+    g_attn_fwd_umma = impl == 3 ? 0 : 1;
+}
 int g_linear_impl = 2;      // 1 = fp32 FFMA, 2 = tcgen05 3xTF32 (bsa_set_linear_impl)
 int linear_impl() { return g_linear_impl; }
 void set_linear_impl(int impl) { g_linear_impl = impl == 1 ? 1 : 2; }

@@ -138,7 +138,9 @@ void bsa_set_linear_impl(int impl);
 int bsa_get_linear_impl(void);
 /* how the attention branch runs: 2 = fused kernel (scores, mask, softmax, dropout and P V in one pass, backward by
  * recomputation from the saved row log-sum-exp; head sizes 32 and 64), 1 = unfused GEMM + softmax kernels that
- * materialise the [B,H,L,L] probabilities (every head size; the on-GPU cross-check).  Process-wide; must not change
+ * materialise the [B,H,L,L] probabilities (every head size; the on-GPU cross-check).  With 2 the forward runs on
+ * tcgen05/TMEM (attn_umma.cu: S = Q K^T into TMEM, softmax in place, P fed back as the TMEM A operand of P V) when the head
+ * size is 64 and L <= 208, else on the mma.sync kernel; 3 = fused, mma.sync kernels only.  Process-wide; must not change
  * between a bsa_block_fwd and its bsa_block_bwd. */
 void bsa_set_attn_impl(int impl);
 int bsa_get_attn_impl(void);

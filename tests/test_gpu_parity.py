@@ -200,7 +200,7 @@ def test_fused_attention_kernel_vs_oracle_and_unfused(cfgkw, B, p_attn, last_row
     ids[0, :] = torch.randint(1, N, (L,))              # one full-length row: every key block is live
     seed = 0x51DE5EED
     grads = {}
-    for impl in (2, 1):
+    for impl in (2, 3, 1):          # tcgen05 forward (where dh == 64) | mma.sync fused | unfused GEMM + softmax
         lib.bsa_set_attn_impl(impl)
         try:
             model = build_model(cfgkw, P, cuda_device, 0.25, p_attn).train()
@@ -216,9 +216,11 @@ def test_fused_attention_kernel_vs_oracle_and_unfused(cfgkw, B, p_attn, last_row
     assert abs(grads[2][0] - float(l64)) < TOL * abs(float(l64))
     check_grads(grads[2][1], g64, g32)
     assert abs(grads[2][0] - grads[1][0]) < 2e-5 * abs(grads[1][0])
+    assert abs(grads[2][0] - grads[3][0]) < 2e-5 * abs(grads[3][0])
     for k in g64:
         if not k.endswith("key.bias"):
             assert rel_err(grads[2][1][k], grads[1][1][k]) < TOL, k
+            assert rel_err(grads[2][1][k], grads[3][1][k]) < TOL, k
 
 
 def test_data_parallel_exchange_path_single_rank_bit_identical(cuda_device):
@@ -249,3 +251,29 @@ def test_data_parallel_exchange_path_single_rank_bit_identical(cuda_device):
     finally:
         if own_group:
             dist.destroy_process_group()
+
+
+def test_tcgen05_attention_forward_matches_mma_sync_kernel(cuda_device):
+    """The two fused forward kernels on the same inputs (C3's head shape: L = 200, dh = 64, dropout on): every layer
+    output within 1e-5 of each other, and the library reports more launches of neither path silently falling back."""
+    from bsarec_b200 import _cabi
+    lib = _cabi.load()
+    cfgkw = dict(item_size=400, hidden_size=128, max_seq_length=200, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.5)
+    cfg = oracle_cfg(cfgkw, 0.2, 0.4)
+    P = perturbed_params(cfg, 13)
+    ids, _ = synth_batch(23, 6, 200, 400)
+    ids[0, :] = torch.randint(1, 400, (200,))
+    outs = {}
+    for impl in (2, 3):
+        lib.bsa_set_attn_impl(impl)
+        try:
+            model = build_model(cfgkw, P, cuda_device, 0.2, 0.4).train()
+            model.set_dropout_seed(4242)
+            outs[impl] = [t.cpu() for t in model.predict(ids.to(cuda_device), None, all_sequence_output=True)]
+        finally:
+            lib.bsa_set_attn_impl(2)
+    for a, b in zip(outs[2], outs[3]):
+        assert rel_err(a, b) < 1e-5
+    ref = oracle.encode({k: v.double() for k, v in P.items()}, ids, cfg, train=True, plan=oracle.DropoutPlan(4242), use_fft=False)
+    for a, b in zip(outs[2], ref):
+        assert rel_err(a, b) < TOL

@@ -8,8 +8,8 @@
 //           that MN-major tf32 operands need); every thread then splits them IN PLACE into the (hi, lo) pair of the
 //           3xTF32 scheme — elementwise, so the swizzled layout is untouched — and publishes with fence.proxy.async.
 //   MMA 1 : S[128, NK] = Q K^T          (both operands from shared memory, accumulator in TMEM columns [0, NK))
-//   warps 4-7 (thread = query row): two sweeps over the row in TMEM — max, then exp / sum / dropout — and the
-//           probabilities go BACK into TMEM as a split pair (hi over S, lo beside it).
+//   all 8 warps (two per TMEM lane quarter, alternate 32-column chunks): two sweeps over the row in TMEM — max, then
+//           exp / sum / dropout — and the probabilities go BACK into TMEM as a split pair (hi over S, lo beside it).
 //   MMA 2 : O[128, dh] = P V            (A operand read from TMEM, B = V rows as MN-major operand)
 //   epilogue: O / rowsum -> ctx, (rowmax, log rowsum) -> lse for the backward pass.
 // TMEM columns: [0,224) S then P_hi, [224,448) P_lo, [448,512) O.
@@ -74,11 +74,11 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     uint64_t* bar_qk = (uint64_t*)(smem + AU_OFF_BAR);       // Q and K tiles landed              (TMA -> all)
     uint64_t* bar_v = bar_qk + 1;                            // V rows landed                     (TMA -> warps 0-3)
     uint64_t* s_full = bar_qk + 2;                           // S complete in TMEM                (MMA -> all)
-    uint64_t* p_ready = bar_qk + 3;                          // P pair written back to TMEM       (warps 4-7 -> MMA)
-    uint64_t* v_ready = bar_qk + 4;                          // V split published                 (warps 0-3 -> MMA)
     uint64_t* o_full = bar_qk + 5;                           // O complete in TMEM                (MMA -> warps 4-7)
     uint32_t* tmem_ptr = (uint32_t*)(bar_qk + 6);
     unsigned char* valid = smem + AU_OFF_BAR + 128;          // [AU_SCOLS + 32]: 1 = key j is an item, 0 = padding / j >= L
+    int* s_first = (int*)(bar_qk + 7);                       // first position holding an item (L if none)
+    float* xch = (float*)(smem + AU_OFF_QHI);                // [2][2][128]: row max / row sum halves (Q is dead after MMA 1)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
@@ -91,13 +91,16 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     if (warp == 0 && elect_one()) { prefetch_tmap(&p.q); prefetch_tmap(&p.k); prefetch_tmap(&p.v); }
     if (warp == 1 && elect_one()) {
         mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(s_full, 1);
-        mbar_init(p_ready, 4); mbar_init(v_ready, 4); mbar_init(o_full, 1);
+        mbar_init(o_full, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    if (threadIdx.x == 0) *s_first = p.L;
     for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AU_THREADS)
         valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
     tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);   // L <= 208 < blockDim
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
@@ -124,86 +127,76 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     fence_proxy_async_smem();
     __syncthreads();
 
-    if (warp < 4) {
-        if (warp == 1 && elect_one()) {
-            // ================================================================= MMA 1: S = Q K^T
-            const uint32_t idesc = idesc_tf32(128, NK, false, false);
-            const uint32_t qh = smem_u32(smem + AU_OFF_QHI), ql = smem_u32(smem + AU_OFF_QLO);
-            const uint32_t kh = smem_u32(smem + AU_OFF_KHI), kl = smem_u32(smem + AU_OFF_KLO);
-            uint32_t acc = 0;
+    if (warp == 1 && elect_one()) {
+        // ===================================================================== MMA 1: S = Q K^T
+        const uint32_t idesc = idesc_tf32(128, NK, false, false);
+        const uint32_t qh = smem_u32(smem + AU_OFF_QHI), ql = smem_u32(smem + AU_OFF_QLO);
+        const uint32_t kh = smem_u32(smem + AU_OFF_KHI), kl = smem_u32(smem + AU_OFF_KLO);
+        uint32_t acc = 0;
 #pragma unroll
-            for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {
-                    const uint64_t dah = smem_desc(qh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
-                    const uint64_t dal = smem_desc(ql + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
-                    const uint64_t dbh = smem_desc(kh + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
-                    const uint64_t dbl = smem_desc(kl + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
-                    mma_tf32(t_s, dal, dbh, idesc, acc);
-                    mma_tf32(t_s, dah, dbl, idesc, 1u);
-                    mma_tf32(t_s, dah, dbh, idesc, 1u);
-                    acc = 1u;
-                }
-            }
-            mma_commit(s_full);
-        }
-        __syncwarp();
-        // ---- V: raw fp32 -> hi in place, lo into the K region once MMA 1 has retired
-        mbar_wait(bar_v, 0);
-        mbar_wait(s_full, 0);
-        split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, 128);
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(v_ready);
-        if (warp == 1 && elect_one()) {
-            // ================================================================= MMA 2: O = P V
-            mbar_wait(v_ready, 0);
-            mbar_wait(p_ready, 0);
-            tc_fence_after();
-            const uint32_t idesc = idesc_tf32(128, AU_DH, false, true);
-            const uint32_t vh = smem_u32(smem + AU_OFF_V), vl = smem_u32(smem + AU_OFF_KHI);
-            uint32_t acc = 0;
-            for (int kstep = 0; kstep < NK / 8; ++kstep) {
-                const int kb = kstep >> 2, ks = kstep & 3;
-                const uint64_t dbh = smem_desc(vh + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
-                const uint64_t dbl = smem_desc(vl + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
-                const uint32_t col = (uint32_t)(kstep * 8);
-                mma_tf32_ts(t_o, t_lo + col, dbh, idesc, acc);
-                mma_tf32_ts(t_o, t_s + col, dbl, idesc, 1u);
-                mma_tf32_ts(t_o, t_s + col, dbh, idesc, 1u);
+            for (int ks = 0; ks < 4; ++ks) {
+                const uint64_t dah = smem_desc(qh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dal = smem_desc(ql + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dbh = smem_desc(kh + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dbl = smem_desc(kl + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                mma_tf32(t_s, dal, dbh, idesc, acc);
+                mma_tf32(t_s, dah, dbl, idesc, 1u);
+                mma_tf32(t_s, dah, dbh, idesc, 1u);
                 acc = 1u;
             }
-            mma_commit(o_full);
         }
-    } else {
-        // ===================================================================== softmax + epilogue (thread = query row)
-        const int quarter = warp - 4;
-        const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
-        const int i = qt * 128 + quarter * 32 + lane;              // position in the sequence
-        const bool row_ok = i < p.L;
-        const int nch = (NK + 31) / 32;
-        const unsigned long long pbase = ((unsigned long long)bh * p.L + (unsigned long long)(row_ok ? i : 0)) * p.L;
-        mbar_wait(s_full, 0);
-        tc_fence_after();
-        float m = -INFINITY;
+        mma_commit(s_full);
+    }
+    __syncwarp();
+    // ---- V: raw fp32 -> hi in place, lo into the K region once MMA 1 has retired
+    mbar_wait(bar_v, 0);
+    mbar_wait(s_full, 0);
+    tc_fence_after();
+    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AU_THREADS);
+    fence_proxy_async_smem();
+
+    // ========================================================================= softmax: thread = (query row, column half)
+    // Two warps share each TMEM lane quarter and take alternate 32-column chunks; row max and row sum are exchanged
+    // through shared memory.  A chunk every pair of which is masked for rows that do have a permitted key contributes
+    // exp(-10000 - max) == 0 exactly: it is not read, P = 0 is stored.
+    const int quarter = warp & 3, half = warp >> 2;
+    const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
+    const int i0 = qt * 128 + quarter * 32;
+    const int i = i0 + lane;                                       // position in the sequence
+    const bool row_ok = i < p.L;
+    const int nch = (NK + 31) / 32;
+    const int first_valid = *s_first;
+    const bool can_skip = i0 >= first_valid;                       // every row of this warp has a permitted key
+    const unsigned long long pbase = ((unsigned long long)bh * p.L + (unsigned long long)(row_ok ? i : 0)) * p.L;
+    unsigned live = 0;
+    for (int c = half; c < nch; c += 2)
+        if (!(can_skip && (c * 32 > i0 + 31 || c * 32 + 31 < first_valid))) live |= 1u << c;
+    float m = -INFINITY;
 #pragma unroll 1
-        for (int c = 0; c < nch; ++c) {                            // sweep 1: row max of the masked, scaled scores
-            float v[32];
-            tmem_ld32(t_s + lane_base + c * 32, v);
+    for (int c = half; c < nch; c += 2) {                          // sweep 1: row max of the masked, scaled scores
+        if (!(live >> c & 1)) continue;
+        float v[32];
+        tmem_ld32(t_s + lane_base + c * 32, v);
 #pragma unroll
-            for (int jj = 0; jj < 32; ++jj) {
-                const int j = c * 32 + jj;
-                const float s = v[jj] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
-                if (j < p.L) m = fmaxf(m, s);
-            }
+        for (int jj = 0; jj < 32; ++jj) {
+            const int j = c * 32 + jj;
+            const float s = v[jj] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
+            if (j < p.L) m = fmaxf(m, s);
         }
-        float l = 0.f;
-        const bool fast_rng = (pbase & 3ull) == 0ull;
+    }
+    xch[half * 128 + quarter * 32 + lane] = m;
+    asm volatile("bar.sync %0, 64;" ::"r"(quarter + 1) : "memory");
+    m = fmaxf(m, xch[(half ^ 1) * 128 + quarter * 32 + lane]);
+    float l = 0.f;
+    const bool fast_rng = (pbase & 3ull) == 0ull;
 #pragma unroll 1
-        for (int c = 0; c < nch; ++c) {                            // sweep 2: exp, sum, dropout, split, back into TMEM
+    for (int c = half; c < nch; c += 2) {                          // sweep 2: exp, sum, dropout, split, back into TMEM
+        uint32_t hi[32], lo[32];
+        if (live >> c & 1) {
             float v[32];
             tmem_ld32(t_s + lane_base + c * 32, v);
-            uint32_t hi[32], lo[32];
 #pragma unroll
             for (int g4 = 0; g4 < 8; ++g4) {
                 float mult[4];
@@ -228,30 +221,53 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
                     hi[g4 * 4 + e] = __float_as_uint(h); lo[g4 * 4 + e] = __float_as_uint(lw);
                 }
             }
-            tmem_st32(t_s + lane_base + c * 32, hi);
-            tmem_st32(t_lo + lane_base + c * 32, lo);
-        }
-        tmem_wait_st();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(p_ready);
-
-        mbar_wait(o_full, 0);
-        tc_fence_after();
-        const float inv = row_ok ? 1.0f / l : 0.f;
-        float* dst = p.ctx + (seq_base + (row_ok ? i : 0)) * p.d + col0;
-#pragma unroll 1
-        for (int c = 0; c < AU_DH / 32; ++c) {
-            float v[32];
-            tmem_ld32(t_o + lane_base + c * 32, v);
-            if (row_ok) {
+        } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e)
-                    *reinterpret_cast<float4*>(dst + c * 32 + e * 4) =
-                        make_float4(v[4 * e] * inv, v[4 * e + 1] * inv, v[4 * e + 2] * inv, v[4 * e + 3] * inv);
-            }
+            for (int e = 0; e < 32; ++e) { hi[e] = 0u; lo[e] = 0u; }
         }
-        if (row_ok) *reinterpret_cast<float2*>(p.lse + 2 * ((long long)bh * p.L + i)) = make_float2(m, logf(l));
+        tmem_st32(t_s + lane_base + c * 32, hi);
+        tmem_st32(t_lo + lane_base + c * 32, lo);
+    }
+    xch[256 + half * 128 + quarter * 32 + lane] = l;
+    tmem_wait_st();
+    tc_fence_before();
+    __syncthreads();                                               // P pair in TMEM, V pair in smem, row sums in xch
+    l += xch[256 + (half ^ 1) * 128 + quarter * 32 + lane];
+
+    if (warp == 1 && elect_one()) {
+        // ===================================================================== MMA 2: O = P V
+        tc_fence_after();
+        const uint32_t idesc = idesc_tf32(128, AU_DH, false, true);
+        const uint32_t vh = smem_u32(smem + AU_OFF_V), vl = smem_u32(smem + AU_OFF_KHI);
+        uint32_t acc = 0;
+        for (int kstep = 0; kstep < NK / 8; ++kstep) {
+            const int kb = kstep >> 2, ks = kstep & 3;
+            const uint64_t dbh = smem_desc(vh + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint64_t dbl = smem_desc(vl + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint32_t col = (uint32_t)(kstep * 8);
+            mma_tf32_ts(t_o, t_lo + col, dbh, idesc, acc);
+            mma_tf32_ts(t_o, t_s + col, dbl, idesc, 1u);
+            mma_tf32_ts(t_o, t_s + col, dbh, idesc, 1u);
+            acc = 1u;
+        }
+        mma_commit(o_full);
+    }
+    __syncwarp();
+    // ========================================================================= epilogue: warp half h stores O columns [32h, 32h+32)
+    mbar_wait(o_full, 0);
+    tc_fence_after();
+    {
+        const float inv = row_ok ? 1.0f / l : 0.f;
+        float* dst = p.ctx + (seq_base + (row_ok ? i : 0)) * p.d + col0 + half * 32;
+        float v[32];
+        tmem_ld32(t_o + lane_base + half * 32, v);
+        if (row_ok) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                *reinterpret_cast<float4*>(dst + e * 4) =
+                    make_float4(v[4 * e] * inv, v[4 * e + 1] * inv, v[4 * e + 2] * inv, v[4 * e + 3] * inv);
+            if (half == 0) *reinterpret_cast<float2*>(p.lse + 2 * ((long long)bh * p.L + i)) = make_float2(m, logf(l));
+        }
     }
     tc_fence_before();
     __syncthreads();

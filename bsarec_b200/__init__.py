@@ -5,7 +5,9 @@
 from .model import BSARecModel
 from .trainer import Trainer
 from .optim import FusedAdam
+from .data import SequenceStore, DeviceBatchLoader, HitRankAccumulator
 
 MODEL_DICT = {"bsarec": BSARecModel}
 
-__all__ = ["BSARecModel", "Trainer", "FusedAdam", "MODEL_DICT"]
+__all__ = ["BSARecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
+           "HitRankAccumulator"]

@@ -249,6 +249,26 @@ int bsa_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
                   float beta2, float eps, float weight_decay, int64_t step, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Either side of the model call: integer kernels, bit-exact.
+ * ---------------------------------------------------------------------------------------------- */
+/* Batch construction from a device-resident CSR of the user sequences — replaces RecDataset.__init__'s prefix
+ * expansion and __getitem__'s slicing / left padding (dataset.py:18-28, 61-72) plus the DataLoader collate.
+ *   seq_indptr int64 [n_users+1], seq_items int64 [nnz]: the lines of <data_name>.txt (dataset.py:184-197).
+ *   mode 0 = train: sample s is the (s - sample_start[u])-th prefix of user u's window seq[-(L+2):-2];
+ *            sample_start int64 [n_users+1] = exclusive prefix sum of min(max(len_u - 2, 0), L).
+ *   mode 1 = valid (items = seq[:-1]), mode 2 = test (items = seq): sample s is user s; sample_start unused.
+ *   sample_idx int64 [B] (the sampler's indices).  Outputs: input_ids int64 [B,L] left-padded with 0,
+ *   answers int64 [B] (= items[-1]), user_ids int64 [B] (train: the owning user; valid/test: s), as the reference's
+ *   batch tuple (dataset.py:74-113).  Every sequence must have len >= 3 (the caller checks once on the host). */
+int bsa_build_batch(int mode, const int64_t* seq_indptr, const int64_t* seq_items, const int64_t* sample_start, int64_t n_users,
+                    const int64_t* sample_idx, int B, int L, int64_t* input_ids, int64_t* answers, int64_t* user_ids,
+                    void* stream);
+/* Hit-rank histogram — what recall_at_k / ndcg_k (metrics.py:3-23) are sums over: hist[r] += number of users whose
+ * answer is at position r of pred[u, :k] (lists hold distinct ids), hist[k] += users without a hit.  pred int64 [U,k],
+ * answers int64 [U], hist int64 [k+1] ACCUMULATED (zero it once per evaluation).  Integer atomics only. */
+int bsa_hit_rank_hist(const int64_t* pred, const int64_t* answers, int64_t U, int k, int64_t* hist, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Small utilities shared by the host wrappers
  * ---------------------------------------------------------------------------------------------- */
 /* dst [B,d] = src[:, L-1, :] */

@@ -173,7 +173,37 @@ def beauty_case():
     print("beauty", info)
 
 
+
+def dataset_case():
+    """Batch construction: the reference's RecDataset / rating matrices on a seeded synthetic corpus -> dataset_small.npz."""
+    rng = np.random.RandomState(5)
+    L, N = 12, 60
+    lens = [3, 4, 5, 13, 14, 15, 16, 40] + list(rng.randint(3, 30, size=40))
+    user_seq = [list(map(int, rng.randint(1, N, size=n))) for n in lens]
+    args = argparse.Namespace(max_seq_length=L, item_size=N, model_type="BSARec")
+    out = {"L": L, "item_size": N, "seq_indptr": np.cumsum([0] + lens).astype(np.int64),
+           "seq_items": np.concatenate(user_seq).astype(np.int64)}
+    import random
+    random.seed(0)
+    for dt in ("train", "valid", "test"):
+        ds = ref_dataset.RecDataset(args, user_seq, data_type=dt)
+        rows = [ds[i] for i in range(len(ds))]
+        out[f"{dt}_user_ids"] = np.array([int(r[0]) for r in rows], dtype=np.int64)
+        out[f"{dt}_input_ids"] = torch.stack([r[1] for r in rows]).numpy()
+        out[f"{dt}_answers"] = np.array([int(r[2]) for r in rows], dtype=np.int64)
+    for dt, fn in (("valid", ref_dataset.generate_rating_matrix_valid), ("test", ref_dataset.generate_rating_matrix_test)):
+        m = fn(user_seq, len(user_seq), N).tocsr()
+        m.sort_indices()
+        out[f"{dt}_hist_indptr"] = m.indptr.astype(np.int64)
+        out[f"{dt}_hist_indices"] = m.indices.astype(np.int64)
+    np.savez_compressed(os.path.join(HERE, "dataset_small.npz"), **out)
+    print("dataset_small.npz", {k: np.asarray(v).shape for k, v in out.items()})
+
+
 if __name__ == "__main__":
+    if "--dataset-only" in sys.argv:
+        dataset_case()
+        sys.exit(0)
     small_case("small_a", 7, B=6, item_size=211, hidden_size=32, max_seq_length=24, num_attention_heads=4,
                num_hidden_layers=2, c=7, alpha=0.7)
     small_case("small_b", 11, B=8, item_size=500, hidden_size=64, max_seq_length=50, num_attention_heads=1,
@@ -181,3 +211,4 @@ if __name__ == "__main__":
     small_case("small_c", 13, B=5, item_size=97, hidden_size=64, max_seq_length=25, num_attention_heads=2,
                num_hidden_layers=3, c=9, alpha=0.3)
     beauty_case()
+    dataset_case()

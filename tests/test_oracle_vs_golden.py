@@ -165,3 +165,49 @@ def test_dropout_rng_statistics_and_determinism():
     # lanes of one 64-bit word are independent enough: no correlation between neighbours
     a = keep.reshape(-1)
     assert abs(np.corrcoef(a[:-1], a[1:])[0, 1]) < 0.01
+
+
+# ------------------------------------------------------------------ batch construction / metrics
+def _dataset_golden():
+    from conftest import GOLDEN
+    z = np.load(os.path.join(GOLDEN, "dataset_small.npz"))
+    d = {k: z[k] for k in z.files}
+    ptr = d["seq_indptr"]
+    user_seq = [d["seq_items"][ptr[u]:ptr[u + 1]].tolist() for u in range(len(ptr) - 1)]
+    return d, user_seq
+
+
+@pytest.mark.parametrize("data_type", ["train", "valid", "test"])
+def test_dataset_oracle_matches_reference_recdataset(data_type):
+    """oracle.dataset_oracle vs the unmodified RecDataset's samples (fixture made by make_golden.dataset_case)."""
+    from oracle import dataset_oracle as do
+    d, user_seq = _dataset_golden()
+    n = len(d[f"{data_type}_answers"])
+    users, ids, answers = do.build_batch(user_seq, int(d["L"]), data_type, range(n))
+    assert np.array_equal(users, d[f"{data_type}_user_ids"])
+    assert np.array_equal(ids, d[f"{data_type}_input_ids"])
+    assert np.array_equal(answers, d[f"{data_type}_answers"])
+    samples, _ = do.expand_samples(user_seq, int(d["L"]), data_type)
+    assert len(samples) == n
+
+
+@pytest.mark.parametrize("data_type", ["valid", "test"])
+def test_history_oracle_matches_reference_rating_matrix(data_type):
+    from oracle import dataset_oracle as do
+    d, user_seq = _dataset_golden()
+    indptr, indices = do.history_csr(user_seq, data_type)
+    assert np.array_equal(indptr, d[f"{data_type}_hist_indptr"])
+    assert np.array_equal(indices, d[f"{data_type}_hist_indices"])
+
+
+def test_hit_rank_hist_reproduces_reference_metrics_on_beauty():
+    """Histogram form of HR/NDCG == the reference's per-user loops on the Beauty test split's pred_list."""
+    from oracle import dataset_oracle as do
+    from bsarec_b200.data import metrics_from_hist
+    _, data = load_golden("beauty_test")
+    hist = do.hit_rank_hist(data["answers"].tolist(), data["pred_list"].tolist(), 20)
+    assert int(hist.sum()) == len(data["answers"])
+    recall, ndcg = metrics_from_hist(hist, [5, 10, 20])
+    got = [recall[0], ndcg[0], recall[1], ndcg[1], recall[2], ndcg[2]]
+    assert got == pytest.approx(list(data["metrics"]), abs=1e-12)
+    assert ["%.4f" % v for v in got] == ["0.0736", "0.0523", "0.1008", "0.0611", "0.1373", "0.0703"]

@@ -81,10 +81,10 @@ int bsa_build_batch(int mode, const int64_t* seq_indptr, const int64_t* seq_item
                     const int64_t* sample_idx, int B, int L, int64_t* input_ids, int64_t* answers, int64_t* user_ids,
                     void* stream) {
     BSA_REQUIRE(mode >= 0 && mode <= 2, "bsa_build_batch: mode must be 0 (train), 1 (valid) or 2 (test)");
-    BSA_REQUIRE(seq_indptr && seq_items && sample_idx && input_ids && answers && user_ids, "bsa_build_batch: null argument");
-    BSA_REQUIRE(mode != 0 || sample_start, "bsa_build_batch: train mode needs sample_start");
     BSA_REQUIRE(B >= 0 && L > 0 && n_users > 0, "bsa_build_batch: bad sizes");
     if (B == 0) return 0;
+    BSA_REQUIRE(seq_indptr && seq_items && sample_idx && input_ids && answers && user_ids, "bsa_build_batch: null argument");
+    BSA_REQUIRE(mode != 0 || sample_start, "bsa_build_batch: train mode needs sample_start");
     const int threads = 256, rows_per_block = threads / 32;
     bsa::build_batch_kernel<<<bsa::cdiv(B, rows_per_block), threads, 0, (cudaStream_t)stream>>>(
         mode, (const long long*)seq_indptr, (const long long*)seq_items, (const long long*)sample_start, n_users,
@@ -94,9 +94,9 @@ int bsa_build_batch(int mode, const int64_t* seq_indptr, const int64_t* seq_item
 }
 
 int bsa_hit_rank_hist(const int64_t* pred, const int64_t* answers, int64_t U, int k, int64_t* hist, void* stream) {
-    BSA_REQUIRE(pred && answers && hist, "bsa_hit_rank_hist: null argument");
     BSA_REQUIRE(k > 0 && k <= 1024 && U >= 0, "bsa_hit_rank_hist: bad sizes");
     if (U == 0) return 0;
+    BSA_REQUIRE(pred && answers && hist, "bsa_hit_rank_hist: null argument");
     const int threads = 256;
     long long blocks = (U + threads - 1) / threads;
     if (blocks > 148 * 8) blocks = 148 * 8;

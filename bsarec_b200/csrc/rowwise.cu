@@ -21,6 +21,13 @@ constexpr float LN_EPS = 1e-12f;
         else { set_error("row length %d > 1024 is not supported", (int)(n)); return -1; }   \
     } while (0)
 
+// the float4 kernels of rowwise_vec.cu need d % 4 == 0 and 16-byte aligned tensors (null pointers = absent operands)
+template <class... P>
+inline bool vec_ok(int d, P... ptrs) {
+    const uintptr_t bits = (... | (uintptr_t)ptrs);
+    return rowwise_vec_ok(d) && (bits & 15u) == 0;
+}
+
 inline int row_grid(long long rows) {
     long long g = (rows + WARPS - 1) / WARPS;
     if (g > MAX_ROW_BLOCKS) g = MAX_ROW_BLOCKS;
@@ -532,6 +539,7 @@ int embed_ln_dropout_fwd(const long long* ids, const float* E, const float* Ppos
     (void)item_size;
     const long long M = (long long)B * L;
     if (M == 0) return 0;
+    if (vec_ok(d, E, Ppos, gamma, beta, out)) return embed_fwd_vec(ids, E, Ppos, gamma, beta, out, mean, rstd, M, L, d, dr, row_grid(M), st);
     BSA_DISPATCH_VPL(d, (embed_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(ids, E, Ppos, gamma, beta, out, mean,
                                                                                   rstd, M, L, d, dr)));
     BSA_LAUNCH_CHECK();
@@ -544,6 +552,7 @@ int embed_ln_dropout_bwd(const float* dout, const long long* ids, const float* E
     const long long M = (long long)B * L;
     const int g = row_grid(M);
     *nblk = g;
+    if (vec_ok(d, dout, E, Ppos, gamma, dz)) return embed_bwd_vec(dout, ids, E, Ppos, gamma, mean, rstd, dz, pgamma, pbeta, M, L, d, dr, g, st);
     BSA_DISPATCH_VPL(d, (embed_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dout, ids, E, Ppos, gamma, mean, rstd, dz,
                                                                        pgamma, pbeta, M, L, d, dr)));
     BSA_LAUNCH_CHECK();
@@ -554,6 +563,9 @@ int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, co
                     float* z_save, float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b,
                     long long M, int d, Dropout dr, cudaStream_t st) {
     if (M == 0) return 0;
+    if (vec_ok(d, tmp, resid, gamma, beta, out, z_save, blend_with))
+        return residual_ln_fwd_vec(tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr,
+                                   row_grid(M), st);
     BSA_DISPATCH_VPL(d, (residual_ln_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(
                             tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr)));
     BSA_LAUNCH_CHECK();
@@ -565,6 +577,7 @@ int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, c
            cudaStream_t st) {
     const int g = row_grid(M);
     *nblk = g;
+    if (vec_ok(d, dy, z, gamma, dz, ddrop)) return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, st);
     BSA_DISPATCH_VPL(d, (ln_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop,
                                                                     pgamma, pbeta, M, d, dr)));
     BSA_LAUNCH_CHECK();
@@ -593,6 +606,7 @@ int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const
                   float* dsp, float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr,
                   cudaStream_t st) {
     if (B == 0) return 0;
+    if (vec_ok(d, x, sqrt_beta, gamma, beta, dsp, z_save)) return filter_ln_fwd_vec(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, B, L, d, r, dr, st);
     const size_t smem = (size_t)r * d * sizeof(float);
     BSA_REQUIRE(smem <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);
     BSA_DISPATCH_VPL(d, {
@@ -609,6 +623,7 @@ int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const
 int filter_bwd(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2,
                int B, int L, int d, int r, Dropout dr, cudaStream_t st) {
     if (B == 0) return 0;
+    if (vec_ok(d, x, sqrt_beta, dz_f, dx)) return filter_bwd_vec(x, Cb, sqrt_beta, dz_f, dx, pbeta2, B, L, d, r, dr, st);
     const size_t smem = 2 * (size_t)r * d * sizeof(float);
     BSA_REQUIRE(smem <= 200 * 1024, "filter bwd: basis rank %d x hidden %d does not fit shared memory", r, d);
     if (smem > 48 * 1024)

@@ -59,6 +59,23 @@ int scatter_plan(const long long* ids, long long M, long long item_size, void* p
 int scatter_add_rows(const void* plan, long long M, const float* dz, float* dE, int d, cudaStream_t st);
 
 int fill_zero(float* p, long long n, cudaStream_t st);
+
+// ---- rowwise_vec.cu: float4 / shared-memory-staged versions, used when rowwise_vec_ok(d) (d % 4 == 0)
+bool rowwise_vec_ok(int d);
+int embed_fwd_vec(const long long* ids, const float* E, const float* Ppos, const float* gamma, const float* beta, float* out,
+                  float* mean, float* rstd, long long M, int L, int d, Dropout dr, int grid, cudaStream_t st);
+int embed_bwd_vec(const float* dout, const long long* ids, const float* E, const float* Ppos, const float* gamma,
+                  const float* mean, const float* rstd, float* dz, float* pgamma, float* pbeta, long long M, int L, int d,
+                  Dropout dr, int grid, cudaStream_t st);
+int residual_ln_fwd_vec(const float* tmp, const float* resid, const float* gamma, const float* beta, float* out, float* z_save,
+                        float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b, long long M, int d,
+                        Dropout dr, int grid, cudaStream_t st);
+int ln_bwd_vec(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
+               float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, cudaStream_t st);
+int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta, float* dsp,
+                      float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st);
+int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2, int B,
+                   int L, int d, int r, Dropout dr, cudaStream_t st);
 // dst[b*L + (L-1)][:] = src[b][:], everything else 0
 int scatter_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st);
 int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st);

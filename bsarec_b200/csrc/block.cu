@@ -100,7 +100,7 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     if (attn_fused_supported(c.L, c.d, c.H) && attn_impl() == 2) b.f((long long)c.B * c.H * c.L);   // delta
     else { b.f(PL); b.f(PL); }
     // partials: LN gamma/beta, column sums, split-K, beta2
-    b.f(2ll * rowwise_partial_blocks(M) * d);
+    b.f(3ll * rowwise_partial_blocks(M) * d);
     b.f((long long)colsum_partial_rows(M) * 4 * d);
     b.f(splitk_floats(M, d));
     b.f((long long)c.B * d);
@@ -147,7 +147,7 @@ int linear_bwd_weight(const Lin& ln, const Act& dy, const Act& x, float* dW, flo
         int rc = umma_gemm_ps(N, K, (int)M, dy.hi, dy.lo, M, N, N, true, x.hi, x.lo, M, K, K, true, dW, K, nullptr, 0, nullptr,
                               nullptr, 1.f, 0, nullptr, nullptr, ln.partial, ln.partial_bytes, st);
         if (rc) return rc;
-        return colsum(dy.x, M, N, part_cs, db, 0, st);
+        return db ? colsum(dy.x, M, N, part_cs, db, 0, st) : 0;      // db == nullptr: the producer already summed the columns
     }
     GemmP p;
     p.A = dy.x; p.B = x.x; p.C = dW; p.M = N; p.N = K; p.K = (int)M; p.lda = N; p.ldb = K; p.ldc = K;
@@ -265,6 +265,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const int nrb = rowwise_partial_blocks(M);
     float* pgam = b.f((long long)nrb * d);
     float* pbet = b.f((long long)nrb * d);
+    float* pcol = b.f((long long)nrb * d);
     float* part_cs = b.f((long long)colsum_partial_rows(M) * 4 * d);
     float* part_sk = b.f(splitk_floats(M, d));
     float* pbeta2 = b.f((long long)B * d);
@@ -283,24 +284,44 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     int rc, nblk = 0;
 
     // ---- feed-forward: x_out = LN(drop(tmp2) + y)
-    if ((rc = ln_bwd(g_out, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_o, st))) return rc;
+    // on the tcgen05 path the LN backward emits the gradient w.r.t. dense_2's output directly as a split-TF32 pair plus its
+    // column partials (= b2's gradient): no fp32 copy, no separate split and column-sum passes over [M, d]
+    const bool fuse_o = lin.umma && ln_bwd_split_ok(d, g_out, s.z_o, w.o_ln_w, dyb, nullptr, g_hi, g_lo);
+    if (fuse_o) {
+        if ((rc = ln_bwd_split(g_out, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, nullptr, pgam, pbet, &nblk, M, d, dr_o, g_hi, g_lo, pcol, st))) return rc;
+        if ((rc = reduce_partials(pcol, nblk, d, g.b2, nullptr, 1.f, 0, st))) return rc;
+        ag = Act{nullptr, g_hi, g_lo};
+    } else {
+        if ((rc = ln_bwd(g_out, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_o, st))) return rc;
+    }
     if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
-    const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
-    if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
-    if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if (!fuse_o) {
+        const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
+        if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
+    }
+    if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, fuse_o ? nullptr : g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, dh_hi, dh_lo, st))) return rc;
     const Act adh{dh_, dh_hi, dh_lo};                                          // emitted split by the epilogue above
     if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
-    if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_a, st))) return rc;
+    const bool fuse_a = lin.umma && ln_bwd_split_ok(d, dyb, s.z_a, w.a_ln_w, dx, nullptr, g_hi, g_lo);
+    if (fuse_a) {
+        if ((rc = ln_bwd_split(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, nullptr, pgam, pbet, &nblk, M, d, dr_a, g_hi, g_lo, pcol, st))) return rc;
+        if ((rc = reduce_partials(pcol, nblk, d, g.bo, nullptr, 1.f, 0, st))) return rc;
+        ag = Act{nullptr, g_hi, g_lo};
+    } else {
+        if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_a, st))) return rc;
+    }
     if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
-    const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
-    if ((rc = split_act(lin, t1, g_hi, g_lo, M * d, ag, st))) return rc;
-    if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, g.bo, M, d, d, part_sk, part_cs, st))) return rc;
+    if (!fuse_a) {
+        const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
+        if ((rc = split_act(lin, t1, g_hi, g_lo, M * d, ag, st))) return rc;
+    }
+    if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, fuse_a ? nullptr : g.bo, M, d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, ag, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     if (s.fused) {
         // dP (workspace, unused by this path) doubles as the [B,H,L] delta scratch

@@ -436,15 +436,35 @@ __global__ void colsum_partial_kernel(const float* __restrict__ X, long long M, 
     }
 }
 
-__global__ void reduce_partials_kernel(const float* __restrict__ part, int nblk, int n, float* __restrict__ out,
-                                       const float* __restrict__ mult, float scale, int accumulate) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
-    float s = 0.f;
-    for (int k = 0; k < nblk; ++k) s += part[(long long)k * n + j];
-    s *= scale;
-    if (mult) s *= mult[j];
-    out[j] = accumulate ? out[j] + s : s;
+// out[j] (+)= mult[j]*scale * sum_k part[k][j].  Block = 32 columns x 8 row groups: group g sums rows k = g, g+8, ...
+// (independent loads, unrolled), then the 8 group sums are added in fixed order -> deterministic.
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const float* __restrict__ part, int nblk, int n, float* __restrict__ out,
+                       const float* __restrict__ mult, float scale, int accumulate) {
+    __shared__ float sh[8][32];
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + lane;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (j < n) {
+        int k = g;
+        for (; k + 24 < nblk; k += 32) {
+            s0 += part[(long long)k * n + j];
+            s1 += part[(long long)(k + 8) * n + j];
+            s2 += part[(long long)(k + 16) * n + j];
+            s3 += part[(long long)(k + 24) * n + j];
+        }
+        for (; k < nblk; k += 8) s0 += part[(long long)k * n + j];
+    }
+    sh[g][lane] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (g == 0 && j < n) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s += sh[k][lane];
+        s *= scale;
+        if (mult) s *= mult[j];
+        out[j] = accumulate ? out[j] + s : s;
+    }
 }
 
 __global__ void pos_grad_kernel(const float* __restrict__ dz, float* __restrict__ dP, int B, long long LD, int accumulate) {
@@ -577,11 +597,26 @@ int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, c
            cudaStream_t st) {
     const int g = row_grid(M);
     *nblk = g;
-    if (vec_ok(d, dy, z, gamma, dz, ddrop)) return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, st);
+    if (vec_ok(d, dy, z, gamma, dz, ddrop))
+        return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, nullptr, nullptr, nullptr, st);
     BSA_DISPATCH_VPL(d, (ln_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop,
                                                                     pgamma, pbeta, M, d, dr)));
     BSA_LAUNCH_CHECK();
     return 0;
+}
+
+bool ln_bwd_split_ok(int d, const float* dy, const float* z, const float* gamma, const float* dz, const float* ddrop,
+                     const float* t_hi, const float* t_lo) {
+    return vec_ok(d, dy, z, gamma, dz, ddrop, t_hi, t_lo);
+}
+
+int ln_bwd_split(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
+                 float* dz, float* ddrop, float* pgamma, float* pbeta, int* nblk, long long M, int d, Dropout dr, float* t_hi,
+                 float* t_lo, float* pcol, cudaStream_t st) {
+    BSA_REQUIRE(ln_bwd_split_ok(d, dy, z, gamma, dz, ddrop, t_hi, t_lo), "ln_bwd_split: needs d %% 4 == 0 and 16-byte aligned tensors");
+    const int g = row_grid(M);
+    *nblk = g;
+    return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, t_hi, t_lo, pcol, st);
 }
 
 int filter_rank(int L, int kept_bins) {
@@ -671,7 +706,7 @@ int colsum(const float* X, long long M, int N, float* part, float* out, int accu
 
 int reduce_partials(const float* part, int nblk, int n, float* out, const float* mult, float scale, int accumulate,
                     cudaStream_t st) {
-    reduce_partials_kernel<<<cdiv(n, 128), 128, 0, st>>>(part, nblk, n, out, mult, scale, accumulate);
+    reduce_partials_kernel<<<cdiv(n, 32), 256, 0, st>>>(part, nblk, n, out, mult, scale, accumulate);
     BSA_LAUNCH_CHECK();
     return 0;
 }

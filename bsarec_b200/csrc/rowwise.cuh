@@ -25,6 +25,13 @@ int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, co
 int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
            float* dz, float* ddrop, float* pgamma, float* pbeta, int* nblk, long long M, int d, Dropout dr,
            cudaStream_t st);
+// Same, and t = (dropout on ? ddrop : dz) also leaves as the split-TF32 pair (t_hi, t_lo) with per-block column partials
+// pcol [nblk][d] (sum = the bias gradient of the nn.Linear that produced the LN input).  Needs ln_bwd_split_ok(...).
+bool ln_bwd_split_ok(int d, const float* dy, const float* z, const float* gamma, const float* dz, const float* ddrop,
+                     const float* t_hi, const float* t_lo);
+int ln_bwd_split(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
+                 float* dz, float* ddrop, float* pgamma, float* pbeta, int* nblk, long long M, int d, Dropout dr, float* t_hi,
+                 float* t_lo, float* pcol, cudaStream_t st);
 
 // ---- filter branch (bsarec.py:90-104) in its exact low-rank real form low = C (C^T x)
 int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta,
@@ -71,7 +78,8 @@ int residual_ln_fwd_vec(const float* tmp, const float* resid, const float* gamma
                         float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b, long long M, int d,
                         Dropout dr, int grid, cudaStream_t st);
 int ln_bwd_vec(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
-               float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, cudaStream_t st);
+               float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, float* t_hi,
+               float* t_lo, float* pcol, cudaStream_t st);
 int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta, float* dsp,
                       float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st);
 int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2, int B,

@@ -39,6 +39,12 @@ __device__ __forceinline__ float4 mult4(const Dropout& dr, unsigned long long i)
     dropout_mult4(dr, i, m);
     return make_float4(m[0], m[1], m[2], m[3]);
 }
+__device__ __forceinline__ void split1(float x, float& hi, float& lo) {      // as umma_engine.cu's split_tf32
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+    hi = __uint_as_float(h);
+    lo = x - hi;
+}
 __device__ __forceinline__ unsigned long long row_index(const Dropout& dr, long long row, int d, int c) {
     return (unsigned long long)((row * dr.rmul + dr.radd) * d + c);
 }
@@ -201,12 +207,12 @@ __global__ void __launch_bounds__(WARPS * 32, NV <= 2 ? 4 : 2)
 ln_bwd_vec_kernel(const float* __restrict__ dy, float dy_scale, const float* __restrict__ z, const float* __restrict__ mean_i,
                   const float* __restrict__ rstd_i, const float* __restrict__ gamma, float* __restrict__ dz,
                   float* __restrict__ ddrop, float* __restrict__ pgamma, float* __restrict__ pbeta, long long M, int d,
-                  Dropout dr) {
+                  Dropout dr, float* __restrict__ t_hi, float* __restrict__ t_lo, float* __restrict__ pcol) {
     extern __shared__ float stage[];
     const int lane = threadIdx.x & 31;
-    float4 ag[NV], ab[NV];
+    float4 ag[NV], ab[NV], ac[NV];
 #pragma unroll
-    for (int i = 0; i < NV; ++i) ag[i] = ab[i] = f4(0.f);
+    for (int i = 0; i < NV; ++i) ag[i] = ab[i] = ac[i] = f4(0.f);
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
         const float mean = mean_i[row], rstd = rstd_i[row];
         float4 xh[NV], g[NV];
@@ -235,12 +241,25 @@ ln_bwd_vec_kernel(const float* __restrict__ dy, float dy_scale, const float* __r
                 const long long o = row * d + c;
                 const float4 r = rstd * (g[i] - f4(c1) - c2 * xh[i]);
                 st4(dz + o, r);
-                if (ddrop) st4(ddrop + o, r * mult4(dr, row_index(dr, row, d, c)));
+                if (ddrop || t_hi) {
+                    // t = gradient w.r.t. the pre-dropout tensor (the nn.Linear output): written as fp32 (ddrop) and / or
+                    // directly as the split-TF32 pair the tcgen05 dW / dX GEMMs consume; its column sums are the bias gradient
+                    const float4 t = dr.thr ? r * mult4(dr, row_index(dr, row, d, c)) : r;
+                    if (ddrop) st4(ddrop + o, t);
+                    if (t_hi) {
+                        float4 h, l;
+                        split1(t.x, h.x, l.x); split1(t.y, h.y, l.y); split1(t.z, h.z, l.z); split1(t.w, h.w, l.w);
+                        st4(t_hi + o, h);
+                        st4(t_lo + o, l);
+                        ac[i] = ac[i] + t;
+                    }
+                }
             }
         }
     }
     block_store_partials4<NV>(ag, pgamma, d, stage);
     block_store_partials4<NV>(ab, pbeta, d, stage);
+    if (pcol) block_store_partials4<NV>(ac, pcol, d, stage);
 }
 
 // ============================================================================ filter branch
@@ -440,10 +459,11 @@ int residual_ln_fwd_vec(const float* tmp, const float* resid, const float* gamma
 }
 
 int ln_bwd_vec(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
-               float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, cudaStream_t st) {
+               float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, float* t_hi,
+               float* t_lo, float* pcol, cudaStream_t st) {
     const size_t smem = (size_t)WARPS * d * sizeof(float);
     BSA_DISPATCH_NV(d, (ln_bwd_vec_kernel<NV><<<grid, WARPS * 32, smem, st>>>(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma,
-                                                                             pbeta, M, d, dr)));
+                                                                             pbeta, M, d, dr, t_hi, t_lo, pcol)));
     BSA_LAUNCH_CHECK();
     return 0;
 }

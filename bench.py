@@ -314,7 +314,8 @@ def main():
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md: 6.65 TB/s, 1.4 PF/s sustained bf16)"
     tensor_peak = bf16_peak / 2.0 / 3.0          # fp32-parity bar => 3xTF32: effective tensor peak
-    hbm_tags = {"adam", "embed_fwd", "embed_bwd", "scatter_add", "last_row_fwd", "last_row_bwd"}       # work counted in algorithmic bytes
+    hbm_tags = {"adam", "embed_fwd", "embed_bwd", "scatter_add", "last_row_fwd", "last_row_bwd", "filter_fwd", "filter_bwd",
+                "residual_ln_fwd", "ln_bwd"}       # work counted in algorithmic bytes
 
     def kernel_line(name, rec):
         sec = rec["ms"] * 1e-3

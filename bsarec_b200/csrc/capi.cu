@@ -56,7 +56,8 @@ struct ProfRec {
     long long launches = 0;
 };
 ProfRec g_prof[PROF_NUM_TAGS] = {{"gemm_simt"}, {"ce_fwd_umma"}, {"ce_bwd_umma"}, {"score_topk_umma"}, {"linear_umma"},
-                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}, {"adam"}, {"last_row_fwd"}, {"last_row_bwd"}};
+                                 {"embed_fwd"}, {"embed_bwd"}, {"scatter_add"}, {"attn_fwd"}, {"attn_bwd"}, {"adam"}, {"last_row_fwd"}, {"last_row_bwd"},
+                                 {"filter_fwd"}, {"filter_bwd"}, {"residual_ln_fwd"}, {"ln_bwd"}};
 std::vector<cudaEvent_t> g_event_pool;
 cudaEvent_t get_event() {
     if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }

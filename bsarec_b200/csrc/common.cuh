@@ -46,7 +46,8 @@ extern int g_profile_on;
 void prof_begin(int tag, cudaStream_t st);
 void prof_end(int tag, cudaStream_t st, double work);
 enum ProfTag : int { PROF_GEMM_SIMT = 0, PROF_CE_FWD_UMMA, PROF_CE_BWD_UMMA, PROF_TOPK_UMMA, PROF_LINEAR_UMMA,
-                     PROF_EMBED_FWD, PROF_EMBED_BWD, PROF_SCATTER_ADD, PROF_ATTN_FWD, PROF_ATTN_BWD, PROF_ADAM, PROF_LAST_FWD, PROF_LAST_BWD, PROF_NUM_TAGS };
+                     PROF_EMBED_FWD, PROF_EMBED_BWD, PROF_SCATTER_ADD, PROF_ATTN_FWD, PROF_ATTN_BWD, PROF_ADAM, PROF_LAST_FWD, PROF_LAST_BWD,
+                     PROF_FILTER_FWD, PROF_FILTER_BWD, PROF_RESID_LN_FWD, PROF_LN_BWD, PROF_NUM_TAGS };
 
 struct ProfScope {
     int tag; cudaStream_t st; double work;

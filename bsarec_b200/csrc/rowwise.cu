@@ -559,6 +559,7 @@ int embed_ln_dropout_fwd(const long long* ids, const float* E, const float* Ppos
     (void)item_size;
     const long long M = (long long)B * L;
     if (M == 0) return 0;
+    ProfScope prof(PROF_EMBED_FWD, st, (double)M * (8.0 + 2.0 * 4.0 * d));          // ids + gathered row read + output written
     if (vec_ok(d, E, Ppos, gamma, beta, out)) return embed_fwd_vec(ids, E, Ppos, gamma, beta, out, mean, rstd, M, L, d, dr, row_grid(M), st);
     BSA_DISPATCH_VPL(d, (embed_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(ids, E, Ppos, gamma, beta, out, mean,
                                                                                   rstd, M, L, d, dr)));
@@ -572,6 +573,7 @@ int embed_ln_dropout_bwd(const float* dout, const long long* ids, const float* E
     const long long M = (long long)B * L;
     const int g = row_grid(M);
     *nblk = g;
+    ProfScope prof(PROF_EMBED_BWD, st, (double)M * (8.0 + 3.0 * 4.0 * d));          // ids + dout, row read + dz written
     if (vec_ok(d, dout, E, Ppos, gamma, dz)) return embed_bwd_vec(dout, ids, E, Ppos, gamma, mean, rstd, dz, pgamma, pbeta, M, L, d, dr, g, st);
     BSA_DISPATCH_VPL(d, (embed_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dout, ids, E, Ppos, gamma, mean, rstd, dz,
                                                                        pgamma, pbeta, M, L, d, dr)));
@@ -583,6 +585,7 @@ int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, co
                     float* z_save, float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b,
                     long long M, int d, Dropout dr, cudaStream_t st) {
     if (M == 0) return 0;
+    ProfScope prof(PROF_RESID_LN_FWD, st, 4.0 * M * d * (3.0 + (z_save ? 1.0 : 0.0) + (blend_with ? 1.0 : 0.0)));
     if (vec_ok(d, tmp, resid, gamma, beta, out, z_save, blend_with))
         return residual_ln_fwd_vec(tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr,
                                    row_grid(M), st);
@@ -597,6 +600,7 @@ int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, c
            cudaStream_t st) {
     const int g = row_grid(M);
     *nblk = g;
+    ProfScope prof(PROF_LN_BWD, st, 4.0 * M * d * (3.0 + (ddrop ? 1.0 : 0.0)));
     if (vec_ok(d, dy, z, gamma, dz, ddrop))
         return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, nullptr, nullptr, nullptr, st);
     BSA_DISPATCH_VPL(d, (ln_bwd_kernel<VPL><<<g, WARPS * 32, 0, st>>>(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop,
@@ -616,6 +620,7 @@ int ln_bwd_split(const float* dy, float dy_scale, const float* z, const float* m
     BSA_REQUIRE(ln_bwd_split_ok(d, dy, z, gamma, dz, ddrop, t_hi, t_lo), "ln_bwd_split: needs d %% 4 == 0 and 16-byte aligned tensors");
     const int g = row_grid(M);
     *nblk = g;
+    ProfScope prof(PROF_LN_BWD, st, 4.0 * M * d * (5.0 + (ddrop ? 1.0 : 0.0)));      // dy, z read; dz, t_hi, t_lo written
     return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, t_hi, t_lo, pcol, st);
 }
 
@@ -641,6 +646,7 @@ int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const
                   float* dsp, float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr,
                   cudaStream_t st) {
     if (B == 0) return 0;
+    ProfScope prof(PROF_FILTER_FWD, st, 4.0 * B * (double)L * d * 3.0);             // x read; z_save, dsp written
     if (vec_ok(d, x, sqrt_beta, gamma, beta, dsp, z_save)) return filter_ln_fwd_vec(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, B, L, d, r, dr, st);
     const size_t smem = (size_t)r * d * sizeof(float);
     BSA_REQUIRE(smem <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);
@@ -658,6 +664,7 @@ int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const
 int filter_bwd(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2,
                int B, int L, int d, int r, Dropout dr, cudaStream_t st) {
     if (B == 0) return 0;
+    ProfScope prof(PROF_FILTER_BWD, st, 4.0 * B * (double)L * d * 4.0);             // x, dz_f read; dx read + written
     if (vec_ok(d, x, sqrt_beta, dz_f, dx)) return filter_bwd_vec(x, Cb, sqrt_beta, dz_f, dx, pbeta2, B, L, d, r, dr, st);
     const size_t smem = 2 * (size_t)r * d * sizeof(float);
     BSA_REQUIRE(smem <= 200 * 1024, "filter bwd: basis rank %d x hidden %d does not fit shared memory", r, d);

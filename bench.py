@@ -191,6 +191,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the one JSON line and nothing else
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(42)
     model = BSARecModel(make_args(cfg, P_DROP, P_DROP, batch_size=B)).to(dev)

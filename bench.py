@@ -18,6 +18,8 @@ import sys
 import threading
 import time
 
+_json_out = sys.stdout
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -151,7 +153,7 @@ def run_reference(args, desc, cfg, cpu_B):
         "e2e": {"value": val, "unit": "seqs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_json_out, flush=True)
 
 
 def main():
@@ -169,6 +171,12 @@ def main():
     ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
                     help="fused: bsarec_b200.FusedAdam (one kernel pass per tensor); torch: torch.optim.Adam (foreach)")
     args = ap.parse_args()
+    # stdout carries the one JSON line and nothing else: native libraries that write to fd 1 (NCCL prints its version banner
+    # there when NCCL_DEBUG is set) are pointed at stderr, the JSON line goes to the saved descriptor
+    global _json_out
+    sys.stdout.flush()
+    _json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     desc, cfg, B, cpu_B = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -191,7 +199,6 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the one JSON line and nothing else
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(42)
     model = BSARecModel(make_args(cfg, P_DROP, P_DROP, batch_size=B)).to(dev)
@@ -381,7 +388,7 @@ def main():
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": n * cpu_B / dt, "unit": "seqs/s", "cores": os.cpu_count(), "kind": "port",
                                 "sample": f"{n} train steps (fwd+bwd+Adam) of {cpu_B} sequences of the same workload, torch CPU, {os.cpu_count()} threads"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_json_out, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

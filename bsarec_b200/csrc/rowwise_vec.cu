@@ -297,18 +297,26 @@ __global__ void __launch_bounds__(FT)
 filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                          const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dsp,
                          float* __restrict__ z_save, float* __restrict__ mean_o, float* __restrict__ rstd_o, int L, int d,
-                         int r, Dropout dr) {
+                         int r, int cb_smem, Dropout dr) {
     extern __shared__ __align__(16) float fsm[];
     float* coef = fsm;                       // [r][d]
-    float* tile = fsm + (long long)r * d;    // [L][d] when STAGE
+    float* par = coef + (long long)r * d;    // [3][d]: beta^2, LayerNorm weight, LayerNorm bias
+    float* cbs = par + 3 * d;                // [L][r] basis copy when cb_smem
+    float* tile = cbs + (cb_smem ? ((L * r + 3) & ~3) : 0);    // [L][d] when STAGE
     const int b = blockIdx.x;
     const float* __restrict__ xb = x + (long long)b * L * d;
-    if (STAGE) {
+    if (STAGE)
         for (int i = threadIdx.x; i < L * d / 4; i += FT) cp_async16(tile + 4 * i, xb + 4 * i);
-        cp_async_wait_all();
-        __syncthreads();
+    for (int j = threadIdx.x; j < d; j += FT) {
+        const float sb = __ldg(sqrt_beta + j);
+        par[j] = sb * sb; par[d + j] = __ldg(gamma + j); par[2 * d + j] = __ldg(beta + j);
     }
+    if (cb_smem)
+        for (int i = threadIdx.x; i < L * r; i += FT) cbs[i] = __ldg(Cb + i);
+    if (STAGE) cp_async_wait_all();
+    __syncthreads();
     const float* src = STAGE ? tile : xb;
+    const float* cb = cb_smem ? cbs : Cb;
     const int LR = d >> 2, G = FT / LR, g = threadIdx.x / LR, c = 4 * (threadIdx.x - g * LR);
     const bool active = g < G;
     for (int r0 = 0; r0 < r; r0 += RCH) {
@@ -320,7 +328,7 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
                 const float4 xv = ld4(src + t * d + c);
 #pragma unroll
                 for (int q = 0; q < RCH; ++q)
-                    if (r0 + q < r) acc[q] = fma4(__ldg(Cb + t * r + r0 + q), xv, acc[q]);
+                    if (r0 + q < r) acc[q] = fma4(cb[t * r + r0 + q], xv, acc[q]);
             }
         fold_groups(coef, acc, r0, r, d, c, g, G, active);
     }
@@ -328,17 +336,24 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
     const int lane = threadIdx.x & 31;
     for (int t = threadIdx.x >> 5; t < L; t += FT / 32) {
         const long long row = (long long)b * L + t;
-        float4 v[NV];
+        float4 v[NV], low[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) low[i] = f4(0.f);
+        for (int q = 0; q < r; ++q) {
+            const float cq = cb[t * r + q];
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const int cc = 4 * (lane + 32 * i);
+                if (cc < d) low[i] = fma4(cq, ld4(coef + q * d + cc), low[i]);
+            }
+        }
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int cc = 4 * (lane + 32 * i);
             v[i] = f4(0.f);
             if (cc < d) {
-                float4 low = f4(0.f);
-                for (int q = 0; q < r; ++q) low = fma4(__ldg(Cb + t * r + q), ld4(coef + q * d + cc), low);
                 const float4 xv = ld4(src + t * d + cc);
-                const float4 sb = ldg4(sqrt_beta + cc);
-                const float4 u = low + (sb * sb) * (xv - low);
+                const float4 u = low[i] + ld4(par + cc) * (xv - low[i]);
                 const long long o = row * d + cc;
                 v[i] = u * mult4(dr, (unsigned long long)o) + xv;
                 st4(z_save + o, v[i]);
@@ -350,7 +365,7 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int cc = 4 * (lane + 32 * i);
-            if (cc < d) st4(dsp + row * d + cc, ldg4(gamma + cc) * (rstd * (v[i] - f4(mean))) + ldg4(beta + cc));
+            if (cc < d) st4(dsp + row * d + cc, ld4(par + d + cc) * (rstd * (v[i] - f4(mean))) + ld4(par + 2 * d + cc));
         }
     }
 }
@@ -361,23 +376,26 @@ template <bool STAGE>
 __global__ void __launch_bounds__(FT)
 filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                       const float* __restrict__ dz_f, float* __restrict__ dx, float* __restrict__ pbeta2, int L, int d, int r,
-                      Dropout dr) {
+                      int cb_smem, Dropout dr) {
     extern __shared__ __align__(16) float fsm[];
     float* coef_x = fsm;                         // [r][d]
     float* coef_g = fsm + (long long)r * d;      // [r][d]
     float* pb = coef_g + (long long)r * d;       // [d]
-    float* tile = pb + d;                        // [L][d] when STAGE
+    float* cbs = pb + d;                         // [L][r] basis copy when cb_smem
+    float* tile = cbs + (cb_smem ? ((L * r + 3) & ~3) : 0);     // [L][d] when STAGE
     const int b = blockIdx.x;
     const long long base = (long long)b * L * d;
     const float* __restrict__ xb = x + base;
     const float* __restrict__ gb = dz_f + base;
     float* __restrict__ dxb = dx + base;
-    if (STAGE) {
+    if (STAGE)
         for (int i = threadIdx.x; i < L * d / 4; i += FT) cp_async16(tile + 4 * i, xb + 4 * i);
-        cp_async_wait_all();
-        __syncthreads();
-    }
+    if (cb_smem)
+        for (int i = threadIdx.x; i < L * r; i += FT) cbs[i] = __ldg(Cb + i);
+    if (STAGE) cp_async_wait_all();
+    __syncthreads();
     const float* src = STAGE ? tile : xb;
+    const float* cb = cb_smem ? cbs : Cb;
     const int LR = d >> 2, G = FT / LR, g = threadIdx.x / LR, c = 4 * (threadIdx.x - g * LR);
     const bool active = g < G;
     float4 b2 = f4(0.f);
@@ -394,9 +412,9 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
 #pragma unroll
                 for (int q = 0; q < RCH; ++q)
                     if (r0 + q < r) {
-                        const float cb = __ldg(Cb + t * r + r0 + q);
-                        ax[q] = fma4(cb, xv, ax[q]);
-                        ag[q] = fma4(cb, gv, ag[q]);
+                        const float cq = cb[t * r + r0 + q];
+                        ax[q] = fma4(cq, xv, ax[q]);
+                        ag[q] = fma4(cq, gv, ag[q]);
                     }
             }
         fold_groups(coef_x, ax, r0, r, d, c, g, G, active);
@@ -407,9 +425,9 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
         for (int t = g; t < L; t += G) {
             float4 low = f4(0.f), fg = f4(0.f);
             for (int q = 0; q < r; ++q) {
-                const float cb = __ldg(Cb + t * r + q);
-                low = fma4(cb, ld4(coef_x + q * d + c), low);
-                fg = fma4(cb, ld4(coef_g + q * d + c), fg);
+                const float cq = cb[t * r + q];
+                low = fma4(cq, ld4(coef_x + q * d + c), low);
+                fg = fma4(cq, ld4(coef_g + q * d + c), fg);
             }
             const int o = t * d + c;
             const float4 dzf = ld4(gb + o);
@@ -474,9 +492,13 @@ static int set_smem(K kernel, size_t smem) {
     return 0;
 }
 
+constexpr size_t CB_SMEM_LIMIT = 16 * 1024;     // the basis [L][r] rides in shared memory when it is this small (C1-C3: 4 KB)
+
 int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta, float* dsp,
                       float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st) {
-    const size_t coef = (size_t)r * d * sizeof(float), tile = (size_t)L * d * sizeof(float);
+    const size_t cbb = (((size_t)L * r + 3) & ~(size_t)3) * sizeof(float);
+    const int cb_smem = cbb <= CB_SMEM_LIMIT;
+    const size_t coef = ((size_t)r * d + 3 * d) * sizeof(float) + (cb_smem ? cbb : 0), tile = (size_t)L * d * sizeof(float);
     BSA_REQUIRE(coef <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);
     const bool stage = coef + tile <= STAGE_SMEM_LIMIT;
     const size_t smem = coef + (stage ? tile : 0);
@@ -484,10 +506,10 @@ int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, c
     BSA_DISPATCH_NV(d, {
         if (stage) {
             if ((rc = set_smem(filter_ln_fwd_vec_kernel<NV, true>, smem))) return rc;
-            filter_ln_fwd_vec_kernel<NV, true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, dr);
+            filter_ln_fwd_vec_kernel<NV, true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr);
         } else {
             if ((rc = set_smem(filter_ln_fwd_vec_kernel<NV, false>, smem))) return rc;
-            filter_ln_fwd_vec_kernel<NV, false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, dr);
+            filter_ln_fwd_vec_kernel<NV, false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr);
         }
     });
     BSA_LAUNCH_CHECK();
@@ -496,17 +518,19 @@ int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, c
 
 int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2, int B,
                    int L, int d, int r, Dropout dr, cudaStream_t st) {
-    const size_t coef = (2 * (size_t)r * d + d) * sizeof(float), tile = (size_t)L * d * sizeof(float);
+    const size_t cbb = (((size_t)L * r + 3) & ~(size_t)3) * sizeof(float);
+    const int cb_smem = cbb <= CB_SMEM_LIMIT;
+    const size_t coef = (2 * (size_t)r * d + d) * sizeof(float) + (cb_smem ? cbb : 0), tile = (size_t)L * d * sizeof(float);
     BSA_REQUIRE(coef <= 200 * 1024, "filter bwd: basis rank %d x hidden %d does not fit shared memory", r, d);
     const bool stage = coef + tile <= STAGE_SMEM_LIMIT;
     const size_t smem = coef + (stage ? tile : 0);
     int rc = 0;
     if (stage) {
         if ((rc = set_smem(filter_bwd_vec_kernel<true>, smem))) return rc;
-        filter_bwd_vec_kernel<true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, dr);
+        filter_bwd_vec_kernel<true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, cb_smem, dr);
     } else {
         if ((rc = set_smem(filter_bwd_vec_kernel<false>, smem))) return rc;
-        filter_bwd_vec_kernel<false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, dr);
+        filter_bwd_vec_kernel<false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, cb_smem, dr);
     }
     BSA_LAUNCH_CHECK();
     return 0;

@@ -59,8 +59,9 @@ class GradExchange:
         in the backward pass; its all-reduce is issued at once on the communicator's stream and runs under the whole
         encoder backward;
       * ``finish``: the 41 small gradients are one flat buffer -> one all-reduce; the sparse gather part is exchanged as
-        rows (ids [B*L] + dz [B*L,d] per rank, 105 MB at C3) and scatter-added on every rank in the same (rank, row)
-        order, so all replicas hold bit-identical gradients.
+        rows — only the positions that hold an item (padding rows carry no gradient), ids + dz rows padded to the largest
+        per-rank count — and scatter-added on every rank in the same (rank, row) order, so all replicas hold
+        bit-identical gradients.
     ``scale`` = 1/world is folded into d_loss (no averaging pass over the gradients).  Ranks must hold equally sized local
     batches (the mean of local means is then the global mean of ``CrossEntropyLoss``, bsarec.py:35)."""
 
@@ -68,7 +69,7 @@ class GradExchange:
         self.group = group
         self.world = dist.get_world_size(group)
         self.scale = 1.0 / self.world
-        self._w_dense = self._w_ids = self._ids_all = None
+        self._w_dense = self._w_counts = self._keep = self._ids_kept = self._counts = None
         self.collectives = 0
 
     def _issue(self, fn, *a):
@@ -76,25 +77,41 @@ class GradExchange:
         return fn(*a, group=self.group, async_op=True)
 
     def begin(self, ids: torch.Tensor):
-        """ids int64 [B,L] of this rank's batch: gathered early, it is not on anybody's critical path."""
-        flat = ids.reshape(-1).contiguous()
-        self._ids_all = torch.empty(self.world * flat.numel(), dtype=flat.dtype, device=flat.device)
-        self._w_ids = self._issue(dist.all_gather_into_tensor, self._ids_all, flat)
+        """ids int64 [B,L] of this rank's batch.  Padding positions (id 0) carry no item-table gradient
+        (``padding_idx=0``, _abstract_model.py:10), so only the rows of real items are exchanged: their positions and the
+        per-rank counts are worked out here, early, off everybody's critical path."""
+        flat = ids.reshape(-1)
+        self._keep = (flat != 0).nonzero(as_tuple=False).view(-1)
+        self._ids_kept = flat[self._keep]
+        self._counts = torch.empty(self.world, dtype=torch.int64, device=flat.device)
+        mine = torch.tensor([self._keep.numel()], dtype=torch.int64, device=flat.device)
+        self._w_counts = self._issue(dist.all_gather_into_tensor, self._counts, mine)
 
     def start_dense(self, g_item: torch.Tensor):
         self._w_dense = self._issue(dist.all_reduce, g_item.view(-1), dist.ReduceOp.SUM)
 
     def finish(self, small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable):
         w_small = self._issue(dist.all_reduce, small_flat, dist.ReduceOp.SUM) if small_flat.numel() else None
-        dz_all = torch.empty(self.world * dz.shape[0], dz.shape[1], dtype=dz.dtype, device=dz.device)
-        w_rows = self._issue(dist.all_gather_into_tensor, dz_all, dz.contiguous())
-        self._w_ids.wait()
-        w_rows.wait()
+        self._w_counts.wait()
+        cap = int(self._counts.max().item())          # rows per rank on the wire (ranks pad up to the largest count)
+        if cap > 0:
+            n = self._keep.numel()
+            ids_c = torch.zeros(cap, dtype=torch.int64, device=dz.device)          # padded slots keep id 0: skipped below
+            dz_c = torch.zeros(cap, dz.shape[1], dtype=dz.dtype, device=dz.device)
+            ids_c[:n] = self._ids_kept
+            torch.index_select(dz, 0, self._keep, out=dz_c[:n])
+            ids_all = torch.empty(self.world * cap, dtype=torch.int64, device=dz.device)
+            dz_all = torch.empty(self.world * cap, dz.shape[1], dtype=dz.dtype, device=dz.device)
+            w_ids = self._issue(dist.all_gather_into_tensor, ids_all, ids_c)
+            w_rows = self._issue(dist.all_gather_into_tensor, dz_all, dz_c)
+            w_ids.wait()
+            w_rows.wait()
         self._w_dense.wait()
-        scatter_fn(self._ids_all, dz_all, g_item)
+        if cap > 0:
+            scatter_fn(ids_all, dz_all, g_item)       # (rank, row) order, the same on every rank -> identical bits
         if w_small is not None:
             w_small.wait()
-        self._w_dense = self._w_ids = self._ids_all = None
+        self._w_dense = self._w_counts = self._keep = self._ids_kept = self._counts = None
 
 
 def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shard_offset: int,

@@ -111,7 +111,9 @@ def _exchange_worker(rank, world, out_dir):
     per_rank = []
     for r in range(world):
         g = torch.Generator().manual_seed(100 + r)
-        ids = torch.randint(0, N, (5, 8), generator=g)            # zeros included: padding rows are skipped
+        ids = torch.randint(1, N, (5, 8), generator=g)
+        for b in range(5):                                        # left padding of a different length per row and rank:
+            ids[b, :int(torch.randint(0, 9, (1,), generator=g))] = 0      # ranks exchange different numbers of rows
         per_rank.append(dict(ids=ids, dense=torch.randn(N, d, generator=g), dz=torch.randn(M, d, generator=g),
                              small=torch.randn(77, generator=g)))
     me = {k: v.clone() for k, v in per_rank[rank].items()}
@@ -128,7 +130,7 @@ def _exchange_worker(rank, world, out_dir):
         small += per_rank[r]["small"].double()
     assert (me["dense"].double() - want).abs().max() < 1e-5
     assert (me["small"].double() - small).abs().max() < 1e-5
-    assert ex.collectives == 4                                    # ids, dense, small, rows
+    assert ex.collectives == 5                                    # counts, dense, small, ids, rows
     torch.save([me["dense"], me["small"]], os.path.join(out_dir, f"x{rank}.pt"))
 
 

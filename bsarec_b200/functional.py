@@ -334,6 +334,8 @@ class FusedLoss(torch.autograd.Function):
         xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
         s = xs[-1]
         loss, lse, ce_ws = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
+        if exchange is not None:
+            exchange.prepare(ids)                            # row counts for the sparse exchange reach the host during the forward
         ctx.hyper, ctx.names, ctx.state, ctx.ce_impl, ctx.exchange = hyper, names, state, ce_impl, exchange
         ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
         ctx.save_for_backward(*tensors)
@@ -351,7 +353,6 @@ class FusedLoss(torch.autograd.Function):
         gE = grads["item_embeddings.weight"]
         if ex is not None:
             d_loss = d_loss * ex.scale                       # sum over ranks == mean over the global batch
-            ex.begin(state.ids)
         ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, gE, ctx.ce_impl, ctx.ce_ws)
         ctx.ce_ws = None
         if ex is not None:

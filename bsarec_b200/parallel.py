@@ -69,37 +69,47 @@ class GradExchange:
         self.group = group
         self.world = dist.get_world_size(group)
         self.scale = 1.0 / self.world
-        self._w_dense = self._w_counts = self._keep = self._ids_kept = self._counts = None
+        self._w_dense = self._order = self._flat_ids = self._cap_host = self._cap_event = None
         self.collectives = 0
 
     def _issue(self, fn, *a):
         self.collectives += 1
         return fn(*a, group=self.group, async_op=True)
 
-    def begin(self, ids: torch.Tensor):
-        """ids int64 [B,L] of this rank's batch.  Padding positions (id 0) carry no item-table gradient
-        (``padding_idx=0``, _abstract_model.py:10), so only the rows of real items are exchanged: their positions and the
-        per-rank counts are worked out here, early, off everybody's critical path."""
+    def prepare(self, ids: torch.Tensor):
+        """Call at the start of the forward pass with this rank's ids int64 [B,L].  Padding positions (id 0) carry no
+        item-table gradient (``padding_idx=0``, _abstract_model.py:10), so only the rows of real items are exchanged.
+        The number of such rows per rank (max over ranks = rows on the wire) travels to the host asynchronously here, a
+        whole forward pass before ``finish`` needs it: no stream synchronisation on the backward's critical path."""
         flat = ids.reshape(-1)
-        self._keep = (flat != 0).nonzero(as_tuple=False).view(-1)
-        self._ids_kept = flat[self._keep]
-        self._counts = torch.empty(self.world, dtype=torch.int64, device=flat.device)
-        mine = torch.tensor([self._keep.numel()], dtype=torch.int64, device=flat.device)
-        self._w_counts = self._issue(dist.all_gather_into_tensor, self._counts, mine)
+        pad = flat == 0
+        # positions of the real items first, in their original order (stable), without a host round trip
+        self._order = torch.argsort(pad.to(torch.int8), stable=True)
+        self._flat_ids = flat
+        counts = torch.empty(self.world, dtype=torch.int64, device=flat.device)
+        mine = (flat.numel() - pad.sum()).reshape(1)
+        dist.all_gather_into_tensor(counts, mine, group=self.group)
+        self.collectives += 1
+        if flat.is_cuda:
+            self._cap_host = torch.empty(1, dtype=torch.int64, pin_memory=True)
+            self._cap_host.copy_(counts.max().reshape(1), non_blocking=True)
+            self._cap_event = torch.cuda.Event()
+            self._cap_event.record()
+        else:
+            self._cap_host, self._cap_event = counts.max().reshape(1), None
 
     def start_dense(self, g_item: torch.Tensor):
         self._w_dense = self._issue(dist.all_reduce, g_item.view(-1), dist.ReduceOp.SUM)
 
     def finish(self, small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable):
         w_small = self._issue(dist.all_reduce, small_flat, dist.ReduceOp.SUM) if small_flat.numel() else None
-        self._w_counts.wait()
-        cap = int(self._counts.max().item())          # rows per rank on the wire (ranks pad up to the largest count)
+        if self._cap_event is not None:
+            self._cap_event.synchronize()             # recorded during the forward pass: long since complete
+        cap = int(self._cap_host[0])                  # rows per rank on the wire (the largest per-rank count)
         if cap > 0:
-            n = self._keep.numel()
-            ids_c = torch.zeros(cap, dtype=torch.int64, device=dz.device)          # padded slots keep id 0: skipped below
-            dz_c = torch.zeros(cap, dz.shape[1], dtype=dz.dtype, device=dz.device)
-            ids_c[:n] = self._ids_kept
-            torch.index_select(dz, 0, self._keep, out=dz_c[:n])
+            idx = self._order[:cap]                   # this rank's real rows, then (if it has fewer) padding rows: id 0, skipped
+            ids_c = self._flat_ids[idx]
+            dz_c = torch.index_select(dz, 0, idx)
             ids_all = torch.empty(self.world * cap, dtype=torch.int64, device=dz.device)
             dz_all = torch.empty(self.world * cap, dz.shape[1], dtype=dz.dtype, device=dz.device)
             w_ids = self._issue(dist.all_gather_into_tensor, ids_all, ids_c)
@@ -111,7 +121,7 @@ class GradExchange:
             scatter_fn(ids_all, dz_all, g_item)       # (rank, row) order, the same on every rank -> identical bits
         if w_small is not None:
             w_small.wait()
-        self._w_dense = self._w_counts = self._keep = self._ids_kept = self._counts = None
+        self._w_dense = self._order = self._flat_ids = self._cap_host = self._cap_event = None
 
 
 def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shard_offset: int,

@@ -100,6 +100,7 @@ SIGNATURES = {
     "bsa_gemm_workspace_bytes": (_SZ, [_I, _I, _I, _I64, _I64, _I, _I]),
     "bsa_gemm": (_I, [_I, _I, _I, _I, _VP, _I64, _I, _VP, _I64, _I, _VP, _I64, _VP, C.c_float, _I, _VP, _SZ, _VP]),
     "bsa_adam_step": (_I, [_VP, _VP, _VP, _VP, _I64] + [C.c_float] * 5 + [_I64, _VP]),
+    "bsa_adam_step_multi": (_I, [_I, _VP, _VP, _VP, _VP, _VP] + [C.c_float] * 5 + [_I64, _VP]),
     "bsa_build_batch": (_I, [_I, _VP, _VP, _VP, _I64, _VP, _I, _I, _VP, _VP, _VP, _VP]),
     "bsa_hit_rank_hist": (_I, [_VP, _VP, _I64, _I, _VP, _VP]),
     "bsa_gather_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),

@@ -36,7 +36,69 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     if (t < n) adam1(p[t], g[t], m[t], v[t], a);
 }
 
+// Up to ADAM_MULTI tensors in one launch (blockIdx.y = tensor): the 41 small parameters of the model are one launch
+// instead of 41.  Pointers travel by value in the kernel parameter block.
+constexpr int ADAM_MULTI = 48;
+struct AdamMulti {
+    float* p[ADAM_MULTI]; const float* g[ADAM_MULTI]; float* m[ADAM_MULTI]; float* v[ADAM_MULTI];
+    long long n[ADAM_MULTI];
+};
+
+__global__ void __launch_bounds__(256)
+adam_multi_kernel(const __grid_constant__ AdamMulti t, AdamP a) {
+    const int k = blockIdx.y;
+    float* __restrict__ p = t.p[k];
+    const float* __restrict__ g = t.g[k];
+    float* __restrict__ m = t.m[k];
+    float* __restrict__ v = t.v[k];
+    const long long n = t.n[k], n4 = n >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 P = reinterpret_cast<float4*>(p)[i];
+        const float4 G = __ldcs(reinterpret_cast<const float4*>(g) + i);
+        float4 Mv = reinterpret_cast<float4*>(m)[i];
+        float4 V = reinterpret_cast<float4*>(v)[i];
+        adam1(P.x, G.x, Mv.x, V.x, a); adam1(P.y, G.y, Mv.y, V.y, a); adam1(P.z, G.z, Mv.z, V.z, a); adam1(P.w, G.w, Mv.w, V.w, a);
+        reinterpret_cast<float4*>(p)[i] = P;
+        reinterpret_cast<float4*>(m)[i] = Mv;
+        reinterpret_cast<float4*>(v)[i] = V;
+    }
+    const long long e = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < n) adam1(p[e], g[e], m[e], v[e], a);
+}
+
 }  // namespace
+
+int adam_step_multi(int count, float* const* p, const float* const* g, float* const* m, float* const* v, const long long* n,
+                    float lr, float beta1, float beta2, float eps, float wd, long long step, cudaStream_t st) {
+    BSA_REQUIRE(step >= 1, "bsa_adam_step_multi: step counts from 1");
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    const AdamP a{(float)((double)lr / bc1), (float)sqrt(bc2), beta1, beta2, eps, wd};
+    for (int base = 0; base < count; base += ADAM_MULTI) {
+        AdamMulti t;
+        const int c = count - base < ADAM_MULTI ? count - base : ADAM_MULTI;
+        long long nmax = 0;
+        double bytes = 0;
+        for (int i = 0; i < ADAM_MULTI; ++i) {
+            const int j = base + (i < c ? i : 0);
+            t.p[i] = p[j]; t.g[i] = g[j]; t.m[i] = m[j]; t.v[i] = v[j]; t.n[i] = i < c ? n[j] : 0;
+            if (i < c) {
+                BSA_REQUIRE(((reinterpret_cast<uintptr_t>(p[j]) | reinterpret_cast<uintptr_t>(g[j]) | reinterpret_cast<uintptr_t>(m[j]) |
+                              reinterpret_cast<uintptr_t>(v[j])) & 15) == 0, "bsa_adam_step_multi: tensors must be 16-byte aligned");
+                if (n[j] > nmax) nmax = n[j];
+                bytes += 28.0 * (double)n[j];
+            }
+        }
+        if (nmax == 0) continue;
+        long long bx = (nmax / 4 + 255) / 256;
+        if (bx > 64) bx = 64;
+        if (bx < 1) bx = 1;
+        ProfScope prof(PROF_ADAM, st, bytes);
+        adam_multi_kernel<<<dim3((unsigned)bx, (unsigned)c), 256, 0, st>>>(t, a);
+        BSA_LAUNCH_CHECK();
+    }
+    return 0;
+}
 
 int adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps,
               float wd, long long step, cudaStream_t st) {
@@ -62,4 +124,14 @@ extern "C" int bsa_adam_step(float* param, const float* grad, float* exp_avg, fl
     using namespace bsa;
     BSA_REQUIRE(n == 0 || (param && grad && exp_avg && exp_avg_sq), "bsa_adam_step: null argument");
     return adam_step(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, (cudaStream_t)stream);
+}
+
+extern "C" int bsa_adam_step_multi(int count, float* const* params_host, const float* const* grads_host, float* const* exp_avg_host,
+                                   float* const* exp_avg_sq_host, const int64_t* sizes_host, float lr, float beta1, float beta2,
+                                   float eps, float weight_decay, int64_t step, void* stream) {
+    using namespace bsa;
+    if (count == 0) return 0;
+    BSA_REQUIRE(count > 0 && params_host && grads_host && exp_avg_host && exp_avg_sq_host && sizes_host, "bsa_adam_step_multi: null argument");
+    return adam_step_multi(count, params_host, grads_host, exp_avg_host, exp_avg_sq_host, (const long long*)sizes_host, lr, beta1, beta2,
+                           eps, weight_decay, step, (cudaStream_t)stream);
 }

@@ -1,10 +1,13 @@
 """``FusedAdam``: drop-in for the ``torch.optim.Adam`` the reference's Trainer builds (``trainers.py:27-28``) with the
-update done by one sm_100a kernel pass per tensor (``bsa_adam_step``) instead of ~13 foreach passes.
+update done by one sm_100a kernel pass per large tensor (``bsa_adam_step``) and one launch for all the small ones
+(``bsa_adam_step_multi``) instead of ~13 foreach passes.
 
 Same constructor arguments, same update rule (no amsgrad / maximize), ``state_dict`` entries named as torch's
 (``step``, ``exp_avg``, ``exp_avg_sq``).  CUDA fp32 parameters only — there is no CPU path.
 """
 from __future__ import annotations
+
+import ctypes as C
 
 import torch
 
@@ -13,6 +16,8 @@ from ._cabi import check
 
 
 class FusedAdam(torch.optim.Optimizer):
+    SMALL = 1 << 20      # tensors up to this many elements are updated together, one launch per 48 of them
+
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
         if lr < 0.0 or eps < 0.0 or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0 or weight_decay < 0.0:
             raise ValueError("invalid Adam hyper-parameter")
@@ -27,6 +32,7 @@ class FusedAdam(torch.optim.Optimizer):
         lib = _cabi.load()
         for group in self.param_groups:
             b1, b2 = group["betas"]
+            small = {}                      # (device index, step) -> tensors updated together by one bsa_adam_step_multi
             for p in group["params"]:
                 if p.grad is None:
                     continue
@@ -43,10 +49,25 @@ class FusedAdam(torch.optim.Optimizer):
                 g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
                 if not p.is_contiguous():
                     raise RuntimeError("FusedAdam: parameters must be contiguous")
+                if p.numel() <= self.SMALL:
+                    small.setdefault((p.device.index, st["step"]), []).append((p, g, st))
+                    continue
                 with torch.cuda.device(p.device):
                     check(lib.bsa_adam_step(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(),
                                             p.numel(), float(group["lr"]), float(b1), float(b2), float(group["eps"]),
                                             float(group["weight_decay"]), st["step"],
                                             torch.cuda.current_stream().cuda_stream), "bsa_adam_step")
                 torch.autograd.graph.increment_version(p)     # written through a raw pointer: tell autograd / caches
+            for (dev, step), items in small.items():
+                n = len(items)
+                arr = lambda f: (C.c_void_p * n)(*[f(it) for it in items])
+                sizes = (C.c_int64 * n)(*[it[0].numel() for it in items])
+                with torch.cuda.device(dev):
+                    check(lib.bsa_adam_step_multi(n, arr(lambda it: it[0].data_ptr()), arr(lambda it: it[1].data_ptr()),
+                                                  arr(lambda it: it[2]["exp_avg"].data_ptr()),
+                                                  arr(lambda it: it[2]["exp_avg_sq"].data_ptr()), sizes, float(group["lr"]),
+                                                  float(b1), float(b2), float(group["eps"]), float(group["weight_decay"]), step,
+                                                  torch.cuda.current_stream().cuda_stream), "bsa_adam_step_multi")
+                for it in items:
+                    torch.autograd.graph.increment_version(it[0])
         return loss

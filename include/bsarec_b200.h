@@ -247,6 +247,11 @@ int bsa_gemm(int impl, int M, int N, int K, const float* A, int64_t lda, int a_m
  * ---------------------------------------------------------------------------------------------- */
 int bsa_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
                   float beta2, float eps, float weight_decay, int64_t step, void* stream);
+/* The same update for `count` tensors in one launch per 48 tensors (the model's 41 small parameters).  The five
+ * arrays are HOST arrays of length count holding DEVICE pointers / element counts; all tensors share `step`. */
+int bsa_adam_step_multi(int count, float* const* params_host, const float* const* grads_host, float* const* exp_avg_host,
+                        float* const* exp_avg_sq_host, const int64_t* sizes_host, float lr, float beta1, float beta2, float eps,
+                        float weight_decay, int64_t step, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Either side of the model call: integer kernels, bit-exact.

@@ -156,10 +156,12 @@ def test_sharded_topk_merge_equals_unsharded(cuda_device):
 
 @pytest.mark.parametrize("wd", [0.0, 0.01])
 def test_fused_adam_matches_torch_adam(wd, cuda_device):
-    """bsa_adam_step vs torch.optim.Adam (trainers.py:27-28) over several steps, ragged sizes included."""
+    """bsa_adam_step (large tensors) and bsa_adam_step_multi (all the small ones in one launch, > 48 of them -> two
+    launches) vs torch.optim.Adam (trainers.py:27-28) over several steps, ragged sizes included."""
     from bsarec_b200 import FusedAdam
     g = torch.Generator().manual_seed(3)
-    shapes = [(1001, 64), (7,), (64, 64), (1, 1, 33)]
+    shapes = [(1001, 64), (7,), (64, 64), (1, 1, 33), (4200, 257)] + [(3 + i, 5) for i in range(50)]
+    assert 4200 * 257 > FusedAdam.SMALL >= 1001 * 64
     ref = [torch.randn(s, generator=g).to(cuda_device).requires_grad_(True) for s in shapes]
     got = [r.detach().clone().requires_grad_(True) for r in ref]
     o_ref = torch.optim.Adam(ref, lr=1e-3, betas=(0.9, 0.999), weight_decay=wd)

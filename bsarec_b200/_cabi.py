@@ -21,7 +21,7 @@ class EmbedDesc(C.Structure):
 class BlockDesc(C.Structure):
     _fields_ = [("B", C.c_int), ("L", C.c_int), ("d", C.c_int), ("H", C.c_int), ("kept_bins", C.c_int),
                 ("alpha", C.c_float), ("p_hidden", C.c_float), ("p_attn", C.c_float), ("training", C.c_int),
-                ("seed", C.c_uint64), ("layer", C.c_int)]
+                ("seed", C.c_uint64), ("layer", C.c_int), ("inference", C.c_int)]
 
 
 BLOCK_FIELDS = ["sqrt_beta", "f_ln_w", "f_ln_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo",

@@ -77,6 +77,7 @@ struct Lin {               // where the linears run: tcgen05 3xTF32 engine (defa
     bool umma;
     float *w_hi, *w_lo;    // [4d*d] scratch for the weight's split pair
     float* partial; size_t partial_bytes;      // split-K slabs (weight gradients)
+    bool inference = false;                    // forward only: nothing is kept for a backward pass
 };
 
 long long lin_ws_floats(long long d) { return 2 * (4 * d * d + 256) + (long long)(umma_gemm_partial_bytes((int)(4 * d), (int)d) / 4); }
@@ -116,8 +117,9 @@ int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, f
     if (ln.umma) {
         int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
         if (rc) return rc;
-        return umma_gemm_ps((int)M, N, K, a.hi, a.lo, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out, N, bias, act, aux_out,
-                            nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
+        // when the epilogue emits the result's split pair, that pair is all the tcgen05 path reads afterwards: no fp32 copy
+        return umma_gemm_ps((int)M, N, K, a.hi, a.lo, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out_hi ? nullptr : out, N, bias,
+                            act, ln.inference ? nullptr : aux_out, nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
     }
     GemmP p;
     p.A = a.x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
@@ -200,7 +202,11 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const int r = filter_rank(L, c.kept_bins);
     int rc;
     // filter branch
-    if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, s.z_f, s.mean_f, s.rstd_f, B, L, d, r, dr_f, st))) return rc;
+    // inference (bsa_block_desc::inference): the LayerNorm inputs / statistics and the GELU pre-activation are not written
+    const bool inf = c.inference != 0;
+    lin.inference = inf && lin.umma;
+    if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, inf ? nullptr : s.z_f, inf ? nullptr : s.mean_f,
+                            inf ? nullptr : s.rstd_f, B, L, d, r, dr_f, st))) return rc;
     // attention branch
     Act ax, actx, ay, ah;
     if ((rc = split_act(lin, x, s.x_hi, s.x_lo, M * d, ax, st))) return rc;        // one split feeds q, k, v (and dW in backward)
@@ -232,14 +238,16 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = split_act(lin, s.ctx, s.ctx_hi, s.ctx_lo, M * d, actx, st))) return rc;
     if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
-    if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, s.z_a, s.mean_a, s.rstd_a, dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
+    if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, inf ? nullptr : s.z_a, inf ? nullptr : s.mean_a, inf ? nullptr : s.rstd_a,
+                              dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
     // feed-forward
     if ((rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
     // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
     if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, s.h_hi, s.h_lo, st))) return rc;
     ah.x = s.h_act; ah.hi = s.h_hi; ah.lo = s.h_lo;
     if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
-    if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, M, d, dr_o, st))) return rc;
+    if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, inf ? nullptr : s.z_o, inf ? nullptr : s.mean_o,
+                              inf ? nullptr : s.rstd_o, nullptr, 0.f, 0.f, M, d, dr_o, st))) return rc;
     return 0;
 }
 

@@ -276,12 +276,12 @@ filter_ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ Cb, 
                 const float u = low + (sb * sb) * (xv - low);
                 const long long o = row * d + j;
                 v[i] = u * dropout_mult(dr, (unsigned long long)o) + xv;
-                z_save[o] = v[i];
+                if (z_save) z_save[o] = v[i];
             }
         }
         float mean, rstd;
         row_stats<VPL>(v, d, lane, mean, rstd);
-        if (lane == 0) { mean_o[row] = mean; rstd_o[row] = rstd; }
+        if (lane == 0 && mean_o) { mean_o[row] = mean; rstd_o[row] = rstd; }
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
             const int j = lane + 32 * i;
@@ -646,7 +646,7 @@ int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const
                   float* dsp, float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr,
                   cudaStream_t st) {
     if (B == 0) return 0;
-    ProfScope prof(PROF_FILTER_FWD, st, 4.0 * B * (double)L * d * 3.0);             // x read; z_save, dsp written
+    ProfScope prof(PROF_FILTER_FWD, st, 4.0 * B * (double)L * d * (z_save ? 3.0 : 2.0));   // x read; z_save, dsp written
     if (vec_ok(d, x, sqrt_beta, gamma, beta, dsp, z_save)) return filter_ln_fwd_vec(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, B, L, d, r, dr, st);
     const size_t smem = (size_t)r * d * sizeof(float);
     BSA_REQUIRE(smem <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);

@@ -356,12 +356,12 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
                 const float4 u = low[i] + ld4(par + cc) * (xv - low[i]);
                 const long long o = row * d + cc;
                 v[i] = u * mult4(dr, (unsigned long long)o) + xv;
-                st4(z_save + o, v[i]);
+                if (z_save) st4(z_save + o, v[i]);
             }
         }
         float mean, rstd;
         row_stats4<NV>(v, d, lane, mean, rstd);
-        if (lane == 0) { mean_o[row] = mean; rstd_o[row] = rstd; }
+        if (lane == 0 && mean_o) { mean_o[row] = mean; rstd_o[row] = rstd; }
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int cc = 4 * (lane + 32 * i);

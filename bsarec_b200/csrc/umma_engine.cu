@@ -103,14 +103,14 @@ struct EpiStore {
                 x.x = p.alpha * x.x + bias4.x; x.y = p.alpha * x.y + bias4.y; x.z = p.alpha * x.z + bias4.z; x.w = p.alpha * x.w + bias4.w;
                 if (full) {
                     if (p.act == 1) {
-                        *reinterpret_cast<float4*>(p.aux_out + off) = x;
+                        if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = x;
                         x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
                     } else if (p.act == 2) {
                         const float4 a = *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= gelu_erf_grad(a.x); x.y *= gelu_erf_grad(a.y); x.z *= gelu_erf_grad(a.z); x.w *= gelu_erf_grad(a.w);
                     }
                     if (p.accumulate) { const float4 o = *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
-                    *reinterpret_cast<float4*>(base + off) = x;
+                    if (base) *reinterpret_cast<float4*>(base + off) = x;      // C == nullptr: only the split pair leaves
                     if (p.out_hi) {
                         float4 h, l;
                         split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y); split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
@@ -121,10 +121,10 @@ struct EpiStore {
                     float xs[4] = {x.x, x.y, x.z, x.w};
                     for (int e = 0; e < 4; ++e) if (col + e < g.N) {
                         float y = xs[e];
-                        if (p.act == 1) { p.aux_out[off + e] = y; y = gelu_erf(y); }
+                        if (p.act == 1) { if (p.aux_out) p.aux_out[off + e] = y; y = gelu_erf(y); }
                         else if (p.act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
                         if (p.accumulate) y += base[off + e];
-                        base[off + e] = y;
+                        if (base) base[off + e] = y;
                         if (p.out_hi) { float h, l; split_tf32(y, h, l); p.out_hi[off + e] = h; p.out_lo[off + e] = l; }
                     }
                 }
@@ -438,6 +438,8 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
                  const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
                  size_t partial_bytes, cudaStream_t st) {
     BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
+    BSA_REQUIRE(C || (out_hi && out_lo && !accumulate), "umma_gemm: C may be omitted only when the split pair is emitted");
+    if (!C) partial = nullptr;                        // no split-K without an fp32 destination
     int rc;
     Operand oa{a_hi, a_lo, a_rows, a_cols, lda, a_mn}, ob{b_hi, b_lo, b_rows, b_cols, ldb, b_mn};
     const int BN = N > 128 ? 256 : 128;

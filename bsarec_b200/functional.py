@@ -60,9 +60,10 @@ def filter_basis(L: int, kept_bins: int, device) -> torch.Tensor:
     return _basis_cache[key]
 
 
-def _block_desc(h: Hyper, B: int, L: int, layer: int, training: bool, seed: int) -> BlockDesc:
+def _block_desc(h: Hyper, B: int, L: int, layer: int, training: bool, seed: int, inference: bool = False) -> BlockDesc:
     return BlockDesc(B=B, L=L, d=h.hidden_size, H=h.num_attention_heads, kept_bins=h.kept_bins, alpha=h.alpha,
-                     p_hidden=h.p_hidden, p_attn=h.p_attn, training=int(training), seed=seed, layer=layer)
+                     p_hidden=h.p_hidden, p_attn=h.p_attn, training=int(training), seed=seed, layer=layer,
+                     inference=int(inference))
 
 
 def _block_ptrs(tensors: Dict[str, torch.Tensor], layer: int) -> BlockPtrs:
@@ -111,7 +112,7 @@ def encoder_forward(h: Hyper, params: Dict[str, torch.Tensor], ids: torch.Tensor
         shared_saved = None
         last_row = False
         for l in range(h.num_hidden_layers):
-            bd = _block_desc(h, B, L, l, training, seed)
+            bd = _block_desc(h, B, L, l, training, seed, inference=not keep_for_backward)
             if last_only and LAST_ROW_PATH and l == h.num_hidden_layers - 1 and lib.bsa_block_last_supported(C.byref(bd)):
                 last_row = True
                 lsaved = torch.empty(lib.bsa_block_last_saved_bytes(C.byref(bd)), dtype=torch.uint8, device=dev)

@@ -110,6 +110,8 @@ typedef struct {
     int training;
     uint64_t seed;
     int layer;                 /* block index: selects the dropout sites 1+4*layer .. 4+4*layer */
+    int inference;             /* != 0: forward only — what exists only for bsa_block_bwd (LayerNorm inputs and statistics,
+                                  GELU pre-activation) is not written; `saved` is scratch and bsa_block_bwd must not follow */
 } bsa_block_desc;
 
 /* nn.Linear weights are [out,in] row-major, exactly the state_dict tensors */

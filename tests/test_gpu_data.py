@@ -136,3 +136,49 @@ def test_trainer_eval_branch_on_device_loader(cuda_device):
         ref += [oracle.recall_at_k(answers, tr.pred_list, k), oracle.ndcg_k(answers, tr.pred_list, k)]
     assert scores == pytest.approx(ref, abs=1e-12)
     assert "HR@5" in text and "NDCG@20" in text
+
+
+@pytest.mark.parametrize("fused_adam", [False, True])
+def test_train_loop_on_device_batches_tracks_oracle_adam(fused_adam, cuda_device):
+    """The reference's train branch (trainers.py:94-116) end to end: DeviceBatchLoader batches -> calculate_loss ->
+    zero_grad -> backward -> Adam.step for 6 steps (dropout 0, sequential sampler), against the oracle's CPU loop on
+    the batches the reference's own RecDataset yields.  Checks every step's loss and the final parameters."""
+    import oracle
+    from helpers import make_args, oracle_cfg, perturbed_params
+    from bsarec_b200 import BSARecModel, Trainer, FusedAdam, SequenceStore, DeviceBatchLoader
+    d, user_seq = _golden()
+    L, N = int(d["L"]), int(d["item_size"])
+    cfgkw = dict(item_size=N, hidden_size=64, max_seq_length=L, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.7)
+    cfg = oracle_cfg(cfgkw)
+    P = perturbed_params(cfg, 4)
+    args = make_args(cfgkw, batch_size=64)
+    model = BSARecModel(args)
+    model.load_state_dict({k: v.clone() for k, v in P.items()})
+    store = SequenceStore(user_seq, L, cuda_device)
+    loader = DeviceBatchLoader(store, "train", 64, shuffle=False)
+    tr = Trainer(model, loader, None, None, args, None)
+    if fused_adam:
+        tr.optim = FusedAdam(tr.model.parameters(), lr=args.lr, betas=(args.adam_beta1, args.adam_beta2), weight_decay=args.weight_decay)
+    losses = []
+    tr.model.train()
+    for step, batch in enumerate(loader):
+        if step == 6:
+            break
+        user_ids, input_ids, answers, neg, same = batch
+        loss = tr.model.calculate_loss(input_ids, answers, neg, same, user_ids)
+        tr.optim.zero_grad()
+        loss.backward()
+        tr.optim.step()
+        losses.append(loss.item())
+    ref = oracle.adam_train_step(P, cfg, lr=args.lr, betas=(args.adam_beta1, args.adam_beta2), weight_decay=args.weight_decay)
+    ref_losses = []
+    for step in range(6):
+        sl = slice(step * 64, (step + 1) * 64)
+        ref_losses.append(ref(torch.from_numpy(d["train_input_ids"][sl]), torch.from_numpy(d["train_answers"][sl])))
+    assert losses == pytest.approx(ref_losses, rel=2e-5)
+    got = {k: v.detach().cpu() for k, v in tr.model.state_dict().items()}
+    for k, v in ref.P.items():
+        if k.endswith("key.bias"):      # analytically zero gradient: Adam turns rounding noise into +-lr steps on both sides
+            continue
+        # Adam's first steps move every weight by ~lr regardless of gradient size: compare against the total update size
+        assert (got[k] - v.detach()).abs().max().item() < 0.05 * 6 * args.lr, k

@@ -485,8 +485,13 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
     const dim3 grid(B * H, (L + AT_ROWS - 1) / AT_ROWS);
     const float scale = 1.0f / sqrtf((float)DH);
     ProfScope prof(PROF_ATTN_BWD, st, 14.0 * B * H * (double)L * L * DH);     // S and dP twice, dQ, dK, dV
-    attn_bwd_kernel<DH, false><<<grid, AT_THREADS, smem, st>>>(q, k, v, ids, ctx, lse, dctx, dq, nullptr, delta, H, L, d, scale, dr);
-    BSA_LAUNCH_CHECK();
+    if (g_attn_bwd_umma && g_attn_fwd_umma && attn_umma_supported(L, d, H)) {   // query owner on tcgen05 (dQ, delta)
+        const int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, B, H, L, d, dr, st);
+        if (rc) return rc;
+    } else {
+        attn_bwd_kernel<DH, false><<<grid, AT_THREADS, smem, st>>>(q, k, v, ids, ctx, lse, dctx, dq, nullptr, delta, H, L, d, scale, dr);
+        BSA_LAUNCH_CHECK();
+    }
     attn_bwd_kernel<DH, true><<<grid, AT_THREADS, smem, st>>>(q, k, v, ids, ctx, lse, dctx, dk, dv, delta, H, L, d, scale, dr);
     BSA_LAUNCH_CHECK();
     return 0;
@@ -496,6 +501,8 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
 
 // 1: the forward goes to the tcgen05 kernel where its shape allows (BSA_ATTN_UMMA=0 keeps the mma.sync kernel)
 int g_attn_fwd_umma = [] { const char* e = getenv("BSA_ATTN_UMMA"); return e ? atoi(e) : 1; }();
+// 1: the query-owner half of the backward goes to the tcgen05 kernel too (BSA_ATTN_BWD_UMMA=0 keeps mma.sync)
+int g_attn_bwd_umma = [] { const char* e = getenv("BSA_ATTN_BWD_UMMA"); return e ? atoi(e) : 1; }();
 
 bool attn_fused_supported(int L, int d, int H) {
     if (H <= 0 || d % H != 0 || d % 4 != 0 || L < 1) return false;

@@ -21,6 +21,12 @@ bool attn_umma_supported(int L, int d, int H);
 int attn_fwd_umma(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
                   int L, int d, Dropout dr, cudaStream_t st);
 
+// Query-owner half of the backward on tcgen05 (dQ and delta; same shapes as attn_fwd_umma).  g_attn_bwd_umma = 1 makes
+// attn_bwd use it and keep only the key-owner launch (dK, dV) on the mma.sync kernel.
+extern int g_attn_bwd_umma;
+int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
+                    const float* dctx, float* dq, float* delta, int B, int H, int L, int d, Dropout dr, cudaStream_t st);
+
 // dq, dk, dv [B*L, d] are overwritten.  delta: [B, H, L] scratch (row sums of dctx * ctx).
 int attn_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
              const float* dctx, float* dq, float* dk, float* dv, float* delta, int B, int H, int L, int d, Dropout dr,

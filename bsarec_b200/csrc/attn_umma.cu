@@ -277,6 +277,269 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     }
 }
 
+
+// ============================================================================ backward, query owner (dQ and delta)
+// Same tile and the same TMEM plan as the forward: S = Q K^T -> columns [0,224); dPd = dO V^T -> columns [224,448); the
+// saved (row max, log row sum) turn S into P, dS = P o (dPd o M - delta) replaces S / dPd as a split pair, and
+// dQ = scale dS K is the third MMA (A from TMEM, B = the K rows as an MN-major operand) into columns [448,512).
+// Shared memory is reused phase by phase: region 1 holds Q then dO, region 2 holds K then V (K-major), region 3 the K
+// rows in the MN-major layout (its lo half moves into region 2 once the dPd MMA has retired).  dK / dV stay on the
+// key-owner mma.sync kernel (they need P^T / dS^T as A operands), which reads the delta written here.
+struct AttnBwdQParams {
+    CUtensorMap q, k, dout, vk, km;    // q, dout: box 32 x 128; k, vk: box 32 x NK/2; km: K rows, box 32 x 32 (atom32)
+    const long long* ids;
+    const float* ctx; const float* dctx; const float* lse;
+    float* dq; float* delta;
+    int H, L, d, NK;
+    float scale;
+    Dropout dr;
+};
+
+__global__ void __launch_bounds__(AU_THREADS, 1)
+attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
+    extern __shared__ __align__(1024) unsigned char au_smem_raw[];
+    unsigned char* smem = (unsigned char*)(((uintptr_t)au_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* bar_qk = (uint64_t*)(smem + AU_OFF_BAR);       // Q and K tiles landed
+    uint64_t* bar_km = bar_qk + 1;                           // K rows (MN-major layout) landed
+    uint64_t* s_full = bar_qk + 2;                           // S complete in TMEM
+    uint64_t* bar_dov = bar_qk + 3;                          // dO and V tiles landed
+    uint64_t* dp_full = bar_qk + 4;                          // dPd complete in TMEM
+    uint64_t* o_full = bar_qk + 5;                           // dQ complete in TMEM
+    uint32_t* tmem_ptr = (uint32_t*)(bar_qk + 6);
+    unsigned char* valid = smem + AU_OFF_BAR + 128;
+    int* s_first = (int*)(bar_qk + 7);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
+    const int qt = blockIdx.y;
+    const long long seq_base = (long long)b * p.L;
+    const int NK = p.NK, nkb = (NK + 31) / 32;
+    const int col0 = h * AU_DH;
+    const int k_kb_bytes = NK * 128;
+
+    if (warp == 0 && elect_one()) {
+        prefetch_tmap(&p.q); prefetch_tmap(&p.k); prefetch_tmap(&p.dout); prefetch_tmap(&p.vk); prefetch_tmap(&p.km);
+    }
+    if (warp == 1 && elect_one()) {
+        mbar_init(bar_qk, 1); mbar_init(bar_km, 1); mbar_init(s_full, 1); mbar_init(bar_dov, 1); mbar_init(dp_full, 1);
+        mbar_init(o_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    if (threadIdx.x == 0) *s_first = p.L;
+    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AU_THREADS)
+        valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t t_s = tmem_base, t_lo = tmem_base + AU_SCOLS, t_o = tmem_base + 2 * AU_SCOLS;
+
+    if (warp == 0 && elect_one()) {
+        mbar_expect_tx(bar_qk, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+            tma_load_2d(smem + AU_OFF_QHI + kb * 16384, &p.q, bar_qk, col0 + kb * 32, (int)(seq_base + qt * 128));
+            tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes, &p.k, bar_qk, col0 + kb * 32, (int)seq_base);
+            tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes + (NK / 2) * 128, &p.k, bar_qk, col0 + kb * 32, (int)seq_base + NK / 2);
+        }
+        mbar_expect_tx(bar_km, (uint32_t)(nkb * 8192));
+        for (int kb = 0; kb < nkb; ++kb) {
+            tma_load_2d(smem + AU_OFF_V + kb * 8192, &p.km, bar_km, col0, (int)seq_base + kb * 32);
+            tma_load_2d(smem + AU_OFF_V + kb * 8192 + 4096, &p.km, bar_km, col0 + 32, (int)seq_base + kb * 32);
+        }
+    }
+    mbar_wait(bar_qk, 0);
+    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AU_THREADS);
+    fence_proxy_async_smem();
+    __syncthreads();
+
+    const uint32_t idesc_s = idesc_tf32(128, NK, false, false);
+    if (warp == 1 && elect_one()) {
+        // ===================================================================== MMA 1: S = Q K^T
+        const uint32_t qh = smem_u32(smem + AU_OFF_QHI), ql = smem_u32(smem + AU_OFF_QLO);
+        const uint32_t kh = smem_u32(smem + AU_OFF_KHI), kl = smem_u32(smem + AU_OFF_KLO);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const uint64_t dah = smem_desc(qh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dal = smem_desc(ql + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dbh = smem_desc(kh + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dbl = smem_desc(kl + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                mma_tf32(t_s, dal, dbh, idesc_s, acc);
+                mma_tf32(t_s, dah, dbl, idesc_s, 1u);
+                mma_tf32(t_s, dah, dbh, idesc_s, 1u);
+                acc = 1u;
+            }
+        }
+        mma_commit(s_full);
+    }
+    __syncwarp();
+
+    // ---- per-thread row state while MMA 1 runs: thread = (query row, column half)
+    const int quarter = warp & 3, half = warp >> 2;
+    const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
+    const int i0 = qt * 128 + quarter * 32;
+    const int i = i0 + lane;
+    const bool row_ok = i < p.L;
+    const int nch = (NK + 31) / 32;
+    const int first_valid = *s_first;
+    const bool can_skip = i0 >= first_valid;
+    const unsigned long long pbase = ((unsigned long long)bh * p.L + (unsigned long long)(row_ok ? i : 0)) * p.L;
+    unsigned live = 0;
+    for (int c = half; c < nch; c += 2)
+        if (!(can_skip && (c * 32 > i0 + 31 || c * 32 + 31 < first_valid))) live |= 1u << c;
+    float2 ls = make_float2(0.f, 0.f);
+    float delta = 0.f;
+    if (row_ok) {
+        ls = *reinterpret_cast<const float2*>(p.lse + 2 * ((long long)bh * p.L + i));
+        const float4* o4 = reinterpret_cast<const float4*>(p.ctx + (seq_base + i) * p.d + col0);
+        const float4* g4 = reinterpret_cast<const float4*>(p.dctx + (seq_base + i) * p.d + col0);
+#pragma unroll
+        for (int e = 0; e < AU_DH / 4; ++e) {
+            const float4 a = o4[e], g = g4[e];
+            delta += a.x * g.x + a.y * g.y + a.z * g.z + a.w * g.w;
+        }
+        if (half == 0) p.delta[(long long)bh * p.L + i] = delta;
+    }
+
+    // ---- Q and K are dead once S is complete: dO and V take their place
+    mbar_wait(s_full, 0);
+    tc_fence_after();
+    if (warp == 0 && elect_one()) {
+        fence_proxy_async_smem();
+        mbar_expect_tx(bar_dov, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+            tma_load_2d(smem + AU_OFF_QHI + kb * 16384, &p.dout, bar_dov, col0 + kb * 32, (int)(seq_base + qt * 128));
+            tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes, &p.vk, bar_dov, col0 + kb * 32, (int)seq_base);
+            tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes + (NK / 2) * 128, &p.vk, bar_dov, col0 + kb * 32, (int)seq_base + NK / 2);
+        }
+    }
+    __syncwarp();
+    mbar_wait(bar_dov, 0);
+    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AU_THREADS);
+    fence_proxy_async_smem();
+    __syncthreads();
+
+    if (warp == 1 && elect_one()) {
+        // ===================================================================== MMA 2: dPd = dO V^T
+        const uint32_t gh = smem_u32(smem + AU_OFF_QHI), gl = smem_u32(smem + AU_OFF_QLO);
+        const uint32_t vh = smem_u32(smem + AU_OFF_KHI), vl = smem_u32(smem + AU_OFF_KLO);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const uint64_t dah = smem_desc(gh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dal = smem_desc(gl + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dbh = smem_desc(vh + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                const uint64_t dbl = smem_desc(vl + kb * k_kb_bytes + ks * 32, 16, 1024, LAYOUT_SW128);
+                mma_tf32(t_lo, dal, dbh, idesc_s, acc);
+                mma_tf32(t_lo, dah, dbl, idesc_s, 1u);
+                mma_tf32(t_lo, dah, dbh, idesc_s, 1u);
+                acc = 1u;
+            }
+        }
+        mma_commit(dp_full);
+    }
+    __syncwarp();
+    mbar_wait(bar_km, 0);
+    mbar_wait(dp_full, 0);
+    tc_fence_after();
+    // K rows (MN-major layout): hi in place, lo into region 2 (V is dead now)
+    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AU_THREADS);
+    fence_proxy_async_smem();
+
+    // ========================================================================= dS = P o (dPd o M - delta), back into TMEM
+    const bool fast_rng = (pbase & 3ull) == 0ull;
+#pragma unroll 1
+    for (int c = half; c < nch; c += 2) {
+        uint32_t hi[32], lo[32];
+        if (live >> c & 1) {
+            float vs[32], vd[32];
+            tmem_ld32(t_s + lane_base + c * 32, vs);
+            tmem_ld32(t_lo + lane_base + c * 32, vd);
+#pragma unroll
+            for (int g4 = 0; g4 < 8; ++g4) {
+                float mult[4];
+                const int j0 = c * 32 + g4 * 4;
+                if (fast_rng) dropout_mult4(p.dr, pbase + j0, mult);
+                else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(p.dr, pbase + j0 + e);
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int j = j0 + e;
+                    float ds = 0.f;
+                    if (row_ok && j < p.L) {
+                        const float sp = vs[g4 * 4 + e] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
+                        const float pr = expf((sp - ls.x) - ls.y);
+                        ds = pr * (vd[g4 * 4 + e] * mult[e] - delta);
+                    }
+                    float hh, lw;
+                    split_tf32_dev(ds, hh, lw);
+                    hi[g4 * 4 + e] = __float_as_uint(hh); lo[g4 * 4 + e] = __float_as_uint(lw);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) { hi[e] = 0u; lo[e] = 0u; }
+        }
+        tmem_st32(t_s + lane_base + c * 32, hi);
+        tmem_st32(t_lo + lane_base + c * 32, lo);
+    }
+    tmem_wait_st();
+    tc_fence_before();
+    __syncthreads();
+
+    if (warp == 1 && elect_one()) {
+        // ===================================================================== MMA 3: dQ = dS K
+        tc_fence_after();
+        const uint32_t idesc = idesc_tf32(128, AU_DH, false, true);
+        const uint32_t kh = smem_u32(smem + AU_OFF_V), kl = smem_u32(smem + AU_OFF_KHI);
+        uint32_t acc = 0;
+        for (int kstep = 0; kstep < NK / 8; ++kstep) {
+            const int kb = kstep >> 2, ks = kstep & 3;
+            const uint64_t dbh = smem_desc(kh + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint64_t dbl = smem_desc(kl + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint32_t col = (uint32_t)(kstep * 8);
+            mma_tf32_ts(t_o, t_lo + col, dbh, idesc, acc);
+            mma_tf32_ts(t_o, t_s + col, dbl, idesc, 1u);
+            mma_tf32_ts(t_o, t_s + col, dbh, idesc, 1u);
+            acc = 1u;
+        }
+        mma_commit(o_full);
+    }
+    __syncwarp();
+    mbar_wait(o_full, 0);
+    tc_fence_after();
+    {
+        float v[32];
+        tmem_ld32(t_o + lane_base + half * 32, v);
+        if (row_ok) {
+            float* dst = p.dq + (seq_base + i) * p.d + col0 + half * 32;
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                *reinterpret_cast<float4*>(dst + e * 4) =
+                    make_float4(v[4 * e] * p.scale, v[4 * e + 1] * p.scale, v[4 * e + 2] * p.scale, v[4 * e + 3] * p.scale);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 }  // namespace
 
 bool attn_umma_supported(int L, int d, int H) {
@@ -306,6 +569,34 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
     const dim3 grid(B * H, (L + 127) / 128);
     ProfScope prof(PROF_ATTN_FWD, st, 4.0 * B * H * (double)L * L * AU_DH);
     attn_fwd_umma_kernel<<<grid, AU_THREADS, AU_SMEM, st>>>(p);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
+                    const float* dctx, float* dq, float* delta, int B, int H, int L, int d, Dropout dr, cudaStream_t st) {
+    BSA_REQUIRE(attn_umma_supported(L, d, H), "attn_bwd_q_umma: unsupported shape (L=%d d=%d H=%d)", L, d, H);
+    if (B == 0) return 0;
+    static bool configured = false;
+    if (!configured) {
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_q_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
+        configured = true;
+    }
+    AttnBwdQParams p;
+    const int NK = (L + 15) / 16 * 16;
+    const long long rows = (long long)B * L;
+    int rc;
+    if ((rc = make_tmap_2d(&p.q, q, rows, d, d, 128, false))) return rc;
+    if ((rc = make_tmap_2d(&p.k, k, rows, d, d, NK / 2, false))) return rc;
+    if ((rc = make_tmap_2d(&p.dout, dctx, rows, d, d, 128, false))) return rc;
+    if ((rc = make_tmap_2d(&p.vk, v, rows, d, d, NK / 2, false))) return rc;
+    if ((rc = make_tmap_2d(&p.km, k, rows, d, d, 32, true))) return rc;
+    p.ids = ids; p.ctx = ctx; p.dctx = dctx; p.lse = lse; p.dq = dq; p.delta = delta;
+    p.H = H; p.L = L; p.d = d; p.NK = NK;
+    p.scale = 1.0f / sqrtf((float)AU_DH);
+    p.dr = dr;
+    const dim3 grid(B * H, (L + 127) / 128);
+    attn_bwd_q_umma_kernel<<<grid, AU_THREADS, AU_SMEM, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }

@@ -277,3 +277,41 @@ def test_tcgen05_attention_forward_matches_mma_sync_kernel(cuda_device):
     ref = oracle.encode({k: v.double() for k, v in P.items()}, ids, cfg, train=True, plan=oracle.DropoutPlan(4242), use_fft=False)
     for a, b in zip(outs[2], ref):
         assert rel_err(a, b) < TOL
+
+
+def test_tcgen05_attention_backward_query_owner_matches_mma_sync_kernel(cuda_device):
+    """dQ (and delta) from the tcgen05 query-owner backward vs the mma.sync kernels on the same inputs (L = 200, dh = 64,
+    both dropouts on, full-length, padded and all-padding rows): every gradient within 1e-5 of each other, and within the
+    parity bar of the oracle (same dropout masks)."""
+    from bsarec_b200 import _cabi, functional as Fn
+    lib = _cabi.load()
+    cfgkw = dict(item_size=400, hidden_size=128, max_seq_length=200, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.5)
+    cfg = oracle_cfg(cfgkw, 0.2, 0.4)
+    P = perturbed_params(cfg, 17)
+    old_last = Fn.LAST_ROW_PATH
+    Fn.LAST_ROW_PATH = False                                 # both layers run the full attention backward
+    ids, answers = synth_batch(29, 6, 200, 400)
+    ids[0, :] = torch.randint(1, 400, (200,))
+    grads, losses = {}, {}
+    for impl in (2, 3):
+        lib.bsa_set_attn_impl(impl)
+        try:
+            model = build_model(cfgkw, P, cuda_device, 0.2, 0.4).train()
+            model.set_dropout_seed(777)
+            loss = model.calculate_loss(ids.to(cuda_device), answers.to(cuda_device), None, None, None)
+            loss.backward()
+            losses[impl] = loss.item()
+            grads[impl] = {n: p.grad.detach().cpu() for n, p in model.named_parameters()}
+        finally:
+            lib.bsa_set_attn_impl(2)
+    Fn.LAST_ROW_PATH = old_last
+    assert abs(losses[2] - losses[3]) < 1e-5 * abs(losses[3])
+    for n in grads[2]:
+        if n.endswith("key.bias"):
+            assert (grads[2][n] - grads[3][n]).abs().max() < 1e-6
+        else:
+            assert rel_err(grads[2][n], grads[3][n]) < 1e-5, n
+    l_ref, g_ref = oracle.loss_and_grads(P, ids, answers, cfg, train=True, plan=oracle.DropoutPlan(777), use_fft=False)
+    for n, g in grads[2].items():
+        if not n.endswith("key.bias"):
+            assert rel_err(g, g_ref[n]) < TOL, n

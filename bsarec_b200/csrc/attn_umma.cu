@@ -25,7 +25,9 @@ namespace {
 constexpr int AU_DH = 64;                  // head size this kernel is built for
 constexpr int AU_NK_MAX = 208;             // keys per sequence (UMMA N, multiple of 16)
 constexpr int AU_SCOLS = 224;              // TMEM columns reserved for S / P_hi (7 chunks of 32)
-constexpr int AU_THREADS = 256;
+constexpr int AU_THREADS = 256;                // backward (query owner): 2 warps per TMEM lane quarter
+constexpr int AUF_PARTS = 4;                   // forward: 4 warps per TMEM lane quarter (its elementwise passes are latency-bound)
+constexpr int AUF_THREADS = 128 * AUF_PARTS;
 constexpr int AU_Q_BYTES = 128 * AU_DH * 4;                 // 32 KiB: 2 k-blocks x [128 rows x 128 B]
 constexpr int AU_K_BYTES = AU_NK_MAX * AU_DH * 4;           // 52 KiB: 2 k-blocks x [NK rows x 128 B]
 constexpr int AU_V_BYTES = 7 * 2 * 4096;                    // 56 KiB: 7 k-blocks x 2 column chunks x [32 rows x 128 B]
@@ -67,7 +69,7 @@ __device__ __forceinline__ void split_region(unsigned char* base, int bytes, int
     }
 }
 
-__global__ void __launch_bounds__(AU_THREADS, 1)
+__global__ void __launch_bounds__(AUF_THREADS, 1)
 attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     extern __shared__ __align__(1024) unsigned char au_smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)au_smem_raw + 1023) & ~(uintptr_t)1023);
@@ -78,7 +80,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     uint32_t* tmem_ptr = (uint32_t*)(bar_qk + 6);
     unsigned char* valid = smem + AU_OFF_BAR + 128;          // [AU_SCOLS + 32]: 1 = key j is an item, 0 = padding / j >= L
     int* s_first = (int*)(bar_qk + 7);                       // first position holding an item (L if none)
-    float* xch = (float*)(smem + AU_OFF_QHI);                // [2][2][128]: row max / row sum halves (Q is dead after MMA 1)
+    float* xch = (float*)(smem + AU_OFF_QHI);                // [2][AUF_PARTS][128]: row max / row sum parts (Q is dead after MMA 1)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
@@ -96,7 +98,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
     if (threadIdx.x == 0) *s_first = p.L;
-    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AU_THREADS)
+    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AUF_THREADS)
         valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
     tc_fence_before();
     __syncthreads();
@@ -122,8 +124,8 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     }
     // ---- Q, K: raw fp32 -> (hi, lo), all 8 warps
     mbar_wait(bar_qk, 0);
-    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AU_THREADS);
-    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
 
@@ -154,14 +156,14 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     mbar_wait(bar_v, 0);
     mbar_wait(s_full, 0);
     tc_fence_after();
-    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
 
-    // ========================================================================= softmax: thread = (query row, column half)
+    // ========================================================================= softmax: thread = (query row, column part)
     // Two warps share each TMEM lane quarter and take alternate 32-column chunks; row max and row sum are exchanged
     // through shared memory.  A chunk every pair of which is masked for rows that do have a permitted key contributes
     // exp(-10000 - max) == 0 exactly: it is not read, P = 0 is stored.
-    const int quarter = warp & 3, half = warp >> 2;
+    const int quarter = warp & 3, part = warp >> 2;        // 4 warps per TMEM lane quarter: chunks c = part, part + 4, ...
     const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
     const int i0 = qt * 128 + quarter * 32;
     const int i = i0 + lane;                                       // position in the sequence
@@ -171,11 +173,11 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     const bool can_skip = i0 >= first_valid;                       // every row of this warp has a permitted key
     const unsigned long long pbase = ((unsigned long long)bh * p.L + (unsigned long long)(row_ok ? i : 0)) * p.L;
     unsigned live = 0;
-    for (int c = half; c < nch; c += 2)
+    for (int c = part; c < nch; c += AUF_PARTS)
         if (!(can_skip && (c * 32 > i0 + 31 || c * 32 + 31 < first_valid))) live |= 1u << c;
     float m = -INFINITY;
 #pragma unroll 1
-    for (int c = half; c < nch; c += 2) {                          // sweep 1: row max of the masked, scaled scores
+    for (int c = part; c < nch; c += AUF_PARTS) {                  // sweep 1: row max of the masked, scaled scores
         if (!(live >> c & 1)) continue;
         float v[32];
         tmem_ld32(t_s + lane_base + c * 32, v);
@@ -186,13 +188,14 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
             if (j < p.L) m = fmaxf(m, s);
         }
     }
-    xch[half * 128 + quarter * 32 + lane] = m;
-    asm volatile("bar.sync %0, 64;" ::"r"(quarter + 1) : "memory");
-    m = fmaxf(m, xch[(half ^ 1) * 128 + quarter * 32 + lane]);
+    xch[part * 128 + quarter * 32 + lane] = m;
+    asm volatile("bar.sync %0, 128;" ::"r"(quarter + 1) : "memory");
+#pragma unroll
+    for (int q = 0; q < AUF_PARTS; ++q) m = fmaxf(m, xch[q * 128 + quarter * 32 + lane]);
     float l = 0.f;
     const bool fast_rng = (pbase & 3ull) == 0ull;
 #pragma unroll 1
-    for (int c = half; c < nch; c += 2) {                          // sweep 2: exp, sum, dropout, split, back into TMEM
+    for (int c = part; c < nch; c += AUF_PARTS) {                  // sweep 2: exp, sum, dropout, split, back into TMEM
         uint32_t hi[32], lo[32];
         if (live >> c & 1) {
             float v[32];
@@ -228,11 +231,13 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         tmem_st32(t_s + lane_base + c * 32, hi);
         tmem_st32(t_lo + lane_base + c * 32, lo);
     }
-    xch[256 + half * 128 + quarter * 32 + lane] = l;
+    xch[AUF_PARTS * 128 + part * 128 + quarter * 32 + lane] = l;
     tmem_wait_st();
     tc_fence_before();
     __syncthreads();                                               // P pair in TMEM, V pair in smem, row sums in xch
-    l += xch[256 + (half ^ 1) * 128 + quarter * 32 + lane];
+    l = 0.f;
+#pragma unroll
+    for (int q = 0; q < AUF_PARTS; ++q) l += xch[AUF_PARTS * 128 + q * 128 + quarter * 32 + lane];
 
     if (warp == 1 && elect_one()) {
         // ===================================================================== MMA 2: O = P V
@@ -253,10 +258,11 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         mma_commit(o_full);
     }
     __syncwarp();
-    // ========================================================================= epilogue: warp half h stores O columns [32h, 32h+32)
+    // ========================================================================= epilogue: parts 0 and 1 store O columns [32 part, 32 part + 32)
     mbar_wait(o_full, 0);
     tc_fence_after();
-    {
+    if (part < 2) {
+        const int half = part;
         const float inv = row_ok ? 1.0f / l : 0.f;
         float* dst = p.ctx + (seq_base + (row_ok ? i : 0)) * p.d + col0 + half * 32;
         float v[32];
@@ -568,7 +574,7 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
     p.dr = dr;
     const dim3 grid(B * H, (L + 127) / 128);
     ProfScope prof(PROF_ATTN_FWD, st, 4.0 * B * H * (double)L * L * AU_DH);
-    attn_fwd_umma_kernel<<<grid, AU_THREADS, AU_SMEM, st>>>(p);
+    attn_fwd_umma_kernel<<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }

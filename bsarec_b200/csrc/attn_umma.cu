@@ -25,8 +25,7 @@ namespace {
 constexpr int AU_DH = 64;                  // head size this kernel is built for
 constexpr int AU_NK_MAX = 208;             // keys per sequence (UMMA N, multiple of 16)
 constexpr int AU_SCOLS = 224;              // TMEM columns reserved for S / P_hi (7 chunks of 32)
-constexpr int AU_THREADS = 256;                // backward (query owner): 2 warps per TMEM lane quarter
-constexpr int AUF_PARTS = 4;                   // forward: 4 warps per TMEM lane quarter (its elementwise passes are latency-bound)
+constexpr int AUF_PARTS = 4;                   // 4 warps per TMEM lane quarter (the elementwise passes are latency-bound)
 constexpr int AUF_THREADS = 128 * AUF_PARTS;
 constexpr int AU_Q_BYTES = 128 * AU_DH * 4;                 // 32 KiB: 2 k-blocks x [128 rows x 128 B]
 constexpr int AU_K_BYTES = AU_NK_MAX * AU_DH * 4;           // 52 KiB: 2 k-blocks x [NK rows x 128 B]
@@ -301,7 +300,7 @@ struct AttnBwdQParams {
     Dropout dr;
 };
 
-__global__ void __launch_bounds__(AU_THREADS, 1)
+__global__ void __launch_bounds__(AUF_THREADS, 1)
 attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     extern __shared__ __align__(1024) unsigned char au_smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)au_smem_raw + 1023) & ~(uintptr_t)1023);
@@ -333,7 +332,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
     if (threadIdx.x == 0) *s_first = p.L;
-    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AU_THREADS)
+    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AUF_THREADS)
         valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
     tc_fence_before();
     __syncthreads();
@@ -358,8 +357,8 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
         }
     }
     mbar_wait(bar_qk, 0);
-    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AU_THREADS);
-    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
 
@@ -388,18 +387,18 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     __syncwarp();
 
     // ---- per-thread row state while MMA 1 runs: thread = (query row, column half)
-    const int quarter = warp & 3, half = warp >> 2;
+    const int quarter = warp & 3, part = warp >> 2;        // 4 warps per TMEM lane quarter, 16-column pieces c = part, part + 4, ...
     const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
     const int i0 = qt * 128 + quarter * 32;
     const int i = i0 + lane;
     const bool row_ok = i < p.L;
-    const int nch = (NK + 31) / 32;
+    const int nch = NK / 16;                                       // 16-column pieces (NK is a multiple of 16)
     const int first_valid = *s_first;
     const bool can_skip = i0 >= first_valid;
     const unsigned long long pbase = ((unsigned long long)bh * p.L + (unsigned long long)(row_ok ? i : 0)) * p.L;
     unsigned live = 0;
-    for (int c = half; c < nch; c += 2)
-        if (!(can_skip && (c * 32 > i0 + 31 || c * 32 + 31 < first_valid))) live |= 1u << c;
+    for (int c = part; c < nch; c += AUF_PARTS)
+        if (!(can_skip && (c * 16 > i0 + 31 || c * 16 + 15 < first_valid))) live |= 1u << c;
     float2 ls = make_float2(0.f, 0.f);
     float delta = 0.f;
     if (row_ok) {
@@ -411,7 +410,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
             const float4 a = o4[e], g = g4[e];
             delta += a.x * g.x + a.y * g.y + a.z * g.z + a.w * g.w;
         }
-        if (half == 0) p.delta[(long long)bh * p.L + i] = delta;
+        if (part == 0) p.delta[(long long)bh * p.L + i] = delta;
     }
 
     // ---- Q and K are dead once S is complete: dO and V take their place
@@ -429,8 +428,8 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     }
     __syncwarp();
     mbar_wait(bar_dov, 0);
-    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AU_THREADS);
-    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
 
@@ -460,22 +459,22 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     mbar_wait(dp_full, 0);
     tc_fence_after();
     // K rows (MN-major layout): hi in place, lo into region 2 (V is dead now)
-    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AU_THREADS);
+    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
 
     // ========================================================================= dS = P o (dPd o M - delta), back into TMEM
     const bool fast_rng = (pbase & 3ull) == 0ull;
 #pragma unroll 1
-    for (int c = half; c < nch; c += 2) {
-        uint32_t hi[32], lo[32];
+    for (int c = part; c < nch; c += AUF_PARTS) {
+        uint32_t hi[16], lo[16];
         if (live >> c & 1) {
-            float vs[32], vd[32];
-            tmem_ld32(t_s + lane_base + c * 32, vs);
-            tmem_ld32(t_lo + lane_base + c * 32, vd);
+            float vs[16], vd[16];
+            tmem_ld16(t_s + lane_base + c * 16, vs);
+            tmem_ld16(t_lo + lane_base + c * 16, vd);
 #pragma unroll
-            for (int g4 = 0; g4 < 8; ++g4) {
+            for (int g4 = 0; g4 < 4; ++g4) {
                 float mult[4];
-                const int j0 = c * 32 + g4 * 4;
+                const int j0 = c * 16 + g4 * 4;
                 if (fast_rng) dropout_mult4(p.dr, pbase + j0, mult);
                 else {
 #pragma unroll
@@ -497,10 +496,10 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
             }
         } else {
 #pragma unroll
-            for (int e = 0; e < 32; ++e) { hi[e] = 0u; lo[e] = 0u; }
+            for (int e = 0; e < 16; ++e) { hi[e] = 0u; lo[e] = 0u; }
         }
-        tmem_st32(t_s + lane_base + c * 32, hi);
-        tmem_st32(t_lo + lane_base + c * 32, lo);
+        tmem_st16(t_s + lane_base + c * 16, hi);
+        tmem_st16(t_lo + lane_base + c * 16, lo);
     }
     tmem_wait_st();
     tc_fence_before();
@@ -528,12 +527,12 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     mbar_wait(o_full, 0);
     tc_fence_after();
     {
-        float v[32];
-        tmem_ld32(t_o + lane_base + half * 32, v);
+        float v[16];
+        tmem_ld16(t_o + lane_base + part * 16, v);                 // part = 0..3 -> dQ columns [16 part, 16 part + 16)
         if (row_ok) {
-            float* dst = p.dq + (seq_base + i) * p.d + col0 + half * 32;
+            float* dst = p.dq + (seq_base + i) * p.d + col0 + part * 16;
 #pragma unroll
-            for (int e = 0; e < 8; ++e)
+            for (int e = 0; e < 4; ++e)
                 *reinterpret_cast<float4*>(dst + e * 4) =
                     make_float4(v[4 * e] * p.scale, v[4 * e + 1] * p.scale, v[4 * e + 2] * p.scale, v[4 * e + 3] * p.scale);
         }
@@ -602,7 +601,7 @@ int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long l
     p.scale = 1.0f / sqrtf((float)AU_DH);
     p.dr = dr;
     const dim3 grid(B * H, (L + 127) / 128);
-    attn_bwd_q_umma_kernel<<<grid, AU_THREADS, AU_SMEM, st>>>(p);
+    attn_bwd_q_umma_kernel<<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }

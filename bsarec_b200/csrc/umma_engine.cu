@@ -44,7 +44,8 @@ struct StoreParams {
     float* out_hi; float* out_lo;        // optional: also emit the result as a split-TF32 (hi, lo) pair [same ldc]
     int partial_accumulate;              // split-K partial slabs are running sums (added to, not overwritten)
 };
-template <int BN>
+// PRE: the epilogue reads global memory (GELU pre-activation and / or the running sum) and prefetches those reads.
+template <int BN, bool PRE = false>
 struct EpiStore {
     using Params = StoreParams;
     static constexpr int WARPS = 8;
@@ -65,6 +66,22 @@ struct EpiStore {
         const bool vec_ok = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
 #pragma unroll 1
         for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
+            // The epilogue's global reads (GELU pre-activation, running sum) are issued before the accumulator leaves
+            // TMEM: inside the store loop each one would wait out its full latency behind the previous row's stores.
+            const int col = n0 + c0 + c4 * 4;
+            const bool full = vec_ok && (col + 3 < g.N);
+            float4 aux[8], old[8];
+            const bool pre_aux = PRE && plain && full && p.act == 2, pre_old = PRE && plain && full && p.accumulate;
+            if (pre_aux || pre_old) {
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const long long row = row0 + it * 4 + sub;
+                    if (row < g.M) {
+                        if (pre_aux) aux[it] = __ldg(reinterpret_cast<const float4*>(p.aux_in + row * ld + col));
+                        if (pre_old) old[it] = *reinterpret_cast<const float4*>(base + row * ld + col);
+                    }
+                }
+            }
             float v[32];
             tmem_ld32(acc + c0, v);
             if (n0 + c0 >= g.N || row0 >= g.M) continue;         // warp-uniform
@@ -72,7 +89,6 @@ struct EpiStore {
             for (int j = 0; j < 8; ++j)
                 stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             __syncwarp();
-            const int col = n0 + c0 + c4 * 4;
             float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
             if (plain && p.bias) {
                 if (col + 3 < g.N) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
@@ -82,7 +98,6 @@ struct EpiStore {
                     if (col + 2 < g.N) bias4.z = __ldg(p.bias + col + 2);
                 }
             }
-            const bool full = vec_ok && (col + 3 < g.N);
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
                 const int r = it * 4 + sub;
@@ -106,10 +121,10 @@ struct EpiStore {
                         if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = x;
                         x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
                     } else if (p.act == 2) {
-                        const float4 a = *reinterpret_cast<const float4*>(p.aux_in + off);
+                        const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= gelu_erf_grad(a.x); x.y *= gelu_erf_grad(a.y); x.z *= gelu_erf_grad(a.z); x.w *= gelu_erf_grad(a.w);
                     }
-                    if (p.accumulate) { const float4 o = *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
+                    if (p.accumulate) { const float4 o = PRE ? old[it] : *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
                     if (base) *reinterpret_cast<float4*>(base + off) = x;      // C == nullptr: only the split pair leaves
                     if (p.out_hi) {
                         float4 h, l;
@@ -463,8 +478,11 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     const int grid = (int)(total < num_sms() ? total : num_sms());
     {
         ProfScope prof(PROF_LINEAR_UMMA, st, 2.0 * M * N * (double)K);
-        if (BN == 256) rc = launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
-        else rc = launch_major<128, 3, EpiStore<128>>(g, ep, a_mn, b_mn, grid, st);
+        const bool pre = act == 2 || accumulate;
+        if (BN == 256) rc = pre ? launch_major<256, 2, EpiStore<256, true>>(g, ep, a_mn, b_mn, grid, st)
+                                : launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
+        else rc = pre ? launch_major<128, 3, EpiStore<128, true>>(g, ep, a_mn, b_mn, grid, st)
+                      : launch_major<128, 3, EpiStore<128>>(g, ep, a_mn, b_mn, grid, st);
     }
     if (rc) return rc;
     if (g.splits > 1) {

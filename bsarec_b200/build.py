@@ -17,7 +17,8 @@ SOURCES = ["capi.cu", "gemm_simt.cu", "rowwise.cu", "block.cu", "ce.cu", "topk.c
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-I", INCLUDE,
-         "--expt-relaxed-constexpr", "--expt-extended-lambda", "-Xptxas", "-v"]
+         "--expt-relaxed-constexpr", "--expt-extended-lambda", "-Xptxas", "-v",
+         *os.environ.get("BSA_EXTRA_NVCC_FLAGS", "").split()]      # e.g. -DBSA_ATTN_STAMPS for profiles/attn_phases.py
 
 
 def _digest():

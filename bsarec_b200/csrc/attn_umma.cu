@@ -17,6 +17,13 @@
 #include "umma.cuh"
 
 namespace bsa {
+#ifdef BSA_ATTN_STAMPS
+// Phase-stamp instrumentation (profiling builds only): one mid-grid CTA records globaltimer at each phase boundary.
+__device__ unsigned long long g_attn_stamps[64];      // [q-tile][16 forward stamps, 16 backward stamps]
+#define BSA_STAMP(i) do { if (threadIdx.x == 0 && blockIdx.x == gridDim.x / 2 && blockIdx.y < 2) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_attn_stamps[blockIdx.y * 32 + (i)] = t_; } } while (0)
+#else
+#define BSA_STAMP(i) do {} while (0)
+#endif
 
 using namespace umma;
 
@@ -36,7 +43,8 @@ constexpr int AU_OFF_KHI = AU_OFF_QLO + AU_Q_BYTES;         // after MMA 1: V_lo
 constexpr int AU_OFF_KLO = AU_OFF_KHI + AU_K_BYTES;
 constexpr int AU_OFF_V = AU_OFF_KLO + AU_K_BYTES;
 constexpr int AU_OFF_BAR = AU_OFF_V + AU_V_BYTES;
-constexpr int AU_SMEM = 1024 + AU_OFF_BAR + 128 + 256;      // alignment slack + barriers + valid[]
+constexpr int AU_OFF_DELTA = AU_OFF_BAR + 128 + 256;         // backward: delta of the CTA's 128 query rows
+constexpr int AU_SMEM = 1024 + AU_OFF_DELTA + 512;           // alignment slack + barriers + valid[] + delta[]
 static_assert(AU_SMEM <= 232448, "attention tile does not fit shared memory");
 static_assert(AU_V_BYTES <= 2 * AU_K_BYTES, "V_lo must fit the retired K region");
 
@@ -89,25 +97,12 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     const int col0 = h * AU_DH;
     const int k_kb_bytes = NK * 128;                         // one 32-float k-block of the K operand
 
-    if (warp == 0 && elect_one()) { prefetch_tmap(&p.q); prefetch_tmap(&p.k); prefetch_tmap(&p.v); }
-    if (warp == 1 && elect_one()) {
+    BSA_STAMP(7);
+    // The operand loads are issued first: the ids reads and the TMEM allocation below run under their latency.
+    if (warp == 0 && elect_one()) {
         mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(s_full, 1);
         mbar_init(o_full, 1);
         fence_barrier_init();
-    }
-    if (warp == 2) tmem_alloc(tmem_ptr, 512);
-    if (threadIdx.x == 0) *s_first = p.L;
-    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AUF_THREADS)
-        valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
-    tc_fence_before();
-    __syncthreads();
-    if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);   // L <= 208 < blockDim
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
-    const uint32_t t_s = tmem_base, t_lo = tmem_base + AU_SCOLS, t_o = tmem_base + 2 * AU_SCOLS;
-
-    if (warp == 0 && elect_one()) {
         mbar_expect_tx(bar_qk, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
 #pragma unroll
         for (int kb = 0; kb < 2; ++kb) {
@@ -121,12 +116,27 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
             tma_load_2d(smem + AU_OFF_V + kb * 8192 + 4096, &p.v, bar_v, col0 + 32, (int)seq_base + kb * 32);
         }
     }
+    if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    if (threadIdx.x == 0) *s_first = p.L;
+    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AUF_THREADS)
+        valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);   // L <= 208 < blockDim
+    __syncthreads();
+    BSA_STAMP(0);
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t t_s = tmem_base, t_lo = tmem_base + AU_SCOLS, t_o = tmem_base + 2 * AU_SCOLS;
+
     // ---- Q, K: raw fp32 -> (hi, lo), all 8 warps
     mbar_wait(bar_qk, 0);
+    BSA_STAMP(1);
     split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
     split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
+    BSA_STAMP(2);
 
     if (warp == 1 && elect_one()) {
         // ===================================================================== MMA 1: S = Q K^T
@@ -154,6 +164,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     // ---- V: raw fp32 -> hi in place, lo into the K region once MMA 1 has retired
     mbar_wait(bar_v, 0);
     mbar_wait(s_full, 0);
+    BSA_STAMP(3);
     tc_fence_after();
     split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
@@ -234,6 +245,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     tmem_wait_st();
     tc_fence_before();
     __syncthreads();                                               // P pair in TMEM, V pair in smem, row sums in xch
+    BSA_STAMP(4);
     l = 0.f;
 #pragma unroll
     for (int q = 0; q < AUF_PARTS; ++q) l += xch[AUF_PARTS * 128 + q * 128 + quarter * 32 + lane];
@@ -259,6 +271,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     __syncwarp();
     // ========================================================================= epilogue: parts 0 and 1 store O columns [32 part, 32 part + 32)
     mbar_wait(o_full, 0);
+    BSA_STAMP(5);
     tc_fence_after();
     if (part < 2) {
         const int half = part;
@@ -276,6 +289,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     }
     tc_fence_before();
     __syncthreads();
+    BSA_STAMP(6);
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -322,27 +336,11 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     const int col0 = h * AU_DH;
     const int k_kb_bytes = NK * 128;
 
+    BSA_STAMP(31);
     if (warp == 0 && elect_one()) {
-        prefetch_tmap(&p.q); prefetch_tmap(&p.k); prefetch_tmap(&p.dout); prefetch_tmap(&p.vk); prefetch_tmap(&p.km);
-    }
-    if (warp == 1 && elect_one()) {
         mbar_init(bar_qk, 1); mbar_init(bar_km, 1); mbar_init(s_full, 1); mbar_init(bar_dov, 1); mbar_init(dp_full, 1);
         mbar_init(o_full, 1);
         fence_barrier_init();
-    }
-    if (warp == 2) tmem_alloc(tmem_ptr, 512);
-    if (threadIdx.x == 0) *s_first = p.L;
-    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AUF_THREADS)
-        valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
-    tc_fence_before();
-    __syncthreads();
-    if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
-    const uint32_t t_s = tmem_base, t_lo = tmem_base + AU_SCOLS, t_o = tmem_base + 2 * AU_SCOLS;
-
-    if (warp == 0 && elect_one()) {
         mbar_expect_tx(bar_qk, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
 #pragma unroll
         for (int kb = 0; kb < 2; ++kb) {
@@ -355,12 +353,28 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
             tma_load_2d(smem + AU_OFF_V + kb * 8192, &p.km, bar_km, col0, (int)seq_base + kb * 32);
             tma_load_2d(smem + AU_OFF_V + kb * 8192 + 4096, &p.km, bar_km, col0 + 32, (int)seq_base + kb * 32);
         }
+        prefetch_tmap(&p.dout); prefetch_tmap(&p.vk);
     }
+    if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    if (threadIdx.x == 0) *s_first = p.L;
+    for (int j = threadIdx.x; j < AU_SCOLS + 32; j += AUF_THREADS)
+        valid[j] = (j < p.L && p.ids[seq_base + j] > 0) ? 1 : 0;
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);
+    __syncthreads();
+    BSA_STAMP(16);
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t t_s = tmem_base, t_lo = tmem_base + AU_SCOLS, t_o = tmem_base + 2 * AU_SCOLS;
+
     mbar_wait(bar_qk, 0);
+    BSA_STAMP(17);
     split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
     split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
+    BSA_STAMP(18);
 
     const uint32_t idesc_s = idesc_tf32(128, NK, false, false);
     if (warp == 1 && elect_one()) {
@@ -400,21 +414,37 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     for (int c = part; c < nch; c += AUF_PARTS)
         if (!(can_skip && (c * 16 > i0 + 31 || c * 16 + 15 < first_valid))) live |= 1u << c;
     float2 ls = make_float2(0.f, 0.f);
-    float delta = 0.f;
-    if (row_ok) {
-        ls = *reinterpret_cast<const float2*>(p.lse + 2 * ((long long)bh * p.L + i));
-        const float4* o4 = reinterpret_cast<const float4*>(p.ctx + (seq_base + i) * p.d + col0);
-        const float4* g4 = reinterpret_cast<const float4*>(p.dctx + (seq_base + i) * p.d + col0);
+    if (row_ok) ls = *reinterpret_cast<const float2*>(p.lse + 2 * ((long long)bh * p.L + i));
+    {   // delta[row] = <ctx[row], dctx[row]> over the head's columns: half a warp per row (coalesced 256-byte rows),
+        // 8 rows per warp; a row-per-thread read of the two tensors costs 5 - 15 us of exposed latency per CTA
+        float* s_delta = reinterpret_cast<float*>(smem + AU_OFF_DELTA);
+        const int hl = lane >> 4, c4 = lane & 15;
+        float4 a[4], g[4];
 #pragma unroll
-        for (int e = 0; e < AU_DH / 4; ++e) {
-            const float4 a = o4[e], g = g4[e];
-            delta += a.x * g.x + a.y * g.y + a.z * g.z + a.w * g.w;
+        for (int it = 0; it < 4; ++it) {
+            const int ri = qt * 128 + warp * 8 + it * 2 + hl;
+            a[it] = g[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ri < p.L) {
+                a[it] = __ldg(reinterpret_cast<const float4*>(p.ctx + (seq_base + ri) * p.d + col0) + c4);
+                g[it] = __ldg(reinterpret_cast<const float4*>(p.dctx + (seq_base + ri) * p.d + col0) + c4);
+            }
         }
-        if (part == 0) p.delta[(long long)bh * p.L + i] = delta;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            float dsum = a[it].x * g[it].x + a[it].y * g[it].y + a[it].z * g[it].z + a[it].w * g[it].w;
+#pragma unroll
+            for (int o = 8; o >= 1; o >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, o);
+            const int r = warp * 8 + it * 2 + hl, ri = qt * 128 + r;
+            if (c4 == 0) {
+                s_delta[r] = dsum;
+                if (ri < p.L) p.delta[(long long)bh * p.L + ri] = dsum;
+            }
+        }
     }
 
     // ---- Q and K are dead once S is complete: dO and V take their place
     mbar_wait(s_full, 0);
+    BSA_STAMP(19);
     tc_fence_after();
     if (warp == 0 && elect_one()) {
         fence_proxy_async_smem();
@@ -428,10 +458,12 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     }
     __syncwarp();
     mbar_wait(bar_dov, 0);
+    BSA_STAMP(20);
     split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
     split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
+    BSA_STAMP(21);
 
     if (warp == 1 && elect_one()) {
         // ===================================================================== MMA 2: dPd = dO V^T
@@ -457,12 +489,14 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     __syncwarp();
     mbar_wait(bar_km, 0);
     mbar_wait(dp_full, 0);
+    BSA_STAMP(22);
     tc_fence_after();
     // K rows (MN-major layout): hi in place, lo into region 2 (V is dead now)
     split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
 
     // ========================================================================= dS = P o (dPd o M - delta), back into TMEM
+    const float delta = reinterpret_cast<const float*>(smem + AU_OFF_DELTA)[quarter * 32 + lane];
     const bool fast_rng = (pbase & 3ull) == 0ull;
 #pragma unroll 1
     for (int c = part; c < nch; c += AUF_PARTS) {
@@ -504,6 +538,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     tmem_wait_st();
     tc_fence_before();
     __syncthreads();
+    BSA_STAMP(23);
 
     if (warp == 1 && elect_one()) {
         // ===================================================================== MMA 3: dQ = dS K
@@ -525,6 +560,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     }
     __syncwarp();
     mbar_wait(o_full, 0);
+    BSA_STAMP(24);
     tc_fence_after();
     {
         float v[16];
@@ -539,6 +575,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     }
     tc_fence_before();
     __syncthreads();
+    BSA_STAMP(25);
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -607,3 +644,9 @@ int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long l
 }
 
 }  // namespace bsa
+
+#ifdef BSA_ATTN_STAMPS
+extern "C" __attribute__((visibility("default"))) int bsa_debug_attn_stamps(unsigned long long* out32) {
+    return (int)cudaMemcpyFromSymbol(out32, bsa::g_attn_stamps, sizeof(unsigned long long) * 64);
+}
+#endif

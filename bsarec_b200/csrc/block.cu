@@ -118,8 +118,9 @@ int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, f
         int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
         if (rc) return rc;
         // when the epilogue emits the result's split pair, that pair is all the tcgen05 path reads afterwards: no fp32 copy
+        if (ln.inference) { aux_out = nullptr; if (act == ACT_GELU_SAVE_GRAD) act = ACT_GELU_SAVE_PRE; }    // nothing kept: plain GELU
         return umma_gemm_ps((int)M, N, K, a.hi, a.lo, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out_hi ? nullptr : out, N, bias,
-                            act, ln.inference ? nullptr : aux_out, nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
+                            act, aux_out, nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
     }
     GemmP p;
     p.A = a.x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
@@ -243,7 +244,8 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     // feed-forward
     if ((rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
     // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
-    if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_PRE, s.h_pre, s.h_hi, s.h_lo, st))) return rc;
+    // (h_pre holds gelu'(pre-activation): the backward's dX epilogue multiplies by it instead of evaluating erf + exp again)
+    if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_GRAD, s.h_pre, s.h_hi, s.h_lo, st))) return rc;
     ah.x = s.h_act; ah.hi = s.h_hi; ah.lo = s.h_lo;
     if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, inf ? nullptr : s.z_o, inf ? nullptr : s.mean_o,
@@ -309,7 +311,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
     }
     if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, fuse_o ? nullptr : g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, dh_hi, dh_lo, st))) return rc;
+    if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st))) return rc;
     const Act adh{dh_, dh_hi, dh_lo};                                          // emitted split by the epilogue above
     if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy

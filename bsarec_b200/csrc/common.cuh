@@ -117,6 +117,13 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 
 __device__ __forceinline__ float gelu_erf(float x) { return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f)); }
+// gelu(x) and gelu'(x) from one erf: same expressions (and bits) as gelu_erf / gelu_erf_grad
+__device__ __forceinline__ float gelu_erf_both(float x, float& grad) {
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
+    grad = cdf + x * pdf;
+    return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+}
 __device__ __forceinline__ float gelu_erf_grad(float x) {
     const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
     const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);

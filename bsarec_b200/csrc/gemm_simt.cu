@@ -149,6 +149,8 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
             if (p.bias) v += __ldg(p.bias + gn);
             if (p.act == ACT_GELU_SAVE_PRE) { auxo[off] = v; v = gelu_erf(v); }
             else if (p.act == ACT_MUL_GELU_GRAD) v *= gelu_erf_grad(auxi[off]);
+            else if (p.act == ACT_GELU_SAVE_GRAD) { float gr; v = gelu_erf_both(v, gr); if (auxo) auxo[off] = gr; }
+            else if (p.act == ACT_MUL_AUX) v *= auxi[off];
             if (p.accumulate) v += C[off];
             C[off] = v;
         }

@@ -13,6 +13,8 @@ enum GemmAct : int {
     ACT_NONE = 0,
     ACT_GELU_SAVE_PRE = 1,    // aux_out = pre-activation, C = gelu(pre)
     ACT_MUL_GELU_GRAD = 2,    // C = value * gelu'(aux_in)
+    ACT_GELU_SAVE_GRAD = 3,   // aux_out = gelu'(pre-activation), C = gelu(pre): erf is evaluated once, in the forward
+    ACT_MUL_AUX = 4,          // C = value * aux_in (the derivative saved by ACT_GELU_SAVE_GRAD)
 };
 
 struct GemmP {

@@ -71,7 +71,7 @@ struct EpiStore {
             const int col = n0 + c0 + c4 * 4;
             const bool full = vec_ok && (col + 3 < g.N);
             float4 aux[8], old[8];
-            const bool pre_aux = PRE && plain && full && p.act == 2, pre_old = PRE && plain && full && p.accumulate;
+            const bool pre_aux = PRE && plain && full && (p.act == 2 || p.act == 4), pre_old = PRE && plain && full && p.accumulate;
             if (pre_aux || pre_old) {
 #pragma unroll
                 for (int it = 0; it < 8; ++it) {
@@ -123,6 +123,13 @@ struct EpiStore {
                     } else if (p.act == 2) {
                         const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= gelu_erf_grad(a.x); x.y *= gelu_erf_grad(a.y); x.z *= gelu_erf_grad(a.z); x.w *= gelu_erf_grad(a.w);
+                    } else if (p.act == 3) {
+                        float4 gr;
+                        x.x = gelu_erf_both(x.x, gr.x); x.y = gelu_erf_both(x.y, gr.y); x.z = gelu_erf_both(x.z, gr.z); x.w = gelu_erf_both(x.w, gr.w);
+                        if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = gr;
+                    } else if (p.act == 4) {
+                        const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
+                        x.x *= a.x; x.y *= a.y; x.z *= a.z; x.w *= a.w;
                     }
                     if (p.accumulate) { const float4 o = PRE ? old[it] : *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
                     if (base) *reinterpret_cast<float4*>(base + off) = x;      // C == nullptr: only the split pair leaves
@@ -138,6 +145,8 @@ struct EpiStore {
                         float y = xs[e];
                         if (p.act == 1) { if (p.aux_out) p.aux_out[off + e] = y; y = gelu_erf(y); }
                         else if (p.act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
+                        else if (p.act == 3) { float gr; y = gelu_erf_both(y, gr); if (p.aux_out) p.aux_out[off + e] = gr; }
+                        else if (p.act == 4) y *= p.aux_in[off + e];
                         if (p.accumulate) y += base[off + e];
                         if (base) base[off + e] = y;
                         if (p.out_hi) { float h, l; split_tf32(y, h, l); p.out_hi[off + e] = h; p.out_lo[off + e] = l; }
@@ -478,7 +487,7 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     const int grid = (int)(total < num_sms() ? total : num_sms());
     {
         ProfScope prof(PROF_LINEAR_UMMA, st, 2.0 * M * N * (double)K);
-        const bool pre = act == 2 || accumulate;
+        const bool pre = act == 2 || act == 4 || accumulate;
         if (BN == 256) rc = pre ? launch_major<256, 2, EpiStore<256, true>>(g, ep, a_mn, b_mn, grid, st)
                                 : launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
         else rc = pre ? launch_major<128, 3, EpiStore<128, true>>(g, ep, a_mn, b_mn, grid, st)

@@ -130,12 +130,13 @@ int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, f
 
 // dx [M, K] (+)= dy [M, N] @ W[N, K]              (nn.Linear input gradient)
 int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
-                     const float* aux_in, float* out_hi, float* out_lo, cudaStream_t st) {
+                     const float* aux_in, float* out_hi, float* out_lo, cudaStream_t st, float* colpart = nullptr) {
     if (ln.umma) {
         int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
         if (rc) return rc;
+        // colpart (tcgen05 path only): the epilogue also leaves column sums of dx per 32-row group, [4 * ceil(M / 128), K]
         return umma_gemm_ps((int)M, K, N, dy.hi, dy.lo, M, N, N, false, ln.w_hi, ln.w_lo, N, K, K, true, dx, K, nullptr, act, nullptr,
-                            aux_in, 1.f, accumulate, out_hi, out_lo, nullptr, 0, st);
+                            aux_in, 1.f, accumulate, out_hi, out_lo, nullptr, 0, st, colpart);
     }
     GemmP p;
     p.A = dy.x; p.B = W; p.C = dx; p.M = (int)M; p.N = K; p.K = N; p.lda = N; p.ldb = K; p.ldc = K;
@@ -311,9 +312,17 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
     }
     if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, fuse_o ? nullptr : g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st))) return rc;
-    const Act adh{dh_, dh_hi, dh_lo};                                          // emitted split by the epilogue above
-    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+    const Act adh{dh_, dh_hi, dh_lo};                                          // split pair emitted by the epilogue below
+    if (lin.umma) {
+        // dh leaves the GEMM only as its split pair (all dW1 / dX read) plus per-32-row column sums for db1: the fp32 copy
+        // and the pass that summed it are gone; the [M,4d] dh_ buffer holds the [M/32, 4d] partial sums instead
+        if ((rc = linear_bwd_input(lin, ag, w.w2, nullptr, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st, dh_))) return rc;
+        if ((rc = reduce_partials(dh_, 4 * (int)((M + 127) / 128), 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+    } else {
+        if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st))) return rc;
+        if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+    }
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)

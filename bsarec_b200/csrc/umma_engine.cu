@@ -43,9 +43,12 @@ struct StoreParams {
     int accumulate; float* partial;
     float* out_hi; float* out_lo;        // optional: also emit the result as a split-TF32 (hi, lo) pair [same ldc]
     int partial_accumulate;              // split-K partial slabs are running sums (added to, not overwritten)
+    float* colpart;                      // optional (PRE epilogue, N % 4 == 0): column sums of the stored values per 32-row
+                                         // group, [4 * m_tiles, N] -> reduce_partials gives the bias gradient
 };
 // PRE: the epilogue reads global memory (GELU pre-activation and / or the running sum) and prefetches those reads.
-template <int BN, bool PRE = false>
+// CS: it also leaves per-32-row-group column sums of what it stores (StoreParams::colpart).
+template <int BN, bool PRE = false, bool CS = false>
 struct EpiStore {
     using Params = StoreParams;
     static constexpr int WARPS = 8;
@@ -84,6 +87,10 @@ struct EpiStore {
             }
             float v[32];
             tmem_ld32(acc + c0, v);
+            float4 csum = make_float4(0.f, 0.f, 0.f, 0.f);
+            const bool want_cs = CS && plain && p.colpart != nullptr;
+            if (want_cs && row0 >= g.M && sub == 0 && full)      // a 32-row group past the last row still owns its partial row
+                *reinterpret_cast<float4*>(p.colpart + ((long long)tc.m * 4 + quarter) * g.N + col) = csum;
             if (n0 + c0 >= g.N || row0 >= g.M) continue;         // warp-uniform
 #pragma unroll
             for (int j = 0; j < 8; ++j)
@@ -132,6 +139,7 @@ struct EpiStore {
                         x.x *= a.x; x.y *= a.y; x.z *= a.z; x.w *= a.w;
                     }
                     if (p.accumulate) { const float4 o = PRE ? old[it] : *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
+                    if (want_cs) { csum.x += x.x; csum.y += x.y; csum.z += x.z; csum.w += x.w; }
                     if (base) *reinterpret_cast<float4*>(base + off) = x;      // C == nullptr: only the split pair leaves
                     if (p.out_hi) {
                         float4 h, l;
@@ -152,6 +160,14 @@ struct EpiStore {
                         if (p.out_hi) { float h, l; split_tf32(y, h, l); p.out_hi[off + e] = h; p.out_lo[off + e] = l; }
                     }
                 }
+            }
+            if (want_cs) {                                       // lanes c4, c4 + 8, c4 + 16, c4 + 24 hold the same 4 columns
+#pragma unroll
+                for (int o = 8; o <= 16; o <<= 1) {
+                    csum.x += __shfl_xor_sync(0xffffffffu, csum.x, o); csum.y += __shfl_xor_sync(0xffffffffu, csum.y, o);
+                    csum.z += __shfl_xor_sync(0xffffffffu, csum.z, o); csum.w += __shfl_xor_sync(0xffffffffu, csum.w, o);
+                }
+                if (sub == 0 && full) *reinterpret_cast<float4*>(p.colpart + ((long long)tc.m * 4 + quarter) * g.N + col) = csum;
             }
             __syncwarp();                                        // staging block is reused by the next chunk
         }
@@ -460,8 +476,10 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
                  const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
-                 size_t partial_bytes, cudaStream_t st) {
+                 size_t partial_bytes, cudaStream_t st, float* colpart) {
     BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
+    BSA_REQUIRE(!colpart || ((N & 3) == 0 && (ldc & 3) == 0), "umma_gemm: fused column sums need N %% 4 == 0");
+    if (colpart) partial = nullptr;                   // the column sums come from complete tiles
     BSA_REQUIRE(C || (out_hi && out_lo && !accumulate), "umma_gemm: C may be omitted only when the split pair is emitted");
     if (!C) partial = nullptr;                        // no split-K without an fp32 destination
     int rc;
@@ -478,7 +496,7 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     }
     GemmCore g;
     if ((rc = make_core(g, M, N, K, oa, ob, BN, SCHED_N_FASTEST, splits))) return rc;
-    StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr, out_hi, out_lo, 0};
+    StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr, out_hi, out_lo, 0, colpart};
     if (g.splits > 1) {
         BSA_REQUIRE((size_t)g.splits * M * N * 4 <= partial_bytes, "umma_gemm: workspace too small for split-K");
         ep.partial = partial;
@@ -487,11 +505,13 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     const int grid = (int)(total < num_sms() ? total : num_sms());
     {
         ProfScope prof(PROF_LINEAR_UMMA, st, 2.0 * M * N * (double)K);
-        const bool pre = act == 2 || act == 4 || accumulate;
-        if (BN == 256) rc = pre ? launch_major<256, 2, EpiStore<256, true>>(g, ep, a_mn, b_mn, grid, st)
-                                : launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
-        else rc = pre ? launch_major<128, 3, EpiStore<128, true>>(g, ep, a_mn, b_mn, grid, st)
-                      : launch_major<128, 3, EpiStore<128>>(g, ep, a_mn, b_mn, grid, st);
+        const bool pre = act == 2 || act == 4 || accumulate || colpart;
+        if (BN == 256) rc = colpart ? launch_major<256, 2, EpiStore<256, true, true>>(g, ep, a_mn, b_mn, grid, st)
+                            : pre   ? launch_major<256, 2, EpiStore<256, true>>(g, ep, a_mn, b_mn, grid, st)
+                                    : launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
+        else rc = colpart ? launch_major<128, 3, EpiStore<128, true, true>>(g, ep, a_mn, b_mn, grid, st)
+                  : pre   ? launch_major<128, 3, EpiStore<128, true>>(g, ep, a_mn, b_mn, grid, st)
+                          : launch_major<128, 3, EpiStore<128>>(g, ep, a_mn, b_mn, grid, st);
     }
     if (rc) return rc;
     if (g.splits > 1) {

@@ -32,6 +32,6 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
                  const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
-                 size_t partial_bytes, cudaStream_t st);
+                 size_t partial_bytes, cudaStream_t st, float* colpart = nullptr);
 
 }  // namespace bsa

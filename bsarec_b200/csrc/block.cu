@@ -391,8 +391,16 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         float* dws3[3] = {g.wq, g.wk, g.wv};
         float* dbs3[3] = {g.bq, g.bk, g.bv};
         for (int i = 0; i < 3; ++i) {
-            if ((rc = split_act(lin, grads3[i], g_hi, g_lo, M * d, ag, st))) return rc;
-            if ((rc = linear_bwd_weight(lin, ag, ax, dws3[i], dbs3[i], M, d, d, part_sk, part_cs, st))) return rc;
+            if (lin.umma && umma_split_colsum_ok(d, grads3[i], g_hi, g_lo) && umma_split_colsum_rows(M) <= colsum_partial_rows(M)) {
+                // the operand split of dq / dk / dv also sums their columns: no separate pass for the bias gradients
+                ag = Act{grads3[i], g_hi, g_lo};
+                if ((rc = umma_split_colsum(grads3[i], g_hi, g_lo, M, d, part_cs, st))) return rc;
+                if ((rc = reduce_partials(part_cs, umma_split_colsum_rows(M), d, dbs3[i], nullptr, 1.f, 0, st))) return rc;
+                if ((rc = linear_bwd_weight(lin, ag, ax, dws3[i], nullptr, M, d, d, part_sk, part_cs, st))) return rc;
+            } else {
+                if ((rc = split_act(lin, grads3[i], g_hi, g_lo, M * d, ag, st))) return rc;
+                if ((rc = linear_bwd_weight(lin, ag, ax, dws3[i], dbs3[i], M, d, d, part_sk, part_cs, st))) return rc;
+            }
             if ((rc = linear_bwd_input(lin, ag, ws3[i], dx, M, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
         }
     }

@@ -32,6 +32,37 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
     if (t < n) split_tf32(x[t], hi[t], lo[t]);
 }
 
+// split + column sums of a [M, N] activation gradient in one pass (N / 4 threads per row, 128 rows per block):
+// part[blockIdx.x][N] = sum over the block's rows, reduced afterwards by reduce_partials -> the bias gradient
+constexpr int SPLIT_CS_ROWS = 128;
+__global__ void __launch_bounds__(256)
+split_colsum_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, long long M, int N,
+                    float* __restrict__ part) {
+    __shared__ float4 red[256];
+    const int tpr = N >> 2, groups = 256 / tpr;               // threads per row, rows in flight
+    const int c4 = threadIdx.x % tpr, rg = threadIdx.x / tpr;
+    const long long r0 = (long long)blockIdx.x * SPLIT_CS_ROWS;
+    float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int r = rg; r < SPLIT_CS_ROWS; r += groups) {
+        const long long row = r0 + r;
+        if (row >= M) break;
+        const long long i = row * tpr + c4;
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        reinterpret_cast<float4*>(hi)[i] = h;
+        reinterpret_cast<float4*>(lo)[i] = l;
+        cs.x += v.x; cs.y += v.y; cs.z += v.z; cs.w += v.w;
+    }
+    red[threadIdx.x] = cs;
+    __syncthreads();
+    if (rg == 0) {
+        for (int g2 = 1; g2 < groups; ++g2) { const float4 o = red[g2 * tpr + c4]; cs.x += o.x; cs.y += o.y; cs.z += o.z; cs.w += o.w; }
+        reinterpret_cast<float4*>(part + (long long)blockIdx.x * N)[c4] = cs;
+    }
+}
+
 // ============================================================================ epilogues
 // ---- plain store: C = alpha*acc (+bias) (act) (+C)   or raw split-K partials
 // Eight epilogue warps: warp e drains TMEM lane quarter e % 4 (32 accumulator rows) and column half e / 4 of the
@@ -468,6 +499,21 @@ size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, in
 }
 
 int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st) { return do_split(x, hi, lo, n, st); }
+
+bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* lo) {
+    const int tpr = N >> 2;
+    return (N & 3) == 0 && tpr >= 1 && tpr <= 256 && 256 % tpr == 0 &&
+           ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(hi) | reinterpret_cast<uintptr_t>(lo)) & 15) == 0;
+}
+int umma_split_colsum_rows(long long M) { return (int)((M + SPLIT_CS_ROWS - 1) / SPLIT_CS_ROWS); }
+// part: [umma_split_colsum_rows(M), N]
+int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st) {
+    BSA_REQUIRE(umma_split_colsum_ok(N, x, hi, lo), "umma_split_colsum: unsupported width %d or alignment", N);
+    if (M == 0) return 0;
+    split_colsum_kernel<<<umma_split_colsum_rows(M), 256, 0, st>>>(x, hi, lo, M, N, part);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
 
 size_t umma_gemm_partial_bytes(int M, int N) { return al((size_t)64 * M * N * 4) + 1024; }
 

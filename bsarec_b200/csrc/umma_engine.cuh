@@ -28,6 +28,11 @@ int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a
 // epilogue and reused by several GEMMs); out_hi/out_lo (optional) also receive the result as a split pair.
 int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st);
 size_t umma_gemm_partial_bytes(int M, int N);
+// One pass: split x [M, N] into (hi, lo) and leave per-128-row column sums in part [umma_split_colsum_rows(M), N]
+// (reduce_partials turns them into the bias gradient of the linear whose output gradient x is).
+bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* lo);
+int umma_split_colsum_rows(long long M);
+int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st);
 int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long long a_rows, long long a_cols,
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,

@@ -158,14 +158,14 @@ struct EpiStore {
                     if (p.act == 1) {
                         if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = x;
                         x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
-                    } else if (p.act == 2) {
+                    } else if (PRE && p.act == 2) {      // activations 2 - 4 are dispatched to the PRE instantiation only
                         const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= gelu_erf_grad(a.x); x.y *= gelu_erf_grad(a.y); x.z *= gelu_erf_grad(a.z); x.w *= gelu_erf_grad(a.w);
-                    } else if (p.act == 3) {
+                    } else if (PRE && p.act == 3) {
                         float4 gr;
                         x.x = gelu_erf_both(x.x, gr.x); x.y = gelu_erf_both(x.y, gr.y); x.z = gelu_erf_both(x.z, gr.z); x.w = gelu_erf_both(x.w, gr.w);
                         if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = gr;
-                    } else if (p.act == 4) {
+                    } else if (PRE && p.act == 4) {
                         const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= a.x; x.y *= a.y; x.z *= a.z; x.w *= a.w;
                     }
@@ -183,9 +183,9 @@ struct EpiStore {
                     for (int e = 0; e < 4; ++e) if (col + e < g.N) {
                         float y = xs[e];
                         if (p.act == 1) { if (p.aux_out) p.aux_out[off + e] = y; y = gelu_erf(y); }
-                        else if (p.act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
-                        else if (p.act == 3) { float gr; y = gelu_erf_both(y, gr); if (p.aux_out) p.aux_out[off + e] = gr; }
-                        else if (p.act == 4) y *= p.aux_in[off + e];
+                        else if (PRE && p.act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
+                        else if (PRE && p.act == 3) { float gr; y = gelu_erf_both(y, gr); if (p.aux_out) p.aux_out[off + e] = gr; }
+                        else if (PRE && p.act == 4) y *= p.aux_in[off + e];
                         if (p.accumulate) y += base[off + e];
                         if (base) base[off + e] = y;
                         if (p.out_hi) { float h, l; split_tf32(y, h, l); p.out_hi[off + e] = h; p.out_lo[off + e] = l; }
@@ -551,7 +551,7 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     const int grid = (int)(total < num_sms() ? total : num_sms());
     {
         ProfScope prof(PROF_LINEAR_UMMA, st, 2.0 * M * N * (double)K);
-        const bool pre = act == 2 || act == 4 || accumulate || colpart;
+        const bool pre = act >= 2 || accumulate || colpart;
         if (BN == 256) rc = colpart ? launch_major<256, 2, EpiStore<256, true, true>>(g, ep, a_mn, b_mn, grid, st)
                             : pre   ? launch_major<256, 2, EpiStore<256, true>>(g, ep, a_mn, b_mn, grid, st)
                                     : launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);

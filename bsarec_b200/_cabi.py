@@ -9,6 +9,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbsarec_sm100a.so")
 
+ABI_VERSION = 2          # == BSA_ABI_VERSION of include/bsarec_b200.h (checked at load)
+
 c_f32p = C.c_void_p
 c_i64p = C.c_void_p
 
@@ -95,7 +97,7 @@ SIGNATURES = {
     "bsa_ce_fwd": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_ce_bwd": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_score_topk_workspace_bytes": (_SZ, [C.POINTER(TopkDesc)]),
-    "bsa_score_topk": (_I, [C.POINTER(TopkDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "bsa_score_topk": (_I, [C.POINTER(TopkDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_topk_merge": (_I, [_VP, _VP, _I, _I, _I, _VP, _VP, _VP]),
     "bsa_gemm_workspace_bytes": (_SZ, [_I, _I, _I, _I64, _I64, _I, _I]),
     "bsa_gemm": (_I, [_I, _I, _I, _I, _VP, _I64, _I, _VP, _I64, _I, _VP, _I64, _VP, C.c_float, _I, _VP, _SZ, _VP]),
@@ -124,7 +126,7 @@ def load():
         fn = getattr(lib, name)          # AttributeError here == header/library mismatch
         fn.restype = res
         fn.argtypes = args
-    if lib.bsa_abi_version() != 1:
+    if lib.bsa_abi_version() != ABI_VERSION:
         raise RuntimeError("bsarec_b200: ABI version mismatch between _cabi.py and the shared library")
     _lib = lib
     return lib

@@ -484,7 +484,7 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
     }
     const dim3 grid(B * H, (L + AT_ROWS - 1) / AT_ROWS);
     const float scale = 1.0f / sqrtf((float)DH);
-    ProfScope prof(PROF_ATTN_BWD, st, 14.0 * B * H * (double)L * L * DH);     // S and dP twice, dQ, dK, dV
+    ProfScope prof(PROF_ATTN_BWD, st, 8.0 * B * H * (double)L * L * DH);      // canonical: dP, dV, dQ, dK (no credit for the S / dP recomputation)
     if (g_attn_bwd_umma && g_attn_fwd_umma && attn_umma_supported(L, d, H)) {   // query owner on tcgen05 (dQ, delta)
         const int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, B, H, L, d, dr, st);
         if (rc) return rc;

@@ -303,18 +303,18 @@ size_t bsa_score_topk_workspace_bytes(const bsa_topk_desc* c) {
 }
 
 int bsa_score_topk(const bsa_topk_desc* c, const float* seq_out, const float* item_shard, const int64_t* hist_indptr,
-                   const int64_t* hist_indices, float* top_val, int64_t* top_idx, void* workspace, size_t workspace_bytes,
-                   void* stream) {
+                   const int64_t* hist_indices, const int64_t* hist_rows, float* top_val, int64_t* top_idx, void* workspace,
+                   size_t workspace_bytes, void* stream) {
     BSA_REQUIRE(c && seq_out && item_shard && top_val && top_idx && workspace, "bsa_score_topk: null argument");
     BSA_REQUIRE((hist_indptr == nullptr) == (hist_indices == nullptr) || hist_indptr, "bsa_score_topk: hist_indices without hist_indptr");
     if (c->B == 0) return 0;
     if (topk_impl(c) == 2) {
         BSA_REQUIRE(umma_topk_supported(c->B, c->d, c->k, c->shard_rows), "bsa_score_topk: tcgen05 path does not support this shape");
         return umma_score_topk(c->B, c->d, c->k, c->shard_rows, c->shard_offset, seq_out, item_shard, (const long long*)hist_indptr,
-                               (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, c->reuse_split != 0, (cudaStream_t)stream);
+                               (const long long*)hist_indices, (const long long*)hist_rows, top_val, (long long*)top_idx, workspace, workspace_bytes, c->reuse_split != 0, (cudaStream_t)stream);
     }
     return score_topk_simt(c->B, c->d, c->k, c->shard_rows, c->shard_offset, seq_out, item_shard, (const long long*)hist_indptr,
-                           (const long long*)hist_indices, top_val, (long long*)top_idx, workspace, workspace_bytes, (cudaStream_t)stream);
+                           (const long long*)hist_indices, (const long long*)hist_rows, top_val, (long long*)top_idx, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int bsa_topk_merge(const float* cand_val, const int64_t* cand_idx, int G, int B, int k, float* top_val, int64_t* top_idx, void* stream) {

@@ -14,8 +14,8 @@ int ce_bwd_simt(int B, int d, long long N, const float* s, const float* E, const
 
 size_t topk_simt_workspace_bytes(int B, long long N);
 int score_topk_simt(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,
-                    const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
-                    void* ws, size_t ws_bytes, cudaStream_t st);
+                    const long long* hist_indptr, const long long* hist_indices, const long long* hist_rows, float* top_val,
+                    long long* top_idx, void* ws, size_t ws_bytes, cudaStream_t st);
 int topk_merge(const float* cand_val, const long long* cand_idx, int G, int B, int k, float* top_val,
                long long* top_idx, cudaStream_t st);
 

@@ -620,7 +620,7 @@ int ln_bwd_split(const float* dy, float dy_scale, const float* z, const float* m
     BSA_REQUIRE(ln_bwd_split_ok(d, dy, z, gamma, dz, ddrop, t_hi, t_lo), "ln_bwd_split: needs d %% 4 == 0 and 16-byte aligned tensors");
     const int g = row_grid(M);
     *nblk = g;
-    ProfScope prof(PROF_LN_BWD, st, 4.0 * M * d * (5.0 + (ddrop ? 1.0 : 0.0)));      // dy, z read; dz, t_hi, t_lo written
+    ProfScope prof(PROF_LN_BWD, st, 4.0 * M * d * (4.0 + (ddrop ? 1.0 : 0.0)));      // dy, z read; dz and t written (t counted once: its (hi, lo) pair is an implementation cost)
     return ln_bwd_vec(dy, dy_scale, z, mean, rstd, gamma, dz, ddrop, pgamma, pbeta, M, d, dr, g, t_hi, t_lo, pcol, st);
 }
 

@@ -54,12 +54,13 @@ __device__ __forceinline__ bool in_history(const long long* __restrict__ h, long
 
 // state := the user's history items that fall in this shard, each with score 0.0 (first k by id)
 __global__ void topk_init_kernel(const long long* __restrict__ indptr, const long long* __restrict__ indices,
-                                 long long offset, long long rows, int k, float* __restrict__ top_val,
+                                 const long long* __restrict__ hrows, long long offset, long long rows, int k, float* __restrict__ top_val,
                                  long long* __restrict__ top_idx) {
     const int row = blockIdx.x;
     if (threadIdx.x != 0) return;
     int n = 0;
-    const long long lo = indptr ? indptr[row] : 0, hi = indptr ? indptr[row + 1] : 0;
+    const long long hr = hrows ? hrows[row] : row;
+    const long long lo = indptr ? indptr[hr] : 0, hi = indptr ? indptr[hr + 1] : 0;
     for (long long p = lo; p < hi && n < k; ++p) {
         const long long gid = indices[p];
         if (gid >= offset && gid < offset + rows) { top_val[(long long)row * k + n] = 0.0f; top_idx[(long long)row * k + n] = gid; ++n; }
@@ -71,8 +72,8 @@ __global__ void topk_init_kernel(const long long* __restrict__ indptr, const lon
 // Candidates are kept in shared memory as (score, shard-local id int32).
 __global__ void __launch_bounds__(TK_THREADS)
 topk_chunk_kernel(const float* __restrict__ scores, int ld, long long offset, int n0, int ncols,
-                  const long long* __restrict__ indptr, const long long* __restrict__ indices, int k,
-                  float* __restrict__ top_val, long long* __restrict__ top_idx) {
+                  const long long* __restrict__ indptr, const long long* __restrict__ indices,
+                  const long long* __restrict__ hrows, int k, float* __restrict__ top_val, long long* __restrict__ top_idx) {
     constexpr int SENT = 0x7fffffff;
     __shared__ float cval[TK_CAP];
     __shared__ int cidx[TK_CAP];
@@ -81,7 +82,8 @@ topk_chunk_kernel(const float* __restrict__ scores, int ld, long long offset, in
     __shared__ int thr_i;
     const int row = blockIdx.x;
     const float* __restrict__ sr = scores + (long long)row * ld;
-    const long long hlo = indptr ? indptr[row] : 0, hhi = indptr ? indptr[row + 1] : 0;
+    const long long hr = hrows ? hrows[row] : row;
+    const long long hlo = indptr ? indptr[hr] : 0, hhi = indptr ? indptr[hr + 1] : 0;
     for (int i = threadIdx.x; i < k; i += TK_THREADS) {
         const long long gi = top_idx[(long long)row * k + i];
         cval[i] = top_val[(long long)row * k + i];
@@ -162,13 +164,13 @@ topk_merge_kernel(const float* __restrict__ cand_val, const long long* __restric
 size_t topk_simt_workspace_bytes(int B, long long N) { return (size_t)B * ce_chunk_cols(B, N) * sizeof(float) + 1024; }
 
 int score_topk_simt(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,
-                    const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
-                    void* ws, size_t ws_bytes, cudaStream_t st) {
+                    const long long* hist_indptr, const long long* hist_indices, const long long* hist_rows, float* top_val,
+                    long long* top_idx, void* ws, size_t ws_bytes, cudaStream_t st) {
     BSA_REQUIRE(ws_bytes >= topk_simt_workspace_bytes(B, rows), "bsa_score_topk: workspace too small");
     BSA_REQUIRE(k >= 1 && k <= 128 && rows < (1ll << 31), "bsa_score_topk: need 1 <= k <= 128 and shard rows < 2^31");
     const int nc = ce_chunk_cols(B, rows);
     float* scores = (float*)ws;
-    topk_init_kernel<<<B, 32, 0, st>>>(hist_indptr, hist_indices, offset, rows, k, top_val, top_idx);
+    topk_init_kernel<<<B, 32, 0, st>>>(hist_indptr, hist_indices, hist_rows, offset, rows, k, top_val, top_idx);
     BSA_LAUNCH_CHECK();
     for (long long n0 = 0; n0 < rows; n0 += nc) {
         const int cols = (int)((rows - n0) < nc ? (rows - n0) : nc);
@@ -176,7 +178,7 @@ int score_topk_simt(int B, int d, int k, long long rows, long long offset, const
         p.A = s; p.B = E + n0 * d; p.C = scores; p.M = B; p.N = cols; p.K = d; p.lda = d; p.ldb = d; p.ldc = nc;
         int rc = launch_gemm(p, st);
         if (rc) return rc;
-        topk_chunk_kernel<<<B, TK_THREADS, 0, st>>>(scores, nc, offset, (int)n0, cols, hist_indptr, hist_indices, k, top_val, top_idx);
+        topk_chunk_kernel<<<B, TK_THREADS, 0, st>>>(scores, nc, offset, (int)n0, cols, hist_indptr, hist_indices, hist_rows, k, top_val, top_idx);
         BSA_LAUNCH_CHECK();
     }
     return 0;

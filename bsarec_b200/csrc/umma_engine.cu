@@ -259,7 +259,7 @@ struct EpiLse {
 template <int BN>
 struct EpiTopk {
     struct Params {
-        const long long* indptr; const long long* indices; long long offset; int k;
+        const long long* indptr; const long long* indices; const long long* hrows; long long offset; int k;
         float* cand_val; long long* cand_idx;      // [nstrips][B][k]
         const float* seed_val;                     // optional [B][seed_ld]: seed_val[row*seed_ld + k-1] is a proven lower
         int seed_ld;                               //   bound of the row's final k-th score (a k-th best over a sample)
@@ -276,7 +276,10 @@ struct EpiTopk {
         li = reinterpret_cast<int*>(smem + KMAX * 128 * 4);
         for (int i = 0; i < p.k; ++i) { lv[i * 128 + rit] = -INFINITY; li[i * 128 + rit] = 0x7fffffff; }
         const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
-        if (row < g.M && p.indptr) { hlo = p.indptr[row]; hhi = p.indptr[row + 1]; if (hlo < hhi) hnext = p.indices[hlo]; }
+        if (row < g.M && p.indptr) {
+            const long long hr = p.hrows ? p.hrows[row] : row;      // CSR row of this batch row (hist_rows indirection)
+            hlo = p.indptr[hr]; hhi = p.indptr[hr + 1]; if (hlo < hhi) hnext = p.indices[hlo];
+        }
         // seeded threshold: (thr, INT_MAX) admits every score >= thr, so the sample's own k-th item re-enters
         if (row < g.M && p.seed_val) thr = p.seed_val[row * p.seed_ld + p.k - 1];
     }
@@ -792,12 +795,13 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
 // ============================================================================ scoring + top-k
 namespace {
 __global__ void hist_list_kernel(const long long* __restrict__ indptr, const long long* __restrict__ indices,
-                                 long long offset, long long rows, int k, int B, float* __restrict__ val,
+                                 const long long* __restrict__ hrows, long long offset, long long rows, int k, int B, float* __restrict__ val,
                                  long long* __restrict__ idx) {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= B) return;
     int n = 0;
-    const long long lo = indptr ? indptr[row] : 0, hi = indptr ? indptr[row + 1] : 0;
+    const long long hr = hrows ? hrows[row] : row;
+    const long long lo = indptr ? indptr[hr] : 0, hi = indptr ? indptr[hr + 1] : 0;
     for (long long q = lo; q < hi && n < k; ++q) {
         const long long gid = indices[q];
         if (gid >= offset && gid < offset + rows) { val[(long long)row * k + n] = 0.0f; idx[(long long)row * k + n] = gid; ++n; }
@@ -826,8 +830,8 @@ size_t umma_topk_workspace_bytes(int B, int d, int k, long long rows) {
 }
 
 int umma_score_topk(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,
-                    const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
-                    void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st) {
+                    const long long* hist_indptr, const long long* hist_indices, const long long* hist_rows, float* top_val,
+                    long long* top_idx, void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st) {
     BSA_REQUIRE(ws_bytes >= umma_topk_workspace_bytes(B, d, k, rows), "bsa_score_topk: workspace too small");
     char* p = (char*)ws;
     auto take = [&](size_t bytes) { char* r = p; p += al(bytes); return r; };
@@ -856,19 +860,19 @@ int umma_score_topk(int B, int d, int k, long long rows, long long offset, const
         Operand obs{e_hi, e_lo, TOPK_SEED_ROWS, d, d, false};
         if ((rc = make_core(gs, B, (int)TOPK_SEED_ROWS, d, oa, obs, CE_BN, SCHED_STRIP, 1))) return rc;
         int ss = nstrips < gs.n_tiles ? nstrips : gs.n_tiles;
-        EpiTopk<CE_BN>::Params sp{hist_indptr, hist_indices, offset, k, cand_val, cand_idx, nullptr, 0};
+        EpiTopk<CE_BN>::Params sp{hist_indptr, hist_indices, hist_rows, offset, k, cand_val, cand_idx, nullptr, 0};
         ProfScope prof(PROF_TOPK_UMMA, st, 0.0);     // time counted, no work credited: the sample is scored again below
         if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiTopk<CE_BN>>(gs, sp, ss * gs.m_tiles, st))) return rc;
         if ((rc = topk_merge(cand_val, cand_idx, ss, B, k, seed_val, seed_idx, st))) return rc;
         seed = seed_val;
     }
-    EpiTopk<CE_BN>::Params ep{hist_indptr, hist_indices, offset, k, cand_val, cand_idx, seed, k};
+    EpiTopk<CE_BN>::Params ep{hist_indptr, hist_indices, hist_rows, offset, k, cand_val, cand_idx, seed, k};
     {
         ProfScope prof(PROF_TOPK_UMMA, st, 2.0 * B * (double)rows * d);
         if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiTopk<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;
     }
     // history items enter as one more candidate list with score exactly 0.0 (trainers.py:134)
-    hist_list_kernel<<<cdiv(B, 128), 128, 0, st>>>(hist_indptr, hist_indices, offset, rows, k, B,
+    hist_list_kernel<<<cdiv(B, 128), 128, 0, st>>>(hist_indptr, hist_indices, hist_rows, offset, rows, k, B,
                                                   cand_val + (size_t)nstrips * B * k, cand_idx + (size_t)nstrips * B * k);
     BSA_LAUNCH_CHECK();
     return topk_merge(cand_val, cand_idx, nstrips + 1, B, k, top_val, top_idx, st);

@@ -14,8 +14,8 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
 bool umma_topk_supported(int B, int d, int k, long long rows);
 size_t umma_topk_workspace_bytes(int B, int d, int k, long long rows);
 int umma_score_topk(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,
-                    const long long* hist_indptr, const long long* hist_indices, float* top_val, long long* top_idx,
-                    void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st);
+                    const long long* hist_indptr, const long long* hist_indices, const long long* hist_rows, float* top_val,
+                    long long* top_idx, void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st);
 
 // generic C = alpha * A B^T (+bias)(act)(+C) on the tcgen05 engine; operands given unsplit (see umma_engine.cu)
 size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, int N, int K);

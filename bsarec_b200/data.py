@@ -92,12 +92,19 @@ class DeviceBatchLoader:
     """Iterable stand-in for ``DataLoader(RecDataset(...), sampler=Random|Sequential, batch_size=...)``."""
 
     def __init__(self, store: SequenceStore, data_type: str, batch_size: int, shuffle: bool | None = None, seed: int = 0,
-                 rank: int = 0, world_size: int = 1):
+                 rank: int = 0, world_size: int = 1, equal_shards: bool | None = None):
+        """``equal_shards`` (default: on for train when world_size > 1): every rank yields the SAME number of batches of
+        the SAME sizes — what the data-parallel gradient exchange needs (its collectives run once per batch and the
+        mean of local means must be the global mean).  The sample order is wrap-padded to a multiple of ``world_size``
+        (at most world_size-1 samples of the epoch are seen twice, as ``DistributedSampler`` does); the short last
+        batch, if any, is equally short on every rank.  Off for valid/test: every user is scored exactly once and the
+        ranks may differ by one sample."""
         if data_type not in MODES:
             raise ValueError(f"data_type must be one of {sorted(MODES)}")
         self.store, self.data_type, self.batch_size = store, data_type, int(batch_size)
         self.shuffle = (data_type == "train") if shuffle is None else bool(shuffle)     # dataset.py:207-208,212,217
         self.rank, self.world_size = rank, world_size
+        self.equal_shards = (data_type == "train" and world_size > 1) if equal_shards is None else bool(equal_shards)
         self._gen = torch.Generator(device=store.device)
         self._gen.manual_seed(seed)
         self._zeros = {}
@@ -108,12 +115,16 @@ class DeviceBatchLoader:
 
     def _num_local(self):
         n = self.store.num_samples(self.data_type)
+        if self.equal_shards:
+            return (n + self.world_size - 1) // self.world_size
         return (n - self.rank + self.world_size - 1) // self.world_size
 
     def __iter__(self):
         n = self.store.num_samples(self.data_type)
         dev = self.store.device
         order = torch.randperm(n, generator=self._gen, device=dev) if self.shuffle else torch.arange(n, device=dev)
+        if self.equal_shards and n % self.world_size:
+            order = torch.cat([order, order[:self.world_size - n % self.world_size]])      # wrap-pad: equal shard sizes
         order = order[self.rank::self.world_size]                 # one process per GPU: disjoint sample shards
         for lo in range(0, order.numel(), self.batch_size):
             idx = order[lo:lo + self.batch_size]

@@ -263,35 +263,52 @@ def scatter_last(ds: torch.Tensor, L: int) -> torch.Tensor:
 
 def score_topk(s: torch.Tensor, item_shard: torch.Tensor, hist_indptr: Optional[torch.Tensor],
                hist_indices: Optional[torch.Tensor], k: int = 20, shard_offset: int = 0, impl: int = 0,
-               cache: Optional[dict] = None):
+               cache: Optional[dict] = None, hist_rows: Optional[torch.Tensor] = None):
     """-> (top_val fp32 [B,k], top_idx int64 [B,k]); replaces trainers.py:62-68,130-149 for one item shard.
 
-    ``cache``: a dict owned by the caller (the model).  While ``item_shard`` is the same storage at the same version
-    counter (no optimizer step, no load_state_dict since) and the batch shape repeats, the workspace — and with it the
-    split-TF32 copy of the shard, 2 N d floats — is kept and ``reuse_split`` is set: an evaluation sweep splits the
-    table once, not once per batch."""
+    ``hist_rows`` int64 [B] (optional): batch row b masks CSR row ``hist_rows[b]`` — the trainer passes its whole
+    rating matrix once and the batch's ``user_ids`` here (trainers.py:131-133), no per-batch CSR is built.
+
+    ``cache``: a dict owned by the caller (the model).  It holds the split-TF32 copy of the shard (2 N d floats inside
+    the workspace) for as long as the shard is the same storage at the same version counter; ``reuse_split`` is then
+    set, so an evaluation sweep splits the table once, not once per batch.  The key does not depend on the batch size
+    (the workspace is kept at the largest B seen), and ``cache.clear()`` — ``BSARecModel.invalidate_eval_cache()`` —
+    must follow any write to the table that bypasses the version counter (``weight.data.copy_``, raw pointers)."""
     lib = _cabi.load()
     B, d = s.shape
     td = TopkDesc(B=B, d=d, k=k, shard_rows=item_shard.shape[0], shard_offset=shard_offset, impl=impl, reuse_split=0)
     with torch.cuda.device(s.device):
         wsb = lib.bsa_score_topk_workspace_bytes(C.byref(td))
-        key = (item_shard.data_ptr(), item_shard._version, tuple(item_shard.shape), B, k, impl, s.device.index)
-        if cache is not None and cache.get("key") == key:
+        key = (item_shard.data_ptr(), item_shard._version, tuple(item_shard.shape), k, impl, s.device.index)
+        # the split pair sits at a B-dependent offset inside the workspace: reusable only for the B it was made with
+        if cache is not None and cache.get("key") == key and cache.get("B") == B:
             ws = cache["ws"]
             td.reuse_split = 1
+        elif cache is not None and cache.get("key") == key and B in cache.get("alt", {}):
+            ws = cache["alt"][B]              # e.g. the short last batch of a sweep: its own workspace, split kept too
+            td.reuse_split = 1
         else:
-            if cache is not None:
-                cache.clear()                   # drop the old 2 N d buffer before taking a new one
             ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
             if cache is not None:
-                cache["key"], cache["ws"] = key, ws
+                if cache.get("key") == key:   # same table, new batch size: keep the main entry
+                    alt = cache.setdefault("alt", {})
+                    if len(alt) >= 2:
+                        alt.clear()
+                    alt[B] = ws
+                else:
+                    cache.clear()             # drop the old 2 N d buffers before keeping a new one
+                    cache["key"], cache["B"], cache["ws"] = key, B, ws
         val = torch.empty(B, k, dtype=torch.float32, device=s.device)
         idx = torch.empty(B, k, dtype=torch.int64, device=s.device)
         if hist_indptr is not None:
             hist_indptr = _require_cuda(hist_indptr, "hist_indptr", torch.int64)
             hist_indices = _require_cuda(hist_indices, "hist_indices", torch.int64)
+        if hist_rows is not None:
+            hist_rows = _require_cuda(hist_rows, "hist_rows", torch.int64)
+            if hist_rows.numel() != B:
+                raise RuntimeError(f"bsarec_b200: hist_rows has {hist_rows.numel()} entries for a batch of {B}")
         check(lib.bsa_score_topk(C.byref(td), _ptr(s.contiguous()), _ptr(item_shard), _ptr(hist_indptr), _ptr(hist_indices),
-                                 _ptr(val), _ptr(idx), _ptr(ws), wsb, _stream()), "bsa_score_topk")
+                                 _ptr(hist_rows), _ptr(val), _ptr(idx), _ptr(ws), wsb, _stream()), "bsa_score_topk")
     return val, idx
 
 
@@ -336,7 +353,7 @@ class FusedLoss(torch.autograd.Function):
         s = xs[-1]
         loss, lse, ce_ws = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
         if exchange is not None:
-            exchange.prepare(ids)                            # row counts for the sparse exchange reach the host during the forward
+            ctx.ex_state = exchange.prepare(ids)             # row counts for the sparse exchange reach the host during the forward
         ctx.hyper, ctx.names, ctx.state, ctx.ce_impl, ctx.exchange = hyper, names, state, ce_impl, exchange
         ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
         ctx.save_for_backward(*tensors)
@@ -357,10 +374,10 @@ class FusedLoss(torch.autograd.Function):
         ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, gE, ctx.ce_impl, ctx.ce_ws)
         ctx.ce_ws = None
         if ex is not None:
-            ex.start_dense(gE)                               # overlaps everything below
+            ex.start_dense(ctx.ex_state, gE)                               # overlaps everything below
         d_out = ds if state.last_row else scatter_last(ds, state.L)
         dz = encoder_backward(hyper, params, state, d_out, grads, rows_only=ex is not None)
         if ex is not None:
-            ex.finish(flat, dz, gE, scatter_add_rows)
+            ex.finish(ctx.ex_state, flat, dz, gE, scatter_add_rows)
         ctx.state = None
         return (None,) * 8 + tuple(grads[n] for n in names)

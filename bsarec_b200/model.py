@@ -154,14 +154,30 @@ class BSARecModel(nn.Module):
         return xs[-1]
 
     @torch.no_grad()
-    def full_sort_topk(self, input_ids, user_ids=None, hist_indptr=None, hist_indices=None, k: int = 20):
+    def full_sort_topk(self, input_ids, user_ids=None, hist_indptr=None, hist_indices=None, k: int = 20,
+                       hist_rows=None):
         """Top-k item ids per user, descending score, history items scored 0.0 — the eval branch of
-        ``Trainer.iteration`` (trainers.py:126-149) kept on the device.  ``hist_indptr`` [B+1] /
-        ``hist_indices`` are a CSR over the batch rows (int64, CUDA).  Returns int64 [B,k]."""
+        ``Trainer.iteration`` (trainers.py:126-149) kept on the device.  ``hist_indptr`` / ``hist_indices`` are a CSR
+        (int64, CUDA) over the batch rows, or — with ``hist_rows`` int64 [B] — over all users, row ``hist_rows[b]``
+        belonging to batch row b (the trainer's rating matrix and ``user_ids``).  Returns int64 [B,k]."""
         s = self.last_hidden(input_ids)
         _, idx = Fn.score_topk(s, self.item_embeddings.weight.detach(), hist_indptr, hist_indices, k, 0, self.topk_impl,
-                               cache=self._topk_cache)
+                               cache=self._topk_cache, hist_rows=hist_rows)
         return idx
+
+    def invalidate_eval_cache(self):
+        """Forget the split copy of the item table kept for evaluation sweeps.  Called by ``train()`` and
+        ``load_state_dict``; call it yourself after writing the table through ``.data`` or a raw pointer."""
+        self._topk_cache.clear()
+
+    def train(self, mode: bool = True):
+        if mode:
+            self.invalidate_eval_cache()
+        return super().train(mode)
+
+    def load_state_dict(self, *a, **kw):
+        self.invalidate_eval_cache()
+        return super().load_state_dict(*a, **kw)
 
     # ------------------------------------------------------------------ helpers
     def set_dropout_seed(self, seed: Optional[int]):
@@ -173,7 +189,10 @@ class BSARecModel(nn.Module):
             return int(self._fixed_seed)
         if not self.training:
             return 0
-        return int(torch.randint(0, 2 ** 62, (1,)).item())
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        if self._exchange is not None:          # identically seeded ranks must not share dropout masks across the global batch
+            seed = (seed ^ ((self._exchange.rank + 1) * 0x9E3779B97F4A7C15)) & (2 ** 62 - 1)
+        return seed
 
     def _hyper(self) -> Fn.Hyper:
         a = self.args

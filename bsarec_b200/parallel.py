@@ -68,8 +68,8 @@ class GradExchange:
     def __init__(self, group=None):
         self.group = group
         self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
         self.scale = 1.0 / self.world
-        self._w_dense = self._order = self._flat_ids = self._cap_host = self._cap_event = None
         self.collectives = 0
 
     def _issue(self, fn, *a):
@@ -80,35 +80,38 @@ class GradExchange:
         """Call at the start of the forward pass with this rank's ids int64 [B,L].  Padding positions (id 0) carry no
         item-table gradient (``padding_idx=0``, _abstract_model.py:10), so only the rows of real items are exchanged.
         The number of such rows per rank (max over ranks = rows on the wire) travels to the host asynchronously here, a
-        whole forward pass before ``finish`` needs it: no stream synchronisation on the backward's critical path."""
+        whole forward pass before ``finish`` needs it: no stream synchronisation on the backward's critical path.
+        Returns the per-call state (kept on the autograd ctx, so several losses may be in flight before a backward)."""
+        st = _ExchangeState()
         flat = ids.reshape(-1)
         pad = flat == 0
         # positions of the real items first, in their original order (stable), without a host round trip
-        self._order = torch.argsort(pad.to(torch.int8), stable=True)
-        self._flat_ids = flat
+        st.order = torch.argsort(pad.to(torch.int8), stable=True)
+        st.flat_ids = flat
         counts = torch.empty(self.world, dtype=torch.int64, device=flat.device)
         mine = (flat.numel() - pad.sum()).reshape(1)
         dist.all_gather_into_tensor(counts, mine, group=self.group)
         self.collectives += 1
         if flat.is_cuda:
-            self._cap_host = torch.empty(1, dtype=torch.int64, pin_memory=True)
-            self._cap_host.copy_(counts.max().reshape(1), non_blocking=True)
-            self._cap_event = torch.cuda.Event()
-            self._cap_event.record()
+            st.cap_host = torch.empty(1, dtype=torch.int64, pin_memory=True)
+            st.cap_host.copy_(counts.max().reshape(1), non_blocking=True)
+            st.cap_event = torch.cuda.Event()
+            st.cap_event.record()
         else:
-            self._cap_host, self._cap_event = counts.max().reshape(1), None
+            st.cap_host, st.cap_event = counts.max().reshape(1), None
+        return st
 
-    def start_dense(self, g_item: torch.Tensor):
-        self._w_dense = self._issue(dist.all_reduce, g_item.view(-1), dist.ReduceOp.SUM)
+    def start_dense(self, st: "_ExchangeState", g_item: torch.Tensor):
+        st.w_dense = self._issue(dist.all_reduce, g_item.view(-1), dist.ReduceOp.SUM)
 
-    def finish(self, small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable):
+    def finish(self, st: "_ExchangeState", small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable):
         w_small = self._issue(dist.all_reduce, small_flat, dist.ReduceOp.SUM) if small_flat.numel() else None
-        if self._cap_event is not None:
-            self._cap_event.synchronize()             # recorded during the forward pass: long since complete
-        cap = int(self._cap_host[0])                  # rows per rank on the wire (the largest per-rank count)
+        if st.cap_event is not None:
+            st.cap_event.synchronize()                # recorded during the forward pass: long since complete
+        cap = int(st.cap_host[0])                     # rows per rank on the wire (the largest per-rank count)
         if cap > 0:
-            idx = self._order[:cap]                   # this rank's real rows, then (if it has fewer) padding rows: id 0, skipped
-            ids_c = self._flat_ids[idx]
+            idx = st.order[:cap]                      # this rank's real rows, then (if it has fewer) padding rows: id 0, skipped
+            ids_c = st.flat_ids[idx]
             dz_c = torch.index_select(dz, 0, idx)
             ids_all = torch.empty(self.world * cap, dtype=torch.int64, device=dz.device)
             dz_all = torch.empty(self.world * cap, dz.shape[1], dtype=dz.dtype, device=dz.device)
@@ -116,12 +119,16 @@ class GradExchange:
             w_rows = self._issue(dist.all_gather_into_tensor, dz_all, dz_c)
             w_ids.wait()
             w_rows.wait()
-        self._w_dense.wait()
+        st.w_dense.wait()
         if cap > 0:
             scatter_fn(ids_all, dz_all, g_item)       # (rank, row) order, the same on every rank -> identical bits
         if w_small is not None:
             w_small.wait()
-        self._w_dense = self._order = self._flat_ids = self._cap_host = self._cap_event = None
+
+
+class _ExchangeState:
+    """What one forward pass leaves for its backward pass's exchange."""
+    __slots__ = ("order", "flat_ids", "cap_host", "cap_event", "w_dense")
 
 
 def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shard_offset: int,

@@ -30,25 +30,17 @@ def ndcg_k(answers, pred_list, k: int) -> float:
 
 
 class BatchHistory:
-    """The trainer's scipy CSR history matrix kept on the device; slices a batch's rows into a batch CSR."""
+    """The trainer's scipy CSR history matrix (``args.train_matrix``, dataset.py:126-160) kept on the device.  The
+    scorer reads row ``user_ids[b]`` of it for batch row b (``hist_rows`` of ``bsa_score_topk``), so the eval loop
+    builds no per-batch CSR and never synchronises with the host."""
 
     def __init__(self, csr, device):
         csr = csr.tocsr()
         csr.sort_indices()
+        self.num_rows = csr.shape[0]
         self.indptr = torch.from_numpy(csr.indptr.astype(np.int64)).to(device)
-        self.indices = torch.from_numpy(csr.indices.astype(np.int64)).to(device)
-
-    def rows(self, user_rows: torch.Tensor):
-        lo = self.indptr[user_rows]
-        cnt = self.indptr[user_rows + 1] - lo
-        indptr = torch.zeros(user_rows.numel() + 1, dtype=torch.int64, device=user_rows.device)
-        torch.cumsum(cnt, 0, out=indptr[1:])
-        total = int(indptr[-1].item())
-        if total == 0:
-            return indptr, torch.zeros(1, dtype=torch.int64, device=user_rows.device)
-        row_of = torch.repeat_interleave(torch.arange(user_rows.numel(), device=user_rows.device), cnt)
-        within = torch.arange(total, device=user_rows.device) - indptr[row_of]
-        return indptr, self.indices[lo[row_of] + within]
+        indices = csr.indices.astype(np.int64) if csr.nnz else np.zeros(1, dtype=np.int64)
+        self.indices = torch.from_numpy(indices).to(device)
 
 
 class Trainer:
@@ -95,11 +87,8 @@ class Trainer:
         not possible (it never materialises it), so this is a plain device matmul for callers that want it."""
         return torch.matmul(seq_out, self.model.item_embeddings.weight.detach().transpose(0, 1))
 
-    def get_full_sort_score(self, epoch, answers, pred_list):
-        recall, ndcg = [], []
-        for k in [5, 10, 15, 20]:
-            recall.append(recall_at_k(answers, pred_list, k))
-            ndcg.append(ndcg_k(answers, pred_list, k))
+    def _post_fix(self, epoch, recall, ndcg):
+        """The log line / return pair of trainers.py:70-83 from HR@k, NDCG@k at k = 5, 10, 15, 20."""
         post_fix = {
             "Epoch": epoch,
             "HR@5": '{:.4f}'.format(recall[0]), "NDCG@5": '{:.4f}'.format(ndcg[0]),
@@ -110,20 +99,16 @@ class Trainer:
             self.logger.info(post_fix)
         return [recall[0], ndcg[0], recall[1], ndcg[1], recall[3], ndcg[3]], str(post_fix)
 
+    def get_full_sort_score(self, epoch, answers, pred_list):
+        ks = [5, 10, 15, 20]
+        return self._post_fix(epoch, [recall_at_k(answers, pred_list, k) for k in ks], [ndcg_k(answers, pred_list, k) for k in ks])
+
     def get_full_sort_score_from_hist(self, epoch, hist):
         """Same return value as ``get_full_sort_score`` from the device-accumulated hit-rank histogram
         (``data.HitRankAccumulator``): no per-user host work, one read of 21 integers."""
         from .data import metrics_from_hist
         recall, ndcg = metrics_from_hist(hist, [5, 10, 15, 20])
-        post_fix = {
-            "Epoch": epoch,
-            "HR@5": '{:.4f}'.format(recall[0]), "NDCG@5": '{:.4f}'.format(ndcg[0]),
-            "HR@10": '{:.4f}'.format(recall[1]), "NDCG@10": '{:.4f}'.format(ndcg[1]),
-            "HR@20": '{:.4f}'.format(recall[3]), "NDCG@20": '{:.4f}'.format(ndcg[3]),
-        }
-        if self.logger is not None:
-            self.logger.info(post_fix)
-        return [recall[0], ndcg[0], recall[1], ndcg[1], recall[3], ndcg[3]], str(post_fix)
+        return self._post_fix(epoch, recall, ndcg)
 
     def _history(self):
         m = self.args.train_matrix
@@ -156,8 +141,7 @@ class Trainer:
         with torch.no_grad():
             for batch in dataloader:
                 user_ids, input_ids, answers = (t.to(self.device, non_blocking=True) for t in batch[:3])
-                indptr, indices = hist.rows(user_ids)
-                pred = self.model.full_sort_topk(input_ids, user_ids, indptr, indices, k=20)
+                pred = self.model.full_sort_topk(input_ids, user_ids, hist.indptr, hist.indices, k=20, hist_rows=user_ids)
                 acc.update(pred, answers)
                 if keep:
                     preds.append(pred)

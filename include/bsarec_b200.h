@@ -29,7 +29,7 @@ extern "C" {
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
 #endif
 
-#define BSA_ABI_VERSION 1
+#define BSA_ABI_VERSION 2      /* bumped whenever a desc struct or an entry point's argument list changes */
 
 /* ------------------------------------------------------------------------------------------------
  * Library
@@ -218,13 +218,14 @@ typedef struct {
 } bsa_topk_desc;
 
 size_t bsa_score_topk_workspace_bytes(const bsa_topk_desc* desc);
-/* History is CSR over the batch rows: hist_indptr int64 [B+1], hist_indices int64 (GLOBAL item ids, sorted
- * ascending within a row).  History items score exactly 0.0f (trainers.py:134), they are not removed.
+/* History is CSR: hist_indices int64 (GLOBAL item ids, sorted ascending within a row); batch row b owns CSR row
+ * hist_rows[b] (int64 [B]; the trainer's `user_ids` into the rating matrix, trainers.py:131-133) or, when hist_rows
+ * is NULL, CSR row b (hist_indptr int64 [B+1]).  History items score exactly 0.0f (trainers.py:134), they are not removed.
  * Outputs: top_val fp32 [B,k], top_idx int64 [B,k] (global ids), descending score, ties by ascending id;
  * unused slots (fewer than k candidates in the shard) hold -inf / -1. */
 int bsa_score_topk(const bsa_topk_desc* desc, const float* seq_out, const float* item_shard,
-                   const int64_t* hist_indptr, const int64_t* hist_indices, float* top_val, int64_t* top_idx,
-                   void* workspace, size_t workspace_bytes, void* stream);
+                   const int64_t* hist_indptr, const int64_t* hist_indices, const int64_t* hist_rows, float* top_val,
+                   int64_t* top_idx, void* workspace, size_t workspace_bytes, void* stream);
 /* merge G candidate lists [G,B,k] (one per shard) into [B,k] */
 int bsa_topk_merge(const float* cand_val, const int64_t* cand_idx, int G, int B, int k, float* top_val,
                    int64_t* top_idx, void* stream);

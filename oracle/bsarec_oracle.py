@@ -154,7 +154,8 @@ def attention_mask(ids: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
     (``_abstract_model.py:53-69``)."""
     B, L = ids.shape
     key_ok = (ids > 0)[:, None, None, :]
-    causal = torch.tril(torch.ones(L, L, dtype=torch.bool))[None, None]
+    # built on the host and moved, as the reference does (_abstract_model.py:61-63: triu on CPU, then .cuda())
+    causal = torch.tril(torch.ones(L, L, dtype=torch.bool))[None, None].to(ids.device)
     allowed = (key_ok & causal).to(dtype)
     return (1.0 - allowed) * -10000.0
 
@@ -181,10 +182,10 @@ def frequency_layer(P, prefix, x, cfg: OracleConfig, layer: int, train=False, pl
     L = x.shape[1]
     if use_fft:
         spec = torch.fft.rfft(x, dim=1, norm="ortho")
-        keep = (torch.arange(spec.shape[1]) < cfg.kept_bins).to(spec.real.dtype)[None, :, None]
+        keep = (torch.arange(spec.shape[1], device=x.device) < cfg.kept_bins).to(spec.real.dtype)[None, :, None]
         low = torch.fft.irfft(spec * keep, n=L, dim=1, norm="ortho")
     else:
-        Fm = torch.from_numpy(filter_matrix(L, cfg.kept_bins)).to(x.dtype)
+        Fm = torch.from_numpy(filter_matrix(L, cfg.kept_bins)).to(device=x.device, dtype=x.dtype)
         low = torch.einsum("ts,bsd->btd", Fm, x)
     beta2 = P[prefix + "sqrt_beta"] ** 2
     mixed = low + beta2 * (x - low)
@@ -312,7 +313,7 @@ def eval_step(P, ids, cfg: OracleConfig, hist_indptr, hist_indices, rows, k: int
     """One eval batch of ``Trainer.iteration(train=False)`` (``trainers.py:123-149``)."""
     with torch.no_grad():
         s = encode(P, ids, cfg, train=False)[-1][:, -1, :]
-        scores = predict_full(s, P["item_embeddings.weight"]).numpy().copy()
+        scores = predict_full(s, P["item_embeddings.weight"]).cpu().numpy().copy()      # trainers.py:129: D2H of [B,N]
     return full_sort_topk(masked_scores(scores, hist_indptr, hist_indices, rows), k)
 
 

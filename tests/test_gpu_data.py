@@ -62,7 +62,7 @@ def test_build_batch_large_ragged_vs_oracle(cuda_device):
     # the loader covers every train sample exactly once per epoch, across 2 ranks, with a short last batch
     seen = []
     for r in range(2):
-        ld = DeviceBatchLoader(store, "train", 1000, seed=1, rank=r, world_size=2)
+        ld = DeviceBatchLoader(store, "train", 1000, seed=1, rank=r, world_size=2, equal_shards=False)
         nb = 0
         for users, ids, answers, neg, same in ld:
             assert ids.shape[1] == L and neg.shape == answers.shape and same.shape == (answers.numel(), 0)
@@ -74,6 +74,23 @@ def test_build_batch_large_ragged_vs_oracle(cuda_device):
     samples, users = do.expand_samples(user_seq, L, "train")
     ref = np.array([[u, s[-1], len(s) - 1] for s, u in zip(samples, users)], dtype=np.int64)
     assert np.array_equal(seen[np.lexsort(seen.T[::-1])], ref[np.lexsort(ref.T[::-1])])
+    # data-parallel default (equal_shards): every rank yields the same number of batches of the same sizes — what
+    # GradExchange's per-batch collectives need — and together they cover every sample, at most world-1 of them twice
+    for world, bs in ((2, 1000), (3, 777), (8, 512)):
+        shapes, rows = [], []
+        for r in range(world):
+            ld = DeviceBatchLoader(store, "train", bs, seed=5, rank=r, world_size=world)
+            sizes = []
+            for users, ids, answers, neg, same in ld:
+                sizes.append(answers.numel())
+                rows.append(torch.stack([users, answers, (ids != 0).sum(1)], 1))
+            assert len(sizes) == len(ld)
+            shapes.append(sizes)
+        assert all(sh == shapes[0] for sh in shapes), shapes
+        got = torch.cat(rows).cpu().numpy()
+        assert 0 <= len(got) - len(ref) < world
+        uniq = np.unique(got, axis=0)
+        assert np.array_equal(uniq, np.unique(ref, axis=0))
 
 
 def test_hit_rank_histogram_and_metrics_on_beauty(cuda_device):

@@ -119,9 +119,9 @@ def _exchange_worker(rank, world, out_dir):
     me = {k: v.clone() for k, v in per_rank[rank].items()}
     ex = GradExchange()
     assert ex.world == world and ex.scale == 1.0 / world
-    ex.prepare(me["ids"])
-    ex.start_dense(me["dense"])
-    ex.finish(me["small"], me["dz"], me["dense"], _index_add_scatter)
+    st = ex.prepare(me["ids"])
+    ex.start_dense(st, me["dense"])
+    ex.finish(st, me["small"], me["dz"], me["dense"], _index_add_scatter)
     want = torch.zeros(N, d, dtype=torch.float64)
     small = torch.zeros(77, dtype=torch.float64)
     for r in range(world):

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — BSARec hot-path throughput on B200 (train seqs/s fwd+bwd+Adam and full-ranking eval users/s).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c3|c2|c1|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c3|c2|c1|c5|c4] [--users U]
 
 N>1 is launched by torchrun (one rank per GPU, NCCL).  One JSON line is printed by rank 0; its keys follow
 the driver's contract.  A "step" is one pass of the hot path over one synthetic batch:
@@ -9,10 +9,17 @@ the driver's contract.  A "step" is one pass of the hot path over one synthetic 
   eval : ids -> encoder -> full-catalog scores -> history mask -> top-20                  (trainers.py:126-149)
 `value` times the train step with the batches already resident in HBM; `e2e` times the same step through the
 public API from pinned HOST batches (H2D of ids/answers inside the timed region, D2H read of the loss).
+The evaluation half of BASELINE.json's metric is reported as `eval_value` / `eval_e2e` / `eval_roofline` and repeated
+inside `e2e`, `roofline` and `config` (objects the driver's record keeps).
+`--workload c4` is the evaluation sweep of BASELINE.json config 4: U synthetic users generated on the device batch by
+batch, item table row-sharded over the ranks, ids in -> HR/NDCG@{5,10,20} out (trainers.py:118-158).
 `--impl reference` times the CPU restatement of the reference (oracle/, kind "port") on the host cores.
+At N=1 the line also carries `reference_gpu`: the same restatement run EAGERLY ON THE B200 in fp32 (what a user of the
+reference gets on this box today), and `peaks`: TF32 / fp32 matmul throughput measured in the same run.
 """
 import argparse
 import json
+import math
 import os
 import sys
 import threading
@@ -23,24 +30,28 @@ _json_out = sys.stdout
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+C3_CFG = dict(item_size=1_000_000, hidden_size=256, max_seq_length=200, num_attention_heads=4, num_hidden_layers=2,
+              c=5, alpha=0.7)
 WORKLOADS = {
     # name: (description, cfg kwargs, per-GPU batch, cpu sample batch)
     "c3": ("C3 synthetic 1M-item catalog, L=200, d=256, 4 heads, 2 layers, c=5, batch 512 per GPU (4096 on 8)",
-           dict(item_size=1_000_000, hidden_size=256, max_seq_length=200, num_attention_heads=4, num_hidden_layers=2,
-                c=5, alpha=0.7), 512, 32),
+           C3_CFG, 512, 128),
     "c2": ("C2 ML-1M shape: 3417 items, L=200, d=64, 2 heads, 2 layers, c=5, batch 256 per GPU",
            dict(item_size=3417, hidden_size=64, max_seq_length=200, num_attention_heads=2, num_hidden_layers=2,
-                c=5, alpha=0.7), 256, 64),
+                c=5, alpha=0.7), 256, 256),
     "c1": ("C1 Beauty shape: 12102 items, L=50, d=64, 1 head, 2 layers, c=5, alpha=0.7, batch 256 per GPU",
            dict(item_size=12102, hidden_size=64, max_seq_length=50, num_attention_heads=1, num_hidden_layers=2,
                 c=5, alpha=0.7), 256, 256),
     "c5": ("C5 long sequence: 12102 items, L=1024, d=128, 2 heads, 2 layers, c=32, batch 128 per GPU",
            dict(item_size=12102, hidden_size=128, max_seq_length=1024, num_attention_heads=2, num_hidden_layers=2,
-                c=32, alpha=0.7), 128, 8),
+                c=32, alpha=0.7), 128, 16),
+    "c4": ("C4 full-ranking eval sweep: synthetic users x 1M items (model as C3: L=200, d=256, 4 heads, 2 layers), "
+           "item table row-sharded across the GPUs, top-20 + HR/NDCG", C3_CFG, 8192, 64),
 }
 P_DROP = 0.5        # both dropout probabilities, the reference's defaults (utils.py:86-87)
 TOPK = 20
 NBATCH = 4          # distinct synthetic batches cycled through
+HIST_SENTINEL = 1 << 62
 
 
 def flops_train_per_seq(c):
@@ -56,7 +67,6 @@ def flops_eval_per_user(c):
 def synth_batches(cfg, B, seed, n):
     """Seeded synthetic batches: lengths U{1..L} left-padded, ids U{1..N-1}, one all-padding
     row per 8 (Beauty has 15 % such rows), answers U{1..N-1}; history = the user's own non-zero ids."""
-    import numpy as np
     import torch
     g = torch.Generator().manual_seed(seed)
     L, N = cfg["max_seq_length"], cfg["item_size"]
@@ -78,6 +88,17 @@ def synth_batches(cfg, B, seed, n):
             indices = torch.zeros(1, dtype=torch.int64)
         out.append(dict(ids=ids, answers=answers, indptr=indptr, indices=indices))
     return out
+
+
+def make_config(name, desc, B, world, args):
+    """The `config` object of the JSON line — identical for the GPU arm and the reference arm of the same command."""
+    cfg = {"workload": desc, "per_gpu_batch": B, "global_batch": B * world, "dropout": P_DROP,
+           "parallelism": f"dp{world}" + (" (train: replica + NCCL gradient exchange; eval: item table row-sharded "
+                                          f"{world} ways, top-k merge)" if world > 1 else ""),
+           "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)" if name in ("c3", "c4") else
+                 "l2_flushed_between_steps (256 MB scratch write)",
+           "optimizer": "Adam inside the step"}
+    return cfg
 
 
 class ClockSampler(threading.Thread):
@@ -116,54 +137,443 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-def run_reference(args, desc, cfg, cpu_B):
-    """The reference's algorithm on the host cores: oracle port, all threads, bounded sample per step."""
+def _oracle_cfg(cfg):
+    import oracle
+    return oracle.OracleConfig(hidden_dropout_prob=P_DROP, attention_probs_dropout_prob=P_DROP, **cfg)
+
+
+def _time_cpu_train(step, batches, n_warm, n_timed, budget_s=None):
+    for i in range(n_warm):
+        step(batches[i % len(batches)]["ids"], batches[i % len(batches)]["answers"])
+    t0 = time.perf_counter()
+    n = 0
+    while n < n_timed or (budget_s is not None and time.perf_counter() - t0 < budget_s and n < 50):
+        b = batches[n % len(batches)]
+        step(b["ids"], b["answers"])
+        n += 1
+        if budget_s is not None and n >= 3 and time.perf_counter() - t0 >= budget_s:
+            break
+    return n, time.perf_counter() - t0
+
+
+def run_reference(args, name, desc, cfg, B, cpu_B, world):
+    """The reference's algorithm on the host cores: oracle port, all threads, bounded sample per step.  `config`,
+    `metric` and `unit` are the GPU arm's; each step is a `cpu_B`-sequence sample of the workload's batch."""
+    import numpy as np
     import torch
     import oracle
     torch.set_num_threads(os.cpu_count())
-    ocfg = oracle.OracleConfig(hidden_dropout_prob=P_DROP, attention_probs_dropout_prob=P_DROP, **cfg)
+    ocfg = _oracle_cfg(cfg)
     P = oracle.init_params(ocfg, seed=42)
-    step = oracle.adam_train_step(P, ocfg)
-    batches = synth_batches(cfg, cpu_B, 1234, max(2, min(NBATCH, args.steps)))
-    for i in range(args.warmup):
-        step(batches[i % len(batches)]["ids"], batches[i % len(batches)]["answers"])
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        b = batches[i % len(batches)]
-        step(b["ids"], b["answers"])
-    dt = time.perf_counter() - t0
-    import numpy as np
-    b = batches[0]
-    Pd = {k: v.detach() for k, v in step.P.items()}
-    oracle.eval_step(Pd, b["ids"], ocfg, b["indptr"].numpy(), b["indices"].numpy(), np.arange(cpu_B), TOPK)
-    t1 = time.perf_counter()
-    neval = max(1, min(3, args.steps))
-    for _ in range(neval):
+    batches = synth_batches(cfg, cpu_B, 1234, 2)
+    if name == "c4":          # evaluation sweep: eval steps only
+        Pd = {k: v.detach() for k, v in P.items()}
+        def ev(b):
+            return oracle.eval_step(Pd, b["ids"], ocfg, b["indptr"].numpy(), b["indices"].numpy(), np.arange(cpu_B), TOPK)
+        for i in range(min(args.warmup, 2)):
+            ev(batches[i % 2])
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            ev(batches[i % 2])
+        dt = time.perf_counter() - t0
+        val = args.steps * cpu_B / dt
+        sample = f"{args.steps} eval batches of {cpu_B} users (encoder + [B,N] scores + mask + argpartition), torch/numpy CPU, {os.cpu_count()} threads"
+        line = {"impl": "reference", "metric": "full-ranking eval users/sec", "value": val, "unit": "users/s"}
+    else:
+        step = oracle.adam_train_step(P, ocfg)
+        _time_cpu_train(step, batches, args.warmup, 0)
+        n, dt = _time_cpu_train(step, batches, 0, args.steps)
+        val = n * cpu_B / dt
+        # fixed (Adam over the table, reading E) vs batch-proportional part of the step, from a second batch size
+        fit = None
+        small_B = max(8, cpu_B // 4)
+        if small_B < cpu_B:
+            sb = synth_batches(cfg, small_B, 77, 2)
+            n2, dt2 = _time_cpu_train(step, sb, 1, 3)
+            t_big, t_small = dt / n, dt2 / n2
+            per_seq = (t_big - t_small) / (cpu_B - small_B)
+            fit = {"per_seq_ms": 1e3 * per_seq, "fixed_ms_per_step": 1e3 * (t_big - per_seq * cpu_B),
+                   "from": f"steps of {cpu_B} and {small_B} sequences"}
+        b = batches[0]
+        Pd = {k: v.detach() for k, v in step.P.items()}
         oracle.eval_step(Pd, b["ids"], ocfg, b["indptr"].numpy(), b["indices"].numpy(), np.arange(cpu_B), TOPK)
-    dte = time.perf_counter() - t1
-    val = args.steps * cpu_B / dt
-    sample = f"{args.steps} train steps of {cpu_B} sequences + {neval} eval batches of {cpu_B} users, torch CPU, {os.cpu_count()} threads"
-    line = {
-        "impl": "reference", "metric": "train seqs/sec (fwd+bwd+Adam)", "value": val, "unit": "seqs/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "cpu_batch": cpu_B},
-        "eval": {"value": neval * cpu_B / dte, "unit": "users/s"},
-        "cpu_baseline": {"value": val, "unit": "seqs/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
-        "e2e": {"value": val, "unit": "seqs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        t1 = time.perf_counter()
+        neval = max(1, min(3, args.steps))
+        for _ in range(neval):
+            oracle.eval_step(Pd, b["ids"], ocfg, b["indptr"].numpy(), b["indices"].numpy(), np.arange(cpu_B), TOPK)
+        dte = time.perf_counter() - t1
+        sample = (f"{n} train steps (fwd+bwd+Adam) of {cpu_B} sequences + {neval} eval batches of {cpu_B} users of the same "
+                  f"workload, torch CPU, {os.cpu_count()} threads")
+        line = {"impl": "reference", "metric": "train seqs/sec (fwd+bwd+Adam)", "value": val, "unit": "seqs/s",
+                "eval_value": neval * cpu_B / dte, "eval_unit": "users/s", "cpu_step_fit": fit}
+    line.update({
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": make_config(name, desc, B, world, args),
+        "cpu_baseline": {"value": val, "unit": line["unit"], "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }
+    })
     print(json.dumps(line), file=_json_out, flush=True)
+
+
+# ------------------------------------------------------------------------------------------- measurement helpers
+
+def measure_peaks(dev):
+    """TF32 tensor-core and fp32 (FFMA) matmul throughput of THIS GPU, measured in this run with cuBLAS through torch
+    (8192^3, CUDA events): best single call (burst) and ~1.5 s back to back (sustained).  SURVEY.md §7.0 / BASELINE.md §3:
+    the roofline denominator of every split-TF32 kernel is the measured TF32 rate / 3."""
+    import torch
+    n = 8192
+    a = torch.randn(n, n, device=dev)
+    b = torch.randn(n, n, device=dev)
+    out = {}
+    old = torch.backends.cuda.matmul.allow_tf32
+    try:
+        for key, tf32, reps in (("tf32", True, 40), ("fp32", False, 6)):
+            torch.backends.cuda.matmul.allow_tf32 = tf32
+            for _ in range(2):
+                torch.matmul(a, b)
+            best = 1e30
+            for _ in range(5):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); torch.matmul(a, b); e1.record(); torch.cuda.synchronize()
+                best = min(best, e0.elapsed_time(e1))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                torch.matmul(a, b)
+            e1.record(); torch.cuda.synchronize()
+            out[key + "_tflops"] = 2.0 * n ** 3 / (best * 1e-3) / 1e12
+            out[key + "_tflops_sustained"] = 2.0 * n ** 3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+    out["how"] = "torch.matmul fp32 8192^3 with allow_tf32 on (tf32) / off (fp32 FFMA), CUDA events, best of 5 and back to back"
+    return out
+
+
+def reference_gpu_leg(cfg, dev, B, host_batches):
+    """The reference's step run eagerly ON THIS B200 in fp32 (allow_tf32 off, as torch's default): the oracle's plain-torch
+    restatement of trainers.py:103-107 (calculate_loss -> zero_grad -> backward -> Adam.step -> loss.item()) and of the
+    eval branch trainers.py:126-149 (predict -> matmul -> D2H of [B,N] -> numpy mask + argpartition), with the parameters on
+    the device.  This is what a user of the reference gets on this box today; reported, not timed inside our region."""
+    import numpy as np
+    import torch
+    import oracle
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    ocfg = _oracle_cfg(cfg)
+    P = {k: v.to(dev) for k, v in oracle.init_params(ocfg, seed=42).items()}
+    out = {"kind": "port (oracle/bsarec_oracle.py eager on cuda, fp32, allow_tf32=False)"}
+    while B >= 16:
+        try:
+            step = oracle.adam_train_step(P, ocfg)
+            hb = [{k: v[:B].to(dev) for k, v in b.items() if k in ("ids", "answers")} for b in host_batches[:2]]
+            for i in range(2):
+                step(hb[i % 2]["ids"], hb[i % 2]["answers"])
+            torch.cuda.synchronize()
+            n = 5
+            t0 = time.perf_counter()
+            for i in range(n):
+                step(hb[i % 2]["ids"], hb[i % 2]["answers"])
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            out.update({"B": B, "train_seqs_per_s": n * B / dt, "train_ms_per_step": 1e3 * dt / n})
+            break
+        except torch.cuda.OutOfMemoryError:
+            B //= 2
+            torch.cuda.empty_cache()
+    Pd = {k: v.detach() for k, v in step.P.items()}
+    del step
+    torch.cuda.empty_cache()
+    b = host_batches[0]
+    Be = min(B, 256)          # the [B,N] scores cross PCIe and numpy partitions them on one host thread: keep the sample small
+    ids = b["ids"][:Be].to(dev)
+    indptr, indices = b["indptr"].numpy(), b["indices"].numpy()
+    oracle.eval_step(Pd, ids, ocfg, indptr, indices, np.arange(Be), TOPK)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    oracle.eval_step(Pd, ids, ocfg, indptr, indices, np.arange(Be), TOPK)
+    dt = time.perf_counter() - t0
+    out.update({"eval_B": Be, "eval_users_per_s": Be / dt, "eval_ms_per_step": 1e3 * dt})
+    return out
+
+
+def tie_aware_equal(idx_a, val_a, idx_b, val_b, rtol=1e-5):
+    """Top-k lists equal as index sets, except where the differing entries' scores tie to rtol (north_star: 'top-k
+    index sets, ties excepted').  Returns (ok, number of rows that needed the tie clause)."""
+    import torch
+    same = (idx_a == idx_b).all(dim=1)
+    tied_rows = 0
+    for r in torch.nonzero(~same).flatten().tolist():
+        sa, sb = set(idx_a[r].tolist()), set(idx_b[r].tolist())
+        if sa == sb:
+            continue
+        tied_rows += 1
+        kth = float(val_a[r, -1])
+        for i, v in list(zip(idx_a[r].tolist(), val_a[r].tolist())) + list(zip(idx_b[r].tolist(), val_b[r].tolist())):
+            if i in sa and i in sb:
+                continue
+            if abs(v - kth) > rtol * max(1.0, abs(kth)):
+                return False, tied_rows
+    return True, tied_rows
+
+
+def device_history(ids):
+    """[B,L] int64 history rows for the scorer: each user's own non-zero ids, sorted ascending, duplicates and padding
+    replaced by a sentinel larger than any item id — a fixed-stride CSR (indptr = arange(B+1)*L), built on the device
+    with no host synchronisation."""
+    import torch
+    h = torch.where(ids > 0, ids, torch.full_like(ids, HIST_SENTINEL))
+    h = torch.sort(h, dim=1).values
+    dup = h[:, 1:] == h[:, :-1]
+    h[:, 1:][dup] = HIST_SENTINEL
+    return torch.sort(h, dim=1).values.contiguous()
+
+
+def gen_users(gen, B, L, N, dev):
+    """One batch of synthetic users generated on the device: lengths U{1..L} left-padded with 0, one
+    all-padding row per 8, ids and answers U{1..N-1}."""
+    import torch
+    lens = torch.randint(1, L + 1, (B,), generator=gen, device=dev)
+    lens[1::8] = 0
+    ids = torch.randint(1, N, (B, L), generator=gen, device=dev)
+    pos = torch.arange(L, device=dev).unsqueeze(0)
+    ids = torch.where(pos >= (L - lens).unsqueeze(1), ids, torch.zeros_like(ids))
+    answers = torch.randint(1, N, (B,), generator=gen, device=dev)
+    return ids, answers
+
+
+class Evaluator:
+    """ids [B_local, L] -> top-20 [B_local, 20] with the item table row-sharded over the ranks."""
+
+    ENC_CHUNK = 2048          # users per encoder launch group (activations of a chunk: ~0.4 GB per [B,L,d] tensor at C3)
+
+    def __init__(self, model, cfg, world, rank, dev):
+        import torch
+        from bsarec_b200.parallel import shard_range
+        self.model, self.cfg, self.world, self.rank, self.dev = model, cfg, world, rank, dev
+        self.lo, self.hi = shard_range(cfg["item_size"], world, rank)
+        self._indptr = {}
+        self.phase_ms = None
+
+    def indptr(self, B, L):
+        import torch
+        if (B, L) not in self._indptr:
+            self._indptr[(B, L)] = torch.arange(B + 1, dtype=torch.int64, device=self.dev) * L
+        return self._indptr[(B, L)]
+
+    def encode(self, ids):
+        import torch
+        if ids.shape[0] <= self.ENC_CHUNK:
+            return self.model.last_hidden(ids)
+        return torch.cat([self.model.last_hidden(ids[i:i + self.ENC_CHUNK]) for i in range(0, ids.shape[0], self.ENC_CHUNK)])
+
+    def __call__(self, ids, hist=None, events=None):
+        """hist: [B,L] rows of device_history(ids) (computed here when None).  events: optional list that receives CUDA
+        events at the phase boundaries (history, encoder, gathers, scoring, candidate exchange + merge)."""
+        import torch
+        import torch.distributed as dist
+        from bsarec_b200 import functional as Fn
+        from bsarec_b200.parallel import sharded_full_sort_topk
+
+        def mark():
+            if events is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                events.append(e)
+        B, L = ids.shape
+        mark()
+        if hist is None:
+            hist = device_history(ids)
+        mark()
+        s_loc = self.encode(ids)
+        mark()
+        if self.world > 1:
+            hist_all = torch.empty(self.world * B, L, dtype=torch.int64, device=self.dev)
+            dist.all_gather_into_tensor(hist_all, hist)
+        else:
+            hist_all = hist
+        mark()
+        E = self.model.item_embeddings.weight.detach()
+        shard = E[self.lo:self.hi] if self.world > 1 else E
+        indptr = self.indptr(self.world * B, L)
+        cache = self.model._topk_cache
+        marks = []
+
+        def score(s_, e_, ip, ix, k, off):
+            out = Fn.score_topk(s_, e_, ip, ix, k, off, 0, cache=cache)
+            if events is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append(e)
+            return out
+        top, val = sharded_full_sort_topk(s_loc, shard, self.lo, indptr, hist_all.view(-1), TOPK, score, Fn.topk_merge,
+                                          return_values=True)
+        if events is not None:
+            events.extend(marks)
+        mark()
+        return top, val
+
+    PHASES = ["history_sort", "encoder", "history_all_gather", "user_vectors_all_gather+score_topk", "candidate_all_to_all+merge"]
+
+
+def multi_gpu_parity(model, ev, cfg, world, rank, dev, params):
+    """Outside every timed region, on real NCCL: (1) item-sharded top-20 == unsharded top-20 (tie-aware) for one batch
+    per rank — every rank holds the full replica, so it can score its own users against the whole table; (2) the
+    gradients left by the overlapped exchange (GradExchange) == local backward + flat bucket all-reduce."""
+    import torch
+    import torch.distributed as dist
+    from bsarec_b200.parallel import allreduce_gradients
+    from bsarec_b200 import functional as Fn
+    out = {}
+    was_training = model.training
+    model.eval()
+    b = synth_batches(cfg, 256, 4321 + rank, 1)[0]
+    ids = b["ids"].to(dev)
+    top_s, val_s = ev(ids)
+    s = model.last_hidden(ids)
+    val_u, top_u = Fn.score_topk(s, model.item_embeddings.weight.detach(), b["indptr"].to(dev), b["indices"].to(dev), TOPK, 0, 0)
+    ok, tied = tie_aware_equal(top_s.cpu(), val_s.cpu(), top_u.cpu(), val_u.cpu())
+    exact = bool((top_s == top_u).all())
+    flag = torch.tensor([int(ok), int(exact)], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    out["sharded_eval_equals_unsharded"] = bool(flag[0].item())
+    out["sharded_eval_bit_identical"] = bool(flag[1].item())
+    # gradients
+    model.train()
+    ex = model._exchange
+    tb = synth_batches(cfg, 64, 999 + rank, 1)[0]
+    tids, tans = tb["ids"].to(dev), tb["answers"].to(dev)
+    model.set_dropout_seed(777 + rank)
+    worst = 0.0
+    if ex is not None:
+        for p in params:
+            p.grad = None
+        model.calculate_loss(tids, tans, None, None, None).backward()
+        g_overlap = [p.grad.clone() for p in params]
+        model.disable_data_parallel()
+        for p in params:
+            p.grad = None
+        model.calculate_loss(tids, tans, None, None, None).backward()
+        allreduce_gradients(params)
+        model._exchange = ex
+        names = [n for n, _ in model.named_parameters()]
+        for n, a, p in zip(names, g_overlap, params):
+            if n.endswith("key.bias"):
+                continue
+            den = float(p.grad.abs().max())
+            err = float((a - p.grad).abs().max()) / (den if den > 0 else 1.0)
+            worst = max(worst, err)
+        w = torch.tensor([worst], device=dev)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        worst = float(w.item())
+        out["dp_overlap_vs_bucket_max_rel_err"] = worst
+    for p in params:
+        p.grad = None
+    model.set_dropout_seed(None)
+    model.train(was_training)
+    good = out["sharded_eval_equals_unsharded"] and worst < 1e-5
+    out["verdict"] = "ok" if good else "FAILED"
+    return out
+
+
+def timed_loop(fn, n, barrier, world, dev, flush=None):
+    """n calls of fn(i) bracketed by barrier+sync; device time by CUDA events, max over ranks.  With `flush` (a callable
+    that writes a buffer larger than L2) each step is timed on its own and the flush runs between steps, untimed."""
+    import torch
+    import torch.distributed as dist
+    barrier()
+    if flush is None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        total = e0.elapsed_time(e1)
+    else:
+        evs = []
+        for i in range(n):
+            flush()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn(i)
+            e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        total = sum(a.elapsed_time(b) for a, b in evs)
+    ms = torch.tensor([total], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    barrier()
+    return float(ms.item())
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+def roofline_objects(prof, steps, ms_region, peaks, tf32_meas):
+    """(dominant-kernel roofline object, {tag: line}) from the library's per-tag CUDA-event timings."""
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md: 6.65 TB/s, 1.4 PF/s sustained bf16)"
+    derived = peaks.get("bf16_tflops_sustained", 1400.0) / 2.0 / 3.0
+    if tf32_meas:
+        tensor_peak = tf32_meas["tf32_tflops_sustained"] / 3.0
+        tsrc = (f"; tensor peak = TF32 matmul measured in this run ({tf32_meas['tf32_tflops_sustained']:.0f} TF/s sustained, "
+                f"{tf32_meas['tf32_tflops']:.0f} burst) / 3 split-TF32 passes (derived bf16/2/3 would be {derived:.0f})")
+        fp32_peak = tf32_meas["fp32_tflops_sustained"]
+    else:
+        tensor_peak, tsrc, fp32_peak = derived, "; tensor peak = bf16 sustained / 2 (TF32 operands) / 3 (split-TF32 passes)", None
+    hbm_tags = {"adam", "embed_fwd", "embed_bwd", "scatter_add", "last_row_fwd", "last_row_bwd", "filter_fwd", "filter_bwd",
+                "residual_ln_fwd", "ln_bwd", "split"}       # work counted in algorithmic bytes
+
+    def kernel_line(name, rec):
+        sec = rec["ms"] * 1e-3
+        if name in hbm_tags:
+            ach = rec["work"] / sec / 1e9
+            return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
+        ach = rec["work"] / sec / 1e12
+        if name == "gemm_simt" and fp32_peak:
+            return {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak}
+        return {"bound": "tensor", "achieved": ach, "peak": tensor_peak, "unit": "TFLOP/s", "frac": ach / tensor_peak}
+
+    prof = {k: v for k, v in prof.items() if v["launches"] > 0 and v["ms"] > 0}
+    traffic = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f)
+    except Exception:
+        pass
+    lines = {k: dict(kernel_line(k, v), ms_per_step=v["ms"] / steps) for k, v in prof.items()}
+    if not prof:
+        return None, lines
+    name, rec = max(prof.items(), key=lambda kv: kv[1]["ms"])
+    roof = kernel_line(name, rec)
+    roof.update({
+        "kernel": name, "traffic": traffic.get(name), "traffic_note": traffic.get("_note") if name in traffic else None,
+        "peak_source": src + (tsrc if roof["bound"] == "tensor" else ""),
+        "avg_launch_ms": rec["ms"] / rec["launches"], "launches_per_step": rec["launches"] / steps,
+        "share_of_step": rec["ms"] / (ms_region if ms_region > 0 else 1.0), "all_kernels": lines})
+    return roof, lines
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--users", type=int, default=None, help="c4: users in the sweep (default 10 M at N>1, 1 M at N=1)")
+    ap.add_argument("--c4-batch", type=int, default=None, help="c4: users per GPU per step (default 8192)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reference-gpu", action="store_true")
     ap.add_argument("--ce-impl", type=int, default=0)
     ap.add_argument("--dp", default="overlap", choices=["overlap", "bucket"],
                     help="N>1 gradient exchange: overlap = GradExchange inside backward (dense CE part all-reduced under the "
@@ -181,27 +591,52 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "c4":
+        if args.c4_batch:
+            B = args.c4_batch
+        if args.impl == "b200" and args.steps is None:
+            users = args.users or (10_000_000 if world > 1 else 1_000_000)
+            args.steps = max(1, math.ceil(users / (B * world)))
+    if args.steps is None:
+        args.steps = 10
 
     if args.impl == "reference":
         if rank == 0:
-            run_reference(args, desc, cfg, cpu_B)
+            run_reference(args, args.workload, desc, cfg, B, cpu_B, world)
         return
-
-    import torch
-    import torch.distributed as dist
-    from bsarec_b200 import BSARecModel, FusedAdam, _cabi
-    from bsarec_b200.parallel import allreduce_gradients
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from helpers import make_args
-
     if args.warmup < 3:
         args.warmup = 3
+    if args.workload == "c4":
+        return run_c4(args, desc, cfg, B, cpu_B, rank, world, local_rank)
+    return run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank)
+
+
+def _setup(args, cfg, B, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from bsarec_b200 import BSARecModel
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import make_args
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(42)
     model = BSARecModel(make_args(cfg, P_DROP, P_DROP, batch_size=B)).to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    return dev, model, barrier
+
+
+def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from bsarec_b200 import FusedAdam, _cabi
+    from bsarec_b200.parallel import allreduce_gradients
+    dev, model, barrier = _setup(args, cfg, B, rank, world, local_rank)
     model.ce_impl = args.ce_impl
     if world > 1 and args.dp == "overlap":
         model.enable_data_parallel()
@@ -211,6 +646,10 @@ def main():
     host = synth_batches(cfg, B, 1234 + rank, NBATCH)
     pinned = [{k: v.pin_memory() for k, v in b.items()} for b in host]
     resident = [{k: v.to(dev) for k, v in b.items()} for b in host]
+    flush = None
+    if args.workload not in ("c3", "c4"):          # the small configs fit L2: flush it between timed steps
+        scratch = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+        flush = lambda: scratch.fill_(1)
 
     def train_step(b):
         loss = model.calculate_loss(b["ids"], b["answers"], None, None, None)
@@ -226,54 +665,26 @@ def main():
         answers = hb["answers"].to(dev, non_blocking=True)
         return train_step({"ids": ids, "answers": answers}).item()
 
+    ev = Evaluator(model, cfg, world, rank, dev)
+    parity = None
     if world > 1:
         # item-sharded evaluation: users split across ranks for the encoder, every rank scores ALL users of
-        # the global batch against its row shard of the item table, candidate lists are all-gathered and merged.
-        from bsarec_b200 import functional as Fn
-        from bsarec_b200.parallel import shard_range, sharded_full_sort_topk
-        lo, hi = shard_range(cfg["item_size"], world, rank)
-        all_host = [synth_batches(cfg, B, 1234 + r, NBATCH) for r in range(world)]
-        for i in range(NBATCH):          # global history CSR, rank-major, same on every rank
-            ptrs, idxs, base = [torch.zeros(1, dtype=torch.int64)], [], 0
-            for r in range(world):
-                hb = all_host[r][i]
-                n = int(hb["indptr"][-1])
-                ptrs.append(hb["indptr"][1:] + base)
-                idxs.append(hb["indices"][:n])
-                base += n
-            gi = torch.cat(idxs) if base > 0 else torch.zeros(1, dtype=torch.int64)
-            resident[i]["g_indptr"], resident[i]["g_indices"] = torch.cat(ptrs).to(dev), gi.to(dev)
-            pinned[i]["g_indptr"], pinned[i]["g_indices"] = torch.cat(ptrs).pin_memory(), gi.pin_memory()
-        del all_host
+        # the global batch against its row shard of the item table, candidates are routed to the user's owner and merged.
+        for i in range(NBATCH):
+            resident[i]["hist"] = device_history(resident[i]["ids"])
+            pinned[i]["hist"] = resident[i]["hist"].cpu().pin_memory()
+        parity = multi_gpu_parity(model, ev, cfg, world, rank, dev, params)
 
         def eval_step(b):
-            s_loc = model.last_hidden(b["ids"])
-            shard = model.item_embeddings.weight.detach()[lo:hi]
-            return sharded_full_sort_topk(s_loc, shard, lo, b["g_indptr"], b["g_indices"], TOPK,
-                                          lambda s_, e_, ip, ix, k, off: Fn.score_topk(s_, e_, ip, ix, k, off, 0, cache=model._topk_cache), Fn.topk_merge)
+            return ev(b["ids"], b["hist"])[0]
+        eval_keys = ("ids", "hist")
     else:
         def eval_step(b):
             return model.full_sort_topk(b["ids"], None, b["indptr"], b["indices"], k=TOPK)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+        eval_keys = ("ids", "indptr", "indices")
 
     def timed(fn, n):
-        """n calls of fn(i) bracketed by barrier+sync; device time by CUDA events, max over ranks."""
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(n):
-            fn(i)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        barrier()
-        return float(ms.item())
+        return timed_loop(fn, n, barrier, world, dev, flush)
 
     model.train()
     for i in range(args.warmup):
@@ -298,96 +709,218 @@ def main():
     for i in range(args.warmup):
         eval_step(resident[i % NBATCH])
     ms_eval = timed(lambda i: eval_step(resident[i % NBATCH]), args.steps)
+    _cabi.profile(True)
+    timed(lambda i: eval_step(resident[i % NBATCH]), args.steps)
+    prof_eval = _cabi.profile_results()
+    _cabi.profile(False)
 
     def eval_e2e(i):
         hb = pinned[i % NBATCH]
-        out = eval_step({k: v.to(dev, non_blocking=True) for k, v in hb.items()})
+        out = eval_step({k: hb[k].to(dev, non_blocking=True) for k in eval_keys})
         return out.cpu()
     eval_e2e(0)
     ms_eval_e2e = timed(eval_e2e, args.steps)
     sampler.join(timeout=2)
 
+    tf32 = None
+    if rank == 0:
+        tf32 = measure_peaks(dev)
+    barrier()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except Exception:
-        pass
-    bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    hbm_peak = peaks.get("hbm_gbs", 6650.0)
-    src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md: 6.65 TB/s, 1.4 PF/s sustained bf16)"
-    tensor_peak = bf16_peak / 2.0 / 3.0          # fp32-parity bar => 3xTF32: effective tensor peak
-    hbm_tags = {"adam", "embed_fwd", "embed_bwd", "scatter_add", "last_row_fwd", "last_row_bwd", "filter_fwd", "filter_bwd",
-                "residual_ln_fwd", "ln_bwd"}       # work counted in algorithmic bytes
-
-    def kernel_line(name, rec):
-        sec = rec["ms"] * 1e-3
-        if name in hbm_tags:
-            ach = rec["work"] / sec / 1e9
-            return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
-        ach = rec["work"] / sec / 1e12
-        return {"bound": "tensor", "achieved": ach, "peak": tensor_peak, "unit": "TFLOP/s", "frac": ach / tensor_peak}
-
-    prof = {k: v for k, v in prof.items() if v["launches"] > 0 and v["ms"] > 0}
-    traffic = {}
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f)
-    except Exception:
-        pass
-    dom = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else (None, None)
-    roofline = None
-    if dom[0]:
-        roofline = kernel_line(dom[0], dom[1])
-        roofline.update({
-            "kernel": dom[0], "traffic": traffic.get(dom[0]), "traffic_note": traffic.get("_note") if dom[0] in traffic else None,
-            "peak_source": src + ("; tensor peak = bf16 sustained / 2 (TF32 operands) / 3 (split-TF32 passes)" if roofline["bound"] == "tensor" else ""),
-            "avg_launch_ms": dom[1]["ms"] / dom[1]["launches"], "launches_per_step": dom[1]["launches"] / args.steps,
-            "share_of_step": dom[1]["ms"] / (ms_train if ms_train > 0 else 1.0),
-            "all_kernels": {k: dict(kernel_line(k, v), ms_per_step=v["ms"] / args.steps) for k, v in prof.items()}})
+    peaks = load_peaks()
+    roofline, _ = roofline_objects(prof, args.steps, ms_train, peaks, tf32)
+    eval_roof, _ = roofline_objects(prof_eval, args.steps, ms_eval, peaks, tf32)
     seqs = args.steps * B * world
     value = seqs / (ms_train * 1e-3)
     h2d = B * cfg["max_seq_length"] * 8 + B * 8
+    eval_value = seqs / (ms_eval * 1e-3)
+    eval_e2e_obj = {"value": seqs / (ms_eval_e2e * 1e-3), "unit": "users/s",
+                    "h2d_bytes_per_step": int(sum(pinned[0][k].numel() * pinned[0][k].element_size() for k in eval_keys)),
+                    "d2h_bytes_per_step": B * TOPK * 8}
+    config = make_config(args.workload, desc, B, world, args)
+    # `config` stays identical to the reference arm's (the driver compares them); run details go beside it
+    run_detail = {"optimizer_impl": "bsarec_b200.FusedAdam" if args.optimizer == "fused" else "torch.optim.Adam",
+                  "dp_exchange": args.dp if world > 1 else None, "ce_impl": args.ce_impl}
+    if roofline is not None and eval_roof is not None:
+        roofline["eval"] = {k: eval_roof[k] for k in ("kernel", "bound", "achieved", "peak", "unit", "frac", "avg_launch_ms",
+                                                       "share_of_step")}
     line = {
         "metric": "train seqs/sec (fwd+bwd+Adam)", "value": value, "unit": "seqs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_train / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "per_gpu_batch": B, "global_batch": B * world, "dropout": P_DROP,
-                   "parallelism": f"dp{world}" + (f" (train: replica + NCCL gradient exchange [{args.dp}]; eval: item table row-sharded {world} ways, top-k merge)" if world > 1 else ""), "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)",
-                   "optimizer": ("bsarec_b200.FusedAdam" if args.optimizer == "fused" else "torch.optim.Adam") + " inside the step",
-                   "ce_impl": args.ce_impl},
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
         "model_tflops": value * flops_train_per_seq(cfg) / 1e12,
-        "eval": {"metric": "full-ranking eval users/sec", "value": seqs / (ms_eval * 1e-3), "unit": "users/s",
-                 "ms_per_step": ms_eval / args.steps,
-                 "e2e": {"value": seqs / (ms_eval_e2e * 1e-3), "unit": "users/s",
-                         "h2d_bytes_per_step": int(sum(v.numel() * v.element_size() for v in pinned[0].values())), "d2h_bytes_per_step": B * TOPK * 8},
-                 "model_tflops": seqs / (ms_eval * 1e-3) * flops_eval_per_user(cfg) / 1e12},
-        "e2e": {"value": seqs / (ms_e2e * 1e-3), "unit": "seqs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "eval_metric": "full-ranking eval users/sec", "eval_value": eval_value, "eval_unit": "users/s",
+        "eval_ms_per_step": ms_eval / args.steps, "eval_e2e": eval_e2e_obj, "eval_roofline": eval_roof,
+        "eval_model_tflops": eval_value * flops_eval_per_user(cfg) / 1e12,
+        "e2e": {"value": seqs / (ms_e2e * 1e-3), "unit": "seqs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                "eval_value": eval_e2e_obj["value"], "eval_unit": "users/s",
+                "eval_h2d_bytes_per_step": eval_e2e_obj["h2d_bytes_per_step"],
+                "eval_d2h_bytes_per_step": eval_e2e_obj["d2h_bytes_per_step"]},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "roofline": roofline,
+        "peaks": tf32,
+        "run_detail": run_detail,
     }
-    if not args.no_cpu_baseline and world == 1:
-        import oracle
-        torch.set_num_threads(os.cpu_count())
-        ocfg = oracle.OracleConfig(hidden_dropout_prob=P_DROP, attention_probs_dropout_prob=P_DROP, **cfg)
-        P = {k: v.detach().cpu() for k, v in model.state_dict().items()}
-        step = oracle.adam_train_step(P, ocfg)
-        cb = synth_batches(cfg, cpu_B, 99, 2)
-        step(cb[0]["ids"], cb[0]["answers"])
-        t0 = time.perf_counter()
-        n = 0
-        while n < 3 or (time.perf_counter() - t0 < 10.0 and n < 50):
-            step(cb[n % 2]["ids"], cb[n % 2]["answers"])
-            n += 1
-        dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": n * cpu_B / dt, "unit": "seqs/s", "cores": os.cpu_count(), "kind": "port",
-                                "sample": f"{n} train steps (fwd+bwd+Adam) of {cpu_B} sequences of the same workload, torch CPU, {os.cpu_count()} threads"}
+    if parity is not None:
+        line["multi_gpu_parity"] = parity["verdict"]
+        line["multi_gpu_parity_detail"] = parity
+        line["e2e"]["multi_gpu_parity"] = parity["verdict"]
+        if roofline is not None:
+            roofline["multi_gpu_parity"] = parity["verdict"]
+    if world == 1:
+        del optim
+        for p in params:
+            p.grad = None
+        torch.cuda.empty_cache()
+        if not args.no_reference_gpu:
+            try:
+                rg = reference_gpu_leg(cfg, dev, B, host)
+                rg["speedup_train"] = value / rg["train_seqs_per_s"] if rg.get("train_seqs_per_s") else None
+                rg["speedup_eval"] = eval_value / rg["eval_users_per_s"] if rg.get("eval_users_per_s") else None
+            except Exception as e:          # a reported bar, never a reason to lose the line
+                rg = {"error": f"{type(e).__name__}: {e}"[:300]}
+            line["reference_gpu"] = rg
+        if not args.no_cpu_baseline:
+            import oracle
+            torch.set_num_threads(os.cpu_count())
+            P = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+            step = oracle.adam_train_step(P, _oracle_cfg(cfg))
+            cb = synth_batches(cfg, cpu_B, 99, 2)
+            n, dt = _time_cpu_train(step, cb, 1, 3, budget_s=10.0)
+            line["cpu_baseline"] = {"value": n * cpu_B / dt, "unit": "seqs/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"{n} train steps (fwd+bwd+Adam) of {cpu_B} sequences of the same workload, torch CPU, {os.cpu_count()} threads"}
+            if "reference_gpu" in line:
+                line["cpu_baseline"]["reference_gpu"] = line["reference_gpu"]
+    print(json.dumps(line), file=_json_out, flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_c4(args, desc, cfg, B, cpu_B, rank, world, local_rank):
+    """BASELINE.json config 4: the evaluation sweep of trainers.py:118-158 over `steps * world * B` synthetic users —
+    users generated on the device batch by batch (never materialised as a whole), item table row-sharded, per-user
+    top-20, hit-rank histogram accumulated on the device and all-reduced once: ids in -> HR/NDCG out."""
+    import torch
+    import torch.distributed as dist
+    from bsarec_b200 import HitRankAccumulator, _cabi
+    dev, model, barrier = _setup(args, cfg, B, rank, world, local_rank)
+    model.eval()
+    L, N = cfg["max_seq_length"], cfg["item_size"]
+    ev = Evaluator(model, cfg, world, rank, dev)
+    parity = multi_gpu_parity(model, ev, cfg, world, rank, dev, []) if world > 1 else None
+    model.eval()
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+
+    def sweep_step(acc, events=None):
+        ids, answers = gen_users(gen, B, L, N, dev)
+        top, _ = ev(ids, None, events)
+        acc.update(top, answers)
+
+    warm = HitRankAccumulator(TOPK, dev)
+    for _ in range(args.warmup):
+        sweep_step(warm)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    acc = HitRankAccumulator(TOPK, dev)
+    l0 = _cabi.launch_count()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        sweep_step(acc)
+    acc.all_reduce()
+    hist_host = acc.hist.cpu()                # the sweep's result: 21 integers
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    barrier()
+    ms_sweep = float(ms.item())
+    launches = _cabi.launch_count() - l0
+    sampler.stop_flag = True
+    # phase shares: a few steps with events at the phase boundaries (max over ranks per phase)
+    nph = min(5, args.steps)
+    phase = torch.zeros(len(Evaluator.PHASES) + 1, device=dev)
+    tmp = HitRankAccumulator(TOPK, dev)
+    for _ in range(nph):
+        evs = []
+        g0 = torch.cuda.Event(enable_timing=True)
+        g0.record()
+        sweep_step(tmp, evs)
+        g1 = torch.cuda.Event(enable_timing=True)
+        g1.record()
+        torch.cuda.synchronize()
+        # evs: [start, hist, enc, gather, score, end]; generation = g0 -> evs[0]; metrics = evs[-1] -> g1
+        for j in range(len(Evaluator.PHASES)):
+            phase[j] += evs[j].elapsed_time(evs[j + 1])
+        phase[-1] += g0.elapsed_time(evs[0]) + evs[-1].elapsed_time(g1)
+    if world > 1:
+        dist.all_reduce(phase, op=dist.ReduceOp.MAX)
+    phase = (phase / nph).tolist()
+    # per-kernel roofline of the scoring kernel
+    _cabi.profile(True)
+    for _ in range(nph):
+        sweep_step(tmp)
+    torch.cuda.synchronize()
+    prof = _cabi.profile_results()
+    _cabi.profile(False)
+    # end to end from pinned host batches: H2D of ids + answers, D2H of the histogram every step
+    pinned = []
+    for i in range(2):
+        ids, answers = gen_users(gen, B, L, N, dev)
+        pinned.append((ids.cpu().pin_memory(), answers.cpu().pin_memory()))
+    acc2 = HitRankAccumulator(TOPK, dev)
+    n_e2e = min(args.steps, 20)
+
+    def e2e_step(i):
+        ids = pinned[i % 2][0].to(dev, non_blocking=True)
+        answers = pinned[i % 2][1].to(dev, non_blocking=True)
+        top, _ = ev(ids)
+        acc2.update(top, answers)
+        return acc2.hist.cpu()
+    e2e_step(0)
+    ms_e2e = timed_loop(e2e_step, n_e2e, barrier, world, dev)
+    sampler.join(timeout=2)
+    tf32 = measure_peaks(dev) if rank == 0 else None
+    barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    from bsarec_b200.data import metrics_from_hist
+    users = args.steps * B * world
+    recall, ndcg = metrics_from_hist(hist_host.numpy(), [5, 10, 20])
+    value = users / (ms_sweep * 1e-3)
+    roofline, _ = roofline_objects(prof, nph, sum(phase) * nph, load_peaks(), tf32)
+    config = make_config("c4", desc, B, world, args)
+    sweep = {"users": users, "items": N,
+             "users_generated": "on the device per batch inside the timed region (torch.Generator(device), seed 1234 + rank)"}
+    tot = sum(phase)
+    line = {
+        "metric": "full-ranking eval users/sec", "value": value, "unit": "users/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_sweep / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+        "model_tflops": value * flops_eval_per_user(cfg) / 1e12,
+        "sweep": sweep, "sweep_seconds": ms_sweep * 1e-3,
+        "metrics": {"HR@5": recall[0], "NDCG@5": ndcg[0], "HR@10": recall[1], "NDCG@10": ndcg[1], "HR@20": recall[2],
+                    "NDCG@20": ndcg[2], "users": int(hist_host.sum())},
+        "phase_ms_per_step": dict(zip(Evaluator.PHASES + ["user_generation+hit_rank_hist"], phase)),
+        "phase_share": dict(zip(Evaluator.PHASES + ["user_generation+hit_rank_hist"], [p / tot for p in phase])),
+        "e2e": {"value": n_e2e * B * world / (ms_e2e * 1e-3), "unit": "users/s", "h2d_bytes_per_step": B * L * 8 + B * 8,
+                "d2h_bytes_per_step": (TOPK + 1) * 8, "steps": n_e2e},
+        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roofline, "peaks": tf32,
+    }
+    if parity is not None:
+        line["multi_gpu_parity"] = parity["verdict"]
+        line["multi_gpu_parity_detail"] = parity
+        line["e2e"]["multi_gpu_parity"] = parity["verdict"]
     print(json.dumps(line), file=_json_out, flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -107,6 +107,7 @@ SIGNATURES = {
     "bsa_hit_rank_hist": (_I, [_VP, _VP, _I64, _I, _VP, _VP]),
     "bsa_gather_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
     "bsa_scatter_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
+    "bsa_gather_rows": (_I, [_VP, _I64, _I64, _VP, _I, _VP, _VP]),
 }
 
 _lib = None

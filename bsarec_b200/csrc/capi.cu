@@ -351,6 +351,12 @@ int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* str
     return gather_last_rows(src, dst, B, L, d, (cudaStream_t)stream);
 }
 
+int bsa_gather_rows(const int64_t* idx, int64_t n_rows, int64_t src_rows, const float* src, int d, float* dst, void* stream) {
+    BSA_REQUIRE(idx && src && dst, "bsa_gather_rows: null argument");
+    BSA_REQUIRE(n_rows >= 0 && src_rows >= 1 && d >= 4, "bsa_gather_rows: bad sizes");
+    return gather_rows((const long long*)idx, n_rows, src_rows, src, d, dst, (cudaStream_t)stream);
+}
+
 int bsa_scatter_last(const float* src, float* dst, int B, int L, int d, void* stream) {
     BSA_REQUIRE(src && dst, "bsa_scatter_last: null argument");
     if (B == 0) return 0;

@@ -770,6 +770,26 @@ int scatter_last_rows(const float* src, float* dst, int B, int L, int d, cudaStr
     return 0;
 }
 
+// dst[i, :] = src[idx[i], :]: a warp per row, float4 lanes (d % 4 == 0) — pure copies, bit-exact by construction
+__global__ void __launch_bounds__(256) gather_rows_kernel(const long long* __restrict__ idx, long long M, long long src_rows,
+                                                          const float* __restrict__ src, int d, float* __restrict__ dst) {
+    const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= M) return;
+    long long r = idx[row];
+    if (r < 0 || r >= src_rows) r = 0;          // out-of-range indices read row 0 (callers validate; never fault)
+    const float4* s4 = reinterpret_cast<const float4*>(src + r * d);
+    float4* d4 = reinterpret_cast<float4*>(dst + row * d);
+    for (int c = threadIdx.x & 31; c < d / 4; c += 32) d4[c] = __ldg(s4 + c);
+}
+
+int gather_rows(const long long* idx, long long M, long long src_rows, const float* src, int d, float* dst, cudaStream_t st) {
+    if (M == 0) return 0;
+    BSA_REQUIRE(d % 4 == 0, "gather_rows: row length must be a multiple of 4");
+    gather_rows_kernel<<<cdiv(M, 8), 256, 0, st>>>(idx, M, src_rows, src, d, dst);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
 int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st) {
     last_rows_kernel<<<cdiv((long long)B * d, 256), 256, 0, st>>>(src, dst, B, L, d, 0);
     BSA_LAUNCH_CHECK();

@@ -87,5 +87,6 @@ int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, cons
 // dst[b*L + (L-1)][:] = src[b][:], everything else 0
 int scatter_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st);
 int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st);
+int gather_rows(const long long* idx, long long M, long long src_rows, const float* src, int d, float* dst, cudaStream_t st);
 
 }  // namespace bsa

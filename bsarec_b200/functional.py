@@ -211,6 +211,18 @@ def scatter_add_rows(ids: torch.Tensor, rows: torch.Tensor, dE: torch.Tensor) ->
                                        _stream()), "bsa_scatter_add_rows")
 
 
+def gather_rows(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """src [R,d] fp32, idx int64 [M] -> [M,d] = src[idx] (bit-exact row copies; the gather of _abstract_model.py:17-18)."""
+    lib = _cabi.load()
+    src = _require_cuda(src, "src", torch.float32)
+    idx = _require_cuda(idx, "idx", torch.int64)
+    out = torch.empty(idx.numel(), src.shape[1], dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        check(lib.bsa_gather_rows(_ptr(idx), idx.numel(), src.shape[0], _ptr(src), src.shape[1], _ptr(out), _stream()),
+              "bsa_gather_rows")
+    return out
+
+
 def gather_last(x: torch.Tensor) -> torch.Tensor:
     lib = _cabi.load()
     B, L, d = x.shape
@@ -378,6 +390,6 @@ class FusedLoss(torch.autograd.Function):
         d_out = ds if state.last_row else scatter_last(ds, state.L)
         dz = encoder_backward(hyper, params, state, d_out, grads, rows_only=ex is not None)
         if ex is not None:
-            ex.finish(ctx.ex_state, flat, dz, gE, scatter_add_rows)
+            ex.finish(ctx.ex_state, flat, dz, gE, scatter_add_rows, gather_rows)
         ctx.state = None
         return (None,) * 8 + tuple(grads[n] for n in names)

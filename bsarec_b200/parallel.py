@@ -104,7 +104,8 @@ class GradExchange:
     def start_dense(self, st: "_ExchangeState", g_item: torch.Tensor):
         st.w_dense = self._issue(dist.all_reduce, g_item.view(-1), dist.ReduceOp.SUM)
 
-    def finish(self, st: "_ExchangeState", small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable):
+    def finish(self, st: "_ExchangeState", small_flat: torch.Tensor, dz: torch.Tensor, g_item: torch.Tensor, scatter_fn: Callable,
+               gather_fn: Optional[Callable] = None):
         w_small = self._issue(dist.all_reduce, small_flat, dist.ReduceOp.SUM) if small_flat.numel() else None
         if st.cap_event is not None:
             st.cap_event.synchronize()                # recorded during the forward pass: long since complete
@@ -112,7 +113,7 @@ class GradExchange:
         if cap > 0:
             idx = st.order[:cap]                      # this rank's real rows, then (if it has fewer) padding rows: id 0, skipped
             ids_c = st.flat_ids[idx]
-            dz_c = torch.index_select(dz, 0, idx)
+            dz_c = gather_fn(dz, idx) if gather_fn is not None else torch.index_select(dz, 0, idx)   # (gloo CPU tests: torch)
             ids_all = torch.empty(self.world * cap, dtype=torch.int64, device=dz.device)
             dz_all = torch.empty(self.world * cap, dz.shape[1], dtype=dz.dtype, device=dz.device)
             w_ids = self._issue(dist.all_gather_into_tensor, ids_all, ids_c)
@@ -133,29 +134,29 @@ class _ExchangeState:
 
 def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shard_offset: int,
                            hist_indptr_all: Optional[torch.Tensor], hist_indices_all: Optional[torch.Tensor], k: int,
-                           score_fn: Callable, merge_fn: Callable, group=None) -> torch.Tensor:
+                           score_fn: Callable, merge_fn: Callable, group=None, return_values: bool = False):
     """Item-sharded evaluation step.
 
     s_local [B_local, d]: this rank's users' last-position vectors (equal B_local on every rank).
     hist_*_all: CSR history of ALL world*B_local users of the global batch, rank-major order.
     score_fn(s, shard, indptr, indices, k, offset) -> (val [B,k], idx [B,k]); merge_fn(val [G,B,k], idx) -> (val, idx).
-    Returns int64 [B_local, k] for this rank's users."""
+    Exchange: one all-gather of the user vectors, then ONE all-to-all per candidate array that routes each user's k
+    candidates from every shard to the rank that owns the user (k*(4+8) bytes per user per shard on the wire — an
+    all-gather would deliver every rank world times more than it merges).
+    Returns int64 [B_local, k] for this rank's users (and the merged scores with ``return_values``)."""
     world = dist.get_world_size(group)
-    rank = dist.get_rank(group)
     Bl = s_local.shape[0]
     if world == 1:
-        _, idx = score_fn(s_local, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)
-        return idx
+        val, idx = score_fn(s_local, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)
+        return (idx, val) if return_values else idx
     s_all = torch.empty(world * Bl, s_local.shape[1], dtype=s_local.dtype, device=s_local.device)
     dist.all_gather_into_tensor(s_all, s_local.contiguous(), group=group)
     val, idx = score_fn(s_all, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)
-    # gathered along dim 0 ([world * B, k], the layout every backend accepts), viewed as [world, B, k]
-    val_all = torch.empty(world * world * Bl, k, dtype=val.dtype, device=val.device)
-    idx_all = torch.empty(world * world * Bl, k, dtype=idx.dtype, device=idx.device)
-    dist.all_gather_into_tensor(val_all, val.contiguous(), group=group)
-    dist.all_gather_into_tensor(idx_all, idx.contiguous(), group=group)
-    val_all = val_all.view(world, world * Bl, k)
-    idx_all = idx_all.view(world, world * Bl, k)
-    mine = slice(rank * Bl, (rank + 1) * Bl)
-    _, top = merge_fn(val_all[:, mine].contiguous(), idx_all[:, mine].contiguous())
-    return top
+    # val / idx are [world * Bl, k] in rank-major user order: block r goes to rank r; what arrives is [world, Bl, k],
+    # shard-major — this rank's users against every shard
+    val_in = torch.empty(world, Bl, k, dtype=val.dtype, device=val.device)
+    idx_in = torch.empty(world, Bl, k, dtype=idx.dtype, device=idx.device)
+    dist.all_to_all_single(val_in.view(-1), val.contiguous().view(-1), group=group)
+    dist.all_to_all_single(idx_in.view(-1), idx.contiguous().view(-1), group=group)
+    top_val, top = merge_fn(val_in, idx_in)
+    return (top, top_val) if return_values else top

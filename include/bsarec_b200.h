@@ -281,6 +281,10 @@ int bsa_hit_rank_hist(const int64_t* pred, const int64_t* answers, int64_t U, in
  * ---------------------------------------------------------------------------------------------- */
 /* dst [B,d] = src[:, L-1, :] */
 int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* stream);
+/* dst [n_rows,d] = src[idx[i], :] — the row gather of nn.Embedding (_abstract_model.py:17-18) on its own: bit-exact
+ * copies.  Used by the data-parallel exchange to pack the rows that carry an item-table gradient; idx int64 [n_rows]
+ * in [0, src_rows), d % 4 == 0. */
+int bsa_gather_rows(const int64_t* idx, int64_t n_rows, int64_t src_rows, const float* src, int d, float* dst, void* stream);
 /* dst [B,L,d] = 0 except dst[:, L-1, :] = src [B,d] */
 int bsa_scatter_last(const float* src, float* dst, int B, int L, int d, void* stream);
 

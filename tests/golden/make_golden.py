@@ -118,21 +118,24 @@ def small_case(name, seed, B, **cfgkw):
     print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
 
 
-def beauty_case():
-    """Known-answer: shipped checkpoint + Beauty test split -> src/output/BSARec_Beauty_best.log:258."""
+def known_answer_case(data_name, split, out_name, store_params=True, **cfgkw):
+    """Known-answer: a shipped checkpoint on a real split through the reference's own Trainer.iteration.
+    Beauty/test -> src/output/BSARec_Beauty_best.log:258; LastFM/test -> BSARec_LastFM_best.log:237; the valid split
+    (history = all but the last two items, dataset.py:132) reproduces the best epoch's validation line of the log."""
     data_dir = REF + "/data/"
-    args = make_args(hidden_size=64, max_seq_length=50, num_attention_heads=1, c=5, alpha=0.7,
-                     hidden_dropout_prob=0.5, attention_probs_dropout_prob=0.5, batch_size=256,
-                     data_dir=data_dir, data_name="Beauty", num_workers=0)
+    args = make_args(hidden_size=64, max_seq_length=50, hidden_dropout_prob=0.5, attention_probs_dropout_prob=0.5,
+                     batch_size=256, data_dir=data_dir, data_name=data_name, num_workers=0, **cfgkw)
     seq_dic, max_item, num_users = ref_dataset.get_seq_dic(args)
     args.item_size = max_item + 1
     args.num_users = num_users + 1
-    test_ds = ref_dataset.RecDataset(args, seq_dic["user_seq"], data_type="test")
-    _, test_matrix = ref_dataset.get_rating_matrix("Beauty", seq_dic, max_item)
+    ds = ref_dataset.RecDataset(args, seq_dic["user_seq"], data_type=split)
+    valid_matrix, test_matrix = ref_dataset.get_rating_matrix(data_name, seq_dic, max_item)
+    matrix = (valid_matrix if split == "valid" else test_matrix).tocsr()
+    matrix.sort_indices()
     model = MODEL_DICT["bsarec"](args=args)
-    sd = torch.load(REF + "/output/BSARec_Beauty_best.pt", map_location="cpu")
+    sd = torch.load(REF + f"/output/BSARec_{data_name}_best.pt", map_location="cpu")
     model.load_state_dict(sd)
-    args.train_matrix = test_matrix
+    args.train_matrix = matrix
     trainer = Trainer(model, None, None, None, args, logging.getLogger("golden"))
     captured = {}
     orig = trainer.get_full_sort_score
@@ -142,9 +145,9 @@ def beauty_case():
         return orig(epoch, answers, pred)
 
     trainer.get_full_sort_score = grab
-    U = len(test_ds)
-    all_ids = torch.stack([test_ds[i][1] for i in range(U)])
-    all_ans = torch.stack([test_ds[i][2] for i in range(U)])
+    U = len(ds)
+    all_ids = torch.stack([ds[i][1] for i in range(U)])
+    all_ans = torch.stack([ds[i][2] for i in range(U)])
     batches = []
     for s in range(0, U, 256):
         e = min(U, s + 256)
@@ -156,22 +159,28 @@ def beauty_case():
     gaps = np.zeros(U, dtype=np.float32)
     for (uids, ids, _, _, _) in batches:
         sc = trainer.predict_full(model.predict(ids, None)[:, -1, :]).numpy().copy()
-        sc[test_matrix[uids.numpy()].toarray() > 0] = 0
+        sc[matrix[uids.numpy()].toarray() > 0] = 0
         top = -np.sort(-sc, axis=1)[:, :21]
         gaps[uids.numpy()] = (top[:, 19] - top[:, 20]) / np.maximum(np.abs(top[:, 19]), 1e-30)
     torch.set_grad_enabled(True)
     out = {
         "ids": all_ids.numpy().astype(np.int16), "answers": all_ans.numpy().astype(np.int32),
-        "hist_indptr": test_matrix.indptr.astype(np.int32), "hist_indices": test_matrix.indices.astype(np.int16),
+        "hist_indptr": matrix.indptr.astype(np.int32), "hist_indices": matrix.indices.astype(np.int16),
         "pred_list": captured["p"].astype(np.int16), "metrics": np.array(scores6, dtype=np.float64),
         "info": np.array(info), "gap_rel": gaps,
         "item_size": np.array(args.item_size),
+        "cfg_keys": np.array(sorted(cfgkw.keys())),
+        "cfg_vals": np.array([float(cfgkw[k]) for k in sorted(cfgkw.keys())]),
     }
-    for n, p in model.state_dict().items():
-        out["param." + n] = p.numpy()
-    np.savez_compressed(os.path.join(HERE, "beauty_test.npz"), **out)
-    print("beauty", info)
+    if store_params:
+        for n, p in model.state_dict().items():
+            out["param." + n] = p.numpy()
+    np.savez_compressed(os.path.join(HERE, out_name + ".npz"), **out)
+    print(out_name, info)
 
+
+def beauty_case():
+    known_answer_case("Beauty", "test", "beauty_test", num_attention_heads=1, c=5, alpha=0.7)
 
 
 def dataset_case():
@@ -201,6 +210,11 @@ def dataset_case():
 
 
 if __name__ == "__main__":
+    if "--known-answer-extra" in sys.argv:
+        known_answer_case("LastFM", "test", "lastfm_test", num_attention_heads=1, c=3, alpha=0.9)
+        known_answer_case("LastFM", "valid", "lastfm_valid", store_params=False, num_attention_heads=1, c=3, alpha=0.9)
+        known_answer_case("Beauty", "valid", "beauty_valid", store_params=False, num_attention_heads=1, c=5, alpha=0.7)
+        sys.exit(0)
     if "--dataset-only" in sys.argv:
         dataset_case()
         sys.exit(0)
@@ -211,4 +225,8 @@ if __name__ == "__main__":
     small_case("small_c", 13, B=5, item_size=97, hidden_size=64, max_seq_length=25, num_attention_heads=2,
                num_hidden_layers=3, c=9, alpha=0.3)
     beauty_case()
+    # the second shipped checkpoint (alpha 0.9, c 3 -> 2 kept bins) and the validation split of the first
+    known_answer_case("LastFM", "test", "lastfm_test", num_attention_heads=1, c=3, alpha=0.9)
+    known_answer_case("LastFM", "valid", "lastfm_valid", store_params=False, num_attention_heads=1, c=3, alpha=0.9)
+    known_answer_case("Beauty", "valid", "beauty_valid", store_params=False, num_attention_heads=1, c=5, alpha=0.7)
     dataset_case()

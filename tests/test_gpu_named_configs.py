@@ -118,3 +118,50 @@ def test_c3_full_size_properties(cuda_device):
     # idempotence / sortedness: returned ids are in descending score order
     got_scores = sc.gather(1, top)
     assert bool((got_scores[:, :-1] >= got_scores[:, 1:] - 1e-5 * got_scores.abs().clamp_min(1.0)[:, 1:]).all())
+
+
+def test_c3_benchmarked_configuration_step_vs_oracle(cuda_device):
+    """The EXACT configuration bench.py times — N = 1 M, L = 200, d = 256, H = 4, P = 2, both dropouts 0.5, last block at
+    position L-1 only, CE backward reusing the forward's operand splits, FusedAdam — on a B = 32 slice, against one
+    oracle step (fp32 torch, same dropout masks through DropoutPlan, torch.optim.Adam): loss, every gradient and the
+    updated item table / weights after the optimizer step."""
+    from helpers import make_args
+    from bsarec_b200 import BSARecModel, FusedAdam
+    from bsarec_b200 import functional as Fn
+    assert Fn.LAST_ROW_PATH
+    B, seed = 32, 20261105
+    cfgkw = dict(C3S, item_size=1_000_000)
+    cfg = oracle_cfg(cfgkw, 0.5, 0.5)
+    torch.manual_seed(42)
+    model = BSARecModel(make_args(cfgkw, 0.5, 0.5, batch_size=512)).to(cuda_device).train()
+    P = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    ids, answers = synth_batch(47, B, 200, 1_000_000)
+    model.set_dropout_seed(seed)
+    optim = FusedAdam(model.parameters(), lr=1e-3, betas=(0.9, 0.999), weight_decay=0.0)
+    loss = model.calculate_loss(ids.to(cuda_device), answers.to(cuda_device), None, None, None)
+    optim.zero_grad()
+    loss.backward()
+    got = grads_of(model)
+    # oracle step (the reference's math on the host, ~1 s at B = 32)
+    Q = {k: v.clone().requires_grad_(True) for k, v in P.items()}
+    l32 = oracle.calculate_loss(Q, ids, answers, cfg, train=True, plan=oracle.DropoutPlan(seed))
+    l32.backward()
+    assert abs(loss.item() - float(l32)) < TOL * abs(float(l32))
+    for k, q in Q.items():
+        if k.endswith("key.bias"):
+            assert got[k].abs().max() < 1e-6, k
+            continue
+        ref = q.grad if q.grad is not None else torch.zeros_like(q)
+        assert rel_err(got[k], ref) < 3e-4, (k, rel_err(got[k], ref))       # fp32 reference vs fp32 kernels, no fp64 arbiter at this size
+    optim.step()
+    ref_opt = torch.optim.Adam(list(Q.values()), lr=1e-3, betas=(0.9, 0.999), weight_decay=0.0)
+    ref_opt.step()
+    new = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    for k, q in Q.items():
+        if k.endswith("key.bias"):
+            continue
+        # Adam's first step moves every element by ~lr * sign(g): elements whose gradient is rounding noise may flip sign,
+        # so compare against the step size, and require the bulk to agree tightly
+        diff = (new[k] - q.detach()).abs()
+        assert diff.max().item() <= 2.0e-3 + 1e-9, k
+        assert (diff < 1e-5).float().mean().item() > 0.98, (k, (diff < 1e-5).float().mean().item())

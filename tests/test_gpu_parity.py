@@ -9,7 +9,7 @@ import torch
 
 import oracle
 from conftest import load_golden, golden_params, golden_grads, rel_err
-from helpers import build_model, oracle_cfg, synth_batch, perturbed_params, csr_from_ids
+from helpers import build_model, oracle_cfg, synth_batch, perturbed_params, csr_from_ids, make_args
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-4
@@ -23,8 +23,9 @@ def grads_of(model):
 def check_grads(got, ref64, ref32, tol=TOL):
     """got: CUDA grads; ref64: fp64 oracle; ref32: the fp32 reference (golden) or the fp32 oracle.
     Bar: within tol of the fp32 reference, or within tol of the fp64 value; on cancellation-heavy tensors
-    (key.weight: softmax shift-invariance) where the fp32 reference is itself ~1e-4 from the fp64 value, at
-    least as close to the fp64 value as twice the fp32 reference's own distance."""
+    (attention key.weight and, through it, query.weight: softmax shift-invariance cancels most of the gradient) where the
+    fp32 reference is ITSELF ~1e-4 from the fp64 value, at least as close to the fp64 value as twice the fp32
+    reference's own distance — and never beyond 3e-4, whatever the reference's own error."""
     for k in ref64:
         if k.endswith("key.bias"):     # analytically zero (SURVEY Appendix B #13): absolute bound
             assert got[k].abs().max() < 1e-6, k
@@ -32,7 +33,7 @@ def check_grads(got, ref64, ref32, tol=TOL):
         e64 = rel_err(got[k], ref64[k])
         e32 = rel_err(got[k], ref32[k])
         own = rel_err(ref32[k], ref64[k])
-        assert min(e64, e32) < max(tol, 2 * own), (k, e64, e32, own)
+        assert min(e64, e32) < min(max(tol, 2 * own), 3 * tol), (k, e64, e32, own)
 
 
 @pytest.mark.parametrize("name", SMALL)
@@ -179,6 +180,48 @@ def test_beauty_test_split_metrics_identical_to_reference(cuda_device):
         got += [recall_at_k(ans, pred, k), ndcg_k(ans, pred, k)]
     assert ["%.4f" % v for v in got] == ["0.0736", "0.0523", "0.1008", "0.0611", "0.1373", "0.0703"]
     assert got == pytest.approx(list(data["metrics"]), abs=1e-9)
+
+
+@pytest.mark.parametrize("name,pname,c,alpha,strings", [
+    ("lastfm_test", "lastfm_test", 3, 0.9, ["0.0523", "0.0344", "0.0807", "0.0435", "0.1174", "0.0526"]),      # BSARec_LastFM_best.log:237
+    ("lastfm_valid", "lastfm_test", 3, 0.9, ["0.0706", "0.0479", "0.1037", "0.0582", "0.1615", "0.0727"]),     # :203
+    ("beauty_valid", "beauty_test", 5, 0.7, ["0.0891", "0.0641", "0.1238", "0.0753", "0.1634", "0.0853"]),     # BSARec_Beauty_best.log:224 (CPU run)
+])
+def test_second_checkpoint_and_validation_split_through_trainer(name, pname, c, alpha, strings, cuda_device):
+    """The other shipped checkpoint (LastFM: alpha 0.9, c 3) and the validation splits, through ``bsarec_b200.Trainer``'s
+    eval branch: the whole rating matrix on the device, ``user_ids`` as ``hist_rows`` (no per-batch CSR), ragged last
+    batch, device-side metrics.  Index sets identical to the reference's (near-ties excepted), metrics identical."""
+    import scipy.sparse as sp
+    from bsarec_b200 import Trainer
+    _, data = load_golden(name)
+    _, pdata = load_golden(pname)
+    cfgkw = dict(item_size=int(data["item_size"]), hidden_size=64, max_seq_length=50, num_attention_heads=1,
+                 num_hidden_layers=2, c=c, alpha=alpha)
+    model = build_model(cfgkw, golden_params(pdata), cuda_device, 0.5, 0.5).eval()
+    ids = torch.from_numpy(data["ids"].astype(np.int64))
+    ans = torch.from_numpy(data["answers"].astype(np.int64))
+    U = ids.shape[0]
+    indptr, indices = data["hist_indptr"].astype(np.int64), data["hist_indices"].astype(np.int64)
+    matrix = sp.csr_matrix((np.ones(len(indices)), indices, indptr), shape=(U, cfgkw["item_size"]))
+    args = make_args(cfgkw, 0.5, 0.5)
+    args.train_matrix = matrix
+    args.keep_pred_list = True
+    empty = torch.zeros(0, dtype=torch.int64)
+    # shuffled user order: hist_rows must follow user_ids, not the batch position
+    order = torch.randperm(U, generator=torch.Generator().manual_seed(3))
+    batches = [(order[s:s + 300], ids[order[s:s + 300]], ans[order[s:s + 300]], empty, empty) for s in range(0, U, 300)]
+    tr = Trainer(model, None, None, batches, args, None)
+    scores, info = tr.iteration(0, batches, train=False)
+    pred = np.empty((U, 20), dtype=np.int64)
+    pred[order.numpy()] = tr.pred_list
+    ref = data["pred_list"].astype(np.int64)
+    same_set = np.array([set(a) == set(b) for a, b in zip(pred, ref)])
+    assert np.all(same_set | (data["gap_rel"] < 1e-5)), int((~same_set).sum())
+    assert same_set.mean() > 0.999
+    assert scores == pytest.approx(list(data["metrics"]), abs=1e-9)
+    assert ["%.4f" % v for v in scores] == strings
+    for s in strings:
+        assert s in info
 
 
 @pytest.mark.parametrize("cfgkw,B,p_attn", [

@@ -78,6 +78,8 @@ SIGNATURES = {
     "bsa_sort_scatter_plan": (_I, [_VP, _I64, _I64, _VP, _SZ, _VP, _VP, _VP]),
     "bsa_filter_rank": (_I, [_I, _I]),
     "bsa_build_filter_basis": (_I, [_VP, _I, _I, _VP]),
+    "bsa_set_ce_mode": (None, [_I]),
+    "bsa_get_ce_mode": (_I, []),
     "bsa_set_linear_impl": (None, [_I]),
     "bsa_get_linear_impl": (_I, []),
     "bsa_set_attn_impl": (None, [_I]),

@@ -219,6 +219,8 @@ int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream) {
     return build_filter_basis(basis, L, kept_bins, nullptr, (cudaStream_t)stream);
 }
 
+void bsa_set_ce_mode(int mode) { set_ce_fused(mode); }
+int bsa_get_ce_mode(void) { return get_ce_fused(); }
 void bsa_set_linear_impl(int impl) { set_linear_impl(impl); }
 int bsa_get_linear_impl(void) { return linear_impl(); }
 void bsa_set_attn_impl(int impl) { set_attn_impl(impl); }
@@ -352,8 +354,9 @@ int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* str
 }
 
 int bsa_gather_rows(const int64_t* idx, int64_t n_rows, int64_t src_rows, const float* src, int d, float* dst, void* stream) {
-    BSA_REQUIRE(idx && src && dst, "bsa_gather_rows: null argument");
     BSA_REQUIRE(n_rows >= 0 && src_rows >= 1 && d >= 4, "bsa_gather_rows: bad sizes");
+    if (n_rows == 0) return 0;
+    BSA_REQUIRE(idx && src && dst, "bsa_gather_rows: null argument");
     return gather_rows((const long long*)idx, n_rows, src_rows, src, d, dst, (cudaStream_t)stream);
 }
 

@@ -207,25 +207,49 @@ struct EpiStore {
 };
 
 // ---- online log-sum-exp over the CTA's strip of item tiles (thread = user row)
+// With `logits` set the fp32 logits tile is also written out, row-contiguous through a per-warp staging block (4 rows x
+// 128 B per store instruction): the backward pass reads it back instead of recomputing s E^T (ce_bwd_logits.cuh).
 template <int BN>
 struct EpiLse {
-    struct Params { const long long* answers; float* part_m; float* part_s; float* tgt; };
-    static constexpr int SMEM_BYTES = 0;
-    static constexpr int WARPS = 4;
+    struct Params { const long long* answers; float* part_m; float* part_s; float* tgt; float* logits; long long ld; };
+    static constexpr int WARPS = 8;                      // two warps per TMEM lane quarter, each owning half of the tile's columns
+    static constexpr int SMEM_BYTES = WARPS * 4096;
     const Params& p; const GemmCore& g; int rit;
+    float4* stg; int quarter, half, lane;
     float m = -INFINITY, s = 0.f;
     long long ans = -1;
-    __device__ EpiLse(const Params& p_, const GemmCore& g_, unsigned char*, int epi_warp, int lane) : p(p_), g(g_), rit(epi_warp * 32 + lane) {
+    __device__ EpiLse(const Params& p_, const GemmCore& g_, unsigned char* smem, int epi_warp, int lane_)
+        : p(p_), g(g_), rit((epi_warp & 3) * 32 + lane_), stg(reinterpret_cast<float4*>(smem) + epi_warp * 256),
+          quarter(epi_warp & 3), half(epi_warp >> 2), lane(lane_) {
         const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
         if (row < g.M) ans = p.answers[row];
     }
     __device__ void tile(uint32_t acc, const TileCoord& tc) {
         const int n0 = tc.n * BN;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
             float v[32];
             tmem_ld32(acc + c0, v);
             if (n0 + c0 >= g.N) continue;
+            if (p.logits) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                __syncwarp();
+                const int sub = lane >> 3, c4 = lane & 7;
+                const int col = n0 + c0 + c4 * 4;
+                const long long row0 = (long long)tc.m * BM + quarter * 32;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const int r = t * 4 + sub;
+                    const float4 x = stg[r * 8 + (c4 ^ (r & 7))];
+                    if (row0 + r < g.M && col < g.N) {
+                        float* dst = p.logits + (row0 + r) * p.ld + col;
+                        if (col + 3 < g.N) *reinterpret_cast<float4*>(dst) = x;
+                        else { const float xs[4] = {x.x, x.y, x.z, x.w}; for (int e = 0; e < 4; ++e) if (col + e < g.N) dst[e] = xs[e]; }
+                    }
+                }
+                __syncwarp();
+            }
             float cm = -INFINITY;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
@@ -248,10 +272,10 @@ struct EpiLse {
             }
         }
     }
-    __device__ void finish() {
+    __device__ void finish() {       // one (max, sum) partial per (strip, column half) and user
         const int m_tile = blockIdx.x % g.m_tiles, strip = blockIdx.x / g.m_tiles;
         const long long row = (long long)m_tile * BM + rit;
-        if (row < g.M) { p.part_m[(long long)strip * g.M + row] = m; p.part_s[(long long)strip * g.M + row] = s; }
+        if (row < g.M) { p.part_m[(long long)(strip * 2 + half) * g.M + row] = m; p.part_s[(long long)(strip * 2 + half) * g.M + row] = s; }
     }
 };
 
@@ -407,6 +431,7 @@ struct EpiCeGrad {
 }  // namespace
 }  // namespace bsa
 #include "ce_grad_ds.cuh"
+#include "ce_bwd_logits.cuh"
 namespace bsa {
 namespace {
 
@@ -598,10 +623,17 @@ constexpr int CE_STAGES = 3;
 
 struct CeWs {
     float *s_hi, *s_lo, *e_hi, *e_lo, *part_m, *part_s, *tgt;
+    float *logits, *lse_pad;      // stored logits S [B, ld] (forward -> backward) and lse padded to a multiple of 128; null if not eligible
+    long long ld;
     float *g_hi, *g_lo, *partial;
     int nstrips, chunk;
     size_t bytes;
 };
+
+// the logits-storing CE (forward writes S, backward reads it: ce_bwd_logits.cuh) needs the 256-column accumulator shape
+bool ce_logits_eligible(int B, int d, long long N) {
+    return d > 128 && d <= CBL_ND && (d & 3) == 0 && N < (1ll << 31) - 256 && B >= 1;
+}
 
 int ce_strips(int B) {
     const int m_tiles = cdiv(B, BM);
@@ -630,8 +662,14 @@ CeWs carve_ce(void* ws, int B, int d, long long N, bool bwd) {
     w.s_hi = take((size_t)B * d * 4); w.s_lo = take((size_t)B * d * 4);
     w.e_hi = take((size_t)N * d * 4); w.e_lo = take((size_t)N * d * 4);
     w.nstrips = ce_strips(B);
-    w.part_m = take((size_t)w.nstrips * B * 4); w.part_s = take((size_t)w.nstrips * B * 4);
+    w.part_m = take((size_t)2 * w.nstrips * B * 4); w.part_s = take((size_t)2 * w.nstrips * B * 4);      // (strip, column half) partials
     w.tgt = take((size_t)B * 4);
+    w.logits = w.lse_pad = nullptr;
+    w.ld = (N + 31) / 32 * 32;
+    if (ce_logits_eligible(B, d, N)) {
+        w.logits = take((size_t)B * w.ld * 4);
+        w.lse_pad = take((size_t)((B + 127) / 128 * 128) * 4);
+    }
     w.chunk = ce_bwd_chunk(B, N);
     if (bwd) {
         w.g_hi = take((size_t)B * w.chunk * 4); w.g_lo = take((size_t)B * w.chunk * 4);
@@ -669,8 +707,45 @@ __global__ void ce_combine_kernel(const float* __restrict__ part_m, const float*
 }
 }  // namespace
 
-int g_ce_fused = 1;      // 1: gradient tile + ds in one kernel (ce_grad_ds.cuh) where d allows; 0: separate GEMMs
-void set_ce_fused(int on) { g_ce_fused = on ? 1 : 0; }
+// 2: forward stores the logits, backward = two A-from-TMEM kernels over them (ce_bwd_logits.cuh), where d allows and the
+//    backward receives the forward's workspace; 1: logits recomputed, gradient tile + ds in one kernel (ce_grad_ds.cuh);
+// 0: logits recomputed, separate GEMMs
+int g_ce_fused = 2;
+void set_ce_fused(int mode) { g_ce_fused = mode < 0 ? 0 : (mode > 2 ? 2 : mode); }
+int get_ce_fused() { return g_ce_fused; }
+
+namespace {
+// ds[u,:] -= scale * E[ans[u],:]  — the "- onehot" part of (softmax - onehot) for the user-side gradient (one block per user)
+__global__ void ce_onehot_fix_ds_kernel(float* __restrict__ ds, const float* __restrict__ E, const long long* __restrict__ answers,
+                                        const float* __restrict__ d_loss, int B, int d, long long N) {
+    const int u = blockIdx.x;
+    const long long a = answers[u];
+    if (a < 0 || a >= N) return;
+    const float scale = __ldg(d_loss) / (float)B;
+    for (int c = threadIdx.x; c < d; c += blockDim.x) ds[(long long)u * d + c] -= scale * E[a * d + c];
+}
+// dE[ans[u],:] -= scale * s[u,:]  — the item-side part.  Users that share an answer are handled by the block of the FIRST
+// such user, in ascending user order, so the result does not depend on scheduling (no atomics).
+__global__ void ce_onehot_fix_de_kernel(float* __restrict__ dE, const float* __restrict__ s, const long long* __restrict__ answers,
+                                        const float* __restrict__ d_loss, int B, int d, long long N) {
+    const int u = blockIdx.x;
+    const long long a = answers[u];
+    if (a < 0 || a >= N) return;
+    int earlier = 0;
+    for (int v = threadIdx.x; v < u; v += blockDim.x) earlier |= (answers[v] == a);
+    if (__syncthreads_or(earlier)) return;
+    const float scale = __ldg(d_loss) / (float)B;
+    for (int c = threadIdx.x; c < d; c += blockDim.x) {
+        float acc = 0.f;
+        for (int v = u; v < B; ++v) if (answers[v] == a) acc += s[(long long)v * d + c];
+        dE[a * d + c] -= scale * acc;
+    }
+}
+__global__ void pad_copy_kernel(const float* __restrict__ src, float* __restrict__ dst, int n, int n_pad) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_pad) dst[i] = i < n ? src[i] : 0.f;
+}
+}  // namespace
 
 bool umma_ce_supported(int B, int d, long long N) { return B >= 1 && d % 4 == 0 && d >= 4 && N >= 1; }
 
@@ -688,12 +763,12 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
     if ((rc = make_core(g, B, (int)N, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;
     int nstrips = w.nstrips;
     if (nstrips > g.n_tiles) nstrips = g.n_tiles;
-    EpiLse<CE_BN>::Params ep{answers, w.part_m, w.part_s, w.tgt};
+    EpiLse<CE_BN>::Params ep{answers, w.part_m, w.part_s, w.tgt, g_ce_fused == 2 ? w.logits : nullptr, w.ld};
     {
         ProfScope prof(PROF_CE_FWD_UMMA, st, 2.0 * B * (double)N * d);
         if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiLse<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;
     }
-    ce_combine_kernel<<<1, 256, 0, st>>>(w.part_m, w.part_s, w.tgt, nstrips, B, lse, loss);
+    ce_combine_kernel<<<1, 256, 0, st>>>(w.part_m, w.part_s, w.tgt, 2 * nstrips, B, lse, loss);
     BSA_LAUNCH_CHECK();
     return 0;
 }
@@ -708,12 +783,52 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
         if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
     }
     ProfScope prof(PROF_CE_BWD_UMMA, st, 4.0 * B * (double)N * d);
+    if (g_ce_fused == 2 && reuse_split && w.logits) {
+        // ---- logits left by the forward pass: ds and dE each by one A-from-TMEM kernel, then the onehot rows
+        static bool configured = false;
+        if (!configured) {
+            BSA_CHECK_CUDA(cudaFuncSetAttribute(ce_bwd_logits_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CBL_SMEM));
+            BSA_CHECK_CUDA(cudaFuncSetAttribute(ce_bwd_logits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CBL_SMEM));
+            configured = true;
+        }
+        const int b_pad = (B + 127) / 128 * 128;
+        pad_copy_kernel<<<cdiv(b_pad, 256), 256, 0, st>>>(lse, w.lse_pad, B, b_pad);
+        BSA_LAUNCH_CHECK();
+        const int m_tiles = cdiv(B, BM), n_tiles = (int)((N + BM - 1) / BM);
+        int nstrips = ce_strips(B);
+        if (nstrips > 64) nstrips = 64;
+        if (nstrips > n_tiles) nstrips = n_tiles;
+        CeBwdLogitsParams up;        // user owner: ds partial slabs
+        if ((rc = make_tmap_2d(&up.s_map, w.logits, B, N, w.ld, BM, false))) return rc;
+        if ((rc = make_tmap_2d(&up.b_hi, w.e_hi, N, d, d, BK, true))) return rc;
+        if ((rc = make_tmap_2d(&up.b_lo, w.e_lo, N, d, d, BK, true))) return rc;
+        up.B = B; up.N = (int)N; up.d = d; up.owner_tiles = m_tiles; up.n_tiles = n_tiles; up.nstrips = nstrips;
+        up.lse = w.lse_pad; up.d_loss = d_loss; up.out = w.partial;
+        ce_bwd_logits_kernel<false><<<nstrips * m_tiles, CBL_THREADS, CBL_SMEM, st>>>(up);
+        BSA_LAUNCH_CHECK();
+        CeBwdLogitsParams ip;        // item owner: dE tiles
+        if ((rc = make_tmap_2d(&ip.s_map, w.logits, B, N, w.ld, CBL_SUB, false))) return rc;
+        if ((rc = make_tmap_2d(&ip.b_hi, w.s_hi, B, d, d, BK, true))) return rc;
+        if ((rc = make_tmap_2d(&ip.b_lo, w.s_lo, B, d, d, BK, true))) return rc;
+        ip.B = B; ip.N = (int)N; ip.d = d; ip.owner_tiles = n_tiles; ip.n_tiles = n_tiles; ip.nstrips = 1;
+        ip.lse = w.lse_pad; ip.d_loss = d_loss; ip.out = dE;
+        ce_bwd_logits_kernel<true><<<n_tiles < num_sms() ? n_tiles : num_sms(), CBL_THREADS, CBL_SMEM, st>>>(ip);
+        BSA_LAUNCH_CHECK();
+        const long long MN = (long long)B * d;
+        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, nstrips, 1.f, 0);
+        BSA_LAUNCH_CHECK();
+        ce_onehot_fix_ds_kernel<<<B, 256, 0, st>>>(ds, E, answers, d_loss, B, d, N);
+        BSA_LAUNCH_CHECK();
+        ce_onehot_fix_de_kernel<<<B, 256, 0, st>>>(dE, s, answers, d_loss, B, d, N);
+        BSA_LAUNCH_CHECK();
+        return 0;
+    }
     const int BNd = d > 128 ? 256 : 128;
     // ds = G E: partial sums stay in `partial` ACROSS chunks and are reduced once at the end
     int ds_splits = num_sms() / (cdiv(B, BM) * cdiv(d, BNd));
     if (ds_splits > 64) ds_splits = 64;
     if (ds_splits < 1) ds_splits = 1;
-    const bool fused = g_ce_fused && d > 128 && d <= CGD_ND && (d & 3) == 0;     // gradient tile + ds in one kernel
+    const bool fused = g_ce_fused >= 1 && d > 128 && d <= CGD_ND && (d & 3) == 0;     // gradient tile + ds in one kernel
     int used_splits = 0;
     bool first = true;
     if (fused) {

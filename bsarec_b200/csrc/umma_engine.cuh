@@ -11,6 +11,9 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
 int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, const float* lse,
                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st);
 
+void set_ce_fused(int mode);
+int get_ce_fused();
+
 bool umma_topk_supported(int B, int d, int k, long long rows);
 size_t umma_topk_workspace_bytes(int B, int d, int k, long long rows);
 int umma_score_topk(int B, int d, int k, long long rows, long long offset, const float* s, const float* E,

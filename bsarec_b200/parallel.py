@@ -144,7 +144,7 @@ def sharded_full_sort_topk(s_local: torch.Tensor, item_shard: torch.Tensor, shar
     candidates from every shard to the rank that owns the user (k*(4+8) bytes per user per shard on the wire — an
     all-gather would deliver every rank world times more than it merges).
     Returns int64 [B_local, k] for this rank's users (and the merged scores with ``return_values``)."""
-    world = dist.get_world_size(group)
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
     Bl = s_local.shape[0]
     if world == 1:
         val, idx = score_fn(s_local, item_shard, hist_indptr_all, hist_indices_all, k, shard_offset)

@@ -134,6 +134,12 @@ typedef struct {
 int bsa_filter_rank(int L, int kept_bins);
 int bsa_build_filter_basis(float* basis, int L, int kept_bins, void* stream);
 
+/* how the tcgen05 cross-entropy backward gets its logits: 2 (default) = bsa_ce_fwd leaves the fp32 logits in the workspace
+ * and bsa_ce_bwd (called with that workspace, reuse_split = 1) reads them back — ds and dE by one A-from-TMEM kernel each;
+ * 1 = logits recomputed, gradient tile + ds fused; 0 = logits recomputed, separate GEMMs.  Process-wide; set it before
+ * the forward call.  Modes 1 and 0 stay as the on-GPU cross-checks of mode 2. */
+void bsa_set_ce_mode(int mode);
+int bsa_get_ce_mode(void);
 /* where the block's nn.Linear contractions run: 2 = tcgen05 3xTF32 engine (default), 1 = fp32 FFMA kernels
  * (the on-GPU cross-check).  Process-wide. */
 void bsa_set_linear_impl(int impl);

@@ -85,6 +85,40 @@ def test_fused_cross_entropy_fwd_bwd(B, d, N, cuda_device):
         assert rel_err(dE, Ed.grad) < 1e-5, impl
 
 
+@pytest.mark.parametrize("B,d,N", [(512, 256, 20000), (77, 256, 333), (300, 192, 40000), (129, 256, 65), (64, 132, 12102),
+                                   (1000, 256, 5000)])
+def test_ce_backward_modes_agree(B, d, N, cuda_device):
+    """The three tcgen05 cross-entropy backward paths — 2: logits stored by the forward, ds / dE by the A-from-TMEM
+    kernels of ce_bwd_logits.cuh (+ onehot rows); 1: logits recomputed, fused gradient-tile + ds kernel; 0: separate
+    GEMMs — against fp64, including duplicate answers (several users with the same target item), ragged user and item
+    tiles, and bit-reproducibility of mode 2."""
+    from bsarec_b200 import _cabi
+    lib = _cabi.load()
+    g = torch.Generator().manual_seed(B * 7 + d + N)
+    s = torch.randn(B, d, generator=g) * 1.5
+    E = torch.randn(N, d, generator=g) * 0.3
+    ans = torch.randint(1, N, (B,), generator=g)
+    ans[0] = N - 1
+    ans[1:6] = ans[7]                               # shared target: the onehot fix must sum them deterministically
+    sd, Ed = s.double().requires_grad_(True), E.double().requires_grad_(True)
+    ref_loss = torch.nn.functional.cross_entropy(sd @ Ed.t(), ans)
+    (1.7 * ref_loss).backward()
+    old = lib.bsa_get_ce_mode()
+    try:
+        outs = {}
+        for mode in (2, 1, 0, 2):
+            lib.bsa_set_ce_mode(mode)
+            loss, lse, ds, dE = _ce(2, s.to(cuda_device), E.to(cuda_device), ans.to(cuda_device), 1.7, True)
+            assert abs(float(loss) - float(ref_loss)) < 2e-6 * abs(float(ref_loss)), mode
+            assert rel_err(ds, sd.grad) < 1e-5, (mode, rel_err(ds, sd.grad))
+            assert rel_err(dE, Ed.grad) < 1e-5, (mode, rel_err(dE, Ed.grad))
+            if mode == 2 and 2 in outs:
+                assert torch.equal(ds, outs[2][0]) and torch.equal(dE, outs[2][1])      # bit-reproducible
+            outs[mode] = (ds, dE)
+    finally:
+        lib.bsa_set_ce_mode(old)
+
+
 def _topk(impl, s, E, indptr, indices, k, offset=0):
     from bsarec_b200 import functional as Fn
     val, idx = Fn.score_topk(s, E, indptr, indices, k, offset, impl)

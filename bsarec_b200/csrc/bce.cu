@@ -1,0 +1,121 @@
+// Pairwise binary cross-entropy at the last position — the loss of the sibling model SASRec
+// (model/sasrec.py:42-63): pos/neg logits = <E[pos_b], s_b>, <E[neg_b], s_b>, BCEWithLogits against ones / zeros, each
+// averaged over the users whose positive id is not padding.  SURVEY.md §8(f) rank 4: the encoder underneath is the
+// BSARec block with the filter branch blended out (alpha = 0), this file is the only new arithmetic.
+// Warp per user, float4 lanes, fixed-order reductions (no atomics) -> bit-reproducible.
+#include "common.cuh"
+#include "rowwise.cuh"
+
+namespace bsa {
+namespace {
+
+inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
+
+__device__ __forceinline__ float warp_sum_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x))); }
+__device__ __forceinline__ float sigmoid_f(float x) { return x >= 0.f ? 1.f / (1.f + expf(-x)) : expf(x) / (1.f + expf(x)); }
+
+// logits[b] = (pos logit, neg logit); one block, warps stride over users; loss = mean_valid softplus(-xp) + mean_valid softplus(xn)
+__global__ void __launch_bounds__(1024) bce_pair_fwd_kernel(const float* __restrict__ s, const float* __restrict__ E,
+                                                             const long long* __restrict__ pos, const long long* __restrict__ neg,
+                                                             int B, int d, long long N, float* __restrict__ logits,
+                                                             float* __restrict__ loss, int* __restrict__ n_valid) {
+    __shared__ float sh_p[32], sh_n[32];
+    __shared__ int sh_c[32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    float lp = 0.f, ln = 0.f;
+    int cnt = 0;
+    for (int b = warp; b < B; b += nw) {
+        long long ip = pos[b], in = neg[b];
+        if (ip < 0 || ip >= N) ip = 0;
+        if (in < 0 || in >= N) in = 0;
+        const float4* sv = reinterpret_cast<const float4*>(s + (long long)b * d);
+        const float4* ep = reinterpret_cast<const float4*>(E + ip * d);
+        const float4* en = reinterpret_cast<const float4*>(E + in * d);
+        float xp = 0.f, xn = 0.f;
+        for (int c = lane; c < d / 4; c += 32) {
+            const float4 a = sv[c], p4 = __ldg(ep + c), n4 = __ldg(en + c);
+            xp += a.x * p4.x + a.y * p4.y + a.z * p4.z + a.w * p4.w;
+            xn += a.x * n4.x + a.y * n4.y + a.z * n4.z + a.w * n4.w;
+        }
+        xp = warp_sum_f(xp); xn = warp_sum_f(xn);
+        if (lane == 0) { logits[2 * b] = xp; logits[2 * b + 1] = xn; }
+        if (pos[b] != 0) { lp += softplus_f(-xp); ln += softplus_f(xn); ++cnt; }     // sasrec.py:58: indices = pos_ids != 0
+    }
+    if (lane == 0) { sh_p[warp] = lp; sh_n[warp] = ln; sh_c[warp] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float tp = 0.f, tn = 0.f;
+        int c = 0;
+        for (int w = 0; w < nw; ++w) { tp += sh_p[w]; tn += sh_n[w]; c += sh_c[w]; }
+        *n_valid = c;
+        *loss = c > 0 ? tp / (float)c + tn / (float)c : nanf("");        // torch: mean over an empty selection is nan
+    }
+}
+
+// ds[b,:] = gp E[pos_b] + gn E[neg_b]; rows[b,:] = gp s_b (-> dE[pos_b]), rows[B+b,:] = gn s_b (-> dE[neg_b]); ids2 = (pos, neg)
+// with users whose positive is padding zeroed out (id 0 rows are skipped by the scatter-add: padding_idx = 0).
+__global__ void __launch_bounds__(256) bce_pair_bwd_kernel(const float* __restrict__ s, const float* __restrict__ E,
+                                                            const long long* __restrict__ pos, const long long* __restrict__ neg,
+                                                            const float* __restrict__ logits, const int* __restrict__ n_valid,
+                                                            const float* __restrict__ d_loss, int B, int d, long long N,
+                                                            float* __restrict__ ds, float* __restrict__ rows, long long* __restrict__ ids2) {
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (b >= B) return;
+    const bool ok = pos[b] != 0 && *n_valid > 0;
+    const float g = ok ? __ldg(d_loss) / (float)(*n_valid) : 0.f;
+    const float gp = (sigmoid_f(logits[2 * b]) - 1.f) * g, gn = sigmoid_f(logits[2 * b + 1]) * g;
+    long long ip = pos[b], in = neg[b];
+    if (ip < 0 || ip >= N) ip = 0;
+    if (in < 0 || in >= N) in = 0;
+    if (lane == 0) { ids2[b] = ok ? ip : 0; ids2[B + b] = ok ? in : 0; }
+    const float4* sv = reinterpret_cast<const float4*>(s + (long long)b * d);
+    const float4* ep = reinterpret_cast<const float4*>(E + ip * d);
+    const float4* en = reinterpret_cast<const float4*>(E + in * d);
+    float4* dso = reinterpret_cast<float4*>(ds + (long long)b * d);
+    float4* rp = reinterpret_cast<float4*>(rows + (long long)b * d);
+    float4* rn = reinterpret_cast<float4*>(rows + (long long)(B + b) * d);
+    for (int c = lane; c < d / 4; c += 32) {
+        const float4 a = sv[c], p4 = __ldg(ep + c), n4 = __ldg(en + c);
+        dso[c] = make_float4(gp * p4.x + gn * n4.x, gp * p4.y + gn * n4.y, gp * p4.z + gn * n4.z, gp * p4.w + gn * n4.w);
+        rp[c] = make_float4(gp * a.x, gp * a.y, gp * a.z, gp * a.w);
+        rn[c] = make_float4(gn * a.x, gn * a.y, gn * a.z, gn * a.w);
+    }
+}
+
+}  // namespace
+
+size_t bce_pair_workspace_bytes(int B, int d) {
+    return al((size_t)2 * B * 4) + al(16) + al((size_t)2 * B * d * 4) + al((size_t)2 * B * 8) + scatter_plan_bytes(2ll * B) + 1024;
+}
+
+int bce_pair_fwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
+                 float* loss, void* ws, cudaStream_t st) {
+    BSA_REQUIRE(d % 4 == 0, "bce_pair: hidden size must be a multiple of 4");
+    float* logits = (float*)ws;
+    int* n_valid = (int*)((char*)ws + al((size_t)2 * B * 4));
+    bce_pair_fwd_kernel<<<1, 1024, 0, st>>>(s, E, pos, neg, B, d, N, logits, loss, n_valid);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int bce_pair_bwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
+                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st) {
+    BSA_REQUIRE(ws_bytes >= bce_pair_workspace_bytes(B, d), "bce_pair_bwd: workspace too small");
+    char* p = (char*)ws;
+    float* logits = (float*)p; p += al((size_t)2 * B * 4);
+    int* n_valid = (int*)p; p += al(16);
+    float* rows = (float*)p; p += al((size_t)2 * B * d * 4);
+    long long* ids2 = (long long*)p; p += al((size_t)2 * B * 8);
+    bce_pair_bwd_kernel<<<cdiv(B, 8), 256, 0, st>>>(s, E, pos, neg, logits, n_valid, d_loss, B, d, N, ds, rows, ids2);
+    BSA_LAUNCH_CHECK();
+    int rc = scatter_plan(ids2, 2ll * B, N, p, scatter_plan_bytes(2ll * B), st);
+    if (rc) return rc;
+    return scatter_add_rows(p, 2ll * B, rows, dE, d, st);       // dE accumulated: the caller zeroes it once per step
+}
+
+}  // namespace bsa

@@ -346,6 +346,26 @@ int bsa_gemm(int impl, int M, int N, int K, const float* A, int64_t lda, int a_m
                      nullptr, alpha, accumulate, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------------------------------ sibling model loss
+size_t bsa_bce_pair_workspace_bytes(int B, int d) { return al(bce_pair_workspace_bytes(B, d)); }
+
+int bsa_bce_pair_fwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
+                     const int64_t* neg_ids, float* loss, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(seq_out && item_emb && pos_ids && neg_ids && loss && workspace, "bsa_bce_pair_fwd: null argument");
+    BSA_REQUIRE(B >= 1 && workspace_bytes >= bce_pair_workspace_bytes(B, d), "bsa_bce_pair_fwd: workspace too small");
+    return bce_pair_fwd(B, d, item_size, seq_out, item_emb, (const long long*)pos_ids, (const long long*)neg_ids, loss, workspace,
+                        (cudaStream_t)stream);
+}
+
+int bsa_bce_pair_bwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
+                     const int64_t* neg_ids, const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace,
+                     size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(seq_out && item_emb && pos_ids && neg_ids && d_loss && d_seq_out && d_item_emb && workspace,
+                "bsa_bce_pair_bwd: null argument");
+    return bce_pair_bwd(B, d, item_size, seq_out, item_emb, (const long long*)pos_ids, (const long long*)neg_ids, d_loss,
+                        d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------------------------------ utilities
 int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* stream) {
     BSA_REQUIRE(src && dst, "bsa_gather_last: null argument");

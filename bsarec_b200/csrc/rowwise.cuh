@@ -87,6 +87,12 @@ int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, cons
 // dst[b*L + (L-1)][:] = src[b][:], everything else 0
 int scatter_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st);
 int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st);
+// pairwise BCE at the last position (SASRec's loss, model/sasrec.py:42-63): bce.cu
+size_t bce_pair_workspace_bytes(int B, int d);
+int bce_pair_fwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
+                 float* loss, void* ws, cudaStream_t st);
+int bce_pair_bwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
+                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st);
 int gather_rows(const long long* idx, long long M, long long src_rows, const float* src, int d, float* dst, cudaStream_t st);
 
 }  // namespace bsa

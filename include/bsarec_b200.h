@@ -283,6 +283,20 @@ int bsa_build_batch(int mode, const int64_t* seq_indptr, const int64_t* seq_item
 int bsa_hit_rank_hist(const int64_t* pred, const int64_t* answers, int64_t U, int k, int64_t* hist, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Sibling model on the same kernels: SASRec = the block with the filter branch blended out
+ * (alpha = 0) + this pairwise BCE at the last position, replacing SASRecModel.calculate_loss (model/sasrec.py:42-63):
+ *   xp_b = <E[pos_b], s_b>, xn_b = <E[neg_b], s_b>; loss = mean_{pos_b != 0} softplus(-xp_b) + mean_{pos_b != 0} softplus(xn_b).
+ * fwd keeps the logits in `workspace` for bwd (same workspace); bwd OVERWRITES d_seq_out [B,d] and ACCUMULATES the 2B
+ * gathered-row gradients into d_item_emb through the sorted atomic-free scatter (id 0 skipped: padding_idx).
+ * ---------------------------------------------------------------------------------------------- */
+size_t bsa_bce_pair_workspace_bytes(int B, int d);
+int bsa_bce_pair_fwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
+                     const int64_t* neg_ids, float* loss, void* workspace, size_t workspace_bytes, void* stream);
+int bsa_bce_pair_bwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
+                     const int64_t* neg_ids, const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Small utilities shared by the host wrappers
  * ---------------------------------------------------------------------------------------------- */
 /* dst [B,d] = src[:, L-1, :] */

@@ -2,12 +2,12 @@
 
 ``MODEL_DICT["bsarec"]`` mirrors ``src/model/__init__.py:10-11`` of the reference.
 """
-from .model import BSARecModel
+from .model import BSARecModel, SASRecModel
 from .trainer import Trainer
 from .optim import FusedAdam
 from .data import SequenceStore, DeviceBatchLoader, HitRankAccumulator
 
-MODEL_DICT = {"bsarec": BSARecModel}
+MODEL_DICT = {"bsarec": BSARecModel, "sasrec": SASRecModel}
 
-__all__ = ["BSARecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
+__all__ = ["BSARecModel", "SASRecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
            "HitRankAccumulator"]

@@ -393,3 +393,62 @@ class FusedLoss(torch.autograd.Function):
             ex.finish(ctx.ex_state, flat, dz, gE, scatter_add_rows, gather_rows)
         ctx.state = None
         return (None,) * 8 + tuple(grads[n] for n in names)
+
+
+def bce_pair_forward(s: torch.Tensor, E: torch.Tensor, pos: torch.Tensor, neg: torch.Tensor):
+    """-> (loss 0-dim, workspace): pairwise BCE at the last position (sasrec.py:46-61) by ``bsa_bce_pair_fwd``."""
+    lib = _cabi.load()
+    B, d = s.shape
+    pos = _require_cuda(pos, "answers", torch.int64)
+    neg = _require_cuda(neg, "neg_answers", torch.int64)
+    with torch.cuda.device(s.device):
+        wsb = lib.bsa_bce_pair_workspace_bytes(B, d)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
+        loss = torch.empty((), dtype=torch.float32, device=s.device)
+        check(lib.bsa_bce_pair_fwd(B, d, E.shape[0], _ptr(s), _ptr(E), _ptr(pos), _ptr(neg), _ptr(loss), _ptr(ws), wsb,
+                                   _stream()), "bsa_bce_pair_fwd")
+    return loss, ws
+
+
+def bce_pair_backward(s, E, pos, neg, d_loss, dE: torch.Tensor, ws: torch.Tensor) -> torch.Tensor:
+    """Accumulates the gathered-row gradients into dE [N,d]; returns ds [B,d]."""
+    lib = _cabi.load()
+    B, d = s.shape
+    with torch.cuda.device(s.device):
+        ds = torch.empty(B, d, dtype=torch.float32, device=s.device)
+        d_loss = d_loss.to(dtype=torch.float32).contiguous()
+        check(lib.bsa_bce_pair_bwd(B, d, E.shape[0], _ptr(s), _ptr(E), _ptr(pos.contiguous()), _ptr(neg.contiguous()),
+                                   _ptr(d_loss), _ptr(ds), _ptr(dE), _ptr(ws), ws.numel(), _stream()), "bsa_bce_pair_bwd")
+    return ds
+
+
+class FusedPairLoss(torch.autograd.Function):
+    """SASRec's calculate_loss (sasrec.py:42-63) as one autograd node: encoder forward (filter branch blended out) ->
+    last position -> pairwise BCE; backward in reverse.  ``names`` are the kernel-side (BSARec-layout) names of
+    ``tensors``; tensors that do not require grad (the constant filter stand-ins) get their gradient dropped."""
+
+    @staticmethod
+    def forward(ctx, hyper: Hyper, names: Sequence[str], ids, pos, neg, training: bool, seed: int, *tensors):
+        params = dict(zip(names, tensors))
+        xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
+        s = xs[-1]
+        loss, ws = bce_pair_forward(s, params["item_embeddings.weight"], pos, neg)
+        ctx.hyper, ctx.names, ctx.state, ctx.s, ctx.pos, ctx.neg, ctx.ws = hyper, names, state, s, pos, neg, ws
+        ctx.save_for_backward(*tensors)
+        return loss
+
+    @staticmethod
+    def backward(ctx, d_loss):
+        tensors = ctx.saved_tensors
+        names, hyper, state = ctx.names, ctx.hyper, ctx.state
+        params = dict(zip(names, tensors))
+        grads, _ = alloc_grads(params)
+        if state.L < params["position_embeddings.weight"].shape[0]:
+            grads["position_embeddings.weight"].zero_()
+        E, gE = params["item_embeddings.weight"], grads["item_embeddings.weight"]
+        gE.zero_()                                       # no dense cross-entropy part here: rows are accumulated into zeros
+        ds = bce_pair_backward(ctx.s, E, ctx.pos, ctx.neg, d_loss, gE, ctx.ws)
+        d_out = ds if state.last_row else scatter_last(ds, state.L)
+        encoder_backward(hyper, params, state, d_out, grads)
+        ctx.state = ctx.ws = None
+        return (None,) * 7 + tuple(grads[n] if t.requires_grad else None for n, t in zip(names, tensors))

@@ -86,6 +86,20 @@ class _Encoder(nn.Module):              # bsarec.py:39-44: one block built, deep
         self.blocks = nn.ModuleList([copy.deepcopy(block) for _ in range(args.num_hidden_layers)])
 
 
+class _TransformerBlock(nn.Module):     # _modules.py:142-151 (SASRec: the attention module IS `layer`)
+    def __init__(self, args):
+        super().__init__()
+        self.layer = _AttentionLayer(args)
+        self.feed_forward = _FeedForward(args)
+
+
+class _TransformerEncoder(nn.Module):   # _modules.py:153-158
+    def __init__(self, args):
+        super().__init__()
+        block = _TransformerBlock(args)
+        self.blocks = nn.ModuleList([copy.deepcopy(block) for _ in range(args.num_hidden_layers)])
+
+
 class BSARecModel(nn.Module):
     def __init__(self, args):
         super().__init__()
@@ -97,11 +111,7 @@ class BSARecModel(nn.Module):
         self.dropout = nn.Dropout(args.hidden_dropout_prob)
         self.item_encoder = _Encoder(args)
         self.apply(self.init_weights)
-        self.ce_impl = 0          # 0 auto | 1 fp32 FFMA | 2 tcgen05 3xTF32   (bsa_ce_desc.impl)
-        self.topk_impl = 0
-        self._fixed_seed: Optional[int] = None
-        self._exchange = None     # parallel.GradExchange when data-parallel training is on
-        self._topk_cache: dict = {}   # scoring workspace kept while the item table is unchanged (functional.score_topk)
+        self._init_runtime()
 
     # ------------------------------------------------------------------ reference-compatible surface
     def init_weights(self, module):
@@ -121,6 +131,13 @@ class BSARecModel(nn.Module):
         xs, _ = Fn.encoder_forward(self._hyper(), self._tensors(), input_ids, self.training, self._next_seed(),
                                    keep_for_backward=False)
         return xs if all_sequence_output else xs[-1]
+
+    def _init_runtime(self):
+        self.ce_impl = 0          # 0 auto | 1 fp32 FFMA | 2 tcgen05 3xTF32   (bsa_ce_desc.impl)
+        self.topk_impl = 0
+        self._fixed_seed = None
+        self._exchange = None     # parallel.GradExchange when data-parallel training is on
+        self._topk_cache = {}     # scoring workspace kept while the item table is unchanged (functional.score_topk)
 
     def predict(self, input_ids, user_ids, all_sequence_output=False):
         return self.forward(input_ids, user_ids, all_sequence_output)
@@ -168,7 +185,7 @@ class BSARecModel(nn.Module):
     def invalidate_eval_cache(self):
         """Forget the split copy of the item table kept for evaluation sweeps.  Called by ``train()`` and
         ``load_state_dict``; call it yourself after writing the table through ``.data`` or a raw pointer."""
-        self._topk_cache.clear()
+        getattr(self, "_topk_cache", {}).clear()
 
     def train(self, mode: bool = True):
         if mode:
@@ -203,3 +220,63 @@ class BSARecModel(nn.Module):
 
     def _tensors(self) -> Dict[str, torch.Tensor]:
         return {n: p.detach() for n, p in self.named_parameters()}
+
+
+class SASRecModel(BSARecModel):
+    """Sibling model on the same kernels: ``SASRecModel`` of ``src/model/sasrec.py:18-63``.
+
+    Same class contract and the reference's own ``state_dict`` keys (``item_encoder.blocks.<l>.layer.{query,key,value,
+    dense,LayerNorm}.*`` — the attention module IS ``layer``, ``_modules.py:142-146`` — and ``feed_forward.*``), same
+    seeded init.  The encoder is the BSARec block with the filter branch blended out: ``alpha = 0`` makes
+    ``alpha * dsp + (1 - alpha) * gsp`` the attention output bit for bit (``0 * finite = 0``, ``1 * x = x``), the filter
+    parameters the kernels still take are constant buffers that never reach the ``state_dict``.  The loss is the pairwise
+    BCE at the last position (``sasrec.py:42-63``) through ``bsa_bce_pair_fwd/bwd``."""
+
+    def __init__(self, args):
+        nn.Module.__init__(self)
+        self.args = args
+        self.item_embeddings = nn.Embedding(args.item_size, args.hidden_size, padding_idx=0)
+        self.position_embeddings = nn.Embedding(args.max_seq_length, args.hidden_size)
+        self.batch_size = args.batch_size
+        self.LayerNorm = TFLayerNorm(args.hidden_size, eps=1e-12)
+        self.dropout = nn.Dropout(args.hidden_dropout_prob)
+        self.item_encoder = _TransformerEncoder(args)
+        self.apply(self.init_weights)
+        d = args.hidden_size
+        self.register_buffer("_f_sqrt_beta", torch.zeros(1, 1, d), persistent=False)
+        self.register_buffer("_f_ln_w", torch.ones(d), persistent=False)
+        self.register_buffer("_f_ln_b", torch.zeros(d), persistent=False)
+        self._init_runtime()
+
+    def _hyper(self) -> Fn.Hyper:
+        a = self.args
+        return Fn.Hyper(item_size=a.item_size, hidden_size=a.hidden_size, max_seq_length=a.max_seq_length,
+                        num_attention_heads=a.num_attention_heads, num_hidden_layers=a.num_hidden_layers,
+                        kept_bins=1, alpha=0.0, p_hidden=float(a.hidden_dropout_prob),
+                        p_attn=float(a.attention_probs_dropout_prob))
+
+    def _kernel_named(self, detach: bool):
+        """[(name the kernels' host code expects (BSARec layout), tensor)] — parameters first-class, filter dummies last."""
+        out = []
+        for n, p in self.named_parameters():
+            if ".layer." in n:
+                n = n.replace(".layer.", ".layer.attention_layer.")
+            out.append((n, p.detach() if detach else p))
+        for l in range(self.args.num_hidden_layers):
+            pre = f"item_encoder.blocks.{l}.layer.filter_layer."
+            out += [(pre + "sqrt_beta", self._f_sqrt_beta), (pre + "LayerNorm.weight", self._f_ln_w),
+                    (pre + "LayerNorm.bias", self._f_ln_b)]
+        return out
+
+    def _tensors(self) -> Dict[str, torch.Tensor]:
+        return dict(self._kernel_named(detach=True))
+
+    def calculate_loss(self, input_ids, answers, neg_answers, same_target, user_ids):
+        """BCE of the positive / negative item against the last position (sasrec.py:42-63); ``same_target`` and
+        ``user_ids`` are accepted and ignored, as in the reference."""
+        if self._exchange is not None:
+            raise RuntimeError("bsarec_b200.SASRecModel: the overlapped data-parallel exchange is BSARec-only; use "
+                               "parallel.allreduce_gradients after backward")
+        named = self._kernel_named(detach=False)
+        return Fn.FusedPairLoss.apply(self._hyper(), [n for n, _ in named], input_ids, answers, neg_answers, self.training,
+                                      self._next_seed(), *[t for _, t in named])

@@ -22,7 +22,7 @@ __all__ = [
     "attention_mask", "layer_norm_tf", "embed", "frequency_layer", "attention_layer",
     "feed_forward", "encode", "calculate_loss", "loss_and_grads", "predict_full",
     "full_sort_topk", "masked_scores", "recall_at_k", "ndcg_k", "full_sort_metrics",
-    "adam_train_step", "eval_step", "param_names",
+    "adam_train_step", "eval_step", "param_names", "encode_sasrec", "sasrec_loss", "sasrec_loss_and_grads",
 ]
 
 
@@ -261,6 +261,42 @@ def loss_and_grads(P, ids, answers, cfg: OracleConfig, train=True, plan=None, us
     loss.backward()
     grads = {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in Q.items()}
     return loss.detach(), grads
+
+
+# ----------------------------------------------------------------------------- sibling model: SASRec
+
+def encode_sasrec(P, ids, cfg: OracleConfig, train=False, plan=None) -> List[torch.Tensor]:
+    """``SASRecModel.forward(all_sequence_output=True)`` (``sasrec.py:27-40``, ``_modules.py:142-172``): the block is
+    MultiHeadAttention -> FeedForward; parameter names are the reference's (``...blocks.<l>.layer.query.weight``)."""
+    dtype = P["item_embeddings.weight"].dtype
+    mask = attention_mask(ids, dtype)
+    x = embed(P, ids, cfg, train, plan)
+    outs = [x]
+    for l in range(cfg.num_hidden_layers):
+        pre = f"item_encoder.blocks.{l}."
+        y = attention_layer(P, pre + "layer.", x, mask, cfg, l, train, plan)
+        x = feed_forward(P, pre + "feed_forward.", y, cfg, l, train, plan)
+        outs.append(x)
+    return outs
+
+
+def sasrec_loss(P, ids, pos, neg, cfg: OracleConfig, train=True, plan=None):
+    """``SASRecModel.calculate_loss`` (``sasrec.py:42-63``): BCE-with-logits of the positive (label 1) and negative
+    (label 0) item against the last position, each averaged over the users whose positive id is not padding."""
+    s = encode_sasrec(P, ids, cfg, train, plan)[-1][:, -1, :]
+    E = P["item_embeddings.weight"]
+    pos_logits = (F.embedding(pos, E, padding_idx=0) * s).sum(-1)
+    neg_logits = (F.embedding(neg, E, padding_idx=0) * s).sum(-1)
+    idx = (pos != 0).nonzero().reshape(-1)
+    loss = F.binary_cross_entropy_with_logits(pos_logits[idx], torch.ones_like(pos_logits[idx]))
+    return loss + F.binary_cross_entropy_with_logits(neg_logits[idx], torch.zeros_like(neg_logits[idx]))
+
+
+def sasrec_loss_and_grads(P, ids, pos, neg, cfg: OracleConfig, train=True, plan=None):
+    Q = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
+    loss = sasrec_loss(Q, ids, pos, neg, cfg, train, plan)
+    loss.backward()
+    return loss.detach(), {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in Q.items()}
 
 
 # ----------------------------------------------------------------------------- evaluation

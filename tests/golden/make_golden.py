@@ -118,6 +118,38 @@ def small_case(name, seed, B, **cfgkw):
     print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
 
 
+def sasrec_case(name, seed, B, **cfgkw):
+    """Sibling model: the reference's SASRecModel (model/sasrec.py) — layer outputs, BCE loss with
+    seeded negative ids (one user's positive is padding: it must drop out of both means), all gradients."""
+    torch.manual_seed(seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    args = make_args(**cfgkw)
+    model = MODEL_DICT["sasrec"](args=args)
+    perturb(model, g)
+    ids, answers = synth_ids(g, B, args.max_seq_length, args.item_size)
+    neg = torch.randint(1, args.item_size, (B,), generator=g)
+    answers[2] = 0
+    model.eval()
+    with torch.no_grad():
+        layers = model.predict(ids, None, all_sequence_output=True)
+    model.train()                      # dropout probs are 0 -> deterministic
+    loss = model.calculate_loss(ids, answers, neg, None, None)
+    model.zero_grad()
+    loss.backward()
+    out = {
+        "cfg_keys": np.array(sorted(cfgkw.keys())),
+        "cfg_vals": np.array([float(cfgkw[k]) for k in sorted(cfgkw.keys())]),
+        "ids": ids.numpy(), "answers": answers.numpy(), "neg": neg.numpy(), "loss": loss.detach().numpy(),
+    }
+    for i, t in enumerate(layers):
+        out[f"layer_out.{i}"] = t.numpy()
+    for n, p in model.named_parameters():
+        out["param." + n] = p.detach().numpy()
+        out["grad." + n] = (p.grad if p.grad is not None else torch.zeros_like(p)).numpy()
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
+
+
 def known_answer_case(data_name, split, out_name, store_params=True, **cfgkw):
     """Known-answer: a shipped checkpoint on a real split through the reference's own Trainer.iteration.
     Beauty/test -> src/output/BSARec_Beauty_best.log:258; LastFM/test -> BSARec_LastFM_best.log:237; the valid split
@@ -210,6 +242,10 @@ def dataset_case():
 
 
 if __name__ == "__main__":
+    if "--sasrec" in sys.argv:
+        sasrec_case("sasrec_small", 17, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
+                    num_hidden_layers=2)
+        sys.exit(0)
     if "--known-answer-extra" in sys.argv:
         known_answer_case("LastFM", "test", "lastfm_test", num_attention_heads=1, c=3, alpha=0.9)
         known_answer_case("LastFM", "valid", "lastfm_valid", store_params=False, num_attention_heads=1, c=3, alpha=0.9)
@@ -229,4 +265,6 @@ if __name__ == "__main__":
     known_answer_case("LastFM", "test", "lastfm_test", num_attention_heads=1, c=3, alpha=0.9)
     known_answer_case("LastFM", "valid", "lastfm_valid", store_params=False, num_attention_heads=1, c=3, alpha=0.9)
     known_answer_case("Beauty", "valid", "beauty_valid", store_params=False, num_attention_heads=1, c=5, alpha=0.7)
+    sasrec_case("sasrec_small", 17, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
+                num_hidden_layers=2)
     dataset_case()

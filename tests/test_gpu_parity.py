@@ -358,3 +358,50 @@ def test_tcgen05_attention_backward_query_owner_matches_mma_sync_kernel(cuda_dev
     for n, g in grads[2].items():
         if not n.endswith("key.bias"):
             assert rel_err(g, g_ref[n]) < TOL, n
+
+
+@pytest.mark.parametrize("last_row", [True, False])
+def test_sasrec_sibling_vs_reference_golden(last_row, cuda_device):
+    """SASRecModel on the BSARec kernels (filter branch blended out, alpha = 0; pairwise BCE by
+    bsa_bce_pair_fwd/bwd) against the reference's SASRecModel: layer outputs, loss, all gradients; then train-mode dropout
+    against the oracle with the same masks."""
+    from bsarec_b200 import SASRecModel
+    from bsarec_b200 import functional as Fn
+    cfgkw, data = load_golden("sasrec_small")
+    P = golden_params(data)
+    model = SASRecModel(make_args(cfgkw))
+    model.load_state_dict({k: v.clone() for k, v in P.items()})
+    model = model.to(cuda_device)
+    ids = torch.from_numpy(data["ids"]).to(cuda_device)
+    pos, neg = torch.from_numpy(data["answers"]).to(cuda_device), torch.from_numpy(data["neg"]).to(cuda_device)
+    old = Fn.LAST_ROW_PATH
+    Fn.LAST_ROW_PATH = last_row
+    try:
+        model.eval()
+        outs = model.predict(ids, None, all_sequence_output=True)
+        for i, o in enumerate(outs):
+            assert rel_err(o.cpu(), data[f"layer_out.{i}"]) < TOL, i
+        model.train()
+        loss = model.calculate_loss(ids, pos, neg, None, None)
+        loss.backward()
+        assert abs(loss.item() - float(data["loss"])) < TOL * abs(float(data["loss"]))
+        cfg = oracle_cfg(cfgkw)
+        _, g64 = oracle.sasrec_loss_and_grads({k: v.double() for k, v in P.items()}, ids.cpu(), pos.cpu(), neg.cpu(), cfg)
+        check_grads(grads_of(model), g64, golden_grads(data))
+        # dropout 0.3 / 0.4 with the kernels' counter RNG restated by the oracle
+        cfg_d = oracle_cfg(cfgkw, 0.3, 0.4)
+        m2 = SASRecModel(make_args(cfgkw, 0.3, 0.4))
+        m2.load_state_dict({k: v.clone() for k, v in P.items()})
+        m2 = m2.to(cuda_device).train()
+        m2.set_dropout_seed(99)
+        l2 = m2.calculate_loss(ids, pos, neg, None, None)
+        l2.backward()
+        l64, g64 = oracle.sasrec_loss_and_grads({k: v.double() for k, v in P.items()}, ids.cpu(), pos.cpu(), neg.cpu(), cfg_d,
+                                                plan=oracle.DropoutPlan(99))
+        _, g32 = oracle.sasrec_loss_and_grads(P, ids.cpu(), pos.cpu(), neg.cpu(), cfg_d, plan=oracle.DropoutPlan(99))
+        assert abs(l2.item() - float(l64)) < TOL * abs(float(l64))
+        check_grads(grads_of(m2), g64, g32)
+        # state_dict stays the reference's: no filter stand-ins leak into it
+        assert sorted(model.state_dict().keys()) == sorted(P.keys())
+    finally:
+        Fn.LAST_ROW_PATH = old

@@ -249,3 +249,48 @@ def test_hit_rank_hist_reproduces_reference_metrics_on_beauty():
     got = [recall[0], ndcg[0], recall[1], ndcg[1], recall[2], ndcg[2]]
     assert got == pytest.approx(list(data["metrics"]), abs=1e-12)
     assert ["%.4f" % v for v in got] == ["0.0736", "0.0523", "0.1008", "0.0611", "0.1373", "0.0703"]
+
+
+def test_sasrec_oracle_vs_reference_golden():
+    """Sibling model: the oracle's SASRec restatement against the reference's SASRecModel —
+    every layer output, the pairwise BCE loss (one user's positive is padding) and all gradients."""
+    cfgkw, data = load_golden("sasrec_small")
+    cfg = OracleConfig(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, **cfgkw)
+    P = golden_params(data)
+    ids = torch.from_numpy(data["ids"])
+    pos, neg = torch.from_numpy(data["answers"]), torch.from_numpy(data["neg"])
+    outs = oracle.encode_sasrec(P, ids, cfg)
+    for i, o in enumerate(outs):
+        assert rel_err(o.detach(), data[f"layer_out.{i}"]) < 1e-5, i
+    loss, grads = oracle.sasrec_loss_and_grads(P, ids, pos, neg, cfg)
+    assert abs(float(loss) - float(data["loss"])) < 1e-6 * abs(float(data["loss"]))
+    ref = golden_grads(data)
+    for k, g in grads.items():
+        if k.endswith("key.bias"):
+            assert g.abs().max() < 1e-6
+            continue
+        assert rel_err(g, ref[k]) < 1e-4, k
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/model"), reason="live reference only in the build container")
+def test_sasrec_container_matches_live_reference_class():
+    """Same state_dict keys / shapes and bit-identical seeded init as the reference's SASRecModel (host side only)."""
+    sys.path.insert(0, "/root/reference/src")
+    try:
+        from model import MODEL_DICT as REF
+        from helpers import make_args
+        import bsarec_b200
+        cfgkw = dict(item_size=123, hidden_size=32, max_seq_length=20, num_attention_heads=2, num_hidden_layers=3)
+        torch.manual_seed(5)
+        ref = REF["sasrec"](args=make_args(cfgkw, 0.5, 0.5))
+        torch.manual_seed(5)
+        ours = bsarec_b200.MODEL_DICT["sasrec"](make_args(cfgkw, 0.5, 0.5))
+        a, b = ref.state_dict(), ours.state_dict()
+        assert list(a.keys()) == list(b.keys())
+        for k in a:
+            assert a[k].shape == b[k].shape and torch.equal(a[k], b[k]), k
+        assert [n for n, _ in ref.named_parameters()] == [n for n, _ in ours.named_parameters()]
+    finally:
+        sys.path.remove("/root/reference/src")
+        for m in [k for k in sys.modules if k == "model" or k.startswith("model.")]:
+            sys.modules.pop(m, None)

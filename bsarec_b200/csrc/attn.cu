@@ -486,7 +486,15 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
     const float scale = 1.0f / sqrtf((float)DH);
     ProfScope prof(PROF_ATTN_BWD, st, 8.0 * B * H * (double)L * L * DH);      // canonical: dP, dV, dQ, dK (no credit for the S / dP recomputation)
     if (g_attn_bwd_umma && g_attn_fwd_umma && attn_umma_supported(L, d, H)) {   // query owner on tcgen05 (dQ, delta)
-        const int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, B, H, L, d, dr, st);
+        if (g_attn_bwd_umma >= 2) {      // ... which also leaves Pd and dS for the tcgen05 key owner (dK, dV): no recomputation
+            const long long NK = (L + 15) / 16 * 16, bhl = (long long)B * H * L;
+            float* pd = delta + (bhl + 63) / 64 * 64;
+            float* ds = pd + bhl * NK;
+            int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, pd, ds, B, H, L, d, dr, st);
+            if (rc) return rc;
+            return attn_bwd_kv_umma(q, dctx, pd, ds, dk, dv, B, H, L, d, st);
+        }
+        const int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, nullptr, nullptr, B, H, L, d, dr, st);
         if (rc) return rc;
     } else {
         attn_bwd_kernel<DH, false><<<grid, AT_THREADS, smem, st>>>(q, k, v, ids, ctx, lse, dctx, dq, nullptr, delta, H, L, d, scale, dr);
@@ -502,7 +510,17 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
 // 1: the forward goes to the tcgen05 kernel where its shape allows (BSA_ATTN_UMMA=0 keeps the mma.sync kernel)
 int g_attn_fwd_umma = [] { const char* e = getenv("BSA_ATTN_UMMA"); return e ? atoi(e) : 1; }();
 // 1: the query-owner half of the backward goes to the tcgen05 kernel too (BSA_ATTN_BWD_UMMA=0 keeps mma.sync)
-int g_attn_bwd_umma = [] { const char* e = getenv("BSA_ATTN_BWD_UMMA"); return e ? atoi(e) : 1; }();
+// 2 (default): the key-owner half too, from the Pd / dS tiles the query owner stores (attn_kv_umma.cu); 1: key owner on mma.sync
+int g_attn_bwd_umma = [] { const char* e = getenv("BSA_ATTN_BWD_UMMA"); return e ? atoi(e) : 2; }();
+
+long long attn_bwd_scratch_floats(int B, int H, int L, int d) {
+    const long long bhl = (long long)B * H * L;
+    if (g_attn_bwd_umma >= 2 && g_attn_fwd_umma && attn_umma_supported(L, d, H)) {
+        const long long NK = (L + 15) / 16 * 16;
+        return (bhl + 63) / 64 * 64 + 2 * bhl * NK + 64;
+    }
+    return bhl;
+}
 
 bool attn_fused_supported(int L, int d, int H) {
     if (H <= 0 || d % H != 0 || d % 4 != 0 || L < 1) return false;

@@ -309,6 +309,7 @@ struct AttnBwdQParams {
     const long long* ids;
     const float* ctx; const float* dctx; const float* lse;
     float* dq; float* delta;
+    float* pd_out; float* ds_out;      // optional [B*H*L, NK] fp32: Pd = P o M and dS, left for the key-owner kernel (attn_kv_umma.cu)
     int H, L, d, NK;
     float scale;
     Dropout dr;
@@ -498,6 +499,8 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     // ========================================================================= dS = P o (dPd o M - delta), back into TMEM
     const float delta = reinterpret_cast<const float*>(smem + AU_OFF_DELTA)[quarter * 32 + lane];
     const bool fast_rng = (pbase & 3ull) == 0ull;
+    float* pd_row = (p.pd_out && row_ok) ? p.pd_out + ((long long)bh * p.L + i) * NK : nullptr;
+    float* ds_row = (p.ds_out && row_ok) ? p.ds_out + ((long long)bh * p.L + i) * NK : nullptr;
 #pragma unroll 1
     for (int c = part; c < nch; c += AUF_PARTS) {
         uint32_t hi[16], lo[16];
@@ -514,23 +517,38 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
 #pragma unroll
                     for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(p.dr, pbase + j0 + e);
                 }
+                float pd4[4], ds4[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const int j = j0 + e;
-                    float ds = 0.f;
+                    float ds = 0.f, pd = 0.f;
                     if (row_ok && j < p.L) {
                         const float sp = vs[g4 * 4 + e] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
                         const float pr = expf((sp - ls.x) - ls.y);
+                        pd = pr * mult[e];
                         ds = pr * (vd[g4 * 4 + e] * mult[e] - delta);
                     }
+                    pd4[e] = pd; ds4[e] = ds;
                     float hh, lw;
                     split_tf32_dev(ds, hh, lw);
                     hi[g4 * 4 + e] = __float_as_uint(hh); lo[g4 * 4 + e] = __float_as_uint(lw);
+                }
+                if (pd_row) {        // 16 contiguous floats per piece: two full 32-byte sectors per row and matrix
+                    *reinterpret_cast<float4*>(pd_row + j0) = make_float4(pd4[0], pd4[1], pd4[2], pd4[3]);
+                    *reinterpret_cast<float4*>(ds_row + j0) = make_float4(ds4[0], ds4[1], ds4[2], ds4[3]);
                 }
             }
         } else {
 #pragma unroll
             for (int e = 0; e < 16; ++e) { hi[e] = 0u; lo[e] = 0u; }
+            if (pd_row) {
+                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int g4 = 0; g4 < 4; ++g4) {
+                    *reinterpret_cast<float4*>(pd_row + c * 16 + g4 * 4) = z;
+                    *reinterpret_cast<float4*>(ds_row + c * 16 + g4 * 4) = z;
+                }
+            }
         }
         tmem_st16(t_s + lane_base + c * 16, hi);
         tmem_st16(t_lo + lane_base + c * 16, lo);
@@ -616,7 +634,8 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
 }
 
 int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
-                    const float* dctx, float* dq, float* delta, int B, int H, int L, int d, Dropout dr, cudaStream_t st) {
+                    const float* dctx, float* dq, float* delta, float* pd_out, float* ds_out, int B, int H, int L, int d,
+                    Dropout dr, cudaStream_t st) {
     BSA_REQUIRE(attn_umma_supported(L, d, H), "attn_bwd_q_umma: unsupported shape (L=%d d=%d H=%d)", L, d, H);
     if (B == 0) return 0;
     static bool configured = false;
@@ -634,6 +653,7 @@ int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long l
     if ((rc = make_tmap_2d(&p.vk, v, rows, d, d, NK / 2, false))) return rc;
     if ((rc = make_tmap_2d(&p.km, k, rows, d, d, 32, true))) return rc;
     p.ids = ids; p.ctx = ctx; p.dctx = dctx; p.lse = lse; p.dq = dq; p.delta = delta;
+    p.pd_out = pd_out; p.ds_out = ds_out;
     p.H = H; p.L = L; p.d = d; p.NK = NK;
     p.scale = 1.0f / sqrtf((float)AU_DH);
     p.dr = dr;

@@ -98,7 +98,7 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     // backward is the larger user: dyb, dd, dzf, dq, dk, dv, dctx [M,d]; dh [M,4d]; Pd, dP [B,H,L,L]
     for (int i = 0; i < 7; ++i) b.f(M * d);
     b.f(M * 4 * d);
-    if (attn_fused_supported(c.L, c.d, c.H) && attn_impl() == 2) b.f((long long)c.B * c.H * c.L);   // delta
+    if (attn_fused_supported(c.L, c.d, c.H) && attn_impl() == 2) b.f(attn_bwd_scratch_floats(c.B, c.H, c.L, c.d));   // delta (+ Pd, dS tiles)
     else { b.f(PL); b.f(PL); }
     // partials: LN gamma/beta, column sums, split-K, beta2
     b.f(3ll * rowwise_partial_blocks(M) * d);
@@ -272,7 +272,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     float* dctx = b.f(M * d);
     float* dh_ = b.f(M * 4 * d);
     float* Pd_ws = s.fused ? nullptr : b.f(PL);
-    float* dP = s.fused ? b.f((long long)B * H * L) : b.f(PL);
+    float* dP = s.fused ? b.f(attn_bwd_scratch_floats(B, H, L, d)) : b.f(PL);
     const int nrb = rowwise_partial_blocks(M);
     float* pgam = b.f((long long)nrb * d);
     float* pbet = b.f((long long)nrb * d);

@@ -10,9 +10,10 @@
 //   (MN-major B operands, 32-B swizzle atom, raw fp32); the 8 converter warps read their key's COLUMN of the two tiles,
 //   split it into TF32 (hi, lo) pairs and store them into TMEM, and split the dO / Q rows in place (hi) / beside (lo);
 //   one elected thread issues dV[128 x 64] += Pd^T[128 x 32] dO[32 x 64] and dK[128 x 64] += dS^T Q (A from TMEM, 3 MMAs
-//   per 8-wide k-step).  Two stages of shared memory and two TMEM pair buffers: block j+1 is converted while block j is
-//   multiplied.  The accumulators leave once, row-contiguous.  No recomputation of exp / dropout here, no atomics.
-// TMEM: buffer b at columns [128 b, 128 b + 128) = Pd hi | Pd lo | dS hi | dS lo (32 each); dV at [256, 320), dK at [320, 384).
+//   per 8-wide k-step).  Three stages of shared memory and three TMEM pair buffers: blocks j+1, j+2 are loaded / converted
+//   while block j is multiplied (the per-block chain TMA -> convert -> MMA is latency-, not throughput-bound).
+//   The accumulators leave once, row-contiguous.  No recomputation of exp / dropout here, no atomics.
+// TMEM: buffer b at columns [128 b, 128 b + 128) = Pd hi | Pd lo | dS hi | dS lo (32 each); dV at [384, 448), dK at [448, 512).
 #include "attn.cuh"
 #include "umma.cuh"
 
@@ -29,7 +30,8 @@ constexpr int KV_OFF_DS = 16384, KV_OFF_DO = 32768, KV_OFF_Q = 40960, KV_OFF_LO 
 constexpr int KV_TX = 32768 + 16384;            // bytes TMA delivers per stage (both tiles + the two raw row blocks)
 constexpr int KV_EPI_WARPS = 8;
 constexpr int KV_THREADS = 128 + 32 * KV_EPI_WARPS;
-constexpr int KV_SMEM = 1024 + 2 * KV_STAGE + 256;
+constexpr int KV_NST = 3;                       // pipeline depth (shared-memory stages == TMEM pair buffers)
+constexpr int KV_SMEM = 1024 + KV_NST * KV_STAGE + 256;
 
 struct AttnBwdKvParams {
     CUtensorMap pd, ds;           // [B*H*L, NK] fp32, box {32 keys, 32 queries}, 128-B swizzle
@@ -50,10 +52,10 @@ __global__ void __launch_bounds__(KV_THREADS, 1)
 attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
     extern __shared__ __align__(1024) unsigned char kv_smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)kv_smem_raw + 1023) & ~(uintptr_t)1023);
-    uint64_t* full_bar = (uint64_t*)(smem + 2 * KV_STAGE);     // stage landed                              (TMA -> converters)
-    uint64_t* g_ready = full_bar + 2;                          // pairs in TMEM, dO / Q rows split           (converters -> MMA)
-    uint64_t* free_bar = g_ready + 2;                          // MMAs reading stage / TMEM buffer retired   (MMA -> TMA)
-    uint64_t* acc_full = free_bar + 2;
+    uint64_t* full_bar = (uint64_t*)(smem + KV_NST * KV_STAGE);   // stage landed                              (TMA -> converters)
+    uint64_t* g_ready = full_bar + KV_NST;                        // pairs in TMEM, dO / Q rows split           (converters -> MMA)
+    uint64_t* free_bar = g_ready + KV_NST;                        // MMAs reading stage / TMEM buffer retired   (MMA -> TMA)
+    uint64_t* acc_full = free_bar + KV_NST;
     uint32_t* tmem_ptr = (uint32_t*)(acc_full + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -65,7 +67,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
 
     if (warp == 0 && elect_one()) { prefetch_tmap(&p.pd); prefetch_tmap(&p.ds); prefetch_tmap(&p.dout); prefetch_tmap(&p.q); }
     if (warp == 1 && elect_one()) {
-        for (int i = 0; i < 2; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&g_ready[i], KV_EPI_WARPS); mbar_init(&free_bar[i], 1); }
+        for (int i = 0; i < KV_NST; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&g_ready[i], KV_EPI_WARPS); mbar_init(&free_bar[i], 1); }
         mbar_init(acc_full, 1);
         fence_barrier_init();
     }
@@ -74,14 +76,14 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    const uint32_t t_dv = tmem_base + 256, t_dk = tmem_base + 320;
+    const uint32_t t_dv = tmem_base + 128 * KV_NST, t_dk = t_dv + KV_DH;
 
     if (warp == 0) {
         // ===================================================================== TMA producer
         if (elect_one()) {
             for (int j = 0; j < nblk; ++j) {
-                const int s = j & 1;
-                mbar_wait(&free_bar[s], (uint32_t)(((j >> 1) & 1) ^ 1));
+                const int s = j % KV_NST;
+                mbar_wait(&free_bar[s], (uint32_t)(((j / KV_NST) & 1) ^ 1));
                 unsigned char* st = smem + s * KV_STAGE;
                 mbar_expect_tx(&full_bar[s], KV_TX);
                 const int grow = (int)((long long)bh * p.L + j * KV_QB);        // row of query j*32 in the [B*H*L, NK] arrays
@@ -104,8 +106,8 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
             constexpr uint32_t IDESC = idesc_tf32(128, KV_DH, false, true);
             uint32_t acc = 0;
             for (int j = 0; j < nblk; ++j) {
-                const int s = j & 1;
-                mbar_wait(&g_ready[s], (uint32_t)((j >> 1) & 1));
+                const int s = j % KV_NST;
+                mbar_wait(&g_ready[s], (uint32_t)((j / KV_NST) & 1));
                 tc_fence_after();
                 const uint32_t tb = tmem_base + (uint32_t)(s * 128);
                 const uint32_t st = smem_u32(smem + s * KV_STAGE);
@@ -135,8 +137,8 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
         const uint32_t lane_base = ((uint32_t)(quarter * 32) << 16);
         const int ct = (warp - 4) * 32 + lane;                           // 0..255 over the converter threads
         for (int j = 0; j < nblk; ++j) {
-            const int s = j & 1;
-            mbar_wait(&full_bar[s], (uint32_t)((j >> 1) & 1));
+            const int s = j % KV_NST;
+            mbar_wait(&full_bar[s], (uint32_t)((j / KV_NST) & 1));
             unsigned char* st = smem + s * KV_STAGE;
             // this thread's key is column `lane` of box `quarter`; the block's 32 queries are its 32 K-columns
             const unsigned char* base = st + half * KV_OFF_DS + quarter * 4096 + ((lane & 3) << 2);

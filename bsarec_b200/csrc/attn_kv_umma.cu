@@ -1,4 +1,4 @@
-// Key-owner half of the attention backward on tcgen05 (dK, dV), for the shapes of attn_umma.cu (head size 64, L <= 208).
+// Key-owner half of the attention backward on tcgen05 (dK, dV), for the shapes of attn_umma.cu (head sizes 64 / 32, L <= 208).
 //
 // dV = Pd^T dO and dK = scale dS^T Q need the TRANSPOSED probability / score-gradient tiles as A operands.  The
 // query-owner kernel (attn_bwd_q_umma_kernel) has both in registers — queries on the TMEM lanes — when it forms dS, so it
@@ -23,7 +23,7 @@ using namespace umma;
 
 namespace {
 
-constexpr int KV_DH = 64;
+constexpr int KV_DH = 64;                       // largest head size (stage layout); instantiated for 64 and 32
 constexpr int KV_QB = 32;                       // queries per block (K of one MMA batch)
 constexpr int KV_STAGE = 64 * 1024;             // Pd tile 16 K | dS tile 16 K | dO hi 8 K | Q hi 8 K | dO lo 8 K | Q lo 8 K
 constexpr int KV_OFF_DS = 16384, KV_OFF_DO = 32768, KV_OFF_Q = 40960, KV_OFF_LO = 16384;    // lo = hi + 16 K
@@ -48,8 +48,10 @@ __device__ __forceinline__ void kv_split(float x, float& hi, float& lo) {
     lo = x - hi;
 }
 
+template <int DH>
 __global__ void __launch_bounds__(KV_THREADS, 1)
 attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
+    constexpr int NCH = DH / 32;                // 32-column slabs of the dO / Q rows
     extern __shared__ __align__(1024) unsigned char kv_smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)kv_smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + KV_NST * KV_STAGE);   // stage landed                              (TMA -> converters)
@@ -62,7 +64,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
     const int bh = blockIdx.x, b = bh / p.H, h = bh - b * p.H;
     const int kt = blockIdx.y;
     const long long seq_base = (long long)b * p.L;
-    const int col0 = h * KV_DH;
+    const int col0 = h * DH;
     const int nblk = (p.L + KV_QB - 1) / KV_QB;
 
     if (warp == 0 && elect_one()) { prefetch_tmap(&p.pd); prefetch_tmap(&p.ds); prefetch_tmap(&p.dout); prefetch_tmap(&p.q); }
@@ -76,7 +78,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    const uint32_t t_dv = tmem_base + 128 * KV_NST, t_dk = t_dv + KV_DH;
+    const uint32_t t_dv = tmem_base + 128 * KV_NST, t_dk = t_dv + KV_DH;      // fixed columns for both head sizes
 
     if (warp == 0) {
         // ===================================================================== TMA producer
@@ -85,7 +87,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
                 const int s = j % KV_NST;
                 mbar_wait(&free_bar[s], (uint32_t)(((j / KV_NST) & 1) ^ 1));
                 unsigned char* st = smem + s * KV_STAGE;
-                mbar_expect_tx(&full_bar[s], KV_TX);
+                mbar_expect_tx(&full_bar[s], 32768 + 2 * NCH * 4096);
                 const int grow = (int)((long long)bh * p.L + j * KV_QB);        // row of query j*32 in the [B*H*L, NK] arrays
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -94,7 +96,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
                 }
                 const int xrow = (int)(seq_base + j * KV_QB);
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
+                for (int c = 0; c < NCH; ++c) {
                     tma_load_2d(st + KV_OFF_DO + c * 4096, &p.dout, &full_bar[s], col0 + c * 32, xrow);
                     tma_load_2d(st + KV_OFF_Q + c * 4096, &p.q, &full_bar[s], col0 + c * 32, xrow);
                 }
@@ -103,7 +105,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
     } else if (warp == 1) {
         // ===================================================================== MMA issuer
         if (elect_one()) {
-            constexpr uint32_t IDESC = idesc_tf32(128, KV_DH, false, true);
+            constexpr uint32_t IDESC = idesc_tf32(128, DH, false, true);
             uint32_t acc = 0;
             for (int j = 0; j < nblk; ++j) {
                 const int s = j % KV_NST;
@@ -178,7 +180,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
         const float mul = half ? p.scale : 1.0f;
         float* dst = (half ? p.dk : p.dv) + (seq_base + (jkey < p.L ? jkey : 0)) * p.d + col0;
 #pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
+        for (int c = 0; c < NCH; ++c) {
             float v[32];
             tmem_ld32((half ? t_dk : t_dv) + lane_base + c * 32, v);
             if (jkey < p.L) {
@@ -204,9 +206,11 @@ int attn_bwd_kv_umma(const float* q, const float* dctx, const float* pd, const f
     if (B == 0) return 0;
     static bool configured = false;
     if (!configured) {
-        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KV_SMEM));
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kv_umma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, KV_SMEM));
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kv_umma_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, KV_SMEM));
         configured = true;
     }
+    const int dh = d / H;
     AttnBwdKvParams p;
     const int NK = (L + 15) / 16 * 16;
     const long long rows = (long long)B * L, grows = (long long)B * H * L;
@@ -216,9 +220,10 @@ int attn_bwd_kv_umma(const float* q, const float* dctx, const float* pd, const f
     if ((rc = make_tmap_2d(&p.dout, dctx, rows, d, d, KV_QB, true))) return rc;
     if ((rc = make_tmap_2d(&p.q, q, rows, d, d, KV_QB, true))) return rc;
     p.dk = dk; p.dv = dv; p.H = H; p.L = L; p.d = d;
-    p.scale = 1.0f / sqrtf((float)KV_DH);
+    p.scale = 1.0f / sqrtf((float)dh);
     const dim3 grid(B * H, (L + 127) / 128);
-    attn_bwd_kv_umma_kernel<<<grid, KV_THREADS, KV_SMEM, st>>>(p);
+    if (dh == 64) attn_bwd_kv_umma_kernel<64><<<grid, KV_THREADS, KV_SMEM, st>>>(p);
+    else          attn_bwd_kv_umma_kernel<32><<<grid, KV_THREADS, KV_SMEM, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }

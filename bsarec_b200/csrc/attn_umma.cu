@@ -29,7 +29,7 @@ using namespace umma;
 
 namespace {
 
-constexpr int AU_DH = 64;                  // head size this kernel is built for
+constexpr int AU_DH = 64;                  // largest head size (the shared-memory plan); kernels are instantiated for 64 and 32
 constexpr int AU_NK_MAX = 208;             // keys per sequence (UMMA N, multiple of 16)
 constexpr int AU_SCOLS = 224;              // TMEM columns reserved for S / P_hi (7 chunks of 32)
 constexpr int AUF_PARTS = 4;                   // 4 warps per TMEM lane quarter (the elementwise passes are latency-bound)
@@ -76,8 +76,11 @@ __device__ __forceinline__ void split_region(unsigned char* base, int bytes, int
     }
 }
 
+template <int DH>
 __global__ void __launch_bounds__(AUF_THREADS, 1)
 attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
+    constexpr int NKB = DH / 32;                 // 32-float k-blocks of the head dimension
+    constexpr int VKB = NKB * 4096;              // bytes of one 32-key block of the MN-major V operand
     extern __shared__ __align__(1024) unsigned char au_smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)au_smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* bar_qk = (uint64_t*)(smem + AU_OFF_BAR);       // Q and K tiles landed              (TMA -> all)
@@ -94,7 +97,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     const int qt = blockIdx.y;
     const long long seq_base = (long long)b * p.L;
     const int NK = p.NK, nkb = (NK + 31) / 32;
-    const int col0 = h * AU_DH;
+    const int col0 = h * DH;
     const int k_kb_bytes = NK * 128;                         // one 32-float k-block of the K operand
 
     BSA_STAMP(7);
@@ -103,17 +106,18 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(s_full, 1);
         mbar_init(o_full, 1);
         fence_barrier_init();
-        mbar_expect_tx(bar_qk, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
+        mbar_expect_tx(bar_qk, (uint32_t)(NKB * (16384 + k_kb_bytes)));
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < NKB; ++kb) {
             tma_load_2d(smem + AU_OFF_QHI + kb * 16384, &p.q, bar_qk, col0 + kb * 32, (int)(seq_base + qt * 128));
             tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes, &p.k, bar_qk, col0 + kb * 32, (int)seq_base);
             tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes + (NK / 2) * 128, &p.k, bar_qk, col0 + kb * 32, (int)seq_base + NK / 2);
         }
-        mbar_expect_tx(bar_v, (uint32_t)(nkb * 8192));
+        mbar_expect_tx(bar_v, (uint32_t)(nkb * VKB));
         for (int kb = 0; kb < nkb; ++kb) {
-            tma_load_2d(smem + AU_OFF_V + kb * 8192, &p.v, bar_v, col0, (int)seq_base + kb * 32);
-            tma_load_2d(smem + AU_OFF_V + kb * 8192 + 4096, &p.v, bar_v, col0 + 32, (int)seq_base + kb * 32);
+#pragma unroll
+            for (int c = 0; c < NKB; ++c)
+                tma_load_2d(smem + AU_OFF_V + kb * VKB + c * 4096, &p.v, bar_v, col0 + c * 32, (int)seq_base + kb * 32);
         }
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
@@ -132,8 +136,8 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     // ---- Q, K: raw fp32 -> (hi, lo), all 8 warps
     mbar_wait(bar_qk, 0);
     BSA_STAMP(1);
-    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
-    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_QHI, NKB * 16384, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_KHI, NKB * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
     BSA_STAMP(2);
@@ -145,7 +149,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         const uint32_t kh = smem_u32(smem + AU_OFF_KHI), kl = smem_u32(smem + AU_OFF_KLO);
         uint32_t acc = 0;
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < NKB; ++kb) {
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
                 const uint64_t dah = smem_desc(qh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
@@ -166,7 +170,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     mbar_wait(s_full, 0);
     BSA_STAMP(3);
     tc_fence_after();
-    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_V, nkb * VKB, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
 
     // ========================================================================= softmax: thread = (query row, column part)
@@ -253,13 +257,13 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     if (warp == 1 && elect_one()) {
         // ===================================================================== MMA 2: O = P V
         tc_fence_after();
-        const uint32_t idesc = idesc_tf32(128, AU_DH, false, true);
+        const uint32_t idesc = idesc_tf32(128, DH, false, true);
         const uint32_t vh = smem_u32(smem + AU_OFF_V), vl = smem_u32(smem + AU_OFF_KHI);
         uint32_t acc = 0;
         for (int kstep = 0; kstep < NK / 8; ++kstep) {
             const int kb = kstep >> 2, ks = kstep & 3;
-            const uint64_t dbh = smem_desc(vh + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
-            const uint64_t dbl = smem_desc(vl + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint64_t dbh = smem_desc(vh + kb * VKB + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint64_t dbl = smem_desc(vl + kb * VKB + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
             const uint32_t col = (uint32_t)(kstep * 8);
             mma_tf32_ts(t_o, t_lo + col, dbh, idesc, acc);
             mma_tf32_ts(t_o, t_s + col, dbl, idesc, 1u);
@@ -273,7 +277,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     mbar_wait(o_full, 0);
     BSA_STAMP(5);
     tc_fence_after();
-    if (part < 2) {
+    if (part < NKB) {
         const int half = part;
         const float inv = row_ok ? 1.0f / l : 0.f;
         float* dst = p.ctx + (seq_base + (row_ok ? i : 0)) * p.d + col0 + half * 32;
@@ -315,8 +319,11 @@ struct AttnBwdQParams {
     Dropout dr;
 };
 
+template <int DH>
 __global__ void __launch_bounds__(AUF_THREADS, 1)
 attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
+    constexpr int NKB = DH / 32;
+    constexpr int VKB = NKB * 4096;
     extern __shared__ __align__(1024) unsigned char au_smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)au_smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* bar_qk = (uint64_t*)(smem + AU_OFF_BAR);       // Q and K tiles landed
@@ -334,7 +341,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     const int qt = blockIdx.y;
     const long long seq_base = (long long)b * p.L;
     const int NK = p.NK, nkb = (NK + 31) / 32;
-    const int col0 = h * AU_DH;
+    const int col0 = h * DH;
     const int k_kb_bytes = NK * 128;
 
     BSA_STAMP(31);
@@ -342,17 +349,18 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
         mbar_init(bar_qk, 1); mbar_init(bar_km, 1); mbar_init(s_full, 1); mbar_init(bar_dov, 1); mbar_init(dp_full, 1);
         mbar_init(o_full, 1);
         fence_barrier_init();
-        mbar_expect_tx(bar_qk, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
+        mbar_expect_tx(bar_qk, (uint32_t)(NKB * (16384 + k_kb_bytes)));
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < NKB; ++kb) {
             tma_load_2d(smem + AU_OFF_QHI + kb * 16384, &p.q, bar_qk, col0 + kb * 32, (int)(seq_base + qt * 128));
             tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes, &p.k, bar_qk, col0 + kb * 32, (int)seq_base);
             tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes + (NK / 2) * 128, &p.k, bar_qk, col0 + kb * 32, (int)seq_base + NK / 2);
         }
-        mbar_expect_tx(bar_km, (uint32_t)(nkb * 8192));
+        mbar_expect_tx(bar_km, (uint32_t)(nkb * VKB));
         for (int kb = 0; kb < nkb; ++kb) {
-            tma_load_2d(smem + AU_OFF_V + kb * 8192, &p.km, bar_km, col0, (int)seq_base + kb * 32);
-            tma_load_2d(smem + AU_OFF_V + kb * 8192 + 4096, &p.km, bar_km, col0 + 32, (int)seq_base + kb * 32);
+#pragma unroll
+            for (int c = 0; c < NKB; ++c)
+                tma_load_2d(smem + AU_OFF_V + kb * VKB + c * 4096, &p.km, bar_km, col0 + c * 32, (int)seq_base + kb * 32);
         }
         prefetch_tmap(&p.dout); prefetch_tmap(&p.vk);
     }
@@ -371,8 +379,8 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
 
     mbar_wait(bar_qk, 0);
     BSA_STAMP(17);
-    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
-    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_QHI, NKB * 16384, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_KHI, NKB * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
     BSA_STAMP(18);
@@ -384,7 +392,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
         const uint32_t kh = smem_u32(smem + AU_OFF_KHI), kl = smem_u32(smem + AU_OFF_KLO);
         uint32_t acc = 0;
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < NKB; ++kb) {
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
                 const uint64_t dah = smem_desc(qh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
@@ -425,7 +433,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
         for (int it = 0; it < 4; ++it) {
             const int ri = qt * 128 + warp * 8 + it * 2 + hl;
             a[it] = g[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ri < p.L) {
+            if (ri < p.L && c4 < DH / 4) {
                 a[it] = __ldg(reinterpret_cast<const float4*>(p.ctx + (seq_base + ri) * p.d + col0) + c4);
                 g[it] = __ldg(reinterpret_cast<const float4*>(p.dctx + (seq_base + ri) * p.d + col0) + c4);
             }
@@ -449,9 +457,9 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     tc_fence_after();
     if (warp == 0 && elect_one()) {
         fence_proxy_async_smem();
-        mbar_expect_tx(bar_dov, (uint32_t)(AU_Q_BYTES + 2 * k_kb_bytes));
+        mbar_expect_tx(bar_dov, (uint32_t)(NKB * (16384 + k_kb_bytes)));
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < NKB; ++kb) {
             tma_load_2d(smem + AU_OFF_QHI + kb * 16384, &p.dout, bar_dov, col0 + kb * 32, (int)(seq_base + qt * 128));
             tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes, &p.vk, bar_dov, col0 + kb * 32, (int)seq_base);
             tma_load_2d(smem + AU_OFF_KHI + kb * k_kb_bytes + (NK / 2) * 128, &p.vk, bar_dov, col0 + kb * 32, (int)seq_base + NK / 2);
@@ -460,8 +468,8 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     __syncwarp();
     mbar_wait(bar_dov, 0);
     BSA_STAMP(20);
-    split_region(smem + AU_OFF_QHI, AU_Q_BYTES, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
-    split_region(smem + AU_OFF_KHI, 2 * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_QHI, NKB * 16384, AU_OFF_QLO - AU_OFF_QHI, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_KHI, NKB * k_kb_bytes, AU_OFF_KLO - AU_OFF_KHI, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
     __syncthreads();
     BSA_STAMP(21);
@@ -472,7 +480,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
         const uint32_t vh = smem_u32(smem + AU_OFF_KHI), vl = smem_u32(smem + AU_OFF_KLO);
         uint32_t acc = 0;
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
+        for (int kb = 0; kb < NKB; ++kb) {
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
                 const uint64_t dah = smem_desc(gh + kb * 16384 + ks * 32, 16, 1024, LAYOUT_SW128);
@@ -493,7 +501,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     BSA_STAMP(22);
     tc_fence_after();
     // K rows (MN-major layout): hi in place, lo into region 2 (V is dead now)
-    split_region(smem + AU_OFF_V, nkb * 8192, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
+    split_region(smem + AU_OFF_V, nkb * VKB, AU_OFF_KHI - AU_OFF_V, threadIdx.x, AUF_THREADS);
     fence_proxy_async_smem();
 
     // ========================================================================= dS = P o (dPd o M - delta), back into TMEM
@@ -561,13 +569,13 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     if (warp == 1 && elect_one()) {
         // ===================================================================== MMA 3: dQ = dS K
         tc_fence_after();
-        const uint32_t idesc = idesc_tf32(128, AU_DH, false, true);
+        const uint32_t idesc = idesc_tf32(128, DH, false, true);
         const uint32_t kh = smem_u32(smem + AU_OFF_V), kl = smem_u32(smem + AU_OFF_KHI);
         uint32_t acc = 0;
         for (int kstep = 0; kstep < NK / 8; ++kstep) {
             const int kb = kstep >> 2, ks = kstep & 3;
-            const uint64_t dbh = smem_desc(kh + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
-            const uint64_t dbl = smem_desc(kl + kb * 8192 + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint64_t dbh = smem_desc(kh + kb * VKB + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
+            const uint64_t dbl = smem_desc(kl + kb * VKB + ks * 1024, 4096, 512, LAYOUT_SW128_BASE32B);
             const uint32_t col = (uint32_t)(kstep * 8);
             mma_tf32_ts(t_o, t_lo + col, dbh, idesc, acc);
             mma_tf32_ts(t_o, t_s + col, dbl, idesc, 1u);
@@ -580,9 +588,9 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     mbar_wait(o_full, 0);
     BSA_STAMP(24);
     tc_fence_after();
-    {
+    if (part < DH / 16) {
         float v[16];
-        tmem_ld16(t_o + lane_base + part * 16, v);                 // part = 0..3 -> dQ columns [16 part, 16 part + 16)
+        tmem_ld16(t_o + lane_base + part * 16, v);                 // part -> dQ columns [16 part, 16 part + 16)
         if (row_ok) {
             float* dst = p.dq + (seq_base + i) * p.d + col0 + part * 16;
 #pragma unroll
@@ -603,7 +611,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
 }  // namespace
 
 bool attn_umma_supported(int L, int d, int H) {
-    if (H <= 0 || d % H != 0 || d / H != AU_DH || d % 4 != 0) return false;
+    if (H <= 0 || d % H != 0 || (d / H != 64 && d / H != 32) || d % 4 != 0) return false;
     return L >= 1 && L <= AU_NK_MAX;
 }
 
@@ -613,9 +621,11 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
     if (B == 0) return 0;
     static bool configured = false;
     if (!configured) {
-        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_umma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_umma_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
         configured = true;
     }
+    const int dh = d / H;
     AttnUmmaParams p;
     const int NK = (L + 15) / 16 * 16;
     const long long rows = (long long)B * L;
@@ -624,11 +634,12 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
     if ((rc = make_tmap_2d(&p.k, k, rows, d, d, NK / 2, false))) return rc;
     if ((rc = make_tmap_2d(&p.v, v, rows, d, d, 32, true))) return rc;
     p.ids = ids; p.ctx = ctx; p.lse = lse; p.H = H; p.L = L; p.d = d; p.NK = NK;
-    p.scale = 1.0f / sqrtf((float)AU_DH);
+    p.scale = 1.0f / sqrtf((float)dh);
     p.dr = dr;
     const dim3 grid(B * H, (L + 127) / 128);
-    ProfScope prof(PROF_ATTN_FWD, st, 4.0 * B * H * (double)L * L * AU_DH);
-    attn_fwd_umma_kernel<<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
+    ProfScope prof(PROF_ATTN_FWD, st, 4.0 * B * H * (double)L * L * dh);
+    if (dh == 64) attn_fwd_umma_kernel<64><<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
+    else          attn_fwd_umma_kernel<32><<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }
@@ -640,9 +651,11 @@ int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long l
     if (B == 0) return 0;
     static bool configured = false;
     if (!configured) {
-        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_q_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_q_umma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
+        BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_q_umma_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, AU_SMEM));
         configured = true;
     }
+    const int dh = d / H;
     AttnBwdQParams p;
     const int NK = (L + 15) / 16 * 16;
     const long long rows = (long long)B * L;
@@ -655,10 +668,11 @@ int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long l
     p.ids = ids; p.ctx = ctx; p.dctx = dctx; p.lse = lse; p.dq = dq; p.delta = delta;
     p.pd_out = pd_out; p.ds_out = ds_out;
     p.H = H; p.L = L; p.d = d; p.NK = NK;
-    p.scale = 1.0f / sqrtf((float)AU_DH);
+    p.scale = 1.0f / sqrtf((float)dh);
     p.dr = dr;
     const dim3 grid(B * H, (L + 127) / 128);
-    attn_bwd_q_umma_kernel<<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
+    if (dh == 64) attn_bwd_q_umma_kernel<64><<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
+    else          attn_bwd_q_umma_kernel<32><<<grid, AUF_THREADS, AU_SMEM, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }

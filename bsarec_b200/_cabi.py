@@ -97,6 +97,7 @@ SIGNATURES = {
                                 C.POINTER(BlockPtrs), _VP, _SZ, _VP]),
     "bsa_ce_workspace_bytes": (_SZ, [C.POINTER(CeDesc)]),
     "bsa_ce_fwd": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "bsa_ce_fwd_partial": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_ce_bwd": (_I, [C.POINTER(CeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_score_topk_workspace_bytes": (_SZ, [C.POINTER(TopkDesc)]),
     "bsa_score_topk": (_I, [C.POINTER(TopkDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),

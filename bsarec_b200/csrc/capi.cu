@@ -282,6 +282,15 @@ int bsa_ce_fwd(const bsa_ce_desc* c, const float* seq_out, const float* item_emb
     return ce_fwd_simt(c->B, c->d, c->item_size, seq_out, item_emb, (const long long*)answers, loss, lse, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+int bsa_ce_fwd_partial(const bsa_ce_desc* c, const float* seq_out, const float* item_shard, const int64_t* answers_local,
+                       float* lse_part, float* tgt_part, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(c && seq_out && item_shard && answers_local && lse_part && tgt_part && workspace, "bsa_ce_fwd_partial: null argument");
+    BSA_REQUIRE(c->B > 0 && c->item_size > 0, "bsa_ce_fwd_partial: empty batch or shard");
+    BSA_REQUIRE(umma_ce_supported(c->B, c->d, c->item_size), "bsa_ce_fwd_partial: tcgen05 path does not support B=%d d=%d", c->B, c->d);
+    return umma_ce_fwd(c->B, c->d, c->item_size, seq_out, item_shard, (const long long*)answers_local, nullptr, lse_part, workspace,
+                       workspace_bytes, (cudaStream_t)stream, tgt_part);
+}
+
 int bsa_ce_bwd(const bsa_ce_desc* c, const float* seq_out, const float* item_emb, const int64_t* answers, const float* lse,
                const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace, size_t workspace_bytes, void* stream) {
     BSA_REQUIRE(c && seq_out && item_emb && answers && lse && d_loss && d_seq_out && d_item_emb && workspace, "bsa_ce_bwd: null argument");

@@ -752,10 +752,14 @@ bool umma_ce_supported(int B, int d, long long N) { return B >= 1 && d % 4 == 0 
 size_t umma_ce_workspace_bytes(int B, int d, long long N) { return carve_ce(nullptr, B, d, N, true).bytes; }
 
 int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, float* loss,
-                float* lse, void* ws, size_t ws_bytes, cudaStream_t st) {
+                float* lse, void* ws, size_t ws_bytes, cudaStream_t st, float* tgt_out) {
     CeWs w = carve_ce(ws, B, d, N, false);
     BSA_REQUIRE(ws_bytes >= w.bytes, "bsa_ce_fwd: workspace too small (%zu < %zu)", ws_bytes, w.bytes);
     int rc;
+    if (tgt_out) {        // one row shard of a vocabulary-parallel CE: targets outside the shard (answer < 0) contribute 0
+        BSA_CHECK_CUDA(cudaMemsetAsync(w.tgt, 0, (size_t)B * 4, st));
+        if (!loss) loss = (float*)((char*)ws + w.bytes - 512);
+    }
     if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
     if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
     Operand oa{w.s_hi, w.s_lo, B, d, d, false}, ob{w.e_hi, w.e_lo, N, d, d, false};
@@ -770,6 +774,7 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
     }
     ce_combine_kernel<<<1, 256, 0, st>>>(w.part_m, w.part_s, w.tgt, 2 * nstrips, B, lse, loss);
     BSA_LAUNCH_CHECK();
+    if (tgt_out) BSA_CHECK_CUDA(cudaMemcpyAsync(tgt_out, w.tgt, (size_t)B * 4, cudaMemcpyDeviceToDevice, st));
     return 0;
 }
 

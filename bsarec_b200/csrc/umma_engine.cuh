@@ -7,7 +7,7 @@ namespace bsa {
 bool umma_ce_supported(int B, int d, long long N);
 size_t umma_ce_workspace_bytes(int B, int d, long long N);
 int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, float* loss,
-                float* lse, void* ws, size_t ws_bytes, cudaStream_t st);
+                float* lse, void* ws, size_t ws_bytes, cudaStream_t st, float* tgt_out = nullptr);
 int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const long long* answers, const float* lse,
                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, bool reuse_split, cudaStream_t st);
 

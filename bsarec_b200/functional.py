@@ -248,6 +248,23 @@ def ce_forward(s: torch.Tensor, E: torch.Tensor, answers: torch.Tensor, impl: in
     return loss, lse, ws
 
 
+def ce_forward_partial(s_all: torch.Tensor, E_shard: torch.Tensor, answers_local: torch.Tensor):
+    """One row shard of a vocabulary-parallel CE (``bsa_ce_fwd_partial``): -> (lse_part [B], tgt_part [B], workspace).
+    ``answers_local`` = answer - shard offset, negative when the target lies in another shard."""
+    lib = _cabi.load()
+    B, d = s_all.shape
+    answers_local = _require_cuda(answers_local, "answers_local", torch.int64)
+    cd = CeDesc(B=B, d=d, item_size=E_shard.shape[0], impl=2, reuse_split=0)
+    with torch.cuda.device(s_all.device):
+        wsb = lib.bsa_ce_workspace_bytes(C.byref(cd))
+        ws = torch.empty(wsb, dtype=torch.uint8, device=s_all.device)
+        lse = torch.empty(B, dtype=torch.float32, device=s_all.device)
+        tgt = torch.empty(B, dtype=torch.float32, device=s_all.device)
+        check(lib.bsa_ce_fwd_partial(C.byref(cd), _ptr(s_all), _ptr(E_shard), _ptr(answers_local), _ptr(lse), _ptr(tgt), _ptr(ws),
+                                     wsb, _stream()), "bsa_ce_fwd_partial")
+    return lse, tgt, ws
+
+
 def ce_backward(s, E, answers, lse, d_loss, dE: torch.Tensor, impl: int = 0, fwd_ws: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Overwrites dE [N,d] with the dense gradient; returns ds [B,d].  ``fwd_ws``: the workspace ``ce_forward``
     returned for the same (s, E) — its split copies of both operands are reused instead of being rebuilt."""
@@ -336,13 +353,13 @@ def topk_merge(cand_val: torch.Tensor, cand_idx: torch.Tensor):
     return val, idx
 
 
-def alloc_grads(params: Dict[str, torch.Tensor], big: str = "item_embeddings.weight"):
+def alloc_grads(params: Dict[str, torch.Tensor], big: str = "item_embeddings.weight", with_big: bool = True):
     """Gradient buffers: the item table's on its own, every other tensor a view into ONE flat fp32 buffer (so a
     data-parallel run all-reduces the 41 small gradients with a single collective and no packing copies).
     -> ({name: tensor}, flat)"""
     small = [(n, t) for n, t in params.items() if n != big]
     flat = torch.empty(sum(t.numel() for _, t in small), dtype=torch.float32, device=params[big].device)
-    grads, off = {big: torch.empty_like(params[big])}, 0
+    grads, off = {big: torch.empty_like(params[big]) if with_big else None}, 0
     for n, t in small:
         grads[n] = flat[off:off + t.numel()].view_as(t)
         off += t.numel()
@@ -363,10 +380,21 @@ class FusedLoss(torch.autograd.Function):
         params = dict(zip(names, tensors))
         xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
         s = xs[-1]
+        ctx.hyper, ctx.names, ctx.state, ctx.ce_impl, ctx.exchange = hyper, names, state, ce_impl, exchange
+        if exchange is not None and exchange.vocab_parallel:
+            # every rank scores ALL users of the global batch against ITS rows of the item table
+            E = params["item_embeddings.weight"]
+            ctx.ex_state = exchange.prepare_routed(ids, E.shape[0])
+            s_all, ans_local = exchange.gather_users(s, _require_cuda(answers, "answers", torch.int64), E.shape[0])
+            lo, hi = exchange.shard(E.shape[0])
+            lse_p, tgt_p, ce_ws = ce_forward_partial(s_all, E[lo:hi], ans_local)
+            loss, lse = exchange.combine_loss(lse_p, tgt_p)
+            ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = ans_local, s_all, lse, ce_ws
+            ctx.save_for_backward(*tensors)
+            return loss
         loss, lse, ce_ws = ce_forward(s, params["item_embeddings.weight"], answers, ce_impl)
         if exchange is not None:
             ctx.ex_state = exchange.prepare(ids)             # row counts for the sparse exchange reach the host during the forward
-        ctx.hyper, ctx.names, ctx.state, ctx.ce_impl, ctx.exchange = hyper, names, state, ce_impl, exchange
         ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
         ctx.save_for_backward(*tensors)
         return loss
@@ -376,10 +404,26 @@ class FusedLoss(torch.autograd.Function):
         tensors = ctx.saved_tensors
         names, hyper, state, ex = ctx.names, ctx.hyper, ctx.state, ctx.exchange
         params = dict(zip(names, tensors))
-        grads, flat = alloc_grads(params)
+        grads, flat = alloc_grads(params, with_big=not (ex is not None and ex.vocab_parallel))
         if state.L < params["position_embeddings.weight"].shape[0]:
             grads["position_embeddings.weight"].zero_()      # rows >= L are never touched by the kernels
         E = params["item_embeddings.weight"]
+        if ex is not None and ex.vocab_parallel:
+            # the item table's gradient lives only as this rank's row shard (complete for its rows); FusedAdam updates the
+            # shard and all-gathers the rows (parallel.ShardedItemGrad), autograd sees no gradient for the table
+            lo, hi = ex.shard(E.shape[0])
+            grads["item_embeddings.weight"] = None
+            buf = torch.empty(hi - lo + 1, E.shape[1], dtype=torch.float32, device=E.device)    # row 0: landing row of the
+            gE_shard = buf[1:]                                                                   # scatter's skipped key 0
+            ds_all = ce_backward(ctx.s, E[lo:hi], ctx.answers, ctx.lse, d_loss, gE_shard, 2, ctx.ce_ws)
+            ctx.ce_ws = None
+            ds = ex.reduce_scatter_users(ds_all)
+            d_out = ds if state.last_row else scatter_last(ds, state.L)
+            dz = encoder_backward(hyper, params, state, d_out, grads, rows_only=True)
+            ex.finish_routed(ctx.ex_state, flat, dz, buf, lo, scatter_add_rows, gather_rows)
+            ex.publish_shard_grad(gE_shard, lo, hi)
+            ctx.state = None
+            return (None,) * 8 + tuple(grads[n] for n in names)
         gE = grads["item_embeddings.weight"]
         if ex is not None:
             d_loss = d_loss * ex.scale                       # sum over ranks == mean over the global batch

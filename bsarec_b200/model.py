@@ -151,12 +151,19 @@ class BSARecModel(nn.Module):
                                   self.ce_impl, self._exchange, *tensors)
 
     # ------------------------------------------------------------------ data-parallel training (additional API)
-    def enable_data_parallel(self, group=None):
+    def enable_data_parallel(self, group=None, vocab_parallel: bool = False):
         """One process per GPU, full replica, equal local batches: after this call ``loss.backward()`` leaves the
         GLOBAL-batch-mean gradient in every ``p.grad`` (NCCL exchange overlapped with the backward pass), so the
-        reference's loop — ``calculate_loss -> zero_grad -> backward -> step`` (trainers.py:103-107) — runs unchanged."""
+        reference's loop — ``calculate_loss -> zero_grad -> backward -> step`` (trainers.py:103-107) — runs unchanged.
+
+        ``vocab_parallel``: the cross-entropy is sharded over the item table's rows instead (every rank scores all users
+        of the global batch against its rows; ``loss`` is then the GLOBAL-batch mean on every rank).  The item table gets
+        no ``.grad``: its row-shard gradient is handed to ``bsarec_b200.FusedAdam`` (required), which updates the shard
+        and all-gathers the rows.  Needs ``item_size % world_size == 0`` and the tcgen05 CE path."""
         from .parallel import GradExchange
-        self._exchange = GradExchange(group)
+        self._exchange = GradExchange(group, vocab_parallel=vocab_parallel, item_param=self.item_embeddings.weight)
+        if vocab_parallel:
+            self._exchange.shard(self.args.item_size)       # raises early when the table does not divide
         return self
 
     def disable_data_parallel(self):

@@ -34,6 +34,11 @@ class FusedAdam(torch.optim.Optimizer):
             b1, b2 = group["betas"]
             small = {}                      # (device index, step) -> tensors updated together by one bsa_adam_step_multi
             for p in group["params"]:
+                shard = getattr(p, "_bsa_shard", None)
+                if shard is not None:            # vocabulary-parallel training: this rank owns rows [lo, hi) of the table
+                    self._step_shard(lib, group, p, shard)
+                    p._bsa_shard = None
+                    continue
                 if p.grad is None:
                     continue
                 if not p.is_cuda or p.dtype != torch.float32 or p.grad.dtype != torch.float32:
@@ -71,3 +76,29 @@ class FusedAdam(torch.optim.Optimizer):
                 for it in items:
                     torch.autograd.graph.increment_version(it[0])
         return loss
+
+    def _step_shard(self, lib, group, p, shard):
+        """Adam on rows [lo, hi) of ``p`` with the complete row-shard gradient ``shard.grad`` (state kept for the shard
+        only: 1/world of the memory and of the 28 B/element pass), then an all-gather of the updated rows so every
+        replica of the table stays identical (parallel.ShardedItemGrad)."""
+        import torch.distributed as dist
+        if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+            raise RuntimeError("FusedAdam: sharded parameters must be contiguous CUDA fp32")
+        b1, b2 = group["betas"]
+        st = self.state[p]
+        rows = p.data[shard.lo:shard.hi]
+        if not st or st.get("shard") != (shard.lo, shard.hi):
+            st.clear()
+            st["step"] = 0
+            st["shard"] = (shard.lo, shard.hi)
+            st["exp_avg"] = torch.zeros_like(rows)
+            st["exp_avg_sq"] = torch.zeros_like(rows)
+        st["step"] = int(st["step"]) + 1
+        g = shard.grad if shard.grad.is_contiguous() else shard.grad.contiguous()
+        with torch.cuda.device(p.device):
+            check(lib.bsa_adam_step(rows.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(),
+                                    rows.numel(), float(group["lr"]), float(b1), float(b2), float(group["eps"]),
+                                    float(group["weight_decay"]), st["step"], torch.cuda.current_stream().cuda_stream),
+                  "bsa_adam_step")
+        dist.all_gather_into_tensor(p.data.view(-1), rows.reshape(-1).clone(), group=shard.group)
+        torch.autograd.graph.increment_version(p)

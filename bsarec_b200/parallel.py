@@ -65,12 +65,15 @@ class GradExchange:
     ``scale`` = 1/world is folded into d_loss (no averaging pass over the gradients).  Ranks must hold equally sized local
     batches (the mean of local means is then the global mean of ``CrossEntropyLoss``, bsarec.py:35)."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, vocab_parallel: bool = False, item_param: Optional[torch.nn.Parameter] = None):
         self.group = group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.scale = 1.0 / self.world
         self.collectives = 0
+        # vocabulary-parallel cross-entropy + sharded item-table optimizer step (methods below, DESIGN.md §7)
+        self.vocab_parallel = bool(vocab_parallel)
+        self.item_param = item_param
 
     def _issue(self, fn, *a):
         self.collectives += 1
@@ -125,6 +128,121 @@ class GradExchange:
             scatter_fn(ids_all, dz_all, g_item)       # (rank, row) order, the same on every rank -> identical bits
         if w_small is not None:
             w_small.wait()
+
+
+    # ------------------------------------------------------------------ vocabulary-parallel cross-entropy
+    # Every rank scores ALL users of the global batch against ITS contiguous row shard of the item table:
+    #   forward : all-gather the [B,d] user vectors and the answers; per-shard (log-sum-exp, target logit) partials are
+    #             all-gathered ([world, 2, B_global] floats) and combined -> the GLOBAL-batch mean loss, identical on every rank;
+    #   backward: each rank gets the COMPLETE gradient of its rows (dense CE part from its own kernel, gather part routed to
+    #             it row by row with one all-to-all) and a partial ds for all users, which a reduce-scatter sums and hands
+    #             back to the users' owners; the 41 small gradients are one all-reduce (sum: the loss is already the global
+    #             mean).  No [N,d] all-reduce, no replicated Adam pass over the table: FusedAdam updates the shard and the
+    #             updated rows are all-gathered (ShardedItemGrad).  Needs item_size % world == 0.
+    def shard(self, n_rows: int) -> Tuple[int, int]:
+        if n_rows % self.world:
+            raise RuntimeError(f"vocabulary-parallel CE needs item_size ({n_rows}) divisible by the world size ({self.world})")
+        per = n_rows // self.world
+        return self.rank * per, (self.rank + 1) * per
+
+    def gather_users(self, s: torch.Tensor, answers: torch.Tensor, n_rows: int):
+        """-> (s_all [world*B, d], answers_local [world*B]: answer - shard offset, -1 when it lies in another shard)."""
+        B = s.shape[0]
+        s_all = torch.empty(self.world * B, s.shape[1], dtype=s.dtype, device=s.device)
+        ans_all = torch.empty(self.world * B, dtype=answers.dtype, device=answers.device)
+        dist.all_gather_into_tensor(s_all, s.contiguous(), group=self.group)
+        dist.all_gather_into_tensor(ans_all, answers.contiguous(), group=self.group)
+        self.collectives += 2
+        lo, hi = self.shard(n_rows)
+        inside = (ans_all >= lo) & (ans_all < hi)
+        return s_all, torch.where(inside, ans_all - lo, torch.full_like(ans_all, -1))
+
+    def combine_loss(self, lse_part: torch.Tensor, tgt_part: torch.Tensor):
+        """Per-shard partials [B_global] -> (global-batch mean loss, global lse [B_global])."""
+        mine = torch.stack([lse_part, tgt_part])                          # [2, Bg]
+        parts = torch.empty(self.world, 2, lse_part.numel(), dtype=mine.dtype, device=mine.device)
+        dist.all_gather_into_tensor(parts.view(self.world * 2, -1), mine, group=self.group)
+        self.collectives += 1
+        lse = torch.logsumexp(parts[:, 0], dim=0)
+        tgt = parts[:, 1].sum(dim=0)
+        return (lse - tgt).mean(), lse.contiguous()
+
+    def reduce_scatter_users(self, ds_all: torch.Tensor) -> torch.Tensor:
+        """[world*B, d] partial (this shard's contribution for every user) -> [B, d] summed over shards for MY users."""
+        B = ds_all.shape[0] // self.world
+        out = torch.empty(B, ds_all.shape[1], dtype=ds_all.dtype, device=ds_all.device)
+        self.collectives += 1
+        if ds_all.is_cuda:
+            dist.reduce_scatter_tensor(out, ds_all.contiguous(), op=dist.ReduceOp.SUM, group=self.group)
+        else:                                                             # gloo (CPU tests) has no reduce-scatter
+            tmp = ds_all.clone()
+            dist.all_reduce(tmp, op=dist.ReduceOp.SUM, group=self.group)
+            out.copy_(tmp[self.rank * B:(self.rank + 1) * B])
+        return out
+
+    def prepare_routed(self, ids: torch.Tensor, n_rows: int):
+        """Forward-time half of the routed row exchange: rows of real items sorted by owner shard (stable), and the
+        [world, world] table of row counts on its way to the host (read in the backward pass: no sync there)."""
+        st = _ExchangeState()
+        flat = ids.reshape(-1)
+        per = n_rows // self.world
+        dest = torch.where(flat > 0, flat // per, torch.full_like(flat, self.world))      # padding sorts last, is never sent
+        st.order = torch.argsort(dest, stable=True)
+        st.flat_ids = flat
+        mine = torch.bincount(dest, minlength=self.world + 1)[:self.world].to(torch.int64)
+        counts = torch.empty(self.world, self.world, dtype=torch.int64, device=flat.device)
+        dist.all_gather_into_tensor(counts.view(-1), mine, group=self.group)
+        self.collectives += 1
+        if flat.is_cuda:
+            st.cap_host = torch.empty(self.world, self.world, dtype=torch.int64, pin_memory=True)
+            st.cap_host.copy_(counts, non_blocking=True)
+            st.cap_event = torch.cuda.Event()
+            st.cap_event.record()
+        else:
+            st.cap_host, st.cap_event = counts, None
+        return st
+
+    def finish_routed(self, st: "_ExchangeState", small_flat: torch.Tensor, dz: torch.Tensor, shard_buf: torch.Tensor, lo: int,
+                      scatter_fn: Callable, gather_fn: Optional[Callable] = None):
+        """shard_buf [rows + 1, d]: row 0 is a landing row (the scatter skips key 0), row 1 + r is shard row r — already
+        holding the dense CE gradient.  Adds the gather-path rows of EVERY rank that fall into this shard."""
+        w_small = self._issue(dist.all_reduce, small_flat, dist.ReduceOp.SUM) if small_flat.numel() else None
+        if st.cap_event is not None:
+            st.cap_event.synchronize()
+        counts = st.cap_host.tolist()
+        send = counts[self.rank]
+        recv = [counts[r][self.rank] for r in range(self.world)]
+        n_send, n_recv = sum(send), sum(recv)
+        idx = st.order[:n_send]
+        ids_s = st.flat_ids[idx]
+        rows_s = gather_fn(dz, idx) if gather_fn is not None else torch.index_select(dz, 0, idx)
+        ids_r = torch.empty(n_recv, dtype=torch.int64, device=dz.device)
+        rows_r = torch.empty(n_recv, dz.shape[1], dtype=dz.dtype, device=dz.device)
+        d = dz.shape[1]
+        w1 = dist.all_to_all_single(ids_r, ids_s, recv, send, group=self.group, async_op=True)
+        w2 = dist.all_to_all_single(rows_r.view(-1), rows_s.view(-1), [c * d for c in recv], [c * d for c in send],
+                                    group=self.group, async_op=True)
+        self.collectives += 2
+        w1.wait()
+        w2.wait()
+        if n_recv:
+            scatter_fn(ids_r - (lo - 1), rows_r, shard_buf)       # (source rank, row) order: fixed -> reproducible bits
+        if w_small is not None:
+            w_small.wait()
+
+    def publish_shard_grad(self, g_shard: torch.Tensor, lo: int, hi: int):
+        if self.item_param is None:
+            raise RuntimeError("vocabulary-parallel exchange: item_param not set (use BSARecModel.enable_data_parallel)")
+        self.item_param._bsa_shard = ShardedItemGrad(g_shard, lo, hi, self.group)
+
+
+class ShardedItemGrad:
+    """Attached to the item-table parameter as ``_bsa_shard`` by a vocabulary-parallel backward pass: the COMPLETE
+    gradient of rows [lo, hi) (global-batch mean).  ``FusedAdam.step`` updates those rows and all-gathers them."""
+    __slots__ = ("grad", "lo", "hi", "group")
+
+    def __init__(self, grad, lo, hi, group):
+        self.grad, self.lo, self.hi, self.group = grad, lo, hi, group
 
 
 class _ExchangeState:

@@ -202,6 +202,15 @@ size_t bsa_ce_workspace_bytes(const bsa_ce_desc* desc);
  * lse [B] is saved for the backward pass. */
 int bsa_ce_fwd(const bsa_ce_desc* desc, const float* seq_out, const float* item_emb, const int64_t* answers,
                float* loss, float* lse, void* workspace, size_t workspace_bytes, void* stream);
+/* One ROW SHARD of a vocabulary-parallel cross-entropy (data-parallel training with the item table's CE sharded over the
+ * ranks): item_shard [desc.item_size = shard rows, d]; answers_local int64 [B] = answer - shard offset, or any
+ * NEGATIVE value when the target lies in another shard.  lse_part [B] = log-sum-exp over the shard's rows, tgt_part [B] =
+ * the target logit (0 when not in this shard): the caller combines them across shards, loss = mean_b(logsumexp_r lse_part -
+ * sum_r tgt_part).  bsa_ce_bwd then takes the GLOBAL lse, the same answers_local and this workspace (reuse_split = 1) and
+ * returns the shard's complete d_item_emb rows and this shard's partial d_seq_out (summed over shards by the caller).
+ * tcgen05 path only. */
+int bsa_ce_fwd_partial(const bsa_ce_desc* desc, const float* seq_out, const float* item_shard, const int64_t* answers_local,
+                       float* lse_part, float* tgt_part, void* workspace, size_t workspace_bytes, void* stream);
 /* d_loss: device scalar (upstream gradient).  d_seq_out [B,d] overwritten; d_item_emb [item_size,d]
  * OVERWRITTEN with the dense gradient (every row, including row 0). */
 int bsa_ce_bwd(const bsa_ce_desc* desc, const float* seq_out, const float* item_emb, const int64_t* answers,

@@ -2,9 +2,11 @@
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/dp_selfcheck.py
 
-Every rank runs its shard of one global batch through the CUDA path with the overlapped GradExchange; rank 0 checks the
-resulting gradients against (a) the flat-bucket all-reduce of the same local gradients and (b) the CPU oracle on the
-GLOBAL batch (<= 1e-4 relative), and all ranks check that replicas are bit-identical."""
+Every rank runs its shard of one global batch through the CUDA path with the overlapped GradExchange and with the
+vocabulary-parallel cross-entropy; rank 0 checks the resulting gradients against (a) the flat-bucket all-reduce of the same
+local gradients and (b) the CPU oracle on the GLOBAL batch (<= 1e-4 relative), all ranks check that replicas are
+bit-identical, and one FusedAdam step of the vocabulary-parallel path (sharded item-table update + all-gather of the rows)
+is compared with the replicated step."""
 import os
 import sys
 
@@ -17,6 +19,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import oracle                                                        # noqa: E402
 from helpers import build_model, oracle_cfg, synth_batch, perturbed_params   # noqa: E402
 from bsarec_b200.parallel import allreduce_gradients                # noqa: E402
+from bsarec_b200 import FusedAdam                                    # noqa: E402
 
 
 def main():
@@ -24,21 +27,32 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    cfgkw = dict(item_size=5003, hidden_size=64, max_seq_length=50, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.7)
+    cfgkw = dict(item_size=5004, hidden_size=64, max_seq_length=50, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.7)
     cfg = oracle_cfg(cfgkw)
     P = perturbed_params(cfg, 7)
     Bl = 24
-    ids, answers = synth_batch(17, Bl * world, 50, 5003)
+    ids, answers = synth_batch(17, Bl * world, 50, 5004)
     mine = slice(rank * Bl, (rank + 1) * Bl)
-    res = {}
-    for mode in ("overlap", "bucket"):
+    res, after = {}, {}
+    for mode in ("overlap", "bucket", "vp"):
         model = build_model(cfgkw, P, dev).train()
-        if mode == "overlap":
-            model.enable_data_parallel()
+        optim = FusedAdam(model.parameters(), lr=1e-3)
+        if mode != "bucket":
+            model.enable_data_parallel(vocab_parallel=mode == "vp")
         model.calculate_loss(ids[mine].to(dev), answers[mine].to(dev), None, None, None).backward()
         if mode == "bucket":
             allreduce_gradients(list(model.parameters()))
-        res[mode] = {n: p.grad.detach().clone() for n, p in model.named_parameters()}
+        res[mode] = {}
+        for n, p in model.named_parameters():
+            if p.grad is None:                  # vp: the item table's gradient is this rank's row shard -> assemble the table's
+                sh = p._bsa_shard
+                full = torch.empty_like(p)
+                dist.all_gather_into_tensor(full.view(-1), sh.grad.reshape(-1).contiguous())
+                res[mode][n] = full
+            else:
+                res[mode][n] = p.grad.detach().clone()
+        optim.step()
+        after[mode] = {n: p.detach().clone() for n, p in model.named_parameters()}
     worst = 0.0
     for n in res["overlap"]:
         a, b = res["overlap"][n], res["bucket"][n]
@@ -49,6 +63,24 @@ def main():
         for g in gathered:
             assert torch.equal(g, gathered[0]), f"replicas differ on {n}"
     assert worst < 2e-6, worst
+    worst_vp, worst_step = 0.0, 0.0
+    for n in res["vp"]:
+        a, b = res["vp"][n], res["bucket"][n]
+        if n.endswith("key.bias"):              # analytically zero: 1e-11 rounding noise on both sides
+            assert a.abs().max().item() < 1e-6
+            continue
+        e = (a - b).abs().max().item() / (b.abs().max().item() or 1.0)
+        if e > 5e-6 and rank == 0:
+            print(f"  vp vs bucket: {n} rel err {e:.3e} (|a| {a.abs().max().item():.3e}, |b| {b.abs().max().item():.3e})", flush=True)
+        worst_vp = max(worst_vp, e)
+        if not n.endswith("key.bias"):          # Adam turns that tensor's rounding noise into +-lr steps on both sides
+            worst_step = max(worst_step, (after["vp"][n] - after["bucket"][n]).abs().max().item())
+        gathered = [torch.empty_like(after["vp"][n]) for _ in range(world)]
+        dist.all_gather(gathered, after["vp"][n].contiguous())
+        for g in gathered:
+            assert torch.equal(g, gathered[0]), f"vp replicas differ after the step on {n}"
+    assert worst_vp < 1e-4, worst_vp            # another problem shape for the CE kernels: the parity bar itself
+    assert worst_step < 2.1e-3, worst_step      # first Adam step: |update| = lr, sign flips only where the gradient is noise
     if rank == 0:
         _, g64 = oracle.loss_and_grads({k: v.double() for k, v in P.items()}, ids, answers, cfg, use_fft=False)
         bad = 0.0
@@ -58,7 +90,8 @@ def main():
             den = g64[n].abs().max().item() or 1.0
             bad = max(bad, (g.cpu().double() - g64[n]).abs().max().item() / den)
         assert bad < 1e-4, bad
-        print(f"dp_selfcheck ok: world {world}, overlap vs bucket {worst:.2e}, vs oracle(global batch) {bad:.2e}", flush=True)
+        print(f"dp_selfcheck ok: world {world}, overlap vs bucket {worst:.2e}, vocab-parallel vs bucket {worst_vp:.2e} "
+              f"(params after one FusedAdam step: max |diff| {worst_step:.2e}), vs oracle(global batch) {bad:.2e}", flush=True)
     dist.destroy_process_group()
 
 

@@ -142,6 +142,77 @@ def test_overlapped_gradient_exchange_equals_full_allreduce(tmp_path):
         assert torch.equal(x, y)
 
 
+def _vocab_parallel_worker(rank, world):
+    """Vocabulary-parallel CE host logic with torch stand-ins for the shard kernels: the combined loss equals the
+    full-catalog cross-entropy of the GLOBAL batch; each rank ends with the complete gradient of ITS rows (dense part +
+    the gather rows of every rank routed to it) and the summed ds of ITS users."""
+    N, d, Bl, L = 48, 8, 5, 6
+    g = torch.Generator().manual_seed(9)
+    E = torch.randn(N, d, generator=g, dtype=torch.float64)
+    s_glob = torch.randn(world * Bl, d, generator=g, dtype=torch.float64)
+    ans_glob = torch.randint(1, N, (world * Bl,), generator=g)
+    ids_glob = torch.randint(1, N, (world * Bl, L), generator=g)
+    ids_glob[:, :2] = 0
+    ids_glob[0] = 0                                              # a rank-0 row that sends nothing
+    dz_glob = torch.randn(world * Bl * L, d, generator=g, dtype=torch.float64)
+    small_glob = torch.randn(world, 13, generator=g, dtype=torch.float64)
+    mine = slice(rank * Bl, (rank + 1) * Bl)
+    ex = GradExchange(vocab_parallel=True)
+    lo, hi = ex.shard(N)
+    st = ex.prepare_routed(ids_glob[mine], N)
+    s_all, ans_local = ex.gather_users(s_glob[mine].clone(), ans_glob[mine].clone(), N)
+    assert torch.equal(s_all, s_glob)
+    inside = (ans_glob >= lo) & (ans_glob < hi)
+    assert torch.equal(ans_local, torch.where(inside, ans_glob - lo, torch.full_like(ans_glob, -1)))
+    # stand-in for bsa_ce_fwd_partial on the shard
+    logits = s_all @ E[lo:hi].T
+    lse_p = torch.logsumexp(logits, 1)
+    tgt_p = torch.where(ans_local >= 0, logits.gather(1, ans_local.clamp_min(0)[:, None]).squeeze(1), torch.zeros_like(lse_p))
+    loss, lse = ex.combine_loss(lse_p, tgt_p)
+    full = s_glob @ E.T
+    want_loss = torch.nn.functional.cross_entropy(full, ans_glob)
+    assert abs(float(loss) - float(want_loss)) < 1e-12
+    assert (lse - torch.logsumexp(full, 1)).abs().max() < 1e-12
+    # stand-in for bsa_ce_bwd on the shard: P = softmax rows of the shard / B_global, minus the onehot where it is local
+    G = torch.exp(logits - lse[:, None]) / (world * Bl)
+    rows_in = (ans_local >= 0).nonzero().flatten()
+    G[rows_in, ans_local[rows_in]] -= 1.0 / (world * Bl)
+    ds_all = G @ E[lo:hi]
+    buf = torch.zeros(hi - lo + 1, d, dtype=torch.float64)
+    buf[1:] = G.T @ s_all
+    ds = ex.reduce_scatter_users(ds_all)
+    sm = small_glob[rank].clone()
+    ex.finish_routed(st, sm, dz_glob[rank * Bl * L:(rank + 1) * Bl * L].clone(), buf, lo, _index_add_scatter)
+    # reference: autograd of the global loss + the scatter of every rank's rows
+    Eg = E.clone().requires_grad_(True)
+    sg = s_glob.clone().requires_grad_(True)
+    torch.nn.functional.cross_entropy(sg @ Eg.T, ans_glob).backward()
+    want_dE = Eg.grad.clone()
+    _index_add_scatter(ids_glob.reshape(-1), dz_glob, want_dE)
+    assert (buf[1:] - want_dE[lo:hi]).abs().max() < 1e-12
+    assert buf[0].abs().max() == 0                               # the landing row of key 0 is never written
+    assert (ds - sg.grad[mine]).abs().max() < 1e-12
+    assert (sm - small_glob.sum(0)).abs().max() < 1e-12
+    item = torch.nn.Parameter(torch.zeros(N, d))
+    ex.item_param = item
+    ex.publish_shard_grad(buf[1:], lo, hi)
+    assert item._bsa_shard.lo == lo and item._bsa_shard.hi == hi and item._bsa_shard.grad.shape == (hi - lo, d)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_vocab_parallel_exchange_equals_global_cross_entropy(world):
+    _spawn(_vocab_parallel_worker, world)
+
+
+def test_vocab_parallel_needs_divisible_table():
+    _spawn(_vv_worker, 2)
+
+
+def _vv_worker(rank, world):
+    with pytest.raises(RuntimeError, match="divisible"):
+        GradExchange(vocab_parallel=True).shard(7)
+
+
 # ------------------------------------------------------------------------------------------- evaluation
 def _np_score_topk(s, shard, indptr, indices, k, offset):
     """numpy stand-in for bsa_score_topk: global ids, score desc then id asc, history items score 0.0,

@@ -93,8 +93,8 @@ def synth_batches(cfg, B, seed, n):
 def make_config(name, desc, B, world, args):
     """The `config` object of the JSON line — identical for the GPU arm and the reference arm of the same command."""
     cfg = {"workload": desc, "per_gpu_batch": B, "global_batch": B * world, "dropout": P_DROP,
-           "parallelism": f"dp{world}" + (" (train: replica + NCCL gradient exchange; eval: item table row-sharded "
-                                          f"{world} ways, top-k merge)" if world > 1 else ""),
+           "parallelism": f"dp{world}" + (" (train: data-parallel over NCCL — the exchange used is run_detail.dp_exchange; eval: item table "
+                                          f"row-sharded {world} ways, top-k merge)" if world > 1 else ""),
            "l2": "inputs_exceed_l2 (item table + activations >> 126 MB)" if name in ("c3", "c4") else
                  "l2_flushed_between_steps (256 MB scratch write)",
            "optimizer": "Adam inside the step"}
@@ -586,8 +586,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-reference-gpu", action="store_true")
     ap.add_argument("--ce-impl", type=int, default=0)
-    ap.add_argument("--dp", default="overlap", choices=["overlap", "bucket", "vp"],
-                    help="N>1 gradient exchange: overlap = GradExchange inside backward (dense CE part all-reduced under the "
+    ap.add_argument("--dp", default="auto", choices=["auto", "overlap", "bucket", "vp"],
+                    help="N>1 gradient exchange: auto = vp where the item table divides by the world size and the optimizer is "
+                         "FusedAdam, else overlap; overlap = GradExchange inside backward (dense CE part all-reduced under the "
                          "encoder backward, sparse rows all-gathered); bucket = one flat all-reduce after backward; vp = "
                          "vocabulary-parallel cross-entropy + sharded item-table Adam (no [N,d] all-reduce)")
     ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
@@ -650,6 +651,8 @@ def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
     from bsarec_b200.parallel import allreduce_gradients
     dev, model, barrier = _setup(args, cfg, B, rank, world, local_rank)
     model.ce_impl = args.ce_impl
+    if args.dp == "auto":
+        args.dp = "vp" if (world > 1 and cfg["item_size"] % world == 0 and args.optimizer == "fused") else "overlap"
     if world > 1 and args.dp in ("overlap", "vp"):
         model.enable_data_parallel(vocab_parallel=args.dp == "vp")
     opt_cls = FusedAdam if args.optimizer == "fused" else torch.optim.Adam

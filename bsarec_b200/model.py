@@ -147,6 +147,11 @@ class BSARecModel(nn.Module):
         and user_ids are accepted and ignored, as in the reference."""
         names = [n for n, _ in self.named_parameters()]
         tensors = [p for _, p in self.named_parameters()]
+        if self._exchange is not None and self._exchange.vocab_parallel and \
+                getattr(self.item_embeddings.weight, "_bsa_shard", None) is not None and torch.is_grad_enabled():
+            raise RuntimeError("bsarec_b200: the previous step's row-shard gradient of the item table was never applied — "
+                               "vocabulary-parallel training needs bsarec_b200.FusedAdam (a stock optimizer sees no .grad "
+                               "on the table and would silently leave it untrained)")
         return Fn.FusedLoss.apply(self._hyper(), names, input_ids, answers, self.training, self._next_seed(),
                                   self.ce_impl, self._exchange, *tensors)
 

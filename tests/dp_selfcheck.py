@@ -27,11 +27,11 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    cfgkw = dict(item_size=5004, hidden_size=64, max_seq_length=50, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.7)
+    cfgkw = dict(item_size=5040, hidden_size=64, max_seq_length=50, num_attention_heads=2, num_hidden_layers=2, c=5, alpha=0.7)
     cfg = oracle_cfg(cfgkw)
     P = perturbed_params(cfg, 7)
     Bl = 24
-    ids, answers = synth_batch(17, Bl * world, 50, 5004)
+    ids, answers = synth_batch(17, Bl * world, 50, 5040)
     mine = slice(rank * Bl, (rank + 1) * Bl)
     res, after = {}, {}
     for mode in ("overlap", "bucket", "vp"):

@@ -111,6 +111,7 @@ SIGNATURES = {
     "bsa_gather_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
     "bsa_scatter_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
     "bsa_gather_rows": (_I, [_VP, _I64, _I64, _VP, _I, _VP, _VP]),
+    "bsa_scatter_rows": (_I, [_VP, _I64, _I64, _VP, _I, _VP, _VP]),
     "bsa_bce_pair_workspace_bytes": (_SZ, [_I, _I]),
     "bsa_bce_pair_fwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_bce_pair_bwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),

@@ -1,6 +1,7 @@
 // bsa_block_fwd / bsa_block_bwd: one BSARecBlock (model/bsarec.py:62-104, model/_modules.py:61-140).
 #include "../../include/bsarec_b200.h"
 #include "common.cuh"
+#include <cstdlib>
 #include "gemm_simt.cuh"
 #include "rowwise.cuh"
 #include "umma_engine.cuh"
@@ -78,7 +79,20 @@ struct Lin {               // where the linears run: tcgen05 3xTF32 engine (defa
     float *w_hi, *w_lo;    // [4d*d] scratch for the weight's split pair
     float* partial; size_t partial_bytes;      // split-K slabs (weight gradients)
     bool inference = false;                    // forward only: nothing is kept for a backward pass
+    // lazy operand splits (the [B, d] last-row path): an Act that arrives without its pair is split here on the fly
+    float *s1_hi = nullptr, *s1_lo = nullptr, *s2_hi = nullptr, *s2_lo = nullptr;
 };
+
+// the (hi, lo) pair of an activation operand: its own, or a split made now into the Lin's scratch
+int act_pair(const Lin& ln, const Act& a, long long n, float* s_hi, float* s_lo, const float*& hi, const float*& lo, cudaStream_t st);
+
+int act_pair(const Lin& ln, const Act& a, long long n, float* s_hi, float* s_lo, const float*& hi, const float*& lo, cudaStream_t st) {
+    (void)ln;
+    if (a.hi) { hi = a.hi; lo = a.lo; return 0; }
+    BSA_REQUIRE(s_hi && s_lo, "tcgen05 linear: operand has no split pair and no scratch was provided");
+    hi = s_hi; lo = s_lo;
+    return umma_split(a.x, s_hi, s_lo, n, st);
+}
 
 long long lin_ws_floats(long long d) { return 2 * (4 * d * d + 256) + (long long)(umma_gemm_partial_bytes((int)(4 * d), (int)d) / 4); }
 
@@ -119,7 +133,9 @@ int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, f
         if (rc) return rc;
         // when the epilogue emits the result's split pair, that pair is all the tcgen05 path reads afterwards: no fp32 copy
         if (ln.inference) { aux_out = nullptr; if (act == ACT_GELU_SAVE_GRAD) act = ACT_GELU_SAVE_PRE; }    // nothing kept: plain GELU
-        return umma_gemm_ps((int)M, N, K, a.hi, a.lo, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out_hi ? nullptr : out, N, bias,
+        const float *ah_, *al_;
+        if ((rc = act_pair(ln, a, M * K, ln.s1_hi, ln.s1_lo, ah_, al_, st))) return rc;
+        return umma_gemm_ps((int)M, N, K, ah_, al_, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out_hi ? nullptr : out, N, bias,
                             act, aux_out, nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
     }
     GemmP p;
@@ -135,7 +151,9 @@ int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, lo
         int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
         if (rc) return rc;
         // colpart (tcgen05 path only): the epilogue also leaves column sums of dx per 32-row group, [4 * ceil(M / 128), K]
-        return umma_gemm_ps((int)M, K, N, dy.hi, dy.lo, M, N, N, false, ln.w_hi, ln.w_lo, N, K, K, true, dx, K, nullptr, act, nullptr,
+        const float *gh_, *gl_;
+        if ((rc = act_pair(ln, dy, M * N, ln.s1_hi, ln.s1_lo, gh_, gl_, st))) return rc;
+        return umma_gemm_ps((int)M, K, N, gh_, gl_, M, N, N, false, ln.w_hi, ln.w_lo, N, K, K, true, dx, K, nullptr, act, nullptr,
                             aux_in, 1.f, accumulate, out_hi, out_lo, nullptr, 0, st, colpart);
     }
     GemmP p;
@@ -148,8 +166,12 @@ int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, lo
 int linear_bwd_weight(const Lin& ln, const Act& dy, const Act& x, float* dW, float* db, long long M, int N, int K, float* part_sk,
                       float* part_cs, cudaStream_t st) {
     if (ln.umma) {
-        int rc = umma_gemm_ps(N, K, (int)M, dy.hi, dy.lo, M, N, N, true, x.hi, x.lo, M, K, K, true, dW, K, nullptr, 0, nullptr,
-                              nullptr, 1.f, 0, nullptr, nullptr, ln.partial, ln.partial_bytes, st);
+        const float *gh_, *gl_, *xh_, *xl_;
+        int rc;
+        if ((rc = act_pair(ln, dy, M * N, ln.s1_hi, ln.s1_lo, gh_, gl_, st))) return rc;
+        if ((rc = act_pair(ln, x, M * K, ln.s2_hi, ln.s2_lo, xh_, xl_, st))) return rc;
+        rc = umma_gemm_ps(N, K, (int)M, gh_, gl_, M, N, N, true, xh_, xl_, M, K, K, true, dW, K, nullptr, 0, nullptr,
+                          nullptr, 1.f, 0, nullptr, nullptr, ln.partial, ln.partial_bytes, st);
         if (rc) return rc;
         return db ? colsum(dy.x, M, N, part_cs, db, 0, st) : 0;      // db == nullptr: the producer already summed the columns
     }
@@ -454,7 +476,22 @@ size_t last_workspace_bytes(const bsa_block_desc& c) {
     b.f(2ll * rowwise_partial_blocks(B) * d);
     b.f((long long)colsum_partial_rows(B) * 4 * d);
     b.f(splitk_floats(B, d));
+    b.f(lin_ws_floats(d));                          // tcgen05 linears: weight pair, split-K slabs ...
+    for (int i = 0; i < 4; ++i) b.f(B * 4 * d + 256);      // ... and two lazily split operand pairs
     return b.off + 8192;
+}
+
+// the [B, d] linears of the last-row path: fp32 FFMA GEMMs by default.  BSA_LAST_UMMA=1 sends them to the tcgen05 engine with
+// operands split on the fly — measured (profiles/r2n_bench*.json): no gain, a [512, 256] x K = 256 problem is 4 output tiles,
+// each launch pays the engine's prologue (TMEM allocation, tensor-map fetch) plus two split launches: C3 step 12.57 ->
+// 12.90 ms, C1 1.55 -> 1.70 ms.  Kept as a switch; the lever for these launches is fusing them, not a bigger engine.
+Lin make_last_lin(Bump& b, long long B, long long d) {
+    static const bool use_umma = [] { const char* e = getenv("BSA_LAST_UMMA"); return e && atoi(e) == 1; }();
+    if (linear_impl() != 2 || !use_umma) return Lin{false, nullptr, nullptr, nullptr, 0};
+    Lin ln = make_lin(b, d);
+    ln.s1_hi = b.f(B * 4 * d + 256); ln.s1_lo = b.f(B * 4 * d + 256);
+    ln.s2_hi = b.f(B * 4 * d + 256); ln.s2_lo = b.f(B * 4 * d + 256);
+    return ln;
 }
 
 }  // namespace
@@ -473,12 +510,12 @@ int block_last_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     float* tmp = b.f((long long)B * d);
     float* u = b.f((long long)B * d);
     float* dsp = b.f((long long)B * d);
+    const Lin lin = make_last_lin(b, B, d);
     BSA_REQUIRE(b.ok(), "bsa_block_last_fwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
     const Dropout dr_f = dropout_rows(make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
     const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
     const Dropout dr_a = dropout_rows(make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
     const Dropout dr_o = dropout_rows(make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
-    const Lin lin{false, nullptr, nullptr, nullptr, 0};           // [B, d] problems: fp32 FFMA GEMMs
     const int r = filter_rank(L, c.kept_bins);
     int rc;
     if ((rc = gather_last_rows(x, s.xl, B, L, d, st))) return rc;
@@ -523,12 +560,12 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     float* pbet = b.f((long long)nrb * d);
     float* part_cs = b.f((long long)colsum_partial_rows(B) * 4 * d);
     float* part_sk = b.f(splitk_floats(B, d));
+    const Lin lin = make_last_lin(b, B, d);
     BSA_REQUIRE(b.ok(), "bsa_block_last_bwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
     const Dropout dr_f = dropout_rows(make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
     const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);
     const Dropout dr_a = dropout_rows(make_dropout(c.seed, 3 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
     const Dropout dr_o = dropout_rows(make_dropout(c.seed, 4 + 4 * c.layer, c.p_hidden, c.training), L, L - 1);
-    const Lin lin{false, nullptr, nullptr, nullptr, 0};
     const int r = filter_rank(L, c.kept_bins);
     int rc, nblk = 0;
     const Act axl{s.xl, nullptr, nullptr}, actx{s.ctx, nullptr, nullptr}, ay{s.y, nullptr, nullptr}, ah{s.h_act, nullptr, nullptr};

@@ -389,6 +389,13 @@ int bsa_gather_rows(const int64_t* idx, int64_t n_rows, int64_t src_rows, const 
     return gather_rows((const long long*)idx, n_rows, src_rows, src, d, dst, (cudaStream_t)stream);
 }
 
+int bsa_scatter_rows(const int64_t* idx, int64_t n_rows, int64_t dst_rows, const float* src, int d, float* dst, void* stream) {
+    BSA_REQUIRE(n_rows >= 0 && dst_rows >= 1 && d >= 4, "bsa_scatter_rows: bad sizes");
+    if (n_rows == 0) return 0;
+    BSA_REQUIRE(idx && src && dst, "bsa_scatter_rows: null argument");
+    return scatter_rows((const long long*)idx, n_rows, dst_rows, src, d, dst, (cudaStream_t)stream);
+}
+
 int bsa_scatter_last(const float* src, float* dst, int B, int L, int d, void* stream) {
     BSA_REQUIRE(src && dst, "bsa_scatter_last: null argument");
     if (B == 0) return 0;

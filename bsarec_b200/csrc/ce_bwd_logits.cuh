@@ -211,7 +211,7 @@ ce_bwd_logits_kernel(const __grid_constant__ CeBwdLogitsParams p) {
                         for (int e = 0; e < 4; ++e) {
                             const int u = half * 32 + i4 * 4 + e;
                             const float v = *reinterpret_cast<const float*>(base + u * 128 + ((((lane >> 2) ^ (u & 7))) << 4));
-                            const float gv = expf(v - ls[e]) * scale;
+                            const float gv = fast_exp(v - ls[e]) * scale;
                             float h, lw;
                             split_tf32(gv, h, lw);
                             hi[i4 * 4 + e] = __float_as_uint(h); lo[i4 * 4 + e] = __float_as_uint(lw);
@@ -225,7 +225,7 @@ ce_bwd_logits_kernel(const __grid_constant__ CeBwdLogitsParams p) {
                         const float xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
-                            const float gv = expf(xs[e] - l_own) * scale;
+                            const float gv = fast_exp(xs[e] - l_own) * scale;
                             float h, lw;
                             split_tf32(gv, h, lw);
                             hi[c * 4 + e] = __float_as_uint(h); lo[c * 4 + e] = __float_as_uint(lw);

@@ -790,6 +790,27 @@ int gather_rows(const long long* idx, long long M, long long src_rows, const flo
     return 0;
 }
 
+// dst[idx[i], :] = src[i, :]: the "put" counterpart (rows fetched from their owner written into the local table replica);
+// duplicate indices carry identical rows by construction, so the write order does not matter
+__global__ void __launch_bounds__(256) scatter_rows_kernel(const long long* __restrict__ idx, long long M, long long dst_rows,
+                                                           const float* __restrict__ src, int d, float* __restrict__ dst) {
+    const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= M) return;
+    const long long r = idx[row];
+    if (r < 0 || r >= dst_rows) return;
+    const float4* s4 = reinterpret_cast<const float4*>(src + row * d);
+    float4* d4 = reinterpret_cast<float4*>(dst + r * d);
+    for (int c = threadIdx.x & 31; c < d / 4; c += 32) d4[c] = s4[c];
+}
+
+int scatter_rows(const long long* idx, long long M, long long dst_rows, const float* src, int d, float* dst, cudaStream_t st) {
+    if (M == 0) return 0;
+    BSA_REQUIRE(d % 4 == 0, "scatter_rows: row length must be a multiple of 4");
+    scatter_rows_kernel<<<cdiv(M, 8), 256, 0, st>>>(idx, M, dst_rows, src, d, dst);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
 int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStream_t st) {
     last_rows_kernel<<<cdiv((long long)B * d, 256), 256, 0, st>>>(src, dst, B, L, d, 0);
     BSA_LAUNCH_CHECK();

@@ -1,6 +1,7 @@
 // tcgen05 3xTF32 engine: epilogues, launchers and the cross-entropy / scoring / linear entry points built on
 // umma_gemm.cuh.
 #include <cstdlib>
+#include <cstring>
 #include "umma_engine.cuh"
 #include "umma_gemm.cuh"
 #include "ce_topk.cuh"
@@ -211,68 +212,78 @@ struct EpiStore {
 // 128 B per store instruction): the backward pass reads it back instead of recomputing s E^T (ce_bwd_logits.cuh).
 template <int BN>
 struct EpiLse {
-    struct Params { const long long* answers; float* part_m; float* part_s; float* tgt; float* logits; long long ld; };
+    struct Params {
+        const long long* answers; float* part_m; float* part_s; float* tgt;
+        int store_logits;                 // 1: also write the tile through `logits_map`
+        CUtensorMap logits_map;           // [M, N] fp32 (pitch ld), box {32 cols, 32 rows}, 128-B swizzle
+    };
     static constexpr int WARPS = 8;                      // two warps per TMEM lane quarter, each owning half of the tile's columns
-    static constexpr int SMEM_BYTES = WARPS * 4096;
+    static constexpr int SMEM_BYTES = WARPS * 4096 + 1024;      // one 32 x 32 fp32 box per warp, 1024-B aligned (swizzle atom)
     const Params& p; const GemmCore& g; int rit;
-    float4* stg; int quarter, half, lane;
+    unsigned char* box; int quarter, half, lane;
     float m = -INFINITY, s = 0.f;
     long long ans = -1;
     __device__ EpiLse(const Params& p_, const GemmCore& g_, unsigned char* smem, int epi_warp, int lane_)
-        : p(p_), g(g_), rit((epi_warp & 3) * 32 + lane_), stg(reinterpret_cast<float4*>(smem) + epi_warp * 256),
-          quarter(epi_warp & 3), half(epi_warp >> 2), lane(lane_) {
+        : p(p_), g(g_), rit((epi_warp & 3) * 32 + lane_), quarter(epi_warp & 3), half(epi_warp >> 2), lane(lane_) {
+        box = (unsigned char*)(((uintptr_t)smem + 1023) & ~(uintptr_t)1023) + epi_warp * 4096;
         const long long row = (long long)(blockIdx.x % g.m_tiles) * BM + rit;
         if (row < g.M) ans = p.answers[row];
     }
-    __device__ void tile(uint32_t acc, const TileCoord& tc) {
-        const int n0 = tc.n * BN;
-#pragma unroll 1
-        for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
-            float v[32];
-            tmem_ld32(acc + c0, v);
-            if (n0 + c0 >= g.N) continue;
-            if (p.logits) {
+    __device__ __forceinline__ void chunk(float (&v)[32], const TileCoord& tc, int n0, int c0) {
+        if (n0 + c0 >= g.N) return;
+        if (p.store_logits) {
+            // this warp's 32 x 32 block leaves through a TMA store: the row goes into the box as 8 swizzled 16-byte chunks
+            // (conflict-free), one lane issues the bulk copy, the LSU never sees the global write and ragged edges are clipped
+            if (lane == 0) tma_store_wait_read<0>();             // the previous block's copy has finished reading the box
+            __syncwarp();
 #pragma unroll
-                for (int j = 0; j < 8; ++j) stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                __syncwarp();
-                const int sub = lane >> 3, c4 = lane & 7;
-                const int col = n0 + c0 + c4 * 4;
-                const long long row0 = (long long)tc.m * BM + quarter * 32;
-#pragma unroll
-                for (int t = 0; t < 8; ++t) {
-                    const int r = t * 4 + sub;
-                    const float4 x = stg[r * 8 + (c4 ^ (r & 7))];
-                    if (row0 + r < g.M && col < g.N) {
-                        float* dst = p.logits + (row0 + r) * p.ld + col;
-                        if (col + 3 < g.N) *reinterpret_cast<float4*>(dst) = x;
-                        else { const float xs[4] = {x.x, x.y, x.z, x.w}; for (int e = 0; e < 4; ++e) if (col + e < g.N) dst[e] = xs[e]; }
-                    }
-                }
-                __syncwarp();
-            }
-            float cm = -INFINITY;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                if (n0 + c0 + j >= g.N) v[j] = -INFINITY;
-                cm = fmaxf(cm, v[j]);
-            }
-            const float mn = fmaxf(m, cm);
-            float acc_s = 0.f;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) acc_s += expf(v[j] - mn);
-            s = s * expf(m - mn) + acc_s;          // m == -inf on the first chunk: exp(-inf) = 0
-            m = mn;
-            const long long a = ans - (n0 + c0);
-            if (a >= 0 && a < 32) {
-                float t = 0.f;
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (j == (int)a) t = v[j];
-                const long long row = (long long)tc.m * BM + rit;
-                p.tgt[row] = t;
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(box + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&p.logits_map, box, n0 + c0, tc.m * BM + quarter * 32);
+                tma_store_commit();
             }
         }
+        float cm = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (n0 + c0 + j >= g.N) v[j] = -INFINITY;
+            cm = fmaxf(cm, v[j]);
+        }
+        const float mn = fmaxf(m, cm);
+        float acc_s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc_s += fast_exp(v[j] - mn);
+        s = s * fast_exp(m - mn) + acc_s;      // m == -inf on the first chunk: ex2(-inf) = 0
+        m = mn;
+        const long long a = ans - (n0 + c0);
+        if (a >= 0 && a < 32) {
+            float t = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (j == (int)a) t = v[j];
+            const long long row = (long long)tc.m * BM + rit;
+            p.tgt[row] = t;
+        }
+    }
+    __device__ void tile(uint32_t acc, const TileCoord& tc) {
+        static_assert(BN == 128, "EpiLse: two 32-column chunks per warp");
+        const int n0 = tc.n * BN, ca = half * (BN / 2), cb = ca + 32;
+        uint32_t ra[32], rb[32];
+        tmem_ld32_issue(acc + ca, ra);                 // both chunks in flight before the single wait
+        tmem_ld32_issue(acc + cb, rb);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(ra[j]);
+        chunk(v, tc, n0, ca);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rb[j]);
+        chunk(v, tc, n0, cb);
     }
     __device__ void finish() {       // one (max, sum) partial per (strip, column half) and user
+        if (p.store_logits && lane == 0) tma_store_wait<0>();        // every store of this warp has landed before the CTA exits
         const int m_tile = blockIdx.x % g.m_tiles, strip = blockIdx.x / g.m_tiles;
         const long long row = (long long)m_tile * BM + rit;
         if (row < g.M) { p.part_m[(long long)(strip * 2 + half) * g.M + row] = m; p.part_s[(long long)(strip * 2 + half) * g.M + row] = s; }
@@ -767,7 +778,11 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
     if ((rc = make_core(g, B, (int)N, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;
     int nstrips = w.nstrips;
     if (nstrips > g.n_tiles) nstrips = g.n_tiles;
-    EpiLse<CE_BN>::Params ep{answers, w.part_m, w.part_s, w.tgt, g_ce_fused == 2 ? w.logits : nullptr, w.ld};
+    EpiLse<CE_BN>::Params ep;
+    ep.answers = answers; ep.part_m = w.part_m; ep.part_s = w.part_s; ep.tgt = w.tgt;
+    ep.store_logits = (g_ce_fused == 2 && w.logits) ? 1 : 0;
+    if (ep.store_logits) { if ((rc = make_tmap_2d(&ep.logits_map, w.logits, B, N, w.ld, 32, false))) return rc; }
+    else memset(&ep.logits_map, 0, sizeof(ep.logits_map));
     {
         ProfScope prof(PROF_CE_FWD_UMMA, st, 2.0 * B * (double)N * d);
         if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiLse<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;

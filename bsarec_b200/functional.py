@@ -223,6 +223,16 @@ def gather_rows(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def scatter_rows(dst: torch.Tensor, idx: torch.Tensor, src: torch.Tensor) -> None:
+    """dst[idx[i], :] = src[i, :] (duplicates in idx must carry identical rows)."""
+    lib = _cabi.load()
+    idx = _require_cuda(idx, "idx", torch.int64)
+    src = _require_cuda(src, "src", torch.float32)
+    with torch.cuda.device(dst.device):
+        check(lib.bsa_scatter_rows(_ptr(idx), idx.numel(), dst.shape[0], _ptr(src), dst.shape[1], _ptr(dst), _stream()),
+              "bsa_scatter_rows")
+
+
 def gather_last(x: torch.Tensor) -> torch.Tensor:
     lib = _cabi.load()
     B, L, d = x.shape

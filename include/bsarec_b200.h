@@ -314,6 +314,9 @@ int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* str
  * copies.  Used by the data-parallel exchange to pack the rows that carry an item-table gradient; idx int64 [n_rows]
  * in [0, src_rows), d % 4 == 0. */
 int bsa_gather_rows(const int64_t* idx, int64_t n_rows, int64_t src_rows, const float* src, int d, float* dst, void* stream);
+/* dst[idx[i], :] = src[i, :] — rows fetched from their owning rank written into the local replica of the item table
+ * (vocabulary-parallel training); idx int64 [n_rows] in [0, dst_rows), duplicates must carry identical rows. */
+int bsa_scatter_rows(const int64_t* idx, int64_t n_rows, int64_t dst_rows, const float* src, int d, float* dst, void* stream);
 /* dst [B,L,d] = 0 except dst[:, L-1, :] = src [B,d] */
 int bsa_scatter_last(const float* src, float* dst, int B, int L, int d, void* stream);
 

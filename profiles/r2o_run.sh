@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_umma.py tests/test_gpu_named_configs.py -m gpu -q -x 2>&1 | tail -6 > gpurun_out/r2o_pytest.log; tail -3 gpurun_out/r2o_pytest.log
+timeout 300 python profiles/ce_probe.py > gpurun_out/r2o_ce_probe.log 2>&1; cat gpurun_out/r2o_ce_probe.log
+timeout 600 python bench.py --no-cpu-baseline --no-reference-gpu > gpurun_out/r2o_bench.json 2> gpurun_out/r2o_bench.err; echo bench rc=$?; tail -3 gpurun_out/r2o_bench.err

@@ -388,13 +388,17 @@ class FusedLoss(torch.autograd.Function):
     def forward(ctx, hyper: Hyper, names: Sequence[str], ids, answers, training: bool, seed: int, ce_impl: int,
                 exchange, *tensors):
         params = dict(zip(names, tensors))
+        if exchange is not None and exchange.vocab_parallel:
+            E = params["item_embeddings.weight"]
+            ctx.ex_state = exchange.prepare_routed(_require_cuda(ids, "input_ids", torch.int64), E.shape[0])
+            if exchange.stale:                               # rows of this batch's items come from the ranks that own them
+                exchange.fetch_rows(ctx.ex_state, E, gather_rows, scatter_rows)
         xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
         s = xs[-1]
         ctx.hyper, ctx.names, ctx.state, ctx.ce_impl, ctx.exchange = hyper, names, state, ce_impl, exchange
         if exchange is not None and exchange.vocab_parallel:
             # every rank scores ALL users of the global batch against ITS rows of the item table
             E = params["item_embeddings.weight"]
-            ctx.ex_state = exchange.prepare_routed(ids, E.shape[0])
             s_all, ans_local = exchange.gather_users(s, _require_cuda(answers, "answers", torch.int64), E.shape[0])
             lo, hi = exchange.shard(E.shape[0])
             lse_p, tgt_p, ce_ws = ce_forward_partial(s_all, E[lo:hi], ans_local)

@@ -202,10 +202,29 @@ class BSARecModel(nn.Module):
     def train(self, mode: bool = True):
         if mode:
             self.invalidate_eval_cache()
+        else:
+            self.sync_item_table()           # evaluation reads the whole table: bring the replica up to date first
         return super().train(mode)
+
+    def sync_item_table(self):
+        """Vocabulary-parallel training leaves each rank's replica of the item table fresh only in its own row shard and
+        the rows its batches read; this all-gathers the shards (a collective: every rank must call it).  ``eval()`` and
+        ``state_dict()`` do."""
+        ex = getattr(self, "_exchange", None)
+        if ex is not None and ex.vocab_parallel and ex.stale:
+            ex.sync_table()
+            torch.autograd.graph.increment_version(self.item_embeddings.weight)
+            self.invalidate_eval_cache()
+
+    def state_dict(self, *a, **kw):
+        self.sync_item_table()
+        return super().state_dict(*a, **kw)
 
     def load_state_dict(self, *a, **kw):
         self.invalidate_eval_cache()
+        ex = getattr(self, "_exchange", None)
+        if ex is not None:
+            ex.stale = False
         return super().load_state_dict(*a, **kw)
 
     # ------------------------------------------------------------------ helpers

@@ -79,8 +79,9 @@ class FusedAdam(torch.optim.Optimizer):
 
     def _step_shard(self, lib, group, p, shard):
         """Adam on rows [lo, hi) of ``p`` with the complete row-shard gradient ``shard.grad`` (state kept for the shard
-        only: 1/world of the memory and of the 28 B/element pass), then an all-gather of the updated rows so every
-        replica of the table stays identical (parallel.ShardedItemGrad)."""
+        only: 1/world of the memory and of the 28 B/element pass).  The other replicas are brought up to date lazily — each
+        rank fetches the rows its next batch reads, `model.eval()` / `state_dict()` all-gather the shards — or, with
+        `exchange.fetch = False`, by an all-gather of the updated rows right here."""
         import torch.distributed as dist
         if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
             raise RuntimeError("FusedAdam: sharded parameters must be contiguous CUDA fp32")
@@ -100,5 +101,8 @@ class FusedAdam(torch.optim.Optimizer):
                                     rows.numel(), float(group["lr"]), float(b1), float(b2), float(group["eps"]),
                                     float(group["weight_decay"]), st["step"], torch.cuda.current_stream().cuda_stream),
                   "bsa_adam_step")
-        dist.all_gather_into_tensor(p.data.view(-1), rows.reshape(-1).clone(), group=shard.group)
+        if shard.exchange is not None and shard.exchange.fetch:
+            shard.exchange.stale = True          # the other ranks fetch the rows they read (GradExchange.fetch_rows / sync_table)
+        else:
+            dist.all_gather_into_tensor(p.data.view(-1), rows.reshape(-1).clone(), group=shard.group)
         torch.autograd.graph.increment_version(p)

@@ -74,6 +74,12 @@ class GradExchange:
         # vocabulary-parallel cross-entropy + sharded item-table optimizer step (methods below)
         self.vocab_parallel = bool(vocab_parallel)
         self.item_param = item_param
+        # vocabulary-parallel training keeps each rank's replica of the item table fresh only where it is read: the rank's own
+        # row shard (updated by its FusedAdam step) and the rows of the current batch, fetched from their owners at the start
+        # of the forward pass (fetch_rows).  `stale` says the rest of the replica lags behind: sync_table() all-gathers the
+        # shards (BSARecModel.eval() / state_dict() call it).
+        self.fetch = True
+        self.stale = False
 
     def _issue(self, fn, *a):
         self.collectives += 1
@@ -202,6 +208,43 @@ class GradExchange:
             st.cap_host, st.cap_event = counts, None
         return st
 
+    def fetch_rows(self, st: "_ExchangeState", table: torch.Tensor, gather_fn: Optional[Callable], scatter_fn: Optional[Callable]):
+        """Bring the rows of this batch's items from the ranks that own them into the local replica `table` [N, d] — the
+        first thing a vocabulary-parallel forward pass does when the replica is stale.  Requests are the batch's non-zero
+        ids sorted by owner (the order prepare_routed made): one all-to-all carries the ids out, the owners gather the rows
+        (bsa_gather_rows), one all-to-all carries them back, bsa_scatter_rows writes them into the replica.  Row 0 (the
+        padding row, read by every padded position) is broadcast from its owner.  ~L*B*(8 + 4d) bytes per rank instead of
+        the whole table after every optimizer step."""
+        if st.cap_event is not None:
+            st.cap_event.synchronize()
+        counts = st.cap_host.tolist()
+        send = counts[self.rank]                                   # my requests per owner
+        recv = [counts[r][self.rank] for r in range(self.world)]   # requests I serve
+        n_send, n_recv = sum(send), sum(recv)
+        d = table.shape[1]
+        ids_req = st.flat_ids[st.order[:n_send]].contiguous()
+        ids_srv = torch.empty(n_recv, dtype=torch.int64, device=table.device)
+        dist.all_to_all_single(ids_srv, ids_req, recv, send, group=self.group)
+        rows_srv = gather_fn(table, ids_srv) if gather_fn is not None else torch.index_select(table, 0, ids_srv)
+        rows_req = torch.empty(n_send, d, dtype=table.dtype, device=table.device)
+        dist.all_to_all_single(rows_req.view(-1), rows_srv.view(-1), [c * d for c in send], [c * d for c in recv], group=self.group)
+        if scatter_fn is not None:
+            scatter_fn(table, ids_req, rows_req)
+        else:
+            table.index_copy_(0, ids_req, rows_req)
+        dist.broadcast(table[0], src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        self.collectives += 3
+
+    def sync_table(self):
+        """All-gather the row shards into every replica (after it: stale == False)."""
+        if not (self.vocab_parallel and self.stale) or self.item_param is None:
+            return
+        E = self.item_param.data
+        lo, hi = self.shard(E.shape[0])
+        dist.all_gather_into_tensor(E.view(-1), E[lo:hi].reshape(-1).clone(), group=self.group)
+        self.collectives += 1
+        self.stale = False
+
     def finish_routed(self, st: "_ExchangeState", small_flat: torch.Tensor, dz: torch.Tensor, shard_buf: torch.Tensor, lo: int,
                       scatter_fn: Callable, gather_fn: Optional[Callable] = None):
         """shard_buf [rows + 1, d]: row 0 is a landing row (the scatter skips key 0), row 1 + r is shard row r — already
@@ -233,16 +276,16 @@ class GradExchange:
     def publish_shard_grad(self, g_shard: torch.Tensor, lo: int, hi: int):
         if self.item_param is None:
             raise RuntimeError("vocabulary-parallel exchange: item_param not set (use BSARecModel.enable_data_parallel)")
-        self.item_param._bsa_shard = ShardedItemGrad(g_shard, lo, hi, self.group)
+        self.item_param._bsa_shard = ShardedItemGrad(g_shard, lo, hi, self.group, self)
 
 
 class ShardedItemGrad:
     """Attached to the item-table parameter as ``_bsa_shard`` by a vocabulary-parallel backward pass: the COMPLETE
     gradient of rows [lo, hi) (global-batch mean).  ``FusedAdam.step`` updates those rows and all-gathers them."""
-    __slots__ = ("grad", "lo", "hi", "group")
+    __slots__ = ("grad", "lo", "hi", "group", "exchange")
 
-    def __init__(self, grad, lo, hi, group):
-        self.grad, self.lo, self.hi, self.group = grad, lo, hi, group
+    def __init__(self, grad, lo, hi, group, exchange=None):
+        self.grad, self.lo, self.hi, self.group, self.exchange = grad, lo, hi, group, exchange
 
 
 class _ExchangeState:

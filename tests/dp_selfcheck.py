@@ -52,7 +52,9 @@ def main():
             else:
                 res[mode][n] = p.grad.detach().clone()
         optim.step()
+        model.eval()                            # vp: all-gathers the row shards into every replica (sync_item_table)
         after[mode] = {n: p.detach().clone() for n, p in model.named_parameters()}
+        model.train()
     worst = 0.0
     for n in res["overlap"]:
         a, b = res["overlap"][n], res["bucket"][n]
@@ -81,6 +83,36 @@ def main():
             assert torch.equal(g, gathered[0]), f"vp replicas differ after the step on {n}"
     assert worst_vp < 1e-4, worst_vp            # another problem shape for the CE kernels: the parity bar itself
     assert worst_step < 2.1e-3, worst_step      # first Adam step: |update| = lr, sign flips only where the gradient is noise
+    # three optimizer steps on fresh batches: the vocabulary-parallel path (rows of each batch fetched from their owners,
+    # row-shard Adam) must follow the replicated path — same global-batch loss every step, same table after the last one
+    traj = {}
+    for mode in ("bucket", "vp"):
+        model = build_model(cfgkw, P, dev).train()
+        optim = FusedAdam(model.parameters(), lr=1e-3)
+        if mode == "vp":
+            model.enable_data_parallel(vocab_parallel=True)
+        losses = []
+        for step in range(3):
+            bi, ba = synth_batch(100 + step, Bl * world, 50, 5040)
+            loss = model.calculate_loss(bi[mine].to(dev), ba[mine].to(dev), None, None, None)
+            optim.zero_grad()
+            loss.backward()
+            if mode == "bucket":
+                allreduce_gradients(list(model.parameters()))
+            optim.step()
+            l = loss.detach().clone()
+            if mode == "bucket":                 # local-batch mean -> global-batch mean
+                dist.all_reduce(l)
+                l /= world
+            losses.append(float(l))
+        model.eval()
+        traj[mode] = (losses, model.item_embeddings.weight.detach().clone())
+    for a, b in zip(traj["vp"][0], traj["bucket"][0]):
+        assert abs(a - b) < 1e-4 * abs(b), (traj["vp"][0], traj["bucket"][0])
+    table_diff = (traj["vp"][1] - traj["bucket"][1]).abs().max().item()
+    assert table_diff < 3 * 2.1e-3, table_diff
+    close = ((traj["vp"][1] - traj["bucket"][1]).abs() < 2e-5).float().mean().item()
+    assert close > 0.98, close
     if rank == 0:
         _, g64 = oracle.loss_and_grads({k: v.double() for k, v in P.items()}, ids, answers, cfg, use_fft=False)
         bad = 0.0
@@ -91,7 +123,8 @@ def main():
             bad = max(bad, (g.cpu().double() - g64[n]).abs().max().item() / den)
         assert bad < 1e-4, bad
         print(f"dp_selfcheck ok: world {world}, overlap vs bucket {worst:.2e}, vocab-parallel vs bucket {worst_vp:.2e} "
-              f"(params after one FusedAdam step: max |diff| {worst_step:.2e}), vs oracle(global batch) {bad:.2e}", flush=True)
+              f"(params after one FusedAdam step: max |diff| {worst_step:.2e}; 3-step losses vp {traj['vp'][0]} vs replicated "
+              f"{traj['bucket'][0]}, table rows within 2e-5: {close:.4f}), vs oracle(global batch) {bad:.2e}", flush=True)
     dist.destroy_process_group()
 
 

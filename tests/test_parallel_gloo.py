@@ -199,6 +199,37 @@ def _vocab_parallel_worker(rank, world):
     assert item._bsa_shard.lo == lo and item._bsa_shard.hi == hi and item._bsa_shard.grad.shape == (hi - lo, d)
 
 
+def _fetch_worker(rank, world):
+    """Lazy replica refresh: every rank's copy of the table is fresh only in its own shard; fetch_rows must bring exactly
+    the rows this rank's batch reads (and row 0) from their owners, leaving them equal to the true table."""
+    N, d, Bl, L = 48, 4, 3, 7
+    g = torch.Generator().manual_seed(21)
+    truth = torch.randn(N, d, generator=g)
+    ids = torch.randint(1, N, (world, Bl, L), generator=g)
+    ids[:, :, :2] = 0
+    ex = GradExchange(vocab_parallel=True)
+    lo, hi = ex.shard(N)
+    table = torch.full((N, d), float("nan"))
+    table[lo:hi] = truth[lo:hi]                                   # stale everywhere else
+    st = ex.prepare_routed(ids[rank], N)
+    ex.fetch_rows(st, table, None, None)
+    need = torch.unique(ids[rank])
+    assert torch.equal(table[need], truth[need])                  # includes row 0 (padding positions read it)
+    untouched = torch.ones(N, dtype=torch.bool)
+    untouched[need] = False
+    untouched[lo:hi] = False
+    assert torch.isnan(table[untouched]).all()                    # nothing else was written
+    ex.item_param = torch.nn.Parameter(table.clone())
+    ex.stale = True
+    ex.sync_table()
+    assert torch.equal(ex.item_param.data, truth) and not ex.stale
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_vocab_parallel_row_fetch_and_table_sync(world):
+    _spawn(_fetch_worker, world)
+
+
 @pytest.mark.parametrize("world", [2, 3])
 def test_vocab_parallel_exchange_equals_global_cross_entropy(world):
     _spawn(_vocab_parallel_worker, world)

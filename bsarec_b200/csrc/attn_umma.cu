@@ -76,6 +76,22 @@ __device__ __forceinline__ void split_region(unsigned char* base, int bytes, int
     }
 }
 
+// bits [0, width) of: columns j0 + b that are <= limit  (limit - j0 >= width - 1: all ones; < 0: none)
+__device__ __forceinline__ uint32_t low_bits_upto(int limit, int j0) {
+    const int rel = limit - j0;
+    return rel >= 31 ? 0xffffffffu : (rel < 0 ? 0u : ((2u << rel) - 1u));
+}
+// valid[] bytes -> one bit per key, 8 words in shared memory (one ballot per word by warp 0)
+__device__ __forceinline__ void pack_valid_bits(const unsigned char* valid, uint32_t* vbits, int warp, int lane) {
+    if (warp == 0) {
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            const uint32_t word = __ballot_sync(0xffffffffu, valid[w * 32 + lane] != 0);
+            if (lane == 0) vbits[w] = word;
+        }
+    }
+}
+
 template <int DH>
 __global__ void __launch_bounds__(AUF_THREADS, 1)
 attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
@@ -89,6 +105,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     uint64_t* o_full = bar_qk + 5;                           // O complete in TMEM                (MMA -> warps 4-7)
     uint32_t* tmem_ptr = (uint32_t*)(bar_qk + 6);
     unsigned char* valid = smem + AU_OFF_BAR + 128;          // [AU_SCOLS + 32]: 1 = key j is an item, 0 = padding / j >= L
+    uint32_t* vbits = (uint32_t*)(smem + AU_OFF_BAR + 64);   // the same as 8 x 32 bits (the mask test is a bit test per score)
     int* s_first = (int*)(bar_qk + 7);                       // first position holding an item (L if none)
     float* xch = (float*)(smem + AU_OFF_QHI);                // [2][AUF_PARTS][128]: row max / row sum parts (Q is dead after MMA 1)
 
@@ -127,6 +144,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);   // L <= 208 < blockDim
+    pack_valid_bits(valid, vbits, warp, threadIdx.x & 31);
     __syncthreads();
     BSA_STAMP(0);
     tc_fence_after();
@@ -195,11 +213,11 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         if (!(live >> c & 1)) continue;
         float v[32];
         tmem_ld32(t_s + lane_base + c * 32, v);
+        const uint32_t allowed = vbits[c] & low_bits_upto(i, c * 32), in_l = low_bits_upto(p.L - 1, c * 32);
 #pragma unroll
         for (int jj = 0; jj < 32; ++jj) {
-            const int j = c * 32 + jj;
-            const float s = v[jj] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
-            if (j < p.L) m = fmaxf(m, s);
+            const float s = v[jj] * p.scale + ((allowed >> jj & 1u) ? 0.f : -10000.f);
+            if (in_l >> jj & 1u) m = fmaxf(m, s);
         }
     }
     xch[part * 128 + quarter * 32 + lane] = m;
@@ -214,6 +232,8 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         if (live >> c & 1) {
             float v[32];
             tmem_ld32(t_s + lane_base + c * 32, v);
+            const uint32_t allowed = vbits[c] & low_bits_upto(i, c * 32);
+            const uint32_t in_l = row_ok ? low_bits_upto(p.L - 1, c * 32) : 0u;
 #pragma unroll
             for (int g4 = 0; g4 < 8; ++g4) {
                 float mult[4];
@@ -225,11 +245,11 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
                 }
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const int j = j0 + e;
-                    const float s = v[g4 * 4 + e] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
+                    const int jj = g4 * 4 + e;
+                    const float s = v[jj] * p.scale + ((allowed >> jj & 1u) ? 0.f : -10000.f);
                     float pr = 0.f;
-                    if (row_ok && j < p.L) {
-                        pr = expf(s - m);
+                    if (in_l >> jj & 1u) {
+                        pr = fast_exp(s - m);
                         l += pr;
                         pr *= mult[e];
                     }
@@ -334,6 +354,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     uint64_t* o_full = bar_qk + 5;                           // dQ complete in TMEM
     uint32_t* tmem_ptr = (uint32_t*)(bar_qk + 6);
     unsigned char* valid = smem + AU_OFF_BAR + 128;
+    uint32_t* vbits = (uint32_t*)(smem + AU_OFF_BAR + 64);
     int* s_first = (int*)(bar_qk + 7);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -371,6 +392,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x < p.L && valid[threadIdx.x]) atomicMin(s_first, (int)threadIdx.x);
+    pack_valid_bits(valid, vbits, warp, threadIdx.x & 31);
     __syncthreads();
     BSA_STAMP(16);
     tc_fence_after();
@@ -516,6 +538,8 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
             float vs[16], vd[16];
             tmem_ld16(t_s + lane_base + c * 16, vs);
             tmem_ld16(t_lo + lane_base + c * 16, vd);
+            const uint32_t allowed = (vbits[(c * 16) >> 5] >> ((c * 16) & 31)) & low_bits_upto(i, c * 16) & 0xffffu;
+            const uint32_t in_l = row_ok ? (low_bits_upto(p.L - 1, c * 16) & 0xffffu) : 0u;
 #pragma unroll
             for (int g4 = 0; g4 < 4; ++g4) {
                 float mult[4];
@@ -528,11 +552,11 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
                 float pd4[4], ds4[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const int j = j0 + e;
+                    const int jj = g4 * 4 + e;
                     float ds = 0.f, pd = 0.f;
-                    if (row_ok && j < p.L) {
-                        const float sp = vs[g4 * 4 + e] * p.scale + ((valid[j] && j <= i) ? 0.f : -10000.f);
-                        const float pr = expf((sp - ls.x) - ls.y);
+                    if (in_l >> jj & 1u) {
+                        const float sp = vs[jj] * p.scale + ((allowed >> jj & 1u) ? 0.f : -10000.f);
+                        const float pr = fast_exp((sp - ls.x) - ls.y);
                         pd = pr * mult[e];
                         ds = pr * (vd[g4 * 4 + e] * mult[e] - delta);
                     }

@@ -295,7 +295,8 @@ __global__ void __launch_bounds__(AT_THREADS)
 attn_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                 const long long* __restrict__ ids, const float* __restrict__ ctx, const float* __restrict__ lse,
                 const float* __restrict__ dctx, float* __restrict__ out1, float* __restrict__ out2, float* __restrict__ delta,
-                int H, int L, int d, float scale, Dropout dr) {
+                int H, int L, int d, float scale, Dropout dr, float* __restrict__ pd_out = nullptr,
+                float* __restrict__ ds_out = nullptr, int NK = 0) {
     extern __shared__ __align__(16) unsigned char at_smem[];
     float* Us = reinterpret_cast<float*>(at_smem);            // streamed operand of S:  K blocks (query owner) / Q blocks
     float* Ws = Us + 2 * AT_BLK * DH;                         // streamed operand of dP: V blocks (query owner) / dctx blocks
@@ -419,6 +420,18 @@ attn_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const 
                         ds[e] = pr * (df[u][e] * mlt - dl);
                         p[e] = pr * mlt;
                     }
+                    if (!KEY_OWNER && pd_out) {
+                        // leave Pd = P o M and dS for the tcgen05 key-owner kernel (attn_kv_umma.cu): [B*H*L, NK] fp32, zeroed by
+                        // the launcher; a fragment row holds columns c, c + 1 -> one float2 per row, 32 contiguous bytes per quad
+                        if (ig0 < L) {
+                            *reinterpret_cast<float2*>(pd_out + ((long long)bh * L + ig0) * NK + c) = make_float2(p[0], p[1]);
+                            *reinterpret_cast<float2*>(ds_out + ((long long)bh * L + ig0) * NK + c) = make_float2(ds[0], ds[1]);
+                        }
+                        if (ig1 < L) {
+                            *reinterpret_cast<float2*>(pd_out + ((long long)bh * L + ig1) * NK + c) = make_float2(p[2], p[3]);
+                            *reinterpret_cast<float2*>(ds_out + ((long long)bh * L + ig1) * NK + c) = make_float2(ds[2], ds[3]);
+                        }
+                    }
                     uint32_t ah[4], al[4];
                     split3(ds[0], ah[0], al[0]); split3(ds[2], ah[1], al[1]); split3(ds[1], ah[2], al[2]); split3(ds[3], ah[3], al[3]);
                     const int rr = nt * 16 + u * 8 + 2 * t;
@@ -496,6 +509,17 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
         }
         const int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, nullptr, nullptr, B, H, L, d, dr, st);
         if (rc) return rc;
+    } else if (g_attn_bwd_umma >= 2 && L > 208) {
+        // long sequences (C5): the mma.sync query owner (the whole key axis does not fit one TMEM accumulator) also leaves
+        // the Pd / dS tiles, and the key owner runs on tcgen05 from them — no second recomputation of the probabilities
+        const long long NK = (L + 15) / 16 * 16, bhl = (long long)B * H * L;
+        float* pd = delta + (bhl + 63) / 64 * 64;
+        float* ds = pd + bhl * NK;
+        BSA_CHECK_CUDA(cudaMemsetAsync(pd, 0, (size_t)(2 * bhl * NK) * sizeof(float), st));      // causal / padding blocks are skipped by the writer
+        attn_bwd_kernel<DH, false><<<grid, AT_THREADS, smem, st>>>(q, k, v, ids, ctx, lse, dctx, dq, nullptr, delta, H, L, d, scale, dr,
+                                                                   pd, ds, (int)NK);
+        BSA_LAUNCH_CHECK();
+        return attn_bwd_kv_umma(q, dctx, pd, ds, dk, dv, B, H, L, d, st);
     } else {
         attn_bwd_kernel<DH, false><<<grid, AT_THREADS, smem, st>>>(q, k, v, ids, ctx, lse, dctx, dq, nullptr, delta, H, L, d, scale, dr);
         BSA_LAUNCH_CHECK();
@@ -515,7 +539,8 @@ int g_attn_bwd_umma = [] { const char* e = getenv("BSA_ATTN_BWD_UMMA"); return e
 
 long long attn_bwd_scratch_floats(int B, int H, int L, int d) {
     const long long bhl = (long long)B * H * L;
-    if (g_attn_bwd_umma >= 2 && g_attn_fwd_umma && attn_umma_supported(L, d, H)) {
+    const bool fused = attn_fused_supported(L, d, H);
+    if (g_attn_bwd_umma >= 2 && fused && ((g_attn_fwd_umma && attn_umma_supported(L, d, H)) || L > 208)) {
         const long long NK = (L + 15) / 16 * 16;
         return (bhl + 63) / 64 * 64 + 2 * bhl * NK + 64;
     }

@@ -10,6 +10,7 @@
 // H weighted sums (and the filter's).  Same result as the full block at row L-1 (up to fp32 rounding), same dropout
 // masks (indices of the full tensors), and the backward is the exact adjoint: dx [B, L, d] for every position.
 // SURVEY.md §7.4 ("last-layer pruning") lists this as a result-preserving shortcut of the reference's math.
+#include <cstdlib>
 #include "lastrow.cuh"
 
 namespace bsa {
@@ -328,7 +329,7 @@ int ew(int op, float* out, float* out2, float* out3, const float* a, const float
     return 0;
 }
 
-constexpr size_t LR_STAGE_LIMIT = 220 * 1024;
+static const size_t LR_STAGE_LIMIT = [] { const char* e = getenv("BSA_LASTROW_STAGE_KB"); return (size_t)(e ? atoi(e) : 220) * 1024; }();   // 0: never stage the tile
 size_t lr_smem_base(int H, int L, int d, bool bwd) { return ((size_t)H * d + (size_t)(H + 1) * d + (size_t)(bwd ? 2 : 1) * H * L + L + 8) * 4; }
 size_t lr_smem_bytes(int H, int L, int d, bool bwd, bool* stage) {
     const size_t base = lr_smem_base(H, L, d, bwd), tile = (size_t)L * d * 4;

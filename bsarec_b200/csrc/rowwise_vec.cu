@@ -5,6 +5,7 @@
 //
 // Why (profiles/r1o_rowwise_ncu_summary.txt): the scalar warp-per-row kernels ran at 13-38 % of DRAM peak — 4-byte
 // loads, one hash per element, and in the filter kernels one thread per channel walking the sequence serially.
+#include <cstdlib>
 #include "rowwise.cuh"
 
 namespace bsa {
@@ -443,7 +444,7 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
     for (int j = threadIdx.x; j < d; j += FT) pbeta2[(long long)b * d + j] = pb[j];
 }
 
-constexpr size_t STAGE_SMEM_LIMIT = 220 * 1024;
+static const size_t STAGE_SMEM_LIMIT = [] { const char* e = getenv("BSA_FILTER_STAGE_KB"); return (size_t)(e ? atoi(e) : 220) * 1024; }();      // BSA_FILTER_STAGE_KB=0: never stage the tile (pass 2 re-reads through L2)
 
 }  // namespace
 

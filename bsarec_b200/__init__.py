@@ -2,12 +2,12 @@
 
 ``MODEL_DICT["bsarec"]`` mirrors ``src/model/__init__.py:10-11`` of the reference.
 """
-from .model import BSARecModel, SASRecModel
+from .model import BSARecModel, SASRecModel, DuoRecModel
 from .trainer import Trainer
 from .optim import FusedAdam
 from .data import SequenceStore, DeviceBatchLoader, HitRankAccumulator
 
-MODEL_DICT = {"bsarec": BSARecModel, "sasrec": SASRecModel}
+MODEL_DICT = {"bsarec": BSARecModel, "sasrec": SASRecModel, "duorec": DuoRecModel}
 
-__all__ = ["BSARecModel", "SASRecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
+__all__ = ["BSARecModel", "SASRecModel", "DuoRecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
            "HitRankAccumulator"]

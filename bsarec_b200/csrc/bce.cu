@@ -87,7 +87,128 @@ __global__ void __launch_bounds__(256) bce_pair_bwd_kernel(const float* __restri
     }
 }
 
+// ------------------------------------------------------------------------------------------ in-batch InfoNCE (DuoRec)
+// model/duorec.py:47-75 with sim = 'dot': z [2B, d] = (view i rows, view j rows); row r's positive is its pair
+// (r + B) mod 2B, its negatives every other row but itself; CrossEntropy(label 0) over (positive, negatives) is
+//   loss_r = -sim[r, pair] + logsumexp_{c != r} sim[r, c],   sim = z z^T / tau;   loss = mean_r loss_r.
+// One block per row; sims are recomputed in the backward (2B x 2B x d FMAs: nothing).  Fixed-order reductions.
+__global__ void __launch_bounds__(256) nce_fwd_kernel(const float* __restrict__ z, int n2, int B, int d, float inv_tau,
+                                                       float* __restrict__ lse, float* __restrict__ loss_rows) {
+    extern __shared__ float nsm[];                 // [d] this row | [n2] sims
+    float* zi = nsm;
+    float* sim = nsm + d;
+    __shared__ float red[8];
+    const int r = blockIdx.x;
+    for (int c = threadIdx.x; c < d; c += blockDim.x) zi[c] = z[(long long)r * d + c];
+    __syncthreads();
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) {
+        const float4* zj = reinterpret_cast<const float4*>(z + (long long)j * d);
+        float acc = 0.f;
+        for (int c = 0; c < d / 4; ++c) {
+            const float4 a = zj[c];
+            acc += a.x * zi[4 * c] + a.y * zi[4 * c + 1] + a.z * zi[4 * c + 2] + a.w * zi[4 * c + 3];
+        }
+        sim[j] = acc * inv_tau;
+    }
+    __syncthreads();
+    float m = -INFINITY;
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) if (j != r) m = fmaxf(m, sim[j]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = red[0];
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) m = fmaxf(m, red[w]);
+    __syncthreads();
+    float su = 0.f;
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) if (j != r) su += expf(sim[j] - m);
+    su = warp_sum_f(su);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = su;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        const float l = m + logf(t);
+        lse[r] = l;
+        loss_rows[r] = l - sim[(r + B) % n2];
+    }
+}
+
+__global__ void nce_mean_kernel(const float* __restrict__ loss_rows, int n2, float* __restrict__ loss) {
+    __shared__ float red[32];
+    float s = 0.f;
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) s += loss_rows[j];
+    s = warp_sum_f(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        *loss = t / (float)n2;
+    }
+}
+
+// dz[r,:] = inv_tau * sum_c (G[r,c] + G[c,r]) z[c,:],  G[r,c] = (exp(sim[r,c] - lse_r) - [c == pair(r)]) * g / 2B for c != r
+__global__ void __launch_bounds__(256) nce_bwd_kernel(const float* __restrict__ z, const float* __restrict__ lse, int n2, int B,
+                                                       int d, float inv_tau, const float* __restrict__ d_loss, float scale,
+                                                       float* __restrict__ dz) {
+    extern __shared__ float nsm[];                 // [d] this row | [n2] coefficients
+    float* zi = nsm;
+    float* coef = nsm + d;
+    const int r = blockIdx.x;
+    const float g = __ldg(d_loss) * scale / (float)n2;
+    for (int c = threadIdx.x; c < d; c += blockDim.x) zi[c] = z[(long long)r * d + c];
+    __syncthreads();
+    const float lr = lse[r];
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) {
+        float cf = 0.f;
+        if (j != r) {
+            const float4* zj = reinterpret_cast<const float4*>(z + (long long)j * d);
+            float acc = 0.f;
+            for (int c = 0; c < d / 4; ++c) {
+                const float4 a = zj[c];
+                acc += a.x * zi[4 * c] + a.y * zi[4 * c + 1] + a.z * zi[4 * c + 2] + a.w * zi[4 * c + 3];
+            }
+            const float sm = acc * inv_tau;
+            const float pair = (j == (r + B) % n2) ? 1.f : 0.f;        // pairing is symmetric: j == pair(r) <=> r == pair(j)
+            cf = (expf(sm - lr) - pair) + (expf(sm - lse[j]) - pair);
+        }
+        coef[j] = cf * g * inv_tau;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < d; c += blockDim.x) {
+        float acc = 0.f;
+        for (int j = 0; j < n2; ++j) acc += coef[j] * z[(long long)j * d + c];
+        dz[(long long)r * d + c] = acc;
+    }
+}
+
 }  // namespace
+
+size_t nce_workspace_bytes(int B) { return al((size_t)2 * B * 4) * 2 + 256; }
+
+// z [2B, d]; loss = mean InfoNCE; ws keeps lse [2B] for the backward
+int nce_fwd(int B, int d, float tau, const float* z, float* loss, void* ws, cudaStream_t st) {
+    BSA_REQUIRE(d % 4 == 0 && B >= 1 && tau > 0.f, "info_nce: need d %% 4 == 0, B >= 1, tau > 0");
+    const int n2 = 2 * B;
+    const size_t smem = (size_t)(d + n2) * 4;
+    BSA_REQUIRE(smem <= 48 * 1024, "info_nce: 2B + d = %d floats exceed the shared-memory plan", d + n2);
+    float* lse = (float*)ws;
+    float* rows = (float*)((char*)ws + al((size_t)n2 * 4));
+    nce_fwd_kernel<<<n2, 256, smem, st>>>(z, n2, B, d, 1.0f / tau, lse, rows);
+    BSA_LAUNCH_CHECK();
+    nce_mean_kernel<<<1, 1024, 0, st>>>(rows, n2, loss);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int nce_bwd(int B, int d, float tau, const float* z, const float* d_loss, float scale, float* dz, const void* ws, cudaStream_t st) {
+    const int n2 = 2 * B;
+    const size_t smem = (size_t)(d + n2) * 4;
+    nce_bwd_kernel<<<n2, 256, smem, st>>>(z, (const float*)ws, n2, B, d, 1.0f / tau, d_loss, scale, dz);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
 
 size_t bce_pair_workspace_bytes(int B, int d) {
     return al((size_t)2 * B * 4) + al(16) + al((size_t)2 * B * d * 4) + al((size_t)2 * B * 8) + scatter_plan_bytes(2ll * B) + 1024;

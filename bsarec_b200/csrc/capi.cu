@@ -375,6 +375,21 @@ int bsa_bce_pair_bwd(int B, int d, int64_t item_size, const float* seq_out, cons
                         d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+size_t bsa_info_nce_workspace_bytes(int B) { return al(nce_workspace_bytes(B)); }
+
+int bsa_info_nce_fwd(int B, int d, float tau, const float* z, float* loss, void* workspace, size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(z && loss && workspace, "bsa_info_nce_fwd: null argument");
+    BSA_REQUIRE(workspace_bytes >= nce_workspace_bytes(B), "bsa_info_nce_fwd: workspace too small");
+    return nce_fwd(B, d, tau, z, loss, workspace, (cudaStream_t)stream);
+}
+
+int bsa_info_nce_bwd(int B, int d, float tau, const float* z, const float* d_loss, float scale, float* dz, const void* workspace,
+                     size_t workspace_bytes, void* stream) {
+    BSA_REQUIRE(z && d_loss && dz && workspace, "bsa_info_nce_bwd: null argument");
+    BSA_REQUIRE(workspace_bytes >= nce_workspace_bytes(B), "bsa_info_nce_bwd: workspace too small");
+    return nce_bwd(B, d, tau, z, d_loss, scale, dz, workspace, (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------------------------------ utilities
 int bsa_gather_last(const float* src, float* dst, int B, int L, int d, void* stream) {
     BSA_REQUIRE(src && dst, "bsa_gather_last: null argument");

@@ -94,6 +94,10 @@ int bce_pair_fwd(int B, int d, long long N, const float* s, const float* E, cons
 int bce_pair_bwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
                  const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st);
 int scatter_rows(const long long* idx, long long M, long long dst_rows, const float* src, int d, float* dst, cudaStream_t st);
+// in-batch InfoNCE of DuoRec (model/duorec.py:47-75, sim = 'dot'): bce.cu
+size_t nce_workspace_bytes(int B);
+int nce_fwd(int B, int d, float tau, const float* z, float* loss, void* ws, cudaStream_t st);
+int nce_bwd(int B, int d, float tau, const float* z, const float* d_loss, float scale, float* dz, const void* ws, cudaStream_t st);
 int gather_rows(const long long* idx, long long M, long long src_rows, const float* src, int d, float* dst, cudaStream_t st);
 
 }  // namespace bsa

@@ -510,3 +510,83 @@ class FusedPairLoss(torch.autograd.Function):
         encoder_backward(hyper, params, state, d_out, grads)
         ctx.state = ctx.ws = None
         return (None,) * 7 + tuple(grads[n] if t.requires_grad else None for n, t in zip(names, tensors))
+
+
+def info_nce_forward(z: torch.Tensor, tau: float):
+    """z [2B, d] (two views stacked) -> (loss 0-dim, workspace): DuoRec's in-batch InfoNCE (duorec.py:47-75, sim='dot')."""
+    lib = _cabi.load()
+    n2, d = z.shape
+    B = n2 // 2
+    with torch.cuda.device(z.device):
+        wsb = lib.bsa_info_nce_workspace_bytes(B)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=z.device)
+        loss = torch.empty((), dtype=torch.float32, device=z.device)
+        check(lib.bsa_info_nce_fwd(B, d, float(tau), _ptr(z), _ptr(loss), _ptr(ws), wsb, _stream()), "bsa_info_nce_fwd")
+    return loss, ws
+
+
+def info_nce_backward(z: torch.Tensor, tau: float, d_loss: torch.Tensor, scale: float, ws: torch.Tensor) -> torch.Tensor:
+    lib = _cabi.load()
+    n2, d = z.shape
+    with torch.cuda.device(z.device):
+        dz = torch.empty_like(z)
+        d_loss = d_loss.to(dtype=torch.float32).contiguous()
+        check(lib.bsa_info_nce_bwd(n2 // 2, d, float(tau), _ptr(z), _ptr(d_loss), float(scale), _ptr(dz), _ptr(ws), ws.numel(),
+                                   _stream()), "bsa_info_nce_bwd")
+    return dz
+
+
+class FusedDuoLoss(torch.autograd.Function):
+    """DuoRec's calculate_loss (duorec.py:91-139, ssl = 'us_x' or CE only) as one autograd node: the sequence, a second
+    dropout view of it and the same-target sequence each go through the encoder (last position only); full-catalog CE on
+    the first (the fused CE kernels), in-batch InfoNCE between the other two (bsa_info_nce_*), weight lmd_sem."""
+
+    @staticmethod
+    def forward(ctx, hyper: Hyper, names: Sequence[str], ids, answers, sem_ids, training: bool, seeds, ce_impl: int,
+                tau: float, lmd_sem: float, *tensors):
+        params = dict(zip(names, tensors))
+        E = params["item_embeddings.weight"]
+        xs, st0 = encoder_forward(hyper, params, ids, training, seeds[0], keep_for_backward=True, last_only=True)
+        s = xs[-1]
+        loss, lse, ce_ws = ce_forward(s, E, answers, ce_impl)
+        states = [st0]
+        ctx.z = None
+        if sem_ids is not None:
+            xa, st1 = encoder_forward(hyper, params, ids, training, seeds[1], keep_for_backward=True, last_only=True)
+            xm, st2 = encoder_forward(hyper, params, sem_ids, training, seeds[2], keep_for_backward=True, last_only=True)
+            z = torch.cat([xa[-1], xm[-1]], dim=0).contiguous()
+            nce, nce_ws = info_nce_forward(z, tau)
+            loss = loss + lmd_sem * nce
+            states += [st1, st2]
+            ctx.z, ctx.nce_ws = z, nce_ws
+        ctx.hyper, ctx.names, ctx.states, ctx.ce_impl, ctx.tau, ctx.lmd_sem = hyper, names, states, ce_impl, tau, lmd_sem
+        ctx.answers, ctx.s, ctx.lse, ctx.ce_ws = answers, s, lse, ce_ws
+        ctx.save_for_backward(*tensors)
+        return loss
+
+    @staticmethod
+    def backward(ctx, d_loss):
+        tensors = ctx.saved_tensors
+        names, hyper = ctx.names, ctx.hyper
+        params = dict(zip(names, tensors))
+        E = params["item_embeddings.weight"]
+        grads, flat = alloc_grads(params)
+        gE = grads["item_embeddings.weight"]
+        ds = ce_backward(ctx.s, E, ctx.answers, ctx.lse, d_loss, gE, ctx.ce_impl, ctx.ce_ws)
+        outs = [ds]
+        if ctx.z is not None:
+            dz = info_nce_backward(ctx.z, ctx.tau, d_loss, ctx.lmd_sem, ctx.nce_ws)
+            B = dz.shape[0] // 2
+            outs += [dz[:B].contiguous(), dz[B:].contiguous()]
+        total = None
+        for state, d_out in zip(ctx.states, outs):
+            g_k, flat_k = alloc_grads(params, with_big=False)
+            g_k["item_embeddings.weight"] = gE                   # the gather part accumulates on top of the dense CE part
+            if state.L < params["position_embeddings.weight"].shape[0]:
+                g_k["position_embeddings.weight"].zero_()
+            d_in = d_out if state.last_row else scatter_last(d_out, state.L)
+            encoder_backward(hyper, params, state, d_in, g_k)
+            total = flat_k if total is None else total.add_(flat_k)
+        flat.copy_(total)
+        ctx.states = None
+        return (None,) * 10 + tuple(grads[n] if t.requires_grad else None for n, t in zip(names, tensors))

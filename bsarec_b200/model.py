@@ -311,3 +311,38 @@ class SASRecModel(BSARecModel):
         named = self._kernel_named(detach=False)
         return Fn.FusedPairLoss.apply(self._hyper(), [n for n, _ in named], input_ids, answers, neg_answers, self.training,
                                       self._next_seed(), *[t for _, t in named])
+
+
+class DuoRecModel(SASRecModel):
+    """Sibling model on the same kernels: ``DuoRecModel`` of ``src/model/duorec.py:16-139``.
+
+    SASRec's encoder (the reference's ``TransformerEncoder``, same ``state_dict`` keys), full-catalog cross-entropy at the
+    last position through the fused CE kernels (``duorec.py:95-98``) and, for ``ssl = 'us_x'`` (the reference's default,
+    ``utils.py:109``), the in-batch InfoNCE between a second dropout view of the sequence and the same-target sequence
+    (``duorec.py:124-137``, ``sim = 'dot'``) through ``bsa_info_nce_fwd/bwd``, weight ``lmd_sem``.  The other ``ssl``
+    modes of the reference stack a ``[B, d]`` and a ``[B, L, d]`` tensor (``duorec.py:54-55`` after ``:93``) and cannot run
+    there either; any value outside {'us', 'un', 'su', 'us_x'} trains on the cross-entropy alone, as in the reference."""
+
+    def __init__(self, args):
+        # the reference builds both embedding tables twice (SequentialRecModel.__init__, then duorec.py:20-21): the seeded
+        # RNG stream is consumed accordingly before init_weights overwrites everything
+        nn.Embedding(args.item_size, args.hidden_size, padding_idx=0)
+        nn.Embedding(args.max_seq_length, args.hidden_size)
+        super().__init__(args)
+        self.tau, self.ssl, self.sim = float(args.tau), str(args.ssl), str(args.sim)
+        self.lmd_sem, self.lmd = float(args.lmd_sem), float(args.lmd)
+        if self.ssl in ("us", "un", "su"):
+            raise ValueError(f"ssl={self.ssl!r}: this mode of the reference concatenates [B,d] with [B,L,d] "
+                             "(duorec.py:54-55) and cannot run there; use 'us_x' or a CE-only setting")
+        if self.ssl == "us_x" and self.sim != "dot":
+            raise ValueError("bsarec_b200.DuoRecModel implements sim='dot' (the reference's default) only")
+
+    def calculate_loss(self, input_ids, answers, neg_answers, same_target, user_ids):
+        if self._exchange is not None:
+            raise RuntimeError("bsarec_b200.DuoRecModel: use parallel.allreduce_gradients after backward for data parallel")
+        named = self._kernel_named(detach=False)
+        base = self._next_seed()
+        seeds = (base, base + 1, base + 2) if self._fixed_seed is not None else (base, self._next_seed(), self._next_seed())
+        sem = same_target if self.ssl == "us_x" else None
+        return Fn.FusedDuoLoss.apply(self._hyper(), [n for n, _ in named], input_ids, answers, sem, self.training, seeds,
+                                     self.ce_impl, self.tau, self.lmd_sem, *[t for _, t in named])

@@ -305,6 +305,15 @@ int bsa_bce_pair_bwd(int B, int d, int64_t item_size, const float* seq_out, cons
                      const int64_t* neg_ids, const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace,
                      size_t workspace_bytes, void* stream);
 
+/* In-batch InfoNCE of the sibling DuoRec (model/duorec.py:47-75, sim = 'dot'; its cross-entropy term is bsa_ce_fwd/bwd):
+ * z [2B, d] = the two views' last-position vectors stacked; row r's positive is row (r + B) mod 2B, its negatives every
+ * other row but itself; loss = mean_r( -sim[r, pair] + logsumexp_{c != r} sim[r, c] ), sim = z z^T / tau.
+ * fwd keeps the row log-sum-exps in `workspace`; bwd writes dz [2B, d] = scale * d_loss * d loss / d z. */
+size_t bsa_info_nce_workspace_bytes(int B);
+int bsa_info_nce_fwd(int B, int d, float tau, const float* z, float* loss, void* workspace, size_t workspace_bytes, void* stream);
+int bsa_info_nce_bwd(int B, int d, float tau, const float* z, const float* d_loss, float scale, float* dz, const void* workspace,
+                     size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Small utilities shared by the host wrappers
  * ---------------------------------------------------------------------------------------------- */

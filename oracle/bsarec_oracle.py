@@ -23,6 +23,7 @@ __all__ = [
     "feed_forward", "encode", "calculate_loss", "loss_and_grads", "predict_full",
     "full_sort_topk", "masked_scores", "recall_at_k", "ndcg_k", "full_sort_metrics",
     "adam_train_step", "eval_step", "param_names", "encode_sasrec", "sasrec_loss", "sasrec_loss_and_grads",
+    "info_nce", "duorec_loss", "duorec_loss_and_grads",
 ]
 
 
@@ -295,6 +296,44 @@ def sasrec_loss(P, ids, pos, neg, cfg: OracleConfig, train=True, plan=None):
 def sasrec_loss_and_grads(P, ids, pos, neg, cfg: OracleConfig, train=True, plan=None):
     Q = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
     loss = sasrec_loss(Q, ids, pos, neg, cfg, train, plan)
+    loss.backward()
+    return loss.detach(), {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in Q.items()}
+
+
+def info_nce(z_i: torch.Tensor, z_j: torch.Tensor, tau: float) -> torch.Tensor:
+    """``DuoRecModel.info_nce`` + ``aug_nce_fct`` (``duorec.py:47-75``, sim='dot') on last-position vectors [B,d]: the
+    positive of row r is its pair in the other view, the negatives every other row of the 2B but itself."""
+    B = z_i.shape[0]
+    n2 = 2 * B
+    z = torch.cat((z_i, z_j), dim=0)
+    sim = torch.mm(z, z.T) / tau
+    pos = torch.cat((torch.diag(sim, B), torch.diag(sim, -B)), dim=0).reshape(n2, 1)
+    mask = torch.ones((n2, n2), dtype=torch.bool)
+    mask.fill_diagonal_(False)
+    for i in range(B):
+        mask[i, B + i] = False
+        mask[B + i, i] = False
+    neg = sim[mask].reshape(n2, -1)
+    logits = torch.cat((pos, neg), dim=1)
+    return F.cross_entropy(logits, torch.zeros(n2, dtype=torch.long))
+
+
+def duorec_loss(P, ids, answers, sem_ids, cfg: OracleConfig, tau: float, lmd_sem: float, train=True, plans=(None, None, None)):
+    """``DuoRecModel.calculate_loss`` (``duorec.py:91-139``) for ssl='us_x' (``sem_ids`` given) or the CE-only setting
+    (``sem_ids`` None): CE of the sequence's last position over the catalog + lmd_sem * InfoNCE(second dropout view of the
+    sequence, the same-target sequence).  ``plans``: one DropoutPlan per encoder pass."""
+    s = encode_sasrec(P, ids, cfg, train, plans[0])[-1][:, -1, :]
+    loss = F.cross_entropy(torch.matmul(s, P["item_embeddings.weight"].transpose(0, 1)), answers)
+    if sem_ids is not None:
+        aug = encode_sasrec(P, ids, cfg, train, plans[1])[-1][:, -1, :]
+        sem = encode_sasrec(P, sem_ids, cfg, train, plans[2])[-1][:, -1, :]
+        loss = loss + lmd_sem * info_nce(aug, sem, tau)
+    return loss
+
+
+def duorec_loss_and_grads(P, ids, answers, sem_ids, cfg, tau, lmd_sem, train=True, plans=(None, None, None)):
+    Q = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
+    loss = duorec_loss(Q, ids, answers, sem_ids, cfg, tau, lmd_sem, train, plans)
     loss.backward()
     return loss.detach(), {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in Q.items()}
 

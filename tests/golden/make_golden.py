@@ -150,6 +150,33 @@ def sasrec_case(name, seed, B, **cfgkw):
     print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
 
 
+def duorec_case(name, seed, B, **cfgkw):
+    """Sibling model: the reference's DuoRecModel with its default ssl='us_x' (CE + lmd_sem * InfoNCE between a second
+    view of the sequence and the same-target sequence), dropout 0 so the run is deterministic: loss and all gradients."""
+    torch.manual_seed(seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    args = make_args(tau=1.0, lmd=0.1, lmd_sem=0.1, ssl="us_x", sim="dot", batch_size=B, **cfgkw)
+    model = MODEL_DICT["duorec"](args=args)
+    perturb(model, g)
+    ids, answers = synth_ids(g, B, args.max_seq_length, args.item_size)
+    sem, _ = synth_ids(g, B, args.max_seq_length, args.item_size, all_pad_rows=(), short_rows=(4,))
+    model.train()
+    loss = model.calculate_loss(ids, answers, None, sem, None)
+    model.zero_grad()
+    loss.backward()
+    out = {
+        "cfg_keys": np.array(sorted(cfgkw.keys())),
+        "cfg_vals": np.array([float(cfgkw[k]) for k in sorted(cfgkw.keys())]),
+        "ids": ids.numpy(), "answers": answers.numpy(), "sem": sem.numpy(), "loss": loss.detach().numpy(),
+        "tau": np.array(1.0), "lmd_sem": np.array(0.1),
+    }
+    for n, p in model.named_parameters():
+        out["param." + n] = p.detach().numpy()
+        out["grad." + n] = (p.grad if p.grad is not None else torch.zeros_like(p)).numpy()
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
+
+
 def known_answer_case(data_name, split, out_name, store_params=True, **cfgkw):
     """Known-answer: a shipped checkpoint on a real split through the reference's own Trainer.iteration.
     Beauty/test -> src/output/BSARec_Beauty_best.log:258; LastFM/test -> BSARec_LastFM_best.log:237; the valid split
@@ -242,6 +269,10 @@ def dataset_case():
 
 
 if __name__ == "__main__":
+    if "--duorec" in sys.argv:
+        duorec_case("duorec_small", 19, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
+                    num_hidden_layers=2)
+        sys.exit(0)
     if "--sasrec" in sys.argv:
         sasrec_case("sasrec_small", 17, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
                     num_hidden_layers=2)
@@ -266,5 +297,7 @@ if __name__ == "__main__":
     known_answer_case("LastFM", "valid", "lastfm_valid", store_params=False, num_attention_heads=1, c=3, alpha=0.9)
     known_answer_case("Beauty", "valid", "beauty_valid", store_params=False, num_attention_heads=1, c=5, alpha=0.7)
     sasrec_case("sasrec_small", 17, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
+                num_hidden_layers=2)
+    duorec_case("duorec_small", 19, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
                 num_hidden_layers=2)
     dataset_case()

@@ -405,3 +405,51 @@ def test_sasrec_sibling_vs_reference_golden(last_row, cuda_device):
         assert sorted(model.state_dict().keys()) == sorted(P.keys())
     finally:
         Fn.LAST_ROW_PATH = old
+
+
+def _duo_args(cfgkw, ph=0.0, pa=0.0, ssl="us_x"):
+    a = make_args(cfgkw, ph, pa)
+    a.tau, a.lmd, a.lmd_sem, a.ssl, a.sim = 1.0, 0.1, 0.1, ssl, "dot"
+    return a
+
+
+def test_duorec_sibling_vs_reference_golden(cuda_device):
+    """DuoRecModel (ssl='us_x') on the same kernels — SASRec-style encoder, fused full-catalog CE,
+    in-batch InfoNCE by bsa_info_nce_fwd/bwd — against the reference class's loss and gradients; train-mode dropout (three
+    encoder passes with three mask streams) against the oracle; the CE-only setting equals the CE term alone."""
+    from bsarec_b200 import DuoRecModel
+    cfgkw, data = load_golden("duorec_small")
+    P = golden_params(data)
+    ids, ans, sem = (torch.from_numpy(data[k]).to(cuda_device) for k in ("ids", "answers", "sem"))
+    model = DuoRecModel(_duo_args(cfgkw))
+    model.load_state_dict({k: v.clone() for k, v in P.items()})
+    model = model.to(cuda_device).train()
+    loss = model.calculate_loss(ids, ans, None, sem, None)
+    loss.backward()
+    assert abs(loss.item() - float(data["loss"])) < TOL * abs(float(data["loss"]))
+    cfg = oracle_cfg(cfgkw)
+    _, g64 = oracle.duorec_loss_and_grads({k: v.double() for k, v in P.items()}, ids.cpu(), ans.cpu(), sem.cpu(), cfg, 1.0, 0.1)
+    check_grads(grads_of(model), g64, golden_grads(data))
+    # dropout: passes use seeds s, s + 1, s + 2
+    cfg_d = oracle_cfg(cfgkw, 0.3, 0.4)
+    m2 = DuoRecModel(_duo_args(cfgkw, 0.3, 0.4))
+    m2.load_state_dict({k: v.clone() for k, v in P.items()})
+    m2 = m2.to(cuda_device).train()
+    m2.set_dropout_seed(41)
+    l2 = m2.calculate_loss(ids, ans, None, sem, None)
+    l2.backward()
+    plans = tuple(oracle.DropoutPlan(41 + k) for k in range(3))
+    l64, g64 = oracle.duorec_loss_and_grads({k: v.double() for k, v in P.items()}, ids.cpu(), ans.cpu(), sem.cpu(), cfg_d, 1.0, 0.1,
+                                            plans=plans)
+    _, g32 = oracle.duorec_loss_and_grads(P, ids.cpu(), ans.cpu(), sem.cpu(), cfg_d, 1.0, 0.1, plans=plans)
+    assert abs(l2.item() - float(l64)) < TOL * abs(float(l64))
+    check_grads(grads_of(m2), g64, g32)
+    # CE-only setting
+    m3 = DuoRecModel(_duo_args(cfgkw, ssl="none"))
+    m3.load_state_dict({k: v.clone() for k, v in P.items()})
+    m3 = m3.to(cuda_device).train()
+    l3 = m3.calculate_loss(ids, ans, None, sem, None)
+    l_ce = oracle.duorec_loss({k: v.double() for k, v in P.items()}, ids.cpu(), ans.cpu(), None, cfg, 1.0, 0.1)
+    assert abs(l3.item() - float(l_ce)) < TOL * abs(float(l_ce))
+    with pytest.raises(ValueError):
+        DuoRecModel(_duo_args(cfgkw, ssl="us"))

@@ -294,3 +294,49 @@ def test_sasrec_container_matches_live_reference_class():
         sys.path.remove("/root/reference/src")
         for m in [k for k in sys.modules if k == "model" or k.startswith("model.")]:
             sys.modules.pop(m, None)
+
+
+def test_duorec_oracle_vs_reference_golden():
+    """Sibling model: the oracle's DuoRec restatement (CE + lmd_sem * InfoNCE, ssl='us_x') against the reference's
+    DuoRecModel — loss and all gradients."""
+    cfgkw, data = load_golden("duorec_small")
+    cfg = OracleConfig(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, **cfgkw)
+    P = golden_params(data)
+    ids, ans, sem = (torch.from_numpy(data[k]) for k in ("ids", "answers", "sem"))
+    loss, grads = oracle.duorec_loss_and_grads(P, ids, ans, sem, cfg, float(data["tau"]), float(data["lmd_sem"]))
+    assert abs(float(loss) - float(data["loss"])) < 1e-6 * abs(float(data["loss"]))
+    ref = golden_grads(data)
+    for k, g in grads.items():
+        if k.endswith("key.bias"):
+            assert g.abs().max() < 1e-6
+            continue
+        assert rel_err(g, ref[k]) < 1e-4, k
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/model"), reason="live reference only in the build container")
+def test_duorec_container_matches_live_reference_class():
+    """Same state_dict keys and bit-identical seeded init as the reference's DuoRecModel (which builds its embedding
+    tables twice before init_weights: the RNG stream must be consumed the same way)."""
+    sys.path.insert(0, "/root/reference/src")
+    try:
+        from model import MODEL_DICT as REF
+        from helpers import make_args
+        import bsarec_b200
+        cfgkw = dict(item_size=123, hidden_size=32, max_seq_length=20, num_attention_heads=2, num_hidden_layers=2)
+        extra = dict(tau=1.0, lmd=0.1, lmd_sem=0.1, ssl="us_x", sim="dot")
+        a1, a2 = make_args(cfgkw, 0.5, 0.5), make_args(cfgkw, 0.5, 0.5)
+        for a in (a1, a2):
+            for k, v in extra.items():
+                setattr(a, k, v)
+        torch.manual_seed(5)
+        ref = REF["duorec"](args=a1)
+        torch.manual_seed(5)
+        ours = bsarec_b200.MODEL_DICT["duorec"](a2)
+        a, b = ref.state_dict(), ours.state_dict()
+        assert list(a.keys()) == list(b.keys())
+        for k in a:
+            assert torch.equal(a[k], b[k]), k
+    finally:
+        sys.path.remove("/root/reference/src")
+        for m in [k for k in sys.modules if k == "model" or k.startswith("model.")]:
+            sys.modules.pop(m, None)

@@ -2,12 +2,12 @@
 
 ``MODEL_DICT["bsarec"]`` mirrors ``src/model/__init__.py:10-11`` of the reference.
 """
-from .model import BSARecModel, SASRecModel, DuoRecModel
+from .model import BSARecModel, SASRecModel, DuoRecModel, FMLPRecModel
 from .trainer import Trainer
 from .optim import FusedAdam
 from .data import SequenceStore, DeviceBatchLoader, HitRankAccumulator
 
-MODEL_DICT = {"bsarec": BSARecModel, "sasrec": SASRecModel, "duorec": DuoRecModel}
+MODEL_DICT = {"bsarec": BSARecModel, "sasrec": SASRecModel, "duorec": DuoRecModel, "fmlprec": FMLPRecModel}
 
-__all__ = ["BSARecModel", "SASRecModel", "DuoRecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
+__all__ = ["BSARecModel", "SASRecModel", "DuoRecModel", "FMLPRecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
            "HitRankAccumulator"]

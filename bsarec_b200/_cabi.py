@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbsarec_sm100a.so")
 
-ABI_VERSION = 2          # == BSA_ABI_VERSION of include/bsarec_b200.h (checked at load)
+ABI_VERSION = 3          # == BSA_ABI_VERSION of include/bsarec_b200.h (checked at load)
 
 c_f32p = C.c_void_p
 c_i64p = C.c_void_p
@@ -23,7 +23,7 @@ class EmbedDesc(C.Structure):
 class BlockDesc(C.Structure):
     _fields_ = [("B", C.c_int), ("L", C.c_int), ("d", C.c_int), ("H", C.c_int), ("kept_bins", C.c_int),
                 ("alpha", C.c_float), ("p_hidden", C.c_float), ("p_attn", C.c_float), ("training", C.c_int),
-                ("seed", C.c_uint64), ("layer", C.c_int), ("inference", C.c_int)]
+                ("seed", C.c_uint64), ("layer", C.c_int), ("inference", C.c_int), ("kind", C.c_int)]
 
 
 BLOCK_FIELDS = ["sqrt_beta", "f_ln_w", "f_ln_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo",
@@ -112,12 +112,16 @@ SIGNATURES = {
     "bsa_scatter_last": (_I, [_VP, _VP, _I, _I, _I, _VP]),
     "bsa_gather_rows": (_I, [_VP, _I64, _I64, _VP, _I, _VP, _VP]),
     "bsa_scatter_rows": (_I, [_VP, _I64, _I64, _VP, _I, _VP, _VP]),
+    "bsa_fmlp_supported": (_I, [_I, _I]),
+    "bsa_fmlp_tables": (_I, [_VP, _VP, _I, _VP]),
+    "bsa_fmlp_kernel_fwd": (_I, [_VP, _VP, _VP, _VP, _I, _I, _VP]),
+    "bsa_fmlp_kernel_bwd": (_I, [_VP, _VP, _VP, _VP, _I, _I, _VP]),
     "bsa_info_nce_workspace_bytes": (_SZ, [_I]),
     "bsa_info_nce_fwd": (_I, [_I, _I, C.c_float, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_info_nce_bwd": (_I, [_I, _I, C.c_float, _VP, _VP, C.c_float, _VP, _VP, _SZ, _VP]),
     "bsa_bce_pair_workspace_bytes": (_SZ, [_I, _I]),
-    "bsa_bce_pair_fwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
-    "bsa_bce_pair_bwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "bsa_bce_pair_fwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _I, _VP]),
+    "bsa_bce_pair_bwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _I, _VP]),
 }
 
 _lib = None

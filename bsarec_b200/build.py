@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libbsarec_sm100a.so")
-SOURCES = ["capi.cu", "gemm_simt.cu", "rowwise.cu", "block.cu", "ce.cu", "topk.cu", "umma_engine.cu", "tmap.cu", "attn.cu", "attn_umma.cu", "attn_kv_umma.cu", "adam.cu", "lastrow.cu", "dataprep.cu", "rowwise_vec.cu", "bce.cu"]
+SOURCES = ["capi.cu", "gemm_simt.cu", "rowwise.cu", "block.cu", "ce.cu", "topk.cu", "umma_engine.cu", "tmap.cu", "attn.cu", "attn_umma.cu", "attn_kv_umma.cu", "adam.cu", "lastrow.cu", "dataprep.cu", "rowwise_vec.cu", "bce.cu", "fmlp.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-I", INCLUDE,

@@ -23,7 +23,7 @@ __device__ __forceinline__ float sigmoid_f(float x) { return x >= 0.f ? 1.f / (1
 __global__ void __launch_bounds__(1024) bce_pair_fwd_kernel(const float* __restrict__ s, const float* __restrict__ E,
                                                              const long long* __restrict__ pos, const long long* __restrict__ neg,
                                                              int B, int d, long long N, float* __restrict__ logits,
-                                                             float* __restrict__ loss, int* __restrict__ n_valid) {
+                                                             float* __restrict__ loss, int* __restrict__ n_valid, int variant) {
     __shared__ float sh_p[32], sh_n[32];
     __shared__ int sh_c[32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -44,7 +44,9 @@ __global__ void __launch_bounds__(1024) bce_pair_fwd_kernel(const float* __restr
         }
         xp = warp_sum_f(xp); xn = warp_sum_f(xn);
         if (lane == 0) { logits[2 * b] = xp; logits[2 * b + 1] = xn; }
-        if (pos[b] != 0) { lp += softplus_f(-xp); ln += softplus_f(xn); ++cnt; }     // sasrec.py:58: indices = pos_ids != 0
+        if (variant == 1) {          // fmlprec.py:55-58: -log(sigmoid(xp) + 1e-24) - log(1 - sigmoid(xn) + 1e-24), mean over ALL users
+            lp += -logf(sigmoid_f(xp) + 1e-24f); ln += -logf(1.0f - sigmoid_f(xn) + 1e-24f); ++cnt;
+        } else if (pos[b] != 0) { lp += softplus_f(-xp); ln += softplus_f(xn); ++cnt; }     // sasrec.py:58: indices = pos_ids != 0
     }
     if (lane == 0) { sh_p[warp] = lp; sh_n[warp] = ln; sh_c[warp] = cnt; }
     __syncthreads();
@@ -63,12 +65,21 @@ __global__ void __launch_bounds__(256) bce_pair_bwd_kernel(const float* __restri
                                                             const long long* __restrict__ pos, const long long* __restrict__ neg,
                                                             const float* __restrict__ logits, const int* __restrict__ n_valid,
                                                             const float* __restrict__ d_loss, int B, int d, long long N,
-                                                            float* __restrict__ ds, float* __restrict__ rows, long long* __restrict__ ids2) {
+                                                            float* __restrict__ ds, float* __restrict__ rows, long long* __restrict__ ids2,
+                                                            int variant) {
     const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (b >= B) return;
-    const bool ok = pos[b] != 0 && *n_valid > 0;
+    const bool ok = (variant == 1 || pos[b] != 0) && *n_valid > 0;
     const float g = ok ? __ldg(d_loss) / (float)(*n_valid) : 0.f;
-    const float gp = (sigmoid_f(logits[2 * b]) - 1.f) * g, gn = sigmoid_f(logits[2 * b + 1]) * g;
+    float gp, gn;
+    if (variant == 1) {              // d/dx of -log(sigmoid(x) + eps) and of -log(1 - sigmoid(x) + eps)
+        const float sp = sigmoid_f(logits[2 * b]), sn = sigmoid_f(logits[2 * b + 1]);
+        gp = -sp * (1.0f - sp) / (sp + 1e-24f) * g;
+        gn = sn * (1.0f - sn) / (1.0f - sn + 1e-24f) * g;
+    } else {
+        gp = (sigmoid_f(logits[2 * b]) - 1.f) * g;
+        gn = sigmoid_f(logits[2 * b + 1]) * g;
+    }
     long long ip = pos[b], in = neg[b];
     if (ip < 0 || ip >= N) ip = 0;
     if (in < 0 || in >= N) in = 0;
@@ -215,24 +226,24 @@ size_t bce_pair_workspace_bytes(int B, int d) {
 }
 
 int bce_pair_fwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
-                 float* loss, void* ws, cudaStream_t st) {
+                 float* loss, void* ws, int variant, cudaStream_t st) {
     BSA_REQUIRE(d % 4 == 0, "bce_pair: hidden size must be a multiple of 4");
     float* logits = (float*)ws;
     int* n_valid = (int*)((char*)ws + al((size_t)2 * B * 4));
-    bce_pair_fwd_kernel<<<1, 1024, 0, st>>>(s, E, pos, neg, B, d, N, logits, loss, n_valid);
+    bce_pair_fwd_kernel<<<1, 1024, 0, st>>>(s, E, pos, neg, B, d, N, logits, loss, n_valid, variant);
     BSA_LAUNCH_CHECK();
     return 0;
 }
 
 int bce_pair_bwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
-                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st) {
+                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, int variant, cudaStream_t st) {
     BSA_REQUIRE(ws_bytes >= bce_pair_workspace_bytes(B, d), "bce_pair_bwd: workspace too small");
     char* p = (char*)ws;
     float* logits = (float*)p; p += al((size_t)2 * B * 4);
     int* n_valid = (int*)p; p += al(16);
     float* rows = (float*)p; p += al((size_t)2 * B * d * 4);
     long long* ids2 = (long long*)p; p += al((size_t)2 * B * 8);
-    bce_pair_bwd_kernel<<<cdiv(B, 8), 256, 0, st>>>(s, E, pos, neg, logits, n_valid, d_loss, B, d, N, ds, rows, ids2);
+    bce_pair_bwd_kernel<<<cdiv(B, 8), 256, 0, st>>>(s, E, pos, neg, logits, n_valid, d_loss, B, d, N, ds, rows, ids2, variant);
     BSA_LAUNCH_CHECK();
     int rc = scatter_plan(ids2, 2ll * B, N, p, scatter_plan_bytes(2ll * B), st);
     if (rc) return rc;

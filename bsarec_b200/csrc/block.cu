@@ -229,10 +229,17 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     // inference (bsa_block_desc::inference): the LayerNorm inputs / statistics and the GELU pre-activation are not written
     const bool inf = c.inference != 0;
     lin.inference = inf && lin.umma;
+    Act ax, actx, ay, ah;
+    if (c.kind == 1) {
+        // FMLPRecBlock (fmlprec.py:84-118): y = LN(drop(circular_conv(x, K)) + x) — K [L,d] arrives as `sqrt_beta` — then the
+        // same feed-forward; no attention
+        if ((rc = circ_apply(x, w.sqrt_beta, false, nullptr, tmp, B, L, d, false, st))) return rc;
+        if ((rc = residual_ln_fwd(tmp, x, w.f_ln_w, w.f_ln_b, s.y, inf ? nullptr : s.z_f, inf ? nullptr : s.mean_f,
+                                  inf ? nullptr : s.rstd_f, nullptr, 0.f, 0.f, M, d, dr_f, st))) return rc;
+    } else {
     if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, inf ? nullptr : s.z_f, inf ? nullptr : s.mean_f,
                             inf ? nullptr : s.rstd_f, B, L, d, r, dr_f, st))) return rc;
     // attention branch
-    Act ax, actx, ay, ah;
     if ((rc = split_act(lin, x, s.x_hi, s.x_lo, M * d, ax, st))) return rc;        // one split feeds q, k, v (and dW in backward)
     if ((rc = linear_fwd(lin, ax, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     if ((rc = linear_fwd(lin, ax, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
@@ -264,6 +271,7 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
     if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, inf ? nullptr : s.z_a, inf ? nullptr : s.mean_a, inf ? nullptr : s.rstd_a,
                               dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
+    }   // kind == 0
     // feed-forward
     if ((rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
     // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
@@ -347,6 +355,16 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     }
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
+    if (c.kind == 1) {
+        // FMLPRecBlock: y = LN(drop(conv(x, K)) + x).  dx = d(LN input) + conv^T(K, d conv); dK = sum_b corr(d conv_b, x_b)
+        if ((rc = ln_bwd(dyb, 1.0f, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, dr_f.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_f, st))) return rc;
+        if ((rc = reduce_partials(pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = reduce_partials(pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
+        const float* gconv = dr_f.thr ? dd : dzf;
+        if ((rc = circ_apply(gconv, x, true, nullptr, dq, B, L, d, true, st))) return rc;              // per-sequence partials of dK
+        if ((rc = reduce_partials(dq, B, L * d, g.sqrt_beta, nullptr, 1.f, 0, st))) return rc;
+        return circ_apply(gconv, w.sqrt_beta, false, dzf, dx, B, L, d, true, st);
+    }
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
     const bool fuse_a = lin.umma && ln_bwd_split_ok(d, dyb, s.z_a, w.a_ln_w, dx, nullptr, g_hi, g_lo);
     if (fuse_a) {
@@ -497,7 +515,7 @@ Lin make_last_lin(Bump& b, long long B, long long d) {
 }  // namespace
 
 bool block_last_supported(const bsa_block_desc& c) {
-    return c.H > 0 && c.d % c.H == 0 && c.d % 4 == 0 && lastrow_supported(c.L, c.d, c.H);
+    return c.kind == 0 && c.H > 0 && c.d % c.H == 0 && c.d % 4 == 0 && lastrow_supported(c.L, c.d, c.H);
 }
 
 int block_last_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,

@@ -359,20 +359,34 @@ int bsa_gemm(int impl, int M, int N, int K, const float* A, int64_t lda, int a_m
 size_t bsa_bce_pair_workspace_bytes(int B, int d) { return al(bce_pair_workspace_bytes(B, d)); }
 
 int bsa_bce_pair_fwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
-                     const int64_t* neg_ids, float* loss, void* workspace, size_t workspace_bytes, void* stream) {
+                     const int64_t* neg_ids, float* loss, void* workspace, size_t workspace_bytes, int variant, void* stream) {
     BSA_REQUIRE(seq_out && item_emb && pos_ids && neg_ids && loss && workspace, "bsa_bce_pair_fwd: null argument");
     BSA_REQUIRE(B >= 1 && workspace_bytes >= bce_pair_workspace_bytes(B, d), "bsa_bce_pair_fwd: workspace too small");
     return bce_pair_fwd(B, d, item_size, seq_out, item_emb, (const long long*)pos_ids, (const long long*)neg_ids, loss, workspace,
-                        (cudaStream_t)stream);
+                        variant, (cudaStream_t)stream);
 }
 
 int bsa_bce_pair_bwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
                      const int64_t* neg_ids, const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace,
-                     size_t workspace_bytes, void* stream) {
+                     size_t workspace_bytes, int variant, void* stream) {
     BSA_REQUIRE(seq_out && item_emb && pos_ids && neg_ids && d_loss && d_seq_out && d_item_emb && workspace,
                 "bsa_bce_pair_bwd: null argument");
     return bce_pair_bwd(B, d, item_size, seq_out, item_emb, (const long long*)pos_ids, (const long long*)neg_ids, d_loss,
-                        d_seq_out, d_item_emb, workspace, workspace_bytes, (cudaStream_t)stream);
+                        d_seq_out, d_item_emb, workspace, workspace_bytes, variant, (cudaStream_t)stream);
+}
+
+int bsa_fmlp_supported(int L, int d) { return fmlp_supported(L, d) ? 1 : 0; }
+int bsa_fmlp_tables(float* Tc, float* Ts, int L, void* stream) {
+    BSA_REQUIRE(Tc && Ts && L >= 1, "bsa_fmlp_tables: bad argument");
+    return fmlp_trig(Tc, Ts, L, (cudaStream_t)stream);
+}
+int bsa_fmlp_kernel_fwd(const float* W, const float* Tc, const float* Ts, float* K, int L, int d, void* stream) {
+    BSA_REQUIRE(W && Tc && Ts && K, "bsa_fmlp_kernel_fwd: null argument");
+    return fmlp_kernel_fwd(W, Tc, Ts, K, L, d, (cudaStream_t)stream);
+}
+int bsa_fmlp_kernel_bwd(const float* dK, const float* Tc, const float* Ts, float* dW, int L, int d, void* stream) {
+    BSA_REQUIRE(dK && Tc && Ts && dW, "bsa_fmlp_kernel_bwd: null argument");
+    return fmlp_kernel_bwd(dK, Tc, Ts, dW, L, d, (cudaStream_t)stream);
 }
 
 size_t bsa_info_nce_workspace_bytes(int B) { return al(nce_workspace_bytes(B)); }

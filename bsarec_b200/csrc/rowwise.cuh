@@ -90,10 +90,17 @@ int gather_last_rows(const float* src, float* dst, int B, int L, int d, cudaStre
 // pairwise BCE at the last position (SASRec's loss, model/sasrec.py:42-63): bce.cu
 size_t bce_pair_workspace_bytes(int B, int d);
 int bce_pair_fwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
-                 float* loss, void* ws, cudaStream_t st);
+                 float* loss, void* ws, int variant, cudaStream_t st);
 int bce_pair_bwd(int B, int d, long long N, const float* s, const float* E, const long long* pos, const long long* neg,
-                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, cudaStream_t st);
+                 const float* d_loss, float* ds, float* dE, void* ws, size_t ws_bytes, int variant, cudaStream_t st);
 int scatter_rows(const long long* idx, long long M, long long dst_rows, const float* src, int d, float* dst, cudaStream_t st);
+// FMLPRec's learned circular filter: fmlp.cu
+bool fmlp_supported(int L, int d);
+int fmlp_trig(float* Tc, float* Ts, int L, cudaStream_t st);
+int fmlp_kernel_fwd(const float* W, const float* Tc, const float* Ts, float* K, int L, int d, cudaStream_t st);
+int fmlp_kernel_bwd(const float* dK, const float* Tc, const float* Ts, float* dW, int L, int d, cudaStream_t st);
+int circ_apply(const float* in, const float* kern, bool kern_per_batch, const float* add, float* out, int B, int L, int d,
+               bool adjoint, cudaStream_t st);
 // in-batch InfoNCE of DuoRec (model/duorec.py:47-75, sim = 'dot'): bce.cu
 size_t nce_workspace_bytes(int B);
 int nce_fwd(int B, int d, float tau, const float* z, float* loss, void* ws, cudaStream_t st);

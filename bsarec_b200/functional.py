@@ -29,6 +29,7 @@ class Hyper:
     alpha: float
     p_hidden: float
     p_attn: float
+    kind: int = 0          # bsa_block_desc.kind: 0 BSARecBlock, 1 FMLPRecBlock (sibling model)
 
 
 def _stream() -> int:
@@ -63,7 +64,7 @@ def filter_basis(L: int, kept_bins: int, device) -> torch.Tensor:
 def _block_desc(h: Hyper, B: int, L: int, layer: int, training: bool, seed: int, inference: bool = False) -> BlockDesc:
     return BlockDesc(B=B, L=L, d=h.hidden_size, H=h.num_attention_heads, kept_bins=h.kept_bins, alpha=h.alpha,
                      p_hidden=h.p_hidden, p_attn=h.p_attn, training=int(training), seed=seed, layer=layer,
-                     inference=int(inference))
+                     inference=int(inference), kind=h.kind)
 
 
 def _block_ptrs(tensors: Dict[str, torch.Tensor], layer: int) -> BlockPtrs:
@@ -453,7 +454,7 @@ class FusedLoss(torch.autograd.Function):
         return (None,) * 8 + tuple(grads[n] for n in names)
 
 
-def bce_pair_forward(s: torch.Tensor, E: torch.Tensor, pos: torch.Tensor, neg: torch.Tensor):
+def bce_pair_forward(s: torch.Tensor, E: torch.Tensor, pos: torch.Tensor, neg: torch.Tensor, variant: int = 0):
     """-> (loss 0-dim, workspace): pairwise BCE at the last position (sasrec.py:46-61) by ``bsa_bce_pair_fwd``."""
     lib = _cabi.load()
     B, d = s.shape
@@ -464,11 +465,11 @@ def bce_pair_forward(s: torch.Tensor, E: torch.Tensor, pos: torch.Tensor, neg: t
         ws = torch.empty(wsb, dtype=torch.uint8, device=s.device)
         loss = torch.empty((), dtype=torch.float32, device=s.device)
         check(lib.bsa_bce_pair_fwd(B, d, E.shape[0], _ptr(s), _ptr(E), _ptr(pos), _ptr(neg), _ptr(loss), _ptr(ws), wsb,
-                                   _stream()), "bsa_bce_pair_fwd")
+                                   int(variant), _stream()), "bsa_bce_pair_fwd")
     return loss, ws
 
 
-def bce_pair_backward(s, E, pos, neg, d_loss, dE: torch.Tensor, ws: torch.Tensor) -> torch.Tensor:
+def bce_pair_backward(s, E, pos, neg, d_loss, dE: torch.Tensor, ws: torch.Tensor, variant: int = 0) -> torch.Tensor:
     """Accumulates the gathered-row gradients into dE [N,d]; returns ds [B,d]."""
     lib = _cabi.load()
     B, d = s.shape
@@ -476,7 +477,7 @@ def bce_pair_backward(s, E, pos, neg, d_loss, dE: torch.Tensor, ws: torch.Tensor
         ds = torch.empty(B, d, dtype=torch.float32, device=s.device)
         d_loss = d_loss.to(dtype=torch.float32).contiguous()
         check(lib.bsa_bce_pair_bwd(B, d, E.shape[0], _ptr(s), _ptr(E), _ptr(pos.contiguous()), _ptr(neg.contiguous()),
-                                   _ptr(d_loss), _ptr(ds), _ptr(dE), _ptr(ws), ws.numel(), _stream()), "bsa_bce_pair_bwd")
+                                   _ptr(d_loss), _ptr(ds), _ptr(dE), _ptr(ws), ws.numel(), int(variant), _stream()), "bsa_bce_pair_bwd")
     return ds
 
 
@@ -490,7 +491,7 @@ class FusedPairLoss(torch.autograd.Function):
         params = dict(zip(names, tensors))
         xs, state = encoder_forward(hyper, params, ids, training, seed, keep_for_backward=True, last_only=True)
         s = xs[-1]
-        loss, ws = bce_pair_forward(s, params["item_embeddings.weight"], pos, neg)
+        loss, ws = bce_pair_forward(s, params["item_embeddings.weight"], pos, neg, variant=hyper.kind)
         ctx.hyper, ctx.names, ctx.state, ctx.s, ctx.pos, ctx.neg, ctx.ws = hyper, names, state, s, pos, neg, ws
         ctx.save_for_backward(*tensors)
         return loss
@@ -505,7 +506,7 @@ class FusedPairLoss(torch.autograd.Function):
             grads["position_embeddings.weight"].zero_()
         E, gE = params["item_embeddings.weight"], grads["item_embeddings.weight"]
         gE.zero_()                                       # no dense cross-entropy part here: rows are accumulated into zeros
-        ds = bce_pair_backward(ctx.s, E, ctx.pos, ctx.neg, d_loss, gE, ctx.ws)
+        ds = bce_pair_backward(ctx.s, E, ctx.pos, ctx.neg, d_loss, gE, ctx.ws, variant=hyper.kind)
         d_out = ds if state.last_row else scatter_last(ds, state.L)
         encoder_backward(hyper, params, state, d_out, grads)
         ctx.state = ctx.ws = None
@@ -590,3 +591,100 @@ class FusedDuoLoss(torch.autograd.Function):
         flat.copy_(total)
         ctx.states = None
         return (None,) * 10 + tuple(grads[n] if t.requires_grad else None for n, t in zip(names, tensors))
+
+
+_fmlp_tables: Dict[Tuple[int, int], Tuple[torch.Tensor, torch.Tensor]] = {}
+
+
+def fmlp_tables(L: int, device):
+    """(Tc, Ts) fp32 [L, L//2+1] with irfft(W, n=L) == Tc W_re + Ts W_im (csrc/fmlp.cu), cached per (L, device)."""
+    lib = _cabi.load()
+    key = (L, torch.device(device).index or 0)
+    if key not in _fmlp_tables:
+        F_ = L // 2 + 1
+        Tc = torch.empty(L, F_, dtype=torch.float32, device=device)
+        Ts = torch.empty(L, F_, dtype=torch.float32, device=device)
+        with torch.cuda.device(device):
+            check(lib.bsa_fmlp_tables(_ptr(Tc), _ptr(Ts), L, _stream()), "bsa_fmlp_tables")
+        _fmlp_tables[key] = (Tc, Ts)
+    return _fmlp_tables[key]
+
+
+def fmlp_kernel(complex_weight: torch.Tensor, L: int) -> torch.Tensor:
+    """complex_weight [1, L//2+1, d, 2] (fmlprec.py:98) -> taps K [L, d] of the equivalent circular convolution."""
+    lib = _cabi.load()
+    cw = _require_cuda(complex_weight, "complex_weight", torch.float32)
+    if cw.shape[1] != L // 2 + 1:
+        raise RuntimeError(f"FMLPRec: sequence length {L} does not match the filter's {cw.shape[1]} frequency bins "
+                           "(the reference multiplies rfft(x) by the weight elementwise: L must equal max_seq_length)")
+    d = cw.shape[2]
+    Tc, Ts = fmlp_tables(L, cw.device)
+    K = torch.empty(L, d, dtype=torch.float32, device=cw.device)
+    with torch.cuda.device(cw.device):
+        check(lib.bsa_fmlp_kernel_fwd(_ptr(cw), _ptr(Tc), _ptr(Ts), _ptr(K), L, d, _stream()), "bsa_fmlp_kernel_fwd")
+    return K
+
+
+def fmlp_kernel_grad(dK: torch.Tensor, L: int) -> torch.Tensor:
+    """dK [L, d] -> gradient of complex_weight [1, L//2+1, d, 2]."""
+    lib = _cabi.load()
+    d = dK.shape[1]
+    Tc, Ts = fmlp_tables(L, dK.device)
+    dW = torch.empty(1, L // 2 + 1, d, 2, dtype=torch.float32, device=dK.device)
+    with torch.cuda.device(dK.device):
+        check(lib.bsa_fmlp_kernel_bwd(_ptr(dK.contiguous()), _ptr(Tc), _ptr(Ts), _ptr(dW), L, d, _stream()), "bsa_fmlp_kernel_bwd")
+    return dW
+
+
+FMLP_CW = "layer.filter_layer.complex_weight"      # kernel-side name of FMLPRecLayer.complex_weight under blocks.<l>.
+FMLP_K = "layer.filter_layer.sqrt_beta"            # where the block kernels expect the taps (bsa_block_desc.kind == 1)
+
+
+def fmlp_kernel_params(hyper: Hyper, params: Dict[str, torch.Tensor], L: int) -> Dict[str, torch.Tensor]:
+    """params with every layer's complex weight replaced by its convolution taps under the name the kernels read."""
+    out = {k: v for k, v in params.items() if not k.endswith(FMLP_CW)}
+    for l in range(hyper.num_hidden_layers):
+        pre = f"item_encoder.blocks.{l}."
+        out[pre + FMLP_K] = fmlp_kernel(params[pre + FMLP_CW], L)
+    return out
+
+
+class FusedFmlpLoss(torch.autograd.Function):
+    """FMLPRec's calculate_loss (fmlprec.py:40-60) as one autograd node: per layer the complex filter weight becomes the
+    taps of a circular convolution (bsa_fmlp_kernel_fwd), the encoder runs the kind-1 block (filter + feed-forward, no
+    attention), the loss is the pairwise log-sigmoid of bsa_bce_pair_* (variant 1); backward maps dK back to d weight."""
+
+    @staticmethod
+    def forward(ctx, hyper: Hyper, names: Sequence[str], ids, pos, neg, training: bool, seed: int, *tensors):
+        params = dict(zip(names, tensors))
+        ids = _require_cuda(ids, "input_ids", torch.int64)
+        kp = fmlp_kernel_params(hyper, params, ids.shape[1])
+        xs, state = encoder_forward(hyper, kp, ids, training, seed, keep_for_backward=True, last_only=True)
+        s = xs[-1]
+        loss, ws = bce_pair_forward(s, kp["item_embeddings.weight"], pos, neg, variant=1)
+        ctx.hyper, ctx.names, ctx.state, ctx.s, ctx.pos, ctx.neg, ctx.ws, ctx.kp = hyper, names, state, s, pos, neg, ws, kp
+        ctx.save_for_backward(*tensors)
+        return loss
+
+    @staticmethod
+    def backward(ctx, d_loss):
+        tensors = ctx.saved_tensors
+        names, hyper, state, kp = ctx.names, ctx.hyper, ctx.state, ctx.kp
+        grads, _ = alloc_grads(kp)
+        if state.L < kp["position_embeddings.weight"].shape[0]:
+            grads["position_embeddings.weight"].zero_()
+        E, gE = kp["item_embeddings.weight"], grads["item_embeddings.weight"]
+        gE.zero_()
+        ds = bce_pair_backward(ctx.s, E, ctx.pos, ctx.neg, d_loss, gE, ctx.ws, variant=1)
+        d_out = ds if state.last_row else scatter_last(ds, state.L)
+        encoder_backward(hyper, kp, state, d_out, grads)
+        out = []
+        for n, t in zip(names, tensors):
+            if not t.requires_grad:
+                out.append(None)
+            elif n.endswith(FMLP_CW):
+                out.append(fmlp_kernel_grad(grads[n[:-len(FMLP_CW)] + FMLP_K], state.L))
+            else:
+                out.append(grads[n])
+        ctx.state = ctx.ws = ctx.kp = None
+        return (None,) * 7 + tuple(out)

@@ -346,3 +346,93 @@ class DuoRecModel(SASRecModel):
         sem = same_target if self.ssl == "us_x" else None
         return Fn.FusedDuoLoss.apply(self._hyper(), [n for n, _ in named], input_ids, answers, sem, self.training, seeds,
                                      self.ce_impl, self.tau, self.lmd_sem, *[t for _, t in named])
+
+
+class _FmlpLayer(nn.Module):            # fmlprec.py:95-100
+    def __init__(self, args):
+        super().__init__()
+        self.complex_weight = nn.Parameter(torch.randn(1, args.max_seq_length // 2 + 1, args.hidden_size, 2,
+                                                       dtype=torch.float32) * 0.02)
+        self.out_dropout = nn.Dropout(args.hidden_dropout_prob)
+        self.LayerNorm = TFLayerNorm(args.hidden_size, eps=1e-12)
+
+
+class _FmlpBlock(nn.Module):            # fmlprec.py:84-88
+    def __init__(self, args):
+        super().__init__()
+        self.layer = _FmlpLayer(args)
+        self.feed_forward = _FeedForward(args)
+
+
+class _FmlpEncoder(nn.Module):          # fmlprec.py:62-68
+    def __init__(self, args):
+        super().__init__()
+        block = _FmlpBlock(args)
+        self.blocks = nn.ModuleList([copy.deepcopy(block) for _ in range(args.num_hidden_layers)])
+
+
+class FMLPRecModel(BSARecModel):
+    """Sibling model on the same kernels: ``FMLPRecModel`` of ``src/model/fmlprec.py:17-118``.
+
+    The reference's ``state_dict`` keys (``item_encoder.blocks.<l>.layer.{complex_weight, LayerNorm.*}``,
+    ``feed_forward.*``) and seeded init.  The filter layer ``irfft(rfft(x) * W)`` with its learned complex weight is run as
+    what it is exactly — a per-channel circular convolution along the sequence with taps ``irfft(W)`` (``csrc/fmlp.cu``) —
+    inside the block kernels' ``kind = 1`` mode (filter + feed-forward, no attention); the loss is the pairwise
+    log-sigmoid of ``fmlprec.py:40-60`` (``bsa_bce_pair_*`` variant 1).  Sequences must have ``max_seq_length`` positions,
+    as in the reference (the weight has ``max_seq_length // 2 + 1`` bins)."""
+
+    def __init__(self, args):
+        nn.Module.__init__(self)
+        self.args = args
+        self.item_embeddings = nn.Embedding(args.item_size, args.hidden_size, padding_idx=0)
+        self.position_embeddings = nn.Embedding(args.max_seq_length, args.hidden_size)
+        self.batch_size = args.batch_size
+        self.LayerNorm = TFLayerNorm(args.hidden_size, eps=1e-12)
+        self.dropout = nn.Dropout(args.hidden_dropout_prob)
+        self.item_encoder = _FmlpEncoder(args)
+        self.apply(self.init_weights)
+        self.register_buffer("_unused", torch.zeros(4), persistent=False)      # stands in for the attention members
+        self._init_runtime()
+
+    def _hyper(self) -> Fn.Hyper:
+        a = self.args
+        return Fn.Hyper(item_size=a.item_size, hidden_size=a.hidden_size, max_seq_length=a.max_seq_length,
+                        num_attention_heads=1, num_hidden_layers=a.num_hidden_layers, kept_bins=1, alpha=1.0,
+                        p_hidden=float(a.hidden_dropout_prob), p_attn=0.0, kind=1)
+
+    def _kernel_named(self, detach: bool):
+        out = []
+        for n, p in self.named_parameters():
+            if ".layer." in n:
+                n = n.replace(".layer.", ".layer.filter_layer.")
+            out.append((n, p.detach() if detach else p))
+        for l in range(self.args.num_hidden_layers):
+            pre = f"item_encoder.blocks.{l}.layer.attention_layer."
+            for lin in ("query", "key", "value", "dense"):
+                out += [(pre + lin + ".weight", self._unused), (pre + lin + ".bias", self._unused)]
+            out += [(pre + "LayerNorm.weight", self._unused), (pre + "LayerNorm.bias", self._unused)]
+        return out
+
+    def _tensors(self) -> Dict[str, torch.Tensor]:
+        params = dict(self._kernel_named(detach=True))
+        return Fn.fmlp_kernel_params(self._hyper(), params, self.args.max_seq_length)
+
+    def _check_length(self, input_ids):
+        if input_ids.shape[1] != self.args.max_seq_length:
+            raise RuntimeError(f"FMLPRec: sequences must have max_seq_length = {self.args.max_seq_length} positions "
+                               f"(got {input_ids.shape[1]}): the filter weight has max_seq_length // 2 + 1 bins (fmlprec.py:98,104)")
+
+    def forward(self, input_ids, user_ids=None, all_sequence_output=False):
+        self._check_length(input_ids)
+        return super().forward(input_ids, user_ids, all_sequence_output)
+
+    def last_hidden(self, input_ids):
+        self._check_length(input_ids)
+        return super().last_hidden(input_ids)
+
+    def calculate_loss(self, input_ids, answers, neg_answers, same_target, user_ids):
+        if self._exchange is not None:
+            raise RuntimeError("bsarec_b200.FMLPRecModel: use parallel.allreduce_gradients after backward for data parallel")
+        named = self._kernel_named(detach=False)
+        return Fn.FusedFmlpLoss.apply(self._hyper(), [n for n, _ in named], input_ids, answers, neg_answers, self.training,
+                                      self._next_seed(), *[t for _, t in named])

@@ -29,7 +29,7 @@ extern "C" {
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
 #endif
 
-#define BSA_ABI_VERSION 2      /* bumped whenever a desc struct or an entry point's argument list changes */
+#define BSA_ABI_VERSION 3      /* bumped whenever a desc struct or an entry point's argument list changes */
 
 /* ------------------------------------------------------------------------------------------------
  * Library
@@ -112,6 +112,10 @@ typedef struct {
     int layer;                 /* block index: selects the dropout sites 1+4*layer .. 4+4*layer */
     int inference;             /* != 0: forward only — what exists only for bsa_block_bwd (LayerNorm inputs and statistics,
                                   GELU pre-activation) is not written; `saved` is scratch and bsa_block_bwd must not follow */
+    int kind;                  /* 0: BSARecBlock.  1: FMLPRecBlock (sibling model, model/fmlprec.py:84-118): no attention; the
+                                  filter layer is a learned per-channel circular convolution whose taps K [L,d]
+                                  (bsa_fmlp_kernel_fwd) arrive as `sqrt_beta`, f_ln_* is its LayerNorm, the attention
+                                  members are ignored; bsa_block_bwd leaves dK [L,d] in grads.sqrt_beta */
 } bsa_block_desc;
 
 /* nn.Linear weights are [out,in] row-major, exactly the state_dict tensors */
@@ -291,19 +295,29 @@ int bsa_build_batch(int mode, const int64_t* seq_indptr, const int64_t* seq_item
  * answers int64 [U], hist int64 [k+1] ACCUMULATED (zero it once per evaluation).  Integer atomics only. */
 int bsa_hit_rank_hist(const int64_t* pred, const int64_t* answers, int64_t U, int k, int64_t* hist, void* stream);
 
+/* FMLPRec's learned filter (model/fmlprec.py:95-118): irfft(rfft(x) * W) == circular convolution with taps
+ * K[:, c] = irfft(W[:, c], n = L).  tables: Tc, Ts fp32 [L, L/2+1] (once per L).  kernel_fwd: complex_weight [L/2+1, d, 2]
+ * -> K [L, d].  kernel_bwd: dK [L, d] (from bsa_block_bwd, kind 1) -> d complex_weight [L/2+1, d, 2] (overwritten). */
+int bsa_fmlp_supported(int L, int d);
+int bsa_fmlp_tables(float* Tc, float* Ts, int L, void* stream);
+int bsa_fmlp_kernel_fwd(const float* complex_weight, const float* Tc, const float* Ts, float* K, int L, int d, void* stream);
+int bsa_fmlp_kernel_bwd(const float* dK, const float* Tc, const float* Ts, float* d_complex_weight, int L, int d, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Sibling model on the same kernels: SASRec = the block with the filter branch blended out
  * (alpha = 0) + this pairwise BCE at the last position, replacing SASRecModel.calculate_loss (model/sasrec.py:42-63):
  *   xp_b = <E[pos_b], s_b>, xn_b = <E[neg_b], s_b>; loss = mean_{pos_b != 0} softplus(-xp_b) + mean_{pos_b != 0} softplus(xn_b).
  * fwd keeps the logits in `workspace` for bwd (same workspace); bwd OVERWRITES d_seq_out [B,d] and ACCUMULATES the 2B
  * gathered-row gradients into d_item_emb through the sorted atomic-free scatter (id 0 skipped: padding_idx).
+ * variant 0: SASRec as above.  variant 1: FMLPRec (model/fmlprec.py:40-60): loss = mean over ALL users of
+ *   -log(sigmoid(xp) + 1e-24) - log(1 - sigmoid(xn) + 1e-24).
  * ---------------------------------------------------------------------------------------------- */
 size_t bsa_bce_pair_workspace_bytes(int B, int d);
 int bsa_bce_pair_fwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
-                     const int64_t* neg_ids, float* loss, void* workspace, size_t workspace_bytes, void* stream);
+                     const int64_t* neg_ids, float* loss, void* workspace, size_t workspace_bytes, int variant, void* stream);
 int bsa_bce_pair_bwd(int B, int d, int64_t item_size, const float* seq_out, const float* item_emb, const int64_t* pos_ids,
                      const int64_t* neg_ids, const float* d_loss, float* d_seq_out, float* d_item_emb, void* workspace,
-                     size_t workspace_bytes, void* stream);
+                     size_t workspace_bytes, int variant, void* stream);
 
 /* In-batch InfoNCE of the sibling DuoRec (model/duorec.py:47-75, sim = 'dot'; its cross-entropy term is bsa_ce_fwd/bwd):
  * z [2B, d] = the two views' last-position vectors stacked; row r's positive is row (r + B) mod 2B, its negatives every

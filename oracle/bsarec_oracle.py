@@ -23,7 +23,7 @@ __all__ = [
     "feed_forward", "encode", "calculate_loss", "loss_and_grads", "predict_full",
     "full_sort_topk", "masked_scores", "recall_at_k", "ndcg_k", "full_sort_metrics",
     "adam_train_step", "eval_step", "param_names", "encode_sasrec", "sasrec_loss", "sasrec_loss_and_grads",
-    "info_nce", "duorec_loss", "duorec_loss_and_grads",
+    "info_nce", "duorec_loss", "duorec_loss_and_grads", "encode_fmlprec", "fmlprec_loss", "fmlprec_loss_and_grads",
 ]
 
 
@@ -334,6 +334,40 @@ def duorec_loss(P, ids, answers, sem_ids, cfg: OracleConfig, tau: float, lmd_sem
 def duorec_loss_and_grads(P, ids, answers, sem_ids, cfg, tau, lmd_sem, train=True, plans=(None, None, None)):
     Q = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
     loss = duorec_loss(Q, ids, answers, sem_ids, cfg, tau, lmd_sem, train, plans)
+    loss.backward()
+    return loss.detach(), {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in Q.items()}
+
+
+def encode_fmlprec(P, ids, cfg: OracleConfig, train=False, plan=None) -> List[torch.Tensor]:
+    """``FMLPRecModel.forward(all_sequence_output=True)`` (``fmlprec.py:27-38,62-118``): per block the learned complex
+    filter ``irfft(rfft(x, 'ortho') * W, 'ortho')`` + dropout + residual + LayerNorm, then the feed-forward.  Dropout sites
+    as the kernels number them: 1 + 4 l for the filter layer, 4 + 4 l for the feed-forward."""
+    x = embed(P, ids, cfg, train, plan)
+    outs = [x]
+    L = ids.shape[1]
+    for l in range(cfg.num_hidden_layers):
+        pre = f"item_encoder.blocks.{l}."
+        w = torch.view_as_complex(P[pre + "layer.complex_weight"].contiguous())
+        f = torch.fft.irfft(torch.fft.rfft(x, dim=1, norm="ortho") * w, n=L, dim=1, norm="ortho")
+        h = _drop(f, 1 + 4 * l, cfg.hidden_dropout_prob, train, plan)
+        y = layer_norm_tf(h + x, P[pre + "layer.LayerNorm.weight"], P[pre + "layer.LayerNorm.bias"])
+        x = feed_forward(P, pre + "feed_forward.", y, cfg, l, train, plan)
+        outs.append(x)
+    return outs
+
+
+def fmlprec_loss(P, ids, pos, neg, cfg: OracleConfig, train=True, plan=None):
+    """``FMLPRecModel.calculate_loss`` (``fmlprec.py:40-60``)."""
+    s = encode_fmlprec(P, ids, cfg, train, plan)[-1][:, -1, :]
+    E = P["item_embeddings.weight"]
+    pos_logits = (F.embedding(pos, E, padding_idx=0) * s).sum(-1)
+    neg_logits = (F.embedding(neg, E, padding_idx=0) * s).sum(-1)
+    return torch.mean(-torch.log(torch.sigmoid(pos_logits) + 1e-24) - torch.log(1 - torch.sigmoid(neg_logits) + 1e-24))
+
+
+def fmlprec_loss_and_grads(P, ids, pos, neg, cfg: OracleConfig, train=True, plan=None):
+    Q = {k: v.detach().clone().requires_grad_(True) for k, v in P.items()}
+    loss = fmlprec_loss(Q, ids, pos, neg, cfg, train, plan)
     loss.backward()
     return loss.detach(), {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in Q.items()}
 

@@ -177,6 +177,42 @@ def duorec_case(name, seed, B, **cfgkw):
     print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
 
 
+def fmlprec_case(name, seed, B, **cfgkw):
+    """Sibling model: the reference's FMLPRecModel — layer outputs, pairwise log-sigmoid loss, all gradients (complex filter
+    weights included).  The filter weights are scaled up so the learned filter is not a near-zero perturbation."""
+    torch.manual_seed(seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    args = make_args(**cfgkw)
+    model = MODEL_DICT["fmlprec"](args=args)
+    perturb(model, g)
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n.endswith("complex_weight"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.5)
+    ids, answers = synth_ids(g, B, args.max_seq_length, args.item_size)
+    neg = torch.randint(1, args.item_size, (B,), generator=g)
+    answers[2] = 0
+    model.eval()
+    with torch.no_grad():
+        layers = model.predict(ids, None, all_sequence_output=True)
+    model.train()
+    loss = model.calculate_loss(ids, answers, neg, None, None)
+    model.zero_grad()
+    loss.backward()
+    out = {
+        "cfg_keys": np.array(sorted(cfgkw.keys())),
+        "cfg_vals": np.array([float(cfgkw[k]) for k in sorted(cfgkw.keys())]),
+        "ids": ids.numpy(), "answers": answers.numpy(), "neg": neg.numpy(), "loss": loss.detach().numpy(),
+    }
+    for i, t in enumerate(layers):
+        out[f"layer_out.{i}"] = t.numpy()
+    for n, p in model.named_parameters():
+        out["param." + n] = p.detach().numpy()
+        out["grad." + n] = (p.grad if p.grad is not None else torch.zeros_like(p)).numpy()
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "loss", float(loss), "params", sum(p.numel() for p in model.parameters()))
+
+
 def known_answer_case(data_name, split, out_name, store_params=True, **cfgkw):
     """Known-answer: a shipped checkpoint on a real split through the reference's own Trainer.iteration.
     Beauty/test -> src/output/BSARec_Beauty_best.log:258; LastFM/test -> BSARec_LastFM_best.log:237; the valid split
@@ -269,6 +305,10 @@ def dataset_case():
 
 
 if __name__ == "__main__":
+    if "--fmlprec" in sys.argv:
+        fmlprec_case("fmlprec_small", 23, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_hidden_layers=2)
+        fmlprec_case("fmlprec_odd", 29, B=5, item_size=97, hidden_size=32, max_seq_length=25, num_hidden_layers=1)
+        sys.exit(0)
     if "--duorec" in sys.argv:
         duorec_case("duorec_small", 19, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
                     num_hidden_layers=2)
@@ -300,4 +340,6 @@ if __name__ == "__main__":
                 num_hidden_layers=2)
     duorec_case("duorec_small", 19, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_attention_heads=2,
                 num_hidden_layers=2)
+    fmlprec_case("fmlprec_small", 23, B=8, item_size=300, hidden_size=64, max_seq_length=50, num_hidden_layers=2)
+    fmlprec_case("fmlprec_odd", 29, B=5, item_size=97, hidden_size=32, max_seq_length=25, num_hidden_layers=1)
     dataset_case()

@@ -453,3 +453,45 @@ def test_duorec_sibling_vs_reference_golden(cuda_device):
     assert abs(l3.item() - float(l_ce)) < TOL * abs(float(l_ce))
     with pytest.raises(ValueError):
         DuoRecModel(_duo_args(cfgkw, ssl="us"))
+
+
+@pytest.mark.parametrize("name", ["fmlprec_small", "fmlprec_odd"])
+def test_fmlprec_sibling_vs_reference_golden(name, cuda_device):
+    """FMLPRecModel — the learned complex filter as a per-channel circular convolution (csrc/fmlp.cu)
+    inside the block kernels' kind-1 mode — against the reference class: layer outputs, loss, all gradients including the
+    complex weights; then train-mode dropout against the oracle with identical masks."""
+    from bsarec_b200 import FMLPRecModel
+    cfgkw, data = load_golden(name)
+    cfgkw = dict(cfgkw, num_attention_heads=1)
+    P = golden_params(data)
+    model = FMLPRecModel(make_args(cfgkw))
+    model.load_state_dict({k: v.clone() for k, v in P.items()})
+    model = model.to(cuda_device)
+    ids = torch.from_numpy(data["ids"]).to(cuda_device)
+    pos, neg = torch.from_numpy(data["answers"]).to(cuda_device), torch.from_numpy(data["neg"]).to(cuda_device)
+    model.eval()
+    outs = model.predict(ids, None, all_sequence_output=True)
+    for i, o in enumerate(outs):
+        assert rel_err(o.cpu(), data[f"layer_out.{i}"]) < TOL, i
+    model.train()
+    loss = model.calculate_loss(ids, pos, neg, None, None)
+    loss.backward()
+    assert abs(loss.item() - float(data["loss"])) < TOL * abs(float(data["loss"]))
+    cfg = oracle_cfg(cfgkw)
+    _, g64 = oracle.fmlprec_loss_and_grads({k: v.double() for k, v in P.items()}, ids.cpu(), pos.cpu(), neg.cpu(), cfg)
+    check_grads(grads_of(model), g64, golden_grads(data))
+    cfg_d = oracle_cfg(cfgkw, 0.3, 0.0)
+    m2 = FMLPRecModel(make_args(cfgkw, 0.3, 0.0))
+    m2.load_state_dict({k: v.clone() for k, v in P.items()})
+    m2 = m2.to(cuda_device).train()
+    m2.set_dropout_seed(7)
+    l2 = m2.calculate_loss(ids, pos, neg, None, None)
+    l2.backward()
+    l64, g64 = oracle.fmlprec_loss_and_grads({k: v.double() for k, v in P.items()}, ids.cpu(), pos.cpu(), neg.cpu(), cfg_d,
+                                             plan=oracle.DropoutPlan(7))
+    _, g32 = oracle.fmlprec_loss_and_grads(P, ids.cpu(), pos.cpu(), neg.cpu(), cfg_d, plan=oracle.DropoutPlan(7))
+    assert abs(l2.item() - float(l64)) < TOL * abs(float(l64))
+    check_grads(grads_of(m2), g64, g32)
+    assert sorted(model.state_dict().keys()) == sorted(P.keys())
+    with pytest.raises(RuntimeError):
+        model.predict(ids[:, 1:], None)

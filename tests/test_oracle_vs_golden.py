@@ -340,3 +340,53 @@ def test_duorec_container_matches_live_reference_class():
         sys.path.remove("/root/reference/src")
         for m in [k for k in sys.modules if k == "model" or k.startswith("model.")]:
             sys.modules.pop(m, None)
+
+
+@pytest.mark.parametrize("name", ["fmlprec_small", "fmlprec_odd"])
+def test_fmlprec_oracle_vs_reference_golden(name):
+    """Sibling model: the oracle's FMLPRec restatement against the reference's FMLPRecModel (even and odd L) — layer outputs,
+    loss, all gradients; and the identity the kernels rest on: the learned filter == a circular convolution with taps
+    irfft(W)."""
+    cfgkw, data = load_golden(name)
+    cfg = OracleConfig(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, num_attention_heads=1, **cfgkw)
+    P = golden_params(data)
+    ids = torch.from_numpy(data["ids"])
+    pos, neg = torch.from_numpy(data["answers"]), torch.from_numpy(data["neg"])
+    outs = oracle.encode_fmlprec(P, ids, cfg)
+    for i, o in enumerate(outs):
+        assert rel_err(o.detach(), data[f"layer_out.{i}"]) < 1e-5, i
+    loss, grads = oracle.fmlprec_loss_and_grads(P, ids, pos, neg, cfg)
+    assert abs(float(loss) - float(data["loss"])) < 1e-6 * abs(float(data["loss"]))
+    ref = golden_grads(data)
+    for k, g in grads.items():
+        assert rel_err(g, ref[k]) < 1e-4, k
+    L = ids.shape[1]
+    w = torch.view_as_complex(P["item_encoder.blocks.0.layer.complex_weight"].double().contiguous())[0]      # [F, d]
+    taps = torch.fft.irfft(w, n=L, dim=0)                                                                       # [L, d]
+    x = torch.randn(3, L, w.shape[1], dtype=torch.float64, generator=torch.Generator().manual_seed(1))
+    want = torch.fft.irfft(torch.fft.rfft(x, dim=1, norm="ortho") * w, n=L, dim=1, norm="ortho")
+    idx = (torch.arange(L)[:, None] - torch.arange(L)[None, :]) % L                                             # (t - s) mod L
+    got = torch.einsum("tsc,bsc->btc", taps[idx], x)
+    assert (got - want).abs().max() < 1e-12
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/model"), reason="live reference only in the build container")
+def test_fmlprec_container_matches_live_reference_class():
+    sys.path.insert(0, "/root/reference/src")
+    try:
+        from model import MODEL_DICT as REF
+        from helpers import make_args
+        import bsarec_b200
+        cfgkw = dict(item_size=123, hidden_size=32, max_seq_length=21, num_hidden_layers=3, num_attention_heads=1)
+        torch.manual_seed(5)
+        ref = REF["fmlprec"](args=make_args(cfgkw, 0.5, 0.5))
+        torch.manual_seed(5)
+        ours = bsarec_b200.MODEL_DICT["fmlprec"](make_args(cfgkw, 0.5, 0.5))
+        a, b = ref.state_dict(), ours.state_dict()
+        assert list(a.keys()) == list(b.keys())
+        for k in a:
+            assert a[k].shape == b[k].shape and torch.equal(a[k], b[k]), k
+    finally:
+        sys.path.remove("/root/reference/src")
+        for m in [k for k in sys.modules if k == "model" or k.startswith("model.")]:
+            sys.modules.pop(m, None)

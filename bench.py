@@ -51,6 +51,7 @@ WORKLOADS = {
 P_DROP = 0.5        # both dropout probabilities, the reference's defaults (utils.py:86-87)
 TOPK = 20
 NBATCH = 4          # distinct synthetic batches cycled through
+GRAPH_AUTO = ("c1", "c2")     # workloads whose step is launch-bound: --graph auto captures them
 HIST_SENTINEL = 1 << 62
 
 
@@ -591,6 +592,9 @@ def main():
                          "FusedAdam, else overlap; overlap = GradExchange inside backward (dense CE part all-reduced under the "
                          "encoder backward, sparse rows all-gathered); bucket = one flat all-reduce after backward; vp = "
                          "vocabulary-parallel cross-entropy + sharded item-table Adam (no [N,d] all-reduce)")
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
+                    help="one CUDA-graph launch per train / eval step (bsarec_b200/graphs.py); auto = on at N=1 with FusedAdam "
+                         "for the launch-bound workloads (c1, c2)")
     ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
                     help="fused: bsarec_b200.FusedAdam (one kernel pass per tensor); torch: torch.optim.Adam (foreach)")
     args = ap.parse_args()
@@ -675,7 +679,22 @@ def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
         optim.step()
         return loss
 
+    use_graph = args.graph == "on" or (args.graph == "auto" and args.workload in GRAPH_AUTO)
+    if use_graph and (world > 1 or args.optimizer != "fused"):
+        if args.graph == "on" and rank == 0:
+            print("bench: --graph on needs N=1 and the fused optimizer; running eager", file=sys.stderr)
+        use_graph = False
+    eager_train_step = train_step
+    if use_graph:
+        from bsarec_b200 import GraphedTrainStep, GraphedTopk
+        gstep = GraphedTrainStep(model, optim)
+
+        def train_step(b):                       # noqa: F811 — the timed loops run the graph, the profiled pass the eager body
+            return gstep(b["ids"], b["answers"])
+
     def e2e_step(hb):
+        if use_graph:                            # pinned host batch straight into the graph's input tensors
+            return gstep(hb["ids"], hb["answers"]).item()
         ids = hb["ids"].to(dev, non_blocking=True)
         answers = hb["answers"].to(dev, non_blocking=True)
         return train_step({"ids": ids, "answers": answers}).item()
@@ -693,10 +712,31 @@ def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
         def eval_step(b):
             return ev(b["ids"], b["hist"])[0]
         eval_keys = ("ids", "hist")
+    elif use_graph:
+        # the trainer's form of the eval call (trainers.py:131-133): the whole history matrix resident on the device once,
+        # the batch's user ids select its rows — fixed shapes, so the step is one graph launch
+        nnz = [0]
+        for b in resident:
+            nnz.append(nnz[-1] + int(b["indptr"][-1]))
+        all_indptr = torch.cat([resident[0]["indptr"][:1]] + [b["indptr"][1:] + nnz[i] for i, b in enumerate(resident)])
+        all_indices = torch.cat([b["indices"][:int(b["indptr"][-1])] for b in resident] + [torch.zeros(1, dtype=torch.int64, device=dev)])
+        for i in range(NBATCH):
+            pinned[i]["rows"] = (torch.arange(B, dtype=torch.int64) + i * B).pin_memory()
+            resident[i]["rows"] = pinned[i]["rows"].to(dev)
+        gtopk = GraphedTopk(model, k=TOPK)
+
+        def eager_eval_step(b):
+            return model.full_sort_topk(b["ids"], None, all_indptr, all_indices, k=TOPK, hist_rows=b["rows"])
+
+        def eval_step(b):
+            return gtopk(b["ids"], all_indptr, all_indices, b["rows"])
+        eval_keys = ("ids", "rows")
     else:
         def eval_step(b):
             return model.full_sort_topk(b["ids"], None, b["indptr"], b["indices"], k=TOPK)
         eval_keys = ("ids", "indptr", "indices")
+    if not use_graph:
+        eager_eval_step = eval_step
 
     def timed(fn, n):
         return timed_loop(fn, n, barrier, world, dev, flush)
@@ -709,10 +749,13 @@ def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
     l0 = _cabi.launch_count()
     ms_train = timed(lambda i: train_step(resident[i % NBATCH]), args.steps)
     launches = _cabi.launch_count() - l0
+    if use_graph:                                # kernels inside a replay are not seen by the host-side counter
+        launches = gstep.launches_per_replay * args.steps
     sampler.stop_flag = True
-    # same region again with per-kernel event timing switched on (roofline of the dominant kernel)
+    # same region again with per-kernel event timing switched on (roofline of the dominant kernel) — the eager body:
+    # events cannot bracket the nodes of a graph
     _cabi.profile(True)
-    timed(lambda i: train_step(resident[i % NBATCH]), args.steps)
+    ms_prof = timed(lambda i: eager_train_step(resident[i % NBATCH]), args.steps)
     prof = _cabi.profile_results()
     _cabi.profile(False)
     # end to end: pinned host batches in, loss out
@@ -725,7 +768,7 @@ def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
         eval_step(resident[i % NBATCH])
     ms_eval = timed(lambda i: eval_step(resident[i % NBATCH]), args.steps)
     _cabi.profile(True)
-    timed(lambda i: eval_step(resident[i % NBATCH]), args.steps)
+    timed(lambda i: eager_eval_step(resident[i % NBATCH]), args.steps)
     prof_eval = _cabi.profile_results()
     _cabi.profile(False)
 
@@ -759,7 +802,10 @@ def run_train_eval(args, desc, cfg, B, cpu_B, rank, world, local_rank):
     config = make_config(args.workload, desc, B, world, args)
     # `config` stays identical to the reference arm's (the driver compares them); run details go beside it
     run_detail = {"optimizer_impl": "bsarec_b200.FusedAdam" if args.optimizer == "fused" else "torch.optim.Adam",
-                  "dp_exchange": args.dp if world > 1 else None, "ce_impl": args.ce_impl}
+                  "dp_exchange": args.dp if world > 1 else None, "ce_impl": args.ce_impl,
+                  "cuda_graph": ("one graph launch per train step (%d kernels of this library inside) and per eval step (%d); "
+                                 "per-kernel roofline timed on the eager body" % (gstep.launches_per_replay, gtopk.launches_per_replay))
+                  if use_graph else None}
     if roofline is not None and eval_roof is not None:
         roofline["eval"] = {k: eval_roof[k] for k in ("kernel", "bound", "achieved", "peak", "unit", "frac", "avg_launch_ms",
                                                        "share_of_step")}

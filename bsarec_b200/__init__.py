@@ -6,8 +6,9 @@ from .model import BSARecModel, SASRecModel, DuoRecModel, FMLPRecModel
 from .trainer import Trainer
 from .optim import FusedAdam
 from .data import SequenceStore, DeviceBatchLoader, HitRankAccumulator
+from .graphs import GraphedTrainStep, GraphedTopk
 
 MODEL_DICT = {"bsarec": BSARecModel, "sasrec": SASRecModel, "duorec": DuoRecModel, "fmlprec": FMLPRecModel}
 
 __all__ = ["BSARecModel", "SASRecModel", "DuoRecModel", "FMLPRecModel", "Trainer", "FusedAdam", "MODEL_DICT", "SequenceStore", "DeviceBatchLoader",
-           "HitRankAccumulator"]
+           "HitRankAccumulator", "GraphedTrainStep", "GraphedTopk"]

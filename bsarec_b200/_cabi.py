@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbsarec_sm100a.so")
 
-ABI_VERSION = 3          # == BSA_ABI_VERSION of include/bsarec_b200.h (checked at load)
+ABI_VERSION = 4          # == BSA_ABI_VERSION of include/bsarec_b200.h (checked at load)
 
 c_f32p = C.c_void_p
 c_i64p = C.c_void_p
@@ -63,6 +63,8 @@ SIGNATURES = {
     "bsa_abi_version": (_I, []),
     "bsa_last_error_string": (C.c_char_p, []),
     "bsa_launch_count": (C.c_ulonglong, []),
+    "bsa_set_replay_state": (None, [_VP]),
+    "bsa_get_replay_state": (_VP, []),
     "bsa_profile_enable": (None, [_I]),
     "bsa_profile_reset": (None, []),
     "bsa_profile_num_tags": (_I, []),

@@ -8,7 +8,32 @@
 namespace bsa {
 namespace {
 
-struct AdamP { float lr_over_bc1, bc2_sqrt, beta1, beta2, eps, wd; };
+struct AdamP {
+    float lr_over_bc1, bc2_sqrt, beta1, beta2, eps, wd;
+    // CUDA-graph replays: the step number is `step + replay[1]`, the bias corrections are formed on the device
+    float lr = 0.f;
+    long long step = 0;
+    const unsigned long long* replay = nullptr;
+};
+
+__device__ __forceinline__ AdamP adam_resolve(AdamP a) {
+    if (a.replay) {
+        const double s = (double)(a.step + (long long)__ldg(a.replay + 1));
+        const double bc1 = 1.0 - pow((double)a.beta1, s), bc2 = 1.0 - pow((double)a.beta2, s);
+        a.lr_over_bc1 = (float)((double)a.lr / bc1);
+        a.bc2_sqrt = (float)sqrt(bc2);
+    }
+    return a;
+}
+
+static AdamP make_adam(float lr, float beta1, float beta2, float eps, float wd, long long step) {
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    AdamP a{(float)((double)lr / bc1), (float)sqrt(bc2), beta1, beta2, eps, wd};
+    a.lr = lr;
+    a.step = step;
+    a.replay = g_replay_state;
+    return a;
+}
 
 __device__ __forceinline__ void adam1(float& p, float g, float& m, float& v, const AdamP& a) {
     if (a.wd != 0.f) g = fmaf(a.wd, p, g);
@@ -19,7 +44,8 @@ __device__ __forceinline__ void adam1(float& p, float g, float& m, float& v, con
 }
 
 __global__ void __launch_bounds__(256)
-adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n, AdamP a) {
+adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n, AdamP a_in) {
+    const AdamP a = adam_resolve(a_in);
     const long long n4 = n >> 2;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -45,7 +71,8 @@ struct AdamMulti {
 };
 
 __global__ void __launch_bounds__(256)
-adam_multi_kernel(const __grid_constant__ AdamMulti t, AdamP a) {
+adam_multi_kernel(const __grid_constant__ AdamMulti t, AdamP a_in) {
+    const AdamP a = adam_resolve(a_in);
     const int k = blockIdx.y;
     float* __restrict__ p = t.p[k];
     const float* __restrict__ g = t.g[k];
@@ -72,8 +99,7 @@ adam_multi_kernel(const __grid_constant__ AdamMulti t, AdamP a) {
 int adam_step_multi(int count, float* const* p, const float* const* g, float* const* m, float* const* v, const long long* n,
                     float lr, float beta1, float beta2, float eps, float wd, long long step, cudaStream_t st) {
     BSA_REQUIRE(step >= 1, "bsa_adam_step_multi: step counts from 1");
-    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
-    const AdamP a{(float)((double)lr / bc1), (float)sqrt(bc2), beta1, beta2, eps, wd};
+    const AdamP a = make_adam(lr, beta1, beta2, eps, wd, step);
     for (int base = 0; base < count; base += ADAM_MULTI) {
         AdamMulti t;
         const int c = count - base < ADAM_MULTI ? count - base : ADAM_MULTI;
@@ -106,8 +132,7 @@ int adam_step(float* p, const float* g, float* m, float* v, long long n, float l
     BSA_REQUIRE(step >= 1, "bsa_adam_step: step counts from 1");
     BSA_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
                   reinterpret_cast<uintptr_t>(v)) & 15) == 0, "bsa_adam_step: tensors must be 16-byte aligned");
-    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
-    AdamP a{(float)((double)lr / bc1), (float)sqrt(bc2), beta1, beta2, eps, wd};
+    const AdamP a = make_adam(lr, beta1, beta2, eps, wd, step);
     long long blocks = (n / 4 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks < 1) blocks = 1;

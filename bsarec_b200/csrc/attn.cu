@@ -99,7 +99,7 @@ __device__ __forceinline__ void load_a_frags(float (&a)[DH / 8][4], const float*
 // dropout multipliers of two consecutive elements idx, idx + 1 of the [B,H,L,L] probability tensor
 __device__ __forceinline__ void dropout_mult2(const Dropout& dr, unsigned long long idx, float& m0, float& m1) {
     if (dr.thr == 0u) { m0 = m1 = 1.0f; return; }
-    const unsigned long long w = splitmix64(dr.key + (idx >> 2));
+    const unsigned long long w = splitmix64(dropout_key(dr) + (idx >> 2));
     const unsigned int s = (unsigned int)(idx & 3ull);
     m0 = (((unsigned int)(w >> (16 * s)) & 0xFFFFu) >= dr.thr) ? dr.scale : 0.0f;
     if (s != 3u) m1 = (((unsigned int)(w >> (16 * (s + 1))) & 0xFFFFu) >= dr.thr) ? dr.scale : 0.0f;

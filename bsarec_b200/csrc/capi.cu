@@ -47,6 +47,7 @@ static inline size_t al(size_t x) { return (x + 255) / 256 * 256; }
 
 // ---- kernel timing registry
 int g_profile_on = 0;
+const unsigned long long* g_replay_state = nullptr;
 namespace {
 struct ProfRec {
     const char* name;
@@ -102,6 +103,9 @@ extern "C" {
 int bsa_abi_version(void) { return BSA_ABI_VERSION; }
 const char* bsa_last_error_string(void) { return g_err; }
 unsigned long long bsa_launch_count(void) { return g_launch_count; }
+
+void bsa_set_replay_state(const uint64_t* state_dev) { g_replay_state = (const unsigned long long*)state_dev; }
+const uint64_t* bsa_get_replay_state(void) { return (const uint64_t*)g_replay_state; }
 
 void bsa_profile_enable(int on) { g_profile_on = on ? 1 : 0; }
 void bsa_profile_reset(void) {

@@ -64,7 +64,15 @@ struct Dropout {
     // row mapping for kernels that run on a row subset of a [rows, d] tensor (the last-position path): element (row, j)
     // draws the mask of element (row * rmul + radd, j) of the full tensor.  Identity by default.
     long long rmul = 1, radd = 0;
+    // CUDA-graph replays (bsa_set_replay_state): when `epoch` is set the key is formed ON THE DEVICE from
+    // pre + *epoch, i.e. the launch behaves as if it had been made with seed + *epoch — one captured launch, a new
+    // dropout stream every replay.  Null (the default) leaves `key` as computed on the host.
+    unsigned long long pre = 0;
+    const unsigned long long* epoch = nullptr;
 };
+
+// device words of the replay state: [0] = seed offset added to every dropout seed, [1] = Adam step offset
+extern const unsigned long long* g_replay_state;
 
 __host__ __device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
     z += 0x9E3779B97F4A7C15ull;
@@ -75,7 +83,9 @@ __host__ __device__ __forceinline__ unsigned long long splitmix64(unsigned long 
 
 static inline Dropout make_dropout(unsigned long long seed, int site, float p, int training) {
     Dropout d;
-    d.key = splitmix64(seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(site + 1));
+    d.pre = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(site + 1);
+    d.key = splitmix64(d.pre);
+    d.epoch = g_replay_state;
     d.thr = (training && p > 0.f) ? (unsigned int)(p * 65536.0f + 0.5f) : 0u;
     d.scale = (d.thr ? 1.0f / (1.0f - p) : 1.0f);
     return d;
@@ -83,10 +93,14 @@ static inline Dropout make_dropout(unsigned long long seed, int site, float p, i
 
 static inline Dropout dropout_rows(Dropout d, long long rmul, long long radd) { d.rmul = rmul; d.radd = radd; return d; }
 
+__device__ __forceinline__ unsigned long long dropout_key(const Dropout& dr) {
+    return dr.epoch ? splitmix64(dr.pre + __ldg(dr.epoch)) : dr.key;
+}
+
 // multiplier (0 or scale) for linear element index i
 __device__ __forceinline__ float dropout_mult(const Dropout& dr, unsigned long long i) {
     if (dr.thr == 0u) return 1.0f;
-    unsigned long long w = splitmix64(dr.key + (i >> 2));
+    unsigned long long w = splitmix64(dropout_key(dr) + (i >> 2));
     unsigned int r16 = (unsigned int)(w >> (16 * (unsigned int)(i & 3ull))) & 0xFFFFu;
     return r16 >= dr.thr ? dr.scale : 0.0f;
 }
@@ -99,7 +113,7 @@ __device__ __forceinline__ float dropout_mult_row(const Dropout& dr, long long r
 // four consecutive elements starting at i (i % 4 == 0): one hash for all four
 __device__ __forceinline__ void dropout_mult4(const Dropout& dr, unsigned long long i, float m[4]) {
     if (dr.thr == 0u) { m[0] = m[1] = m[2] = m[3] = 1.0f; return; }
-    unsigned long long w = splitmix64(dr.key + (i >> 2));
+    unsigned long long w = splitmix64(dropout_key(dr) + (i >> 2));
 #pragma unroll
     for (int j = 0; j < 4; ++j) m[j] = (((unsigned int)(w >> (16 * j)) & 0xFFFFu) >= dr.thr) ? dr.scale : 0.0f;
 }

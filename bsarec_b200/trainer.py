@@ -4,6 +4,10 @@ Same constructor and methods (train / valid / test / save / load / predict_full 
 iteration).  The train branch is the reference's loop unchanged in meaning (H2D copy, calculate_loss,
 zero_grad, backward, Adam.step, loss.item()); the eval branch keeps scoring, history masking and top-20 on
 the device through ``BSARecModel.full_sort_topk`` and returns the same ``(scores, str)`` pair.
+
+``args.cuda_graph = True`` (additional, off by default): the optimizer is ``bsarec_b200.FusedAdam`` and both loop
+bodies run as one CUDA-graph launch per full-size batch (``bsarec_b200/graphs.py``) — for the launch-bound shapes of
+the real datasets.
 """
 from __future__ import annotations
 
@@ -56,7 +60,15 @@ class Trainer:
         self.eval_dataloader = eval_dataloader
         self.test_dataloader = test_dataloader
         betas = (args.adam_beta1, args.adam_beta2)
-        self.optim = Adam(self.model.parameters(), lr=args.lr, betas=betas, weight_decay=args.weight_decay)
+        self.cuda_graph = bool(getattr(args, "cuda_graph", False))
+        if self.cuda_graph:
+            from .graphs import GraphedTrainStep, GraphedTopk
+            from .optim import FusedAdam
+            self.optim = FusedAdam(self.model.parameters(), lr=args.lr, betas=betas, weight_decay=args.weight_decay)
+            self._train_step = GraphedTrainStep(self.model, self.optim)
+            self._topk = GraphedTopk(self.model, k=20)
+        else:
+            self.optim = Adam(self.model.parameters(), lr=args.lr, betas=betas, weight_decay=args.weight_decay)
         self._hist_cache = {}
         if logger is not None:
             logger.info(f"Total Parameters: {sum([p.nelement() for p in self.model.parameters()])}")
@@ -122,10 +134,13 @@ class Trainer:
             rec_loss, steps = 0.0, 0
             for batch in dataloader:
                 user_ids, input_ids, answers, neg_answer, same_target = (t.to(self.device, non_blocking=True) for t in batch)
-                loss = self.model.calculate_loss(input_ids, answers, neg_answer, same_target, user_ids)
-                self.optim.zero_grad()
-                loss.backward()
-                self.optim.step()
+                if self.cuda_graph:
+                    loss = self._train_step(input_ids, answers, neg_answer, same_target, user_ids)
+                else:
+                    loss = self.model.calculate_loss(input_ids, answers, neg_answer, same_target, user_ids)
+                    self.optim.zero_grad()
+                    loss.backward()
+                    self.optim.step()
                 rec_loss += loss.item()
                 steps += 1
             post_fix = {"epoch": epoch, "rec_loss": '{:.4f}'.format(rec_loss / max(steps, 1))}
@@ -141,7 +156,12 @@ class Trainer:
         with torch.no_grad():
             for batch in dataloader:
                 user_ids, input_ids, answers = (t.to(self.device, non_blocking=True) for t in batch[:3])
-                pred = self.model.full_sort_topk(input_ids, user_ids, hist.indptr, hist.indices, k=20, hist_rows=user_ids)
+                if self.cuda_graph and input_ids.shape[0] == getattr(self.args, "batch_size", -1):
+                    pred = self._topk(input_ids, hist.indptr, hist.indices, user_ids)
+                    if keep:
+                        pred = pred.clone()          # the graph's output tensor is rewritten by the next replay
+                else:
+                    pred = self.model.full_sort_topk(input_ids, user_ids, hist.indptr, hist.indices, k=20, hist_rows=user_ids)
                 acc.update(pred, answers)
                 if keep:
                     preds.append(pred)

@@ -29,7 +29,7 @@ extern "C" {
 #pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
 #endif
 
-#define BSA_ABI_VERSION 3      /* bumped whenever a desc struct or an entry point's argument list changes */
+#define BSA_ABI_VERSION 4      /* bumped whenever a desc struct or an entry point's argument list changes */
 
 /* ------------------------------------------------------------------------------------------------
  * Library
@@ -38,6 +38,16 @@ int bsa_abi_version(void);
 const char* bsa_last_error_string(void);
 /* kernels launched by this library since load (bench.py's "gpu_launches") */
 unsigned long long bsa_launch_count(void);
+/* CUDA-graph capture of a whole step (bsarec_b200/graphs.py; "capture launch-bound inner loops in CUDA graphs"):
+ * every launch argument is frozen at capture time, so the two per-step host values of the path — the dropout seed
+ * and Adam's step number (trainers.py:103-107 draws fresh masks and advances the optimizer every iteration) — can be
+ * taken from device memory instead.  state_dev points to two uint64 words that the caller advances between replays:
+ *   [0] is added to every `seed` (a launch made with seed s behaves exactly like a launch made with s + state[0]),
+ *   [1] is added to every Adam `step`.
+ * Launches made while the pointer is set read the words when they RUN.  Null (the default) restores host values.
+ * Process-global (one process per GPU), not thread-safe against concurrent launches from other threads. */
+void bsa_set_replay_state(const uint64_t* state_dev);
+const uint64_t* bsa_get_replay_state(void);
 /* Per-kernel device timing for the roofline report: when enabled, tagged launches are bracketed by CUDA
  * events on the launching stream.  bsa_profile_get synchronises them and returns the tag's name, total
  * device milliseconds, algorithmic work (FLOPs or bytes as the tag defines) and launch count. */

@@ -64,7 +64,7 @@ def test_library_is_sm100a_with_tcgen05_and_tma(lib):
 def test_abi_version_and_pure_host_queries(lib):
     from bsarec_b200._cabi import BlockDesc, CeDesc, EmbedDesc, TopkDesc
     from bsarec_b200 import _cabi
-    assert lib.bsa_abi_version() == _cabi.ABI_VERSION == 3
+    assert lib.bsa_abi_version() == _cabi.ABI_VERSION == 4
     # filter rank = 2*kept-1, capped by L (exact low-pass operator, bsarec.py:87,93-97)
     assert lib.bsa_filter_rank(50, 3) == 5
     assert lib.bsa_filter_rank(200, 3) == 5

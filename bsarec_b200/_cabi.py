@@ -121,6 +121,8 @@ SIGNATURES = {
     "bsa_info_nce_workspace_bytes": (_SZ, [_I]),
     "bsa_info_nce_fwd": (_I, [_I, _I, C.c_float, _VP, _VP, _VP, _SZ, _VP]),
     "bsa_info_nce_bwd": (_I, [_I, _I, C.c_float, _VP, _VP, C.c_float, _VP, _VP, _SZ, _VP]),
+    "bsa_info_nce_static_max_b": (_I, []),
+    "bsa_info_nce_fwd_static": (_I, [_I, _I, C.c_float, _VP, _VP, _VP]),
     "bsa_bce_pair_workspace_bytes": (_SZ, [_I, _I]),
     "bsa_bce_pair_fwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _I, _VP]),
     "bsa_bce_pair_bwd": (_I, [_I, _I, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _SZ, _I, _VP]),

@@ -3,8 +3,10 @@
 // averaged over the users whose positive id is not padding.  SURVEY.md §8(f) rank 4: the encoder underneath is the
 // BSARec block with the filter branch blended out (alpha = 0), this file is the only new arithmetic.
 // Warp per user, float4 lanes, fixed-order reductions (no atomics) -> bit-reproducible.
+#include "../../include/bsarec_b200.h"
 #include "common.cuh"
 #include "rowwise.cuh"
+#include <mutex>
 
 namespace bsa {
 namespace {
@@ -251,3 +253,64 @@ int bce_pair_bwd(int B, int d, long long N, const float* s, const float* E, cons
 }
 
 }  // namespace bsa
+
+// ================================================================================================ no-allocation variant
+// bsa_info_nce_fwd_static: the InfoNCE forward with its scratch (row log-sum-exps and per-row losses, 2 x [2B] floats) in
+// a file-scope device array instead of a caller-provided workspace — for callers that cannot allocate (code under CUDA
+// graph capture, tight serving loops).  Every GPU that loads the library holds the array until exit.  All calls share it
+// and it keeps the last call's contents; both kernels overwrite every element they later read (nothing has to start at
+// zero), but two calls that overlap on the GPU (different streams) race on it.
+namespace bsa {
+namespace {
+constexpr int NCE_STATIC_MAX_B = BSA_INFO_NCE_STATIC_MAX_B;
+constexpr size_t NCE_STATIC_HALF = ((size_t)2 * NCE_STATIC_MAX_B * 4 + 255) / 256 * 256;     // bytes of one [2B] array
+static __device__ __align__(256) unsigned char g_nce_static_scratch[2 * NCE_STATIC_HALF];
+
+constexpr int NCE_MAX_DEVICES = 64;
+void* g_nce_static_ptr[NCE_MAX_DEVICES] = {};
+std::mutex g_nce_static_mu;
+
+// the array's NAME is a host-side stand-in in host code: its device address is looked up once per device, with that
+// device current, and that pointer is what the kernels get
+int nce_static_scratch(void** out) {
+    int dev = -1;
+    BSA_CHECK_CUDA(cudaGetDevice(&dev));
+    BSA_REQUIRE(dev >= 0 && dev < NCE_MAX_DEVICES, "bsa_info_nce_fwd_static: device index %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_nce_static_mu);
+    if (!g_nce_static_ptr[dev]) {
+        void* p = nullptr;
+        BSA_CHECK_CUDA(cudaGetSymbolAddress(&p, g_nce_static_scratch));
+        BSA_REQUIRE(p != nullptr, "bsa_info_nce_fwd_static: cudaGetSymbolAddress returned a null address");
+        g_nce_static_ptr[dev] = p;
+    }
+    *out = g_nce_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+}  // namespace bsa
+
+extern "C" int bsa_info_nce_static_max_b(void) { return bsa::NCE_STATIC_MAX_B; }
+
+extern "C" int bsa_info_nce_fwd_static(int B, int d, float tau, const float* z, float* loss, void* stream) {
+    using namespace bsa;
+    BSA_REQUIRE(z && loss, "bsa_info_nce_fwd_static: null argument");
+    BSA_REQUIRE(B >= 1 && B <= NCE_STATIC_MAX_B,
+                "bsa_info_nce_fwd_static: B = %d outside [1, %d] (the static scratch holds 2 x [2 * %d] floats; use "
+                "bsa_info_nce_fwd with a workspace for larger batches)", B, NCE_STATIC_MAX_B, NCE_STATIC_MAX_B);
+    BSA_REQUIRE(d >= 4 && d % 4 == 0 && tau > 0.f, "bsa_info_nce_fwd_static: need d %% 4 == 0, tau > 0");
+    const int n2 = 2 * B;
+    const size_t smem = (size_t)(d + n2) * 4;
+    BSA_REQUIRE(smem <= 48 * 1024, "bsa_info_nce_fwd_static: 2B + d = %d floats exceed the shared-memory plan", d + n2);
+    void* base = nullptr;
+    int rc = nce_static_scratch(&base);
+    if (rc) return rc;
+    float* lse = (float*)base;
+    float* rows = (float*)((char*)base + NCE_STATIC_HALF);
+    cudaStream_t st = (cudaStream_t)stream;
+    nce_fwd_kernel<<<n2, 256, smem, st>>>(z, n2, B, d, 1.0f / tau, lse, rows);
+    BSA_LAUNCH_CHECK();
+    nce_mean_kernel<<<1, 1024, 0, st>>>(rows, n2, loss);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+

@@ -337,6 +337,18 @@ size_t bsa_info_nce_workspace_bytes(int B);
 int bsa_info_nce_fwd(int B, int d, float tau, const float* z, float* loss, void* workspace, size_t workspace_bytes, void* stream);
 int bsa_info_nce_bwd(int B, int d, float tau, const float* z, const float* d_loss, float scale, float* dz, const void* workspace,
                      size_t workspace_bytes, void* stream);
+/* No-allocation variant of bsa_info_nce_fwd.  NO counterpart in the reference: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same inputs and `loss` output as bsa_info_nce_fwd, no workspace argument: the scratch (row
+ * log-sum-exps and per-row losses, 2 x [2B] floats) is a file-scope device array of the library, sized for
+ * B <= BSA_INFO_NCE_STATIC_MAX_B (64 KB; every GPU that loads the library holds it until exit).  Larger B, or
+ * 2B + d > 12288 floats, is rejected with an error (-1, bsa_last_error_string).  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine).  All calls share the array and it keeps the last call's contents; every element
+ * read is written first by the same call, so nothing needs clearing, but calls that OVERLAP on the GPU (two streams) race on
+ * it — serialise them.  The log-sum-exps are not handed back: use bsa_info_nce_fwd when bsa_info_nce_bwd follows. */
+#define BSA_INFO_NCE_STATIC_MAX_B 4096
+int bsa_info_nce_static_max_b(void);
+int bsa_info_nce_fwd_static(int B, int d, float tau, const float* z, float* loss, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Small utilities shared by the host wrappers

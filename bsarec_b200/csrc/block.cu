@@ -115,7 +115,8 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     if (attn_fused_supported(c.L, c.d, c.H) && attn_impl() == 2) b.f(attn_bwd_scratch_floats(c.B, c.H, c.L, c.d));   // delta (+ Pd, dS tiles)
     else { b.f(PL); b.f(PL); }
     // partials: LN gamma/beta, column sums, split-K, beta2
-    b.f(3ll * rowwise_partial_blocks(M) * d);
+    for (int i = 0; i < 9; ++i) b.f((long long)rowwise_partial_blocks(M) * d);     // three LayerNorm sites x (gamma, beta, column) partials
+    for (int i = 0; i < 3; ++i) b.f((long long)colsum_partial_rows(M) * d);        // dq / dk / dv column partials
     b.f((long long)colsum_partial_rows(M) * 4 * d);
     b.f(splitk_floats(M, d));
     b.f((long long)c.B * d);
@@ -144,6 +145,24 @@ int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, f
     return launch_gemm(p, st);
 }
 
+// q, k, v = x Wq^T + bq, x Wk^T + bk, x Wv^T + bv in ONE tcgen05 launch (N = 3d, the three weights split into one [3d, d]
+// pair): the shared A operand is read once and the epilogue sends each column segment to its own [M, d] tensor
+// (q + s * seg_stride).  BSA_QKV_FUSE=0 restores the three launches.
+bool qkv_fuse_enabled() {
+    static const bool on = [] { const char* e = getenv("BSA_QKV_FUSE"); return !(e && atoi(e) == 0); }();
+    return on;
+}
+int linear_fwd_qkv(const Lin& ln, const Act& a, const bsa_block_weights& w, float* q, long long seg_stride, long long M, int d,
+                   cudaStream_t st) {
+    const long long dd = (long long)d * d;
+    int rc;
+    if ((rc = umma_split(w.wq, ln.w_hi, ln.w_lo, dd, st))) return rc;
+    if ((rc = umma_split(w.wk, ln.w_hi + dd, ln.w_lo + dd, dd, st))) return rc;
+    if ((rc = umma_split(w.wv, ln.w_hi + 2 * dd, ln.w_lo + 2 * dd, dd, st))) return rc;
+    return umma_gemm_ps((int)M, 3 * d, d, a.hi, a.lo, M, d, d, false, ln.w_hi, ln.w_lo, 3 * d, d, d, false, q, d, w.bq, ACT_NONE,
+                        nullptr, nullptr, 1.f, 0, nullptr, nullptr, nullptr, 0, st, nullptr, d, seg_stride, w.bk, w.bv);
+}
+
 // dx [M, K] (+)= dy [M, N] @ W[N, K]              (nn.Linear input gradient)
 int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
                      const float* aux_in, float* out_hi, float* out_lo, cudaStream_t st, float* colpart = nullptr) {
@@ -164,13 +183,14 @@ int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, lo
 
 // dW [N, K] = dy[M, N]^T @ x [M, K] ; db [N] = colsum(dy)   (deterministic split-K + column sums)
 int linear_bwd_weight(const Lin& ln, const Act& dy, const Act& x, float* dW, float* db, long long M, int N, int K, float* part_sk,
-                      float* part_cs, cudaStream_t st) {
+                      float* part_cs, cudaStream_t st, long long ld_dy = 0) {
     if (ln.umma) {
         const float *gh_, *gl_, *xh_, *xl_;
         int rc;
         if ((rc = act_pair(ln, dy, M * N, ln.s1_hi, ln.s1_lo, gh_, gl_, st))) return rc;
         if ((rc = act_pair(ln, x, M * K, ln.s2_hi, ln.s2_lo, xh_, xl_, st))) return rc;
-        rc = umma_gemm_ps(N, K, (int)M, gh_, gl_, M, N, N, true, xh_, xl_, M, K, K, true, dW, K, nullptr, 0, nullptr,
+        // ld_dy: dy's pair is a column window of a wider [M, ld_dy] buffer (the packed dq | dk | dv pair)
+        rc = umma_gemm_ps(N, K, (int)M, gh_, gl_, M, N, ld_dy ? ld_dy : N, true, xh_, xl_, M, K, K, true, dW, K, nullptr, 0, nullptr,
                           nullptr, 1.f, 0, nullptr, nullptr, ln.partial, ln.partial_bytes, st);
         if (rc) return rc;
         return db ? colsum(dy.x, M, N, part_cs, db, 0, st) : 0;      // db == nullptr: the producer already summed the columns
@@ -241,9 +261,13 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
                             inf ? nullptr : s.rstd_f, B, L, d, r, dr_f, st))) return rc;
     // attention branch
     if ((rc = split_act(lin, x, s.x_hi, s.x_lo, M * d, ax, st))) return rc;        // one split feeds q, k, v (and dW in backward)
-    if ((rc = linear_fwd(lin, ax, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
-    if ((rc = linear_fwd(lin, ax, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
-    if ((rc = linear_fwd(lin, ax, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    if (lin.umma && qkv_fuse_enabled() && d % 32 == 0 && (s.k - s.q) == (s.v - s.k)) {
+        if ((rc = linear_fwd_qkv(lin, ax, w, s.q, s.k - s.q, M, d, st))) return rc;
+    } else {
+        if ((rc = linear_fwd(lin, ax, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+        if ((rc = linear_fwd(lin, ax, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+        if ((rc = linear_fwd(lin, ax, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    }
     if (s.fused) {
         if ((rc = attn_fwd(s.q, s.k, s.v, ids, s.ctx, s.lse, B, H, L, d, dr_p, st))) return rc;
     } else {
@@ -303,13 +327,19 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     float* dh_ = b.f(M * 4 * d);
     float* Pd_ws = s.fused ? nullptr : b.f(PL);
     float* dP = s.fused ? b.f(attn_bwd_scratch_floats(B, H, L, d)) : b.f(PL);
+    // Parameter-gradient partials: every site has its own slab and the reductions run as ONE launch at the end of the call
+    // (ReduceBatch) instead of ~16 dependent 8-CTA launches between the GEMMs.
     const int nrb = rowwise_partial_blocks(M);
-    float* pgam = b.f((long long)nrb * d);
-    float* pbet = b.f((long long)nrb * d);
-    float* pcol = b.f((long long)nrb * d);
+    float* lnp[3][3];                                      // [feed-forward LN, attention LN, filter LN][gamma, beta, column]
+    for (int i = 0; i < 3; ++i)
+        for (int k = 0; k < 3; ++k) lnp[i][k] = b.f((long long)nrb * d);
+    float* part_qkv[3];
+    for (int i = 0; i < 3; ++i) part_qkv[i] = b.f((long long)colsum_partial_rows(M) * d);
     float* part_cs = b.f((long long)colsum_partial_rows(M) * 4 * d);
     float* part_sk = b.f(splitk_floats(M, d));
     float* pbeta2 = b.f((long long)B * d);
+    ReduceBatch rb;
+    float *pgam = lnp[0][0], *pbet = lnp[0][1], *pcol = lnp[0][2];
     Lin lin = make_lin(b, d);
     float* g_hi = b.f(M * d); float* g_lo = b.f(M * d);            // split pair of the current [M,d] upstream gradient
     float* dh_hi = b.f(M * 4 * d); float* dh_lo = b.f(M * 4 * d);  // split pair of dh [M,4d]
@@ -330,13 +360,13 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const bool fuse_o = lin.umma && ln_bwd_split_ok(d, g_out, s.z_o, w.o_ln_w, dyb, nullptr, g_hi, g_lo);
     if (fuse_o) {
         if ((rc = ln_bwd_split(g_out, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, nullptr, pgam, pbet, &nblk, M, d, dr_o, g_hi, g_lo, pcol, st))) return rc;
-        if ((rc = reduce_partials(pcol, nblk, d, g.b2, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = reduce_batch_add(rb, pcol, nblk, d, g.b2, nullptr, 1.f, 0, st))) return rc;
         ag = Act{nullptr, g_hi, g_lo};
     } else {
         if ((rc = ln_bwd(g_out, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_o, st))) return rc;
     }
-    if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
     if (!fuse_o) {
         const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
         if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
@@ -347,7 +377,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         // dh leaves the GEMM only as its split pair (all dW1 / dX read) plus per-32-row column sums for db1: the fp32 copy
         // and the pass that summed it are gone; the [M,4d] dh_ buffer holds the [M/32, 4d] partial sums instead
         if ((rc = linear_bwd_input(lin, ag, w.w2, nullptr, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st, dh_))) return rc;
-        if ((rc = reduce_partials(dh_, 4 * (int)((M + 127) / 128), 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = reduce_batch_add(rb, dh_, 4 * (int)((M + 127) / 128), 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
         if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, M, 4 * d, d, part_sk, part_cs, st))) return rc;
     } else {
         if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st))) return rc;
@@ -357,25 +387,28 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
 
     if (c.kind == 1) {
         // FMLPRecBlock: y = LN(drop(conv(x, K)) + x).  dx = d(LN input) + conv^T(K, d conv); dK = sum_b corr(d conv_b, x_b)
+        pgam = lnp[2][0]; pbet = lnp[2][1];
         if ((rc = ln_bwd(dyb, 1.0f, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, dr_f.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_f, st))) return rc;
-        if ((rc = reduce_partials(pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
-        if ((rc = reduce_partials(pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
         const float* gconv = dr_f.thr ? dd : dzf;
         if ((rc = circ_apply(gconv, x, true, nullptr, dq, B, L, d, true, st))) return rc;              // per-sequence partials of dK
-        if ((rc = reduce_partials(dq, B, L * d, g.sqrt_beta, nullptr, 1.f, 0, st))) return rc;
-        return circ_apply(gconv, w.sqrt_beta, false, dzf, dx, B, L, d, true, st);
+        if ((rc = reduce_batch_add(rb, dq, B, L * d, g.sqrt_beta, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = circ_apply(gconv, w.sqrt_beta, false, dzf, dx, B, L, d, true, st))) return rc;
+        return reduce_batch_flush(rb, st);
     }
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
+    pgam = lnp[1][0]; pbet = lnp[1][1]; pcol = lnp[1][2];
     const bool fuse_a = lin.umma && ln_bwd_split_ok(d, dyb, s.z_a, w.a_ln_w, dx, nullptr, g_hi, g_lo);
     if (fuse_a) {
         if ((rc = ln_bwd_split(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, nullptr, pgam, pbet, &nblk, M, d, dr_a, g_hi, g_lo, pcol, st))) return rc;
-        if ((rc = reduce_partials(pcol, nblk, d, g.bo, nullptr, 1.f, 0, st))) return rc;
+        if ((rc = reduce_batch_add(rb, pcol, nblk, d, g.bo, nullptr, 1.f, 0, st))) return rc;
         ag = Act{nullptr, g_hi, g_lo};
     } else {
         if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dx, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, M, d, dr_a, st))) return rc;
     }
-    if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
     if (!fuse_a) {
         const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
         if ((rc = split_act(lin, t1, g_hi, g_lo, M * d, ag, st))) return rc;
@@ -430,12 +463,30 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         const float* ws3[3] = {w.wq, w.wk, w.wv};
         float* dws3[3] = {g.wq, g.wk, g.wv};
         float* dbs3[3] = {g.bq, g.bk, g.bv};
+        // tcgen05 path: dq | dk | dv leave their split as ONE packed [M, 3d] pair (in the dead dh pair buffers), so the input
+        // gradient is a single K = 3d GEMM against the [3d, d] weight pair instead of three accumulating launches that each
+        // re-read and re-write dx; the three weight gradients read their column window of the packed pair.
+        const bool pack = lin.umma && qkv_fuse_enabled() && d % 32 == 0 && umma_split_colsum_ok(d, dq, dh_hi, dh_lo) &&
+                          umma_split_colsum_ok(d, dk, dh_hi + d, dh_lo + d) && umma_split_colsum_ok(d, dv, dh_hi + 2 * d, dh_lo + 2 * d) &&
+                          umma_split_colsum_rows(M) <= colsum_partial_rows(M);
+        if (pack) {
+            const long long dd = (long long)d * d;
+            for (int i = 0; i < 3; ++i) {
+                float *ph = dh_hi + (long long)i * d, *pl = dh_lo + (long long)i * d;
+                if ((rc = umma_split_colsum(grads3[i], ph, pl, M, d, part_qkv[i], st, 3 * d))) return rc;
+                if ((rc = reduce_batch_add(rb, part_qkv[i], umma_split_colsum_rows(M), d, dbs3[i], nullptr, 1.f, 0, st))) return rc;
+                if ((rc = linear_bwd_weight(lin, Act{grads3[i], ph, pl}, ax, dws3[i], nullptr, M, d, d, part_sk, part_cs, st, 3 * d))) return rc;
+                if ((rc = umma_split(ws3[i], lin.w_hi + i * dd, lin.w_lo + i * dd, dd, st))) return rc;
+            }
+            if ((rc = umma_gemm_ps((int)M, d, 3 * d, dh_hi, dh_lo, M, 3 * d, 3 * d, false, lin.w_hi, lin.w_lo, 3 * d, d, d, true, dx, d,
+                                   nullptr, ACT_NONE, nullptr, nullptr, 1.f, 1, nullptr, nullptr, nullptr, 0, st))) return rc;
+        } else
         for (int i = 0; i < 3; ++i) {
             if (lin.umma && umma_split_colsum_ok(d, grads3[i], g_hi, g_lo) && umma_split_colsum_rows(M) <= colsum_partial_rows(M)) {
                 // the operand split of dq / dk / dv also sums their columns: no separate pass for the bias gradients
                 ag = Act{grads3[i], g_hi, g_lo};
-                if ((rc = umma_split_colsum(grads3[i], g_hi, g_lo, M, d, part_cs, st))) return rc;
-                if ((rc = reduce_partials(part_cs, umma_split_colsum_rows(M), d, dbs3[i], nullptr, 1.f, 0, st))) return rc;
+                if ((rc = umma_split_colsum(grads3[i], g_hi, g_lo, M, d, part_qkv[i], st))) return rc;
+                if ((rc = reduce_batch_add(rb, part_qkv[i], umma_split_colsum_rows(M), d, dbs3[i], nullptr, 1.f, 0, st))) return rc;
                 if ((rc = linear_bwd_weight(lin, ag, ax, dws3[i], nullptr, M, d, d, part_sk, part_cs, st))) return rc;
             } else {
                 if ((rc = split_act(lin, grads3[i], g_hi, g_lo, M * d, ag, st))) return rc;
@@ -446,12 +497,13 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     }
 
     // ---- filter branch: dsp = LN(drop(u) + x), weight alpha
+    pgam = lnp[2][0]; pbet = lnp[2][1];
     if ((rc = ln_bwd(dyb, c.alpha, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, nullptr, pgam, pbet, &nblk, M, d, dr_f, st))) return rc;
-    if ((rc = reduce_partials(pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
     if ((rc = filter_bwd(x, basis, w.sqrt_beta, dzf, dx, pbeta2, B, L, d, r, dr_f, st))) return rc;
-    if ((rc = reduce_partials(pbeta2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
-    return 0;
+    if ((rc = reduce_batch_add(rb, pbeta2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
+    return reduce_batch_flush(rb, st);
 }
 
 // ================================================================================================ last block, last row
@@ -491,7 +543,7 @@ size_t last_workspace_bytes(const bsa_block_desc& c) {
     for (int i = 0; i < 10; ++i) b.f(B * d);        // tmp, u, dsp | dyb, dd, dxl, dzf, dctx, dql, dlow/pb2/tmp
     b.f(B * 4 * d);                                 // dh
     b.f(B * H * d); b.f(B * H * d); b.f(B * H); b.f(B * H);       // dxs, dgq, dsp, dcq
-    b.f(2ll * rowwise_partial_blocks(B) * d);
+    for (int i = 0; i < 6; ++i) b.f((long long)rowwise_partial_blocks(B) * d);      // three LayerNorm sites x (gamma, beta) partials
     b.f((long long)colsum_partial_rows(B) * 4 * d);
     b.f(splitk_floats(B, d));
     b.f(lin_ws_floats(d));                          // tcgen05 linears: weight pair, split-K slabs ...
@@ -574,8 +626,11 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     float* dh_ = b.f(Bd * 4);
     float* dxs = b.f(Bd * H); float* dgq = b.f(Bd * H); float* dsp = b.f((long long)B * H); float* dcq = b.f((long long)B * H);
     const int nrb = rowwise_partial_blocks(B);
-    float* pgam = b.f((long long)nrb * d);
-    float* pbet = b.f((long long)nrb * d);
+    float* lnp[3][2];                                      // per LayerNorm site: reduced together at the end (ReduceBatch)
+    for (int i = 0; i < 3; ++i)
+        for (int k = 0; k < 2; ++k) lnp[i][k] = b.f((long long)nrb * d);
+    float *pgam = lnp[0][0], *pbet = lnp[0][1];
+    ReduceBatch rb;
     float* part_cs = b.f((long long)colsum_partial_rows(B) * 4 * d);
     float* part_sk = b.f(splitk_floats(B, d));
     const Lin lin = make_last_lin(b, B, d);
@@ -590,8 +645,8 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
 
     // ---- feed-forward
     if ((rc = ln_bwd(d_out_last, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, B, d, dr_o, st))) return rc;
-    if ((rc = reduce_partials(pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
     const Act at2{dr_o.thr ? dd : dyb, nullptr, nullptr};
     if ((rc = linear_bwd_weight(lin, at2, ah, g.w2, g.b2, B, d, 4 * d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, at2, w.w2, dh_, B, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, nullptr, nullptr, st))) return rc;
@@ -600,9 +655,10 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, B, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
     // ---- attention branch: gsp = LN(drop(tmp) + xl), weight (1-alpha); dxl starts as the residual gradient
+    pgam = lnp[1][0]; pbet = lnp[1][1];
     if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dxl, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, B, d, dr_a, st))) return rc;
-    if ((rc = reduce_partials(pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
     const Act at1{dr_a.thr ? dd : dxl, nullptr, nullptr};
     if ((rc = linear_bwd_weight(lin, at1, actx, g.wo, g.bo, B, d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, at1, w.wo, dctx, B, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
@@ -616,11 +672,12 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     if ((rc = last_dsp(dctx, w.bv, dsp, B, d, H, st))) return rc;
 
     // ---- filter branch: dsp = LN(drop(u) + xl), weight alpha
+    pgam = lnp[2][0]; pbet = lnp[2][1];
     if ((rc = ln_bwd(dyb, c.alpha, s.z_f, s.mean_f, s.rstd_f, w.f_ln_w, dzf, nullptr, pgam, pbet, &nblk, B, d, dr_f, st))) return rc;
-    if ((rc = reduce_partials(pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.f_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
     if ((rc = last_filter_bwd(dzf, s.xl, s.low, w.sqrt_beta, dlow, dxl, pb2, B, d, dr_f, st))) return rc;
-    if ((rc = reduce_partials(pb2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pb2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
 
     // ---- per-sequence adjoint over all positions
     if ((rc = last_attn_bwd(x, s.p, s.gq, dxs, dsp, dlow, basis, r, dx, dgq, dcq, B, H, L, d, dr_p, st))) return rc;
@@ -635,7 +692,8 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     if ((rc = linear_bwd_weight(lin, adql, axl, g.wq, g.bq, B, d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, adql, w.wq, dxl, B, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // value.bias / key.bias done; the row L-1 residual paths go into dx last
-    return last_add_rows(dx, dxl, B, L, d, st);
+    if ((rc = last_add_rows(dx, dxl, B, L, d, st))) return rc;
+    return reduce_batch_flush(rb, st);
 }
 
 size_t block_last_saved_bytes(const bsa_block_desc& c) { return carve_saved_last(nullptr, c).bytes + 256; }

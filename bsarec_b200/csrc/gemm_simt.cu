@@ -9,14 +9,19 @@ namespace {
 // BM = 128: (2x4) x (CGx4) register tile per thread.  BM = 32: 2 x (CGx4) — the small-problem variant: a [512, 256]
 // output (the last-row path's [B, d] linears) is 8 CTAs at 128 x 128 but 64 at 32 x 64, and those launches are bound by
 // how many SMs they reach, not by FMA:LDS ratio.
-template <int BM, int BN, bool AK, bool BKM>
+// BK = 16 with two shared-memory buffers, or BK = 64 with one (BM = 32 only): the small launches are a chain of k-tiles
+// that each wait out one global-load latency (profiles/r2u launch list: 17 us for K = 256, 52 us for K = 1024 — one
+// microsecond per 16-wide tile), so the deep variant keeps 4x the bytes in flight per round trip.
+template <int BM, int BN, int BK, bool AK, bool BKM>
 __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
-    constexpr int BK = 16, LDSA = BM + 4, LDSB = BN + 4;
+    constexpr int LDSA = BM + 4, LDSB = BN + 4;
+    constexpr int NBUF = BK == 16 ? 2 : 1;
     constexpr int TM = BM / 16;            // rows per thread
     constexpr int CG = BN / 64;            // column groups of 4 per thread
-    constexpr int NBL = BN / 16;           // B elements loaded per thread per k-tile
-    __shared__ __align__(16) float As[2][BK][LDSA];
-    __shared__ __align__(16) float Bs[2][BK][LDSB];
+    constexpr int NAL = BM * BK / 256;     // A elements loaded per thread per k-tile
+    constexpr int NBL = BN * BK / 256;     // B elements loaded per thread per k-tile
+    __shared__ __align__(16) float As[NBUF][BK][LDSA];
+    __shared__ __align__(16) float Bs[NBUF][BK][LDSB];
 
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
@@ -40,14 +45,15 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
         for (int j = 0; j < CG * 4; ++j) acc[i][j] = 0.f;
     auto row_of = [&](int i) { return BM == 128 ? (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4)) : ty * TM + i; };
 
-    float ra[TM], rb[NBL];
+    float ra[NAL], rb[NBL];
 
     auto load_tiles = [&](int k0) {
 #pragma unroll
-        for (int i = 0; i < TM; ++i) {
+        for (int i = 0; i < NAL; ++i) {
+            const int e = tid + 256 * i;
             int m, k;
-            if (AK) { k = tid & 15; m = (tid >> 4) + 16 * i; }
-            else    { m = tid % BM; k = tid / BM + (256 / BM) * i; }
+            if (AK) { k = e % BK; m = e / BK; }
+            else    { m = e % BM; k = e / BM; }
             const int gm = m0 + m, gk = k0 + k;
             float v = 0.f;
             if (gm < p.M && gk < kend)
@@ -56,9 +62,10 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
         }
 #pragma unroll
         for (int i = 0; i < NBL; ++i) {
+            const int e = tid + 256 * i;
             int n, k;
-            if (BKM) { k = tid & 15; n = (tid >> 4) + 16 * i; }
-            else     { n = tid % BN; k = tid / BN + (256 / BN) * i; }
+            if (BKM) { k = e % BK; n = e / BK; }
+            else     { n = e % BN; k = e / BN; }
             const int gn = n0 + n, gk = k0 + k;
             float v = 0.f;
             if (gn < p.N && gk < kend)
@@ -68,17 +75,19 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
     };
     auto store_tiles = [&](int buf) {
 #pragma unroll
-        for (int i = 0; i < TM; ++i) {
+        for (int i = 0; i < NAL; ++i) {
+            const int e = tid + 256 * i;
             int m, k;
-            if (AK) { k = tid & 15; m = (tid >> 4) + 16 * i; }
-            else    { m = tid % BM; k = tid / BM + (256 / BM) * i; }
+            if (AK) { k = e % BK; m = e / BK; }
+            else    { m = e % BM; k = e / BM; }
             As[buf][k][m] = ra[i];
         }
 #pragma unroll
         for (int i = 0; i < NBL; ++i) {
+            const int e = tid + 256 * i;
             int n, k;
-            if (BKM) { k = tid & 15; n = (tid >> 4) + 16 * i; }
-            else     { n = tid % BN; k = tid / BN + (256 / BN) * i; }
+            if (BKM) { k = e % BK; n = e / BK; }
+            else     { n = e % BN; k = e / BN; }
             Bs[buf][k][n] = rb[i];
         }
     };
@@ -90,7 +99,7 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
     }
     __syncthreads();
     for (int t = 0; t < ntiles; ++t) {
-        const int buf = t & 1;
+        const int buf = NBUF == 2 ? (t & 1) : 0;
         if (t + 1 < ntiles) load_tiles(kbeg + (t + 1) * BK);
 #pragma unroll
         for (int k = 0; k < BK; ++k) {
@@ -114,7 +123,8 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
 #pragma unroll
                 for (int j = 0; j < CG * 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
         }
-        if (t + 1 < ntiles) store_tiles(buf ^ 1);
+        if (NBUF == 1) __syncthreads();                  // single buffer: everyone has finished reading it
+        if (t + 1 < ntiles) store_tiles(NBUF == 2 ? (buf ^ 1) : 0);
         __syncthreads();
     }
 
@@ -170,12 +180,12 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, float* __re
     C[off] = v;
 }
 
-template <int BM, int BN>
+template <int BM, int BN, int BK = 16>
 int dispatch(const GemmP& p, dim3 grid, cudaStream_t st) {
-    if (p.a_kmajor && p.b_kmajor) gemm_kernel<BM, BN, true, true><<<grid, 256, 0, st>>>(p);
-    else if (p.a_kmajor && !p.b_kmajor) gemm_kernel<BM, BN, true, false><<<grid, 256, 0, st>>>(p);
-    else if (!p.a_kmajor && p.b_kmajor) gemm_kernel<BM, BN, false, true><<<grid, 256, 0, st>>>(p);
-    else gemm_kernel<BM, BN, false, false><<<grid, 256, 0, st>>>(p);
+    if (p.a_kmajor && p.b_kmajor) gemm_kernel<BM, BN, BK, true, true><<<grid, 256, 0, st>>>(p);
+    else if (p.a_kmajor && !p.b_kmajor) gemm_kernel<BM, BN, BK, true, false><<<grid, 256, 0, st>>>(p);
+    else if (!p.a_kmajor && p.b_kmajor) gemm_kernel<BM, BN, BK, false, true><<<grid, 256, 0, st>>>(p);
+    else gemm_kernel<BM, BN, BK, false, false><<<grid, 256, 0, st>>>(p);
     BSA_LAUNCH_CHECK();
     return 0;
 }
@@ -206,7 +216,9 @@ int launch_gemm(const GemmP& p, cudaStream_t st) {
     int rc;
     {
         ProfScope prof(PROF_GEMM_SIMT, st, 2.0 * p.M * p.N * (double)p.K * p.batch);
-        rc = small ? dispatch<32, 64>(p, grid, st) : BN == 64 ? dispatch<128, 64>(p, grid, st) : dispatch<128, 128>(p, grid, st);
+        const int kspan = p.splitk > 1 ? (p.K + p.splitk - 1) / p.splitk : p.K;
+        rc = small ? (kspan >= 128 ? dispatch<32, 64, 64>(p, grid, st) : dispatch<32, 64>(p, grid, st))
+                   : BN == 64 ? dispatch<128, 64>(p, grid, st) : dispatch<128, 128>(p, grid, st);
     }
     if (rc) return rc;
     if (p.splitk > 1) {

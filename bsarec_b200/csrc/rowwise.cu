@@ -467,6 +467,46 @@ reduce_partials_kernel(const float* __restrict__ part, int nblk, int n, float* _
     }
 }
 
+// Up to ReduceBatch::MAXJ of those reductions in one launch (blockIdx.y = job): the parameter-gradient partials of a block's
+// backward pass are reduced together at its end — ~25 dependent 5 - 20 us launches of 8 CTAs become one launch that fills the
+// GPU.  Block = 32 columns x 32 row groups; fixed summation order -> deterministic.
+struct ReduceJobsP {
+    const float* part[ReduceBatch::MAXJ]; float* out[ReduceBatch::MAXJ]; const float* mult[ReduceBatch::MAXJ];
+    int nblk[ReduceBatch::MAXJ]; int n[ReduceBatch::MAXJ]; float scale[ReduceBatch::MAXJ]; int acc[ReduceBatch::MAXJ];
+};
+__global__ void __launch_bounds__(1024)
+reduce_partials_multi_kernel(const __grid_constant__ ReduceJobsP t) {
+    __shared__ float sh[32][33];
+    const int job = blockIdx.y;
+    const int n = t.n[job], nblk = t.nblk[job];
+    if ((int)blockIdx.x * 32 >= n) return;                       // block-uniform
+    const float* __restrict__ part = t.part[job];
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + lane;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (j < n) {
+        int k = g;
+        for (; k + 96 < nblk; k += 128) {
+            s0 += part[(long long)k * n + j];
+            s1 += part[(long long)(k + 32) * n + j];
+            s2 += part[(long long)(k + 64) * n + j];
+            s3 += part[(long long)(k + 96) * n + j];
+        }
+        for (; k < nblk; k += 32) s0 += part[(long long)k * n + j];
+    }
+    sh[g][lane] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (g == 0 && j < n) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) s += sh[k][lane];
+        s *= t.scale[job];
+        if (t.mult[job]) s *= t.mult[job][j];
+        float* out = t.out[job];
+        out[j] = t.acc[job] ? out[j] + s : s;
+    }
+}
+
 __global__ void pos_grad_kernel(const float* __restrict__ dz, float* __restrict__ dP, int B, long long LD, int accumulate) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= LD) return;
@@ -706,6 +746,9 @@ int colsum_partial_rows(long long M) { return (int)((M + COLSUM_ROWS - 1) / COLS
 int colsum(const float* X, long long M, int N, float* part, float* out, int accumulate, cudaStream_t st) {
     const int nblk = colsum_partial_rows(M);
     if (nblk == 0) return 0;
+    // few rows (the [B, d] tensors of the last-row path): the rows themselves are the partials — one launch instead of a
+    // 4-CTA partial pass plus the reduction
+    if (M <= 1024) return reduce_partials(X, (int)M, N, out, nullptr, 1.0f, accumulate, st);
     colsum_partial_kernel<<<nblk, 256, 0, st>>>(X, M, N, COLSUM_ROWS, part);
     BSA_LAUNCH_CHECK();
     return reduce_partials(part, nblk, N, out, nullptr, 1.0f, accumulate, st);
@@ -715,6 +758,33 @@ int reduce_partials(const float* part, int nblk, int n, float* out, const float*
                     cudaStream_t st) {
     reduce_partials_kernel<<<cdiv(n, 32), 256, 0, st>>>(part, nblk, n, out, mult, scale, accumulate);
     BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int reduce_batch_flush(ReduceBatch& b, cudaStream_t st) {
+    if (b.count == 0) return 0;
+    ReduceJobsP t;
+    int nmax = 0;
+    for (int i = 0; i < ReduceBatch::MAXJ; ++i) {
+        const int j = i < b.count ? i : 0;
+        t.part[i] = b.part[j]; t.out[i] = b.out[j]; t.mult[i] = b.mult[j]; t.nblk[i] = b.nblk[j]; t.n[i] = b.n[j];
+        t.scale[i] = b.scale[j]; t.acc[i] = b.acc[j];
+        if (i < b.count && b.n[i] > nmax) nmax = b.n[i];
+    }
+    const int count = b.count;
+    b.count = 0;
+    if (nmax == 0) return 0;
+    reduce_partials_multi_kernel<<<dim3((unsigned)cdiv(nmax, 32), (unsigned)count), 1024, 0, st>>>(t);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
+int reduce_batch_add(ReduceBatch& b, const float* part, int nblk, int n, float* out, const float* mult, float scale,
+                     int accumulate, cudaStream_t st) {
+    if (n <= 0) return 0;
+    if (b.count == ReduceBatch::MAXJ) { int rc = reduce_batch_flush(b, st); if (rc) return rc; }
+    const int i = b.count++;
+    b.part[i] = part; b.nblk[i] = nblk; b.n[i] = n; b.out[i] = out; b.mult[i] = mult; b.scale[i] = scale; b.acc[i] = accumulate;
     return 0;
 }
 

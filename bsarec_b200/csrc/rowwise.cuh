@@ -57,6 +57,16 @@ int colsum_partial_rows(long long M);
 // out[n] (+)= mult[n]*scale * sum_{k<nblk} part[k][n]
 int reduce_partials(const float* part, int nblk, int n, float* out, const float* mult, float scale, int accumulate,
                     cudaStream_t st);
+// The same reductions collected and run as ONE launch (reduce_batch_flush).  Every job's `part` must stay untouched and
+// every `out` unread until the flush; the flush is stream-ordered like any other launch.
+struct ReduceBatch {
+    static constexpr int MAXJ = 24;
+    const float* part[MAXJ]; float* out[MAXJ]; const float* mult[MAXJ]; int nblk[MAXJ]; int n[MAXJ]; float scale[MAXJ]; int acc[MAXJ];
+    int count = 0;
+};
+int reduce_batch_add(ReduceBatch& b, const float* part, int nblk, int n, float* out, const float* mult, float scale,
+                     int accumulate, cudaStream_t st);
+int reduce_batch_flush(ReduceBatch& b, cudaStream_t st);
 // dP[t][j] (+)= sum_b dz[b][t][j]
 int pos_grad(const float* dz, float* dP, int B, int L, int d, int accumulate, cudaStream_t st);
 

@@ -38,7 +38,7 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
 constexpr int SPLIT_CS_ROWS = 128;
 __global__ void __launch_bounds__(256)
 split_colsum_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, long long M, int N,
-                    float* __restrict__ part) {
+                    float* __restrict__ part, long long out_pitch4) {
     __shared__ float4 red[256];
     const int tpr = N >> 2, groups = 256 / tpr;               // threads per row, rows in flight
     const int c4 = threadIdx.x % tpr, rg = threadIdx.x / tpr;
@@ -52,8 +52,9 @@ split_colsum_kernel(const float* __restrict__ x, float* __restrict__ hi, float* 
         const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
         float4 h, l;
         split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
-        reinterpret_cast<float4*>(hi)[i] = h;
-        reinterpret_cast<float4*>(lo)[i] = l;
+        const long long o = row * out_pitch4 + c4;            // the pair may be a column window of a wider [M, pitch] buffer
+        reinterpret_cast<float4*>(hi)[o] = h;
+        reinterpret_cast<float4*>(lo)[o] = l;
         cs.x += v.x; cs.y += v.y; cs.z += v.z; cs.w += v.w;
     }
     red[threadIdx.x] = cs;
@@ -77,6 +78,10 @@ struct StoreParams {
     int partial_accumulate;              // split-K partial slabs are running sums (added to, not overwritten)
     float* colpart;                      // optional (PRE epilogue, N % 4 == 0): column sums of the stored values per 32-row
                                          // group, [4 * m_tiles, N] -> reduce_partials gives the bias gradient
+    // Segmented output (plain epilogue only, seg_cols % 32 == 0): columns [s * seg_cols, (s + 1) * seg_cols) of the result
+    // are the separate [M, seg_cols] tensor C + s * seg_stride (pitch ldc) with its own bias — one launch computes
+    // q, k and v from one read of the shared A operand.
+    int seg_cols = 0; long long seg_stride = 0; const float* bias1 = nullptr; const float* bias2 = nullptr;
 };
 // PRE: the epilogue reads global memory (GELU pre-activation and / or the running sum) and prefetches those reads.
 // CS: it also leaves per-32-row-group column sums of what it stores (StoreParams::colpart).
@@ -98,9 +103,19 @@ struct EpiStore {
         float* base; long long ld; bool plain = p.partial == nullptr;
         if (plain) { base = p.C; ld = p.ldc; }
         else { base = p.partial + (long long)tc.split * g.M * g.N; ld = g.N; }
-        const bool vec_ok = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
+        float* const base0 = base;
+        bool vec_ok = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
 #pragma unroll 1
         for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
+            int segc = 0;                                        // first column of this chunk's output segment
+            const float* bias_p = p.bias;
+            if (!PRE && plain && p.seg_cols) {                   // warp-uniform: a 32-column chunk never straddles segments
+                const int seg = (n0 + c0) / p.seg_cols;
+                segc = seg * p.seg_cols;
+                base = base0 + (long long)seg * p.seg_stride;
+                bias_p = seg == 0 ? p.bias : (seg == 1 ? p.bias1 : p.bias2);
+                vec_ok = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
+            }
             // The epilogue's global reads (GELU pre-activation, running sum) are issued before the accumulator leaves
             // TMEM: inside the store loop each one would wait out its full latency behind the previous row's stores.
             const int col = n0 + c0 + c4 * 4;
@@ -129,12 +144,13 @@ struct EpiStore {
                 stg[lane * 8 + (j ^ (lane & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             __syncwarp();
             float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (plain && p.bias) {
-                if (col + 3 < g.N) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+            if (plain && bias_p) {
+                const float* bp = bias_p + (col - segc);
+                if (col + 3 < g.N) bias4 = __ldg(reinterpret_cast<const float4*>(bp));
                 else {
-                    if (col < g.N) bias4.x = __ldg(p.bias + col);
-                    if (col + 1 < g.N) bias4.y = __ldg(p.bias + col + 1);
-                    if (col + 2 < g.N) bias4.z = __ldg(p.bias + col + 2);
+                    if (col < g.N) bias4.x = __ldg(bp);
+                    if (col + 1 < g.N) bias4.y = __ldg(bp + 1);
+                    if (col + 2 < g.N) bias4.z = __ldg(bp + 2);
                 }
             }
 #pragma unroll
@@ -143,7 +159,7 @@ struct EpiStore {
                 const long long row = row0 + r;
                 float4 x = stg[r * 8 + (c4 ^ (r & 7))];
                 if (row >= g.M || col >= g.N) continue;
-                const long long off = row * ld + col;
+                const long long off = row * ld + (col - segc);
                 if (!plain) {                                    // split-K partials: raw (or running) sums
                     if (full) {
                         if (p.partial_accumulate) { const float4 o = *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
@@ -546,10 +562,12 @@ bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* l
 }
 int umma_split_colsum_rows(long long M) { return (int)((M + SPLIT_CS_ROWS - 1) / SPLIT_CS_ROWS); }
 // part: [umma_split_colsum_rows(M), N]
-int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st) {
+int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st, long long out_pitch) {
     BSA_REQUIRE(umma_split_colsum_ok(N, x, hi, lo), "umma_split_colsum: unsupported width %d or alignment", N);
+    if (out_pitch == 0) out_pitch = N;
+    BSA_REQUIRE(out_pitch >= N && (out_pitch & 3) == 0, "umma_split_colsum: bad output pitch %lld", out_pitch);
     if (M == 0) return 0;
-    split_colsum_kernel<<<umma_split_colsum_rows(M), 256, 0, st>>>(x, hi, lo, M, N, part);
+    split_colsum_kernel<<<umma_split_colsum_rows(M), 256, 0, st>>>(x, hi, lo, M, N, part, out_pitch >> 2);
     BSA_LAUNCH_CHECK();
     return 0;
 }
@@ -561,8 +579,14 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
                  const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
-                 size_t partial_bytes, cudaStream_t st, float* colpart) {
+                 size_t partial_bytes, cudaStream_t st, float* colpart, int seg_cols, long long seg_stride, const float* bias1,
+                 const float* bias2) {
     BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
+    if (seg_cols) {
+        BSA_REQUIRE(C && act == 0 && !accumulate && !colpart && !out_hi && seg_cols % 32 == 0 && N % seg_cols == 0 &&
+                    N / seg_cols <= 3, "umma_gemm: segmented output needs a plain epilogue and segments of a multiple of 32 columns");
+        partial = nullptr;
+    }
     BSA_REQUIRE(!colpart || ((N & 3) == 0 && (ldc & 3) == 0), "umma_gemm: fused column sums need N %% 4 == 0");
     if (colpart) partial = nullptr;                   // the column sums come from complete tiles
     BSA_REQUIRE(C || (out_hi && out_lo && !accumulate), "umma_gemm: C may be omitted only when the split pair is emitted");
@@ -582,6 +606,7 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     GemmCore g;
     if ((rc = make_core(g, M, N, K, oa, ob, BN, SCHED_N_FASTEST, splits))) return rc;
     StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr, out_hi, out_lo, 0, colpart};
+    ep.seg_cols = seg_cols; ep.seg_stride = seg_stride; ep.bias1 = bias1; ep.bias2 = bias2;
     if (g.splits > 1) {
         BSA_REQUIRE((size_t)g.splits * M * N * 4 <= partial_bytes, "umma_gemm: workspace too small for split-K");
         ep.partial = partial;
@@ -690,23 +715,29 @@ CeWs carve_ce(void* ws, int B, int d, long long N, bool bwd) {
     return w;
 }
 
-__global__ void ce_combine_kernel(const float* __restrict__ part_m, const float* __restrict__ part_s,
-                                  const float* __restrict__ tgt, int nstrips, int B, float* __restrict__ lse,
-                                  float* __restrict__ loss) {
+// Row r's log-sum-exp from the per-strip (max, sum) partials: one WARP per row, lanes over the strips (the first version
+// ran one thread per row in a single block: 2 x 74 dependent strided loads per thread, 43 us warm / 81 us cold at C3).
+__global__ void __launch_bounds__(256)
+ce_combine_kernel(const float* __restrict__ part_m, const float* __restrict__ part_s, int nstrips, int B, float* __restrict__ lse) {
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= B) return;
+    float m = -INFINITY;
+    for (int s = lane; s < nstrips; s += 32) m = fmaxf(m, part_m[(long long)s * B + r]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float sum = 0.f;
+    for (int s = lane; s < nstrips; s += 32) {
+        const float ps = part_s[(long long)s * B + r];
+        if (ps > 0.f) sum += ps * expf(part_m[(long long)s * B + r] - m);
+    }
+    sum = warp_sum(sum);                                   // xor butterfly: every lane holds the same bits
+    if (lane == 0) lse[r] = m + logf(sum);
+}
+// loss = mean_r (lse[r] - tgt[r]) in a fixed order (one block)
+__global__ void ce_loss_kernel(const float* __restrict__ lse, const float* __restrict__ tgt, int B, float* __restrict__ loss) {
     __shared__ float sh[8];
     float acc = 0.f;
-    for (int r = threadIdx.x; r < B; r += blockDim.x) {
-        float m = -INFINITY;
-        for (int s = 0; s < nstrips; ++s) m = fmaxf(m, part_m[(long long)s * B + r]);
-        float sum = 0.f;
-        for (int s = 0; s < nstrips; ++s) {
-            const float ps = part_s[(long long)s * B + r];
-            if (ps > 0.f) sum += ps * expf(part_m[(long long)s * B + r] - m);
-        }
-        const float l = m + logf(sum);
-        lse[r] = l;
-        acc += l - tgt[r];
-    }
+    for (int r = threadIdx.x; r < B; r += blockDim.x) acc += lse[r] - tgt[r];
     acc = warp_sum(acc);
     if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
     __syncthreads();
@@ -787,7 +818,9 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
         ProfScope prof(PROF_CE_FWD_UMMA, st, 2.0 * B * (double)N * d);
         if ((rc = launch<CE_BN, CE_STAGES, false, false, EpiLse<CE_BN>>(g, ep, nstrips * g.m_tiles, st))) return rc;
     }
-    ce_combine_kernel<<<1, 256, 0, st>>>(w.part_m, w.part_s, w.tgt, 2 * nstrips, B, lse, loss);
+    ce_combine_kernel<<<cdiv(B, 8), 256, 0, st>>>(w.part_m, w.part_s, 2 * nstrips, B, lse);
+    BSA_LAUNCH_CHECK();
+    ce_loss_kernel<<<1, 256, 0, st>>>(lse, w.tgt, B, loss);
     BSA_LAUNCH_CHECK();
     if (tgt_out) BSA_CHECK_CUDA(cudaMemcpyAsync(tgt_out, w.tgt, (size_t)B * 4, cudaMemcpyDeviceToDevice, st));
     return 0;

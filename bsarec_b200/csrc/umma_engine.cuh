@@ -35,11 +35,15 @@ size_t umma_gemm_partial_bytes(int M, int N);
 // (reduce_partials turns them into the bias gradient of the linear whose output gradient x is).
 bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* lo);
 int umma_split_colsum_rows(long long M);
-int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st);
+// out_pitch (floats, 0 = N): hi / lo may point at a column window of a wider [M, out_pitch] pair buffer
+int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st, long long out_pitch = 0);
 int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long long a_rows, long long a_cols,
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
                  const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
-                 size_t partial_bytes, cudaStream_t st, float* colpart = nullptr);
+                 size_t partial_bytes, cudaStream_t st, float* colpart = nullptr,
+                 // segmented output: columns [s * seg_cols, (s + 1) * seg_cols) go to C + s * seg_stride (pitch ldc) with
+                 // bias / bias1 / bias2 — q, k, v in one launch over one read of A (plain epilogue, seg_cols % 32 == 0)
+                 int seg_cols = 0, long long seg_stride = 0, const float* bias1 = nullptr, const float* bias2 = nullptr);
 
 }  // namespace bsa

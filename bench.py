@@ -51,7 +51,9 @@ WORKLOADS = {
 P_DROP = 0.5        # both dropout probabilities, the reference's defaults (utils.py:86-87)
 TOPK = 20
 NBATCH = 4          # distinct synthetic batches cycled through
-GRAPH_AUTO = ("c1", "c2")     # workloads whose step is launch-bound: --graph auto captures them
+# --graph auto captures these at N=1: c1 / c2 are launch-bound (1.6 -> 0.9 ms per step); at c3 / c5 the device time is the
+# same but the end-to-end number no longer pays ~150 host-side launches per step (profiles/r2x_bench_c3*.json: e2e +3.4 %)
+GRAPH_AUTO = ("c1", "c2", "c3", "c5")
 HIST_SENTINEL = 1 << 62
 
 
@@ -594,7 +596,7 @@ def main():
                          "vocabulary-parallel cross-entropy + sharded item-table Adam (no [N,d] all-reduce)")
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="one CUDA-graph launch per train / eval step (bsarec_b200/graphs.py); auto = on at N=1 with FusedAdam "
-                         "for the launch-bound workloads (c1, c2)")
+                         "(c1, c2, c3, c5); eager at N>1")
     ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
                     help="fused: bsarec_b200.FusedAdam (one kernel pass per tensor); torch: torch.optim.Adam (foreach)")
     args = ap.parse_args()

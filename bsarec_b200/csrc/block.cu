@@ -81,7 +81,16 @@ struct Lin {               // where the linears run: tcgen05 3xTF32 engine (defa
     bool inference = false;                    // forward only: nothing is kept for a backward pass
     // lazy operand splits (the [B, d] last-row path): an Act that arrives without its pair is split here on the fly
     float *s1_hi = nullptr, *s1_lo = nullptr, *s2_hi = nullptr, *s2_lo = nullptr;
+    // FFMA path, small problems: split-K slabs for the forward / input-gradient GEMMs (their epilogue runs in the reduction)
+    float* sk = nullptr; long long sk_floats = 0;
 };
+// floats of split-K scratch that covers any [B, <= 4d] output of the last-row path: s <= 296 / tiles + 1 slabs of M x N
+long long small_sk_floats(long long B, long long d) { return 296ll * 32 * 64 + 2 * B * 4 * d + 1024; }
+void ffma_splitk(const Lin& ln, GemmP& p) {
+    if (!ln.sk) return;
+    const int s = choose_splitk(p.M, p.N, p.K);
+    if (s > 1 && (long long)s * p.M * p.N <= ln.sk_floats) { p.splitk = s; p.partial = ln.sk; }
+}
 
 // the (hi, lo) pair of an activation operand: its own, or a split made now into the Lin's scratch
 int act_pair(const Lin& ln, const Act& a, long long n, float* s_hi, float* s_lo, const float*& hi, const float*& lo, cudaStream_t st);
@@ -142,6 +151,7 @@ int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, f
     GemmP p;
     p.A = a.x; p.B = W; p.C = out; p.M = (int)M; p.N = N; p.K = K; p.lda = K; p.ldb = K; p.ldc = N;
     p.bias = bias; p.act = act; p.aux_out = aux_out;
+    ffma_splitk(ln, p);
     return launch_gemm(p, st);
 }
 
@@ -178,6 +188,7 @@ int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, lo
     GemmP p;
     p.A = dy.x; p.B = W; p.C = dx; p.M = (int)M; p.N = K; p.K = N; p.lda = N; p.ldb = K; p.ldc = K;
     p.b_kmajor = false; p.accumulate = accumulate; p.act = act; p.aux_in = aux_in;
+    ffma_splitk(ln, p);
     return launch_gemm(p, st);
 }
 
@@ -293,11 +304,13 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = split_act(lin, s.ctx, s.ctx_hi, s.ctx_lo, M * d, actx, st))) return rc;
     if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
+    // (tcgen05 path) y also leaves the LayerNorm kernel as the split pair dense_1 reads: no separate pass over y
     if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, inf ? nullptr : s.z_a, inf ? nullptr : s.mean_a, inf ? nullptr : s.rstd_a,
-                              dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st))) return rc;
+                              dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st, lin.umma ? s.y_hi : nullptr, lin.umma ? s.y_lo : nullptr))) return rc;
+    ay = Act{s.y, lin.umma ? s.y_hi : nullptr, lin.umma ? s.y_lo : nullptr};
     }   // kind == 0
     // feed-forward
-    if ((rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
+    if (c.kind == 1 && (rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
     // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
     // (h_pre holds gelu'(pre-activation): the backward's dX epilogue multiplies by it instead of evaluating erf + exp again)
     if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_GRAD, s.h_pre, s.h_hi, s.h_lo, st))) return rc;
@@ -548,6 +561,7 @@ size_t last_workspace_bytes(const bsa_block_desc& c) {
     b.f(splitk_floats(B, d));
     b.f(lin_ws_floats(d));                          // tcgen05 linears: weight pair, split-K slabs ...
     for (int i = 0; i < 4; ++i) b.f(B * 4 * d + 256);      // ... and two lazily split operand pairs
+    b.f(small_sk_floats(B, d));                     // FFMA linears: split-K slabs
     return b.off + 8192;
 }
 
@@ -557,7 +571,12 @@ size_t last_workspace_bytes(const bsa_block_desc& c) {
 // 12.90 ms, C1 1.55 -> 1.70 ms.  Kept as a switch; the lever for these launches is fusing them, not a bigger engine.
 Lin make_last_lin(Bump& b, long long B, long long d) {
     static const bool use_umma = [] { const char* e = getenv("BSA_LAST_UMMA"); return e && atoi(e) == 1; }();
-    if (linear_impl() != 2 || !use_umma) return Lin{false, nullptr, nullptr, nullptr, 0};
+    if (linear_impl() != 2 || !use_umma) {
+        Lin ln{false, nullptr, nullptr, nullptr, 0};
+        ln.sk_floats = small_sk_floats(B, d);
+        ln.sk = b.f(ln.sk_floats);
+        return ln;
+    }
     Lin ln = make_lin(b, d);
     ln.s1_hi = b.f(B * 4 * d + 256); ln.s1_lo = b.f(B * 4 * d + 256);
     ln.s2_hi = b.f(B * 4 * d + 256); ln.s2_lo = b.f(B * 4 * d + 256);

@@ -130,18 +130,35 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
-__device__ __forceinline__ float gelu_erf(float x) { return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f)); }
-// gelu(x) and gelu'(x) from one erf: same expressions (and bits) as gelu_erf / gelu_erf_grad
+// GELU, erf form (_modules.py:47-56): gelu(x) = x Phi(x), gelu'(x) = Phi(x) + x phi(x).
+// Phi through erfc's rational form (Abramowitz & Stegun 7.1.26, |error| <= 1.5e-7 on erf, i.e. 7.5e-8 on Phi — below fp32
+// rounding of the values it multiplies and four orders under the 1e-4 parity bar): one rcp.approx, one ex2.approx and five
+// FMAs give the value AND the derivative, because erfc's exp(-x^2/2) is also phi's.  erff + expf cost ~2x the instructions,
+// and the FFN epilogues of the tcgen05 GEMMs are bound by exactly that count.
+__device__ __forceinline__ float gelu_cdf(float x, float& e) {       // returns Phi(x); e = exp(-x^2 / 2)
+    const float u = fabsf(x) * 0.70710678118654752440f;
+    float t;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, u, 1.0f)));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170368f));      // -0.5 * log2(e)
+    float poly = fmaf(t, 1.061405429f, -1.453152027f);
+    poly = fmaf(t, poly, 1.421413741f);
+    poly = fmaf(t, poly, -0.284496736f);
+    poly = fmaf(t, poly, 0.254829592f);
+    const float q = 0.5f * (poly * t) * e;                           // 0.5 erfc(|x| / sqrt 2)
+    return x < 0.f ? q : 1.0f - q;
+}
+__device__ __forceinline__ float gelu_erf(float x) { float e; return x * gelu_cdf(x, e); }
+// gelu(x) and gelu'(x) from one evaluation: same expressions (and bits) as gelu_erf / gelu_erf_grad
 __device__ __forceinline__ float gelu_erf_both(float x, float& grad) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
-    const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
-    grad = cdf + x * pdf;
-    return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    float e;
+    const float cdf = gelu_cdf(x, e);
+    grad = fmaf(x * 0.39894228040143267794f, e, cdf);
+    return x * cdf;
 }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
-    const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
-    return cdf + x * pdf;
+    float e;
+    const float cdf = gelu_cdf(x, e);
+    return fmaf(x * 0.39894228040143267794f, e, cdf);
 }
 
 }  // namespace bsa

@@ -167,17 +167,22 @@ __global__ void __launch_bounds__(256) gemm_kernel(GemmP p) {
     }
 }
 
-__global__ void splitk_reduce_kernel(const float* __restrict__ part, float* __restrict__ C, long long MN, int N,
-                                     int ldc, int splitk, float alpha, int accumulate) {
+// fixed-order sum of the split-K slabs, then the same epilogue as the unsplit kernel (bias, activation, accumulate)
+__global__ void splitk_reduce_kernel(GemmP p, long long MN) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= MN) return;
     float s = 0.f;
-    for (int k = 0; k < splitk; ++k) s += part[(long long)k * MN + i];   // fixed order
-    const long long m = i / N, n = i - m * N;
-    const long long off = m * ldc + n;
-    float v = alpha * s;
-    if (accumulate) v += C[off];
-    C[off] = v;
+    for (int k = 0; k < p.splitk; ++k) s += p.partial[(long long)k * MN + i];
+    const long long m = i / p.N, n = i - m * p.N;
+    const long long off = m * p.ldc + n;
+    float v = p.alpha * s;
+    if (p.bias) v += __ldg(p.bias + n);
+    if (p.act == ACT_GELU_SAVE_PRE) { p.aux_out[off] = v; v = gelu_erf(v); }
+    else if (p.act == ACT_MUL_GELU_GRAD) v *= gelu_erf_grad(p.aux_in[off]);
+    else if (p.act == ACT_GELU_SAVE_GRAD) { float gr; v = gelu_erf_both(v, gr); if (p.aux_out) p.aux_out[off] = gr; }
+    else if (p.act == ACT_MUL_AUX) v *= p.aux_in[off];
+    if (p.accumulate) v += p.C[off];
+    p.C[off] = v;
 }
 
 template <int BM, int BN, int BK = 16>
@@ -194,6 +199,17 @@ int dispatch(const GemmP& p, dim3 grid, cudaStream_t st) {
 
 int choose_splitk(int M, int N, int K) {
     const int tiles = cdiv(M, 128) * cdiv(N, N <= 64 ? 64 : 128);
+    if (tiles < 96 && K <= 4096) {
+        // the [B, d]-sized problems of the last-row path run on 32 x 64 tiles (launch_gemm's `small`): one CTA per SM walks
+        // its k-tiles as a chain of load -> store -> barrier -> compute phases with nothing to overlap them (17 - 50 us for
+        // 0.07 - 0.27 GFLOP).  Splitting K down to 64 per CTA puts 2 - 4 independent CTAs on every SM instead.
+        const int t32 = cdiv(M, 32) * cdiv(N, 64);
+        int s = (148 * 2 + t32 - 1) / t32;
+        const int maxs = K / 64 > 1 ? K / 64 : 1;
+        if (s > maxs) s = maxs;
+        if (s > 1) { const int kc = ((K + s - 1) / s + 63) / 64 * 64; s = (K + kc - 1) / kc; }      // no empty split
+        return s < 1 ? 1 : s;
+    }
     int s = (148 * 2 + tiles - 1) / tiles;
     const int maxs = (K + 255) / 256;      // at least 256 of K per split
     if (s > maxs) s = maxs;
@@ -204,8 +220,7 @@ int choose_splitk(int M, int N, int K) {
 
 int launch_gemm(const GemmP& p, cudaStream_t st) {
     if (p.M <= 0 || p.N <= 0 || p.batch <= 0) return 0;
-    BSA_REQUIRE(p.splitk >= 1 && (p.splitk == 1 || (p.batch == 1 && p.partial && !p.bias && p.act == ACT_NONE)),
-                "launch_gemm: invalid split-K configuration");
+    BSA_REQUIRE(p.splitk >= 1 && (p.splitk == 1 || (p.batch == 1 && p.partial)), "launch_gemm: invalid split-K configuration");
     BSA_REQUIRE(p.inner >= 1 && p.batch % p.inner == 0, "launch_gemm: batch %% inner != 0");
     int BN = p.N <= 64 ? 64 : 128;
     const int nz = p.splitk > 1 ? p.splitk : p.batch;
@@ -217,14 +232,13 @@ int launch_gemm(const GemmP& p, cudaStream_t st) {
     {
         ProfScope prof(PROF_GEMM_SIMT, st, 2.0 * p.M * p.N * (double)p.K * p.batch);
         const int kspan = p.splitk > 1 ? (p.K + p.splitk - 1) / p.splitk : p.K;
-        rc = small ? (kspan >= 128 ? dispatch<32, 64, 64>(p, grid, st) : dispatch<32, 64>(p, grid, st))
+        rc = small ? (kspan >= 64 ? dispatch<32, 64, 64>(p, grid, st) : dispatch<32, 64>(p, grid, st))
                    : BN == 64 ? dispatch<128, 64>(p, grid, st) : dispatch<128, 128>(p, grid, st);
     }
     if (rc) return rc;
     if (p.splitk > 1) {
         const long long MN = (long long)p.M * p.N;
-        splitk_reduce_kernel<<<cdiv(MN, 256), 256, 0, st>>>(p.partial, p.C, MN, p.N, p.ldc, p.splitk, p.alpha,
-                                                           p.accumulate);
+        splitk_reduce_kernel<<<cdiv(MN, 256), 256, 0, st>>>(p, MN);
         BSA_LAUNCH_CHECK();
     }
     return 0;

@@ -1,5 +1,6 @@
 // Row-wise kernels (one warp per row of d or L values, values held in registers).
 #include "rowwise.cuh"
+#include "umma_engine.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cmath>
@@ -623,16 +624,18 @@ int embed_ln_dropout_bwd(const float* dout, const long long* ids, const float* E
 
 int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, const float* beta, float* out,
                     float* z_save, float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b,
-                    long long M, int d, Dropout dr, cudaStream_t st) {
+                    long long M, int d, Dropout dr, cudaStream_t st, float* out_hi, float* out_lo) {
     if (M == 0) return 0;
-    ProfScope prof(PROF_RESID_LN_FWD, st, 4.0 * M * d * (3.0 + (z_save ? 1.0 : 0.0) + (blend_with ? 1.0 : 0.0)));
-    if (vec_ok(d, tmp, resid, gamma, beta, out, z_save, blend_with))
-        return residual_ln_fwd_vec(tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr,
-                                   row_grid(M), st);
-    BSA_DISPATCH_VPL(d, (residual_ln_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(
-                            tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr)));
-    BSA_LAUNCH_CHECK();
-    return 0;
+    {
+        ProfScope prof(PROF_RESID_LN_FWD, st, 4.0 * M * d * (3.0 + (z_save ? 1.0 : 0.0) + (blend_with ? 1.0 : 0.0)));      // the optional split pair is not credited
+        if (vec_ok(d, tmp, resid, gamma, beta, out, z_save, blend_with) && vec_ok(d, out_hi, out_lo))
+            return residual_ln_fwd_vec(tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr,
+                                       row_grid(M), st, out_hi, out_lo);
+        BSA_DISPATCH_VPL(d, (residual_ln_fwd_kernel<VPL><<<row_grid(M), WARPS * 32, 0, st>>>(
+                                tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr)));
+        BSA_LAUNCH_CHECK();
+    }
+    return out_hi ? umma_split(out, out_hi, out_lo, M * d, st) : 0;
 }
 
 int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,

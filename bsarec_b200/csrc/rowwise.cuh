@@ -19,7 +19,8 @@ int rowwise_partial_blocks(long long rows);   // how many partial rows the *_bwd
 // ---- z = drop(tmp) + resid ; ln = LN(z) ; out = blend_a*blend_with + blend_b*ln  (blend optional)
 int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, const float* beta, float* out,
                     float* z_save, float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b,
-                    long long M, int d, Dropout dr, cudaStream_t st);
+                    long long M, int d, Dropout dr, cudaStream_t st, float* out_hi = nullptr, float* out_lo = nullptr);
+// out_hi / out_lo (optional): `out` also leaves as its split-TF32 pair (the A operand of the tcgen05 linear that follows)
 // LN backward: upstream = dy * dy_scale.  dz (grad wrt LN input) always written; ddrop = dz * dropout
 // multiplier (grad wrt the pre-dropout tensor) written when ddrop != nullptr.
 int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
@@ -86,7 +87,7 @@ int embed_bwd_vec(const float* dout, const long long* ids, const float* E, const
                   Dropout dr, int grid, cudaStream_t st);
 int residual_ln_fwd_vec(const float* tmp, const float* resid, const float* gamma, const float* beta, float* out, float* z_save,
                         float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b, long long M, int d,
-                        Dropout dr, int grid, cudaStream_t st);
+                        Dropout dr, int grid, cudaStream_t st, float* y_hi = nullptr, float* y_lo = nullptr);
 int ln_bwd_vec(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,
                float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, float* t_hi,
                float* t_lo, float* pcol, cudaStream_t st);

@@ -173,7 +173,8 @@ __global__ void __launch_bounds__(WARPS * 32, NV <= 2 ? 4 : 2)
 residual_ln_fwd_vec_kernel(const float* __restrict__ tmp, const float* __restrict__ resid, const float* __restrict__ gamma,
                            const float* __restrict__ beta, float* __restrict__ out, float* __restrict__ z_save,
                            float* __restrict__ mean_o, float* __restrict__ rstd_o, const float* __restrict__ blend_with,
-                           float blend_a, float blend_b, long long M, int d, Dropout dr) {
+                           float blend_a, float blend_b, long long M, int d, Dropout dr, float* __restrict__ y_hi,
+                           float* __restrict__ y_lo) {
     const int lane = threadIdx.x & 31;
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
         float4 v[NV], bw[NV];
@@ -198,6 +199,12 @@ residual_ln_fwd_vec_kernel(const float* __restrict__ tmp, const float* __restric
                 float4 y = ldg4(gamma + c) * (rstd * (v[i] - f4(mean))) + ldg4(beta + c);
                 if (blend_with) y = blend_a * bw[i] + blend_b * y;
                 st4(out + row * d + c, y);
+                if (y_hi) {          // the next tcgen05 linear's A operand: the split pair leaves here, no separate pass over `out`
+                    float4 h, l;
+                    split1(y.x, h.x, l.x); split1(y.y, h.y, l.y); split1(y.z, h.z, l.z); split1(y.w, h.w, l.w);
+                    st4(y_hi + row * d + c, h);
+                    st4(y_lo + row * d + c, l);
+                }
             }
         }
     }
@@ -470,9 +477,9 @@ int embed_bwd_vec(const float* dout, const long long* ids, const float* E, const
 
 int residual_ln_fwd_vec(const float* tmp, const float* resid, const float* gamma, const float* beta, float* out, float* z_save,
                         float* mean, float* rstd, const float* blend_with, float blend_a, float blend_b, long long M, int d,
-                        Dropout dr, int grid, cudaStream_t st) {
+                        Dropout dr, int grid, cudaStream_t st, float* y_hi, float* y_lo) {
     BSA_DISPATCH_NV(d, (residual_ln_fwd_vec_kernel<NV><<<grid, WARPS * 32, 0, st>>>(tmp, resid, gamma, beta, out, z_save, mean, rstd,
-                                                                                   blend_with, blend_a, blend_b, M, d, dr)));
+                                                                                   blend_with, blend_a, blend_b, M, d, dr, y_hi, y_lo)));
     BSA_LAUNCH_CHECK();
     return 0;
 }

@@ -35,6 +35,9 @@ struct Saved {              // layout of the per-layer saved-activation buffer
     // tcgen05 path: split-TF32 (hi, lo) copies of the four linear inputs, written once in forward and reused by the
     // weight-gradient GEMMs in backward
     float *x_hi, *x_lo, *ctx_hi, *ctx_lo, *y_hi, *y_lo, *h_hi, *h_lo;
+    // ... and of the six weight matrices, [wq | wk | wv | wo | w1 | w2] = 12 d^2 floats each: split by ONE launch at the top of
+    // the forward pass and read again by the backward pass (the weights do not change in between)
+    float *w_hi, *w_lo;
     bool fused;             // attention ran in the fused kernel: lse [B,H,L] is saved instead of P [B,H,L,L]
     size_t bytes;
 };
@@ -53,10 +56,11 @@ Saved carve_saved(void* p, const bsa_block_desc& c) {
     s.y = b.f(M * d);
     s.h_pre = b.f(M * 4 * d); s.h_act = b.f(M * 4 * d);
     s.z_o = b.f(M * d); s.mean_o = b.f(M); s.rstd_o = b.f(M);
-    s.x_hi = s.x_lo = s.ctx_hi = s.ctx_lo = s.y_hi = s.y_lo = s.h_hi = s.h_lo = nullptr;
+    s.x_hi = s.x_lo = s.ctx_hi = s.ctx_lo = s.y_hi = s.y_lo = s.h_hi = s.h_lo = s.w_hi = s.w_lo = nullptr;
     if (linear_impl() == 2) {
         s.x_hi = b.f(M * d); s.x_lo = b.f(M * d); s.ctx_hi = b.f(M * d); s.ctx_lo = b.f(M * d);
         s.y_hi = b.f(M * d); s.y_lo = b.f(M * d); s.h_hi = b.f(M * 4 * d); s.h_lo = b.f(M * 4 * d);
+        s.w_hi = b.f(12 * d * d); s.w_lo = b.f(12 * d * d);
     }
     s.bytes = b.off;
     return s;
@@ -135,17 +139,36 @@ size_t workspace_bytes(const bsa_block_desc& c) {
     return b.off + 8192;
 }
 
+// offsets (in units of d^2 floats) of the weight pairs inside Saved::w_hi / w_lo
+enum WeightSlot : int { W_Q = 0, W_K = 1, W_V = 2, W_O = 3, W_1 = 4, W_2 = 8 };
+
+// all six weight matrices of the block -> their split pairs in the saved buffer, one launch
+int split_block_weights(const Saved& s, const bsa_block_desc& c, const bsa_block_weights& w, cudaStream_t st) {
+    const long long dd = (long long)c.d * c.d;
+    const float* src[6]; float* hi[6]; float* lo[6]; long long n[6];
+    int k = 0;
+    auto add = [&](const float* W, int slot, long long cnt) {
+        if (!W) return;
+        src[k] = W; hi[k] = s.w_hi + slot * dd; lo[k] = s.w_lo + slot * dd; n[k] = cnt; ++k;
+    };
+    if (c.kind == 0) { add(w.wq, W_Q, dd); add(w.wk, W_K, dd); add(w.wv, W_V, dd); add(w.wo, W_O, dd); }
+    add(w.w1, W_1, 4 * dd); add(w.w2, W_2, 4 * dd);
+    return umma_split_multi(k, src, hi, lo, n, st);
+}
+
 // x [M, K] @ W[N, K]^T + bias -> out [M, N]      (nn.Linear forward); out_hi/out_lo: also emit out's split pair
+// pw_hi / pw_lo (tcgen05 path, optional): W's split pair made earlier (split_block_weights) — no split launch here
 int linear_fwd(const Lin& ln, const Act& a, const float* W, const float* bias, float* out, long long M, int N, int K, int act,
-               float* aux_out, float* out_hi, float* out_lo, cudaStream_t st) {
+               float* aux_out, float* out_hi, float* out_lo, cudaStream_t st, const float* pw_hi = nullptr, const float* pw_lo = nullptr) {
     if (ln.umma) {
-        int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
+        int rc = 0;
+        if (!pw_hi) { rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st); pw_hi = ln.w_hi; pw_lo = ln.w_lo; }
         if (rc) return rc;
         // when the epilogue emits the result's split pair, that pair is all the tcgen05 path reads afterwards: no fp32 copy
         if (ln.inference) { aux_out = nullptr; if (act == ACT_GELU_SAVE_GRAD) act = ACT_GELU_SAVE_PRE; }    // nothing kept: plain GELU
         const float *ah_, *al_;
         if ((rc = act_pair(ln, a, M * K, ln.s1_hi, ln.s1_lo, ah_, al_, st))) return rc;
-        return umma_gemm_ps((int)M, N, K, ah_, al_, M, K, K, false, ln.w_hi, ln.w_lo, N, K, K, false, out_hi ? nullptr : out, N, bias,
+        return umma_gemm_ps((int)M, N, K, ah_, al_, M, K, K, false, pw_hi, pw_lo, N, K, K, false, out_hi ? nullptr : out, N, bias,
                             act, aux_out, nullptr, 1.f, 0, out_hi, out_lo, nullptr, 0, st);
     }
     GemmP p;
@@ -163,26 +186,24 @@ bool qkv_fuse_enabled() {
     return on;
 }
 int linear_fwd_qkv(const Lin& ln, const Act& a, const bsa_block_weights& w, float* q, long long seg_stride, long long M, int d,
-                   cudaStream_t st) {
-    const long long dd = (long long)d * d;
-    int rc;
-    if ((rc = umma_split(w.wq, ln.w_hi, ln.w_lo, dd, st))) return rc;
-    if ((rc = umma_split(w.wk, ln.w_hi + dd, ln.w_lo + dd, dd, st))) return rc;
-    if ((rc = umma_split(w.wv, ln.w_hi + 2 * dd, ln.w_lo + 2 * dd, dd, st))) return rc;
-    return umma_gemm_ps((int)M, 3 * d, d, a.hi, a.lo, M, d, d, false, ln.w_hi, ln.w_lo, 3 * d, d, d, false, q, d, w.bq, ACT_NONE,
+                   cudaStream_t st, const float* pw_hi, const float* pw_lo) {      // pw: the [wq | wk | wv] pair, [3d, d]
+    (void)ln;
+    return umma_gemm_ps((int)M, 3 * d, d, a.hi, a.lo, M, d, d, false, pw_hi, pw_lo, 3 * d, d, d, false, q, d, w.bq, ACT_NONE,
                         nullptr, nullptr, 1.f, 0, nullptr, nullptr, nullptr, 0, st, nullptr, d, seg_stride, w.bk, w.bv);
 }
 
 // dx [M, K] (+)= dy [M, N] @ W[N, K]              (nn.Linear input gradient)
 int linear_bwd_input(const Lin& ln, const Act& dy, const float* W, float* dx, long long M, int N, int K, int accumulate, int act,
-                     const float* aux_in, float* out_hi, float* out_lo, cudaStream_t st, float* colpart = nullptr) {
+                     const float* aux_in, float* out_hi, float* out_lo, cudaStream_t st, float* colpart = nullptr,
+                     const float* pw_hi = nullptr, const float* pw_lo = nullptr) {
     if (ln.umma) {
-        int rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st);
+        int rc = 0;
+        if (!pw_hi) { rc = umma_split(W, ln.w_hi, ln.w_lo, (long long)N * K, st); pw_hi = ln.w_hi; pw_lo = ln.w_lo; }
         if (rc) return rc;
         // colpart (tcgen05 path only): the epilogue also leaves column sums of dx per 32-row group, [4 * ceil(M / 128), K]
         const float *gh_, *gl_;
         if ((rc = act_pair(ln, dy, M * N, ln.s1_hi, ln.s1_lo, gh_, gl_, st))) return rc;
-        return umma_gemm_ps((int)M, K, N, gh_, gl_, M, N, N, false, ln.w_hi, ln.w_lo, N, K, K, true, dx, K, nullptr, act, nullptr,
+        return umma_gemm_ps((int)M, K, N, gh_, gl_, M, N, N, false, pw_hi, pw_lo, N, K, K, true, dx, K, nullptr, act, nullptr,
                             aux_in, 1.f, accumulate, out_hi, out_lo, nullptr, 0, st, colpart);
     }
     GemmP p;
@@ -260,6 +281,10 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     // inference (bsa_block_desc::inference): the LayerNorm inputs / statistics and the GELU pre-activation are not written
     const bool inf = c.inference != 0;
     lin.inference = inf && lin.umma;
+    const long long dd = (long long)d * d;
+    if (lin.umma && (rc = split_block_weights(s, c, w, st))) return rc;
+    auto wh = [&](int slot) -> const float* { return lin.umma ? s.w_hi + slot * dd : nullptr; };
+    auto wl = [&](int slot) -> const float* { return lin.umma ? s.w_lo + slot * dd : nullptr; };
     Act ax, actx, ay, ah;
     if (c.kind == 1) {
         // FMLPRecBlock (fmlprec.py:84-118): y = LN(drop(circular_conv(x, K)) + x) — K [L,d] arrives as `sqrt_beta` — then the
@@ -273,11 +298,11 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     // attention branch
     if ((rc = split_act(lin, x, s.x_hi, s.x_lo, M * d, ax, st))) return rc;        // one split feeds q, k, v (and dW in backward)
     if (lin.umma && qkv_fuse_enabled() && d % 32 == 0 && (s.k - s.q) == (s.v - s.k)) {
-        if ((rc = linear_fwd_qkv(lin, ax, w, s.q, s.k - s.q, M, d, st))) return rc;
+        if ((rc = linear_fwd_qkv(lin, ax, w, s.q, s.k - s.q, M, d, st, wh(W_Q), wl(W_Q)))) return rc;
     } else {
-        if ((rc = linear_fwd(lin, ax, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
-        if ((rc = linear_fwd(lin, ax, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
-        if ((rc = linear_fwd(lin, ax, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+        if ((rc = linear_fwd(lin, ax, w.wq, w.bq, s.q, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_Q), wl(W_Q)))) return rc;
+        if ((rc = linear_fwd(lin, ax, w.wk, w.bk, s.k, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_K), wl(W_K)))) return rc;
+        if ((rc = linear_fwd(lin, ax, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_V), wl(W_V)))) return rc;
     }
     if (s.fused) {
         if ((rc = attn_fwd(s.q, s.k, s.v, ids, s.ctx, s.lse, B, H, L, d, dr_p, st))) return rc;
@@ -302,7 +327,7 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         }
     }
     if ((rc = split_act(lin, s.ctx, s.ctx_hi, s.ctx_lo, M * d, actx, st))) return rc;
-    if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_O), wl(W_O)))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
     // (tcgen05 path) y also leaves the LayerNorm kernel as the split pair dense_1 reads: no separate pass over y
     if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, inf ? nullptr : s.z_a, inf ? nullptr : s.mean_a, inf ? nullptr : s.rstd_a,
@@ -313,9 +338,9 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if (c.kind == 1 && (rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
     // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
     // (h_pre holds gelu'(pre-activation): the backward's dX epilogue multiplies by it instead of evaluating erf + exp again)
-    if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_GRAD, s.h_pre, s.h_hi, s.h_lo, st))) return rc;
+    if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_GRAD, s.h_pre, s.h_hi, s.h_lo, st, wh(W_1), wl(W_1)))) return rc;
     ah.x = s.h_act; ah.hi = s.h_hi; ah.lo = s.h_lo;
-    if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, M, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_2), wl(W_2)))) return rc;
     if ((rc = residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, x_out, inf ? nullptr : s.z_o, inf ? nullptr : s.mean_o,
                               inf ? nullptr : s.rstd_o, nullptr, 0.f, 0.f, M, d, dr_o, st))) return rc;
     return 0;
@@ -366,6 +391,10 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const int r = filter_rank(L, c.kept_bins);
     const float inv_sqrt_dh = 1.0f / sqrtf((float)dh);
     int rc, nblk = 0;
+    // the weight pairs the forward pass left in the saved buffer (split_block_weights)
+    const long long dsq = (long long)d * d;
+    auto wh = [&](int slot) -> const float* { return lin.umma ? s.w_hi + slot * dsq : nullptr; };
+    auto wl = [&](int slot) -> const float* { return lin.umma ? s.w_lo + slot * dsq : nullptr; };
 
     // ---- feed-forward: x_out = LN(drop(tmp2) + y)
     // on the tcgen05 path the LN backward emits the gradient w.r.t. dense_2's output directly as a split-TF32 pair plus its
@@ -389,14 +418,14 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if (lin.umma) {
         // dh leaves the GEMM only as its split pair (all dW1 / dX read) plus per-32-row column sums for db1: the fp32 copy
         // and the pass that summed it are gone; the [M,4d] dh_ buffer holds the [M/32, 4d] partial sums instead
-        if ((rc = linear_bwd_input(lin, ag, w.w2, nullptr, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st, dh_))) return rc;
+        if ((rc = linear_bwd_input(lin, ag, w.w2, nullptr, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st, dh_, wh(W_2), wl(W_2)))) return rc;
         if ((rc = reduce_batch_add(rb, dh_, 4 * (int)((M + 127) / 128), 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
         if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, M, 4 * d, d, part_sk, part_cs, st))) return rc;
     } else {
         if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st))) return rc;
         if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
     }
-    if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
+    if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, M, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st, nullptr, wh(W_1), wl(W_1)))) return rc;   // dyb = dL/dy
 
     if (c.kind == 1) {
         // FMLPRecBlock: y = LN(drop(conv(x, K)) + x).  dx = d(LN input) + conv^T(K, d conv); dK = sum_b corr(d conv_b, x_b)
@@ -427,7 +456,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         if ((rc = split_act(lin, t1, g_hi, g_lo, M * d, ag, st))) return rc;
     }
     if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, fuse_a ? nullptr : g.bo, M, d, d, part_sk, part_cs, st))) return rc;
-    if ((rc = linear_bwd_input(lin, ag, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+    if ((rc = linear_bwd_input(lin, ag, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st, nullptr, wh(W_O), wl(W_O)))) return rc;
     if (s.fused) {
         // dP (workspace, unused by this path) doubles as the [B,H,L] delta scratch
         if ((rc = attn_bwd(s.q, s.k, s.v, ids, s.ctx, s.lse, dctx, dq, dk, dv, dP, B, H, L, d, dr_p, st))) return rc;
@@ -482,16 +511,21 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         const bool pack = lin.umma && qkv_fuse_enabled() && d % 32 == 0 && umma_split_colsum_ok(d, dq, dh_hi, dh_lo) &&
                           umma_split_colsum_ok(d, dk, dh_hi + d, dh_lo + d) && umma_split_colsum_ok(d, dv, dh_hi + 2 * d, dh_lo + 2 * d) &&
                           umma_split_colsum_rows(M) <= colsum_partial_rows(M);
+        const bool pack_dw = pack && ax.hi && umma_gemm_splits(3 * d, d, (int)M) > 1 &&
+                             (size_t)umma_gemm_splits(3 * d, d, (int)M) * 3 * d * d * 4 <= lin.partial_bytes;
         if (pack) {
-            const long long dd = (long long)d * d;
             for (int i = 0; i < 3; ++i) {
                 float *ph = dh_hi + (long long)i * d, *pl = dh_lo + (long long)i * d;
                 if ((rc = umma_split_colsum(grads3[i], ph, pl, M, d, part_qkv[i], st, 3 * d))) return rc;
                 if ((rc = reduce_batch_add(rb, part_qkv[i], umma_split_colsum_rows(M), d, dbs3[i], nullptr, 1.f, 0, st))) return rc;
-                if ((rc = linear_bwd_weight(lin, Act{grads3[i], ph, pl}, ax, dws3[i], nullptr, M, d, d, part_sk, part_cs, st, 3 * d))) return rc;
-                if ((rc = umma_split(ws3[i], lin.w_hi + i * dd, lin.w_lo + i * dd, dd, st))) return rc;
+                if (!pack_dw && (rc = linear_bwd_weight(lin, Act{grads3[i], ph, pl}, ax, dws3[i], nullptr, M, d, d, part_sk, part_cs, st, 3 * d))) return rc;
             }
-            if ((rc = umma_gemm_ps((int)M, d, 3 * d, dh_hi, dh_lo, M, 3 * d, 3 * d, false, lin.w_hi, lin.w_lo, 3 * d, d, d, true, dx, d,
+            // [dWq; dWk; dWv] = [dq | dk | dv]^T x: one split-K GEMM over the packed pair (x's pair read once instead of three
+            // times), its reduction writes the three [d, d] gradient tensors
+            if (pack_dw && (rc = umma_gemm_ps(3 * d, d, (int)M, dh_hi, dh_lo, M, 3 * d, 3 * d, true, ax.hi, ax.lo, M, d, d, true, g.wq, d,
+                                              nullptr, 0, nullptr, nullptr, 1.f, 0, nullptr, nullptr, lin.partial, lin.partial_bytes, st,
+                                              nullptr, 0, 0, nullptr, nullptr, d, g.wk, g.wv))) return rc;
+            if ((rc = umma_gemm_ps((int)M, d, 3 * d, dh_hi, dh_lo, M, 3 * d, 3 * d, false, s.w_hi, s.w_lo, 3 * d, d, d, true, dx, d,
                                    nullptr, ACT_NONE, nullptr, nullptr, 1.f, 1, nullptr, nullptr, nullptr, 0, st))) return rc;
         } else
         for (int i = 0; i < 3; ++i) {
@@ -505,7 +539,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
                 if ((rc = split_act(lin, grads3[i], g_hi, g_lo, M * d, ag, st))) return rc;
                 if ((rc = linear_bwd_weight(lin, ag, ax, dws3[i], dbs3[i], M, d, d, part_sk, part_cs, st))) return rc;
             }
-            if ((rc = linear_bwd_input(lin, ag, ws3[i], dx, M, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
+            if ((rc = linear_bwd_input(lin, ag, ws3[i], dx, M, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st, nullptr, wh(W_Q + i), wl(W_Q + i)))) return rc;
         }
     }
 

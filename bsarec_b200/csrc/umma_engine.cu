@@ -33,6 +33,26 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
     if (t < n) split_tf32(x[t], hi[t], lo[t]);
 }
 
+// up to SplitMulti::MAXT tensors in one launch (blockIdx.y = tensor): the block's weight matrices are split together
+struct SplitMultiP { const float* x[8]; float* hi[8]; float* lo[8]; long long n[8]; };
+__global__ void split_tf32_multi_kernel(const __grid_constant__ SplitMultiP t) {
+    const int k = blockIdx.y;
+    const float* __restrict__ x = t.x[k];
+    float* __restrict__ hi = t.hi[k];
+    float* __restrict__ lo = t.lo[k];
+    const long long n = t.n[k], n4 = n >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = reinterpret_cast<const float4*>(x)[i];
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        reinterpret_cast<float4*>(hi)[i] = h;
+        reinterpret_cast<float4*>(lo)[i] = l;
+    }
+    const long long e = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < n) split_tf32(x[e], hi[e], lo[e]);
+}
+
 // split + column sums of a [M, N] activation gradient in one pass (N / 4 threads per row, 128 rows per block):
 // part[blockIdx.x][N] = sum over the block's rows, reduced afterwards by reduce_partials -> the bias gradient
 constexpr int SPLIT_CS_ROWS = 128;
@@ -520,16 +540,26 @@ int launch_major(const GemmCore& g, const typename Epi::Params& ep, bool a_mn, b
     return launch<BN, STAGES, true, true, Epi>(g, ep, grid, st);
 }
 
+// seg_rows > 0: rows [s * seg_rows, (s + 1) * seg_rows) of the result are the separate tensor C / C1 / C2 (pitch ldc) — the
+// three weight gradients of the q / k / v projections leave one GEMM
 __global__ void splitk_reduce_kernel2(const float* __restrict__ part, float* __restrict__ C, long long MN, int N, long long ldc,
-                                      int splits, float alpha, int accumulate) {
+                                      int splits, float alpha, int accumulate, int seg_rows, float* __restrict__ C1,
+                                      float* __restrict__ C2) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= MN) return;
     float s = 0.f;
     for (int k = 0; k < splits; ++k) s += part[(long long)k * MN + i];
-    const long long m = i / N, n = i - m * N;
+    long long m = i / N;
+    const long long n = i - m * N;
+    float* dst = C;
+    if (seg_rows) {
+        const int seg = (int)(m / seg_rows);
+        m -= (long long)seg * seg_rows;
+        dst = seg == 0 ? C : (seg == 1 ? C1 : C2);
+    }
     float v = alpha * s;
-    if (accumulate) v += C[m * ldc + n];
-    C[m * ldc + n] = v;
+    if (accumulate) v += dst[m * ldc + n];
+    dst[m * ldc + n] = v;
 }
 
 int do_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st) {
@@ -555,6 +585,29 @@ size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, in
 
 int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st) { return do_split(x, hi, lo, n, st); }
 
+int umma_split_multi(int count, const float* const* x, float* const* hi, float* const* lo, const long long* n, cudaStream_t st) {
+    BSA_REQUIRE(count >= 0 && count <= 8, "umma_split_multi: at most 8 tensors");
+    if (count == 0) return 0;
+    SplitMultiP t;
+    long long nmax = 0;
+    for (int i = 0; i < 8; ++i) {
+        const int j = i < count ? i : 0;
+        t.x[i] = x[j]; t.hi[i] = hi[j]; t.lo[i] = lo[j]; t.n[i] = i < count ? n[j] : 0;
+        if (i < count) {
+            BSA_REQUIRE(((reinterpret_cast<uintptr_t>(x[j]) | reinterpret_cast<uintptr_t>(hi[j]) | reinterpret_cast<uintptr_t>(lo[j])) & 15) == 0,
+                        "umma_split_multi: tensors must be 16-byte aligned");
+            if (n[j] > nmax) nmax = n[j];
+        }
+    }
+    if (nmax == 0) return 0;
+    long long bx = (nmax / 4 + 255) / 256;
+    if (bx > 128) bx = 128;
+    if (bx < 1) bx = 1;
+    split_tf32_multi_kernel<<<dim3((unsigned)bx, (unsigned)count), 256, 0, st>>>(t);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+
 bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* lo) {
     const int tpr = N >> 2;
     return (N & 3) == 0 && tpr >= 1 && tpr <= 256 && 256 % tpr == 0 &&
@@ -574,14 +627,29 @@ int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, 
 
 size_t umma_gemm_partial_bytes(int M, int N) { return al((size_t)64 * M * N * 4) + 1024; }
 
+// K-splits a plain-epilogue umma_gemm_ps launch uses when it is given split-K scratch (1 = none)
+int umma_gemm_splits(int M, int N, int K) {
+    const int BN = N > 128 ? 256 : 128;
+    const int tiles = cdiv(M, BM) * cdiv(N, BN);
+    if (tiles >= num_sms()) return 1;
+    int splits = num_sms() / tiles;
+    const int kb = cdiv(K, BK);
+    if (splits > kb / 4) splits = kb / 4;
+    if (splits > 64) splits = 64;
+    return splits < 1 ? 1 : splits;
+}
+
 // Operands already split: a = (a_hi, a_lo), b = (b_hi, b_lo).  `partial` backs split-K (may be null: no split-K).
 int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long long a_rows, long long a_cols,
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,
                  const float* aux_in, float alpha, int accumulate, float* out_hi, float* out_lo, float* partial,
                  size_t partial_bytes, cudaStream_t st, float* colpart, int seg_cols, long long seg_stride, const float* bias1,
-                 const float* bias2) {
+                 const float* bias2, int seg_rows, float* C1, float* C2) {
     BSA_REQUIRE(M > 0 && N > 0 && K > 0, "umma_gemm: empty problem");
+    BSA_REQUIRE(!seg_rows || (umma_gemm_splits(M, N, K) > 1 && partial && C && C1 && C2 && !bias && act == 0 && !out_hi && !colpart &&
+                              M % seg_rows == 0 && M / seg_rows == 3),
+                "umma_gemm: row-segmented output needs the split-K path (3 segments, plain epilogue)");
     if (seg_cols) {
         BSA_REQUIRE(C && act == 0 && !accumulate && !colpart && !out_hi && seg_cols % 32 == 0 && N % seg_cols == 0 &&
                     N / seg_cols <= 3, "umma_gemm: segmented output needs a plain epilogue and segments of a multiple of 32 columns");
@@ -594,19 +662,13 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     int rc;
     Operand oa{a_hi, a_lo, a_rows, a_cols, lda, a_mn}, ob{b_hi, b_lo, b_rows, b_cols, ldb, b_mn};
     const int BN = N > 128 ? 256 : 128;
-    const int tiles = cdiv(M, BM) * cdiv(N, BN);
     int splits = 1;
-    if (tiles < num_sms() && !bias && act == 0 && !out_hi && partial) {
-        splits = num_sms() / tiles;
-        const int kb = cdiv(K, BK);
-        if (splits > kb / 4) splits = kb / 4;
-        if (splits > 64) splits = 64;
-        if (splits < 1) splits = 1;
-    }
+    if (!bias && act == 0 && !out_hi && partial) splits = umma_gemm_splits(M, N, K);
     GemmCore g;
     if ((rc = make_core(g, M, N, K, oa, ob, BN, SCHED_N_FASTEST, splits))) return rc;
     StoreParams ep{C, ldc, bias, act, aux_out, aux_in, alpha, accumulate, nullptr, out_hi, out_lo, 0, colpart};
     ep.seg_cols = seg_cols; ep.seg_stride = seg_stride; ep.bias1 = bias1; ep.bias2 = bias2;
+    BSA_REQUIRE(!seg_rows || g.splits > 1, "umma_gemm: row-segmented output needs more than one K-split");
     if (g.splits > 1) {
         BSA_REQUIRE((size_t)g.splits * M * N * 4 <= partial_bytes, "umma_gemm: workspace too small for split-K");
         ep.partial = partial;
@@ -626,7 +688,7 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     if (rc) return rc;
     if (g.splits > 1) {
         const long long MN = (long long)M * N;
-        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(partial, C, MN, N, ldc, g.splits, alpha, accumulate);
+        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(partial, C, MN, N, ldc, g.splits, alpha, accumulate, seg_rows, C1, C2);
         BSA_LAUNCH_CHECK();
     }
     return 0;
@@ -868,7 +930,7 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
         ce_bwd_logits_kernel<true><<<n_tiles < num_sms() ? n_tiles : num_sms(), CBL_THREADS, CBL_SMEM, st>>>(ip);
         BSA_LAUNCH_CHECK();
         const long long MN = (long long)B * d;
-        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, nstrips, 1.f, 0);
+        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, nstrips, 1.f, 0, 0, nullptr, nullptr);
         BSA_LAUNCH_CHECK();
         ce_onehot_fix_ds_kernel<<<B, 256, 0, st>>>(ds, E, answers, d_loss, B, d, N);
         BSA_LAUNCH_CHECK();
@@ -954,7 +1016,7 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
     }
     {
         const long long MN = (long long)B * d;
-        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, used_splits, 1.f, 0);
+        splitk_reduce_kernel2<<<cdiv(MN, 256), 256, 0, st>>>(w.partial, ds, MN, d, d, used_splits, 1.f, 0, 0, nullptr, nullptr);
         BSA_LAUNCH_CHECK();
     }
     return 0;

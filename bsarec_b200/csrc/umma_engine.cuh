@@ -30,6 +30,8 @@ int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a
 // the same with operands supplied as split-TF32 (hi, lo) pairs (produced once by umma_split or by a producer
 // epilogue and reused by several GEMMs); out_hi/out_lo (optional) also receive the result as a split pair.
 int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st);
+// the same for up to 8 tensors in one launch (16-byte aligned)
+int umma_split_multi(int count, const float* const* x, float* const* hi, float* const* lo, const long long* n, cudaStream_t st);
 size_t umma_gemm_partial_bytes(int M, int N);
 // One pass: split x [M, N] into (hi, lo) and leave per-128-row column sums in part [umma_split_colsum_rows(M), N]
 // (reduce_partials turns them into the bias gradient of the linear whose output gradient x is).
@@ -44,6 +46,10 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
                  size_t partial_bytes, cudaStream_t st, float* colpart = nullptr,
                  // segmented output: columns [s * seg_cols, (s + 1) * seg_cols) go to C + s * seg_stride (pitch ldc) with
                  // bias / bias1 / bias2 — q, k, v in one launch over one read of A (plain epilogue, seg_cols % 32 == 0)
-                 int seg_cols = 0, long long seg_stride = 0, const float* bias1 = nullptr, const float* bias2 = nullptr);
+                 int seg_cols = 0, long long seg_stride = 0, const float* bias1 = nullptr, const float* bias2 = nullptr,
+                 // row-segmented output (split-K launches only, see umma_gemm_splits): rows [s * seg_rows, (s + 1) * seg_rows)
+                 // go to C / C1 / C2 — the three weight gradients of q, k, v from one GEMM
+                 int seg_rows = 0, float* C1 = nullptr, float* C2 = nullptr);
+int umma_gemm_splits(int M, int N, int K);
 
 }  // namespace bsa

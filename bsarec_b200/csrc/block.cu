@@ -58,8 +58,8 @@ Saved carve_saved(void* p, const bsa_block_desc& c) {
     s.z_o = b.f(M * d); s.mean_o = b.f(M); s.rstd_o = b.f(M);
     s.x_hi = s.x_lo = s.ctx_hi = s.ctx_lo = s.y_hi = s.y_lo = s.h_hi = s.h_lo = s.w_hi = s.w_lo = nullptr;
     if (linear_impl() == 2) {
-        s.x_hi = b.f(M * d); s.x_lo = b.f(M * d); s.ctx_hi = b.f(M * d); s.ctx_lo = b.f(M * d);
-        s.y_hi = b.f(M * d); s.y_lo = b.f(M * d); s.h_hi = b.f(M * 4 * d); s.h_lo = b.f(M * 4 * d);
+        s.x_lo = b.f(M * d); s.ctx_lo = b.f(M * d);       // x, ctx, y are their own hi halves: only lo = t - truncate_tf32(t) is kept
+        s.y_lo = b.f(M * d); s.h_hi = b.f(M * 4 * d); s.h_lo = b.f(M * 4 * d);
         s.w_hi = b.f(12 * d * d); s.w_lo = b.f(12 * d * d);
     }
     s.bytes = b.off;
@@ -237,6 +237,13 @@ int linear_bwd_weight(const Lin& ln, const Act& dy, const Act& x, float* dW, flo
     return colsum(dy.x, M, N, part_cs, db, 0, st);
 }
 
+// the same with the tensor as its own hi half: only lo = x - truncate_tf32(x) is written (umma_split_lo)
+int split_act_lo(const Lin& ln, const float* x, float* lo, long long n, Act& out, cudaStream_t st) {
+    out.x = x; out.hi = ln.umma ? x : nullptr; out.lo = ln.umma ? lo : nullptr;
+    if (!ln.umma) return 0;
+    return umma_split_lo(x, lo, n, st);
+}
+
 // split an activation into (hi, lo) when the tcgen05 path will consume it
 int split_act(const Lin& ln, const float* x, float* hi, float* lo, long long n, Act& out, cudaStream_t st) {
     out.x = x; out.hi = hi; out.lo = lo;
@@ -296,7 +303,7 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, inf ? nullptr : s.z_f, inf ? nullptr : s.mean_f,
                             inf ? nullptr : s.rstd_f, B, L, d, r, dr_f, st))) return rc;
     // attention branch
-    if ((rc = split_act(lin, x, s.x_hi, s.x_lo, M * d, ax, st))) return rc;        // one split feeds q, k, v (and dW in backward)
+    if ((rc = split_act_lo(lin, x, s.x_lo, M * d, ax, st))) return rc;              // one split feeds q, k, v (and dW in backward)
     if (lin.umma && qkv_fuse_enabled() && d % 32 == 0 && (s.k - s.q) == (s.v - s.k)) {
         if ((rc = linear_fwd_qkv(lin, ax, w, s.q, s.k - s.q, M, d, st, wh(W_Q), wl(W_Q)))) return rc;
     } else {
@@ -326,16 +333,16 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
             if ((rc = launch_gemm(p, st))) return rc;
         }
     }
-    if ((rc = split_act(lin, s.ctx, s.ctx_hi, s.ctx_lo, M * d, actx, st))) return rc;
+    if ((rc = split_act_lo(lin, s.ctx, s.ctx_lo, M * d, actx, st))) return rc;
     if ((rc = linear_fwd(lin, actx, w.wo, w.bo, tmp, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_O), wl(W_O)))) return rc;
     // y = alpha*dsp + (1-alpha)*LN(drop(tmp) + x)
     // (tcgen05 path) y also leaves the LayerNorm kernel as the split pair dense_1 reads: no separate pass over y
     if ((rc = residual_ln_fwd(tmp, x, w.a_ln_w, w.a_ln_b, s.y, inf ? nullptr : s.z_a, inf ? nullptr : s.mean_a, inf ? nullptr : s.rstd_a,
-                              dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st, lin.umma ? s.y_hi : nullptr, lin.umma ? s.y_lo : nullptr))) return rc;
-    ay = Act{s.y, lin.umma ? s.y_hi : nullptr, lin.umma ? s.y_lo : nullptr};
+                              dsp, c.alpha, 1.0f - c.alpha, M, d, dr_a, st, nullptr, lin.umma ? s.y_lo : nullptr))) return rc;
+    ay = Act{s.y, lin.umma ? s.y : nullptr, lin.umma ? s.y_lo : nullptr};
     }   // kind == 0
     // feed-forward
-    if (c.kind == 1 && (rc = split_act(lin, s.y, s.y_hi, s.y_lo, M * d, ay, st))) return rc;
+    if (c.kind == 1 && (rc = split_act_lo(lin, s.y, s.y_lo, M * d, ay, st))) return rc;
     // dense_1's epilogue emits gelu(h) together with its split pair: dense_2 reads it without a separate pass
     // (h_pre holds gelu'(pre-activation): the backward's dX epilogue multiplies by it instead of evaluating erf + exp again)
     if ((rc = linear_fwd(lin, ay, w.w1, w.b1, s.h_act, M, 4 * d, d, ACT_GELU_SAVE_GRAD, s.h_pre, s.h_hi, s.h_lo, st, wh(W_1), wl(W_1)))) return rc;
@@ -382,7 +389,10 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     float* g_hi = b.f(M * d); float* g_lo = b.f(M * d);            // split pair of the current [M,d] upstream gradient
     float* dh_hi = b.f(M * 4 * d); float* dh_lo = b.f(M * 4 * d);  // split pair of dh [M,4d]
     BSA_REQUIRE(b.ok(), "bsa_block_bwd: workspace too small (%zu < %zu)", ws_bytes, b.off);
-    const Act ax{x, s.x_hi, s.x_lo}, actx{s.ctx, s.ctx_hi, s.ctx_lo}, ay{s.y, s.y_hi, s.y_lo}, ah{s.h_act, s.h_hi, s.h_lo};
+    // x, ctx and y are their own hi halves (split_act_lo in the forward pass)
+    const bool um = linear_impl() == 2;
+    const Act ax{x, um ? x : nullptr, s.x_lo}, actx{s.ctx, um ? s.ctx : nullptr, s.ctx_lo}, ay{s.y, um ? s.y : nullptr, s.y_lo},
+        ah{s.h_act, s.h_hi, s.h_lo};
     Act ag;
     const Dropout dr_f = make_dropout(c.seed, 1 + 4 * c.layer, c.p_hidden, c.training);
     const Dropout dr_p = make_dropout(c.seed, 2 + 4 * c.layer, c.p_attn, c.training);

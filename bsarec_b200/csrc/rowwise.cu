@@ -628,6 +628,7 @@ int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, co
     if (M == 0) return 0;
     {
         ProfScope prof(PROF_RESID_LN_FWD, st, 4.0 * M * d * (3.0 + (z_save ? 1.0 : 0.0) + (blend_with ? 1.0 : 0.0)));      // the optional split pair is not credited
+        // out_lo without out_hi: `out` is its own hi half, lo = out - truncate_tf32(out)
         if (vec_ok(d, tmp, resid, gamma, beta, out, z_save, blend_with) && vec_ok(d, out_hi, out_lo))
             return residual_ln_fwd_vec(tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr,
                                        row_grid(M), st, out_hi, out_lo);
@@ -635,7 +636,7 @@ int residual_ln_fwd(const float* tmp, const float* resid, const float* gamma, co
                                 tmp, resid, gamma, beta, out, z_save, mean, rstd, blend_with, blend_a, blend_b, M, d, dr)));
         BSA_LAUNCH_CHECK();
     }
-    return out_hi ? umma_split(out, out_hi, out_lo, M * d, st) : 0;
+    return out_hi ? umma_split(out, out_hi, out_lo, M * d, st) : (out_lo ? umma_split_lo(out, out_lo, M * d, st) : 0);
 }
 
 int ln_bwd(const float* dy, float dy_scale, const float* z, const float* mean, const float* rstd, const float* gamma,

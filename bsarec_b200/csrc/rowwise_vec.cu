@@ -46,6 +46,7 @@ __device__ __forceinline__ void split1(float x, float& hi, float& lo) {      // 
     hi = __uint_as_float(h);
     lo = x - hi;
 }
+__device__ __forceinline__ float lo_trunc(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 __device__ __forceinline__ unsigned long long row_index(const Dropout& dr, long long row, int d, int c) {
     return (unsigned long long)((row * dr.rmul + dr.radd) * d + c);
 }
@@ -199,11 +200,15 @@ residual_ln_fwd_vec_kernel(const float* __restrict__ tmp, const float* __restric
                 float4 y = ldg4(gamma + c) * (rstd * (v[i] - f4(mean))) + ldg4(beta + c);
                 if (blend_with) y = blend_a * bw[i] + blend_b * y;
                 st4(out + row * d + c, y);
-                if (y_hi) {          // the next tcgen05 linear's A operand: the split pair leaves here, no separate pass over `out`
-                    float4 h, l;
-                    split1(y.x, h.x, l.x); split1(y.y, h.y, l.y); split1(y.z, h.z, l.z); split1(y.w, h.w, l.w);
-                    st4(y_hi + row * d + c, h);
-                    st4(y_lo + row * d + c, l);
+                if (y_lo) {          // the next tcgen05 linear's A operand: `out` itself is the hi half (the MMA reads its upper
+                                     // 19 bits), lo = y - truncate(y) leaves here — no separate split pass over `out`
+                    st4(y_lo + row * d + c, make_float4(lo_trunc(y.x), lo_trunc(y.y), lo_trunc(y.z), lo_trunc(y.w)));
+                    if (y_hi) {      // a separate (rna hi, lo) pair was asked for
+                        float4 h, l;
+                        split1(y.x, h.x, l.x); split1(y.y, h.y, l.y); split1(y.z, h.z, l.z); split1(y.w, h.w, l.w);
+                        st4(y_hi + row * d + c, h);
+                        st4(y_lo + row * d + c, l);
+                    }
                 }
             }
         }

@@ -33,6 +33,24 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
     if (t < n) split_tf32(x[t], hi[t], lo[t]);
 }
 
+// "hi = the tensor itself": a kind::tf32 MMA reads only the upper 19 bits of each fp32 operand word, so the fp32 tensor
+// can serve as its own hi part when lo = x - truncate(x) (13 low mantissa bits cleared).  The split then writes 4 B per
+// element instead of 8 and the hi copy does not exist: item table of the cross-entropy (0.51 -> 0.32 ms at C3, same-box
+// A/B profiles/r3e_*), block inputs x / ctx / y.  Verified by the 1e-5 fp64 bars of test_fused_cross_entropy_fwd_bwd and
+// test_ce_backward_modes_agree (a rounding MMA input stage would fail them at 2^-11).  BSA_E_TRUNC=0 restores the (rna hi, lo)
+// pair for the item table.
+__global__ void split_lo_trunc_kernel(const float* __restrict__ x, float* __restrict__ lo, long long n) {
+    const long long n4 = n >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    auto lo1 = [](float v) { return v - __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); };
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = reinterpret_cast<const float4*>(x)[i];
+        reinterpret_cast<float4*>(lo)[i] = make_float4(lo1(v.x), lo1(v.y), lo1(v.z), lo1(v.w));
+    }
+    const long long t = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) lo[t] = lo1(x[t]);
+}
+
 // up to SplitMulti::MAXT tensors in one launch (blockIdx.y = tensor): the block's weight matrices are split together
 struct SplitMultiP { const float* x[8]; float* hi[8]; float* lo[8]; long long n[8]; };
 __global__ void split_tf32_multi_kernel(const __grid_constant__ SplitMultiP t) {
@@ -572,6 +590,20 @@ int do_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st)
     return 0;
 }
 
+int do_split_lo(const float* x, float* lo, long long n, cudaStream_t st) {
+    if (n == 0) return 0;
+    long long blocks = (n / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    split_lo_trunc_kernel<<<(int)blocks, 256, 0, st>>>(x, lo, n);
+    BSA_LAUNCH_CHECK();
+    return 0;
+}
+bool e_trunc() {
+    static const bool on = [] { const char* e = getenv("BSA_E_TRUNC"); return !(e && atoi(e) == 0); }();
+    return on;
+}
+
 inline size_t al(size_t x) { return (x + 1023) / 1024 * 1024; }
 
 }  // namespace
@@ -584,6 +616,8 @@ size_t umma_gemm_workspace_bytes(long long a_elems, long long b_elems, int M, in
 }
 
 int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st) { return do_split(x, hi, lo, n, st); }
+
+int umma_split_lo(const float* x, float* lo, long long n, cudaStream_t st) { return do_split_lo(x, lo, n, st); }
 
 int umma_split_multi(int count, const float* const* x, float* const* hi, float* const* lo, const long long* n, cudaStream_t st) {
     BSA_REQUIRE(count >= 0 && count <= 8, "umma_split_multi: at most 8 tensors");
@@ -865,7 +899,10 @@ int umma_ce_fwd(int B, int d, long long N, const float* s, const float* E, const
         if (!loss) loss = (float*)((char*)ws + w.bytes - 512);
     }
     if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
-    if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
+    if (e_trunc()) {
+        w.e_hi = const_cast<float*>(E);
+        if ((rc = do_split_lo(E, w.e_lo, N * d, st))) return rc;
+    } else if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
     Operand oa{w.s_hi, w.s_lo, B, d, d, false}, ob{w.e_hi, w.e_lo, N, d, d, false};
     GemmCore g;
     if ((rc = make_core(g, B, (int)N, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;
@@ -893,9 +930,11 @@ int umma_ce_bwd(int B, int d, long long N, const float* s, const float* E, const
     CeWs w = carve_ce(ws, B, d, N, true);
     BSA_REQUIRE(ws_bytes >= w.bytes, "bsa_ce_bwd: workspace too small (%zu < %zu)", ws_bytes, w.bytes);
     int rc;
+    if (e_trunc()) w.e_hi = const_cast<float*>(E);
     if (!reuse_split) {       // else: left there by umma_ce_fwd (same carve order for the forward-only part)
         if ((rc = do_split(s, w.s_hi, w.s_lo, (long long)B * d, st))) return rc;
-        if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
+        if (e_trunc()) { if ((rc = do_split_lo(E, w.e_lo, N * d, st))) return rc; }
+        else if ((rc = do_split(E, w.e_hi, w.e_lo, N * d, st))) return rc;
     }
     ProfScope prof(PROF_CE_BWD_UMMA, st, 4.0 * B * (double)N * d);
     if (g_ce_fused == 2 && reuse_split && w.logits) {

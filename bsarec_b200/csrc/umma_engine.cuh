@@ -30,6 +30,9 @@ int umma_gemm(int M, int N, int K, const float* A, long long a_rows, long long a
 // the same with operands supplied as split-TF32 (hi, lo) pairs (produced once by umma_split or by a producer
 // epilogue and reused by several GEMMs); out_hi/out_lo (optional) also receive the result as a split pair.
 int umma_split(const float* x, float* hi, float* lo, long long n, cudaStream_t st);
+// lo = x - truncate_tf32(x): with it the fp32 tensor x itself is the hi half of its pair (the tensor core reads only the upper
+// 19 bits of a tf32 operand word), so the split writes 4 B per element and no hi copy exists
+int umma_split_lo(const float* x, float* lo, long long n, cudaStream_t st);
 // the same for up to 8 tensors in one launch (16-byte aligned)
 int umma_split_multi(int count, const float* const* x, float* const* hi, float* const* lo, const long long* n, cudaStream_t st);
 size_t umma_gemm_partial_bytes(int M, int N);

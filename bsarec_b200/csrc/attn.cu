@@ -487,8 +487,9 @@ int launch_fwd(const float* q, const float* k, const float* v, const long long* 
 template <int DH>
 int launch_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
                const float* dctx, float* dq, float* dk, float* dv, float* delta, int B, int H, int L, int d, Dropout dr,
-               cudaStream_t st) {
+               cudaStream_t st, int ldo) {
     const size_t smem = attn_bwd_smem_bytes<DH>(L);
+    BSA_REQUIRE(ldo == 0 || ldo == d || attn_bwd_strided_ok(L, d, H), "attn_bwd: strided outputs need the tcgen05 backward");
     static size_t configured = 0;
     if (smem > configured) {
         BSA_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<DH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -503,9 +504,9 @@ int launch_bwd(const float* q, const float* k, const float* v, const long long* 
             const long long NK = (L + 15) / 16 * 16, bhl = (long long)B * H * L;
             float* pd = delta + (bhl + 63) / 64 * 64;
             float* ds = pd + bhl * NK;
-            int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, pd, ds, B, H, L, d, dr, st);
+            int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, pd, ds, B, H, L, d, dr, st, ldo);
             if (rc) return rc;
-            return attn_bwd_kv_umma(q, dctx, pd, ds, dk, dv, B, H, L, d, st);
+            return attn_bwd_kv_umma(q, dctx, pd, ds, dk, dv, B, H, L, d, st, ldo);
         }
         const int rc = attn_bwd_q_umma(q, k, v, ids, ctx, lse, dctx, dq, delta, nullptr, nullptr, B, H, L, d, dr, st);
         if (rc) return rc;
@@ -564,11 +565,15 @@ int attn_fwd(const float* q, const float* k, const float* v, const long long* id
 
 int attn_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
              const float* dctx, float* dq, float* dk, float* dv, float* delta, int B, int H, int L, int d, Dropout dr,
-             cudaStream_t st) {
+             cudaStream_t st, int ldo) {
     BSA_REQUIRE(attn_fused_supported(L, d, H), "attn_bwd: unsupported head size %d", H ? d / H : 0);
     if (B == 0) return 0;
-    if (d / H == 64) return launch_bwd<64>(q, k, v, ids, ctx, lse, dctx, dq, dk, dv, delta, B, H, L, d, dr, st);
-    return launch_bwd<32>(q, k, v, ids, ctx, lse, dctx, dq, dk, dv, delta, B, H, L, d, dr, st);
+    if (d / H == 64) return launch_bwd<64>(q, k, v, ids, ctx, lse, dctx, dq, dk, dv, delta, B, H, L, d, dr, st, ldo);
+    return launch_bwd<32>(q, k, v, ids, ctx, lse, dctx, dq, dk, dv, delta, B, H, L, d, dr, st, ldo);
+}
+
+bool attn_bwd_strided_ok(int L, int d, int H) {
+    return g_attn_bwd_umma >= 2 && g_attn_fwd_umma && attn_fused_supported(L, d, H) && attn_umma_supported(L, d, H);
 }
 
 }  // namespace bsa

@@ -26,17 +26,20 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
 extern int g_attn_bwd_umma;
 int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
                     const float* dctx, float* dq, float* delta, float* pd_out, float* ds_out, int B, int H, int L, int d,
-                    Dropout dr, cudaStream_t st);
+                    Dropout dr, cudaStream_t st, int ldo = 0);
 // Key-owner half on tcgen05 (attn_kv_umma.cu): dK, dV from the Pd / dS tiles [B*H*L, NK] the query-owner kernel left in HBM.
 // g_attn_bwd_umma = 2 (default) selects it; 1 keeps the key-owner launch on the mma.sync kernel (recomputation).
 int attn_bwd_kv_umma(const float* q, const float* dctx, const float* pd, const float* ds, float* dk, float* dv, int B, int H,
-                     int L, int d, cudaStream_t st);
+                     int L, int d, cudaStream_t st, int ldo = 0);
 // floats of scratch attn_bwd needs behind `delta` for (B, H, L, d) under the current settings
 long long attn_bwd_scratch_floats(int B, int H, int L, int d);
 
 // dq, dk, dv [B*L, d] are overwritten.  delta: [B, H, L] scratch (row sums of dctx * ctx).
 int attn_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
              const float* dctx, float* dq, float* dk, float* dv, float* delta, int B, int H, int L, int d, Dropout dr,
-             cudaStream_t st);
+             cudaStream_t st, int ldo = 0);
+// ldo (0 = d): row pitch of dq / dk / dv — 3d when the three are column windows of one packed [B*L, 3d] tensor; only the
+// two-kernel tcgen05 backward writes strided outputs: attn_bwd_strided_ok(L, d, H)
+bool attn_bwd_strided_ok(int L, int d, int H);
 
 }  // namespace bsa

@@ -37,6 +37,7 @@ struct AttnBwdKvParams {
     CUtensorMap pd, ds;           // [B*H*L, NK] fp32, box {32 keys, 32 queries}, 128-B swizzle
     CUtensorMap dout, q;          // [B*L, d] fp32, box {32 cols, 32 rows}, 32-B swizzle atom (MN-major B operands)
     float* dk; float* dv;
+    int ldo;                      // row pitch of dk / dv (d, or 3d when dq | dk | dv are one packed [B*L, 3d] tensor)
     int H, L, d;
     float scale;
 };
@@ -178,7 +179,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
         tc_fence_after();
         const int jkey = kt * 128 + quarter * 32 + lane;
         const float mul = half ? p.scale : 1.0f;
-        float* dst = (half ? p.dk : p.dv) + (seq_base + (jkey < p.L ? jkey : 0)) * p.d + col0;
+        float* dst = (half ? p.dk : p.dv) + (seq_base + (jkey < p.L ? jkey : 0)) * p.ldo + col0;
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
             float v[32];
@@ -202,7 +203,7 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
 }  // namespace
 
 int attn_bwd_kv_umma(const float* q, const float* dctx, const float* pd, const float* ds, float* dk, float* dv, int B, int H,
-                     int L, int d, cudaStream_t st) {
+                     int L, int d, cudaStream_t st, int ldo) {
     if (B == 0) return 0;
     static bool configured = false;
     if (!configured) {
@@ -219,7 +220,7 @@ int attn_bwd_kv_umma(const float* q, const float* dctx, const float* pd, const f
     if ((rc = make_tmap_2d(&p.ds, ds, grows, NK, NK, KV_QB, false))) return rc;
     if ((rc = make_tmap_2d(&p.dout, dctx, rows, d, d, KV_QB, true))) return rc;
     if ((rc = make_tmap_2d(&p.q, q, rows, d, d, KV_QB, true))) return rc;
-    p.dk = dk; p.dv = dv; p.H = H; p.L = L; p.d = d;
+    p.dk = dk; p.dv = dv; p.H = H; p.L = L; p.d = d; p.ldo = ldo ? ldo : d;
     p.scale = 1.0f / sqrtf((float)dh);
     const dim3 grid(B * H, (L + 127) / 128);
     if (dh == 64) attn_bwd_kv_umma_kernel<64><<<grid, KV_THREADS, KV_SMEM, st>>>(p);

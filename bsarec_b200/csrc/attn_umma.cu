@@ -334,6 +334,7 @@ struct AttnBwdQParams {
     const float* ctx; const float* dctx; const float* lse;
     float* dq; float* delta;
     float* pd_out; float* ds_out;      // optional [B*H*L, NK] fp32: Pd = P o M and dS, left for the key-owner kernel (attn_kv_umma.cu)
+    int ldo;                           // row pitch of dq (d, or 3d when dq | dk | dv are one packed [B*L, 3d] tensor)
     int H, L, d, NK;
     float scale;
     Dropout dr;
@@ -616,7 +617,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
         float v[16];
         tmem_ld16(t_o + lane_base + part * 16, v);                 // part -> dQ columns [16 part, 16 part + 16)
         if (row_ok) {
-            float* dst = p.dq + (seq_base + i) * p.d + col0 + part * 16;
+            float* dst = p.dq + (seq_base + i) * p.ldo + col0 + part * 16;
 #pragma unroll
             for (int e = 0; e < 4; ++e)
                 *reinterpret_cast<float4*>(dst + e * 4) =
@@ -670,7 +671,7 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
 
 int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,
                     const float* dctx, float* dq, float* delta, float* pd_out, float* ds_out, int B, int H, int L, int d,
-                    Dropout dr, cudaStream_t st) {
+                    Dropout dr, cudaStream_t st, int ldo) {
     BSA_REQUIRE(attn_umma_supported(L, d, H), "attn_bwd_q_umma: unsupported shape (L=%d d=%d H=%d)", L, d, H);
     if (B == 0) return 0;
     static bool configured = false;
@@ -691,6 +692,7 @@ int attn_bwd_q_umma(const float* q, const float* k, const float* v, const long l
     if ((rc = make_tmap_2d(&p.km, k, rows, d, d, 32, true))) return rc;
     p.ids = ids; p.ctx = ctx; p.dctx = dctx; p.lse = lse; p.dq = dq; p.delta = delta;
     p.pd_out = pd_out; p.ds_out = ds_out;
+    p.ldo = ldo ? ldo : d;
     p.H = H; p.L = L; p.d = d; p.NK = NK;
     p.scale = 1.0f / sqrtf((float)dh);
     p.dr = dr;

@@ -234,7 +234,7 @@ int linear_bwd_weight(const Lin& ln, const Act& dy, const Act& x, float* dW, flo
     if (p.splitk > 1) p.partial = part_sk;
     int rc = launch_gemm(p, st);
     if (rc) return rc;
-    return colsum(dy.x, M, N, part_cs, db, 0, st);
+    return db ? colsum(dy.x, M, N, part_cs, db, 0, st) : 0;
 }
 
 // the same with the tensor as its own hi half: only lo = x - truncate_tf32(x) is written (umma_split_lo)
@@ -467,9 +467,17 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     }
     if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, fuse_a ? nullptr : g.bo, M, d, d, part_sk, part_cs, st))) return rc;
     if ((rc = linear_bwd_input(lin, ag, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st, nullptr, wh(W_O), wl(W_O)))) return rc;
+    const bool qkv_pack_ok = lin.umma && qkv_fuse_enabled() && d % 32 == 0 && umma_split_colsum_rows(M) <= colsum_partial_rows(M) &&
+                             umma_split_colsum_ok(d, dq, dh_hi, dh_lo) && umma_split_colsum_ok(d, dk, dh_hi + d, dh_lo + d) &&
+                             umma_split_colsum_ok(d, dv, dh_hi + 2 * d, dh_lo + 2 * d);
+    bool pack32 = false;
     if (s.fused) {
         // dP (workspace, unused by this path) doubles as the [B,H,L] delta scratch
-        if ((rc = attn_bwd(s.q, s.k, s.v, ids, s.ctx, s.lse, dctx, dq, dk, dv, dP, B, H, L, d, dr_p, st))) return rc;
+        // pack32: the tcgen05 kernels write dq | dk | dv straight into ONE packed [M, 3d] fp32 tensor (the three contiguous
+        // [M, d] buffers seen with pitch 3d), which is then its own hi half for the packed dX / dW GEMMs below
+        pack32 = qkv_pack_ok && attn_bwd_strided_ok(L, d, H) && dk == dq + M * d && dv == dk + M * d;
+        if (pack32) { dk = dq + d; dv = dq + 2 * d; }
+        if ((rc = attn_bwd(s.q, s.k, s.v, ids, s.ctx, s.lse, dctx, dq, dk, dv, dP, B, H, L, d, dr_p, st, pack32 ? 3 * d : 0))) return rc;
     } else {
         const float* Pd = s.P;
         if (dr_p.thr) {
@@ -518,24 +526,23 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         // tcgen05 path: dq | dk | dv leave their split as ONE packed [M, 3d] pair (in the dead dh pair buffers), so the input
         // gradient is a single K = 3d GEMM against the [3d, d] weight pair instead of three accumulating launches that each
         // re-read and re-write dx; the three weight gradients read their column window of the packed pair.
-        const bool pack = lin.umma && qkv_fuse_enabled() && d % 32 == 0 && umma_split_colsum_ok(d, dq, dh_hi, dh_lo) &&
-                          umma_split_colsum_ok(d, dk, dh_hi + d, dh_lo + d) && umma_split_colsum_ok(d, dv, dh_hi + 2 * d, dh_lo + 2 * d) &&
-                          umma_split_colsum_rows(M) <= colsum_partial_rows(M);
+        const bool pack = qkv_pack_ok;
+        float* const g3_hi = pack32 ? dq : dh_hi;          // hi half of the packed pair: the packed fp32 tensor itself, or a copy
         const bool pack_dw = pack && ax.hi && umma_gemm_splits(3 * d, d, (int)M) > 1 &&
                              (size_t)umma_gemm_splits(3 * d, d, (int)M) * 3 * d * d * 4 <= lin.partial_bytes;
         if (pack) {
             for (int i = 0; i < 3; ++i) {
-                float *ph = dh_hi + (long long)i * d, *pl = dh_lo + (long long)i * d;
-                if ((rc = umma_split_colsum(grads3[i], ph, pl, M, d, part_qkv[i], st, 3 * d))) return rc;
+                float *ph = g3_hi + (long long)i * d, *pl = dh_lo + (long long)i * d;
+                if ((rc = umma_split_colsum(grads3[i], pack32 ? nullptr : ph, pl, M, d, part_qkv[i], st, 3 * d, pack32 ? 3 * d : 0))) return rc;
                 if ((rc = reduce_batch_add(rb, part_qkv[i], umma_split_colsum_rows(M), d, dbs3[i], nullptr, 1.f, 0, st))) return rc;
                 if (!pack_dw && (rc = linear_bwd_weight(lin, Act{grads3[i], ph, pl}, ax, dws3[i], nullptr, M, d, d, part_sk, part_cs, st, 3 * d))) return rc;
             }
             // [dWq; dWk; dWv] = [dq | dk | dv]^T x: one split-K GEMM over the packed pair (x's pair read once instead of three
             // times), its reduction writes the three [d, d] gradient tensors
-            if (pack_dw && (rc = umma_gemm_ps(3 * d, d, (int)M, dh_hi, dh_lo, M, 3 * d, 3 * d, true, ax.hi, ax.lo, M, d, d, true, g.wq, d,
+            if (pack_dw && (rc = umma_gemm_ps(3 * d, d, (int)M, g3_hi, dh_lo, M, 3 * d, 3 * d, true, ax.hi, ax.lo, M, d, d, true, g.wq, d,
                                               nullptr, 0, nullptr, nullptr, 1.f, 0, nullptr, nullptr, lin.partial, lin.partial_bytes, st,
                                               nullptr, 0, 0, nullptr, nullptr, d, g.wk, g.wv))) return rc;
-            if ((rc = umma_gemm_ps((int)M, d, 3 * d, dh_hi, dh_lo, M, 3 * d, 3 * d, false, s.w_hi, s.w_lo, 3 * d, d, d, true, dx, d,
+            if ((rc = umma_gemm_ps((int)M, d, 3 * d, g3_hi, dh_lo, M, 3 * d, 3 * d, false, s.w_hi, s.w_lo, 3 * d, d, d, true, dx, d,
                                    nullptr, ACT_NONE, nullptr, nullptr, 1.f, 1, nullptr, nullptr, nullptr, 0, st))) return rc;
         } else
         for (int i = 0; i < 3; ++i) {
@@ -597,7 +604,7 @@ int head_gemm(const float* A, int lda, bool a_k, long long sA, const float* Bm, 
 size_t last_workspace_bytes(const bsa_block_desc& c) {
     const long long B = c.B, d = c.d, H = c.H;
     Bump b(nullptr, ~(size_t)0);
-    for (int i = 0; i < 10; ++i) b.f(B * d);        // tmp, u, dsp | dyb, dd, dxl, dzf, dctx, dql, dlow/pb2/tmp
+    for (int i = 0; i < 13; ++i) b.f(B * d);        // tmp, u, dsp | dyb, dd, dxl, dzf, dctx, dql, dlow, pb2, tmp, dd_a, tmp2
     b.f(B * 4 * d);                                 // dh
     b.f(B * H * d); b.f(B * H * d); b.f(B * H); b.f(B * H);       // dxs, dgq, dsp, dcq
     for (int i = 0; i < 6; ++i) b.f((long long)rowwise_partial_blocks(B) * d);      // three LayerNorm sites x (gamma, beta) partials
@@ -686,6 +693,9 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     const long long Bd = (long long)B * d;
     float* dyb = b.f(Bd); float* dd = b.f(Bd); float* dxl = b.f(Bd); float* dzf = b.f(Bd); float* dctx = b.f(Bd);
     float* dql = b.f(Bd); float* dlow = b.f(Bd); float* pb2 = b.f(Bd); float* tmpbd = b.f(Bd);
+    // The six bias gradients are column sums of [B, .] tensors: each source keeps its own buffer (dd / dd_a always receive
+    // the pre-dropout gradient, tmpbd / tmpbd2) so that the sums join the one reduction launch at the end of the call.
+    float* dd_a = b.f(Bd); float* tmpbd2 = b.f(Bd);
     float* dh_ = b.f(Bd * 4);
     float* dxs = b.f(Bd * H); float* dgq = b.f(Bd * H); float* dsp = b.f((long long)B * H); float* dcq = b.f((long long)B * H);
     const int nrb = rowwise_partial_blocks(B);
@@ -707,29 +717,32 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     const Act axl{s.xl, nullptr, nullptr}, actx{s.ctx, nullptr, nullptr}, ay{s.y, nullptr, nullptr}, ah{s.h_act, nullptr, nullptr};
 
     // ---- feed-forward
-    if ((rc = ln_bwd(d_out_last, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dr_o.thr ? dd : nullptr, pgam, pbet, &nblk, B, d, dr_o, st))) return rc;
+    if ((rc = ln_bwd(d_out_last, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dd, pgam, pbet, &nblk, B, d, dr_o, st))) return rc;
     if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
-    const Act at2{dr_o.thr ? dd : dyb, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, at2, ah, g.w2, g.b2, B, d, 4 * d, part_sk, part_cs, st))) return rc;
+    const Act at2{dd, nullptr, nullptr};
+    if ((rc = linear_bwd_weight(lin, at2, ah, g.w2, nullptr, B, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = reduce_batch_add(rb, dd, B, d, g.b2, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, at2, w.w2, dh_, B, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, nullptr, nullptr, st))) return rc;
     const Act adh{dh_, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, B, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, B, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = reduce_batch_add(rb, dh_, B, 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, B, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
     // ---- attention branch: gsp = LN(drop(tmp) + xl), weight (1-alpha); dxl starts as the residual gradient
     pgam = lnp[1][0]; pbet = lnp[1][1];
-    if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dxl, dr_a.thr ? dd : nullptr, pgam, pbet, &nblk, B, d, dr_a, st))) return rc;
+    if ((rc = ln_bwd(dyb, 1.0f - c.alpha, s.z_a, s.mean_a, s.rstd_a, w.a_ln_w, dxl, dd_a, pgam, pbet, &nblk, B, d, dr_a, st))) return rc;
     if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
-    const Act at1{dr_a.thr ? dd : dxl, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, at1, actx, g.wo, g.bo, B, d, d, part_sk, part_cs, st))) return rc;
+    const Act at1{dd_a, nullptr, nullptr};
+    if ((rc = linear_bwd_weight(lin, at1, actx, g.wo, nullptr, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = reduce_batch_add(rb, dd_a, B, d, g.bo, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, at1, w.wo, dctx, B, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // ctx_h = Wv_h xs_h + bv_h sp_h
     //   dWv[h rows] = sum_b dctx_h^T xs_h   (M = dh, N = d, K = B per head)
     if ((rc = head_gemm(dctx, d, false, dh, s.xs, H * d, false, d, g.wv, d, (long long)dh * d, dh, d, B, H, st))) return rc;
     if ((rc = last_head_scale(tmpbd, dctx, s.sp, B, d, H, st))) return rc;
-    if ((rc = colsum(tmpbd, B, d, part_cs, g.bv, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, tmpbd, B, d, g.bv, nullptr, 1.f, 0, st))) return rc;
     //   dxs_h = Wv_h^T dctx_h  ;  dsp_h = bv_h . dctx_h
     if ((rc = head_gemm(dctx, d, true, dh, w.wv, d, false, (long long)dh * d, dxs, H * d, d, B, d, dh, H, st))) return rc;
     if ((rc = last_dsp(dctx, w.bv, dsp, B, d, H, st))) return rc;
@@ -748,11 +761,12 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     if ((rc = head_gemm(dgq, H * d, true, d, w.wk, d, true, (long long)dh * d, dql, d, dh, B, dh, d, H, st))) return rc;
     if ((rc = last_add_head_bias(dql, dcq, w.bk, B, d, H, st))) return rc;
     if ((rc = head_gemm(s.ql, d, false, dh, dgq, H * d, false, d, g.wk, d, (long long)dh * d, dh, d, B, H, st))) return rc;
-    if ((rc = last_head_scale(tmpbd, s.ql, dcq, B, d, H, st))) return rc;
-    if ((rc = colsum(tmpbd, B, d, part_cs, g.bk, 0, st))) return rc;
+    if ((rc = last_head_scale(tmpbd2, s.ql, dcq, B, d, H, st))) return rc;
+    if ((rc = reduce_batch_add(rb, tmpbd2, B, d, g.bk, nullptr, 1.f, 0, st))) return rc;
     // q = xl Wq^T + bq
     const Act adql{dql, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, adql, axl, g.wq, g.bq, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, adql, axl, g.wq, nullptr, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = reduce_batch_add(rb, dql, B, d, g.bq, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, adql, w.wq, dxl, B, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // value.bias / key.bias done; the row L-1 residual paths go into dx last
     if ((rc = last_add_rows(dx, dxl, B, L, d, st))) return rc;

@@ -150,8 +150,10 @@ static int embed_bwd_rows(const bsa_embed_desc* c, const int64_t* ids, const flo
     int nblk = 0, rc;
     if ((rc = embed_ln_dropout_bwd(d_out, (const long long*)ids, item_emb, pos_emb, ln_w, mean, rstd, dz, pg, pbt, &nblk,
                                    c->B, c->L, c->d, make_dropout(c->seed, 0, c->p_hidden, c->training), st))) return rc;
-    if ((rc = reduce_partials(pg, nblk, c->d, d_ln_w, nullptr, 1.f, 0, st))) return rc;
-    if ((rc = reduce_partials(pbt, nblk, c->d, d_ln_b, nullptr, 1.f, 0, st))) return rc;
+    ReduceBatch rb;                                   // both LayerNorm parameter gradients in one launch
+    if ((rc = reduce_batch_add(rb, pg, nblk, c->d, d_ln_w, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_add(rb, pbt, nblk, c->d, d_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((rc = reduce_batch_flush(rb, st))) return rc;
     return pos_grad(dz, d_pos_emb, c->B, c->L, c->d, 0, st);
 }
 

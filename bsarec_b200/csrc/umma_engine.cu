@@ -76,7 +76,7 @@ __global__ void split_tf32_multi_kernel(const __grid_constant__ SplitMultiP t) {
 constexpr int SPLIT_CS_ROWS = 128;
 __global__ void __launch_bounds__(256)
 split_colsum_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, long long M, int N,
-                    float* __restrict__ part, long long out_pitch4) {
+                    float* __restrict__ part, long long out_pitch4, long long in_pitch4) {
     __shared__ float4 red[256];
     const int tpr = N >> 2, groups = 256 / tpr;               // threads per row, rows in flight
     const int c4 = threadIdx.x % tpr, rg = threadIdx.x / tpr;
@@ -86,13 +86,21 @@ split_colsum_kernel(const float* __restrict__ x, float* __restrict__ hi, float* 
     for (int r = rg; r < SPLIT_CS_ROWS; r += groups) {
         const long long row = r0 + r;
         if (row >= M) break;
-        const long long i = row * tpr + c4;
-        const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
-        float4 h, l;
-        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
-        const long long o = row * out_pitch4 + c4;            // the pair may be a column window of a wider [M, pitch] buffer
-        reinterpret_cast<float4*>(hi)[o] = h;
-        reinterpret_cast<float4*>(lo)[o] = l;
+        const long long i = row * in_pitch4 + c4;             // x and the pair may be column windows of wider [M, pitch] buffers
+        const long long o = row * out_pitch4 + c4;
+        if (hi) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
+            float4 h, l;
+            split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+            reinterpret_cast<float4*>(hi)[o] = h;
+            reinterpret_cast<float4*>(lo)[o] = l;
+            cs.x += v.x; cs.y += v.y; cs.z += v.z; cs.w += v.w;
+            continue;
+        }
+        // hi == nullptr: x is its own hi half (it is read again by the GEMMs), only lo = x - truncate_tf32(x) is written
+        const float4 v = reinterpret_cast<const float4*>(x)[i];
+        auto lo1 = [](float t) { return t - __uint_as_float(__float_as_uint(t) & 0xFFFFE000u); };
+        reinterpret_cast<float4*>(lo)[o] = make_float4(lo1(v.x), lo1(v.y), lo1(v.z), lo1(v.w));
         cs.x += v.x; cs.y += v.y; cs.z += v.z; cs.w += v.w;
     }
     red[threadIdx.x] = cs;
@@ -649,12 +657,14 @@ bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* l
 }
 int umma_split_colsum_rows(long long M) { return (int)((M + SPLIT_CS_ROWS - 1) / SPLIT_CS_ROWS); }
 // part: [umma_split_colsum_rows(M), N]
-int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st, long long out_pitch) {
+int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st, long long out_pitch,
+                      long long in_pitch) {
     BSA_REQUIRE(umma_split_colsum_ok(N, x, hi, lo), "umma_split_colsum: unsupported width %d or alignment", N);
     if (out_pitch == 0) out_pitch = N;
-    BSA_REQUIRE(out_pitch >= N && (out_pitch & 3) == 0, "umma_split_colsum: bad output pitch %lld", out_pitch);
+    if (in_pitch == 0) in_pitch = N;
+    BSA_REQUIRE(out_pitch >= N && (out_pitch & 3) == 0 && in_pitch >= N && (in_pitch & 3) == 0, "umma_split_colsum: bad pitch");
     if (M == 0) return 0;
-    split_colsum_kernel<<<umma_split_colsum_rows(M), 256, 0, st>>>(x, hi, lo, M, N, part, out_pitch >> 2);
+    split_colsum_kernel<<<umma_split_colsum_rows(M), 256, 0, st>>>(x, hi, lo, M, N, part, out_pitch >> 2, in_pitch >> 2);
     BSA_LAUNCH_CHECK();
     return 0;
 }

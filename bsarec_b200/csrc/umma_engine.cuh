@@ -40,8 +40,10 @@ size_t umma_gemm_partial_bytes(int M, int N);
 // (reduce_partials turns them into the bias gradient of the linear whose output gradient x is).
 bool umma_split_colsum_ok(int N, const float* x, const float* hi, const float* lo);
 int umma_split_colsum_rows(long long M);
-// out_pitch (floats, 0 = N): hi / lo may point at a column window of a wider [M, out_pitch] pair buffer
-int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st, long long out_pitch = 0);
+// out_pitch / in_pitch (floats, 0 = N): the pair / x may be column windows of wider [M, pitch] buffers.  hi == nullptr: x is
+// its own hi half, only lo = x - truncate_tf32(x) is written (see umma_split_lo)
+int umma_split_colsum(const float* x, float* hi, float* lo, long long M, int N, float* part, cudaStream_t st, long long out_pitch = 0,
+                      long long in_pitch = 0);
 int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long long a_rows, long long a_cols,
                  long long lda, bool a_mn, const float* b_hi, const float* b_lo, long long b_rows, long long b_cols,
                  long long ldb, bool b_mn, float* C, long long ldc, const float* bias, int act, float* aux_out,

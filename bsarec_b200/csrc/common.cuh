@@ -136,15 +136,14 @@ __device__ __forceinline__ float warp_max(float v) {
 // FMAs give the value AND the derivative, because erfc's exp(-x^2/2) is also phi's.  erff + expf cost ~2x the instructions,
 // and the FFN epilogues of the tcgen05 GEMMs are bound by exactly that count.
 __device__ __forceinline__ float gelu_cdf(float x, float& e) {       // returns Phi(x); e = exp(-x^2 / 2)
-    const float u = fabsf(x) * 0.70710678118654752440f;
-    float t;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, u, 1.0f)));
+    float t;                                                         // 1 / (1 + p |x| / sqrt 2)
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.23164189f, fabsf(x), 1.0f)));
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170368f));      // -0.5 * log2(e)
-    float poly = fmaf(t, 1.061405429f, -1.453152027f);
-    poly = fmaf(t, poly, 1.421413741f);
-    poly = fmaf(t, poly, -0.284496736f);
-    poly = fmaf(t, poly, 0.254829592f);
-    const float q = 0.5f * (poly * t) * e;                           // 0.5 erfc(|x| / sqrt 2)
+    float poly = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);  // the 0.5 of erfc / 2 rides in the coefficients
+    poly = fmaf(t, poly, 0.5f * 1.421413741f);
+    poly = fmaf(t, poly, 0.5f * -0.284496736f);
+    poly = fmaf(t, poly, 0.5f * 0.254829592f);
+    const float q = (poly * t) * e;                                  // 0.5 erfc(|x| / sqrt 2)
     return x < 0.f ? q : 1.0f - q;
 }
 __device__ __forceinline__ float gelu_erf(float x) { float e; return x * gelu_cdf(x, e); }

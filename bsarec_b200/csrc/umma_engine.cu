@@ -131,7 +131,10 @@ struct StoreParams {
 };
 // PRE: the epilogue reads global memory (GELU pre-activation and / or the running sum) and prefetches those reads.
 // CS: it also leaves per-32-row-group column sums of what it stores (StoreParams::colpart).
-template <int BN, bool PRE = false, bool CS = false>
+// ACT >= 0: the activation is a compile-time constant and nothing accumulates (the two FFN GEMMs with an activation in the
+// epilogue get their own instantiations: the generic body carries all four activations inside its 8-fold unrolled store
+// loop, and ncu showed those launches stalled on branch resolution and instruction fetch — profiles/r3i_*)
+template <int BN, bool PRE = false, bool CS = false, int ACT = -1>
 struct EpiStore {
     using Params = StoreParams;
     static constexpr int WARPS = 8;
@@ -146,6 +149,8 @@ struct EpiStore {
         const long long row0 = (long long)tc.m * BM + quarter * 32;
         const int n0 = tc.n * BN;
         const int sub = lane >> 3, c4 = lane & 7;                // store phase: 4 rows x 8 float4 per instruction
+        const int act = ACT >= 0 ? ACT : p.act;
+        const bool accum = ACT >= 0 ? false : (p.accumulate != 0);
         float* base; long long ld; bool plain = p.partial == nullptr;
         if (plain) { base = p.C; ld = p.ldc; }
         else { base = p.partial + (long long)tc.split * g.M * g.N; ld = g.N; }
@@ -167,7 +172,7 @@ struct EpiStore {
             const int col = n0 + c0 + c4 * 4;
             const bool full = vec_ok && (col + 3 < g.N);
             float4 aux[8], old[8];
-            const bool pre_aux = PRE && plain && full && (p.act == 2 || p.act == 4), pre_old = PRE && plain && full && p.accumulate;
+            const bool pre_aux = PRE && plain && full && (act == 2 || act == 4), pre_old = PRE && plain && full && accum;
             if (pre_aux || pre_old) {
 #pragma unroll
                 for (int it = 0; it < 8; ++it) {
@@ -218,21 +223,21 @@ struct EpiStore {
                 }
                 x.x = p.alpha * x.x + bias4.x; x.y = p.alpha * x.y + bias4.y; x.z = p.alpha * x.z + bias4.z; x.w = p.alpha * x.w + bias4.w;
                 if (full) {
-                    if (p.act == 1) {
+                    if (act == 1) {
                         if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = x;
                         x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
-                    } else if (PRE && p.act == 2) {      // activations 2 - 4 are dispatched to the PRE instantiation only
+                    } else if (PRE && act == 2) {      // activations 2 - 4 are dispatched to the PRE instantiation only
                         const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= gelu_erf_grad(a.x); x.y *= gelu_erf_grad(a.y); x.z *= gelu_erf_grad(a.z); x.w *= gelu_erf_grad(a.w);
-                    } else if (PRE && p.act == 3) {
+                    } else if (PRE && act == 3) {
                         float4 gr;
                         x.x = gelu_erf_both(x.x, gr.x); x.y = gelu_erf_both(x.y, gr.y); x.z = gelu_erf_both(x.z, gr.z); x.w = gelu_erf_both(x.w, gr.w);
                         if (p.aux_out) *reinterpret_cast<float4*>(p.aux_out + off) = gr;
-                    } else if (PRE && p.act == 4) {
+                    } else if (PRE && act == 4) {
                         const float4 a = PRE ? aux[it] : *reinterpret_cast<const float4*>(p.aux_in + off);
                         x.x *= a.x; x.y *= a.y; x.z *= a.z; x.w *= a.w;
                     }
-                    if (p.accumulate) { const float4 o = PRE ? old[it] : *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
+                    if (accum) { const float4 o = PRE ? old[it] : *reinterpret_cast<const float4*>(base + off); x.x += o.x; x.y += o.y; x.z += o.z; x.w += o.w; }
                     if (want_cs) { csum.x += x.x; csum.y += x.y; csum.z += x.z; csum.w += x.w; }
                     if (base) *reinterpret_cast<float4*>(base + off) = x;      // C == nullptr: only the split pair leaves
                     if (p.out_hi) {
@@ -245,11 +250,11 @@ struct EpiStore {
                     float xs[4] = {x.x, x.y, x.z, x.w};
                     for (int e = 0; e < 4; ++e) if (col + e < g.N) {
                         float y = xs[e];
-                        if (p.act == 1) { if (p.aux_out) p.aux_out[off + e] = y; y = gelu_erf(y); }
-                        else if (PRE && p.act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
-                        else if (PRE && p.act == 3) { float gr; y = gelu_erf_both(y, gr); if (p.aux_out) p.aux_out[off + e] = gr; }
-                        else if (PRE && p.act == 4) y *= p.aux_in[off + e];
-                        if (p.accumulate) y += base[off + e];
+                        if (act == 1) { if (p.aux_out) p.aux_out[off + e] = y; y = gelu_erf(y); }
+                        else if (PRE && act == 2) y *= gelu_erf_grad(p.aux_in[off + e]);
+                        else if (PRE && act == 3) { float gr; y = gelu_erf_both(y, gr); if (p.aux_out) p.aux_out[off + e] = gr; }
+                        else if (PRE && act == 4) y *= p.aux_in[off + e];
+                        if (accum) y += base[off + e];
                         if (base) base[off + e] = y;
                         if (p.out_hi) { float h, l; split_tf32(y, h, l); p.out_hi[off + e] = h; p.out_lo[off + e] = l; }
                     }
@@ -722,7 +727,13 @@ int umma_gemm_ps(int M, int N, int K, const float* a_hi, const float* a_lo, long
     {
         ProfScope prof(PROF_LINEAR_UMMA, st, 2.0 * M * N * (double)K);
         const bool pre = act >= 2 || accumulate || colpart;
-        if (BN == 256) rc = colpart ? launch_major<256, 2, EpiStore<256, true, true>>(g, ep, a_mn, b_mn, grid, st)
+        if (BN == 256 && !a_mn && !b_mn && act == 3 && !accumulate && !colpart && !seg_cols)          // FFN d -> 4d, GELU
+            rc = launch<256, 2, false, false, EpiStore<256, true, false, 3>>(g, ep, grid, st);
+        else if (BN == 256 && !a_mn && !b_mn && act == 1 && !accumulate && !colpart && !seg_cols)     // the same in inference mode
+            rc = launch<256, 2, false, false, EpiStore<256, false, false, 1>>(g, ep, grid, st);
+        else if (BN == 256 && !a_mn && b_mn && act == 4 && !accumulate && colpart)                   // FFN dX 4d <- d, x GELU'
+            rc = launch<256, 2, false, true, EpiStore<256, true, true, 4>>(g, ep, grid, st);
+        else if (BN == 256) rc = colpart ? launch_major<256, 2, EpiStore<256, true, true>>(g, ep, a_mn, b_mn, grid, st)
                             : pre   ? launch_major<256, 2, EpiStore<256, true>>(g, ep, a_mn, b_mn, grid, st)
                                     : launch_major<256, 2, EpiStore<256>>(g, ep, a_mn, b_mn, grid, st);
         else rc = colpart ? launch_major<128, 3, EpiStore<128, true, true>>(g, ep, a_mn, b_mn, grid, st)

@@ -155,15 +155,14 @@ attn_bwd_kv_umma_kernel(const __grid_constant__ AttnBwdKvParams p) {
                 kv_split(v, hh, lw);
                 hi[u] = __float_as_uint(hh); lo[u] = __float_as_uint(lw);
             }
-            // dO and Q rows: raw fp32 -> hi in place, lo 16 KiB further (same swizzled positions); 16 KiB / 256 threads
+            // dO and Q rows: raw fp32 stays as hi, lo 16 KiB further (same swizzled positions); 16 KiB / 256 threads
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 unsigned char* ptr = st + KV_OFF_DO + k * 4096 + ct * 16;
                 const float4 x = *reinterpret_cast<const float4*>(ptr);
-                float4 hh, ll;
-                kv_split(x.x, hh.x, ll.x); kv_split(x.y, hh.y, ll.y); kv_split(x.z, hh.z, ll.z); kv_split(x.w, hh.w, ll.w);
-                *reinterpret_cast<float4*>(ptr) = hh;
-                *reinterpret_cast<float4*>(ptr + KV_OFF_LO) = ll;
+                // the raw words stay as the hi half (the MMA reads their upper 19 bits); lo = x - truncate_tf32(x)
+                auto lo1 = [](float t) { return t - __uint_as_float(__float_as_uint(t) & 0xFFFFE000u); };
+                *reinterpret_cast<float4*>(ptr + KV_OFF_LO) = make_float4(lo1(x.x), lo1(x.y), lo1(x.z), lo1(x.w));
             }
             fence_proxy_async_smem();
             const uint32_t tb = tmem_base + (uint32_t)(s * 128 + half * 64) + lane_base;

@@ -64,15 +64,13 @@ __device__ __forceinline__ void split_tf32_dev(float x, float& hi, float& lo) {
     lo = x - hi;
 }
 
-// raw fp32 region -> hi in place, lo at +lo_off (same swizzled positions)
+// raw fp32 region -> the raw words stay as the hi half (a tf32 MMA reads only their upper 19 bits), lo = x - truncate_tf32(x)
+// goes to +lo_off (same swizzled positions): one shared-memory store per element instead of two
+__device__ __forceinline__ float lo_trunc_dev(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 __device__ __forceinline__ void split_region(unsigned char* base, int bytes, int lo_off, int tid, int nthreads) {
     for (int o = tid * 16; o < bytes; o += nthreads * 16) {
         const float4 x = *reinterpret_cast<const float4*>(base + o);
-        float4 h, l;
-        split_tf32_dev(x.x, h.x, l.x); split_tf32_dev(x.y, h.y, l.y);
-        split_tf32_dev(x.z, h.z, l.z); split_tf32_dev(x.w, h.w, l.w);
-        *reinterpret_cast<float4*>(base + o) = h;
-        *reinterpret_cast<float4*>(base + o + lo_off) = l;
+        *reinterpret_cast<float4*>(base + o + lo_off) = make_float4(lo_trunc_dev(x.x), lo_trunc_dev(x.y), lo_trunc_dev(x.z), lo_trunc_dev(x.w));
     }
 }
 

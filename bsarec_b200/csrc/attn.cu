@@ -11,6 +11,7 @@
 // left padding) attends to ALL L keys.  Key tiles whose every pair is masked for rows that do have a permitted key
 // contribute exp(-10000 - max) == 0 exactly and are skipped.
 #include "attn.cuh"
+#include "umma_engine.cuh"
 #include <cstdlib>
 
 namespace bsa {
@@ -555,12 +556,13 @@ bool attn_fused_supported(int L, int d, int H) {
 }
 
 int attn_fwd(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
-             int L, int d, Dropout dr, cudaStream_t st) {
+             int L, int d, Dropout dr, cudaStream_t st, float* ctx_lo) {
     BSA_REQUIRE(attn_fused_supported(L, d, H), "attn_fwd: unsupported head size %d", H ? d / H : 0);
     if (B == 0) return 0;
-    if (g_attn_fwd_umma && attn_umma_supported(L, d, H)) return attn_fwd_umma(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
-    if (d / H == 64) return launch_fwd<64>(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
-    return launch_fwd<32>(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
+    if (g_attn_fwd_umma && attn_umma_supported(L, d, H)) return attn_fwd_umma(q, k, v, ids, ctx, lse, B, H, L, d, dr, st, ctx_lo);
+    const int rc = d / H == 64 ? launch_fwd<64>(q, k, v, ids, ctx, lse, B, H, L, d, dr, st) : launch_fwd<32>(q, k, v, ids, ctx, lse, B, H, L, d, dr, st);
+    if (rc || !ctx_lo) return rc;
+    return umma_split_lo(ctx, ctx_lo, (long long)B * L * d, st);       // the mma.sync kernel does not emit it
 }
 
 int attn_bwd(const float* q, const float* k, const float* v, const long long* ids, const float* ctx, const float* lse,

@@ -12,14 +12,15 @@ bool attn_fused_supported(int L, int d, int H);
 // q, k, v, ctx: [B*L, d] row-major, head h in columns [h*dh, (h+1)*dh).  lse: [B, H, L, 2] = (row max, log row sum) of the
 // masked, scaled scores of each query row, saved for the backward pass (kept apart: rows whose every key is masked
 // sit near -10000, where max + log sum would lose the low bits the softmax needs).
+// ctx_lo (optional): also leave ctx - truncate_tf32(ctx), the lo half of ctx as a tcgen05 A operand (ctx is its own hi half)
 int attn_fwd(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
-             int L, int d, Dropout dr, cudaStream_t st);
+             int L, int d, Dropout dr, cudaStream_t st, float* ctx_lo = nullptr);
 
 // The same forward on tcgen05 / TMEM (attn_umma.cu): head size 64 and L <= 208, i.e. the whole key axis in one accumulator.
 extern int g_attn_fwd_umma;      // 1 (default): use it where the shape allows; 0: always the mma.sync kernel
 bool attn_umma_supported(int L, int d, int H);
 int attn_fwd_umma(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
-                  int L, int d, Dropout dr, cudaStream_t st);
+                  int L, int d, Dropout dr, cudaStream_t st, float* ctx_lo = nullptr);
 
 // Query-owner half of the backward on tcgen05 (dQ and delta; same shapes as attn_fwd_umma).  g_attn_bwd_umma = 1 makes
 // attn_bwd use it and keep only the key-owner launch (dK, dV) on the mma.sync kernel.

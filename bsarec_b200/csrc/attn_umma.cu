@@ -52,6 +52,7 @@ struct AttnUmmaParams {
     CUtensorMap q, k, v;          // [B*L, d] fp32: box 32 x 128, box 32 x NK/2, box 32 x 32 (atom32)
     const long long* ids;
     float* ctx; float* lse;
+    float* ctx_lo;                // optional: ctx - truncate_tf32(ctx), the lo half of the output projection's A operand
     int H, L, d, NK;
     float scale;
     Dropout dr;
@@ -303,9 +304,13 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
         tmem_ld32(t_o + lane_base + half * 32, v);
         if (row_ok) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e)
-                *reinterpret_cast<float4*>(dst + e * 4) =
-                    make_float4(v[4 * e] * inv, v[4 * e + 1] * inv, v[4 * e + 2] * inv, v[4 * e + 3] * inv);
+            for (int e = 0; e < 8; ++e) {
+                const float4 o = make_float4(v[4 * e] * inv, v[4 * e + 1] * inv, v[4 * e + 2] * inv, v[4 * e + 3] * inv);
+                *reinterpret_cast<float4*>(dst + e * 4) = o;
+                if (p.ctx_lo)
+                    *reinterpret_cast<float4*>(p.ctx_lo + (dst - p.ctx) + e * 4) =
+                        make_float4(lo_trunc_dev(o.x), lo_trunc_dev(o.y), lo_trunc_dev(o.z), lo_trunc_dev(o.w));
+            }
             if (half == 0) *reinterpret_cast<float2*>(p.lse + 2 * ((long long)bh * p.L + i)) = make_float2(m, logf(l));
         }
     }
@@ -639,7 +644,7 @@ bool attn_umma_supported(int L, int d, int H) {
 }
 
 int attn_fwd_umma(const float* q, const float* k, const float* v, const long long* ids, float* ctx, float* lse, int B, int H,
-                  int L, int d, Dropout dr, cudaStream_t st) {
+                  int L, int d, Dropout dr, cudaStream_t st, float* ctx_lo) {
     BSA_REQUIRE(attn_umma_supported(L, d, H), "attn_fwd_umma: unsupported shape (L=%d d=%d H=%d)", L, d, H);
     if (B == 0) return 0;
     static bool configured = false;
@@ -657,6 +662,7 @@ int attn_fwd_umma(const float* q, const float* k, const float* v, const long lon
     if ((rc = make_tmap_2d(&p.k, k, rows, d, d, NK / 2, false))) return rc;
     if ((rc = make_tmap_2d(&p.v, v, rows, d, d, 32, true))) return rc;
     p.ids = ids; p.ctx = ctx; p.lse = lse; p.H = H; p.L = L; p.d = d; p.NK = NK;
+    p.ctx_lo = ctx_lo;
     p.scale = 1.0f / sqrtf((float)dh);
     p.dr = dr;
     const dim3 grid(B * H, (L + 127) / 128);

@@ -301,9 +301,9 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
                                   inf ? nullptr : s.rstd_f, nullptr, 0.f, 0.f, M, d, dr_f, st))) return rc;
     } else {
     if ((rc = filter_ln_fwd(x, basis, w.sqrt_beta, w.f_ln_w, w.f_ln_b, dsp, inf ? nullptr : s.z_f, inf ? nullptr : s.mean_f,
-                            inf ? nullptr : s.rstd_f, B, L, d, r, dr_f, st))) return rc;
-    // attention branch
-    if ((rc = split_act_lo(lin, x, s.x_lo, M * d, ax, st))) return rc;              // one split feeds q, k, v (and dW in backward)
+                            inf ? nullptr : s.rstd_f, B, L, d, r, dr_f, st, lin.umma ? s.x_lo : nullptr))) return rc;
+    // attention branch: x is its own hi half, its lo half was left by the filter kernel (which reads all of x anyway)
+    ax = Act{x, lin.umma ? x : nullptr, lin.umma ? s.x_lo : nullptr};
     if (lin.umma && qkv_fuse_enabled() && d % 32 == 0 && (s.k - s.q) == (s.v - s.k)) {
         if ((rc = linear_fwd_qkv(lin, ax, w, s.q, s.k - s.q, M, d, st, wh(W_Q), wl(W_Q)))) return rc;
     } else {
@@ -312,6 +312,8 @@ int block_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         if ((rc = linear_fwd(lin, ax, w.wv, w.bv, s.v, M, d, d, ACT_NONE, nullptr, nullptr, nullptr, st, wh(W_V), wl(W_V)))) return rc;
     }
     if (s.fused) {
+        // ctx's lo half comes from a split pass afterwards: letting the attention epilogue store it (attn_fwd's ctx_lo argument)
+        // costs that latency-bound kernel more (+0.054 ms at C3) than the pass it saves (0.034 ms) — profiles/r3n vs r3k
         if ((rc = attn_fwd(s.q, s.k, s.v, ids, s.ctx, s.lse, B, H, L, d, dr_p, st))) return rc;
     } else {
         {   // scores = q k^T / sqrt(dh)   -> written where P will live

@@ -688,10 +688,15 @@ int build_filter_basis(float* Cb, int L, int kept_bins, int* r_out, cudaStream_t
 
 int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta,
                   float* dsp, float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr,
-                  cudaStream_t st) {
+                  cudaStream_t st, float* x_lo) {
     if (B == 0) return 0;
-    ProfScope prof(PROF_FILTER_FWD, st, 4.0 * B * (double)L * d * (z_save ? 3.0 : 2.0));   // x read; z_save, dsp written
-    if (vec_ok(d, x, sqrt_beta, gamma, beta, dsp, z_save)) return filter_ln_fwd_vec(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, B, L, d, r, dr, st);
+    if (x_lo && !vec_ok(d, x, sqrt_beta, gamma, beta, dsp, z_save, x_lo)) {      // scalar kernel below: separate split pass
+        const int rc = umma_split_lo(x, x_lo, (long long)B * L * d, st);
+        if (rc) return rc;
+        x_lo = nullptr;
+    }
+    ProfScope prof(PROF_FILTER_FWD, st, 4.0 * B * (double)L * d * (z_save ? 3.0 : 2.0));   // x read; z_save, dsp written (x_lo not credited)
+    if (vec_ok(d, x, sqrt_beta, gamma, beta, dsp, z_save)) return filter_ln_fwd_vec(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, B, L, d, r, dr, st, x_lo);
     const size_t smem = (size_t)r * d * sizeof(float);
     BSA_REQUIRE(smem <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);
     BSA_DISPATCH_VPL(d, {

@@ -37,7 +37,8 @@ int ln_bwd_split(const float* dy, float dy_scale, const float* z, const float* m
 // ---- filter branch (bsarec.py:90-104) in its exact low-rank real form low = C (C^T x)
 int filter_ln_fwd(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta,
                   float* dsp, float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr,
-                  cudaStream_t st);
+                  cudaStream_t st, float* x_lo = nullptr);
+// x_lo (optional): the kernel also leaves x - truncate_tf32(x) — x is the A operand of the q / k / v projection that follows
 // dx += beta2*du + C C^T((1-beta2)*du), du = dz_f * dropout ; also dx += dz_f (residual) ;
 // pbeta2 [B][d] partial sums of du*(x-low)
 int filter_bwd(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2,
@@ -92,7 +93,8 @@ int ln_bwd_vec(const float* dy, float dy_scale, const float* z, const float* mea
                float* dz, float* ddrop, float* pgamma, float* pbeta, long long M, int d, Dropout dr, int grid, float* t_hi,
                float* t_lo, float* pcol, cudaStream_t st);
 int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta, float* dsp,
-                      float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st);
+                      float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st,
+                      float* x_lo = nullptr);
 int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* dz_f, float* dx, float* pbeta2, int B,
                    int L, int d, int r, Dropout dr, cudaStream_t st);
 // dst[b*L + (L-1)][:] = src[b][:], everything else 0

@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(FT)
 filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                          const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dsp,
                          float* __restrict__ z_save, float* __restrict__ mean_o, float* __restrict__ rstd_o, int L, int d,
-                         int r, int cb_smem, Dropout dr) {
+                         int r, int cb_smem, Dropout dr, float* __restrict__ x_lo) {
     extern __shared__ __align__(16) float fsm[];
     float* coef = fsm;                       // [r][d]
     float* par = coef + (long long)r * d;    // [3][d]: beta^2, LayerNorm weight, LayerNorm bias
@@ -368,6 +368,7 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
                 const float4 xv = ld4(src + t * d + cc);
                 const float4 u = low[i] + ld4(par + cc) * (xv - low[i]);
                 const long long o = row * d + cc;
+                if (x_lo) st4(x_lo + o, make_float4(lo_trunc(xv.x), lo_trunc(xv.y), lo_trunc(xv.z), lo_trunc(xv.w)));
                 v[i] = u * mult4(dr, (unsigned long long)o) + xv;
                 if (z_save) st4(z_save + o, v[i]);
             }
@@ -508,7 +509,7 @@ static int set_smem(K kernel, size_t smem) {
 constexpr size_t CB_SMEM_LIMIT = 16 * 1024;     // the basis [L][r] rides in shared memory when it is this small (C1-C3: 4 KB)
 
 int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, const float* gamma, const float* beta, float* dsp,
-                      float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st) {
+                      float* z_save, float* mean, float* rstd, int B, int L, int d, int r, Dropout dr, cudaStream_t st, float* x_lo) {
     const size_t cbb = (((size_t)L * r + 3) & ~(size_t)3) * sizeof(float);
     const int cb_smem = cbb <= CB_SMEM_LIMIT;
     const size_t coef = ((size_t)r * d + 3 * d) * sizeof(float) + (cb_smem ? cbb : 0), tile = (size_t)L * d * sizeof(float);
@@ -519,10 +520,10 @@ int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, c
     BSA_DISPATCH_NV(d, {
         if (stage) {
             if ((rc = set_smem(filter_ln_fwd_vec_kernel<NV, true>, smem))) return rc;
-            filter_ln_fwd_vec_kernel<NV, true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr);
+            filter_ln_fwd_vec_kernel<NV, true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr, x_lo);
         } else {
             if ((rc = set_smem(filter_ln_fwd_vec_kernel<NV, false>, smem))) return rc;
-            filter_ln_fwd_vec_kernel<NV, false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr);
+            filter_ln_fwd_vec_kernel<NV, false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr, x_lo);
         }
     });
     BSA_LAUNCH_CHECK();

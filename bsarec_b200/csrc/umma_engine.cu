@@ -1132,7 +1132,10 @@ int umma_score_topk(int B, int d, int k, long long rows, long long offset, const
     long long* cand_idx = (long long*)take((size_t)(nstrips + 1) * B * k * 8);
     int rc;
     if ((rc = do_split(s, s_hi, s_lo, (long long)B * d, st))) return rc;
-    if (!reuse_split && (rc = do_split(E, e_hi, e_lo, rows * d, st))) return rc;
+    if (e_trunc()) {          // the shard is its own hi half: only lo = E - truncate_tf32(E) is kept (the e_hi slot stays unused)
+        e_hi = const_cast<float*>(E);
+        if (!reuse_split && (rc = do_split_lo(E, e_lo, rows * d, st))) return rc;
+    } else if (!reuse_split && (rc = do_split(E, e_hi, e_lo, rows * d, st))) return rc;
     Operand oa{s_hi, s_lo, B, d, d, false}, ob{e_hi, e_lo, rows, d, d, false};
     GemmCore g;
     if ((rc = make_core(g, B, (int)rows, d, oa, ob, CE_BN, SCHED_STRIP, 1))) return rc;

@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(AT_THREADS)
 attn_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                 const long long* __restrict__ ids, float* __restrict__ ctx, float* __restrict__ lse, int H, int L, int d,
                 float scale, Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ __align__(16) unsigned char at_smem[];
     float* Ks = reinterpret_cast<float*>(at_smem);
     float* Vs = Ks + 2 * AT_BLK * DH;
@@ -298,6 +299,7 @@ attn_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const 
                 const float* __restrict__ dctx, float* __restrict__ out1, float* __restrict__ out2, float* __restrict__ delta,
                 int H, int L, int d, float scale, Dropout dr, float* __restrict__ pd_out = nullptr,
                 float* __restrict__ ds_out = nullptr, int NK = 0) {
+    dr = dropout_resolve(dr);
     extern __shared__ __align__(16) unsigned char at_smem[];
     float* Us = reinterpret_cast<float*>(at_smem);            // streamed operand of S:  K blocks (query owner) / Q blocks
     float* Ws = Us + 2 * AT_BLK * DH;                         // streamed operand of dP: V blocks (query owner) / dctx blocks

@@ -225,6 +225,7 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
     for (int q = 0; q < AUF_PARTS; ++q) m = fmaxf(m, xch[q * 128 + quarter * 32 + lane]);
     float l = 0.f;
     const bool fast_rng = (pbase & 3ull) == 0ull;
+    const Dropout drr = dropout_resolve(p.dr);                     // the site key, formed once per thread
 #pragma unroll 1
     for (int c = part; c < nch; c += AUF_PARTS) {                  // sweep 2: exp, sum, dropout, split, back into TMEM
         uint32_t hi[32], lo[32];
@@ -237,10 +238,10 @@ attn_fwd_umma_kernel(const __grid_constant__ AttnUmmaParams p) {
             for (int g4 = 0; g4 < 8; ++g4) {
                 float mult[4];
                 const int j0 = c * 32 + g4 * 4;
-                if (fast_rng) dropout_mult4(p.dr, pbase + j0, mult);
+                if (fast_rng) dropout_mult4(drr, pbase + j0, mult);
                 else {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(p.dr, pbase + j0 + e);
+                    for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(drr, pbase + j0 + e);
                 }
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
@@ -533,6 +534,7 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
     // ========================================================================= dS = P o (dPd o M - delta), back into TMEM
     const float delta = reinterpret_cast<const float*>(smem + AU_OFF_DELTA)[quarter * 32 + lane];
     const bool fast_rng = (pbase & 3ull) == 0ull;
+    const Dropout drr = dropout_resolve(p.dr);                     // the site key, formed once per thread
     float* pd_row = (p.pd_out && row_ok) ? p.pd_out + ((long long)bh * p.L + i) * NK : nullptr;
     float* ds_row = (p.ds_out && row_ok) ? p.ds_out + ((long long)bh * p.L + i) * NK : nullptr;
 #pragma unroll 1
@@ -548,10 +550,10 @@ attn_bwd_q_umma_kernel(const __grid_constant__ AttnBwdQParams p) {
             for (int g4 = 0; g4 < 4; ++g4) {
                 float mult[4];
                 const int j0 = c * 16 + g4 * 4;
-                if (fast_rng) dropout_mult4(p.dr, pbase + j0, mult);
+                if (fast_rng) dropout_mult4(drr, pbase + j0, mult);
                 else {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(p.dr, pbase + j0 + e);
+                    for (int e = 0; e < 4; ++e) mult[e] = dropout_mult(drr, pbase + j0 + e);
                 }
                 float pd4[4], ds4[4];
 #pragma unroll

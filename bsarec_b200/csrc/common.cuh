@@ -97,6 +97,13 @@ __device__ __forceinline__ unsigned long long dropout_key(const Dropout& dr) {
     return dr.epoch ? splitmix64(dr.pre + __ldg(dr.epoch)) : dr.key;
 }
 
+// Kernels call this once at entry: with a replay epoch the key is a second hash of a device word, and leaving that inside
+// dropout_mult* repeats it for every group of four elements (ncu, attention forward: 20 IMAD per mask hash instead of 8).
+__device__ __forceinline__ Dropout dropout_resolve(Dropout dr) {
+    if (dr.epoch) { dr.key = splitmix64(dr.pre + __ldg(dr.epoch)); dr.epoch = nullptr; }
+    return dr;
+}
+
 // multiplier (0 or scale) for linear element index i
 __device__ __forceinline__ float dropout_mult(const Dropout& dr, unsigned long long i) {
     if (dr.thr == 0u) return 1.0f;

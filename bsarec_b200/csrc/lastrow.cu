@@ -104,6 +104,7 @@ last_attn_fwd_kernel(const float* __restrict__ x, const long long* __restrict__ 
                      const float* __restrict__ ql, const float* __restrict__ bk, const float* __restrict__ Cb, int r,
                      float* __restrict__ p_out, float* __restrict__ xs, float* __restrict__ sp, float* __restrict__ low,
                      int H, int L, int d, float scale, Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ __align__(16) float lr_smem[];
     const LrSmem m = lr_carve(lr_smem, H, L, d, STAGE, false);
     float *sc = m.sc, *f = m.f, *vec = m.vec, *cq = m.small;
@@ -189,6 +190,7 @@ last_attn_bwd_kernel(const float* __restrict__ x, const float* __restrict__ p_in
                      const float* __restrict__ dxs, const float* __restrict__ dsp, const float* __restrict__ dlow,
                      const float* __restrict__ Cb, int r, float* __restrict__ dx, float* __restrict__ dgq,
                      float* __restrict__ dcq, int H, int L, int d, float scale, Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ __align__(16) float lr_smem[];
     const LrSmem m = lr_carve(lr_smem, H, L, d, STAGE, true);
     float *a = m.sc, *pdv = m.aux, *f = m.f, *vec = m.vec, *bias = m.small;
@@ -280,6 +282,7 @@ __global__ void last_ew_kernel(int op, float* __restrict__ out, float* __restric
                                const float* __restrict__ a, const float* __restrict__ b2, const float* __restrict__ c2,
                                const float* __restrict__ vcol, const float* __restrict__ shead, int B, int d, int H,
                                Dropout dr) {
+    dr = dropout_resolve(dr);
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)B * d) return;
     const int c = (int)(i % d);

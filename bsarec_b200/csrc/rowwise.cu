@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(WARPS * 32)
 embed_fwd_kernel(const long long* __restrict__ ids, const float* __restrict__ E, const float* __restrict__ Ppos,
                  const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
                  float* __restrict__ mean_o, float* __restrict__ rstd_o, long long M, int L, int d, Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
         const long long id = ids[row];
@@ -105,6 +106,7 @@ embed_bwd_kernel(const float* __restrict__ dout, const long long* __restrict__ i
                  const float* __restrict__ Ppos, const float* __restrict__ gamma, const float* __restrict__ mean_i,
                  const float* __restrict__ rstd_i, float* __restrict__ dz, float* __restrict__ pgamma,
                  float* __restrict__ pbeta, long long M, int L, int d, Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     float ag[VPL], ab[VPL];
 #pragma unroll
@@ -149,6 +151,7 @@ residual_ln_fwd_kernel(const float* __restrict__ tmp, const float* __restrict__ 
                        const float* __restrict__ beta, float* __restrict__ out, float* __restrict__ z_save,
                        float* __restrict__ mean_o, float* __restrict__ rstd_o, const float* __restrict__ blend_with,
                        float blend_a, float blend_b, long long M, int d, Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
         float v[VPL];
@@ -184,6 +187,7 @@ ln_bwd_kernel(const float* __restrict__ dy, float dy_scale, const float* __restr
               const float* __restrict__ rstd_i, const float* __restrict__ gamma, float* __restrict__ dz,
               float* __restrict__ ddrop, float* __restrict__ pgamma, float* __restrict__ pbeta, long long M, int d,
               Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     float ag[VPL], ab[VPL];
 #pragma unroll
@@ -256,6 +260,7 @@ filter_ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ Cb, 
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dsp,
                      float* __restrict__ z_save, float* __restrict__ mean_o, float* __restrict__ rstd_o, int L, int d,
                      int r, Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ float coef[];     // [r][d]
     const int b = blockIdx.x;
     const float* __restrict__ xb = x + (long long)b * L * d;
@@ -297,6 +302,7 @@ __global__ void __launch_bounds__(WARPS * 32)
 filter_bwd_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                   const float* __restrict__ dz_f, float* __restrict__ dx, float* __restrict__ pbeta2, int L, int d, int r,
                   Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ float sm[];       // coef_x [r][d], coef_g [r][d]
     float* coef_x = sm;
     float* coef_g = sm + (long long)r * d;
@@ -351,6 +357,7 @@ template <int VPL>
 __global__ void __launch_bounds__(WARPS * 32)
 softmax_fwd_kernel(const float* __restrict__ S, const long long* __restrict__ ids, float* __restrict__ P,
                    float* __restrict__ Pd, long long rows, int H, int L, Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < rows; row += (long long)gridDim.x * WARPS) {
         const int i = (int)(row % L);
@@ -394,6 +401,7 @@ softmax_fwd_kernel(const float* __restrict__ S, const long long* __restrict__ id
 template <int VPL>
 __global__ void __launch_bounds__(WARPS * 32)
 softmax_bwd_kernel(const float* __restrict__ P, float* __restrict__ G, long long rows, int L, Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < rows; row += (long long)gridDim.x * WARPS) {
         float p[VPL], dp[VPL];
@@ -419,6 +427,7 @@ softmax_bwd_kernel(const float* __restrict__ P, float* __restrict__ G, long long
 }
 
 __global__ void apply_dropout_kernel(const float* __restrict__ x, float* __restrict__ y, long long n, Dropout dr) {
+    dr = dropout_resolve(dr);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         y[i] = x[i] * dropout_mult(dr, (unsigned long long)i);
 }

@@ -90,6 +90,7 @@ __global__ void __launch_bounds__(WARPS * 32, NV <= 2 ? 4 : 2)
 embed_fwd_vec_kernel(const long long* __restrict__ ids, const float* __restrict__ E, const float* __restrict__ Ppos,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
                      float* __restrict__ mean_o, float* __restrict__ rstd_o, long long M, int L, int d, Dropout dr) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     const long long stride = (long long)gridDim.x * WARPS;
     long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5);
@@ -126,6 +127,7 @@ embed_bwd_vec_kernel(const float* __restrict__ dout, const long long* __restrict
                      const float* __restrict__ Ppos, const float* __restrict__ gamma, const float* __restrict__ mean_i,
                      const float* __restrict__ rstd_i, float* __restrict__ dz, float* __restrict__ pgamma,
                      float* __restrict__ pbeta, long long M, int L, int d, Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ float stage[];
     const int lane = threadIdx.x & 31;
     float4 ag[NV], ab[NV];
@@ -176,6 +178,7 @@ residual_ln_fwd_vec_kernel(const float* __restrict__ tmp, const float* __restric
                            float* __restrict__ mean_o, float* __restrict__ rstd_o, const float* __restrict__ blend_with,
                            float blend_a, float blend_b, long long M, int d, Dropout dr, float* __restrict__ y_hi,
                            float* __restrict__ y_lo) {
+    dr = dropout_resolve(dr);
     const int lane = threadIdx.x & 31;
     for (long long row = (long long)blockIdx.x * WARPS + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * WARPS) {
         float4 v[NV], bw[NV];
@@ -221,6 +224,7 @@ ln_bwd_vec_kernel(const float* __restrict__ dy, float dy_scale, const float* __r
                   const float* __restrict__ rstd_i, const float* __restrict__ gamma, float* __restrict__ dz,
                   float* __restrict__ ddrop, float* __restrict__ pgamma, float* __restrict__ pbeta, long long M, int d,
                   Dropout dr, float* __restrict__ t_hi, float* __restrict__ t_lo, float* __restrict__ pcol) {
+    dr = dropout_resolve(dr);
     extern __shared__ float stage[];
     const int lane = threadIdx.x & 31;
     float4 ag[NV], ab[NV], ac[NV];
@@ -311,6 +315,7 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
                          const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dsp,
                          float* __restrict__ z_save, float* __restrict__ mean_o, float* __restrict__ rstd_o, int L, int d,
                          int r, int cb_smem, Dropout dr, float* __restrict__ x_lo) {
+    dr = dropout_resolve(dr);
     extern __shared__ __align__(16) float fsm[];
     float* coef = fsm;                       // [r][d]
     float* par = coef + (long long)r * d;    // [3][d]: beta^2, LayerNorm weight, LayerNorm bias
@@ -391,6 +396,7 @@ __global__ void __launch_bounds__(FT)
 filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                       const float* __restrict__ dz_f, float* __restrict__ dx, float* __restrict__ pbeta2, int L, int d, int r,
                       int cb_smem, Dropout dr) {
+    dr = dropout_resolve(dr);
     extern __shared__ __align__(16) float fsm[];
     float* coef_x = fsm;                         // [r][d]
     float* coef_g = fsm + (long long)r * d;      // [r][d]

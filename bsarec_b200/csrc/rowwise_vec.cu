@@ -309,12 +309,33 @@ __device__ __forceinline__ void fold_groups(float* __restrict__ coef, const floa
     }
 }
 
+// The same fold in ONE barrier round when shared memory has room for every group's partials (scratch [G][min(r, RCH)][d]):
+// all groups store, then the thread of group q sums coefficient row q over the groups in the same fixed order (bit-identical
+// to the sequential fold).  Small tiles (C1: L = 50, d = 64 -> G = 32 groups) spent most of their time in the G barrier
+// rounds of the sequential version; at C3 the staged 205 KB tile leaves no room and the sequential fold stays.
+__device__ __forceinline__ void fold_groups_scratch(float* __restrict__ scratch, float* __restrict__ coef, const float4 (&acc)[RCH],
+                                                    int r0, int r, int d, int c, int g, int G, bool active) {
+    const int rr = min(r - r0, RCH);
+    if (active)
+#pragma unroll
+        for (int q = 0; q < RCH; ++q)
+            if (q < rr) st4(scratch + ((long long)g * rr + q) * d + c, acc[q]);
+    __syncthreads();
+    if (active)
+        for (int q = g; q < rr; q += G) {
+            float4 sum = ld4(scratch + (long long)q * d + c);
+            for (int gg = 1; gg < G; ++gg) sum = sum + ld4(scratch + ((long long)gg * rr + q) * d + c);
+            st4(coef + (long long)(r0 + q) * d + c, sum);
+        }
+    __syncthreads();
+}
+
 template <int NV, bool STAGE>
 __global__ void __launch_bounds__(FT)
 filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                          const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dsp,
                          float* __restrict__ z_save, float* __restrict__ mean_o, float* __restrict__ rstd_o, int L, int d,
-                         int r, int cb_smem, Dropout dr, float* __restrict__ x_lo) {
+                         int r, int cb_smem, Dropout dr, float* __restrict__ x_lo, int fold_off) {
     dr = dropout_resolve(dr);
     extern __shared__ __align__(16) float fsm[];
     float* coef = fsm;                       // [r][d]
@@ -348,7 +369,8 @@ filter_ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ 
                 for (int q = 0; q < RCH; ++q)
                     if (r0 + q < r) acc[q] = fma4(cb[t * r + r0 + q], xv, acc[q]);
             }
-        fold_groups(coef, acc, r0, r, d, c, g, G, active);
+        if (fold_off) fold_groups_scratch(fsm + fold_off, coef, acc, r0, r, d, c, g, G, active);
+        else fold_groups(coef, acc, r0, r, d, c, g, G, active);
     }
     // pass 2: warp per position
     const int lane = threadIdx.x & 31;
@@ -395,7 +417,7 @@ template <bool STAGE>
 __global__ void __launch_bounds__(FT)
 filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb, const float* __restrict__ sqrt_beta,
                       const float* __restrict__ dz_f, float* __restrict__ dx, float* __restrict__ pbeta2, int L, int d, int r,
-                      int cb_smem, Dropout dr) {
+                      int cb_smem, Dropout dr, int fold_off) {
     dr = dropout_resolve(dr);
     extern __shared__ __align__(16) float fsm[];
     float* coef_x = fsm;                         // [r][d]
@@ -437,8 +459,13 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
                         ag[q] = fma4(cq, gv, ag[q]);
                     }
             }
-        fold_groups(coef_x, ax, r0, r, d, c, g, G, active);
-        fold_groups(coef_g, ag, r0, r, d, c, g, G, active);
+        if (fold_off) {
+            fold_groups_scratch(fsm + fold_off, coef_x, ax, r0, r, d, c, g, G, active);
+            fold_groups_scratch(fsm + fold_off, coef_g, ag, r0, r, d, c, g, G, active);
+        } else {
+            fold_groups(coef_x, ax, r0, r, d, c, g, G, active);
+            fold_groups(coef_g, ag, r0, r, d, c, g, G, active);
+        }
     }
     float4 acc = f4(0.f);
     if (active)
@@ -455,7 +482,18 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
             acc = acc + du * (ld4(src + o) - low);
             st4(dxb + o, ld4(dxb + o) + dzf + b2 * du + fg);
         }
-    // fold the per-group dbeta2 partials, group after group
+    // fold the per-group dbeta2 partials, group after group (or through the scratch: same order, one barrier round)
+    if (fold_off) {
+        float* scratch = fsm + fold_off;
+        if (active) st4(scratch + (long long)g * d + c, acc);
+        __syncthreads();
+        if (active && g == 0) {
+            float4 sum = ld4(scratch + c);
+            for (int gg = 1; gg < G; ++gg) sum = sum + ld4(scratch + (long long)gg * d + c);
+            st4(pb + c, sum);
+        }
+        __syncthreads();
+    } else
     for (int gg = 0; gg < G; ++gg) {
         if (active && g == gg) st4(pb + c, gg == 0 ? acc : ld4(pb + c) + acc);
         __syncthreads();
@@ -463,6 +501,7 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
     for (int j = threadIdx.x; j < d; j += FT) pbeta2[(long long)b * d + j] = pb[j];
 }
 
+constexpr size_t FOLD_SMEM_LIMIT = 110 * 1024;      // with the fold scratch two CTAs still share an SM
 static const size_t STAGE_SMEM_LIMIT = [] { const char* e = getenv("BSA_FILTER_STAGE_KB"); return (size_t)(e ? atoi(e) : 220) * 1024; }();      // BSA_FILTER_STAGE_KB=0: never stage the tile (pass 2 re-reads through L2)
 
 }  // namespace
@@ -521,15 +560,19 @@ int filter_ln_fwd_vec(const float* x, const float* Cb, const float* sqrt_beta, c
     const size_t coef = ((size_t)r * d + 3 * d) * sizeof(float) + (cb_smem ? cbb : 0), tile = (size_t)L * d * sizeof(float);
     BSA_REQUIRE(coef <= 200 * 1024, "filter: basis rank %d x hidden %d does not fit shared memory", r, d);
     const bool stage = coef + tile <= STAGE_SMEM_LIMIT;
-    const size_t smem = coef + (stage ? tile : 0);
+    size_t smem = coef + (stage ? tile : 0);
+    // one-round fold of the projection partials when its scratch [G][min(r, RCH)][d] still fits (small tiles: C1, C2)
+    const size_t fold_bytes = (size_t)(FT / (d >> 2)) * (r < RCH ? r : RCH) * d * sizeof(float);
+    int fold_off = 0;
+    if (smem + fold_bytes <= FOLD_SMEM_LIMIT) { fold_off = (int)(smem / sizeof(float)); smem += fold_bytes; }
     int rc = 0;
     BSA_DISPATCH_NV(d, {
         if (stage) {
             if ((rc = set_smem(filter_ln_fwd_vec_kernel<NV, true>, smem))) return rc;
-            filter_ln_fwd_vec_kernel<NV, true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr, x_lo);
+            filter_ln_fwd_vec_kernel<NV, true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr, x_lo, fold_off);
         } else {
             if ((rc = set_smem(filter_ln_fwd_vec_kernel<NV, false>, smem))) return rc;
-            filter_ln_fwd_vec_kernel<NV, false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr, x_lo);
+            filter_ln_fwd_vec_kernel<NV, false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, gamma, beta, dsp, z_save, mean, rstd, L, d, r, cb_smem, dr, x_lo, fold_off);
         }
     });
     BSA_LAUNCH_CHECK();
@@ -543,14 +586,17 @@ int filter_bwd_vec(const float* x, const float* Cb, const float* sqrt_beta, cons
     const size_t coef = (2 * (size_t)r * d + d) * sizeof(float) + (cb_smem ? cbb : 0), tile = (size_t)L * d * sizeof(float);
     BSA_REQUIRE(coef <= 200 * 1024, "filter bwd: basis rank %d x hidden %d does not fit shared memory", r, d);
     const bool stage = coef + tile <= STAGE_SMEM_LIMIT;
-    const size_t smem = coef + (stage ? tile : 0);
+    size_t smem = coef + (stage ? tile : 0);
+    const size_t fold_bytes = (size_t)(FT / (d >> 2)) * (r < RCH ? r : RCH) * d * sizeof(float);
+    int fold_off = 0;
+    if (smem + fold_bytes <= FOLD_SMEM_LIMIT) { fold_off = (int)(smem / sizeof(float)); smem += fold_bytes; }
     int rc = 0;
     if (stage) {
         if ((rc = set_smem(filter_bwd_vec_kernel<true>, smem))) return rc;
-        filter_bwd_vec_kernel<true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, cb_smem, dr);
+        filter_bwd_vec_kernel<true><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, cb_smem, dr, fold_off);
     } else {
         if ((rc = set_smem(filter_bwd_vec_kernel<false>, smem))) return rc;
-        filter_bwd_vec_kernel<false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, cb_smem, dr);
+        filter_bwd_vec_kernel<false><<<B, FT, smem, st>>>(x, Cb, sqrt_beta, dz_f, dx, pbeta2, L, d, r, cb_smem, dr, fold_off);
     }
     BSA_LAUNCH_CHECK();
     return 0;

@@ -150,9 +150,14 @@ static int embed_bwd_rows(const bsa_embed_desc* c, const int64_t* ids, const flo
     int nblk = 0, rc;
     if ((rc = embed_ln_dropout_bwd(d_out, (const long long*)ids, item_emb, pos_emb, ln_w, mean, rstd, dz, pg, pbt, &nblk,
                                    c->B, c->L, c->d, make_dropout(c->seed, 0, c->p_hidden, c->training), st))) return rc;
-    ReduceBatch rb;                                   // both LayerNorm parameter gradients in one launch
+    // both LayerNorm parameter gradients and the position-table gradient (column sums of dz seen as [B, L*d]) in one launch
+    ReduceBatch rb;
     if ((rc = reduce_batch_add(rb, pg, nblk, c->d, d_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_batch_add(rb, pbt, nblk, c->d, d_ln_b, nullptr, 1.f, 0, st))) return rc;
+    if ((long long)c->L * c->d < (1ll << 30)) {
+        if ((rc = reduce_batch_add(rb, dz, c->B, c->L * c->d, d_pos_emb, nullptr, 1.f, 0, st))) return rc;
+        return reduce_batch_flush(rb, st);
+    }
     if ((rc = reduce_batch_flush(rb, st))) return rc;
     return pos_grad(dz, d_pos_emb, c->B, c->L, c->d, 0, st);
 }

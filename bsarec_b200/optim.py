@@ -16,7 +16,8 @@ from ._cabi import check
 
 
 class FusedAdam(torch.optim.Optimizer):
-    SMALL = 1 << 20      # tensors up to this many elements are updated together, one launch per 48 of them
+    SMALL = 1 << 18      # tensors up to this many elements are updated together, one launch per 48 of them (the grouped
+                         # launch gives every tensor at most 64 blocks: Beauty's 775 k-element item table took 18 us there)
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
         if lr < 0.0 or eps < 0.0 or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0 or weight_decay < 0.0:

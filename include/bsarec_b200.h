@@ -171,12 +171,16 @@ size_t bsa_block_saved_bytes(const bsa_block_desc* desc);      /* activations ke
 size_t bsa_block_workspace_bytes(const bsa_block_desc* desc);  /* scratch for fwd and bwd */
 
 /* x_out [B,L,d] = block(x_in); `saved` receives the activations backward needs (always required:
- * inference may reuse one buffer for all layers). */
+ * inference may reuse one buffer for all layers).  On the tcgen05 path `saved` also receives the split-TF32 pairs of the
+ * block's six weight matrices (one launch at the top of the forward pass) and the lo halves of x_in / ctx / y, whose hi
+ * halves are those fp32 tensors themselves: bsa_block_bwd multiplies by the weights the forward pass saw and must be given
+ * the same x_in. */
 int bsa_block_fwd(const bsa_block_desc* desc, const bsa_block_weights* w, const float* basis,
                   const int64_t* ids, const float* x_in, float* x_out, void* saved, void* workspace,
                   size_t workspace_bytes, void* stream);
 
-/* d_x_in [B,L,d] and every member of `g` are OVERWRITTEN with this block's gradients. */
+/* d_x_in [B,L,d] and every member of `g` are OVERWRITTEN with this block's gradients (the parameter gradients by one batched
+ * reduction launch at the end of the call). */
 int bsa_block_bwd(const bsa_block_desc* desc, const bsa_block_weights* w, const float* basis,
                   const int64_t* ids, const float* x_in, const void* saved, const float* d_x_out,
                   float* d_x_in, const bsa_block_grads* g, void* workspace, size_t workspace_bytes,

@@ -681,6 +681,57 @@ int block_last_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     return residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, out_last, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, B, d, dr_o, st);
 }
 
+// A second stream per device for the weight-gradient GEMMs of the small paths.  They are leaves of the backward pass (their
+// outputs are read by the optimizer only), so each one forks from the main stream where its inputs are complete and the call
+// joins the side stream before it returns: callers see ordinary single-stream semantics, CUDA-graph capture records the fork
+// and join as dependencies.  The [B, d]-sized launches of the last-row path leave most of the GPU idle; the weight gradients
+// now run beside the input-gradient chain instead of inside it.  BSA_SIDE_STREAM=0 keeps everything on the caller's stream.
+namespace {
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t fork[8] = {};
+    cudaEvent_t join = nullptr;
+    bool ok = false;
+};
+SideStream* side_stream_for_current_device() {
+    static const bool enabled = [] { const char* e = getenv("BSA_SIDE_STREAM"); return !(e && atoi(e) == 0); }();
+    if (!enabled) return nullptr;
+    static SideStream pool[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream& ss = pool[dev];
+    if (!ss.ok) {
+        if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (auto& e : ss.fork)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        ss.ok = true;
+    }
+    return &ss;
+}
+struct Fork {
+    cudaStream_t main; SideStream* ss; int used = 0;
+    Fork(cudaStream_t m, bool enable = true) : main(m), ss(enable ? side_stream_for_current_device() : nullptr) {}
+    ~Fork() {               // an error return between a fork and the join: still hand the side stream back to the main one
+        if (ss && used) { if (cudaEventRecord(ss->join, ss->s) == cudaSuccess) cudaStreamWaitEvent(main, ss->join, 0); }
+    }
+    // the stream for a leaf launch whose inputs are complete on the main stream NOW
+    cudaStream_t leaf() {
+        if (!ss || used >= 8) return main;
+        if (cudaEventRecord(ss->fork[used], main) != cudaSuccess || cudaStreamWaitEvent(ss->s, ss->fork[used], 0) != cudaSuccess) return main;
+        ++used;
+        return ss->s;
+    }
+    int join() {
+        if (!ss || used == 0) return 0;
+        BSA_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
+        BSA_CHECK_CUDA(cudaStreamWaitEvent(main, ss->join, 0));
+        used = 0;
+        return 0;
+    }
+};
+}  // namespace
+
 // d_out_last [B,d] = gradient wrt the block's output at position L-1.  dx [B,L,d] (every position) and all of `g`
 // are overwritten.
 int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* basis, const long long* ids,
@@ -717,17 +768,20 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     const int r = filter_rank(L, c.kept_bins);
     int rc, nblk = 0;
     const Act axl{s.xl, nullptr, nullptr}, actx{s.ctx, nullptr, nullptr}, ay{s.y, nullptr, nullptr}, ah{s.h_act, nullptr, nullptr};
+    // weight-gradient GEMMs (leaves) run on the side stream; they share part_sk, in launch order (the BSA_LAST_UMMA variant
+    // shares more scratch with the main chain and stays on one stream)
+    Fork fk(st, !lin.umma);
 
     // ---- feed-forward
     if ((rc = ln_bwd(d_out_last, 1.0f, s.z_o, s.mean_o, s.rstd_o, w.o_ln_w, dyb, dd, pgam, pbet, &nblk, B, d, dr_o, st))) return rc;
     if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.o_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.o_ln_b, nullptr, 1.f, 0, st))) return rc;
     const Act at2{dd, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, at2, ah, g.w2, nullptr, B, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, at2, ah, g.w2, nullptr, B, d, 4 * d, part_sk, part_cs, fk.leaf()))) return rc;
     if ((rc = reduce_batch_add(rb, dd, B, d, g.b2, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, at2, w.w2, dh_, B, d, 4 * d, 0, ACT_MUL_GELU_GRAD, s.h_pre, nullptr, nullptr, st))) return rc;
     const Act adh{dh_, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, B, 4 * d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, B, 4 * d, d, part_sk, part_cs, fk.leaf()))) return rc;
     if ((rc = reduce_batch_add(rb, dh_, B, 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, adh, w.w1, dyb, B, 4 * d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;   // dyb = dL/dy
 
@@ -737,12 +791,12 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     if ((rc = reduce_batch_add(rb, pgam, nblk, d, g.a_ln_w, nullptr, 1.f, 0, st))) return rc;
     if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.a_ln_b, nullptr, 1.f, 0, st))) return rc;
     const Act at1{dd_a, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, at1, actx, g.wo, nullptr, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, at1, actx, g.wo, nullptr, B, d, d, part_sk, part_cs, fk.leaf()))) return rc;
     if ((rc = reduce_batch_add(rb, dd_a, B, d, g.bo, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, at1, w.wo, dctx, B, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // ctx_h = Wv_h xs_h + bv_h sp_h
     //   dWv[h rows] = sum_b dctx_h^T xs_h   (M = dh, N = d, K = B per head)
-    if ((rc = head_gemm(dctx, d, false, dh, s.xs, H * d, false, d, g.wv, d, (long long)dh * d, dh, d, B, H, st))) return rc;
+    if ((rc = head_gemm(dctx, d, false, dh, s.xs, H * d, false, d, g.wv, d, (long long)dh * d, dh, d, B, H, fk.leaf()))) return rc;
     if ((rc = last_head_scale(tmpbd, dctx, s.sp, B, d, H, st))) return rc;
     if ((rc = reduce_batch_add(rb, tmpbd, B, d, g.bv, nullptr, 1.f, 0, st))) return rc;
     //   dxs_h = Wv_h^T dctx_h  ;  dsp_h = bv_h . dctx_h
@@ -762,17 +816,18 @@ int block_last_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     // gq_h = Wk_h^T q_h ; cq_h = q_h . bk_h
     if ((rc = head_gemm(dgq, H * d, true, d, w.wk, d, true, (long long)dh * d, dql, d, dh, B, dh, d, H, st))) return rc;
     if ((rc = last_add_head_bias(dql, dcq, w.bk, B, d, H, st))) return rc;
-    if ((rc = head_gemm(s.ql, d, false, dh, dgq, H * d, false, d, g.wk, d, (long long)dh * d, dh, d, B, H, st))) return rc;
+    if ((rc = head_gemm(s.ql, d, false, dh, dgq, H * d, false, d, g.wk, d, (long long)dh * d, dh, d, B, H, fk.leaf()))) return rc;
     if ((rc = last_head_scale(tmpbd2, s.ql, dcq, B, d, H, st))) return rc;
     if ((rc = reduce_batch_add(rb, tmpbd2, B, d, g.bk, nullptr, 1.f, 0, st))) return rc;
     // q = xl Wq^T + bq
     const Act adql{dql, nullptr, nullptr};
-    if ((rc = linear_bwd_weight(lin, adql, axl, g.wq, nullptr, B, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, adql, axl, g.wq, nullptr, B, d, d, part_sk, part_cs, fk.leaf()))) return rc;
     if ((rc = reduce_batch_add(rb, dql, B, d, g.bq, nullptr, 1.f, 0, st))) return rc;
     if ((rc = linear_bwd_input(lin, adql, w.wq, dxl, B, d, d, 1, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     // value.bias / key.bias done; the row L-1 residual paths go into dx last
     if ((rc = last_add_rows(dx, dxl, B, L, d, st))) return rc;
-    return reduce_batch_flush(rb, st);
+    if ((rc = reduce_batch_flush(rb, st))) return rc;
+    return fk.join();
 }
 
 size_t block_last_saved_bytes(const bsa_block_desc& c) { return carve_saved_last(nullptr, c).bytes + 256; }

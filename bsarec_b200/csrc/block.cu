@@ -253,6 +253,57 @@ int split_act(const Lin& ln, const float* x, float* hi, float* lo, long long n, 
 
 }  // namespace
 
+// A second stream per device for the weight-gradient GEMMs of the small paths.  They are leaves of the backward pass (their
+// outputs are read by the optimizer only), so each one forks from the main stream where its inputs are complete and the call
+// joins the side stream before it returns: callers see ordinary single-stream semantics, CUDA-graph capture records the fork
+// and join as dependencies.  The [B, d]-sized launches of the last-row path leave most of the GPU idle; the weight gradients
+// now run beside the input-gradient chain instead of inside it.  BSA_SIDE_STREAM=0 keeps everything on the caller's stream.
+namespace {
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t fork[8] = {};
+    cudaEvent_t join = nullptr;
+    bool ok = false;
+};
+SideStream* side_stream_for_current_device() {
+    static const bool enabled = [] { const char* e = getenv("BSA_SIDE_STREAM"); return !(e && atoi(e) == 0); }();
+    if (!enabled) return nullptr;
+    static SideStream pool[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream& ss = pool[dev];
+    if (!ss.ok) {
+        if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (auto& e : ss.fork)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        ss.ok = true;
+    }
+    return &ss;
+}
+struct Fork {
+    cudaStream_t main; SideStream* ss; int used = 0;
+    Fork(cudaStream_t m, bool enable = true) : main(m), ss(enable ? side_stream_for_current_device() : nullptr) {}
+    ~Fork() {               // an error return between a fork and the join: still hand the side stream back to the main one
+        if (ss && used) { if (cudaEventRecord(ss->join, ss->s) == cudaSuccess) cudaStreamWaitEvent(main, ss->join, 0); }
+    }
+    // the stream for a leaf launch whose inputs are complete on the main stream NOW
+    cudaStream_t leaf() {
+        if (!ss || used >= 8) return main;
+        if (cudaEventRecord(ss->fork[used], main) != cudaSuccess || cudaStreamWaitEvent(ss->s, ss->fork[used], 0) != cudaSuccess) return main;
+        ++used;
+        return ss->s;
+    }
+    int join() {
+        if (!ss || used == 0) return 0;
+        BSA_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
+        BSA_CHECK_CUDA(cudaStreamWaitEvent(main, ss->join, 0));
+        used = 0;
+        return 0;
+    }
+};
+}  // namespace
+
 int g_attn_impl = 2;        // 1 = unfused GEMM + softmax kernels, 2 = fused attention kernel where the head size allows
 int attn_impl() { return g_attn_impl == 2 && !g_attn_fwd_umma ? 3 : g_attn_impl; }
 void set_attn_impl(int impl) {        // 1 unfused | 2 fused, forward on tcgen05 where the shape allows | 3 fused, mma.sync only
@@ -403,6 +454,9 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     const int r = filter_rank(L, c.kept_bins);
     const float inv_sqrt_dh = 1.0f / sqrtf((float)dh);
     int rc, nblk = 0;
+    // Small problems (one wave of 128-row tiles or less, e.g. C1): each weight-gradient GEMM runs on the side stream beside
+    // the input-gradient GEMM that reads the same operands; the main stream joins before those operands are overwritten.
+    Fork fk(st, lin.umma && M <= 128ll * 148);
     // the weight pairs the forward pass left in the saved buffer (split_block_weights)
     const long long dsq = (long long)d * d;
     auto wh = [&](int slot) -> const float* { return lin.umma ? s.w_hi + slot * dsq : nullptr; };
@@ -425,14 +479,14 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         const float* t2 = dr_o.thr ? dd : dyb;                       // grad wrt dense_2 output
         if ((rc = split_act(lin, t2, g_hi, g_lo, M * d, ag, st))) return rc;     // one split feeds dW2 and dh
     }
-    if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, fuse_o ? nullptr : g.b2, M, d, 4 * d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, ag, ah, g.w2, fuse_o ? nullptr : g.b2, M, d, 4 * d, part_sk, part_cs, fuse_o ? fk.leaf() : st))) return rc;
     const Act adh{dh_, dh_hi, dh_lo};                                          // split pair emitted by the epilogue below
     if (lin.umma) {
         // dh leaves the GEMM only as its split pair (all dW1 / dX read) plus per-32-row column sums for db1: the fp32 copy
         // and the pass that summed it are gone; the [M,4d] dh_ buffer holds the [M/32, 4d] partial sums instead
         if ((rc = linear_bwd_input(lin, ag, w.w2, nullptr, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st, dh_, wh(W_2), wl(W_2)))) return rc;
         if ((rc = reduce_batch_add(rb, dh_, 4 * (int)((M + 127) / 128), 4 * d, g.b1, nullptr, 1.f, 0, st))) return rc;
-        if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, M, 4 * d, d, part_sk, part_cs, st))) return rc;
+        if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, nullptr, M, 4 * d, d, part_sk, part_cs, fk.leaf()))) return rc;
     } else {
         if ((rc = linear_bwd_input(lin, ag, w.w2, dh_, M, d, 4 * d, 0, ACT_MUL_AUX, s.h_pre, dh_hi, dh_lo, st))) return rc;
         if ((rc = linear_bwd_weight(lin, adh, ay, g.w1, g.b1, M, 4 * d, d, part_sk, part_cs, st))) return rc;
@@ -452,6 +506,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         return reduce_batch_flush(rb, st);
     }
     // ---- attention branch: gsp = LN(drop(tmp) + x), weight (1-alpha)
+    if ((rc = fk.join())) return rc;        // the next LayerNorm backward overwrites the gradient pair the side GEMMs read
     pgam = lnp[1][0]; pbet = lnp[1][1]; pcol = lnp[1][2];
     const bool fuse_a = lin.umma && ln_bwd_split_ok(d, dyb, s.z_a, w.a_ln_w, dx, nullptr, g_hi, g_lo);
     if (fuse_a) {
@@ -467,7 +522,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         const float* t1 = dr_a.thr ? dd : dx;                        // grad wrt dense output
         if ((rc = split_act(lin, t1, g_hi, g_lo, M * d, ag, st))) return rc;
     }
-    if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, fuse_a ? nullptr : g.bo, M, d, d, part_sk, part_cs, st))) return rc;
+    if ((rc = linear_bwd_weight(lin, ag, actx, g.wo, fuse_a ? nullptr : g.bo, M, d, d, part_sk, part_cs, fuse_a ? fk.leaf() : st))) return rc;
     if ((rc = linear_bwd_input(lin, ag, w.wo, dctx, M, d, d, 0, ACT_NONE, nullptr, nullptr, nullptr, st, nullptr, wh(W_O), wl(W_O)))) return rc;
     const bool qkv_pack_ok = lin.umma && qkv_fuse_enabled() && d % 32 == 0 && umma_split_colsum_rows(M) <= colsum_partial_rows(M) &&
                              umma_split_colsum_ok(d, dq, dh_hi, dh_lo) && umma_split_colsum_ok(d, dk, dh_hi + d, dh_lo + d) &&
@@ -528,6 +583,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
         // tcgen05 path: dq | dk | dv leave their split as ONE packed [M, 3d] pair (in the dead dh pair buffers), so the input
         // gradient is a single K = 3d GEMM against the [3d, d] weight pair instead of three accumulating launches that each
         // re-read and re-write dx; the three weight gradients read their column window of the packed pair.
+        if ((rc = fk.join())) return rc;    // dWo is done before the pair buffers are reused below
         const bool pack = qkv_pack_ok;
         float* const g3_hi = pack32 ? dq : dh_hi;          // hi half of the packed pair: the packed fp32 tensor itself, or a copy
         const bool pack_dw = pack && ax.hi && umma_gemm_splits(3 * d, d, (int)M) > 1 &&
@@ -542,7 +598,7 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
             // [dWq; dWk; dWv] = [dq | dk | dv]^T x: one split-K GEMM over the packed pair (x's pair read once instead of three
             // times), its reduction writes the three [d, d] gradient tensors
             if (pack_dw && (rc = umma_gemm_ps(3 * d, d, (int)M, g3_hi, dh_lo, M, 3 * d, 3 * d, true, ax.hi, ax.lo, M, d, d, true, g.wq, d,
-                                              nullptr, 0, nullptr, nullptr, 1.f, 0, nullptr, nullptr, lin.partial, lin.partial_bytes, st,
+                                              nullptr, 0, nullptr, nullptr, 1.f, 0, nullptr, nullptr, lin.partial, lin.partial_bytes, fk.leaf(),
                                               nullptr, 0, 0, nullptr, nullptr, d, g.wk, g.wv))) return rc;
             if ((rc = umma_gemm_ps((int)M, d, 3 * d, g3_hi, dh_lo, M, 3 * d, 3 * d, false, s.w_hi, s.w_lo, 3 * d, d, d, true, dx, d,
                                    nullptr, ACT_NONE, nullptr, nullptr, 1.f, 1, nullptr, nullptr, nullptr, 0, st))) return rc;
@@ -569,7 +625,8 @@ int block_bwd(const bsa_block_desc& c, const bsa_block_weights& w, const float* 
     if ((rc = reduce_batch_add(rb, pbet, nblk, d, g.f_ln_b, nullptr, 1.f, 0, st))) return rc;
     if ((rc = filter_bwd(x, basis, w.sqrt_beta, dzf, dx, pbeta2, B, L, d, r, dr_f, st))) return rc;
     if ((rc = reduce_batch_add(rb, pbeta2, B, d, g.sqrt_beta, w.sqrt_beta, 2.0f, 0, st))) return rc;
-    return reduce_batch_flush(rb, st);
+    if ((rc = reduce_batch_flush(rb, st))) return rc;
+    return fk.join();
 }
 
 // ================================================================================================ last block, last row
@@ -680,57 +737,6 @@ int block_last_fwd(const bsa_block_desc& c, const bsa_block_weights& w, const fl
     if ((rc = linear_fwd(lin, ah, w.w2, w.b2, tmp, B, d, 4 * d, ACT_NONE, nullptr, nullptr, nullptr, st))) return rc;
     return residual_ln_fwd(tmp, s.y, w.o_ln_w, w.o_ln_b, out_last, s.z_o, s.mean_o, s.rstd_o, nullptr, 0.f, 0.f, B, d, dr_o, st);
 }
-
-// A second stream per device for the weight-gradient GEMMs of the small paths.  They are leaves of the backward pass (their
-// outputs are read by the optimizer only), so each one forks from the main stream where its inputs are complete and the call
-// joins the side stream before it returns: callers see ordinary single-stream semantics, CUDA-graph capture records the fork
-// and join as dependencies.  The [B, d]-sized launches of the last-row path leave most of the GPU idle; the weight gradients
-// now run beside the input-gradient chain instead of inside it.  BSA_SIDE_STREAM=0 keeps everything on the caller's stream.
-namespace {
-struct SideStream {
-    cudaStream_t s = nullptr;
-    cudaEvent_t fork[8] = {};
-    cudaEvent_t join = nullptr;
-    bool ok = false;
-};
-SideStream* side_stream_for_current_device() {
-    static const bool enabled = [] { const char* e = getenv("BSA_SIDE_STREAM"); return !(e && atoi(e) == 0); }();
-    if (!enabled) return nullptr;
-    static SideStream pool[64];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    SideStream& ss = pool[dev];
-    if (!ss.ok) {
-        if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
-        for (auto& e : ss.fork)
-            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        if (cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        ss.ok = true;
-    }
-    return &ss;
-}
-struct Fork {
-    cudaStream_t main; SideStream* ss; int used = 0;
-    Fork(cudaStream_t m, bool enable = true) : main(m), ss(enable ? side_stream_for_current_device() : nullptr) {}
-    ~Fork() {               // an error return between a fork and the join: still hand the side stream back to the main one
-        if (ss && used) { if (cudaEventRecord(ss->join, ss->s) == cudaSuccess) cudaStreamWaitEvent(main, ss->join, 0); }
-    }
-    // the stream for a leaf launch whose inputs are complete on the main stream NOW
-    cudaStream_t leaf() {
-        if (!ss || used >= 8) return main;
-        if (cudaEventRecord(ss->fork[used], main) != cudaSuccess || cudaStreamWaitEvent(ss->s, ss->fork[used], 0) != cudaSuccess) return main;
-        ++used;
-        return ss->s;
-    }
-    int join() {
-        if (!ss || used == 0) return 0;
-        BSA_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
-        BSA_CHECK_CUDA(cudaStreamWaitEvent(main, ss->join, 0));
-        used = 0;
-        return 0;
-    }
-};
-}  // namespace
 
 // d_out_last [B,d] = gradient wrt the block's output at position L-1.  dx [B,L,d] (every position) and all of `g`
 // are overwritten.

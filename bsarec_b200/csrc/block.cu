@@ -253,57 +253,6 @@ int split_act(const Lin& ln, const float* x, float* hi, float* lo, long long n, 
 
 }  // namespace
 
-// A second stream per device for the weight-gradient GEMMs of the small paths.  They are leaves of the backward pass (their
-// outputs are read by the optimizer only), so each one forks from the main stream where its inputs are complete and the call
-// joins the side stream before it returns: callers see ordinary single-stream semantics, CUDA-graph capture records the fork
-// and join as dependencies.  The [B, d]-sized launches of the last-row path leave most of the GPU idle; the weight gradients
-// now run beside the input-gradient chain instead of inside it.  BSA_SIDE_STREAM=0 keeps everything on the caller's stream.
-namespace {
-struct SideStream {
-    cudaStream_t s = nullptr;
-    cudaEvent_t fork[8] = {};
-    cudaEvent_t join = nullptr;
-    bool ok = false;
-};
-SideStream* side_stream_for_current_device() {
-    static const bool enabled = [] { const char* e = getenv("BSA_SIDE_STREAM"); return !(e && atoi(e) == 0); }();
-    if (!enabled) return nullptr;
-    static SideStream pool[64];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    SideStream& ss = pool[dev];
-    if (!ss.ok) {
-        if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
-        for (auto& e : ss.fork)
-            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        if (cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        ss.ok = true;
-    }
-    return &ss;
-}
-struct Fork {
-    cudaStream_t main; SideStream* ss; int used = 0;
-    Fork(cudaStream_t m, bool enable = true) : main(m), ss(enable ? side_stream_for_current_device() : nullptr) {}
-    ~Fork() {               // an error return between a fork and the join: still hand the side stream back to the main one
-        if (ss && used) { if (cudaEventRecord(ss->join, ss->s) == cudaSuccess) cudaStreamWaitEvent(main, ss->join, 0); }
-    }
-    // the stream for a leaf launch whose inputs are complete on the main stream NOW
-    cudaStream_t leaf() {
-        if (!ss || used >= 8) return main;
-        if (cudaEventRecord(ss->fork[used], main) != cudaSuccess || cudaStreamWaitEvent(ss->s, ss->fork[used], 0) != cudaSuccess) return main;
-        ++used;
-        return ss->s;
-    }
-    int join() {
-        if (!ss || used == 0) return 0;
-        BSA_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
-        BSA_CHECK_CUDA(cudaStreamWaitEvent(main, ss->join, 0));
-        used = 0;
-        return 0;
-    }
-};
-}  // namespace
-
 int g_attn_impl = 2;        // 1 = unfused GEMM + softmax kernels, 2 = fused attention kernel where the head size allows
 int attn_impl() { return g_attn_impl == 2 && !g_attn_fwd_umma ? 3 : g_attn_impl; }
 void set_attn_impl(int impl) {        // 1 unfused | 2 fused, forward on tcgen05 where the shape allows | 3 fused, mma.sync only

@@ -175,11 +175,14 @@ int bsa_embed_ln_dropout_bwd(const bsa_embed_desc* c, const int64_t* ids, const 
     char* p = (char*)workspace;
     float* dz = (float*)p; p += al((size_t)M * c->d * sizeof(float));
     int rc;
-    if ((rc = embed_bwd_rows(c, ids, item_emb, pos_emb, ln_w, mean, rstd, d_out, dz, d_pos_emb, d_ln_w, d_ln_b, p, st))) return rc;
-    p += 2 * al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float));
-    void* plan = p;
+    // the scatter plan (key extraction + radix sort) depends on the ids only: it runs on the side stream beside the row kernel
+    // and its reductions, and the main stream joins before the scatter-add reads it
+    void* plan = p + 2 * al((size_t)rowwise_partial_blocks(M) * c->d * sizeof(float));
     const size_t plan_bytes = al(scatter_plan_bytes(M));
-    if ((rc = scatter_plan((const long long*)ids, M, c->item_size, plan, plan_bytes, st))) return rc;
+    Fork fk(st);
+    if ((rc = scatter_plan((const long long*)ids, M, c->item_size, plan, plan_bytes, fk.leaf()))) return rc;
+    if ((rc = embed_bwd_rows(c, ids, item_emb, pos_emb, ln_w, mean, rstd, d_out, dz, d_pos_emb, d_ln_w, d_ln_b, p, st))) return rc;
+    if ((rc = fk.join())) return rc;
     return scatter_add_rows(plan, M, dz, d_item_emb, c->d, st);
 }
 

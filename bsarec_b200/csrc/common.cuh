@@ -1,5 +1,6 @@
 // Shared device/host helpers for the bsarec_b200 kernels (sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -166,5 +167,54 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     const float cdf = gelu_cdf(x, e);
     return fmaf(x * 0.39894228040143267794f, e, cdf);
 }
+
+// A second stream per device for leaf launches (Fork): the weight-gradient GEMMs of the small paths, the scatter plan.  They are leaves of the backward pass (their
+// outputs are read by the optimizer only), so each one forks from the main stream where its inputs are complete and the call
+// joins the side stream before it returns: callers see ordinary single-stream semantics, CUDA-graph capture records the fork
+// and join as dependencies.  The [B, d]-sized launches of the last-row path leave most of the GPU idle; the weight gradients
+// now run beside the input-gradient chain instead of inside it.  BSA_SIDE_STREAM=0 keeps everything on the caller's stream.
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t fork[8] = {};
+    cudaEvent_t join = nullptr;
+    bool ok = false;
+};
+inline SideStream* side_stream_for_current_device() {
+    static const bool enabled = [] { const char* e = getenv("BSA_SIDE_STREAM"); return !(e && atoi(e) == 0); }();
+    if (!enabled) return nullptr;
+    static SideStream pool[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream& ss = pool[dev];
+    if (!ss.ok) {
+        if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (auto& e : ss.fork)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        ss.ok = true;
+    }
+    return &ss;
+}
+struct Fork {
+    cudaStream_t main; SideStream* ss; int used = 0;
+    Fork(cudaStream_t m, bool enable = true) : main(m), ss(enable ? side_stream_for_current_device() : nullptr) {}
+    ~Fork() {               // an error return between a fork and the join: still hand the side stream back to the main one
+        if (ss && used) { if (cudaEventRecord(ss->join, ss->s) == cudaSuccess) cudaStreamWaitEvent(main, ss->join, 0); }
+    }
+    // the stream for a leaf launch whose inputs are complete on the main stream NOW
+    cudaStream_t leaf() {
+        if (!ss || used >= 8) return main;
+        if (cudaEventRecord(ss->fork[used], main) != cudaSuccess || cudaStreamWaitEvent(ss->s, ss->fork[used], 0) != cudaSuccess) return main;
+        ++used;
+        return ss->s;
+    }
+    int join() {
+        if (!ss || used == 0) return 0;
+        BSA_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
+        BSA_CHECK_CUDA(cudaStreamWaitEvent(main, ss->join, 0));
+        used = 0;
+        return 0;
+    }
+};
 
 }  // namespace bsa

@@ -173,6 +173,8 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
 // joins the side stream before it returns: callers see ordinary single-stream semantics, CUDA-graph capture records the fork
 // and join as dependencies.  The [B, d]-sized launches of the last-row path leave most of the GPU idle; the weight gradients
 // now run beside the input-gradient chain instead of inside it.  BSA_SIDE_STREAM=0 keeps everything on the caller's stream.
+// One side stream and one set of events per device: like the rest of the library (one process per GPU, one host thread driving
+// it — trainers.py's loop), this is not meant for several host threads issuing backward calls on the same device at once.
 struct SideStream {
     cudaStream_t s = nullptr;
     cudaEvent_t fork[8] = {};

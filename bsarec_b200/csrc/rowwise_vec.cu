@@ -502,7 +502,10 @@ filter_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ Cb,
 }
 
 constexpr size_t FOLD_SMEM_LIMIT = 110 * 1024;      // with the fold scratch two CTAs still share an SM
-static const size_t STAGE_SMEM_LIMIT = [] { const char* e = getenv("BSA_FILTER_STAGE_KB"); return (size_t)(e ? atoi(e) : 220) * 1024; }();      // BSA_FILTER_STAGE_KB=0: never stage the tile (pass 2 re-reads through L2)
+static const size_t STAGE_SMEM_LIMIT = [] { const char* e = getenv("BSA_FILTER_STAGE_KB"); return (size_t)(e ? atoi(e) : 100) * 1024; }();
+// The tile is staged in shared memory only while two CTAs still fit an SM (<= 100 KB: C1, C2).  A 205 KB tile (C3) means one CTA
+// per SM whose load, projection and store phases cannot overlap anything; unstaged, four CTAs share the SM, pass 2 re-reads the
+// tile through L2, and the one-round fold's scratch fits (profiles/r2s_*, r4h_*).  BSA_FILTER_STAGE_KB=220 restores staging.
 
 }  // namespace
 
